@@ -1,0 +1,221 @@
+/* fugue_cuda.h -- C ABI of the B200-native inference backend for fugue.
+ *
+ * This is what a Rust `fugue-cuda` crate binds with `extern "C"`.
+ * Every entry point names the reference interface it replaces (paths relative to
+ * /root/reference). Plain C: pointers + sizes, int32 status codes, no exceptions.
+ *
+ * Layout conventions
+ *   q  : continuous site values, [d_cont][C] doubles, chain-minor (q[s*C + c]); site order is
+ *        the SORTED address order (BTreeMap<Address,_> iteration, src/inference/hmc.rs:238-248,
+ *        src/core/address.rs:150-157) as returned by fc_program_sites().
+ *   qd : discrete site values, [d_disc][C] int64, same conventions.
+ *   Pointers named h_* are HOST memory, d_* are DEVICE memory. Functions without a suffix
+ *   take host buffers and copy (the reference-facing path); *_dev variants take device pointers.
+ */
+#ifndef FUGUE_CUDA_H
+#define FUGUE_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes: numerically equal to ErrorCode (src/error.rs:40-58) ---- */
+enum {
+  FC_OK = 0,
+  FC_ERR_INVALID_MEAN = 100, FC_ERR_INVALID_VARIANCE = 101, FC_ERR_INVALID_PROBABILITY = 102,
+  FC_ERR_INVALID_RANGE = 103, FC_ERR_INVALID_SHAPE = 104, FC_ERR_INVALID_RATE = 105,
+  FC_ERR_INVALID_COUNT = 106,
+  FC_ERR_ADDRESS_CONFLICT = 301,            /* src/runtime/interpreters.rs:23-45 */
+  FC_ERR_UNEXPECTED_MODEL_STRUCTURE = 302,  /* src/runtime/interpreters.rs:667-679 */
+  FC_ERR_TRACE_ADDRESS_NOT_FOUND = 500,
+  FC_ERR_TYPE_MISMATCH = 600,
+  FC_ERR_UNSUPPORTED_OP = 1000, FC_ERR_CUDA = 1001, FC_ERR_NCCL = 1002, FC_ERR_INVALID_ARGUMENT = 1003
+};
+
+/* ---- distribution ids: order of src/core/distribution.rs:125-1936 ---- */
+enum {
+  FC_NORMAL = 0, FC_UNIFORM = 1, FC_LOGNORMAL = 2, FC_EXPONENTIAL = 3, FC_BERNOULLI = 4,
+  FC_CATEGORICAL = 5, FC_BETA = 6, FC_GAMMA = 7, FC_BINOMIAL = 8, FC_POISSON = 9,
+  FC_STUDENT_T = 10, FC_CAUCHY = 11, FC_LAPLACE = 12, FC_WEIBULL = 13, FC_CHI_SQUARED = 14,
+  FC_INVERSE_GAMMA = 15, FC_DISCRETE_UNIFORM = 16, FC_N_DISTS = 17
+};
+
+/* ---- op kinds (Model variants: src/core/model.rs:20-131; plate!: src/macros/mod.rs:82-86) ---- */
+enum { FC_OP_SAMPLE = 0, FC_OP_OBSERVE = 1, FC_OP_FACTOR = 2, FC_OP_PLATE_SAMPLE = 3, FC_OP_PLATE_OBSERVE = 4 };
+
+/* ---- value types (ChoiceValue: src/runtime/trace.rs:32-47) ---- */
+enum { FC_T_F64 = 0, FC_T_I64 = 1, FC_T_U64 = 2, FC_T_USIZE = 3, FC_T_BOOL = 4 };
+
+/* ---- parameter expressions: value = link(term0 + term1 + term2), evaluated left to right ---- */
+enum {
+  FC_TERM_NONE = 0,
+  FC_TERM_CONST = 1,      /* c                                                            */
+  FC_TERM_LATENT = 2,     /* q[slot]                                                      */
+  FC_TERM_LATENT_X = 3,   /* q[slot] * col[i]               (col: f64 vector column)      */
+  FC_TERM_DENSE = 4,      /* sum_k q[slot+k]*X[i][k], k=0..K-1 left-to-right from 0.0     */
+                          /*   (col: f64 row-major matrix column, K = its width)          */
+  FC_TERM_GATHER = 5,     /* q[slot + idx[i]]               (col: index column)           */
+  FC_TERM_SELECT2 = 6,    /* z==0 ? q[slot] : q[slot_b]     z = plate-discrete site i of  */
+                          /*   PLATE_SAMPLE op `col` (an op index, not a column)          */
+  FC_TERM_PLATE_LATENT = 7/* q[slot + i]  (element i of a continuous plate)               */
+};
+enum { FC_LINK_IDENTITY = 0, FC_LINK_EXP = 1, FC_LINK_SIGMOID_CLAMPED = 2, FC_LINK_CLAMP = 3 };
+
+typedef struct fc_term {
+  int32_t kind;
+  int32_t slot;    /* PROGRAM-order continuous slot index (see fc_program_create) */
+  int32_t slot_b;
+  int32_t col;
+  double  c;
+} fc_term;
+
+typedef struct fc_param {
+  fc_term term[3];
+  int32_t link;
+  int32_t _pad;
+  double  lo, hi;  /* SIGMOID_CLAMPED / CLAMP bounds (examples/classification.rs:127,
+                      examples/mixture_models.rs:93) */
+} fc_param;
+
+typedef struct fc_op {
+  int32_t kind;        /* FC_OP_*                                                     */
+  int32_t dist;        /* FC_NORMAL.. ; ignored for FACTOR                            */
+  int32_t value_type;  /* FC_T_*                                                      */
+  int32_t n_params;    /* 1..3 (Categorical: params = probs of category 0; 2-way)     */
+  const char* name;    /* address base; scalar ops use addr!(name), plates addr!(name,i)
+                          => "name#i" (src/core/address.rs:208-223)                   */
+  int64_t plate_len;   /* PLATE_*: number of elements; else 0                         */
+  int32_t value_col;   /* OBSERVE/PLATE_OBSERVE: data column holding the value(s)     */
+  int32_t _pad;
+  double  value;       /* OBSERVE (scalar): observed value; FACTOR: log-weight        */
+  fc_param param[3];
+} fc_op;
+
+/* ---- data columns ---- */
+enum { FC_COL_F64 = 0, FC_COL_U8 = 1, FC_COL_U32 = 2, FC_COL_I64 = 3 };
+typedef struct fc_column {
+  int32_t dtype;      /* FC_COL_*                               */
+  int32_t width;      /* 1 = vector; K = row-major [rows][K]    */
+  int64_t rows;
+  const void* data;   /* host pointer; copied at create         */
+} fc_column;
+
+typedef struct fc_program fc_program;
+
+/* ---- library ---- */
+const char* fc_last_error(void);
+int32_t fc_device_count(int32_t* out);
+int32_t fc_set_device(int32_t device);
+
+/* ---- program (replaces: run(handler, model_fn()) lowering; src/runtime/handler.rs:124-209) ----
+ * Ops are in PROGRAM order. Continuous program slots are numbered in program order, a
+ * PLATE_SAMPLE of f64 occupying plate_len consecutive slots. Duplicate addresses ->
+ * FC_ERR_ADDRESS_CONFLICT. Columns are copied to the current device. */
+int32_t fc_program_create(const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols,
+                          fc_program** out);
+int32_t fc_program_destroy(fc_program* p);
+/* Checks a second trace of the same model against the program (address sequence, kinds, types);
+ * mismatch -> FC_ERR_UNEXPECTED_MODEL_STRUCTURE (src/runtime/interpreters.rs:271-283). */
+int32_t fc_program_check_structure(const fc_program* p, const fc_op* ops, size_t n_ops);
+int32_t fc_program_dims(const fc_program* p, int64_t* d_cont, int64_t* d_disc);
+/* Sorted site names (BTreeMap order) of the continuous sites; pointers owned by the program.
+ * perm[i] = program-order slot of sorted site i. */
+int32_t fc_program_sites(const fc_program* p, const char* const** names, const int64_t** perm,
+                         int64_t* n);
+/* cudaStream_t the program launches on (for CUDA-event timing by the caller). */
+int32_t fc_program_stream(const fc_program* p, void** stream);
+
+/* ---- scoring: replaces run(ScoreGivenTrace{base}, model) (src/runtime/interpreters.rs:138-163,
+ * src/inference/hmc.rs:264-299). Three accumulators as in Trace (src/runtime/trace.rs:168-177). */
+int32_t fc_logp(fc_program* p, const double* h_q, const int64_t* h_qd, size_t C,
+                double* h_log_prior, double* h_log_lik, double* h_log_factors);
+/* value + analytic gradient (replaces grad_log_joint, src/inference/hmc.rs:304-329);
+ * h_grad is [d_cont][C]. */
+int32_t fc_logp_grad(fc_program* p, const double* h_q, const int64_t* h_qd, size_t C,
+                     double* h_lp, double* h_grad);
+int32_t fc_logp_grad_dev(fc_program* p, const double* d_q, const int64_t* d_qd, size_t C,
+                         double* d_lp, double* d_grad);
+
+/* ---- HMC (src/inference/hmc.rs) ---- */
+typedef struct fc_hmc_config {   /* HMCConfig, hmc.rs:105-135 */
+  uint64_t n_leapfrog;           /* 16    */
+  double   target_accept;        /* 0.8   */
+  double   init_step_size;       /* NaN = None */
+  double   finite_diff_eps;      /* 1e-5 (used only by grad_mode = 1) */
+  int32_t  adapt_mass;           /* false */
+  int32_t  grad_mode;            /* 0 = analytic (device), 1 = central finite differences */
+} fc_hmc_config;
+typedef struct fc_hmc_stats {
+  uint64_t n_accept, n_divergent;
+  double   step_size;            /* current (warmup) or frozen step size */
+} fc_hmc_stats;
+typedef struct fc_hmc_session fc_hmc_session;
+
+void    fc_hmc_config_default(fc_hmc_config* cfg);
+/* HmcSession::new (hmc.rs:667): prior init (or h_q0 if non-NULL), find_reasonable_epsilon. */
+int32_t fc_hmc_create(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
+                      size_t n_warmup, const double* h_q0, const int64_t* h_qd0,
+                      fc_hmc_session** out);
+int32_t fc_hmc_destroy(fc_hmc_session* s);
+/* HmcSession::step / advance (hmc.rs:819-919): n transitions for all C chains, device resident. */
+int32_t fc_hmc_step(fc_hmc_session* s, size_t n);
+/* HmcSession::position / trace (hmc.rs:700-760): copy state to host. Any pointer may be NULL. */
+int32_t fc_hmc_get(fc_hmc_session* s, double* h_q, double* h_lp, fc_hmc_stats* h_stats);
+int32_t fc_hmc_set_position(fc_hmc_session* s, const double* h_q);
+int32_t fc_hmc_set_step_size(fc_hmc_session* s, double eps);      /* hmc.rs:792 */
+int32_t fc_hmc_set_n_leapfrog(fc_hmc_session* s, uint64_t l);     /* hmc.rs:803 */
+int32_t fc_hmc_grad_evals(const fc_hmc_session* s, uint64_t* per_chain);
+/* hmc_chain (hmc.rs:566-583): warmup then n_samples draws; h_draws [n_samples][d][C]. */
+int32_t fc_hmc_run(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
+                   size_t n_warmup, size_t n_samples, double* h_draws, double* h_lp,
+                   fc_hmc_stats* h_stats);
+
+/* ---- single-site MH (src/inference/mh.rs:698-744, 921-1014) ---- */
+typedef struct fc_mh_config {
+  double target_accept;   /* 0.44 (mh.rs:946) */
+  double gamma;           /* 0.7               */
+} fc_mh_config;
+typedef struct fc_mh_stats { uint64_t n_accept; uint64_t n_steps; } fc_mh_stats;
+void    fc_mh_config_default(fc_mh_config* cfg);
+int32_t fc_mh_run(fc_program* p, const fc_mh_config* cfg, uint64_t seed, size_t C,
+                  size_t n_warmup, size_t n_samples, size_t thin, double* h_draws, double* h_lp,
+                  fc_mh_stats* h_stats);
+
+/* ---- SMC (src/inference/smc.rs) ---- */
+enum { FC_RESAMPLE_MULTINOMIAL = 0, FC_RESAMPLE_SYSTEMATIC = 1, FC_RESAMPLE_STRATIFIED = 2 };
+typedef struct fc_smc_config {  /* SMCConfig, smc.rs:172-189 */
+  int32_t  resampling_method;   /* Systematic */
+  int32_t  _pad;
+  double   ess_threshold;       /* 0.5 */
+  uint64_t rejuvenation_steps;  /* 0   */
+} fc_smc_config;
+void    fc_smc_config_default(fc_smc_config* cfg);
+/* adaptive_smc (smc.rs:455-581). h_values [d_cont][P], h_dvalues [d_disc][P]; outputs may be NULL.
+ * n_temper_steps returns the number of tempering steps taken. */
+int32_t fc_smc_run(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t P,
+                   double* h_values, int64_t* h_dvalues, double* h_weight, double* h_log_weight,
+                   double* log_evidence, uint64_t* n_temper_steps);
+/* systematic/stratified/multinomial_indices (smc.rs:255-314) with the uniforms passed explicitly:
+ * 1 uniform for systematic (the raw rng.gen::<f64>(), before /n), n for the others. */
+int32_t fc_resample(int32_t method, const double* h_w, size_t n, const double* h_uniforms,
+                    uint64_t* h_idx);
+int32_t fc_resample_dev(int32_t method, const double* d_w, size_t n, const double* d_uniforms,
+                        uint64_t* d_idx, void* stream);
+int32_t fc_log_sum_exp(const double* h_x, size_t n, double* out);        /* numerical.rs:15-38 */
+int32_t fc_ess(const double* h_w, size_t n, double* out);                /* smc.rs:230-233     */
+int32_t fc_normalize_log_probs(const double* h_x, size_t n, double* h_out); /* numerical.rs:87-90 */
+
+/* ---- diagnostics (src/inference/diagnostics.rs:218-304, src/inference/mcmc_utils.rs:195-339).
+ * h_draws is [S][C] for one parameter (draw-major, chain-minor). ---- */
+int32_t fc_split_rhat(const double* h_draws, size_t S, size_t C, double* out);
+int32_t fc_classic_rhat(const double* h_draws, size_t S, size_t C, double* out);
+int32_t fc_ess_multichain(const double* h_draws, size_t S, size_t C, double* out);
+/* all parameters at once: h_draws [S][d][C] (the fc_hmc_run layout); out arrays of length d. */
+int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, double* h_mean,
+                       double* h_std, double* h_rhat, double* h_ess);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
