@@ -1,0 +1,475 @@
+// fc_dense.cu -- dense GLM plate: value + analytic gradient of
+//     sum_i log p(y_i | link(off_c + sum_k X[i][k] * beta[k][c]), other params_c)     for C chains.
+//
+// Replaces, for a whole block of chains at once, the reference's per-observation walk
+// (examples/classification.rs:118-130 builds eta_i left to right, then Bernoulli::log_prob,
+// src/core/distribution.rs:598-619) that hmc.rs:304-329 repeats 2*d times per force.
+//
+// B200 mapping (sm_100a):
+//   * one CTA = 128 chains x a contiguous range of observation rows; 8 warps, warp w owns
+//     chains [16w, 16w+16) in both contractions, so the residual tile never leaves the warp.
+//   * X is streamed once per CTA in tiles of 32 rows by 1-D bulk TMA (cp.async.bulk ->
+//     UBLKCP) into a 2-stage shared-memory ring guarded by mbarriers; the tile of 32 rows is
+//     contiguous in the row-major matrix, so one bulk copy moves it.
+//   * both contractions  eta = X_tile * beta  and  g += X_tile^T * r  run on the FP64 tensor
+//     path (mma.sync.m8n8k4.f64 -> DMMA); beta lives in shared memory for the CTA's lifetime,
+//     the D x 128 gradient tile lives in registers (52 doubles / thread at D = 100).
+//   * the link + log-density + residual is evaluated on the accumulator fragments in between.
+//   * per-CTA partial sums go to [split][acc][C]; fc_score.cu's k_finish folds them in fixed
+//     order (no atomics => bit-reproducible run to run).
+// FP64 has no tcgen05 path; DMMA is the tensor-core route that meets the 1e-10 gate.
+#include "fc_dist.cuh"
+#include "fc_internal.cuh"
+
+namespace fc {
+
+#define DN_BC 128     // chains per CTA
+#define DN_TN 32      // observation rows per tile
+#define DN_LDB 132    // beta smem row stride (doubles), == 4 mod 16 -> conflict-free B fragments
+#define DN_LDW 20     // per-warp residual tile row stride (doubles)
+#define DN_THREADS 256
+#define DN_STAGES 2
+
+enum { GLM_GENERIC = 0, GLM_BERN_SIGMOID = 1, GLM_POISSON_ID = 2 };
+
+struct DenseArgs {
+  DOp op;
+  AccMap acc;
+  const double* X;      // [N][K] row-major
+  const int32_t* crow;  // program slot -> sorted row
+  const double* q;
+  double* part;
+  int64_t C, N;
+  int64_t rows_per_split;  // multiple of DN_TN
+  int32_t K, dj, dt;       // dense width, dense param index, dense term index
+  int32_t n_acc;           // accumulators per split in `part`
+  int32_t n_red;
+};
+
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void load_value(const DCol& c, int64_t i, bool cont, double& x, long long& xi) {
+  x = 0.0;
+  xi = 0;
+  switch (c.dtype) {
+    case FC_COL_F64: { double v = __ldg((const double*)c.ptr + i); if (cont) x = v; else xi = (long long)v; } break;
+    case FC_COL_U8: { long long v = __ldg((const uint8_t*)c.ptr + i); if (cont) x = (double)v; else xi = v; } break;
+    case FC_COL_U32: { long long v = __ldg((const uint32_t*)c.ptr + i); if (cont) x = (double)v; else xi = v; } break;
+    default: { long long v = __ldg((const long long*)c.ptr + i); if (cont) x = (double)v; else xi = v; } break;
+  }
+}
+
+__device__ __forceinline__ double link_apply(int link, double s, double lo, double hi, double& dl) {
+  switch (link) {
+    case FC_LINK_EXP: { double e = exp(s); dl = e; return e; }
+    case FC_LINK_SIGMOID_CLAMPED: {
+      double p = 1.0 / (1.0 + exp(-s));
+      dl = (p > lo && p < hi) ? p * (1.0 - p) : 0.0;
+      return p < lo ? lo : (p > hi ? hi : p);
+    }
+    case FC_LINK_CLAMP: dl = (s > lo && s < hi) ? 1.0 : 0.0; return s < lo ? lo : (s > hi ? hi : s);
+    default: dl = 1.0; return s;
+  }
+}
+
+
+// generic distribution / link (kept out of line: it is instantiated once, not 16x per tile)
+template <bool GRAD>
+__device__ __noinline__ void glm_generic_elem(const DOp& op, int dj, double sarg, double p0, double p1, double p2, double l0, double l1, double l2,
+                                              double x, long long xi, double lg, double& lp, double& w, double* other) {
+  double pv[3] = {p0, p1, p2}, dl[3] = {l0, l1, l2};
+  double dlk;
+  double val = link_apply(op.p[dj].link, sarg, op.p[dj].lo, op.p[dj].hi, dlk);
+  pv[dj] = val;
+  dl[dj] = dlk;
+  DistOut o = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, lg);
+  lp = o.lp;
+  w = 0.0;
+  other[0] = other[1] = other[2] = 0.0;
+  if (GRAD) {
+    double dpj[3] = {o.dp0, o.dp1, o.dp2};
+    for (int pj = 0; pj < 3; pj++) {
+      double ww = dpj[pj] * dl[pj];
+      if (pj == dj) w = ww;
+      else other[pj] = ww;
+    }
+  }
+}
+
+// MT = number of 8-row gradient tiles per warp (K padded to 8*MT); GRAD=false skips the
+// second contraction (value only: MH / SMC).
+template <int MODE, bool GRAD, int MT>
+__global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_constant__ DenseArgs A) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int K = A.K;
+  const int KP4 = (K + 3) & ~3;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gid = lane >> 2, tig = lane & 3;  // mma "groupID" / "threadID_in_group"
+  const int64_t C = A.C;
+  const int64_t cb0 = (int64_t)blockIdx.x * DN_BC;
+  const DOp& op = A.op;
+
+  // ---- shared memory carve-up ----
+  uint64_t* bars = (uint64_t*)smem_raw;                                   // DN_STAGES mbarriers
+  double* s_beta = (double*)(smem_raw + 128);                             // [KP4][DN_LDB]
+  double* s_w = s_beta + (size_t)KP4 * DN_LDB;                            // [8 warps][DN_TN][DN_LDW]
+  double* s_x = s_w + 8 * DN_TN * DN_LDW;                                 // [DN_STAGES][DN_TN*K + pad]
+  const int x_stage_elems = ((DN_TN * K + 8 + 15) & ~15);                 // + zero pad for k >= K reads
+
+  const int64_t row_begin = (int64_t)blockIdx.y * A.rows_per_split;
+  const int64_t row_end = min(A.N, row_begin + A.rows_per_split);
+  const int n_tiles = (int)((row_end - row_begin + DN_TN - 1) / DN_TN);
+
+  if (tid == 0) {
+    for (int s = 0; s < DN_STAGES; s++) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  // beta tile: s_beta[k][cl] = q[crow[slot+k]][cb0+cl]; zero for padded k / chains
+  const int dslot = op.p[A.dj].t[A.dt].slot;
+  for (int idx = tid; idx < KP4 * DN_BC; idx += DN_THREADS) {
+    int k = idx / DN_BC, cl = idx % DN_BC;
+    double v = 0.0;
+    if (k < K && cb0 + cl < C) v = A.q[(int64_t)A.crow[dslot + k] * C + cb0 + cl];
+    s_beta[k * DN_LDB + cl] = v;
+  }
+  // zero the pad after each X stage once (bulk copies never touch it)
+  for (int s = 0; s < DN_STAGES; s++)
+    for (int idx = DN_TN * K + tid; idx < x_stage_elems; idx += DN_THREADS) s_x[(size_t)s * x_stage_elems + idx] = 0.0;
+  __syncthreads();
+
+  auto issue_tile = [&](int t) {  // called by thread 0 only, full tiles only
+    int s = t % DN_STAGES;
+    const double* src = A.X + (row_begin + (int64_t)t * DN_TN) * K;
+    uint32_t bytes = (uint32_t)(DN_TN * K * sizeof(double));
+    mbar_expect_tx(&bars[s], bytes);
+    tma_bulk_g2s(s_x + (size_t)s * x_stage_elems, src, bytes, &bars[s]);
+  };
+  auto tile_rows = [&](int t) -> int { return (int)min((int64_t)DN_TN, row_end - (row_begin + (int64_t)t * DN_TN)); };
+  // bulk copies need 16-byte sizes; a partial (last) tile is copied cooperatively instead
+  auto tile_is_bulk = [&](int t) -> bool { return tile_rows(t) == DN_TN && ((DN_TN * K) % 2 == 0); };
+
+  if (tid == 0) {
+    for (int t = 0; t < DN_STAGES && t < n_tiles; t++)
+      if (tile_is_bulk(t)) issue_tile(t);
+  }
+
+  // ---- per-thread chain columns: c = cb0 + warp*16 + nt*8 + tig*2 + j ----
+  double off[2][2];                 // CONST/LATENT part of the dense parameter
+  double po[3][2][2], pdl[3][2][2]; // the other (per-chain) parameters, linked, and dlink
+#pragma unroll
+  for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      int64_t c = cb0 + warp * 16 + nt * 8 + tig * 2 + j;
+      bool ok = c < C;
+      double s = 0.0;
+#pragma unroll
+      for (int t = 0; t < 3; t++) {
+        const DTerm& tm = op.p[A.dj].t[t];
+        if (tm.kind == FC_TERM_CONST) s += tm.c;
+        else if (tm.kind == FC_TERM_LATENT && ok) s += A.q[(int64_t)tm.row * C + c];
+      }
+      off[nt][j] = s;
+#pragma unroll
+      for (int pj = 0; pj < 3; pj++) {
+        po[pj][nt][j] = 0.0;
+        pdl[pj][nt][j] = 0.0;
+        if (MODE == GLM_GENERIC && pj < op.n_params && pj != A.dj) {
+          double sp = 0.0;
+#pragma unroll
+          for (int t = 0; t < 3; t++) {
+            const DTerm& tm = op.p[pj].t[t];
+            if (tm.kind == FC_TERM_CONST) sp += tm.c;
+            else if (tm.kind == FC_TERM_LATENT && ok) sp += A.q[(int64_t)tm.row * C + c];
+          }
+          po[pj][nt][j] = link_apply(op.p[pj].link, sp, op.p[pj].lo, op.p[pj].hi, pdl[pj][nt][j]);
+        }
+      }
+    }
+
+  double g[MT][2][2];  // gradient tile fragments: k = mt*8+gid, c as above
+#pragma unroll
+  for (int mt = 0; mt < MT; mt++)
+#pragma unroll
+    for (int nt = 0; nt < 2; nt++) g[mt][nt][0] = g[mt][nt][1] = 0.0;
+  double a_lp[2][2], a_w[2][2], a_p[3][2][2];
+#pragma unroll
+  for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      a_lp[nt][j] = a_w[nt][j] = 0.0;
+      a_p[0][nt][j] = a_p[1][nt][j] = a_p[2][nt][j] = 0.0;
+    }
+
+  double* my_w = s_w + warp * DN_TN * DN_LDW;
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  const double lnk_lo = op.p[A.dj].lo, lnk_hi = op.p[A.dj].hi;
+  const int lnk = op.p[A.dj].link;
+
+  for (int t = 0; t < n_tiles; t++) {
+    const int s = t % DN_STAGES;
+    double* xs = s_x + (size_t)s * x_stage_elems;
+    const int64_t r0 = row_begin + (int64_t)t * DN_TN;
+    const int valid = tile_rows(t);
+    // observed values for this thread's 4 rows (issued before the wait to overlap)
+    double yx[4], ylg[4];
+    long long yi[4];
+#pragma unroll
+    for (int mt = 0; mt < 4; mt++) {
+      int r = mt * 8 + gid;
+      yx[mt] = 0.0; yi[mt] = 0; ylg[mt] = qnan;
+      if (r < valid) {
+        load_value(op.value_col, r0 + r, op.cont != 0, yx[mt], yi[mt]);
+        if (op.lgam) ylg[mt] = __ldg(op.lgam + r0 + r);
+      }
+    }
+    if (tile_is_bulk(t)) {
+      mbar_wait(&bars[s], (uint32_t)((t / DN_STAGES) & 1));
+    } else {
+      // cooperative copy + zero fill of the missing rows
+      const double* src = A.X + r0 * K;
+      for (int idx = tid; idx < DN_TN * K; idx += DN_THREADS) xs[idx] = (idx < valid * K) ? __ldg(src + idx) : 0.0;
+      __syncthreads();
+    }
+
+    // ---- contraction 1: eta[32][16 per warp] = X_tile[32][K] * beta[K][16] ----
+    double eta[4][2][2];
+#pragma unroll
+    for (int mt = 0; mt < 4; mt++)
+#pragma unroll
+      for (int nt = 0; nt < 2; nt++) eta[mt][nt][0] = eta[mt][nt][1] = 0.0;
+#pragma unroll 5
+    for (int k4 = 0; k4 < KP4; k4 += 4) {
+      double a[4], b[2];
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) a[mt] = xs[(mt * 8 + gid) * K + k4 + tig];
+#pragma unroll
+      for (int nt = 0; nt < 2; nt++) b[nt] = s_beta[(k4 + tig) * DN_LDB + warp * 16 + nt * 8 + gid];
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++)
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++) dmma884(eta[mt][nt][0], eta[mt][nt][1], a[mt], b[nt]);
+    }
+
+    // ---- link + log-density + residual on the accumulator fragments ----
+#pragma unroll
+    for (int mt = 0; mt < 4; mt++) {
+      const bool rv = (mt * 8 + gid) < valid;
+#pragma unroll
+      for (int nt = 0; nt < 2; nt++) {
+        double wv[2];
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          double sarg = off[nt][j] + eta[mt][nt][j];
+          double lp = 0.0, w = 0.0;
+          if (MODE == GLM_BERN_SIGMOID) {
+            // classification.rs:124-130: p = 1/(1+exp(-eta)); clamp; Bernoulli::log_prob
+            double p = 1.0 / (1.0 + exp(-sarg));
+            bool inside = (p > lnk_lo && p < lnk_hi);
+            double pc = p < lnk_lo ? lnk_lo : (p > lnk_hi ? lnk_hi : p);
+            if (!(pc >= 0.0 && pc <= 1.0)) lp = d_neg_inf();
+            else if (yi[mt] != 0) lp = pc <= 0.0 ? d_neg_inf() : log(pc);
+            else lp = pc >= 1.0 ? d_neg_inf() : log(1.0 - pc);
+            if (GRAD && inside && d_fin(lp)) w = (yi[mt] != 0) ? (1.0 - p) : -p;
+          } else if (MODE == GLM_POISSON_ID) {
+            // distribution.rs:1237-1258 with lambda = eta
+            double lam = sarg;
+            if (lam <= 0.0 || !d_fin(lam) || yi[mt] < 0) lp = d_neg_inf();
+            else {
+              double kf = (double)yi[mt];
+              if (lam > 700.0 && yi[mt] == 0) lp = -lam;
+              else lp = kf * log(lam) - lam - ylg[mt];
+              if (GRAD && d_fin(lp)) w = kf / lam - 1.0;
+            }
+          } else {
+            double op_other[3];
+            glm_generic_elem<GRAD>(op, A.dj, sarg, po[0][nt][j], po[1][nt][j], po[2][nt][j], pdl[0][nt][j], pdl[1][nt][j], pdl[2][nt][j], yx[mt], yi[mt], ylg[mt], lp, w, op_other);
+            if (GRAD && rv) {
+#pragma unroll
+              for (int pj = 0; pj < 3; pj++) a_p[pj][nt][j] += op_other[pj];
+            }
+          }
+          if (rv) { a_lp[nt][j] += lp; a_w[nt][j] += w; }
+          else w = 0.0;
+          wv[j] = w;
+        }
+        if (GRAD) *(double2*)&my_w[(mt * 8 + gid) * DN_LDW + nt * 8 + tig * 2] = make_double2(wv[0], wv[1]);
+      }
+    }
+
+    // ---- contraction 2: g[K][16 per warp] += X_tile^T[K][32] * r[32][16] ----
+    if (GRAD) {
+      __syncwarp();
+#pragma unroll
+      for (int i4 = 0; i4 < DN_TN; i4 += 4) {
+        double b[2];
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++) b[nt] = my_w[(i4 + tig) * DN_LDW + nt * 8 + gid];
+        const double* xr = xs + (i4 + tig) * K + gid;
+#pragma unroll
+        for (int mt = 0; mt < MT; mt++) {
+          if (mt * 8 < K) {  // k >= K overshoots by < 8 doubles into the zero pad only
+            double a = xr[mt * 8];
+#pragma unroll
+            for (int nt = 0; nt < 2; nt++) dmma884(g[mt][nt][0], g[mt][nt][1], a, b[nt]);
+          }
+        }
+      }
+      __syncwarp();
+    }
+
+    // ---- release the stage and refill it ----
+    __syncthreads();
+    if (tid == 0 && t + DN_STAGES < n_tiles && tile_is_bulk(t + DN_STAGES)) issue_tile(t + DN_STAGES);
+  }
+
+  // ---- write this CTA's partial: lp / reduced scalars (sum over gid via shuffles), then g ----
+  const int lp_slot = op.is_sample ? 0 : 1;
+  double* part = A.part + (int64_t)blockIdx.y * A.n_acc * C;
+#pragma unroll
+  for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      double v_lp = a_lp[nt][j], v_w = a_w[nt][j], v_p[3] = {a_p[0][nt][j], a_p[1][nt][j], a_p[2][nt][j]};
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+        v_lp += __shfl_xor_sync(0xffffffffu, v_lp, o);
+        v_w += __shfl_xor_sync(0xffffffffu, v_w, o);
+#pragma unroll
+        for (int pj = 0; pj < 3; pj++) v_p[pj] += __shfl_xor_sync(0xffffffffu, v_p[pj], o);
+      }
+      int64_t c = cb0 + warp * 16 + nt * 8 + tig * 2 + j;
+      if (gid == 0 && c < C) {
+        for (int a = 0; a < 3; a++) part[(int64_t)a * C + c] = (a == lp_slot) ? v_lp : 0.0;
+        if (GRAD) {
+          for (int a = 3; a < 3 + A.n_red; a++) {
+            double v = 0.0;
+#pragma unroll
+            for (int pj = 0; pj < 3; pj++)
+#pragma unroll
+              for (int t = 0; t < 3; t++)
+                if (A.acc.a_idx[pj][t] == a) v += (pj == A.dj) ? v_w : v_p[pj];
+            part[(int64_t)a * C + c] = v;
+          }
+        }
+      }
+    }
+  if (GRAD) {
+#pragma unroll
+    for (int mt = 0; mt < MT; mt++) {
+      int k = mt * 8 + gid;
+      if (k < K) {
+#pragma unroll
+        for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+          for (int j = 0; j < 2; j++) {
+            int64_t c = cb0 + warp * 16 + nt * 8 + tig * 2 + j;
+            if (c < C) part[(int64_t)(3 + A.n_red + k) * C + c] = g[mt][nt][j];
+          }
+      }
+    }
+  }
+}
+
+static size_t dense_smem_bytes(int K) {
+  int KP4 = (K + 3) & ~3;
+  size_t x_stage = ((size_t)DN_TN * K + 8 + 15) & ~(size_t)15;
+  return 128 + sizeof(double) * ((size_t)KP4 * DN_LDB + 8 * DN_TN * DN_LDW + DN_STAGES * x_stage);
+}
+
+static int g_dense_sms = 0;
+int64_t dense_plate_splits(const fc_program* P, const PlateInfo& pl, int64_t C) {
+  if (!g_dense_sms) {
+    cudaDeviceGetAttribute(&g_dense_sms, cudaDevAttrMultiProcessorCount, P->device);
+    if (g_dense_sms <= 0) g_dense_sms = 148;
+  }
+  int64_t n_tiles = cdiv(pl.dop.plate_len, DN_TN);
+  int64_t ncb = cdiv(C, DN_BC);
+  // grid = ncb x S CTAs, one CTA per SM at a time: make it a whole number of waves when the
+  // plate is long enough (148 = 4*37), with at least 8 tiles per CTA.
+  auto gcd = [](int64_t a, int64_t b) { while (b) { int64_t t = a % b; a = b; b = t; } return a; };
+  int64_t s0 = g_dense_sms / gcd(g_dense_sms, ncb);
+  int64_t max_s = std::max<int64_t>(1, n_tiles / 8);
+  int64_t S = s0;
+  while (ncb * S < 2 * g_dense_sms) S += s0;
+  if (S > max_s) S = max_s;
+  return std::max<int64_t>(1, S);
+}
+
+template <int MODE, bool GRAD>
+static int32_t launch_mt(const DenseArgs& A, dim3 grid, size_t smem, cudaStream_t st) {
+  int MT = (A.K + 7) / 8;
+#define DN_LAUNCH(M)                                                                                          \
+  {                                                                                                           \
+    FC_CUDA(cudaFuncSetAttribute(k_dense_glm<MODE, GRAD, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    k_dense_glm<MODE, GRAD, M><<<grid, DN_THREADS, smem, st>>>(A);                                            \
+  }
+  if (!GRAD) DN_LAUNCH(1)
+  else if (MT <= 1) DN_LAUNCH(1)
+  else if (MT <= 2) DN_LAUNCH(2)
+  else if (MT <= 4) DN_LAUNCH(4)
+  else if (MT <= 7) DN_LAUNCH(7)
+  else if (MT <= 10) DN_LAUNCH(10)
+  else DN_LAUNCH(13)
+#undef DN_LAUNCH
+  FC_KERNEL_CHECK();
+  return FC_OK;
+}
+
+int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int64_t C, double* d_part, int64_t max_splits, bool grad, int64_t* n_splits) {
+  const DOp& op = pl.dop;
+  const DTerm& dt = op.p[pl.dense_param].t[pl.dense_term];
+  int K = dt.col.width;
+  if (K > 104) { set_error("dense GLM plate: matrix width %d > 104 is not supported yet", K); return FC_ERR_UNSUPPORTED_OP; }
+  DenseArgs A;
+  A.op = op; A.acc = pl.acc; A.X = (const double*)dt.col.ptr; A.crow = P->d_crow.p; A.q = d_q; A.part = d_part;
+  A.C = C; A.N = op.plate_len; A.K = K; A.dj = pl.dense_param; A.dt = pl.dense_term;
+  A.n_red = pl.acc.n_acc - 3;
+  A.n_acc = grad ? 3 + A.n_red + K : 3;
+  int64_t n_tiles = cdiv(A.N, DN_TN);
+  int64_t S = std::max<int64_t>(1, std::min(max_splits, n_tiles));
+  int64_t tiles_per_split = cdiv(n_tiles, S);
+  A.rows_per_split = tiles_per_split * DN_TN;
+  S = cdiv(A.N, A.rows_per_split);
+  *n_splits = S;
+  dim3 grid((unsigned)cdiv(C, DN_BC), (unsigned)S);
+  size_t smem = dense_smem_bytes(K);
+  // single-parameter fast paths (link and distribution fixed at compile time)
+  bool only_dense_param = true;
+  for (int t = 0; t < 3; t++) {
+    int k = op.p[pl.dense_param].t[t].kind;
+    (void)k;
+  }
+  int mode = GLM_GENERIC;
+  if (op.dist == FC_BERNOULLI && op.p[0].link == FC_LINK_SIGMOID_CLAMPED && only_dense_param) mode = GLM_BERN_SIGMOID;
+  if (op.dist == FC_POISSON && op.p[0].link == FC_LINK_IDENTITY && op.lgam) mode = GLM_POISSON_ID;
+  int32_t rc;
+  if (mode == GLM_BERN_SIGMOID) rc = grad ? launch_mt<GLM_BERN_SIGMOID, true>(A, grid, smem, P->stream) : launch_mt<GLM_BERN_SIGMOID, false>(A, grid, smem, P->stream);
+  else if (mode == GLM_POISSON_ID) rc = grad ? launch_mt<GLM_POISSON_ID, true>(A, grid, smem, P->stream) : launch_mt<GLM_POISSON_ID, false>(A, grid, smem, P->stream);
+  else rc = grad ? launch_mt<GLM_GENERIC, true>(A, grid, smem, P->stream) : launch_mt<GLM_GENERIC, false>(A, grid, smem, P->stream);
+  if (rc == FC_OK) P->n_kernel_launches += 1;
+  return rc;
+}
+
+}  // namespace fc

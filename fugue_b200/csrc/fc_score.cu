@@ -1,0 +1,497 @@
+// fc_score.cu -- batched per-chain log-density and analytic gradient of an op list.
+//
+// Replaces run(ScoreGivenTrace{base}, model_fn()) (src/runtime/interpreters.rs:138-163,
+// src/inference/hmc.rs:264-299) and the finite-difference force grad_log_joint
+// (src/inference/hmc.rs:304-329). The three Trace accumulators log_prior / log_likelihood /
+// log_factors (src/runtime/trace.rs:168-177) are kept separate and combined as
+// (prior + lik) + factors (trace.rs:198-200).
+//
+// Launch structure per evaluation of C chains (all on the program's stream, no atomics, so
+// results are run-to-run reproducible):
+//   k_scalar      one thread per chain walks the scalar sample/observe/factor ops in program order
+//   k_plate       one launch per plate op: chains on threadIdx.x (coalesced q rows), plate
+//                 elements split over threadIdx.y and blockIdx.y; per-chain partial sums of
+//                 the log-density and of the reduced gradient rows go to a partial buffer
+//   dense kernel  (fc_dense.cu) for plates whose parameter is a dense X*beta contraction
+//   k_finish      sums the partials in fixed order into lp3 / grad
+#include "fc_dist.cuh"
+#include "fc_internal.cuh"
+
+namespace fc {
+
+__device__ __forceinline__ double dcol_f64(const DCol& c, int64_t i) {
+  switch (c.dtype) {
+    case FC_COL_F64: return __ldg((const double*)c.ptr + i);
+    case FC_COL_U8: return (double)__ldg((const uint8_t*)c.ptr + i);
+    case FC_COL_U32: return (double)__ldg((const uint32_t*)c.ptr + i);
+    default: return (double)__ldg((const long long*)c.ptr + i);
+  }
+}
+__device__ __forceinline__ long long dcol_i64(const DCol& c, int64_t i) {
+  switch (c.dtype) {
+    case FC_COL_F64: return (long long)__ldg((const double*)c.ptr + i);
+    case FC_COL_U8: return __ldg((const uint8_t*)c.ptr + i);
+    case FC_COL_U32: return __ldg((const uint32_t*)c.ptr + i);
+    default: return __ldg((const long long*)c.ptr + i);
+  }
+}
+
+// link(s) and d link / d s. SIGMOID_CLAMPED follows examples/classification.rs:124-127
+// (p = 1/(1+exp(-s)) then clamp); the derivative is that of the CLAMPED function.
+__device__ __forceinline__ double apply_link(int link, double s, double lo, double hi, double& dl) {
+  switch (link) {
+    case FC_LINK_EXP: { double e = exp(s); dl = e; return e; }
+    case FC_LINK_SIGMOID_CLAMPED: {
+      double p = 1.0 / (1.0 + exp(-s));
+      dl = (p > lo && p < hi) ? p * (1.0 - p) : 0.0;
+      return p < lo ? lo : (p > hi ? hi : p);
+    }
+    case FC_LINK_CLAMP: {
+      dl = (s > lo && s < hi) ? 1.0 : 0.0;
+      return s < lo ? lo : (s > hi ? hi : s);
+    }
+    default: dl = 1.0; return s;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// scalar ops: one thread per chain, program order
+// ---------------------------------------------------------------------------------------
+template <bool GRAD>
+__global__ void k_scalar(const DOp* __restrict__ ops, int n_ops, const int32_t* __restrict__ crow, const int32_t* __restrict__ drow,
+                         const double* __restrict__ q, const disc_t* __restrict__ qd, int64_t C, double* __restrict__ grad, double* __restrict__ part) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double a_prior = 0.0, a_lik = 0.0, a_fac = 0.0;
+  for (int oi = 0; oi < n_ops; oi++) {
+    const DOp& op = ops[oi];
+    if (op.kind == FC_OP_FACTOR) { a_fac += op.value; continue; }
+    double pv[3] = {0.0, 0.0, 0.0}, dl[3] = {0.0, 0.0, 0.0};
+    for (int j = 0; j < op.n_params; j++) {
+      const DParam& pr = op.p[j];
+      double s = 0.0;
+      bool first = true;
+      for (int t = 0; t < 3; t++) {
+        const DTerm& tm = pr.t[t];
+        if (tm.kind == FC_TERM_NONE) continue;
+        double v = tm.kind == FC_TERM_CONST ? tm.c : q[(int64_t)tm.row * C + c];
+        s = first ? v : s + v;
+        first = false;
+      }
+      pv[j] = apply_link(pr.link, s, pr.lo, pr.hi, dl[j]);
+    }
+    double x = 0.0;
+    long long xi = 0;
+    if (op.is_sample) {
+      if (op.cont) x = q[(int64_t)crow[op.cslot0] * C + c];
+      else xi = qd[(int64_t)drow[op.dslot0] * C + c];
+    } else {
+      if (op.cont) x = op.value;
+      else xi = (long long)op.value;
+    }
+    DistOut g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, __longlong_as_double(0x7ff8000000000000LL));
+    if (op.is_sample) a_prior += g.lp;
+    else a_lik += g.lp;
+    if (GRAD) {
+      if (op.is_sample && op.cont) grad[(int64_t)crow[op.cslot0] * C + c] += g.dx;
+      double dpj[3] = {g.dp0, g.dp1, g.dp2};
+      for (int j = 0; j < op.n_params; j++) {
+        double w = dpj[j] * dl[j];
+        if (w != 0.0)
+          for (int t = 0; t < 3; t++)
+            if (op.p[j].t[t].kind == FC_TERM_LATENT) grad[(int64_t)op.p[j].t[t].row * C + c] += w;
+      }
+    }
+  }
+  part[0 * C + c] = a_prior;
+  part[1 * C + c] = a_lik;
+  part[2 * C + c] = a_fac;
+}
+
+// ---------------------------------------------------------------------------------------
+// generic plate op
+// ---------------------------------------------------------------------------------------
+#define PL_TX 32
+#define PL_TY 8
+
+struct PlateArgs {
+  DOp op;
+  AccMap acc;
+  const int32_t* crow;
+  const int32_t* drow;
+  const double* q;
+  const disc_t* qd;
+  double* grad;
+  double* part;           // [n_splits][n_acc][C]
+  const int32_t* grp_ptr; // CSR by gather index (or null)
+  const int32_t* grp_elems;
+  int64_t C;
+  int64_t n_units;        // groups if CSR else elements
+  int64_t units_per_split;
+};
+
+template <bool GRAD>
+__global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ PlateArgs A) {
+  const DOp& op = A.op;
+  const int64_t C = A.C;
+  const int64_t c = (int64_t)blockIdx.x * PL_TX + threadIdx.x;
+  const bool active = c < C;
+  const int64_t u0 = (int64_t)blockIdx.y * A.units_per_split;
+  const int64_t u1 = min(A.n_units, u0 + A.units_per_split);
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+
+  double lp = 0.0;
+  double acc_a[3][3], acc_b[3][3];
+#pragma unroll
+  for (int j = 0; j < 3; j++)
+#pragma unroll
+    for (int t = 0; t < 3; t++) acc_a[j][t] = acc_b[j][t] = 0.0;
+
+  if (active) {
+    // element-invariant parameters are evaluated once per chain
+    double pv_inv[3] = {0.0, 0.0, 0.0}, dl_inv[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      if (j < op.n_params && op.p[j].invariant) {
+        const DParam& pr = op.p[j];
+        double s = 0.0;
+        bool first = true;
+#pragma unroll
+        for (int t = 0; t < 3; t++) {
+          const DTerm& tm = pr.t[t];
+          if (tm.kind == FC_TERM_NONE) continue;
+          double v = tm.kind == FC_TERM_CONST ? tm.c : A.q[(int64_t)tm.row * C + c];
+          s = first ? v : s + v;
+          first = false;
+        }
+        pv_inv[j] = apply_link(pr.link, s, pr.lo, pr.hi, dl_inv[j]);
+      }
+    }
+    // Normal with an element-invariant sigma: hoist log(sigma) and 1/sigma out of the plate loop
+    const bool fast_normal = op.dist == FC_NORMAL && op.p[1].invariant;
+    double n_logsig = 0.0, n_inv = 0.0;
+    bool n_ok = false;
+    if (fast_normal) {
+      n_ok = pv_inv[1] > 0.0 && d_fin(pv_inv[1]);
+      if (n_ok) { n_logsig = log(pv_inv[1]); n_inv = 1.0 / pv_inv[1]; }
+    }
+
+    for (int64_t u = u0 + threadIdx.y; u < u1; u += PL_TY) {
+      int64_t e0 = u, e1 = u + 1;
+      if (A.grp_ptr) { e0 = A.grp_ptr[u]; e1 = A.grp_ptr[u + 1]; }
+      double gacc[3][3];
+#pragma unroll
+      for (int j = 0; j < 3; j++)
+#pragma unroll
+        for (int t = 0; t < 3; t++) gacc[j][t] = 0.0;
+      for (int64_t e = e0; e < e1; e++) {
+        const int64_t i = A.grp_elems ? (int64_t)A.grp_elems[e] : e;
+        double pv[3] = {pv_inv[0], pv_inv[1], pv_inv[2]}, dl[3] = {dl_inv[0], dl_inv[1], dl_inv[2]};
+        double lx[3][3];   // LATENT_X column values
+        int zsel[3][3];    // SELECT2 branch
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+          if (j >= op.n_params || op.p[j].invariant) continue;
+          const DParam& pr = op.p[j];
+          double s = 0.0;
+          bool first = true;
+#pragma unroll
+          for (int t = 0; t < 3; t++) {
+            const DTerm& tm = pr.t[t];
+            if (tm.kind == FC_TERM_NONE) continue;
+            double v = 0.0;
+            switch (tm.kind) {
+              case FC_TERM_CONST: v = tm.c; break;
+              case FC_TERM_LATENT: v = A.q[(int64_t)tm.row * C + c]; break;
+              case FC_TERM_LATENT_X: lx[j][t] = dcol_f64(tm.col, i); v = A.q[(int64_t)tm.row * C + c] * lx[j][t]; break;
+              case FC_TERM_GATHER: v = A.q[(int64_t)A.crow[tm.slot + dcol_i64(tm.col, i)] * C + c]; break;
+              case FC_TERM_SELECT2: zsel[j][t] = (A.qd[(int64_t)A.drow[tm.dslot + i] * C + c] == 0) ? 0 : 1; v = A.q[(int64_t)(zsel[j][t] ? tm.row_b : tm.row) * C + c]; break;
+              case FC_TERM_PLATE_LATENT: v = A.q[(int64_t)A.crow[tm.slot + i] * C + c]; break;
+              default: break;
+            }
+            s = first ? v : s + v;
+            first = false;
+          }
+          pv[j] = apply_link(pr.link, s, pr.lo, pr.hi, dl[j]);
+        }
+        double x = 0.0;
+        long long xi = 0;
+        int64_t xrow = 0;
+        if (op.is_sample) {
+          if (op.cont) { xrow = (int64_t)A.crow[op.cslot0 + i] * C + c; x = A.q[xrow]; }
+          else xi = A.qd[(int64_t)A.drow[op.dslot0 + i] * C + c];
+        } else {
+          if (op.cont) x = dcol_f64(op.value_col, i);
+          else xi = dcol_i64(op.value_col, i);
+        }
+        DistOut g;
+        if (fast_normal) {
+          g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
+          if (!n_ok || !d_fin(pv[0]) || !d_fin(x)) g.lp = d_neg_inf();
+          else {
+            double z = (x - pv[0]) * n_inv;
+            g.lp = -0.5 * z * z - n_logsig - 0.5 * FC_LN_2PI;
+            if (GRAD && d_fin(g.lp)) { g.dp0 = z * n_inv; g.dx = -g.dp0; g.dp1 = (z * z - 1.0) * n_inv; }
+          }
+        } else {
+          g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, op.lgam ? op.lgam[i] : qnan);
+        }
+        lp += g.lp;
+        if (GRAD) {
+          if (op.is_sample && op.cont) A.grad[xrow] += g.dx;
+          const double dpj[3] = {g.dp0, g.dp1, g.dp2};
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            if (j >= op.n_params) continue;
+            const double w = dpj[j] * dl[j];
+            if (w == 0.0) continue;
+#pragma unroll
+            for (int t = 0; t < 3; t++) {
+              const DTerm& tm = op.p[j].t[t];
+              switch (tm.kind) {
+                case FC_TERM_LATENT: acc_a[j][t] += w; break;
+                case FC_TERM_LATENT_X: acc_a[j][t] += w * lx[j][t]; break;
+                case FC_TERM_SELECT2: if (zsel[j][t]) acc_b[j][t] += w; else acc_a[j][t] += w; break;
+                case FC_TERM_GATHER: gacc[j][t] += w; break;
+                case FC_TERM_PLATE_LATENT: A.grad[(int64_t)A.crow[tm.slot + i] * C + c] += w; break;
+                default: break;
+              }
+            }
+          }
+        }
+      }
+      if (GRAD && A.grp_ptr) {  // this thread is the only writer of group u's gathered rows
+#pragma unroll
+        for (int j = 0; j < 3; j++)
+#pragma unroll
+          for (int t = 0; t < 3; t++)
+            if (j < op.n_params && op.p[j].t[t].kind == FC_TERM_GATHER) A.grad[(int64_t)A.crow[op.p[j].t[t].slot + u] * C + c] += gacc[j][t];
+      }
+    }
+  }
+  // ---- reduce over threadIdx.y in shared memory (fixed order), write the split's partial ----
+  __shared__ double sm[PL_TY][PL_TX + 1];
+  const int n_acc = GRAD ? A.acc.n_acc : 3;
+  const int lp_slot = op.is_sample ? 0 : 1;
+  for (int a = 0; a < n_acc; a++) {
+    double v = 0.0;
+    if (a < 3) v = (a == lp_slot) ? lp : 0.0;
+    else {
+#pragma unroll
+      for (int j = 0; j < 3; j++)
+#pragma unroll
+        for (int t = 0; t < 3; t++) {
+          if (A.acc.a_idx[j][t] == a) v += acc_a[j][t];
+          if (A.acc.b_idx[j][t] == a) v += acc_b[j][t];
+        }
+    }
+    __syncthreads();
+    sm[threadIdx.y][threadIdx.x] = v;
+    __syncthreads();
+    if (threadIdx.y == 0 && active) {
+      double s = sm[0][threadIdx.x];
+#pragma unroll
+      for (int y = 1; y < PL_TY; y++) s += sm[y][threadIdx.x];
+      A.part[((int64_t)blockIdx.y * n_acc + a) * C + c] = s;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// finish: fold one launch's partial segment into lp3 / grad (fixed split order)
+// ---------------------------------------------------------------------------------------
+struct FinishArgs {
+  const double* part;
+  int64_t n_splits;
+  int32_t n_acc;
+  int32_t rows[24 + 128];  // target grad rows of accumulators 3.. (dense plates use up to 128+)
+  double* lp3;
+  double* grad;
+  int64_t C;
+};
+__global__ void k_finish(const __grid_constant__ FinishArgs A) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int a = blockIdx.y;
+  if (c >= A.C) return;
+  double s = 0.0;
+  for (int64_t sp = 0; sp < A.n_splits; sp++) s += A.part[(sp * A.n_acc + a) * A.C + c];
+  if (a < 3) A.lp3[(int64_t)a * A.C + c] += s;
+  else A.grad[(int64_t)A.rows[a - 3] * A.C + c] += s;
+}
+__global__ void k_total(const double* __restrict__ lp3, double* __restrict__ total, int64_t C) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) total[c] = (lp3[c] + lp3[C + c]) + lp3[2 * C + c];  // trace.rs:198-200
+}
+
+static int64_t plate_splits(const PlateInfo& pl, int64_t C, int sm_count) {
+  int64_t units = pl.has_gather ? pl.n_groups : pl.dop.plate_len;
+  int64_t cblocks = cdiv(C, PL_TX);
+  int64_t want = cdiv((int64_t)sm_count * 8, cblocks);           // ~8 CTAs per SM
+  int64_t max_by_work = std::max<int64_t>(1, units / (PL_TY * 4));  // >= 4 units per thread
+  return std::max<int64_t>(1, std::min(want, max_by_work));
+}
+
+static int g_sm_count = 0;
+static int sm_count() {
+  if (!g_sm_count) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
+int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t C, double* d_lp3, double* d_total, double* d_grad) {
+  if (C <= 0) return FC_OK;
+  cudaStream_t st = P->stream;
+  const bool grad = d_grad != nullptr;
+  if (P->d_disc > 0 && !d_qd) { set_error("program has %lld discrete sites but qd is NULL", (long long)P->d_disc); return FC_ERR_TRACE_ADDRESS_NOT_FOUND; }
+  // partial buffer size
+  int64_t need = 3 * C;
+  std::vector<int64_t> splits(P->plates.size());
+  for (size_t i = 0; i < P->plates.size(); i++) {
+    PlateInfo& pl = *P->plates[i];
+    splits[i] = pl.dense ? dense_plate_splits(P, pl, C) : plate_splits(pl, C, sm_count());
+    int64_t n_acc = pl.dense ? (3 + 24 + pl.dop.p[pl.dense_param].t[pl.dense_term].col.width) : pl.acc.n_acc;
+    need = std::max(need, splits[i] * n_acc * C);
+  }
+  FC_CUDA(P->ws.part.reserve(need));
+  FC_CUDA(cudaMemsetAsync(d_lp3, 0, 3 * C * sizeof(double), st));
+  if (grad && P->d_cont > 0) FC_CUDA(cudaMemsetAsync(d_grad, 0, P->d_cont * C * sizeof(double), st));
+  FinishArgs F;
+  F.lp3 = d_lp3; F.grad = d_grad; F.C = C; F.part = P->ws.part.p;
+  const unsigned fin_bx = (unsigned)cdiv(C, 128);
+  if (!P->scalar_ops.empty()) {
+    unsigned nb = (unsigned)cdiv(C, 128);
+    if (grad) k_scalar<true><<<nb, 128, 0, st>>>(P->d_scalar_ops.p, (int)P->scalar_ops.size(), P->d_crow.p, P->d_drow.p, d_q, d_qd, C, d_grad, P->ws.part.p);
+    else k_scalar<false><<<nb, 128, 0, st>>>(P->d_scalar_ops.p, (int)P->scalar_ops.size(), P->d_crow.p, P->d_drow.p, d_q, d_qd, C, d_grad, P->ws.part.p);
+    FC_KERNEL_CHECK();
+    F.n_splits = 1; F.n_acc = 3;
+    k_finish<<<dim3(fin_bx, 3), 128, 0, st>>>(F);
+    FC_KERNEL_CHECK();
+    P->n_kernel_launches += 2;
+  }
+  for (size_t i = 0; i < P->plates.size(); i++) {
+    PlateInfo& pl = *P->plates[i];
+    if (pl.dop.plate_len == 0) continue;
+    if (pl.dense) {
+      int64_t ns = 0;
+      FC_TRY(dense_plate_launch(P, pl, d_q, C, P->ws.part.p, splits[i], grad, &ns));
+      const DTerm& dt = pl.dop.p[pl.dense_param].t[pl.dense_term];
+      int K = dt.col.width;
+      // accumulators: 0..2 lp, then the AccMap's reduced rows, then K dense rows
+      int n_red = pl.acc.n_acc - 3;
+      F.n_splits = ns;
+      F.n_acc = grad ? 3 + n_red + K : 3;
+      for (int a = 0; a < n_red; a++) F.rows[a] = pl.acc.rows[a];
+      for (int k = 0; k < K; k++) F.rows[n_red + k] = P->crow[dt.slot + k];
+      k_finish<<<dim3(fin_bx, F.n_acc), 128, 0, st>>>(F);
+      FC_KERNEL_CHECK();
+      P->n_kernel_launches += 1;
+      continue;
+    }
+    PlateArgs A;
+    A.op = pl.dop; A.acc = pl.acc; A.crow = P->d_crow.p; A.drow = P->d_drow.p;
+    A.q = d_q; A.qd = d_qd; A.grad = d_grad; A.part = P->ws.part.p;
+    A.grp_ptr = pl.has_gather ? pl.grp_ptr.p : nullptr;
+    A.grp_elems = pl.has_gather ? pl.grp_elems.p : nullptr;
+    A.C = C;
+    A.n_units = pl.has_gather ? pl.n_groups : pl.dop.plate_len;
+    A.units_per_split = cdiv(A.n_units, splits[i]);
+    int64_t ns = cdiv(A.n_units, A.units_per_split);
+    dim3 grid((unsigned)cdiv(C, PL_TX), (unsigned)ns), block(PL_TX, PL_TY);
+    if (grad) k_plate<true><<<grid, block, 0, st>>>(A);
+    else k_plate<false><<<grid, block, 0, st>>>(A);
+    FC_KERNEL_CHECK();
+    F.n_splits = ns;
+    F.n_acc = grad ? pl.acc.n_acc : 3;
+    for (int a = 0; a < pl.acc.n_acc - 3; a++) F.rows[a] = pl.acc.rows[a];
+    k_finish<<<dim3(fin_bx, F.n_acc), 128, 0, st>>>(F);
+    FC_KERNEL_CHECK();
+    P->n_kernel_launches += 2;
+  }
+  if (d_total) {
+    k_total<<<fin_bx, 128, 0, st>>>(d_lp3, d_total, C);
+    FC_KERNEL_CHECK();
+    P->n_kernel_launches += 1;
+  }
+  return FC_OK;
+}
+
+__global__ void k_i64_to_disc(const long long* __restrict__ in, disc_t* __restrict__ out, int64_t n, int* __restrict__ overflow) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  long long v = in[i];
+  if (v > 2147483647LL || v < -2147483648LL) { *overflow = 1; v = v > 0 ? 2147483647LL : -2147483648LL; }
+  out[i] = (disc_t)v;
+}
+
+// host int64 [d_disc][C] -> device disc_t plane in the workspace
+int32_t convert_qd(fc_program* P, const int64_t* h_qd, int64_t C, const disc_t** out) {
+  *out = nullptr;
+  if (P->d_disc == 0) return FC_OK;
+  if (!h_qd) { set_error("program has %lld discrete sites but qd is NULL", (long long)P->d_disc); return FC_ERR_TRACE_ADDRESS_NOT_FOUND; }
+  int64_t n = P->d_disc * C;
+  FC_CUDA(P->ws.qd64.reserve(n + 1));
+  FC_CUDA(P->ws.qd.reserve(n));
+  FC_CUDA(cudaMemcpyAsync(P->ws.qd64.p, h_qd, n * 8, cudaMemcpyHostToDevice, P->stream));
+  int* flag = (int*)(P->ws.qd64.p + n);
+  FC_CUDA(cudaMemsetAsync(flag, 0, 4, P->stream));
+  k_i64_to_disc<<<(unsigned)cdiv(n, 256), 256, 0, P->stream>>>((const long long*)P->ws.qd64.p, P->ws.qd.p, n, flag);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
+  int h = 0;
+  FC_CUDA(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, P->stream));
+  FC_CUDA(cudaStreamSynchronize(P->stream));
+  if (h) { set_error("discrete site value outside the int32 range of the device planes"); return FC_ERR_UNSUPPORTED_OP; }
+  *out = P->ws.qd.p;
+  return FC_OK;
+}
+
+static int32_t score_host(fc_program* P, const double* h_q, const int64_t* h_qd, size_t C, double* h_lp3[3], double* h_total, double* h_grad) {
+  if (!P) { set_error("program is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  if (C == 0) return FC_OK;
+  if (P->d_cont > 0 && !h_q) { set_error("q is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(P->device));
+  int64_t nq = P->d_cont * (int64_t)C;
+  FC_CUDA(P->ws.q.reserve(nq));
+  FC_CUDA(P->ws.lp3.reserve(3 * C));
+  FC_CUDA(P->ws.total.reserve(C));
+  if (h_grad) FC_CUDA(P->ws.grad.reserve(nq));
+  if (nq) FC_CUDA(cudaMemcpyAsync(P->ws.q.p, h_q, nq * 8, cudaMemcpyHostToDevice, P->stream));
+  const disc_t* d_qd = nullptr;
+  FC_TRY(convert_qd(P, h_qd, (int64_t)C, &d_qd));
+  FC_TRY(score_dev(P, P->ws.q.p, d_qd, (int64_t)C, P->ws.lp3.p, P->ws.total.p, h_grad ? P->ws.grad.p : nullptr));
+  for (int a = 0; a < 3; a++)
+    if (h_lp3[a]) FC_CUDA(cudaMemcpyAsync(h_lp3[a], P->ws.lp3.p + a * C, C * 8, cudaMemcpyDeviceToHost, P->stream));
+  if (h_total) FC_CUDA(cudaMemcpyAsync(h_total, P->ws.total.p, C * 8, cudaMemcpyDeviceToHost, P->stream));
+  if (h_grad && nq) FC_CUDA(cudaMemcpyAsync(h_grad, P->ws.grad.p, nq * 8, cudaMemcpyDeviceToHost, P->stream));
+  FC_CUDA(cudaStreamSynchronize(P->stream));
+  return FC_OK;
+}
+
+}  // namespace fc
+
+extern "C" {
+
+int32_t fc_logp(fc_program* p, const double* h_q, const int64_t* h_qd, size_t C, double* h_log_prior, double* h_log_lik, double* h_log_factors) {
+  double* lp3[3] = {h_log_prior, h_log_lik, h_log_factors};
+  return fc::score_host(p, h_q, h_qd, C, lp3, nullptr, nullptr);
+}
+
+int32_t fc_logp_grad(fc_program* p, const double* h_q, const int64_t* h_qd, size_t C, double* h_lp, double* h_grad) {
+  double* lp3[3] = {nullptr, nullptr, nullptr};
+  if (!h_grad) { fc::set_error("grad is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  return fc::score_host(p, h_q, h_qd, C, lp3, h_lp, h_grad);
+}
+
+// device-resident variant: d_qd is an int32 plane [d_disc][C]; d_lp [C]; d_grad [d_cont][C] or NULL.
+// Asynchronous on the program's stream (fc_program_stream).
+int32_t fc_logp_grad_dev(fc_program* p, const double* d_q, const int32_t* d_qd, size_t C, double* d_lp, double* d_grad) {
+  if (!p) { fc::set_error("program is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(p->device));
+  FC_CUDA(p->ws.lp3.reserve(3 * C));
+  return fc::score_dev(p, d_q, d_qd, (int64_t)C, p->ws.lp3.p, d_lp, d_grad);
+}
+}

@@ -125,6 +125,8 @@ int32_t fc_program_sites(const fc_program* p, const char* const** names, const i
                          int64_t* n);
 /* cudaStream_t the program launches on (for CUDA-event timing by the caller). */
 int32_t fc_program_stream(const fc_program* p, void** stream);
+/* Number of kernels this library has launched on behalf of the program (bench.py gpu_launches). */
+int32_t fc_program_launch_count(const fc_program* p, uint64_t* n);
 
 /* ---- scoring: replaces run(ScoreGivenTrace{base}, model) (src/runtime/interpreters.rs:138-163,
  * src/inference/hmc.rs:264-299). Three accumulators as in Trace (src/runtime/trace.rs:168-177). */
@@ -134,7 +136,9 @@ int32_t fc_logp(fc_program* p, const double* h_q, const int64_t* h_qd, size_t C,
  * h_grad is [d_cont][C]. */
 int32_t fc_logp_grad(fc_program* p, const double* h_q, const int64_t* h_qd, size_t C,
                      double* h_lp, double* h_grad);
-int32_t fc_logp_grad_dev(fc_program* p, const double* d_q, const int64_t* d_qd, size_t C,
+/* Device-resident variant: d_qd is the int32 plane [d_disc][C] discrete values live in on the
+ * device; d_grad may be NULL (value only). Asynchronous on fc_program_stream(). */
+int32_t fc_logp_grad_dev(fc_program* p, const double* d_q, const int32_t* d_qd, size_t C,
                          double* d_lp, double* d_grad);
 
 /* ---- HMC (src/inference/hmc.rs) ---- */
