@@ -153,3 +153,173 @@ class Program:
     def logp_grad_dev(self, d_q, d_qd, n, d_lp, d_grad):
         """Device pointers (ints); asynchronous on self.stream."""
         check(lib.fc_logp_grad_dev(self.h, vp(d_q), vp(d_qd) if d_qd else None, n, vp(d_lp), vp(d_grad) if d_grad else None))
+
+
+# ---------------------------------------------------------------------------------------------
+# HMC (src/inference/hmc.rs)
+# ---------------------------------------------------------------------------------------------
+i32p = C.POINTER(C.c_int32)
+_sig("fc_hmc_create", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, vp, vp, C.POINTER(vp))
+_sig("fc_hmc_create_sharded", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, vp, vp, C.c_uint64, C.POINTER(vp))
+_sig("fc_hmc_destroy", vp)
+_sig("fc_hmc_step", vp, C.c_size_t)
+_sig("fc_hmc_sync", vp)
+_sig("fc_hmc_get", vp, vp, vp, vp)
+_sig("fc_hmc_trace", vp, vp, vp, vp)
+_sig("fc_hmc_device_state", vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp))
+_sig("fc_hmc_set_position", vp, vp)
+_sig("fc_hmc_set_step_size", vp, C.c_double)
+_sig("fc_hmc_set_n_leapfrog", vp, C.c_uint64)
+_sig("fc_hmc_grad_evals", vp, u64p)
+_sig("fc_hmc_iterations", vp, u64p, i32p)
+_sig("fc_hmc_last_accept_prob", vp, vp, vp, vp)
+_sig("fc_hmc_set_explicit_randomness", vp, vp, vp)
+_sig("fc_hmc_find_reasonable_epsilon", vp, vp)
+_sig("fc_hmc_run", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp)
+lib.fc_hmc_config_default.argtypes = [C.POINTER(_ir.fc_hmc_config)]
+lib.fc_hmc_config_default.restype = None
+
+
+class HMCConfig:
+    """HMCConfig (hmc.rs:105-135), field for field; `grad_mode` 0 = analytic force on device,
+    1 = the reference's central finite differences."""
+
+    def __init__(self, n_leapfrog=16, target_accept=0.8, init_step_size=None, finite_diff_eps=1e-5, adapt_mass=False,
+                 grad_mode=0):
+        self.n_leapfrog, self.target_accept, self.init_step_size = n_leapfrog, target_accept, init_step_size
+        self.finite_diff_eps, self.adapt_mass, self.grad_mode = finite_diff_eps, adapt_mass, grad_mode
+
+    def _c(self):
+        c = _ir.fc_hmc_config()
+        c.n_leapfrog, c.target_accept = self.n_leapfrog, self.target_accept
+        c.init_step_size = float("nan") if self.init_step_size is None else float(self.init_step_size)
+        c.finite_diff_eps, c.adapt_mass, c.grad_mode = self.finite_diff_eps, int(self.adapt_mass), self.grad_mode
+        return c
+
+
+def _as_program(model):
+    return model if isinstance(model, Program) else Program(model)
+
+
+class HmcSession:
+    """HmcSession (hmc.rs:643-919) for n_chains independent chains resident on the GPU."""
+
+    def __init__(self, model, n_chains=1, n_warmup=0, config=None, seed=0, q0=None, qd0=None, first_chain=0):
+        self.program = _as_program(model)
+        self.config = config or HMCConfig()
+        self.n_chains = int(n_chains)
+        d, dd = self.program.d_cont, self.program.d_disc
+        q0a = None if q0 is None else _f64(q0).reshape(d, self.n_chains)
+        qd0a = None if qd0 is None else np.ascontiguousarray(qd0, dtype=np.int64).reshape(dd, self.n_chains)
+        cfg = self.config._c()
+        h = vp()
+        check(lib.fc_hmc_create_sharded(self.program.h, C.byref(cfg), seed, self.n_chains, n_warmup, _ptr(q0a), _ptr(qd0a),
+                                        first_chain, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib.fc_hmc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sites(self):
+        return list(self.program.sites)
+
+    def step(self, n=1):
+        check(lib.fc_hmc_step(self.h, n))
+
+    def sync(self):
+        check(lib.fc_hmc_sync(self.h))
+
+    def position(self):
+        q = np.zeros((self.program.d_cont, self.n_chains))
+        check(lib.fc_hmc_get(self.h, _ptr(q), None, None))
+        return q
+
+    def log_joint(self):
+        lp = np.zeros(self.n_chains)
+        check(lib.fc_hmc_get(self.h, None, _ptr(lp), None))
+        return lp
+
+    def trace(self):
+        """(log_prior, log_likelihood, log_factors) of the current state of every chain."""
+        a, b, c = np.zeros(self.n_chains), np.zeros(self.n_chains), np.zeros(self.n_chains)
+        check(lib.fc_hmc_trace(self.h, _ptr(a), _ptr(b), _ptr(c)))
+        return a, b, c
+
+    def stats(self):
+        st = (_ir.fc_hmc_stats * self.n_chains)()
+        check(lib.fc_hmc_get(self.h, None, None, C.cast(st, vp)))
+        return dict(n_accept=np.array([s.n_accept for s in st]), n_divergent=np.array([s.n_divergent for s in st]),
+                    step_size=np.array([s.step_size for s in st]))
+
+    def step_size(self):
+        return self.stats()["step_size"]
+
+    def last_step_info(self):
+        ap = np.zeros(self.n_chains)
+        acc = np.zeros(self.n_chains, dtype=np.int32)
+        div = np.zeros(self.n_chains, dtype=np.int32)
+        check(lib.fc_hmc_last_accept_prob(self.h, _ptr(ap), _ptr(acc), _ptr(div)))
+        return dict(accept_prob=ap, accepted=acc.astype(bool), divergent=div.astype(bool))
+
+    def iterations(self):
+        n, w = C.c_uint64(), C.c_int32()
+        check(lib.fc_hmc_iterations(self.h, C.byref(n), C.byref(w)))
+        return n.value
+
+    def is_warming_up(self):
+        n, w = C.c_uint64(), C.c_int32()
+        check(lib.fc_hmc_iterations(self.h, C.byref(n), C.byref(w)))
+        return bool(w.value)
+
+    def grad_evals(self):
+        n = C.c_uint64()
+        check(lib.fc_hmc_grad_evals(self.h, C.byref(n)))
+        return n.value
+
+    def set_position(self, q):
+        q = _f64(q).reshape(self.program.d_cont, self.n_chains)
+        check(lib.fc_hmc_set_position(self.h, _ptr(q)))
+
+    def set_step_size(self, eps):
+        check(lib.fc_hmc_set_step_size(self.h, float(eps)))
+
+    def set_n_leapfrog(self, l):
+        check(lib.fc_hmc_set_n_leapfrog(self.h, int(l)))
+
+    def set_explicit_randomness(self, z, u):
+        z = _f64(z).reshape(self.program.d_cont, self.n_chains)
+        u = _f64(u).reshape(self.n_chains)
+        check(lib.fc_hmc_set_explicit_randomness(self.h, _ptr(z), _ptr(u)))
+
+    def find_reasonable_epsilon(self):
+        e = np.zeros(self.n_chains)
+        check(lib.fc_hmc_find_reasonable_epsilon(self.h, _ptr(e)))
+        return e
+
+    def device_state(self):
+        a, b, c = vp(), vp(), vp()
+        check(lib.fc_hmc_device_state(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+
+def hmc_chain(model, n_samples, n_warmup, config=None, n_chains=1, seed=0):
+    """hmc_chain (hmc.rs:566-583) for n_chains independent chains.
+    Returns (draws [n_samples][d][n_chains], log_joint [n_samples][n_chains], stats)."""
+    P = _as_program(model)
+    cfg = (config or HMCConfig())._c()
+    d = P.d_cont
+    draws = np.zeros((n_samples, d, n_chains))
+    lp = np.zeros((n_samples, n_chains))
+    st = (_ir.fc_hmc_stats * n_chains)()
+    check(lib.fc_hmc_run(P.h, C.byref(cfg), seed, n_chains, n_warmup, n_samples, _ptr(draws), _ptr(lp), C.cast(st, vp)))
+    stats = dict(n_accept=np.array([s.n_accept for s in st]), n_divergent=np.array([s.n_divergent for s in st]),
+                 step_size=np.array([s.step_size for s in st]))
+    return draws, lp, stats

@@ -89,6 +89,8 @@ struct fc_program {
   std::vector<const char*> sorted_c_ptr;
   std::vector<int32_t> site_dist_c;      // per sorted continuous site: prior dist id
   fc::DevBuf<int32_t> d_crow, d_drow;
+  std::vector<fc::DOp> all_ops;           // every op, program order (prior pass)
+  fc::DevBuf<fc::DOp> d_all_ops;
   std::vector<fc::DOp> scalar_ops;
   fc::DevBuf<fc::DOp> d_scalar_ops;
   std::vector<std::unique_ptr<fc::PlateInfo>> plates;
@@ -105,5 +107,8 @@ int32_t score_dev(fc_program* p, const double* d_q, const disc_t* d_qd, int64_t 
 // dense GLM plate (fc_dense.cu): writes its partial segment, returns the number of splits used
 int32_t dense_plate_launch(fc_program* p, PlateInfo& pl, const double* d_q, int64_t C, double* d_part, int64_t max_splits, bool grad, int64_t* n_splits);
 int64_t dense_plate_splits(const fc_program* p, const PlateInfo& pl, int64_t C);
+// PriorHandler replacement: draws every sample site of chains [0,C) in program order;
+// chain c uses Philox stream (seed, stream0 + c), counter tag `tag`.
+int32_t prior_sample_dev(fc_program* p, double* d_q, disc_t* d_qd, int64_t C, uint64_t seed, uint64_t stream0, uint64_t tag);
 int32_t convert_qd(fc_program* p, const int64_t* h_qd, int64_t C, const disc_t** out);
 }  // namespace fc

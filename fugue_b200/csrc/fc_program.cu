@@ -326,6 +326,14 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
         if (am.n_acc > 3 + 24) { set_error("op %zu: too many reduced gradient targets", i); return FC_ERR_UNSUPPORTED_OP; }
       }
     }
+    if (op.kind == FC_OP_PLATE_OBSERVE && (op.dist == FC_POISSON || op.dist == FC_BINOMIAL) && op.plate_len > 0) {
+      // precomputed lgamma(k+1) for count-valued observations (constant per model)
+      FC_CUDA(pl->lgam.reserve(op.plate_len));
+      k_lgam_col<<<(unsigned)cdiv(op.plate_len, 256), 256, 0, P->stream>>>(d.value_col, op.plate_len, pl->lgam.p);
+      FC_KERNEL_CHECK();
+      d.lgam = pl->lgam.p;
+    }
+    P->all_ops.push_back(d);
     if (!plate) { P->scalar_ops.push_back(d); continue; }
     if (n_dense > 1) { set_error("op %zu: at most one DENSE term per plate", i); return FC_ERR_UNSUPPORTED_OP; }
     if (pl->dense) {
@@ -335,13 +343,6 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
           int k = d.p[j].t[t].kind;
           if (k != FC_TERM_NONE && k != FC_TERM_CONST && k != FC_TERM_LATENT && k != FC_TERM_DENSE) { set_error("op %zu: a dense GLM plate may combine DENSE only with CONST/LATENT terms", i); return FC_ERR_UNSUPPORTED_OP; }
         }
-    }
-    // precomputed lgamma(k+1) for count-valued observations (constant per model)
-    if (op.kind == FC_OP_PLATE_OBSERVE && (op.dist == FC_POISSON || op.dist == FC_BINOMIAL) && op.plate_len > 0) {
-      FC_CUDA(pl->lgam.reserve(op.plate_len));
-      k_lgam_col<<<(unsigned)cdiv(op.plate_len, 256), 256, 0, P->stream>>>(d.value_col, op.plate_len, pl->lgam.p);
-      FC_KERNEL_CHECK();
-      d.lgam = pl->lgam.p;
     }
     if (gather_col >= 0) {  // CSR of elements by gather index (stable => element order kept)
       const fc_column& c = cols[gather_col];
@@ -364,6 +365,8 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
     pl->acc = am;
     P->plates.push_back(std::move(pl));
   }
+  FC_CUDA(P->d_all_ops.reserve(P->all_ops.size()));
+  if (!P->all_ops.empty()) FC_CUDA(cudaMemcpyAsync(P->d_all_ops.p, P->all_ops.data(), P->all_ops.size() * sizeof(DOp), cudaMemcpyHostToDevice, P->stream));
   FC_CUDA(P->d_scalar_ops.reserve(P->scalar_ops.size()));
   if (!P->scalar_ops.empty()) FC_CUDA(cudaMemcpyAsync(P->d_scalar_ops.p, P->scalar_ops.data(), P->scalar_ops.size() * sizeof(DOp), cudaMemcpyHostToDevice, P->stream));
   FC_CUDA(cudaStreamSynchronize(P->stream));

@@ -157,20 +157,40 @@ typedef struct fc_hmc_stats {
 typedef struct fc_hmc_session fc_hmc_session;
 
 void    fc_hmc_config_default(fc_hmc_config* cfg);
-/* HmcSession::new (hmc.rs:667): prior init (or h_q0 if non-NULL), find_reasonable_epsilon. */
+/* HmcSession::new (hmc.rs:667): prior init (or h_q0 / h_qd0 if non-NULL), find_reasonable_epsilon
+ * unless cfg->init_step_size is set. C independent chains, device resident. */
 int32_t fc_hmc_create(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
                       size_t n_warmup, const double* h_q0, const int64_t* h_qd0,
                       fc_hmc_session** out);
+/* Same, for one shard of a multi-GPU job: local chain c uses the random stream of global chain
+ * first_chain + c, so the union over ranks equals the single-GPU run. */
+int32_t fc_hmc_create_sharded(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
+                              size_t n_warmup, const double* h_q0, const int64_t* h_qd0,
+                              uint64_t first_chain, fc_hmc_session** out);
 int32_t fc_hmc_destroy(fc_hmc_session* s);
-/* HmcSession::step / advance (hmc.rs:819-919): n transitions for all C chains, device resident. */
+/* HmcSession::step / advance (hmc.rs:819-919): n transitions for all C chains. Asynchronous on
+ * the program's stream; fc_hmc_sync() or any getter waits. */
 int32_t fc_hmc_step(fc_hmc_session* s, size_t n);
-/* HmcSession::position / trace (hmc.rs:700-760): copy state to host. Any pointer may be NULL. */
+int32_t fc_hmc_sync(fc_hmc_session* s);
+/* HmcSession::position / step_size (hmc.rs:752-777): copy state to host. Any pointer may be NULL. */
 int32_t fc_hmc_get(fc_hmc_session* s, double* h_q, double* h_lp, fc_hmc_stats* h_stats);
+/* HmcSession::trace accumulators of the current state (trace.rs:168-177). */
+int32_t fc_hmc_trace(fc_hmc_session* s, double* h_log_prior, double* h_log_lik, double* h_log_factors);
+/* device pointers of the resident state: q [d][C], log-joint [C], accumulators [3][C] */
+int32_t fc_hmc_device_state(fc_hmc_session* s, double** d_q, double** d_lj, double** d_lp3);
 int32_t fc_hmc_set_position(fc_hmc_session* s, const double* h_q);
-int32_t fc_hmc_set_step_size(fc_hmc_session* s, double eps);      /* hmc.rs:792 */
-int32_t fc_hmc_set_n_leapfrog(fc_hmc_session* s, uint64_t l);     /* hmc.rs:803 */
+int32_t fc_hmc_set_step_size(fc_hmc_session* s, double eps);      /* hmc.rs:738-744 */
+int32_t fc_hmc_set_n_leapfrog(fc_hmc_session* s, uint64_t l);     /* hmc.rs:748-750 */
 int32_t fc_hmc_grad_evals(const fc_hmc_session* s, uint64_t* per_chain);
-/* hmc_chain (hmc.rs:566-583): warmup then n_samples draws; h_draws [n_samples][d][C]. */
+int32_t fc_hmc_iterations(const fc_hmc_session* s, uint64_t* iters, int32_t* warming); /* hmc.rs:780-787 */
+/* HmcStepInfo of the last transition (hmc.rs:585-600): accept_prob, accepted, divergent per chain */
+int32_t fc_hmc_last_accept_prob(fc_hmc_session* s, double* h_ap, int32_t* h_accepted, int32_t* h_divergent);
+/* Parity hooks: supply the StandardNormal draws z [d][C] and the accept uniform u [C] of the next
+ * transition / step-size search (hmc.rs:436-441,461,489-495). */
+int32_t fc_hmc_set_explicit_randomness(fc_hmc_session* s, const double* h_z, const double* h_u);
+int32_t fc_hmc_find_reasonable_epsilon(fc_hmc_session* s, double* h_eps);  /* hmc.rs:479-535 */
+/* hmc_chain (hmc.rs:566-583): warmup then n_samples draws; h_draws [n_samples][d][C], h_lp
+ * [n_samples][C] (either may be NULL). */
 int32_t fc_hmc_run(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
                    size_t n_warmup, size_t n_samples, double* h_draws, double* h_lp,
                    fc_hmc_stats* h_stats);
