@@ -51,6 +51,8 @@ _sig("fc_program_dims", vp, i64p, i64p)
 _sig("fc_program_sites", vp, C.POINTER(C.POINTER(C.c_char_p)), C.POINTER(i64p), i64p)
 _sig("fc_program_stream", vp, C.POINTER(vp))
 _sig("fc_program_launch_count", vp, u64p)
+_sig("fc_program_kernel_timing", vp, C.c_int32)
+_sig("fc_program_kernel_time", vp, dp, u64p)
 _sig("fc_logp", vp, vp, vp, C.c_size_t, vp, vp, vp)
 _sig("fc_logp_grad", vp, vp, vp, C.c_size_t, vp, vp)
 _sig("fc_logp_grad_dev", vp, vp, vp, C.c_size_t, vp, vp)
@@ -122,6 +124,15 @@ class Program:
         n = C.c_uint64()
         check(lib.fc_program_launch_count(self.h, C.byref(n)))
         return n.value
+
+    def kernel_timing(self, enable=True):
+        check(lib.fc_program_kernel_timing(self.h, int(enable)))
+
+    def kernel_time(self):
+        """(summed ms, launches) of the dominant observation-streaming kernel since kernel_timing(True)."""
+        t, n = C.c_double(), C.c_uint64()
+        check(lib.fc_program_kernel_time(self.h, C.byref(t), C.byref(n)))
+        return t.value, n.value
 
     def check_structure(self, builder):
         """Second trace of the same model must match (ErrorCode 302 otherwise)."""

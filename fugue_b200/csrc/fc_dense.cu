@@ -465,9 +465,19 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
   if (op.dist == FC_BERNOULLI && op.p[0].link == FC_LINK_SIGMOID_CLAMPED && only_dense_param) mode = GLM_BERN_SIGMOID;
   if (op.dist == FC_POISSON && op.p[0].link == FC_LINK_IDENTITY && op.lgam) mode = GLM_POISSON_ID;
   int32_t rc;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (P->timing) {
+    FC_CUDA(cudaEventCreate(&e0));
+    FC_CUDA(cudaEventCreate(&e1));
+    FC_CUDA(cudaEventRecord(e0, P->stream));
+  }
   if (mode == GLM_BERN_SIGMOID) rc = grad ? launch_mt<GLM_BERN_SIGMOID, true>(A, grid, smem, P->stream) : launch_mt<GLM_BERN_SIGMOID, false>(A, grid, smem, P->stream);
   else if (mode == GLM_POISSON_ID) rc = grad ? launch_mt<GLM_POISSON_ID, true>(A, grid, smem, P->stream) : launch_mt<GLM_POISSON_ID, false>(A, grid, smem, P->stream);
   else rc = grad ? launch_mt<GLM_GENERIC, true>(A, grid, smem, P->stream) : launch_mt<GLM_GENERIC, false>(A, grid, smem, P->stream);
+  if (P->timing) {
+    FC_CUDA(cudaEventRecord(e1, P->stream));
+    P->timing_events.emplace_back(e0, e1);
+  }
   if (rc == FC_OK) P->n_kernel_launches += 1;
   return rc;
 }

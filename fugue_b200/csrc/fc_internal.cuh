@@ -98,6 +98,9 @@ struct fc_program {
   int device = 0;
   fc::Workspace ws;
   uint64_t n_kernel_launches = 0;  // counted on the host at every launch site
+  // optional CUDA-event timing of the dominant (plate) kernels, on the launching stream
+  bool timing = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
 };
 
 namespace fc {

@@ -403,6 +403,7 @@ int32_t fc_program_create(const fc_op* ops, size_t n_ops, const fc_column* cols,
 int32_t fc_program_destroy(fc_program* p) {
   if (!p) return FC_OK;
   if (p->stream) { cudaStreamSynchronize(p->stream); cudaStreamDestroy(p->stream); }
+  for (auto& e : p->timing_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   delete p;
   return FC_OK;
 }
@@ -438,6 +439,27 @@ int32_t fc_program_sites(const fc_program* p, const char* const** names, const i
 
 int32_t fc_program_stream(const fc_program* p, void** stream) {
   *stream = (void*)p->stream;
+  return FC_OK;
+}
+
+// CUDA-event timing of the dominant plate kernel (the dense GLM kernel), recorded on the
+// launching stream. enable(1) clears previous records.
+int32_t fc_program_kernel_timing(fc_program* p, int32_t enable) {
+  for (auto& e : p->timing_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+  p->timing_events.clear();
+  p->timing = enable != 0;
+  return FC_OK;
+}
+int32_t fc_program_kernel_time(fc_program* p, double* total_ms, uint64_t* launches) {
+  FC_CUDA(cudaStreamSynchronize(p->stream));
+  double t = 0.0;
+  for (auto& e : p->timing_events) {
+    float ms = 0.f;
+    FC_CUDA(cudaEventElapsedTime(&ms, e.first, e.second));
+    t += ms;
+  }
+  if (total_ms) *total_ms = t;
+  if (launches) *launches = p->timing_events.size();
   return FC_OK;
 }
 

@@ -127,6 +127,10 @@ int32_t fc_program_sites(const fc_program* p, const char* const** names, const i
 int32_t fc_program_stream(const fc_program* p, void** stream);
 /* Number of kernels this library has launched on behalf of the program (bench.py gpu_launches). */
 int32_t fc_program_launch_count(const fc_program* p, uint64_t* n);
+/* CUDA-event timing (on the launching stream) of the dominant observation-streaming kernel:
+ * enable, run, then read the summed duration and the number of timed launches. */
+int32_t fc_program_kernel_timing(fc_program* p, int32_t enable);
+int32_t fc_program_kernel_time(fc_program* p, double* total_ms, uint64_t* launches);
 
 /* ---- scoring: replaces run(ScoreGivenTrace{base}, model) (src/runtime/interpreters.rs:138-163,
  * src/inference/hmc.rs:264-299). Three accumulators as in Trace (src/runtime/trace.rs:168-177). */
