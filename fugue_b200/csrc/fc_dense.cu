@@ -19,6 +19,7 @@
 //     order (no atomics => bit-reproducible run to run).
 // FP64 has no tcgen05 path; DMMA is the tensor-core route that meets the 1e-10 gate.
 #include "fc_dist.cuh"
+#include "fc_fastmath.cuh"
 #include "fc_internal.cuh"
 
 namespace fc {
@@ -284,23 +285,30 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
           double sarg = off[nt][j] + eta[mt][nt][j];
           double lp = 0.0, w = 0.0;
           if (MODE == GLM_BERN_SIGMOID) {
-            // classification.rs:124-130: p = 1/(1+exp(-eta)); clamp; Bernoulli::log_prob
-            double p = 1.0 / (1.0 + exp(-sarg));
+            // classification.rs:124-130: p = 1/(1+exp(-eta)); clamp; Bernoulli::log_prob.
+            // Same formula, branch-free primitives (host guarantees 1e-300 < lo <= hi < 1).
+            double p = fast_rcp(1.0 + fast_exp(-sarg));
             bool inside = (p > lnk_lo && p < lnk_hi);
-            double pc = p < lnk_lo ? lnk_lo : (p > lnk_hi ? lnk_hi : p);
-            if (!(pc >= 0.0 && pc <= 1.0)) lp = d_neg_inf();
-            else if (yi[mt] != 0) lp = pc <= 0.0 ? d_neg_inf() : log(pc);
-            else lp = pc >= 1.0 ? d_neg_inf() : log(1.0 - pc);
-            if (GRAD && inside && d_fin(lp)) w = (yi[mt] != 0) ? (1.0 - p) : -p;
+            double pc = fmin(fmax(p, lnk_lo), lnk_hi);
+            lp = fast_log(yi[mt] != 0 ? pc : 1.0 - pc);
+            if (GRAD) w = inside ? ((yi[mt] != 0) ? (1.0 - p) : -p) : 0.0;
+            if (sarg != sarg) { lp = d_neg_inf(); w = 0.0; }  // NaN eta => Bernoulli(NaN) => -inf
           } else if (MODE == GLM_POISSON_ID) {
             // distribution.rs:1237-1258 with lambda = eta
             double lam = sarg;
-            if (lam <= 0.0 || !d_fin(lam) || yi[mt] < 0) lp = d_neg_inf();
-            else {
+            if (!(lam >= 1e-300 && lam <= 1e300) || yi[mt] < 0) {
+              // out of the fast range: exact reference guards via the library functions
+              if (lam <= 0.0 || !d_fin(lam) || yi[mt] < 0) lp = d_neg_inf();
+              else {
+                double kf = (double)yi[mt];
+                lp = (lam > 700.0 && yi[mt] == 0) ? -lam : kf * log(lam) - lam - ylg[mt];
+                if (GRAD && d_fin(lp)) w = kf / lam - 1.0;
+              }
+            } else {
               double kf = (double)yi[mt];
               if (lam > 700.0 && yi[mt] == 0) lp = -lam;
-              else lp = kf * log(lam) - lam - ylg[mt];
-              if (GRAD && d_fin(lp)) w = kf / lam - 1.0;
+              else lp = kf * fast_log(lam) - lam - ylg[mt];
+              if (GRAD && d_fin(lp)) w = kf * fast_rcp(lam) - 1.0;
             }
           } else {
             double op_other[3];
@@ -462,7 +470,7 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
     (void)k;
   }
   int mode = GLM_GENERIC;
-  if (op.dist == FC_BERNOULLI && op.p[0].link == FC_LINK_SIGMOID_CLAMPED && only_dense_param) mode = GLM_BERN_SIGMOID;
+  if (op.dist == FC_BERNOULLI && op.p[0].link == FC_LINK_SIGMOID_CLAMPED && only_dense_param && op.p[0].lo > 1e-300 && op.p[0].hi < 1.0 && op.p[0].lo <= op.p[0].hi) mode = GLM_BERN_SIGMOID;
   if (op.dist == FC_POISSON && op.p[0].link == FC_LINK_IDENTITY && op.lgam) mode = GLM_POISSON_ID;
   int32_t rc;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
