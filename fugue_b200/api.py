@@ -334,3 +334,275 @@ def hmc_chain(model, n_samples, n_warmup, config=None, n_chains=1, seed=0):
     stats = dict(n_accept=np.array([s.n_accept for s in st]), n_divergent=np.array([s.n_divergent for s in st]),
                  step_size=np.array([s.step_size for s in st]))
     return draws, lp, stats
+
+
+# ---------------------------------------------------------------------------------------------
+# single-site MH (src/inference/mh.rs)
+# ---------------------------------------------------------------------------------------------
+class fc_site_proposal(C.Structure):
+    _fields_ = [("address", C.c_char_p), ("kind", C.c_int32), ("_pad", C.c_int32), ("lower", C.c_double), ("upper", C.c_double)]
+
+
+_sig("fc_mh_create", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, vp, C.c_size_t, C.c_uint64, C.POINTER(vp))
+_sig("fc_mh_destroy", vp)
+_sig("fc_mh_step", vp, C.c_size_t)
+_sig("fc_mh_get", vp, vp, vp, vp, vp, vp)
+_sig("fc_mh_n_sites", vp, i64p)
+_sig("fc_mh_run", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp)
+
+
+class SiteProposal:
+    """SiteProposal (mh.rs:145-161)."""
+    Gaussian = ("gaussian", 0, 0.0, 0.0)
+    LogSpace = ("logspace", 1, 0.0, 0.0)
+    PriorResample = ("prior", 3, 0.0, 0.0)
+
+    @staticmethod
+    def Reflect(lower, upper):
+        return ("reflect", 2, float(lower), float(upper))
+
+
+class MhSession:
+    """C independent adaptive single-site MH chains on device (adaptive_mcmc_chain, mh.rs:921-1014)."""
+
+    def __init__(self, model, n_chains=1, n_warmup=0, seed=0, overrides=None, target_accept=0.44, gamma=0.7, first_chain=0):
+        self.program = _as_program(model)
+        self.n_chains = int(n_chains)
+        cfg = _ir.fc_mh_config(target_accept, gamma)
+        ov, n_ov = None, 0
+        if overrides:
+            n_ov = len(overrides)
+            ov = (fc_site_proposal * n_ov)()
+            for i, (a, k) in enumerate(overrides.items()):
+                ov[i].address, ov[i].kind, ov[i].lower, ov[i].upper = a.encode(), k[1], k[2], k[3]
+        h = vp()
+        check(lib.fc_mh_create(self.program.h, C.byref(cfg), seed, self.n_chains, n_warmup, C.cast(ov, vp) if ov else None, n_ov,
+                               first_chain, C.byref(h)))
+        self.h = h
+        n = C.c_int64()
+        check(lib.fc_mh_n_sites(h, C.byref(n)))
+        self.n_sites = n.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib.fc_mh_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def step(self, n=1):
+        check(lib.fc_mh_step(self.h, n))
+
+    def get(self, scales=False):
+        P, n = self.program, self.n_chains
+        q = np.zeros((P.d_cont, n))
+        qd = np.zeros((P.d_disc, n), dtype=np.int64)
+        lp = np.zeros(n)
+        st = (_ir.fc_mh_stats * n)()
+        sc = np.zeros((self.n_sites, n)) if scales else None
+        check(lib.fc_mh_get(self.h, _ptr(q), _ptr(qd), _ptr(lp), C.cast(st, vp), _ptr(sc)))
+        out = dict(q=q, qd=qd, log_joint=lp, n_accept=np.array([s.n_accept for s in st]), n_steps=st[0].n_steps)
+        if scales:
+            out["scales"] = sc
+        return out
+
+
+def adaptive_mcmc_chain(model, n_samples, n_warmup, n_chains=1, seed=0, thin=1, target_accept=0.44, gamma=0.7):
+    """adaptive_mcmc_chain (mh.rs:921-936) for n_chains chains.
+    Returns (draws [n_kept][d_cont][C], ddraws [n_kept][d_disc][C], log_joint [n_kept][C], stats)."""
+    P = _as_program(model)
+    cfg = _ir.fc_mh_config(target_accept, gamma)
+    kept = (n_samples + thin - 1) // thin if n_samples else 0
+    kept = n_samples // thin
+    draws = np.zeros((kept, P.d_cont, n_chains))
+    ddraws = np.zeros((kept, P.d_disc, n_chains), dtype=np.int64)
+    lp = np.zeros((kept, n_chains))
+    st = (_ir.fc_mh_stats * n_chains)()
+    check(lib.fc_mh_run(P.h, C.byref(cfg), seed, n_chains, n_warmup, n_samples, thin, _ptr(draws), _ptr(ddraws), _ptr(lp), C.cast(st, vp)))
+    return draws, ddraws, lp, dict(n_accept=np.array([s.n_accept for s in st]), n_steps=st[0].n_steps)
+
+
+# ---------------------------------------------------------------------------------------------
+# SMC (src/inference/smc.rs) and the weight numerics (src/core/numerical.rs)
+# ---------------------------------------------------------------------------------------------
+_sig("fc_smc_run", vp, vp, C.c_uint64, C.c_size_t, vp, vp, vp, vp, dp, u64p)
+_sig("fc_smc_create", vp, vp, C.c_uint64, C.c_size_t, C.c_uint64, C.POINTER(vp))
+_sig("fc_smc_step", vp, dp)
+_sig("fc_smc_get", vp, vp, vp, vp, vp, dp, u64p)
+_sig("fc_smc_device_state", vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp))
+_sig("fc_smc_destroy", vp)
+_sig("fc_resample", C.c_int32, vp, C.c_size_t, vp, vp)
+_sig("fc_resample_dev", C.c_int32, vp, C.c_size_t, vp, vp, vp)
+_sig("fc_exact_prefix_sums", vp, C.c_size_t, vp)
+_sig("fc_log_sum_exp", vp, C.c_size_t, dp)
+_sig("fc_ess", vp, C.c_size_t, dp)
+_sig("fc_normalize_log_probs", vp, C.c_size_t, vp)
+
+
+class ResamplingMethod:
+    """ResamplingMethod (smc.rs:132-160)."""
+    Multinomial, Systematic, Stratified = 0, 1, 2
+
+
+class SMCConfig:
+    """SMCConfig (smc.rs:172-189)."""
+
+    def __init__(self, resampling_method=ResamplingMethod.Systematic, ess_threshold=0.5, rejuvenation_steps=0):
+        self.resampling_method, self.ess_threshold, self.rejuvenation_steps = resampling_method, ess_threshold, rejuvenation_steps
+
+    def _c(self):
+        return _ir.fc_smc_config(self.resampling_method, 0, self.ess_threshold, self.rejuvenation_steps)
+
+
+class SMCResult:
+    """SMCResult (smc.rs:360-373) as arrays: values [d_cont][P], dvalues [d_disc][P], weight, log_weight."""
+
+    def __init__(self, values, dvalues, weight, log_weight, log_evidence, n_temper_steps, sites):
+        self.values, self.dvalues, self.weight, self.log_weight = values, dvalues, weight, log_weight
+        self.log_evidence, self.n_temper_steps, self.sites = log_evidence, n_temper_steps, sites
+
+
+class SmcSession:
+    def __init__(self, model, num_particles, config=None, seed=0, first_particle=0):
+        self.program = _as_program(model)
+        self.n = int(num_particles)
+        cfg = (config or SMCConfig())._c()
+        h = vp()
+        check(lib.fc_smc_create(self.program.h, C.byref(cfg), seed, self.n, first_particle, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib.fc_smc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def step(self):
+        b = C.c_double()
+        check(lib.fc_smc_step(self.h, C.byref(b)))
+        return b.value
+
+    def result(self, values=True):
+        P, n = self.program, self.n
+        v = np.zeros((P.d_cont, n)) if values else None
+        dv = np.zeros((P.d_disc, n), dtype=np.int64) if values else None
+        w, lw = np.zeros(n), np.zeros(n)
+        le, ns = C.c_double(), C.c_uint64()
+        check(lib.fc_smc_get(self.h, _ptr(v), _ptr(dv), _ptr(w), _ptr(lw), C.byref(le), C.byref(ns)))
+        return SMCResult(v, dv, w, lw, le.value, ns.value, list(P.sites))
+
+
+def adaptive_smc(model, num_particles, config=None, seed=0):
+    """adaptive_smc (smc.rs:455-581)."""
+    P = _as_program(model)
+    n = int(num_particles)
+    if n == 0:
+        return SMCResult(np.zeros((P.d_cont, 0)), np.zeros((P.d_disc, 0), dtype=np.int64), np.zeros(0), np.zeros(0), 0.0, 0, list(P.sites))
+    S = SmcSession(P, n, config, seed)
+    while S.step() < 1.0:
+        pass
+    r = S.result()
+    S.close()
+    return r
+
+
+def resample_indices(method, weights, uniforms):
+    """systematic / stratified / multinomial_indices (smc.rs:255-314) with explicit uniforms."""
+    w = _f64(weights)
+    us = _f64(np.atleast_1d(uniforms))
+    idx = np.zeros(w.size, dtype=np.uint64)
+    check(lib.fc_resample(method, _ptr(w), w.size, _ptr(us), _ptr(idx)))
+    return idx
+
+
+def exact_prefix_sums(weights):
+    w = _f64(weights)
+    S = np.zeros(w.size + 1)
+    check(lib.fc_exact_prefix_sums(_ptr(w), w.size, _ptr(S)))
+    return S
+
+
+def log_sum_exp(x):
+    x = _f64(x)
+    o = C.c_double()
+    check(lib.fc_log_sum_exp(_ptr(x), x.size, C.byref(o)))
+    return o.value
+
+
+def effective_sample_size(weights):
+    w = _f64(weights)
+    o = C.c_double()
+    check(lib.fc_ess(_ptr(w), w.size, C.byref(o)))
+    return o.value
+
+
+def normalize_log_probs(x):
+    x = _f64(x)
+    out = np.zeros_like(x)
+    check(lib.fc_normalize_log_probs(_ptr(x), x.size, _ptr(out)))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# diagnostics (src/inference/diagnostics.rs, src/inference/mcmc_utils.rs)
+# ---------------------------------------------------------------------------------------------
+_sig("fc_split_rhat", vp, C.c_size_t, C.c_size_t, dp)
+_sig("fc_classic_rhat", vp, C.c_size_t, C.c_size_t, dp)
+_sig("fc_ess_multichain", vp, C.c_size_t, C.c_size_t, dp)
+_sig("fc_diagnostics", vp, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp)
+
+
+def _one(fn, draws):
+    d = _f64(draws)
+    o = C.c_double()
+    check(fn(_ptr(d), d.shape[0], d.shape[1], C.byref(o)))
+    return o.value
+
+
+def r_hat_f64(draws):
+    """split-R-hat of one parameter; draws [S][C] (diagnostics.rs:230-260)."""
+    return _one(lib.fc_split_rhat, draws)
+
+
+def classic_r_hat_f64(draws):
+    return _one(lib.fc_classic_rhat, draws)
+
+
+def effective_sample_size_multichain(draws):
+    """mcmc_utils.rs:214-224; draws [S][C]."""
+    return _one(lib.fc_ess_multichain, draws)
+
+
+def diagnostics(draws):
+    """All parameters at once; draws [S][d][C] -> dict of arrays of length d."""
+    x = _f64(draws)
+    S, d, Cn = x.shape
+    mean, std, rh, ess = np.zeros(d), np.zeros(d), np.zeros(d), np.zeros(d)
+    check(lib.fc_diagnostics(_ptr(x), S, d, Cn, _ptr(mean), _ptr(std), _ptr(rh), _ptr(ess)))
+    return dict(mean=mean, std=std, r_hat=rh, ess=ess)
+
+
+def summarize_f64_parameter(draws):
+    """ParameterSummary (diagnostics.rs:321-391) of one parameter; draws [S][C]. Mean/std/R-hat/ESS
+    come from the device; the five quantiles use the reference's rule round((len-1)*p) on the
+    sorted pooled draws (host sort: not on the hot path)."""
+    x = _f64(draws)
+    if x.size == 0:
+        return dict(mean=math.nan, std=math.nan, quantiles={}, r_hat=math.nan, ess=0.0)
+    dg = diagnostics(x[:, None, :])
+    srt = np.sort(x.reshape(-1))
+    qs = {}
+    for name, p in (("2.5%", 0.025), ("25%", 0.25), ("50%", 0.5), ("75%", 0.75), ("97.5%", 0.975)):
+        v = (srt.size - 1) * p
+        idx = int(math.floor(v + 0.5))  # f64::round: half away from zero
+        qs[name] = float(srt[idx])
+    return dict(mean=float(dg["mean"][0]), std=float(dg["std"][0]), quantiles=qs, r_hat=float(dg["r_hat"][0]), ess=float(dg["ess"][0]))

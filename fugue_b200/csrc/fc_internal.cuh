@@ -64,6 +64,16 @@ struct PlateInfo {
   DevBuf<double> lgam;
 };
 
+// one sample site in the global BTreeMap order over ALL addresses (continuous and discrete)
+struct SiteInfo {
+  int32_t is_cont;  // 1: row indexes q, 0: row indexes qd
+  int32_t row;      // sorted row within its plane
+  int32_t op;       // index into all_ops
+  int32_t elem;     // plate element (0 for scalar ops)
+  int32_t value_type;
+  int32_t dist;
+};
+
 struct Workspace {
   DevBuf<double> part;   // partial accumulators of all launches
   DevBuf<double> lp3;    // [3][C]
@@ -89,6 +99,9 @@ struct fc_program {
   std::vector<const char*> sorted_c_ptr;
   std::vector<int32_t> site_dist_c;      // per sorted continuous site: prior dist id
   fc::DevBuf<int32_t> d_crow, d_drow;
+  std::vector<fc::SiteInfo> sites_all;    // every sample site, global address order (mh.rs:965)
+  fc::DevBuf<fc::SiteInfo> d_sites_all;
+  std::vector<std::string> sites_all_names;
   std::vector<fc::DOp> all_ops;           // every op, program order (prior pass)
   fc::DevBuf<fc::DOp> d_all_ops;
   std::vector<fc::DOp> scalar_ops;

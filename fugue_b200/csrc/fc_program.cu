@@ -365,6 +365,24 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
     pl->acc = am;
     P->plates.push_back(std::move(pl));
   }
+  {  // global site table: every sample address in BTreeMap order (adaptive_mcmc_chain's `sites`, mh.rs:965)
+    std::vector<std::pair<std::string, SiteInfo>> all;
+    for (size_t i = 0; i < n_ops; i++) {
+      const fc_op& op = P->ops[i];
+      if (op.kind != FC_OP_SAMPLE && op.kind != FC_OP_PLATE_SAMPLE) continue;
+      bool cont = op.value_type == FC_T_F64;
+      int64_t len = op.kind == FC_OP_SAMPLE ? 1 : op.plate_len;
+      for (int64_t e = 0; e < len; e++) {
+        int64_t slot = (cont ? P->cslot0[i] : P->dslot0[i]) + e;
+        SiteInfo si{cont ? 1 : 0, cont ? P->crow[slot] : P->drow[slot], (int32_t)i, (int32_t)e, op.value_type, op.dist};
+        all.emplace_back(cont ? P->site_c[slot] : P->site_d[slot], si);
+      }
+    }
+    std::sort(all.begin(), all.end(), [](const std::pair<std::string, SiteInfo>& a, const std::pair<std::string, SiteInfo>& b) { return a.first < b.first; });
+    for (auto& a : all) { P->sites_all_names.push_back(a.first); P->sites_all.push_back(a.second); }
+    FC_CUDA(P->d_sites_all.reserve(P->sites_all.size()));
+    if (!P->sites_all.empty()) FC_CUDA(cudaMemcpyAsync(P->d_sites_all.p, P->sites_all.data(), P->sites_all.size() * sizeof(SiteInfo), cudaMemcpyHostToDevice, P->stream));
+  }
   FC_CUDA(P->d_all_ops.reserve(P->all_ops.size()));
   if (!P->all_ops.empty()) FC_CUDA(cudaMemcpyAsync(P->d_all_ops.p, P->all_ops.data(), P->all_ops.size() * sizeof(DOp), cudaMemcpyHostToDevice, P->stream));
   FC_CUDA(P->d_scalar_ops.reserve(P->scalar_ops.size()));

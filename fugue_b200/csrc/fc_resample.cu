@@ -1,0 +1,483 @@
+// fc_resample.cu -- bit-exact systematic / stratified / multinomial resampling on device, plus
+// the weight numerics (log_sum_exp, ESS, normalisation).
+//
+// Reference: src/inference/smc.rs:255-314 (the three *_indices fns), :230-233 (ESS),
+// src/core/numerical.rs:15-38,87-90 (log_sum_exp, normalize_log_probs).
+//
+// All three reference resamplers walk ONE running sum `cum += w[i]` from left to right in f64.
+// The index they return for a threshold t is determined by the SEQUENTIALLY ROUNDED prefix sums
+//     S_0 = 0,  S_{k+1} = fl(S_k + w_k).
+// A parallel scan re-associates the additions and its prefix sums differ from S_k in the last
+// bits, which flips indices whenever a threshold falls between the two. This file
+// reproduces S_k bit for bit, in parallel:
+//   * while the running sum stays inside one binade [2^e, 2^(e+1)) its ulp U is fixed, the sum
+//     is a multiple of U, and fl(S + w) = S + U * r(w) where r(w) = round-to-nearest-even of w/U
+//     evaluated against the PARITY of S/U (the parity only matters for exact ties). So each
+//     weight maps to a pair of integers (increment if S/U even, increment if odd), and pairs
+//     compose associatively: the prefix sums inside a binade are an exact integer scan.
+//   * the element at which the sum leaves the binade is found by the scan itself (first prefix
+//     that reaches the binade's top); that single addition is done in floating point, which is
+//     exactly what the sequential loop does, and the scan restarts in the new binade.
+// There are at most ~60 binade changes between the first weight and 1.0, each a few launches.
+// Thresholds are then resolved by binary search over S (S and the thresholds are monotone).
+#include "fc_internal.cuh"
+
+namespace fc {
+
+// ---------------------------------------------------------------------------------------------
+// reductions (deterministic: fixed grid, fixed order)
+// ---------------------------------------------------------------------------------------------
+#define RD_BLOCKS 1024
+#define RD_THREADS 256
+
+template <int OP>  // 0: max(x)   1: sum exp(x - m)   2: sum x^2   3: sum x   4: count of invalid weights
+__global__ void k_reduce(const double* __restrict__ x, int64_t n, double m, double* __restrict__ part) {
+  double acc = OP == 0 ? d_neg_inf() : 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double v = x[i];
+    if (OP == 0) acc = fmax(acc, v);
+    if (OP == 1) acc += exp(v - m);
+    if (OP == 2) acc += v * v;
+    if (OP == 3) acc += v;
+    if (OP == 4) acc += (v >= 0.0 && isfinite(v)) ? 0.0 : 1.0;
+  }
+  __shared__ double sm[RD_THREADS];
+  sm[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = RD_THREADS / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sm[threadIdx.x] = OP == 0 ? fmax(sm[threadIdx.x], sm[threadIdx.x + o]) : sm[threadIdx.x] + sm[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = sm[0];
+}
+template <int OP>
+__global__ void k_reduce_final(const double* __restrict__ part, int nb, double* __restrict__ out) {
+  __shared__ double sm[RD_THREADS];
+  double acc = OP == 0 ? d_neg_inf() : 0.0;
+  for (int i = threadIdx.x; i < nb; i += RD_THREADS) acc = OP == 0 ? fmax(acc, part[i]) : acc + part[i];
+  sm[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = RD_THREADS / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sm[threadIdx.x] = OP == 0 ? fmax(sm[threadIdx.x], sm[threadIdx.x + o]) : sm[threadIdx.x] + sm[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = sm[0];
+}
+
+// d_scratch: RD_BLOCKS + 4 doubles. Result in d_out (device scalar).
+int32_t dev_reduce(int op, const double* d_x, int64_t n, double m, double* d_scratch, double* d_out, cudaStream_t st) {
+  int nb = (int)std::max<int64_t>(1, std::min<int64_t>(RD_BLOCKS, cdiv(n, RD_THREADS)));
+  switch (op) {
+    case 0: k_reduce<0><<<nb, RD_THREADS, 0, st>>>(d_x, n, m, d_scratch); k_reduce_final<0><<<1, RD_THREADS, 0, st>>>(d_scratch, nb, d_out); break;
+    case 1: k_reduce<1><<<nb, RD_THREADS, 0, st>>>(d_x, n, m, d_scratch); k_reduce_final<1><<<1, RD_THREADS, 0, st>>>(d_scratch, nb, d_out); break;
+    case 2: k_reduce<2><<<nb, RD_THREADS, 0, st>>>(d_x, n, m, d_scratch); k_reduce_final<2><<<1, RD_THREADS, 0, st>>>(d_scratch, nb, d_out); break;
+    case 3: k_reduce<3><<<nb, RD_THREADS, 0, st>>>(d_x, n, m, d_scratch); k_reduce_final<3><<<1, RD_THREADS, 0, st>>>(d_scratch, nb, d_out); break;
+    default: k_reduce<4><<<nb, RD_THREADS, 0, st>>>(d_x, n, m, d_scratch); k_reduce_final<3><<<1, RD_THREADS, 0, st>>>(d_scratch, nb, d_out); break;
+  }
+  FC_KERNEL_CHECK();
+  return FC_OK;
+}
+
+// log_sum_exp (numerical.rs:15-38) of a device array; result on the host.
+int32_t dev_log_sum_exp(const double* d_x, int64_t n, double* d_scratch, double* h_out, cudaStream_t st) {
+  if (n == 0) { *h_out = -INFINITY; return FC_OK; }
+  double* d_res = d_scratch + RD_BLOCKS;
+  FC_TRY(dev_reduce(0, d_x, n, 0.0, d_scratch, d_res, st));
+  double mx;
+  FC_CUDA(cudaMemcpyAsync(&mx, d_res, 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  if (mx == -INFINITY) { *h_out = -INFINITY; return FC_OK; }
+  if (mx != mx || mx == INFINITY) { *h_out = mx; return FC_OK; }
+  FC_TRY(dev_reduce(1, d_x, n, mx, d_scratch, d_res, st));
+  double s;
+  FC_CUDA(cudaMemcpyAsync(&s, d_res, 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  *h_out = (s == 0.0) ? -INFINITY : mx + std::log(s);
+  return FC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// exact sequentially-rounded prefix sums
+// ---------------------------------------------------------------------------------------------
+#define SAT_INC (1LL << 61)
+struct Inc2 { long long e, o; };
+
+__device__ __forceinline__ long long sat_add(long long a, long long b) { return (a >= SAT_INC || b >= SAT_INC || a + b >= SAT_INC) ? SAT_INC : a + b; }
+__device__ __forceinline__ Inc2 combine(const Inc2& a, const Inc2& b) {
+  Inc2 r;
+  r.e = a.e >= SAT_INC ? SAT_INC : sat_add(a.e, (a.e & 1) ? b.o : b.e);
+  r.o = a.o >= SAT_INC ? SAT_INC : sat_add(a.o, (a.o & 1) ? b.e : b.o);
+  return r;
+}
+// base = bottom of the binade (0 for the subnormal/first-normal region), U = its ulp,
+// lim = weights >= lim certainly leave the binade.
+__device__ __forceinline__ Inc2 make_inc(double w, double base, double U, double lim) {
+  Inc2 r;
+  if (!(w < lim)) { r.e = r.o = SAT_INC; return r; }
+  double b1 = base + U;
+  double te = __dadd_rn(__dadd_rn(base, w), -base);
+  double to = __dadd_rn(__dadd_rn(b1, w), -b1);
+  r.e = (long long)(te / U);
+  r.o = (long long)(to / U);
+  return r;
+}
+
+#define SC_THREADS 256
+#define SC_ITEMS 8
+#define SC_TILE (SC_THREADS * SC_ITEMS)
+
+__device__ __forceinline__ Inc2 block_exclusive_scan(Inc2 v, Inc2* total) {
+  // exclusive scan of per-thread aggregates across the block under `combine`
+  __shared__ Inc2 warp_agg[SC_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  Inc2 incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    Inc2 other;
+    other.e = __shfl_up_sync(0xffffffffu, incl.e, o);
+    other.o = __shfl_up_sync(0xffffffffu, incl.o, o);
+    if (lane >= o) incl = combine(other, incl);
+  }
+  if (lane == 31) warp_agg[warp] = incl;
+  __syncthreads();
+  Inc2 excl;
+  excl.e = __shfl_up_sync(0xffffffffu, incl.e, 1);
+  excl.o = __shfl_up_sync(0xffffffffu, incl.o, 1);
+  if (lane == 0) { excl.e = 0; excl.o = 0; }
+  Inc2 pre; pre.e = 0; pre.o = 0;
+  for (int w = 0; w < warp; w++) pre = combine(pre, warp_agg[w]);
+  if (total) {
+    Inc2 t; t.e = 0; t.o = 0;
+    for (int w = 0; w < SC_THREADS / 32; w++) t = combine(t, warp_agg[w]);
+    *total = t;
+  }
+  __syncthreads();
+  return combine(pre, excl);
+}
+
+__global__ void __launch_bounds__(SC_THREADS) k_scan_agg(const double* __restrict__ w, int64_t k0, int64_t len, double base, double U, double lim, Inc2* __restrict__ agg) {
+  int64_t t0 = (int64_t)blockIdx.x * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
+  Inc2 a; a.e = 0; a.o = 0;
+#pragma unroll
+  for (int i = 0; i < SC_ITEMS; i++) {
+    int64_t j = t0 + i;
+    if (j < len) a = combine(a, make_inc(w[k0 + j], base, U, lim));
+  }
+  Inc2 total;
+  block_exclusive_scan(a, &total);
+  if (threadIdx.x == 0) agg[blockIdx.x] = total;
+}
+// single block: exclusive scan of the block aggregates (nb <= SC_TILE * 8)
+__global__ void __launch_bounds__(SC_THREADS) k_scan_top(Inc2* __restrict__ agg, int nb) {
+  __shared__ Inc2 carry;
+  if (threadIdx.x == 0) { carry.e = 0; carry.o = 0; }
+  __syncthreads();
+  for (int base_i = 0; base_i < nb; base_i += SC_TILE) {
+    Inc2 items[SC_ITEMS];
+    Inc2 a; a.e = 0; a.o = 0;
+#pragma unroll
+    for (int i = 0; i < SC_ITEMS; i++) {
+      int j = base_i + threadIdx.x * SC_ITEMS + i;
+      items[i].e = 0; items[i].o = 0;
+      if (j < nb) items[i] = agg[j];
+      a = combine(a, items[i]);
+    }
+    Inc2 total;
+    Inc2 pre = block_exclusive_scan(a, &total);
+    Inc2 run = combine(carry, pre);
+#pragma unroll
+    for (int i = 0; i < SC_ITEMS; i++) {
+      int j = base_i + threadIdx.x * SC_ITEMS + i;
+      if (j < nb) agg[j] = run;  // exclusive prefix for block j
+      run = combine(run, items[i]);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry = combine(carry, total);
+    __syncthreads();
+  }
+}
+struct ScanState {
+  long long k0;
+  double s0;
+  long long first_cross;
+};
+// writes S[k0 + j + 1] for every window element j BEFORE the first crossing and records the
+// first element whose addition reaches the binade top.
+__global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const double* __restrict__ w, int64_t k0, int64_t len, double base, double U, double lim, double s0,
+                                                           int parity, long long need, const Inc2* __restrict__ agg, double* __restrict__ S, ScanState* __restrict__ state) {
+  int64_t t0 = (int64_t)blockIdx.x * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
+  Inc2 items[SC_ITEMS];
+  Inc2 a; a.e = 0; a.o = 0;
+#pragma unroll
+  for (int i = 0; i < SC_ITEMS; i++) {
+    int64_t j = t0 + i;
+    items[i].e = 0; items[i].o = 0;
+    if (j < len) items[i] = make_inc(w[k0 + j], base, U, lim);
+    a = combine(a, items[i]);
+  }
+  Inc2 pre = block_exclusive_scan(a, nullptr);
+  Inc2 run = combine(agg[blockIdx.x], pre);
+  long long cross = 0x7fffffffffffffffLL;
+#pragma unroll
+  for (int i = 0; i < SC_ITEMS; i++) {
+    int64_t j = t0 + i;
+    run = combine(run, items[i]);
+    if (j < len) {
+      long long p = parity ? run.o : run.e;
+      if (p >= need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
+      else S[k0 + j + 1] = __dadd_rn(s0, __dmul_rn((double)p, U));  // exact: on the U grid below the binade top
+    }
+  }
+  if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&state->first_cross, (unsigned long long)cross);
+}
+__global__ void k_scan_advance(const double* __restrict__ w, double* __restrict__ S, ScanState* __restrict__ state, int64_t len) {
+  long long k0 = state->k0;
+  long long fc = state->first_cross;
+  if (fc < len) {
+    long long k = k0 + fc;
+    double nxt = __dadd_rn(S[k], w[k]);  // the one addition that changes binade: plain IEEE add, as the reference does
+    S[k + 1] = nxt;
+    state->k0 = k + 1;
+    state->s0 = nxt;
+  } else {
+    state->k0 = k0 + len;
+    state->s0 = S[k0 + len];
+  }
+  state->first_cross = 0x7fffffffffffffffLL;
+}
+// correctness fallback (weights with negatives / non-finite values): one thread, the reference loop
+__global__ void k_scan_serial(const double* __restrict__ w, int64_t from, int64_t n, double* __restrict__ S) {
+  double cum = S[from];
+  for (int64_t i = from; i < n; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
+}
+
+// S[0..n] := sequentially rounded prefix sums of w[0..n). d_work: >= cdiv(n, SC_TILE) Inc2 + ScanState.
+int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_work, double* d_scratch, cudaStream_t st, uint64_t* launches) {
+  FC_CUDA(cudaMemsetAsync(d_S, 0, 8, st));
+  if (n == 0) return FC_OK;
+  // validity: all weights finite and >= 0, else the serial fallback
+  double bad = 0.0;
+  FC_TRY(dev_reduce(4, d_w, n, 0.0, d_scratch, d_scratch + RD_BLOCKS, st));
+  FC_CUDA(cudaMemcpyAsync(&bad, d_scratch + RD_BLOCKS, 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  if (launches) *launches += 2;
+  if (bad != 0.0) {
+    k_scan_serial<<<1, 1, 0, st>>>(d_w, 0, n, d_S);
+    FC_KERNEL_CHECK();
+    if (launches) *launches += 1;
+    return FC_OK;
+  }
+  ScanState* d_state = (ScanState*)d_work;
+  Inc2* d_agg = (Inc2*)((char*)d_work + 64);
+  ScanState hs;
+  hs.k0 = 0; hs.s0 = 0.0; hs.first_cross = 0x7fffffffffffffffLL;
+  FC_CUDA(cudaMemcpyAsync(d_state, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
+  int64_t win = 1 << 16;
+  int guard = 0;
+  while (hs.k0 < n) {
+    if (++guard > 100000) { set_error("exact_prefix_sums: no progress"); return FC_ERR_CUDA; }
+    double s0 = hs.s0;
+    if (!(s0 == s0) || s0 == INFINITY) {  // cannot happen with finite weights unless the sum overflows
+      k_scan_serial<<<1, 1, 0, st>>>(d_w, hs.k0, n, d_S);
+      FC_KERNEL_CHECK();
+      if (launches) *launches += 1;
+      return FC_OK;
+    }
+    // binade of s0
+    double base, U, T;
+    const double two_m1021 = std::ldexp(1.0, -1021);
+    if (s0 < two_m1021) { base = 0.0; U = std::ldexp(1.0, -1074); T = two_m1021; }
+    else {
+      int e;
+      std::frexp(s0, &e);  // s0 = m * 2^e, m in [0.5,1) => s0 in [2^(e-1), 2^e)
+      base = std::ldexp(1.0, e - 1); U = std::ldexp(1.0, e - 1 - 52); T = std::ldexp(1.0, e);
+    }
+    double lim = (base == 0.0) ? T : base;
+    long long need = (long long)((T - s0) / U);  // exact: both multiples of U, quotient <= 2^53
+    int parity = (int)(((long long)((s0 - base) / U)) & 1LL);
+    int64_t len = std::min<int64_t>(win, n - hs.k0);
+    int nb = (int)cdiv(len, SC_TILE);
+    k_scan_agg<<<nb, SC_THREADS, 0, st>>>(d_w, hs.k0, len, base, U, lim, d_agg);
+    k_scan_top<<<1, SC_THREADS, 0, st>>>(d_agg, nb);
+    k_scan_apply<<<nb, SC_THREADS, 0, st>>>(d_w, hs.k0, len, base, U, lim, s0, parity, need, d_agg, d_S, d_state);
+    k_scan_advance<<<1, 1, 0, st>>>(d_w, d_S, d_state, len);
+    FC_KERNEL_CHECK();
+    if (launches) *launches += 4;
+    long long prev_k0 = hs.k0;
+    FC_CUDA(cudaMemcpyAsync(&hs, d_state, sizeof(hs), cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    bool crossed = hs.k0 < prev_k0 + len || (hs.k0 == prev_k0 + len && !(hs.s0 < T));
+    win = crossed ? (1 << 16) : std::min<int64_t>(win * 2, (int64_t)1 << 26);
+  }
+  return FC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// threshold search
+// ---------------------------------------------------------------------------------------------
+// first i in [0, n] with S[i] >= t, or n + 1 if none
+__device__ __forceinline__ int64_t lower_bound_S(const double* __restrict__ S, int64_t n, double t) {
+  int64_t lo = 0, hi = n + 1;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (S[mid] >= t) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+// systematic (smc.rs:255-272) / stratified (smc.rs:275-292): the shared walk stops at the first i
+// with !(cum < thr) i.e. S_i >= thr (or i == n); the index is (i - 1).min(n - 1), and i == 0
+// wraps in release builds to n - 1.
+__global__ void k_resample_walk(const double* __restrict__ S, int64_t n, int method, const double* __restrict__ us, uint64_t* __restrict__ idx) {
+  int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double nf = (double)n;
+  double thr = method == FC_RESAMPLE_SYSTEMATIC ? __dadd_rn(__ddiv_rn(us[0], nf), __ddiv_rn((double)j, nf))  // u = gen()/n; thr = u + j/n
+                                                : __ddiv_rn(__dadd_rn((double)j, us[j]), nf);                 // (j + u_j)/n
+  int64_t i = lower_bound_S(S, n, thr);
+  if (i > n) i = n;
+  int64_t k = (i == 0) ? n - 1 : (i - 1 < n - 1 ? i - 1 : n - 1);
+  if (!(thr == thr)) k = n - 1;  // NaN threshold: `cum < thr` is false at once => i = 0
+  idx[j] = (uint64_t)k;
+}
+// multinomial (smc.rs:295-314): per draw, first i with u <= cum (cum = S_{i+1}), default n - 1
+__global__ void k_resample_multinomial(const double* __restrict__ S, int64_t n, const double* __restrict__ us, uint64_t* __restrict__ idx) {
+  int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double u = us[j];
+  int64_t lo = 1, hi = n + 1;  // over S[1..n]
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (S[mid] >= u) hi = mid; else lo = mid + 1;
+  }
+  idx[j] = (uint64_t)((lo <= n && u == u) ? lo - 1 : n - 1);
+}
+
+struct ResampleWork {
+  DevBuf<double> S, scratch;
+  DevBuf<char> work;
+  int32_t reserve(int64_t n) {
+    FC_CUDA(S.reserve(n + 2));
+    FC_CUDA(scratch.reserve(RD_BLOCKS + 8));
+    FC_CUDA(work.reserve(64 + (cdiv(std::max<int64_t>(n, 1), SC_TILE) + 8) * sizeof(Inc2)));
+    return FC_OK;
+  }
+};
+
+int32_t resample_dev(int method, const double* d_w, int64_t n, const double* d_us, uint64_t* d_idx, ResampleWork& W, cudaStream_t st, uint64_t* launches) {
+  if (n == 0) return FC_OK;
+  if (method < FC_RESAMPLE_MULTINOMIAL || method > FC_RESAMPLE_STRATIFIED) { set_error("bad resampling method %d", method); return FC_ERR_INVALID_ARGUMENT; }
+  FC_TRY(W.reserve(n));
+  FC_TRY(exact_prefix_sums(d_w, n, W.S.p, W.work.p, W.scratch.p, st, launches));
+  unsigned nb = (unsigned)cdiv(n, 256);
+  if (method == FC_RESAMPLE_MULTINOMIAL) k_resample_multinomial<<<nb, 256, 0, st>>>(W.S.p, n, d_us, d_idx);
+  else k_resample_walk<<<nb, 256, 0, st>>>(W.S.p, n, method, d_us, d_idx);
+  FC_KERNEL_CHECK();
+  if (launches) *launches += 1;
+  return FC_OK;
+}
+
+ResampleWork* resample_work_new() { return new ResampleWork(); }
+void resample_work_free(ResampleWork* w) { delete w; }
+
+static cudaStream_t g_util_stream = nullptr;
+static int32_t util_stream(cudaStream_t* st) {
+  if (!g_util_stream) FC_CUDA(cudaStreamCreateWithFlags(&g_util_stream, cudaStreamNonBlocking));
+  *st = g_util_stream;
+  return FC_OK;
+}
+
+__global__ void k_exp_shift(const double* __restrict__ x, double lse, double* __restrict__ out, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = exp(x[i] - lse);
+}
+
+}  // namespace fc
+
+extern "C" {
+
+// systematic / stratified / multinomial indices with the uniforms passed explicitly
+// (1 raw uniform for systematic, n for the others). Host buffers.
+int32_t fc_resample(int32_t method, const double* h_w, size_t n, const double* h_uniforms, uint64_t* h_idx) {
+  using namespace fc;
+  if (n == 0) return FC_OK;
+  if (!h_w || !h_uniforms || !h_idx) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
+  cudaStream_t st;
+  FC_TRY(util_stream(&st));
+  size_t nu = method == FC_RESAMPLE_SYSTEMATIC ? 1 : n;
+  DevBuf<double> w, us;
+  DevBuf<uint64_t> idx;
+  FC_CUDA(w.reserve(n)); FC_CUDA(us.reserve(nu)); FC_CUDA(idx.reserve(n));
+  FC_CUDA(cudaMemcpyAsync(w.p, h_w, n * 8, cudaMemcpyHostToDevice, st));
+  FC_CUDA(cudaMemcpyAsync(us.p, h_uniforms, nu * 8, cudaMemcpyHostToDevice, st));
+  ResampleWork W;
+  FC_TRY(resample_dev(method, w.p, (int64_t)n, us.p, idx.p, W, st, nullptr));
+  FC_CUDA(cudaMemcpyAsync(h_idx, idx.p, n * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  return FC_OK;
+}
+
+int32_t fc_resample_dev(int32_t method, const double* d_w, size_t n, const double* d_uniforms, uint64_t* d_idx, void* stream) {
+  using namespace fc;
+  static thread_local ResampleWork W;  // grows to the largest n seen on this thread
+  return resample_dev(method, d_w, (int64_t)n, d_uniforms, d_idx, W, (cudaStream_t)stream, nullptr);
+}
+
+// the sequentially rounded prefix sums themselves (S[0..n]), for tests and multi-GPU carries
+int32_t fc_exact_prefix_sums(const double* h_w, size_t n, double* h_S) {
+  using namespace fc;
+  cudaStream_t st;
+  FC_TRY(util_stream(&st));
+  DevBuf<double> w;
+  ResampleWork W;
+  FC_CUDA(w.reserve(n));
+  FC_TRY(W.reserve((int64_t)n));
+  if (n) FC_CUDA(cudaMemcpyAsync(w.p, h_w, n * 8, cudaMemcpyHostToDevice, st));
+  FC_TRY(exact_prefix_sums(w.p, (int64_t)n, W.S.p, W.work.p, W.scratch.p, st, nullptr));
+  FC_CUDA(cudaMemcpyAsync(h_S, W.S.p, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  return FC_OK;
+}
+
+int32_t fc_log_sum_exp(const double* h_x, size_t n, double* out) {  // numerical.rs:15-38
+  using namespace fc;
+  if (n == 0) { *out = -INFINITY; return FC_OK; }
+  cudaStream_t st;
+  FC_TRY(util_stream(&st));
+  DevBuf<double> x, scratch;
+  FC_CUDA(x.reserve(n)); FC_CUDA(scratch.reserve(RD_BLOCKS + 8));
+  FC_CUDA(cudaMemcpyAsync(x.p, h_x, n * 8, cudaMemcpyHostToDevice, st));
+  return dev_log_sum_exp(x.p, (int64_t)n, scratch.p, out, st);
+}
+
+int32_t fc_ess(const double* h_w, size_t n, double* out) {  // smc.rs:230-233
+  using namespace fc;
+  cudaStream_t st;
+  FC_TRY(util_stream(&st));
+  DevBuf<double> x, scratch;
+  FC_CUDA(x.reserve(n)); FC_CUDA(scratch.reserve(RD_BLOCKS + 8));
+  if (n) FC_CUDA(cudaMemcpyAsync(x.p, h_w, n * 8, cudaMemcpyHostToDevice, st));
+  FC_TRY(dev_reduce(2, x.p, (int64_t)n, 0.0, scratch.p, scratch.p + RD_BLOCKS, st));
+  double s;
+  FC_CUDA(cudaMemcpyAsync(&s, scratch.p + RD_BLOCKS, 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  *out = 1.0 / s;
+  return FC_OK;
+}
+
+int32_t fc_normalize_log_probs(const double* h_x, size_t n, double* h_out) {  // numerical.rs:87-90
+  using namespace fc;
+  if (n == 0) return FC_OK;
+  cudaStream_t st;
+  FC_TRY(util_stream(&st));
+  DevBuf<double> x, scratch;
+  FC_CUDA(x.reserve(n)); FC_CUDA(scratch.reserve(RD_BLOCKS + 8));
+  FC_CUDA(cudaMemcpyAsync(x.p, h_x, n * 8, cudaMemcpyHostToDevice, st));
+  double lse;
+  FC_TRY(dev_log_sum_exp(x.p, (int64_t)n, scratch.p, &lse, st));
+  k_exp_shift<<<(unsigned)cdiv((int64_t)n, 256), 256, 0, st>>>(x.p, lse, x.p, (int64_t)n);
+  FC_KERNEL_CHECK();
+  FC_CUDA(cudaMemcpyAsync(h_out, x.p, n * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  return FC_OK;
+}
+}

@@ -205,10 +205,34 @@ typedef struct fc_mh_config {
   double gamma;           /* 0.7               */
 } fc_mh_config;
 typedef struct fc_mh_stats { uint64_t n_accept; uint64_t n_steps; } fc_mh_stats;
+/* SiteProposal override for an f64 site (mh.rs:145-161), matched by address string */
+enum { FC_PROPOSAL_GAUSSIAN = 0, FC_PROPOSAL_LOGSPACE = 1, FC_PROPOSAL_REFLECT = 2, FC_PROPOSAL_PRIOR_RESAMPLE = 3 };
+typedef struct fc_site_proposal {
+  const char* address;
+  int32_t kind;           /* FC_PROPOSAL_* */
+  int32_t _pad;
+  double  lower, upper;   /* REFLECT bounds */
+} fc_site_proposal;
+typedef struct fc_mh_session fc_mh_session;
 void    fc_mh_config_default(fc_mh_config* cfg);
+/* adaptive_mcmc_chain_with_overrides set-up (mh.rs:938-965): prior init, one scoring pass.
+ * Chain c uses the random stream of global chain first_chain + c. */
+int32_t fc_mh_create(fc_program* p, const fc_mh_config* cfg, uint64_t seed, size_t C, size_t n_warmup,
+                     const fc_site_proposal* overrides, size_t n_overrides, uint64_t first_chain,
+                     fc_mh_session** out);
+int32_t fc_mh_destroy(fc_mh_session* s);
+/* n single_site_mh_step()s for every chain (mh.rs:698-744); the first n_warmup steps adapt. */
+int32_t fc_mh_step(fc_mh_session* s, size_t n);
+/* h_q [d_cont][C], h_qd [d_disc][C], h_lp [C], h_scales [n_sites][C] (DiminishingAdaptation
+ * scales, global address order); any pointer may be NULL. */
+int32_t fc_mh_get(fc_mh_session* s, double* h_q, int64_t* h_qd, double* h_lp, fc_mh_stats* h_stats,
+                  double* h_scales);
+int32_t fc_mh_n_sites(const fc_mh_session* s, int64_t* n);
+/* adaptive_mcmc_chain (mh.rs:921-1014). Every thin-th sampling step is kept:
+ * h_draws [n_kept][d_cont][C], h_ddraws [n_kept][d_disc][C], h_lp [n_kept][C]. */
 int32_t fc_mh_run(fc_program* p, const fc_mh_config* cfg, uint64_t seed, size_t C,
-                  size_t n_warmup, size_t n_samples, size_t thin, double* h_draws, double* h_lp,
-                  fc_mh_stats* h_stats);
+                  size_t n_warmup, size_t n_samples, size_t thin, double* h_draws, int64_t* h_ddraws,
+                  double* h_lp, fc_mh_stats* h_stats);
 
 /* ---- SMC (src/inference/smc.rs) ---- */
 enum { FC_RESAMPLE_MULTINOMIAL = 0, FC_RESAMPLE_SYSTEMATIC = 1, FC_RESAMPLE_STRATIFIED = 2 };
@@ -218,18 +242,35 @@ typedef struct fc_smc_config {  /* SMCConfig, smc.rs:172-189 */
   double   ess_threshold;       /* 0.5 */
   uint64_t rejuvenation_steps;  /* 0   */
 } fc_smc_config;
+typedef struct fc_smc_session fc_smc_session;
 void    fc_smc_config_default(fc_smc_config* cfg);
 /* adaptive_smc (smc.rs:455-581). h_values [d_cont][P], h_dvalues [d_disc][P]; outputs may be NULL.
  * n_temper_steps returns the number of tempering steps taken. */
 int32_t fc_smc_run(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t P,
                    double* h_values, int64_t* h_dvalues, double* h_weight, double* h_log_weight,
                    double* log_evidence, uint64_t* n_temper_steps);
+/* The same, one tempering step at a time, particles resident on the device:
+ * create = smc_prior_particles (smc.rs:764-790); step = one pass of the while loop (smc.rs:499-560:
+ * next_beta, reweight, evidence, resample, rejuvenate) and returns the new beta (1.0 = finished);
+ * get = final normalisation (smc.rs:565-575) + copy-out. Particle j of this call uses the random
+ * stream of global particle first_particle + j. */
+int32_t fc_smc_create(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t P,
+                      uint64_t first_particle, fc_smc_session** out);
+int32_t fc_smc_step(fc_smc_session* s, double* beta_out);
+int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, double* h_weight,
+                   double* h_log_weight, double* log_evidence, uint64_t* n_temper_steps);
+int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dvalues,
+                            double** d_log_w, double** d_loglik);
+int32_t fc_smc_destroy(fc_smc_session* s);
 /* systematic/stratified/multinomial_indices (smc.rs:255-314) with the uniforms passed explicitly:
- * 1 uniform for systematic (the raw rng.gen::<f64>(), before /n), n for the others. */
+ * 1 uniform for systematic (the raw rng.gen::<f64>(), before /n), n for the others.
+ * Indices are bit-exact w.r.t. the reference's sequential running sum. */
 int32_t fc_resample(int32_t method, const double* h_w, size_t n, const double* h_uniforms,
                     uint64_t* h_idx);
 int32_t fc_resample_dev(int32_t method, const double* d_w, size_t n, const double* d_uniforms,
                         uint64_t* d_idx, void* stream);
+/* S[0..n]: the sequentially rounded running sums cum_weight takes in smc.rs:262-268 */
+int32_t fc_exact_prefix_sums(const double* h_w, size_t n, double* h_S);
 int32_t fc_log_sum_exp(const double* h_x, size_t n, double* out);        /* numerical.rs:15-38 */
 int32_t fc_ess(const double* h_w, size_t n, double* out);                /* smc.rs:230-233     */
 int32_t fc_normalize_log_probs(const double* h_x, size_t n, double* h_out); /* numerical.rs:87-90 */
