@@ -282,4 +282,48 @@ int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, doub
   }
   return fc::diagnostics_host(h_draws, S, d, C, what, h_mean, h_std, h_rhat, h_ess);
 }
+// Per-rank partial statistics for multi-GPU R-hat / ESS: split-half means and sums of
+// squares per chain, chain means, and the chain-SUM of autocovariances per lag. A rank holds
+// C_local chains; the cross-rank combine needs only all-reduces of O(d * (lags + 3)) doubles
+// plus the per-chain means (fugue_b200/dist.py).
+//   h_seg_mean, h_seg_ss : [d][nseg*C]  (nseg = 2 if S >= 2 else 1; order c0h0, c0h1, c1h0, ...)
+//   h_cmean              : [d][C]
+//   h_lagsum             : [d][max_lag+1], max_lag = min(S-1, 2048)   (NULL or S < 4: skipped)
+int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean, double* h_seg_ss, double* h_cmean, double* h_lagsum) {
+  using namespace fc;
+  if (d == 0 || C == 0 || S == 0) return FC_OK;
+  if (!g_diag_stream) FC_CUDA(cudaStreamCreateWithFlags(&g_diag_stream, cudaStreamNonBlocking));
+  cudaStream_t st = g_diag_stream;
+  DiagWork W;
+  size_t n = S * d * C;
+  FC_CUDA(W.x.reserve(n));
+  FC_CUDA(cudaMemcpyAsync(W.x.p, h_draws, n * 8, cudaMemcpyHostToDevice, st));
+  Draws D{W.x.p, (int64_t)S, (int64_t)d, (int64_t)C};
+  const unsigned cbx = (unsigned)cdiv((int64_t)C, 128);
+  int nseg = (S / 2 > 0) ? 2 : 1;
+  int64_t m = (int64_t)nseg * C;
+  int64_t max_lag = std::min<int64_t>((int64_t)S - 1, 2048);
+  bool do_acov = h_lagsum && S >= 4;
+  int64_t per_param = m * 2 + (do_acov ? ((max_lag + 1 + (int64_t)S) * (int64_t)C) : 0);
+  int64_t batch = std::max<int64_t>(1, std::min<int64_t>((int64_t)d, (int64_t)(1 << 26) / std::max<int64_t>(1, per_param)));
+  FC_CUDA(W.a.reserve(batch * m)); FC_CUDA(W.b.reserve(batch * m));
+  if (do_acov) { FC_CUDA(W.cen.reserve(batch * S * C)); FC_CUDA(W.acov.reserve(batch * (max_lag + 1) * C)); FC_CUDA(W.lagsum.reserve(batch * (max_lag + 1))); FC_CUDA(W.out.reserve(batch * C)); }
+  for (int64_t k0 = 0; k0 < (int64_t)d; k0 += batch) {
+    int64_t nk = std::min<int64_t>(batch, (int64_t)d - k0);
+    k_seg_stats<<<dim3(cbx, (unsigned)nk), 128, 0, st>>>(D, k0, nk, 1, W.a.p, W.b.p);
+    FC_KERNEL_CHECK();
+    if (h_seg_mean) FC_CUDA(cudaMemcpyAsync(h_seg_mean + k0 * m, W.a.p, nk * m * 8, cudaMemcpyDeviceToHost, st));
+    if (h_seg_ss) FC_CUDA(cudaMemcpyAsync(h_seg_ss + k0 * m, W.b.p, nk * m * 8, cudaMemcpyDeviceToHost, st));
+    if (do_acov) {
+      k_center<<<dim3(cbx, (unsigned)nk), 128, 0, st>>>(D, k0, nk, W.cen.p, W.out.p);
+      k_acov<<<dim3(cbx, (unsigned)nk, (unsigned)cdiv(max_lag + 1, LAG_CHUNK)), 128, 0, st>>>(W.cen.p, (int64_t)S, (int64_t)C, nk, max_lag, W.acov.p);
+      k_acov_chainsum<<<dim3((unsigned)cdiv(max_lag + 1, 128), (unsigned)nk), 128, 0, st>>>(W.acov.p, (int64_t)C, nk, max_lag, W.lagsum.p);
+      FC_KERNEL_CHECK();
+      if (h_cmean) FC_CUDA(cudaMemcpyAsync(h_cmean + k0 * C, W.out.p, nk * C * 8, cudaMemcpyDeviceToHost, st));
+      FC_CUDA(cudaMemcpyAsync(h_lagsum + k0 * (max_lag + 1), W.lagsum.p, nk * (max_lag + 1) * 8, cudaMemcpyDeviceToHost, st));
+    }
+    FC_CUDA(cudaStreamSynchronize(st));
+  }
+  return FC_OK;
+}
 }

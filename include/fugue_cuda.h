@@ -284,6 +284,12 @@ int32_t fc_ess_multichain(const double* h_draws, size_t S, size_t C, double* out
 int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, double* h_mean,
                        double* h_std, double* h_rhat, double* h_ess);
 
+/* Per-rank partial statistics for multi-GPU R-hat / ESS (chains sharded over ranks): split-half
+ * means / sums of squares per chain [d][2C], chain means [d][C], and chain-summed autocovariances
+ * per lag [d][min(S-1,2048)+1]. Combined across ranks by all-reduce (fugue_b200/dist.py). */
+int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean,
+                         double* h_seg_ss, double* h_cmean, double* h_lagsum);
+
 #ifdef __cplusplus
 }
 #endif
