@@ -20,6 +20,7 @@
 // FP64 has no tcgen05 path; DMMA is the tensor-core route that meets the 1e-10 gate.
 #include "fc_dist.cuh"
 #include "fc_fastmath.cuh"
+#include <cstdlib>
 #include "fc_internal.cuh"
 
 namespace fc {
@@ -27,8 +28,9 @@ namespace fc {
 #define DN_BC 128     // chains per CTA
 #define DN_TN 32      // observation rows per tile
 #define DN_LDB 132    // beta smem row stride (doubles), == 4 mod 16 -> conflict-free B fragments
-#define DN_LDW 20     // per-warp residual tile row stride (doubles)
-#define DN_THREADS 256
+#define DN_LDW(NT) ((NT) == 2 ? 20 : 12)  // per-warp residual tile row stride (doubles), == 4 mod 8
+#define DN_NW(NT) (16 / (NT))             // warps per CTA: each owns NT n-tiles of 8 chains
+#define DN_THREADS(NT) (32 * DN_NW(NT))
 #define DN_STAGES 2
 
 enum { GLM_GENERIC = 0, GLM_BERN_SIGMOID = 1, GLM_POISSON_ID = 2 };
@@ -120,9 +122,10 @@ __device__ __noinline__ void glm_generic_elem(const DOp& op, int dj, double sarg
 
 // MT = number of 8-row gradient tiles per warp (K padded to 8*MT); GRAD=false skips the
 // second contraction (value only: MH / SMC).
-template <int MODE, bool GRAD, int MT>
-__global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_constant__ DenseArgs A) {
+template <int MODE, bool GRAD, int MT, int NT>
+__global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_constant__ DenseArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int NW = DN_NW(NT), NTHR = DN_THREADS(NT), LDW = DN_LDW(NT), WC = 8 * NT;  // WC = chains per warp
   const int K = A.K;
   const int KP4 = (K + 3) & ~3;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -132,10 +135,11 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
   const DOp& op = A.op;
 
   // ---- shared memory carve-up ----
+  int* done = (int*)(smem_raw + 64);                                       // per-stage warp arrival counters
   uint64_t* bars = (uint64_t*)smem_raw;                                   // DN_STAGES mbarriers
   double* s_beta = (double*)(smem_raw + 128);                             // [KP4][DN_LDB]
   double* s_w = s_beta + (size_t)KP4 * DN_LDB;                            // [8 warps][DN_TN][DN_LDW]
-  double* s_x = s_w + 8 * DN_TN * DN_LDW;                                 // [DN_STAGES][DN_TN*K + pad]
+  double* s_x = s_w + NW * DN_TN * LDW;                                 // [DN_STAGES][DN_TN*K + pad]
   const int x_stage_elems = ((DN_TN * K + 8 + 15) & ~15);                 // + zero pad for k >= K reads
 
   const int64_t row_begin = (int64_t)blockIdx.y * A.rows_per_split;
@@ -143,12 +147,12 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
   const int n_tiles = (int)((row_end - row_begin + DN_TN - 1) / DN_TN);
 
   if (tid == 0) {
-    for (int s = 0; s < DN_STAGES; s++) mbar_init(&bars[s], 1);
+    for (int s = 0; s < DN_STAGES; s++) { mbar_init(&bars[s], 1); done[s] = 0; }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // beta tile: s_beta[k][cl] = q[crow[slot+k]][cb0+cl]; zero for padded k / chains
   const int dslot = op.p[A.dj].t[A.dt].slot;
-  for (int idx = tid; idx < KP4 * DN_BC; idx += DN_THREADS) {
+  for (int idx = tid; idx < KP4 * DN_BC; idx += NTHR) {
     int k = idx / DN_BC, cl = idx % DN_BC;
     double v = 0.0;
     if (k < K && cb0 + cl < C) v = A.q[(int64_t)A.crow[dslot + k] * C + cb0 + cl];
@@ -156,7 +160,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
   }
   // zero the pad after each X stage once (bulk copies never touch it)
   for (int s = 0; s < DN_STAGES; s++)
-    for (int idx = DN_TN * K + tid; idx < x_stage_elems; idx += DN_THREADS) s_x[(size_t)s * x_stage_elems + idx] = 0.0;
+    for (int idx = DN_TN * K + tid; idx < x_stage_elems; idx += NTHR) s_x[(size_t)s * x_stage_elems + idx] = 0.0;
   __syncthreads();
 
   auto issue_tile = [&](int t) {  // called by thread 0 only, full tiles only
@@ -176,13 +180,13 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
   }
 
   // ---- per-thread chain columns: c = cb0 + warp*16 + nt*8 + tig*2 + j ----
-  double off[2][2];                 // CONST/LATENT part of the dense parameter
-  double po[3][2][2], pdl[3][2][2]; // the other (per-chain) parameters, linked, and dlink
+  double off[NT][2];                 // CONST/LATENT part of the dense parameter
+  double po[3][NT][2], pdl[3][NT][2]; // the other (per-chain) parameters, linked, and dlink
 #pragma unroll
-  for (int nt = 0; nt < 2; nt++)
+  for (int nt = 0; nt < NT; nt++)
 #pragma unroll
     for (int j = 0; j < 2; j++) {
-      int64_t c = cb0 + warp * 16 + nt * 8 + tig * 2 + j;
+      int64_t c = cb0 + warp * WC + nt * 8 + tig * 2 + j;
       bool ok = c < C;
       double s = 0.0;
 #pragma unroll
@@ -209,21 +213,21 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
       }
     }
 
-  double g[MT][2][2];  // gradient tile fragments: k = mt*8+gid, c as above
+  double g[MT][NT][2];  // gradient tile fragments: k = mt*8+gid, c as above
 #pragma unroll
   for (int mt = 0; mt < MT; mt++)
 #pragma unroll
-    for (int nt = 0; nt < 2; nt++) g[mt][nt][0] = g[mt][nt][1] = 0.0;
-  double a_lp[2][2], a_w[2][2], a_p[3][2][2];
+    for (int nt = 0; nt < NT; nt++) g[mt][nt][0] = g[mt][nt][1] = 0.0;
+  double a_lp[NT][2], a_w[NT][2], a_p[3][NT][2];
 #pragma unroll
-  for (int nt = 0; nt < 2; nt++)
+  for (int nt = 0; nt < NT; nt++)
 #pragma unroll
     for (int j = 0; j < 2; j++) {
       a_lp[nt][j] = a_w[nt][j] = 0.0;
       a_p[0][nt][j] = a_p[1][nt][j] = a_p[2][nt][j] = 0.0;
     }
 
-  double* my_w = s_w + warp * DN_TN * DN_LDW;
+  double* my_w = s_w + warp * DN_TN * LDW;
   const double qnan = __longlong_as_double(0x7ff8000000000000LL);
   const double lnk_lo = op.p[A.dj].lo, lnk_hi = op.p[A.dj].hi;
   const int lnk = op.p[A.dj].link;
@@ -249,28 +253,29 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
       mbar_wait(&bars[s], (uint32_t)((t / DN_STAGES) & 1));
     } else {
       // cooperative copy + zero fill of the missing rows
+      __syncthreads();  // every warp has left tile t-1 (and so t-2, the stage's previous user)
       const double* src = A.X + r0 * K;
-      for (int idx = tid; idx < DN_TN * K; idx += DN_THREADS) xs[idx] = (idx < valid * K) ? __ldg(src + idx) : 0.0;
+      for (int idx = tid; idx < DN_TN * K; idx += NTHR) xs[idx] = (idx < valid * K) ? __ldg(src + idx) : 0.0;
       __syncthreads();
     }
 
     // ---- contraction 1: eta[32][16 per warp] = X_tile[32][K] * beta[K][16] ----
-    double eta[4][2][2];
+    double eta[4][NT][2];
 #pragma unroll
     for (int mt = 0; mt < 4; mt++)
 #pragma unroll
-      for (int nt = 0; nt < 2; nt++) eta[mt][nt][0] = eta[mt][nt][1] = 0.0;
+      for (int nt = 0; nt < NT; nt++) eta[mt][nt][0] = eta[mt][nt][1] = 0.0;
 #pragma unroll 5
     for (int k4 = 0; k4 < KP4; k4 += 4) {
-      double a[4], b[2];
+      double a[4], b[NT];
 #pragma unroll
       for (int mt = 0; mt < 4; mt++) a[mt] = xs[(mt * 8 + gid) * K + k4 + tig];
 #pragma unroll
-      for (int nt = 0; nt < 2; nt++) b[nt] = s_beta[(k4 + tig) * DN_LDB + warp * 16 + nt * 8 + gid];
+      for (int nt = 0; nt < NT; nt++) b[nt] = s_beta[(k4 + tig) * DN_LDB + warp * WC + nt * 8 + gid];
 #pragma unroll
       for (int mt = 0; mt < 4; mt++)
 #pragma unroll
-        for (int nt = 0; nt < 2; nt++) dmma884(eta[mt][nt][0], eta[mt][nt][1], a[mt], b[nt]);
+        for (int nt = 0; nt < NT; nt++) dmma884(eta[mt][nt][0], eta[mt][nt][1], a[mt], b[nt]);
     }
 
     // ---- link + log-density + residual on the accumulator fragments ----
@@ -278,7 +283,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
     for (int mt = 0; mt < 4; mt++) {
       const bool rv = (mt * 8 + gid) < valid;
 #pragma unroll
-      for (int nt = 0; nt < 2; nt++) {
+      for (int nt = 0; nt < NT; nt++) {
         double wv[2];
 #pragma unroll
         for (int j = 0; j < 2; j++) {
@@ -322,7 +327,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
           else w = 0.0;
           wv[j] = w;
         }
-        if (GRAD) *(double2*)&my_w[(mt * 8 + gid) * DN_LDW + nt * 8 + tig * 2] = make_double2(wv[0], wv[1]);
+        if (GRAD) *(double2*)&my_w[(mt * 8 + gid) * LDW + nt * 8 + tig * 2] = make_double2(wv[0], wv[1]);
       }
     }
 
@@ -331,16 +336,16 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
       __syncwarp();
 #pragma unroll
       for (int i4 = 0; i4 < DN_TN; i4 += 4) {
-        double b[2];
+        double b[NT];
 #pragma unroll
-        for (int nt = 0; nt < 2; nt++) b[nt] = my_w[(i4 + tig) * DN_LDW + nt * 8 + gid];
+        for (int nt = 0; nt < NT; nt++) b[nt] = my_w[(i4 + tig) * LDW + nt * 8 + gid];
         const double* xr = xs + (i4 + tig) * K + gid;
 #pragma unroll
         for (int mt = 0; mt < MT; mt++) {
           if (mt * 8 < K) {  // k >= K overshoots by < 8 doubles into the zero pad only
             double a = xr[mt * 8];
 #pragma unroll
-            for (int nt = 0; nt < 2; nt++) dmma884(g[mt][nt][0], g[mt][nt][1], a, b[nt]);
+            for (int nt = 0; nt < NT; nt++) dmma884(g[mt][nt][0], g[mt][nt][1], a, b[nt]);
           }
         }
       }
@@ -348,15 +353,26 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
     }
 
     // ---- release the stage and refill it ----
-    __syncthreads();
-    if (tid == 0 && t + DN_STAGES < n_tiles && tile_is_bulk(t + DN_STAGES)) issue_tile(t + DN_STAGES);
+    // Warps are NOT barriered against each other: the last warp to leave the stage refills it, so a
+    // warp in its link/log-density phase overlaps other warps' DMMA phases (they drift <= 1 tile).
+    __syncwarp();
+    if (lane == 0) {
+      int old = atomicAdd(&done[s], 1);
+      if (old == NW - 1) {
+        atomicExch(&done[s], 0);
+        if (t + DN_STAGES < n_tiles && tile_is_bulk(t + DN_STAGES)) {
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          issue_tile(t + DN_STAGES);
+        }
+      }
+    }
   }
 
   // ---- write this CTA's partial: lp / reduced scalars (sum over gid via shuffles), then g ----
   const int lp_slot = op.is_sample ? 0 : 1;
   double* part = A.part + (int64_t)blockIdx.y * A.n_acc * C;
 #pragma unroll
-  for (int nt = 0; nt < 2; nt++)
+  for (int nt = 0; nt < NT; nt++)
 #pragma unroll
     for (int j = 0; j < 2; j++) {
       double v_lp = a_lp[nt][j], v_w = a_w[nt][j], v_p[3] = {a_p[0][nt][j], a_p[1][nt][j], a_p[2][nt][j]};
@@ -367,7 +383,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
 #pragma unroll
         for (int pj = 0; pj < 3; pj++) v_p[pj] += __shfl_xor_sync(0xffffffffu, v_p[pj], o);
       }
-      int64_t c = cb0 + warp * 16 + nt * 8 + tig * 2 + j;
+      int64_t c = cb0 + warp * WC + nt * 8 + tig * 2 + j;
       if (gid == 0 && c < C) {
         for (int a = 0; a < 3; a++) part[(int64_t)a * C + c] = (a == lp_slot) ? v_lp : 0.0;
         if (GRAD) {
@@ -389,10 +405,10 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
       int k = mt * 8 + gid;
       if (k < K) {
 #pragma unroll
-        for (int nt = 0; nt < 2; nt++)
+        for (int nt = 0; nt < NT; nt++)
 #pragma unroll
           for (int j = 0; j < 2; j++) {
-            int64_t c = cb0 + warp * 16 + nt * 8 + tig * 2 + j;
+            int64_t c = cb0 + warp * WC + nt * 8 + tig * 2 + j;
             if (c < C) part[(int64_t)(3 + A.n_red + k) * C + c] = g[mt][nt][j];
           }
       }
@@ -400,12 +416,14 @@ __global__ void __launch_bounds__(DN_THREADS, 1) k_dense_glm(const __grid_consta
   }
 }
 
-static size_t dense_smem_bytes(int K) {
+static size_t dense_smem_bytes(int K, int NT) {
   int KP4 = (K + 3) & ~3;
   size_t x_stage = ((size_t)DN_TN * K + 8 + 15) & ~(size_t)15;
-  return 128 + sizeof(double) * ((size_t)KP4 * DN_LDB + 8 * DN_TN * DN_LDW + DN_STAGES * x_stage);
+  return 128 + sizeof(double) * ((size_t)KP4 * DN_LDB + DN_NW(NT) * DN_TN * DN_LDW(NT) + DN_STAGES * x_stage);
 }
 
+// warps per CTA = 16 / NT: NT = 1 -> 16 warps (8 chains each, <= 128 registers), NT = 2 -> 8 warps
+static int g_dense_nt = getenv("FC_DENSE_NT") ? atoi(getenv("FC_DENSE_NT")) : 1;
 static int g_dense_sms = 0;
 int64_t dense_plate_splits(const fc_program* P, const PlateInfo& pl, int64_t C) {
   if (!g_dense_sms) {
@@ -425,13 +443,13 @@ int64_t dense_plate_splits(const fc_program* P, const PlateInfo& pl, int64_t C) 
   return std::max<int64_t>(1, S);
 }
 
-template <int MODE, bool GRAD>
+template <int MODE, bool GRAD, int NT>
 static int32_t launch_mt(const DenseArgs& A, dim3 grid, size_t smem, cudaStream_t st) {
   int MT = (A.K + 7) / 8;
 #define DN_LAUNCH(M)                                                                                          \
   {                                                                                                           \
-    FC_CUDA(cudaFuncSetAttribute(k_dense_glm<MODE, GRAD, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    k_dense_glm<MODE, GRAD, M><<<grid, DN_THREADS, smem, st>>>(A);                                            \
+    FC_CUDA(cudaFuncSetAttribute(k_dense_glm<MODE, GRAD, M, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    k_dense_glm<MODE, GRAD, M, NT><<<grid, DN_THREADS(NT), smem, st>>>(A);                                            \
   }
   if (!GRAD) DN_LAUNCH(1)
   else if (MT <= 1) DN_LAUNCH(1)
@@ -462,7 +480,8 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
   S = cdiv(A.N, A.rows_per_split);
   *n_splits = S;
   dim3 grid((unsigned)cdiv(C, DN_BC), (unsigned)S);
-  size_t smem = dense_smem_bytes(K);
+  const int NT = g_dense_nt;
+  size_t smem = dense_smem_bytes(K, NT);
   // single-parameter fast paths (link and distribution fixed at compile time)
   bool only_dense_param = true;
   for (int t = 0; t < 3; t++) {
@@ -479,9 +498,13 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
     FC_CUDA(cudaEventCreate(&e1));
     FC_CUDA(cudaEventRecord(e0, P->stream));
   }
-  if (mode == GLM_BERN_SIGMOID) rc = grad ? launch_mt<GLM_BERN_SIGMOID, true>(A, grid, smem, P->stream) : launch_mt<GLM_BERN_SIGMOID, false>(A, grid, smem, P->stream);
-  else if (mode == GLM_POISSON_ID) rc = grad ? launch_mt<GLM_POISSON_ID, true>(A, grid, smem, P->stream) : launch_mt<GLM_POISSON_ID, false>(A, grid, smem, P->stream);
-  else rc = grad ? launch_mt<GLM_GENERIC, true>(A, grid, smem, P->stream) : launch_mt<GLM_GENERIC, false>(A, grid, smem, P->stream);
+#define DN_DISPATCH(MODE_)                                                                              \
+  rc = NT == 1 ? (grad ? launch_mt<MODE_, true, 1>(A, grid, smem, P->stream) : launch_mt<MODE_, false, 1>(A, grid, smem, P->stream)) \
+               : (grad ? launch_mt<MODE_, true, 2>(A, grid, smem, P->stream) : launch_mt<MODE_, false, 2>(A, grid, smem, P->stream));
+  if (mode == GLM_BERN_SIGMOID) { DN_DISPATCH(GLM_BERN_SIGMOID) }
+  else if (mode == GLM_POISSON_ID) { DN_DISPATCH(GLM_POISSON_ID) }
+  else { DN_DISPATCH(GLM_GENERIC) }
+#undef DN_DISPATCH
   if (P->timing) {
     FC_CUDA(cudaEventRecord(e1, P->stream));
     P->timing_events.emplace_back(e0, e1);
