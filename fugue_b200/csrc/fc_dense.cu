@@ -514,3 +514,22 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
 }
 
 }  // namespace fc
+
+// accuracy probe for fc_fastmath.cuh (tests/test_gpu_fastmath.py): op 0 exp, 1 log, 2 reciprocal
+namespace fc {
+__global__ void k_debug_fastmath(int op, const double* __restrict__ x, int64_t n, double* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double v = x[i];
+  out[i] = op == 0 ? fast_exp(v) : (op == 1 ? fast_log(v) : fast_rcp(v));
+}
+}  // namespace fc
+extern "C" int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out) {
+  fc::DevBuf<double> x, o;
+  FC_CUDA(x.reserve(n)); FC_CUDA(o.reserve(n));
+  FC_CUDA(cudaMemcpy(x.p, h_x, n * 8, cudaMemcpyHostToDevice));
+  fc::k_debug_fastmath<<<(unsigned)fc::cdiv((int64_t)n, 256), 256>>>(op, x.p, (int64_t)n, o.p);
+  FC_KERNEL_CHECK();
+  FC_CUDA(cudaMemcpy(h_out, o.p, n * 8, cudaMemcpyDeviceToHost));
+  return FC_OK;
+}

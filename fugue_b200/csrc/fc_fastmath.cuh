@@ -4,8 +4,7 @@
 // assume the argument ranges the kernels guarantee and stay within ~1 ulp:
 //   fast_exp : x clamped to [-708, 708]                      (Cody-Waite + degree-13 Taylor)
 //   fast_log : x a positive NORMAL double                    (fdlibm e_log.c polynomial)
-//   fast_rcp : x a positive normal double in [2^-1000, 2^1000] (MUFU.RCP64H seed + 2 Newton steps
-//              + residual correction)
+//   fast_rcp : x a positive normal double in [2^-1000, 2^1000] (MUFU.RCP64H seed + 2 Newton steps)
 // Accuracy is checked on the GPU against the CUDA library functions (tests/test_gpu_fastmath.py).
 #pragma once
 #include <cuda_runtime.h>
@@ -40,10 +39,8 @@ __device__ __forceinline__ double fast_exp(double x) {
 __device__ __forceinline__ double fast_rcp(double d) {
   double y;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
-  double e = fma(-d, y, 1.0);
-  y = fma(y, e, y);
-  e = fma(-d, y, 1.0);
-  y = fma(y, e, y);
+  double e = fma(-d, y, 1.0);   // seed is good to ~2^-20: two Newton steps reach 2^-80,
+  y = fma(y, e, y);             // i.e. the result is limited by the final rounding only
   e = fma(-d, y, 1.0);
   return fma(y, e, y);
 }

@@ -290,6 +290,9 @@ int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, doub
 int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean,
                          double* h_seg_ss, double* h_cmean, double* h_lagsum);
 
+/* accuracy probe of the kernels' branch-free FP64 primitives: op 0 exp, 1 log, 2 reciprocal */
+int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out);
+
 #ifdef __cplusplus
 }
 #endif
