@@ -14,6 +14,7 @@
 //                 the log-density and of the reduced gradient rows go to a partial buffer
 //   dense kernel  (fc_dense.cu) for plates whose parameter is a dense X*beta contraction
 //   k_finish      sums the partials in fixed order into lp3 / grad
+#include <cstdlib>
 #include "fc_dist.cuh"
 #include "fc_internal.cuh"
 
@@ -113,6 +114,9 @@ __global__ void k_scalar(const DOp* __restrict__ ops, int n_ops, const int32_t* 
 // ---------------------------------------------------------------------------------------
 #define PL_TX 32
 #define PL_TY 8
+#define PL_PF 4  // prefetch distance in plate iterations
+
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 struct PlateArgs {
   DOp op;
@@ -131,7 +135,7 @@ struct PlateArgs {
 };
 
 template <bool GRAD>
-__global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ PlateArgs A) {
+__global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate(const __grid_constant__ PlateArgs A) {
   const DOp& op = A.op;
   const int64_t C = A.C;
   const int64_t c = (int64_t)blockIdx.x * PL_TX + threadIdx.x;
@@ -148,7 +152,23 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
     for (int t = 0; t < 3; t++) acc_a[j][t] = acc_b[j][t] = 0.0;
 
   if (active) {
-    // element-invariant parameters are evaluated once per chain
+    // ---- everything that is constant along the plate for this chain is loaded / evaluated once:
+    //      CONST and LATENT term values, the latent factor of LATENT_X, both SELECT2 branches,
+    //      and whole parameters whose terms are all element-invariant ----
+    double tva[3][3], tvb[3][3];
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+#pragma unroll
+      for (int t = 0; t < 3; t++) {
+        tva[j][t] = tvb[j][t] = 0.0;
+        if (j >= op.n_params) continue;
+        const DTerm& tm = op.p[j].t[t];
+        if (tm.kind == FC_TERM_CONST) tva[j][t] = tm.c;
+        else if (tm.kind == FC_TERM_LATENT || tm.kind == FC_TERM_LATENT_X || tm.kind == FC_TERM_SELECT2) {
+          tva[j][t] = A.q[(int64_t)tm.row * C + c];
+          if (tm.kind == FC_TERM_SELECT2) tvb[j][t] = A.q[(int64_t)tm.row_b * C + c];
+        }
+      }
     double pv_inv[3] = {0.0, 0.0, 0.0}, dl_inv[3] = {0.0, 0.0, 0.0};
 #pragma unroll
     for (int j = 0; j < 3; j++) {
@@ -158,37 +178,70 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
         bool first = true;
 #pragma unroll
         for (int t = 0; t < 3; t++) {
-          const DTerm& tm = pr.t[t];
-          if (tm.kind == FC_TERM_NONE) continue;
-          double v = tm.kind == FC_TERM_CONST ? tm.c : A.q[(int64_t)tm.row * C + c];
-          s = first ? v : s + v;
+          if (pr.t[t].kind == FC_TERM_NONE) continue;
+          s = first ? tva[j][t] : s + tva[j][t];
           first = false;
         }
         pv_inv[j] = apply_link(pr.link, s, pr.lo, pr.hi, dl_inv[j]);
       }
     }
-    // Normal with an element-invariant sigma: hoist log(sigma) and 1/sigma out of the plate loop
-    const bool fast_normal = op.dist == FC_NORMAL && op.p[1].invariant;
-    double n_logsig = 0.0, n_inv = 0.0;
-    bool n_ok = false;
-    if (fast_normal) {
-      n_ok = pv_inv[1] > 0.0 && d_fin(pv_inv[1]);
-      if (n_ok) { n_logsig = log(pv_inv[1]); n_inv = 1.0 / pv_inv[1]; }
+    // Normal likelihood/prior: log(sigma) and 1/sigma are memoised on the sigma value (two
+    // entries: covers an element-invariant sigma and a SELECT2 sigma that takes two values)
+    const bool is_normal = op.dist == FC_NORMAL;
+    double mem_sig[2] = {qnan, qnan}, mem_log[2] = {0.0, 0.0}, mem_inv[2] = {0.0, 0.0};
+    // two-valued discrete likelihoods with an invariant parameter: both log-probs up front
+    const bool two_valued = (op.dist == FC_BERNOULLI || op.dist == FC_CATEGORICAL) && op.p[0].invariant;
+    DistOut tv0, tv1;
+    if (two_valued) {
+      tv0 = dist_eval<GRAD>(op.dist, pv_inv[0], 0.0, 0.0, 0.0, 0, qnan);
+      tv1 = dist_eval<GRAD>(op.dist, pv_inv[0], 0.0, 0.0, 0.0, 1, qnan);
     }
+    const int32_t* __restrict__ crow = A.crow;
+    const int32_t* __restrict__ drow = A.drow;
 
     for (int64_t u = u0 + threadIdx.y; u < u1; u += PL_TY) {
       int64_t e0 = u, e1 = u + 1;
       if (A.grp_ptr) { e0 = A.grp_ptr[u]; e1 = A.grp_ptr[u + 1]; }
-      double gacc[3][3];
+      // The per-unit state rows (own site value, SELECT2 selector, plate/gathered latent) are the
+      // only loads that go to HBM; each iteration depends on them, so without help a warp has one
+      // 128-byte line in flight. Prefetch the rows PL_PF iterations ahead into L1 (no registers,
+      // no dependency) to keep several lines per warp outstanding.
+      {
+        const int64_t up = u + (int64_t)PL_PF * PL_TY;
+        if (up < u1) {
+          if (op.is_sample) {
+            if (!A.grp_ptr) {
+              if (op.cont) prefetch_l1(A.q + (int64_t)crow[op.cslot0 + up] * C + c);
+              else prefetch_l1(A.qd + (int64_t)drow[op.dslot0 + up] * C + c);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 3; j++)
+#pragma unroll
+            for (int t = 0; t < 3; t++) {
+              if (j >= op.n_params) continue;
+              const DTerm& tm = op.p[j].t[t];
+              if (tm.kind == FC_TERM_GATHER && A.grp_ptr) prefetch_l1(A.q + (int64_t)crow[tm.slot + up] * C + c);
+              else if (!A.grp_ptr && tm.kind == FC_TERM_SELECT2) prefetch_l1(A.qd + (int64_t)drow[tm.dslot + up] * C + c);
+              else if (!A.grp_ptr && tm.kind == FC_TERM_PLATE_LATENT) prefetch_l1(A.q + (int64_t)crow[tm.slot + up] * C + c);
+            }
+        }
+      }
+      double gacc[3][3], gval[3][3];
 #pragma unroll
       for (int j = 0; j < 3; j++)
 #pragma unroll
-        for (int t = 0; t < 3; t++) gacc[j][t] = 0.0;
+        for (int t = 0; t < 3; t++) {
+          gacc[j][t] = 0.0;
+          gval[j][t] = 0.0;
+          // a gathered latent is constant within its CSR group: one load per group
+          if (A.grp_ptr && j < op.n_params && op.p[j].t[t].kind == FC_TERM_GATHER) gval[j][t] = A.q[(int64_t)crow[op.p[j].t[t].slot + u] * C + c];
+        }
       for (int64_t e = e0; e < e1; e++) {
         const int64_t i = A.grp_elems ? (int64_t)A.grp_elems[e] : e;
         double pv[3] = {pv_inv[0], pv_inv[1], pv_inv[2]}, dl[3] = {dl_inv[0], dl_inv[1], dl_inv[2]};
-        double lx[3][3];   // LATENT_X column values
-        int zsel[3][3];    // SELECT2 branch
+        double lx[3][3];
+        int zsel[3][3];
 #pragma unroll
         for (int j = 0; j < 3; j++) {
           if (j >= op.n_params || op.p[j].invariant) continue;
@@ -199,14 +252,12 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
           for (int t = 0; t < 3; t++) {
             const DTerm& tm = pr.t[t];
             if (tm.kind == FC_TERM_NONE) continue;
-            double v = 0.0;
+            double v = tva[j][t];  // CONST / LATENT
             switch (tm.kind) {
-              case FC_TERM_CONST: v = tm.c; break;
-              case FC_TERM_LATENT: v = A.q[(int64_t)tm.row * C + c]; break;
-              case FC_TERM_LATENT_X: lx[j][t] = dcol_f64(tm.col, i); v = A.q[(int64_t)tm.row * C + c] * lx[j][t]; break;
-              case FC_TERM_GATHER: v = A.q[(int64_t)A.crow[tm.slot + dcol_i64(tm.col, i)] * C + c]; break;
-              case FC_TERM_SELECT2: zsel[j][t] = (A.qd[(int64_t)A.drow[tm.dslot + i] * C + c] == 0) ? 0 : 1; v = A.q[(int64_t)(zsel[j][t] ? tm.row_b : tm.row) * C + c]; break;
-              case FC_TERM_PLATE_LATENT: v = A.q[(int64_t)A.crow[tm.slot + i] * C + c]; break;
+              case FC_TERM_LATENT_X: lx[j][t] = dcol_f64(tm.col, i); v = tva[j][t] * lx[j][t]; break;
+              case FC_TERM_GATHER: v = A.grp_ptr ? gval[j][t] : A.q[(int64_t)crow[tm.slot + dcol_i64(tm.col, i)] * C + c]; break;
+              case FC_TERM_SELECT2: zsel[j][t] = (A.qd[(int64_t)drow[tm.dslot + i] * C + c] == 0) ? 0 : 1; v = zsel[j][t] ? tvb[j][t] : tva[j][t]; break;
+              case FC_TERM_PLATE_LATENT: v = A.q[(int64_t)crow[tm.slot + i] * C + c]; break;
               default: break;
             }
             s = first ? v : s + v;
@@ -218,21 +269,32 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
         long long xi = 0;
         int64_t xrow = 0;
         if (op.is_sample) {
-          if (op.cont) { xrow = (int64_t)A.crow[op.cslot0 + i] * C + c; x = A.q[xrow]; }
-          else xi = A.qd[(int64_t)A.drow[op.dslot0 + i] * C + c];
+          if (op.cont) { xrow = (int64_t)crow[op.cslot0 + i] * C + c; x = A.q[xrow]; }
+          else xi = A.qd[(int64_t)drow[op.dslot0 + i] * C + c];
         } else {
           if (op.cont) x = dcol_f64(op.value_col, i);
           else xi = dcol_i64(op.value_col, i);
         }
         DistOut g;
-        if (fast_normal) {
-          g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
-          if (!n_ok || !d_fin(pv[0]) || !d_fin(x)) g.lp = d_neg_inf();
-          else {
-            double z = (x - pv[0]) * n_inv;
-            g.lp = -0.5 * z * z - n_logsig - 0.5 * FC_LN_2PI;
-            if (GRAD && d_fin(g.lp)) { g.dp0 = z * n_inv; g.dx = -g.dp0; g.dp1 = (z * z - 1.0) * n_inv; }
+        if (is_normal) {
+          const double sig = pv[1];
+          int m = (sig == mem_sig[0]) ? 0 : ((sig == mem_sig[1]) ? 1 : -1);
+          if (m < 0) {  // miss: evaluate once, replace the older entry
+            m = 1;
+            mem_sig[1] = mem_sig[0]; mem_log[1] = mem_log[0]; mem_inv[1] = mem_inv[0];
+            m = 0;
+            mem_sig[0] = sig; mem_log[0] = log(sig); mem_inv[0] = 1.0 / sig;
           }
+          g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
+          if (!(sig > 0.0) || !d_fin(sig) || !d_fin(pv[0]) || !d_fin(x)) g.lp = d_neg_inf();
+          else {
+            const double inv = m == 0 ? mem_inv[0] : mem_inv[1], lg = m == 0 ? mem_log[0] : mem_log[1];
+            double z = (x - pv[0]) * inv;
+            g.lp = -0.5 * z * z - lg - 0.5 * FC_LN_2PI;
+            if (GRAD && d_fin(g.lp)) { g.dp0 = z * inv; g.dx = -g.dp0; g.dp1 = (z * z - 1.0) * inv; }
+          }
+        } else if (two_valued && (xi == 0 || xi == 1)) {
+          g = xi ? tv1 : tv0;
         } else {
           g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, op.lgam ? op.lgam[i] : qnan);
         }
@@ -252,8 +314,10 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
                 case FC_TERM_LATENT: acc_a[j][t] += w; break;
                 case FC_TERM_LATENT_X: acc_a[j][t] += w * lx[j][t]; break;
                 case FC_TERM_SELECT2: if (zsel[j][t]) acc_b[j][t] += w; else acc_a[j][t] += w; break;
-                case FC_TERM_GATHER: gacc[j][t] += w; break;
-                case FC_TERM_PLATE_LATENT: A.grad[(int64_t)A.crow[tm.slot + i] * C + c] += w; break;
+                case FC_TERM_GATHER:
+                  if (A.grp_ptr) gacc[j][t] += w;
+                  break;
+                case FC_TERM_PLATE_LATENT: A.grad[(int64_t)crow[tm.slot + i] * C + c] += w; break;
                 default: break;
               }
             }
@@ -265,7 +329,7 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
         for (int j = 0; j < 3; j++)
 #pragma unroll
           for (int t = 0; t < 3; t++)
-            if (j < op.n_params && op.p[j].t[t].kind == FC_TERM_GATHER) A.grad[(int64_t)A.crow[op.p[j].t[t].slot + u] * C + c] += gacc[j][t];
+            if (j < op.n_params && op.p[j].t[t].kind == FC_TERM_GATHER) A.grad[(int64_t)crow[op.p[j].t[t].slot + u] * C + c] += gacc[j][t];
       }
     }
   }
@@ -295,6 +359,234 @@ __global__ void __launch_bounds__(PL_TX* PL_TY) k_plate(const __grid_constant__ 
       A.part[((int64_t)blockIdx.y * n_acc + a) * C + c] = s;
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------
+// specialised plate kernel: at most two element-dependent terms whose KINDS are compile-time
+// (everything else about the op is hoisted out of the plate loop), Normal on a fast path.
+// The generic k_plate above costs ~220 issued instructions per (element, chain); this one ~25.
+// Eligibility and dispatch: plate_fast_launch(). Same partial layout and summation structure.
+// ---------------------------------------------------------------------------------------
+enum { EK_NONE = 0, EK_LATENT_X = 1, EK_GATHER = 2, EK_SELECT2 = 3, EK_PLATE_LATENT = 4 };
+
+struct FastArgs {
+  PlateArgs P;
+  int32_t ej[2], et[2];  // (param, term) of the two element-dependent terms
+};
+
+template <int KIND>
+__device__ __forceinline__ double eterm_value(const FastArgs& F, int k, const DTerm& tm, int64_t i, int64_t u, int64_t c, int64_t C, double va, double vb, double gv, double& aux) {
+  const PlateArgs& A = F.P;
+  if (KIND == EK_LATENT_X) { aux = __ldg((const double*)tm.col.ptr + i); return va * aux; }
+  if (KIND == EK_GATHER) { aux = 1.0; return gv; }
+  if (KIND == EK_SELECT2) { int z = A.qd[(int64_t)A.drow[tm.dslot + i] * C + c] != 0; aux = (double)z; return z ? vb : va; }
+  if (KIND == EK_PLATE_LATENT) { aux = 1.0; return A.q[(int64_t)A.crow[tm.slot + i] * C + c]; }
+  aux = 0.0;
+  return 0.0;
+}
+
+template <bool GRAD, bool NORMAL, int K0, int K1>
+__global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate_fast(const __grid_constant__ FastArgs F) {
+  const PlateArgs& A = F.P;
+  const DOp& op = A.op;
+  const int64_t C = A.C;
+  const int64_t c = (int64_t)blockIdx.x * PL_TX + threadIdx.x;
+  const bool active = c < C;
+  const int64_t u0 = (int64_t)blockIdx.y * A.units_per_split;
+  const int64_t u1 = min(A.n_units, u0 + A.units_per_split);
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  const int j0 = F.ej[0], j1 = F.ej[1];
+  double lp = 0.0;
+  double acc_c[3] = {0.0, 0.0, 0.0};            // sum of w_j: goes to every LATENT term of parameter j
+  double acc_e[2] = {0.0, 0.0}, acc_eb[2] = {0.0, 0.0};  // element-term accumulators (b: SELECT2 second branch)
+  if (active) {
+    // chain-constant part of every parameter
+    double base[3] = {0.0, 0.0, 0.0}, dl[3] = {1.0, 1.0, 1.0};
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      if (j >= op.n_params) continue;
+      double s = 0.0;
+#pragma unroll
+      for (int t = 0; t < 3; t++) {
+        const DTerm& tm = op.p[j].t[t];
+        if (tm.kind == FC_TERM_CONST) s += tm.c;
+        else if (tm.kind == FC_TERM_LATENT) s += A.q[(int64_t)tm.row * C + c];
+      }
+      base[j] = op.p[j].invariant ? apply_link(op.p[j].link, s, op.p[j].lo, op.p[j].hi, dl[j]) : s;
+    }
+    const DTerm& T0 = op.p[K0 ? j0 : 0].t[K0 ? F.et[0] : 0];
+    const DTerm& T1 = op.p[K1 ? j1 : 0].t[K1 ? F.et[1] : 0];
+    double va0 = 0.0, vb0 = 0.0, va1 = 0.0, vb1 = 0.0;
+    if (K0 == EK_LATENT_X || K0 == EK_SELECT2) va0 = A.q[(int64_t)T0.row * C + c];
+    if (K0 == EK_SELECT2) vb0 = A.q[(int64_t)T0.row_b * C + c];
+    if (K1 == EK_LATENT_X || K1 == EK_SELECT2) va1 = A.q[(int64_t)T1.row * C + c];
+    if (K1 == EK_SELECT2) vb1 = A.q[(int64_t)T1.row_b * C + c];
+    // Normal: sigma handling. Invariant sigma -> constants; SELECT2 sigma -> two constants.
+    double n_inv_a = 0.0, n_log_a = 0.0, n_inv_b = 0.0, n_log_b = 0.0;
+    bool n_ok_a = false, n_ok_b = false;
+    const bool sig_is_e0 = NORMAL && K0 == EK_SELECT2 && j0 == 1, sig_is_e1 = NORMAL && K1 == EK_SELECT2 && j1 == 1;
+    if (NORMAL) {
+      double sa = base[1], sb = base[1];
+      if (sig_is_e0) { sa = base[1] + va0; sb = base[1] + vb0; }
+      if (sig_is_e1) { sa = base[1] + va1; sb = base[1] + vb1; }
+      n_ok_a = sa > 0.0 && d_fin(sa);
+      n_ok_b = sb > 0.0 && d_fin(sb);
+      if (n_ok_a) { n_log_a = log(sa); n_inv_a = 1.0 / sa; }
+      if (n_ok_b) { n_log_b = log(sb); n_inv_b = 1.0 / sb; }
+    }
+    const bool two_valued = !NORMAL && (op.dist == FC_BERNOULLI || op.dist == FC_CATEGORICAL) && op.p[0].invariant;
+    DistOut tv0, tv1;
+    if (two_valued) {
+      tv0 = dist_eval<GRAD>(op.dist, base[0], 0.0, 0.0, 0.0, 0, qnan);
+      tv1 = dist_eval<GRAD>(op.dist, base[0], 0.0, 0.0, 0.0, 1, qnan);
+    }
+    for (int64_t u = u0 + threadIdx.y; u < u1; u += PL_TY) {
+      int64_t e0 = u, e1 = u + 1;
+      if (A.grp_ptr) { e0 = A.grp_ptr[u]; e1 = A.grp_ptr[u + 1]; }
+      double gv0 = 0.0, gv1 = 0.0, ga0 = 0.0, ga1 = 0.0;
+      if (K0 == EK_GATHER) gv0 = A.q[(int64_t)A.crow[T0.slot + u] * C + c];
+      if (K1 == EK_GATHER) gv1 = A.q[(int64_t)A.crow[T1.slot + u] * C + c];
+      for (int64_t e = e0; e < e1; e++) {
+        const int64_t i = A.grp_elems ? (int64_t)A.grp_elems[e] : e;
+        double aux0, aux1;
+        const double v0 = eterm_value<K0>(F, 0, T0, i, u, c, C, va0, vb0, gv0, aux0);
+        const double v1 = eterm_value<K1>(F, 1, T1, i, u, c, C, va1, vb1, gv1, aux1);
+        double pv0 = base[0], pv1 = base[1], pv2 = base[2];
+        if (K0) { pv0 += (j0 == 0) ? v0 : 0.0; pv1 += (j0 == 1) ? v0 : 0.0; pv2 += (j0 == 2) ? v0 : 0.0; }
+        if (K1) { pv0 += (j1 == 0) ? v1 : 0.0; pv1 += (j1 == 1) ? v1 : 0.0; pv2 += (j1 == 2) ? v1 : 0.0; }
+        double x = 0.0;
+        long long xi = 0;
+        int64_t xrow = 0;
+        if (op.is_sample) {
+          if (op.cont) { xrow = (int64_t)A.crow[op.cslot0 + i] * C + c; x = A.q[xrow]; }
+          else xi = A.qd[(int64_t)A.drow[op.dslot0 + i] * C + c];
+        } else {
+          if (op.cont) x = dcol_f64(op.value_col, i);
+          else xi = dcol_i64(op.value_col, i);
+        }
+        double g_lp, g_dx = 0.0, g_dp0 = 0.0, g_dp1 = 0.0, g_dp2 = 0.0;
+        if (NORMAL) {
+          const bool useb = (sig_is_e0 && aux0 != 0.0) || (sig_is_e1 && aux1 != 0.0);
+          const bool ok = useb ? n_ok_b : n_ok_a;
+          const double inv = useb ? n_inv_b : n_inv_a, lg = useb ? n_log_b : n_log_a;
+          if (!ok || !d_fin(pv0) || !d_fin(x)) g_lp = d_neg_inf();
+          else {
+            double z = (x - pv0) * inv;
+            g_lp = -0.5 * z * z - lg - 0.5 * FC_LN_2PI;
+            if (GRAD && d_fin(g_lp)) { g_dp0 = z * inv; g_dx = -g_dp0; g_dp1 = (z * z - 1.0) * inv; }
+          }
+        } else if (two_valued && (xi == 0 || xi == 1)) {
+          const DistOut& o = xi ? tv1 : tv0;
+          g_lp = o.lp; g_dp0 = o.dp0;
+        } else {
+          DistOut o = dist_eval<GRAD>(op.dist, pv0, pv1, pv2, x, xi, op.lgam ? op.lgam[i] : qnan);
+          g_lp = o.lp; g_dx = o.dx; g_dp0 = o.dp0; g_dp1 = o.dp1; g_dp2 = o.dp2;
+        }
+        lp += g_lp;
+        if (GRAD) {
+          if (op.is_sample && op.cont) A.grad[xrow] += g_dx;
+          const double w0 = g_dp0 * dl[0], w1 = g_dp1 * dl[1], w2 = g_dp2 * dl[2];
+          acc_c[0] += w0; acc_c[1] += w1; acc_c[2] += w2;
+          if (K0) {
+            const double w = j0 == 0 ? w0 : (j0 == 1 ? w1 : w2);
+            if (K0 == EK_LATENT_X) acc_e[0] += w * aux0;
+            else if (K0 == EK_SELECT2) { if (aux0 != 0.0) acc_eb[0] += w; else acc_e[0] += w; }
+            else if (K0 == EK_GATHER) ga0 += w;
+            else if (K0 == EK_PLATE_LATENT && w != 0.0) A.grad[(int64_t)A.crow[T0.slot + i] * C + c] += w;
+          }
+          if (K1) {
+            const double w = j1 == 0 ? w0 : (j1 == 1 ? w1 : w2);
+            if (K1 == EK_LATENT_X) acc_e[1] += w * aux1;
+            else if (K1 == EK_SELECT2) { if (aux1 != 0.0) acc_eb[1] += w; else acc_e[1] += w; }
+            else if (K1 == EK_GATHER) ga1 += w;
+            else if (K1 == EK_PLATE_LATENT && w != 0.0) A.grad[(int64_t)A.crow[T1.slot + i] * C + c] += w;
+          }
+        }
+      }
+      if (GRAD) {
+        if (K0 == EK_GATHER) A.grad[(int64_t)A.crow[T0.slot + u] * C + c] += ga0;
+        if (K1 == EK_GATHER) A.grad[(int64_t)A.crow[T1.slot + u] * C + c] += ga1;
+      }
+    }
+  }
+  __shared__ double sm[PL_TY][PL_TX + 1];
+  const int n_acc = GRAD ? A.acc.n_acc : 3;
+  const int lp_slot = op.is_sample ? 0 : 1;
+  for (int a = 0; a < n_acc; a++) {
+    double v = 0.0;
+    if (a < 3) v = (a == lp_slot) ? lp : 0.0;
+    else {
+#pragma unroll
+      for (int j = 0; j < 3; j++)
+#pragma unroll
+        for (int t = 0; t < 3; t++) {
+          const bool is0 = K0 && j == j0 && t == F.et[0], is1 = K1 && j == j1 && t == F.et[1];
+          if (A.acc.a_idx[j][t] == a) v += is0 ? acc_e[0] : (is1 ? acc_e[1] : acc_c[j]);
+          if (A.acc.b_idx[j][t] == a) v += is0 ? acc_eb[0] : (is1 ? acc_eb[1] : 0.0);
+        }
+    }
+    __syncthreads();
+    sm[threadIdx.y][threadIdx.x] = v;
+    __syncthreads();
+    if (threadIdx.y == 0 && active) {
+      double s = sm[0][threadIdx.x];
+#pragma unroll
+      for (int y = 1; y < PL_TY; y++) s += sm[y][threadIdx.x];
+      A.part[((int64_t)blockIdx.y * n_acc + a) * C + c] = s;
+    }
+  }
+}
+
+// host side: eligibility + dispatch. Returns 1 if launched, 0 if the op needs the generic kernel.
+template <bool GRAD, bool NORMAL>
+static int fast_dispatch(int k0, int k1, const FastArgs& F, dim3 grid, dim3 block, cudaStream_t st) {
+#define FAST_CASE(A_, B_) if (k0 == A_ && k1 == B_) { k_plate_fast<GRAD, NORMAL, A_, B_><<<grid, block, 0, st>>>(F); return 1; }
+  FAST_CASE(EK_NONE, EK_NONE)
+  FAST_CASE(EK_LATENT_X, EK_NONE)
+  FAST_CASE(EK_GATHER, EK_NONE)
+  FAST_CASE(EK_SELECT2, EK_NONE)
+  FAST_CASE(EK_PLATE_LATENT, EK_NONE)
+  FAST_CASE(EK_GATHER, EK_LATENT_X)
+  FAST_CASE(EK_LATENT_X, EK_GATHER)
+  FAST_CASE(EK_SELECT2, EK_SELECT2)
+  FAST_CASE(EK_LATENT_X, EK_LATENT_X)
+#undef FAST_CASE
+  return 0;
+}
+
+static int plate_fast_launch(const PlateArgs& A, bool grad, dim3 grid, dim3 block, cudaStream_t st) {
+  static const bool disabled = getenv("FC_PLATE_GENERIC") != nullptr;
+  if (disabled) return 0;
+  const DOp& op = A.op;
+  FastArgs F;
+  F.P = A;
+  F.ej[0] = F.ej[1] = F.et[0] = F.et[1] = 0;
+  int kinds[2] = {EK_NONE, EK_NONE}, n = 0;
+  for (int j = 0; j < op.n_params; j++)
+    for (int t = 0; t < 3; t++) {
+      int k = op.p[j].t[t].kind, ek = EK_NONE;
+      if (k == FC_TERM_LATENT_X) ek = EK_LATENT_X;
+      else if (k == FC_TERM_GATHER) ek = EK_GATHER;
+      else if (k == FC_TERM_SELECT2) ek = EK_SELECT2;
+      else if (k == FC_TERM_PLATE_LATENT) ek = EK_PLATE_LATENT;
+      else if (k == FC_TERM_DENSE) return 0;
+      if (ek == EK_NONE) continue;
+      if (n == 2) return 0;
+      if (op.p[j].link != FC_LINK_IDENTITY) return 0;
+      if (ek == EK_LATENT_X && op.p[j].t[t].col.dtype != FC_COL_F64) return 0;
+      kinds[n] = ek; F.ej[n] = j; F.et[n] = t; n++;
+    }
+  bool normal = op.dist == FC_NORMAL;
+  if (normal) {  // sigma must be chain-constant or a single SELECT2
+    int n_sig = 0;
+    for (int k = 0; k < n; k++)
+      if (F.ej[k] == 1) { n_sig++; if (kinds[k] != EK_SELECT2) normal = false; }
+    if (n_sig > 1) normal = false;
+  }
+  int ok;
+  if (grad) ok = normal ? fast_dispatch<true, true>(kinds[0], kinds[1], F, grid, block, st) : fast_dispatch<true, false>(kinds[0], kinds[1], F, grid, block, st);
+  else ok = normal ? fast_dispatch<false, true>(kinds[0], kinds[1], F, grid, block, st) : fast_dispatch<false, false>(kinds[0], kinds[1], F, grid, block, st);
+  return ok;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -401,8 +693,10 @@ int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t 
     A.units_per_split = cdiv(A.n_units, splits[i]);
     int64_t ns = cdiv(A.n_units, A.units_per_split);
     dim3 grid((unsigned)cdiv(C, PL_TX), (unsigned)ns), block(PL_TX, PL_TY);
-    if (grad) k_plate<true><<<grid, block, 0, st>>>(A);
-    else k_plate<false><<<grid, block, 0, st>>>(A);
+    if (!plate_fast_launch(A, grad, grid, block, st)) {
+      if (grad) k_plate<true><<<grid, block, 0, st>>>(A);
+      else k_plate<false><<<grid, block, 0, st>>>(A);
+    }
     FC_KERNEL_CHECK();
     F.n_splits = ns;
     F.n_acc = grad ? pl.acc.n_acc : 3;

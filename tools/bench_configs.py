@@ -1,0 +1,93 @@
+"""Secondary BASELINE configs (C3 hierarchical HMC + R-hat/ESS, C4 mixture SMC, C5 Poisson-GLM MH):
+throughput with CUDA events on the program's stream and the HBM-streaming roofline fraction of
+SURVEY 8(d). Usage: python tools/bench_configs.py [c3|c4|c5] [scale]   (scale < 1 shrinks sizes)."""
+import json, os, sys, time
+import numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from fugue_b200 import api, models
+
+HBM = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) else 6650.0
+which = sys.argv[1]
+scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
+
+
+def timed(P, fn, reps):
+    ext = torch.cuda.ExternalStream(P.stream)
+    fn()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(ext):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        e1.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+if which == "c3":
+    G, Cn = int(10000 * scale), int(1024 * max(scale, 0.25))
+    m, _ = models.hierarchical(G=G, per_group=15)
+    P = api.Program(m)
+    N, d = G * 15, P.d_cont
+    S = api.HmcSession(P, n_chains=Cn, n_warmup=10**9, config=api.HMCConfig(n_leapfrog=16, adapt_mass=False), seed=1)
+    S.step(2); S.sync()
+    g0 = S.grad_evals()
+    ms = timed(P, lambda: S.step(1), 5)
+    ge = (S.grad_evals() - g0) / 6
+    rate = Cn * ge / (ms * 1e-3)
+    alg = 20 * N + 16 * d
+    out = dict(config="C3 hierarchical normal", G=G, N=N, d=d, chains=Cn, ms_per_transition=ms, grad_evals_per_s=rate,
+               hbm_alg_GBps=rate * alg / 1e9, hbm_frac=rate * alg / 1e9 / HBM, accept=float(np.mean(S.stats()["n_accept"]) / S.iterations()))
+    # diagnostics on a short run of all d parameters
+    t0 = time.time()
+    draws, lp, st = api.hmc_chain(P, n_samples=40, n_warmup=20, config=api.HMCConfig(n_leapfrog=8), n_chains=min(Cn, 256), seed=2)
+    t1 = time.time()
+    dg = api.diagnostics(draws)
+    out.update(diag_params=d, diag_seconds=time.time() - t1, rhat_median=float(np.nanmedian(dg["r_hat"])), ess_median=float(np.nanmedian(dg["ess"])))
+elif which == "c5":
+    N, Cn = int(4_000_000 * scale), int(65536 * scale)
+    m, _ = models.poisson_glm(N=N, D=8)
+    P = api.Program(m)
+    S = api.MhSession(P, n_chains=Cn, n_warmup=10**9, seed=1)
+    S.step(2)
+    ms = timed(P, lambda: S.step(1), 3)
+    rate = Cn / (ms * 1e-3)
+    alg = N * (8 * 8 + 4)
+    g = S.get()
+    out = dict(config="C5 poisson GLM RW-Metropolis", N=N, D=8, chains=Cn, ms_per_step=ms, evals_per_s=rate, hbm_alg_GBps=rate * alg / 1e9,
+               hbm_frac=rate * alg / 1e9 / HBM, log_per_s=rate * N, accept=float(g["n_accept"].mean() / g["n_steps"]))
+elif which == "c4":
+    Pn = int((1 << 24) * scale)
+    R = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+    m, _ = models.gaussian_mixture(n_obs=80)
+    P = api.Program(m)
+    t0 = time.time()
+    S = api.SmcSession(P, Pn, api.SMCConfig(rejuvenation_steps=R), seed=3)
+    t_init = time.time() - t0
+    ext = torch.cuda.ExternalStream(P.stream)
+    steps, betas = 0, []
+    torch.cuda.synchronize()
+    t0 = time.time()
+    while True:
+        b = S.step()
+        steps += 1
+        betas.append(b)
+        if b >= 1.0 or steps > 200:
+            break
+    torch.cuda.synchronize()
+    dt = time.time() - t0
+    r = S.result(values=False)
+    rate = Pn * steps / dt
+    alg = 488 if R == 1 else 136 + 352 * R / 1  # 488 B at R=1, 840 B at R=3
+    alg = {1: 488, 3: 840}.get(R, 488)
+    out = dict(config="C4 gaussian mixture SMC", particles=Pn, rejuvenation_steps=R, temper_steps=steps, init_seconds=t_init, seconds=dt,
+               particle_updates_per_s=rate, hbm_alg_GBps=rate * alg / 1e9, hbm_frac=rate * alg / 1e9 / HBM, log_evidence=r.log_evidence,
+               ess_final=float(1.0 / (r.weight ** 2).sum()), betas=betas[:6])
+    # standalone global systematic resample of the final weights
+    w = r.weight
+    t0 = time.time()
+    idx = api.resample_indices(1, w, [0.5])
+    out["resample_host_api_seconds"] = time.time() - t0
+out["gpu_launches"] = P.launch_count
+print(json.dumps(out))
