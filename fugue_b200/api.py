@@ -441,6 +441,7 @@ _sig("fc_exact_prefix_sums", vp, C.c_size_t, vp)
 _sig("fc_log_sum_exp", vp, C.c_size_t, dp)
 _sig("fc_ess", vp, C.c_size_t, dp)
 _sig("fc_normalize_log_probs", vp, C.c_size_t, vp)
+_sig("fc_next_beta", vp, vp, C.c_size_t, C.c_double, C.c_double, dp)
 
 
 class ResamplingMethod:
@@ -535,6 +536,15 @@ def log_sum_exp(x):
     x = _f64(x)
     o = C.c_double()
     check(lib.fc_log_sum_exp(_ptr(x), x.size, C.byref(o)))
+    return o.value
+
+
+def next_beta(beta, log_w, loglik, target_ess):
+    """next_beta (smc.rs:588-622): the next tempering exponent keeping ESS >= target_ess."""
+    lw, ll = _f64(log_w), _f64(loglik)
+    assert lw.size == ll.size
+    o = C.c_double()
+    check(lib.fc_next_beta(_ptr(lw), _ptr(ll), ll.size, float(beta), float(target_ess), C.byref(o)))
     return o.value
 
 

@@ -183,37 +183,51 @@ struct AcceptArgs {
 
 __global__ void k_move_accept(const __grid_constant__ AcceptArgs A) {
   int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= A.C) return;
   const int64_t C = A.C;
-  int g = A.target[c];
-  if (g < 0) return;
-  double log_alpha;
-  if (A.smc_mode) {  // smc.rs:679-680
-    double dprior = A.lp3_new[c] - A.lp3_cur[c];
-    double dll = (A.lp3_new[C + c] + A.lp3_new[2 * C + c]) - (A.lp3_cur[C + c] + A.lp3_cur[2 * C + c]);
-    log_alpha = dprior + A.beta * dll;
-  } else {  // mh.rs:731-732 (dim_term = 0 for fixed structure)
-    log_alpha = (A.total_new[c] - A.total_cur[c]) + A.lqdiff[c];
-  }
-  Philox ph(A.seed, A.chain0 + (uint64_t)c);
-  double u_site, u_acc;
-  ph.uniform2(0, A.step_tag, u_site, u_acc);
-  bool accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);  // mh.rs:733
-  if (accept) {
-    for (int a = 0; a < 3; a++) A.lp3_cur[a * C + c] = A.lp3_new[a * C + c];
-    A.total_cur[c] = A.total_new[c];
-    if (A.n_accept) A.n_accept[c] += 1;
-  } else {
-    if (A.smc_mode) A.q[(int64_t)g * C + c] = A.old_x[c];
-    else {
-      const SiteInfo si = A.sites[g];
-      if (si.is_cont) A.q[(int64_t)si.row * C + c] = A.old_x[c];
-      else A.qd[(int64_t)si.row * C + c] = (disc_t)A.old_x[c];
+  int g = c < C ? A.target[c] : -1;
+  const bool valid = g >= 0;
+  bool accept = false;
+  if (valid) {
+    double log_alpha;
+    if (A.smc_mode) {  // smc.rs:679-680
+      double dprior = A.lp3_new[c] - A.lp3_cur[c];
+      double dll = (A.lp3_new[C + c] + A.lp3_new[2 * C + c]) - (A.lp3_cur[C + c] + A.lp3_cur[2 * C + c]);
+      log_alpha = dprior + A.beta * dll;
+    } else {  // mh.rs:731-732 (dim_term = 0 for fixed structure)
+      log_alpha = (A.total_new[c] - A.total_cur[c]) + A.lqdiff[c];
+    }
+    Philox ph(A.seed, A.chain0 + (uint64_t)c);
+    double u_site, u_acc;
+    ph.uniform2(0, A.step_tag, u_site, u_acc);
+    accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);  // mh.rs:733
+    if (accept) {
+      for (int a = 0; a < 3; a++) A.lp3_cur[a * C + c] = A.lp3_new[a * C + c];
+      A.total_cur[c] = A.total_new[c];
+      if (A.n_accept) A.n_accept[c] += 1;
+    } else {
+      if (A.smc_mode) A.q[(int64_t)g * C + c] = A.old_x[c];
+      else {
+        const SiteInfo si = A.sites[g];
+        if (si.is_cont) A.q[(int64_t)si.row * C + c] = A.old_x[c];
+        else A.qd[(int64_t)si.row * C + c] = (disc_t)A.old_x[c];
+      }
     }
   }
   if (A.smc_mode) {
-    if (A.adapt) { atomicAdd(&A.tot_cnt[g], 1u); if (accept) atomicAdd(&A.acc_cnt[g], 1u); }
-  } else if (A.adapt) {  // DiminishingAdaptation::update (mcmc_utils.rs:88-150), per chain and address
+    if (!A.adapt) return;
+    // shared per-site counters: aggregate in shared memory, one global atomic per site per CTA
+    __shared__ unsigned s_tot[64], s_acc[64];
+    if (A.n_sites <= 64) {
+      for (int i = threadIdx.x; i < 64; i += blockDim.x) { s_tot[i] = 0; s_acc[i] = 0; }
+      __syncthreads();
+      if (valid) { atomicAdd(&s_tot[g], 1u); if (accept) atomicAdd(&s_acc[g], 1u); }
+      __syncthreads();
+      for (int i = threadIdx.x; i < A.n_sites; i += blockDim.x) {
+        if (s_tot[i]) atomicAdd(&A.tot_cnt[i], s_tot[i]);
+        if (s_acc[i]) atomicAdd(&A.acc_cnt[i], s_acc[i]);
+      }
+    } else if (valid) { atomicAdd(&A.tot_cnt[g], 1u); if (accept) atomicAdd(&A.acc_cnt[g], 1u); }
+  } else if (A.adapt && valid) {  // DiminishingAdaptation::update (mcmc_utils.rs:88-150), per chain and address
     int64_t i = (int64_t)g * C + c;
     uint32_t tot = A.tot_cnt[i] + 1, acc = A.acc_cnt[i] + (accept ? 1u : 0u);
     A.tot_cnt[i] = tot;
@@ -298,7 +312,7 @@ int32_t MoveEngine::step(double* q, disc_t* qd, double* lp3_cur, double* total_c
   A.scale = scale.p; A.log_scale = log_scale.p; A.acc_cnt = acc_cnt.p; A.tot_cnt = tot_cnt.p; A.n_accept = n_accept;
   A.C = C; A.n_sites = n_sites; A.seed = seed; A.chain0 = chain0; A.step_tag = step_tag;
   A.beta = beta; A.target_rate = target_rate; A.gamma = gamma; A.smc_mode = smc_mode ? 1 : 0; A.adapt = adapt ? 1 : 0;
-  k_move_accept<<<nb, 128, 0, st>>>(A);
+  k_move_accept<<<(unsigned)cdiv(C, 256), 256, 0, st>>>(A);
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 2;
   return FC_OK;

@@ -374,19 +374,36 @@ struct FastArgs {
   int32_t ej[2], et[2];  // (param, term) of the two element-dependent terms
 };
 
+// raw per-element input of an element-dependent term (the only loads that go to HBM / L1)
 template <int KIND>
-__device__ __forceinline__ double eterm_value(const FastArgs& F, int k, const DTerm& tm, int64_t i, int64_t u, int64_t c, int64_t C, double va, double vb, double gv, double& aux) {
-  const PlateArgs& A = F.P;
-  if (KIND == EK_LATENT_X) { aux = __ldg((const double*)tm.col.ptr + i); return va * aux; }
+__device__ __forceinline__ double eterm_load(const PlateArgs& A, const DTerm& tm, int64_t i, int64_t c, int64_t C) {
+  if (KIND == EK_LATENT_X) return __ldg((const double*)tm.col.ptr + i);
+  if (KIND == EK_SELECT2) return (double)(A.qd[(int64_t)A.drow[tm.dslot + i] * C + c] != 0);
+  if (KIND == EK_PLATE_LATENT) return A.q[(int64_t)A.crow[tm.slot + i] * C + c];
+  return 0.0;
+}
+// term value from the raw input; aux = d value / d (reduced latent) or the SELECT2 branch flag
+template <int KIND>
+__device__ __forceinline__ double eterm_apply(double raw, double va, double vb, double gv, double& aux) {
+  if (KIND == EK_LATENT_X) { aux = raw; return va * raw; }
   if (KIND == EK_GATHER) { aux = 1.0; return gv; }
-  if (KIND == EK_SELECT2) { int z = A.qd[(int64_t)A.drow[tm.dslot + i] * C + c] != 0; aux = (double)z; return z ? vb : va; }
-  if (KIND == EK_PLATE_LATENT) { aux = 1.0; return A.q[(int64_t)A.crow[tm.slot + i] * C + c]; }
+  if (KIND == EK_SELECT2) { aux = raw; return raw != 0.0 ? vb : va; }
+  if (KIND == EK_PLATE_LATENT) { aux = 1.0; return raw; }
   aux = 0.0;
   return 0.0;
 }
 
-template <bool GRAD, bool NORMAL, int K0, int K1>
-__global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate_fast(const __grid_constant__ FastArgs F) {
+enum { DK_GENERIC = 0, DK_NORMAL = 1, DK_TWOVAL = 2 };
+#define PL_UB 8  // elements whose loads are issued together (memory-level parallelism)
+
+// DK: DK_NORMAL = Normal with chain-constant / SELECT2 sigma; DK_TWOVAL = Bernoulli or two-way
+// Categorical with a chain-constant parameter (both log-probs evaluated once per chain).
+// Value-only launches (MH / SMC: many chains, short plates) run at 4 CTAs per SM so that
+// 32 warps x PL_UB independent row loads are in flight per SM.
+template <bool GRAD, int DK, int K0, int K1>
+__global__ void __launch_bounds__(PL_TX* PL_TY, GRAD ? 2 : 3) k_plate_fast(const __grid_constant__ FastArgs F) {
+  constexpr bool NORMAL = DK == DK_NORMAL;
+  constexpr bool CSR = (K0 == EK_GATHER || K1 == EK_GATHER);
   const PlateArgs& A = F.P;
   const DOp& op = A.op;
   const int64_t C = A.C;
@@ -434,78 +451,113 @@ __global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate_fast(const __grid_con
       if (n_ok_a) { n_log_a = log(sa); n_inv_a = 1.0 / sa; }
       if (n_ok_b) { n_log_b = log(sb); n_inv_b = 1.0 / sb; }
     }
-    const bool two_valued = !NORMAL && (op.dist == FC_BERNOULLI || op.dist == FC_CATEGORICAL) && op.p[0].invariant;
-    DistOut tv0, tv1;
-    if (two_valued) {
-      tv0 = dist_eval<GRAD>(op.dist, base[0], 0.0, 0.0, 0.0, 0, qnan);
-      tv1 = dist_eval<GRAD>(op.dist, base[0], 0.0, 0.0, 0.0, 1, qnan);
+    double tv_lp0 = 0.0, tv_lp1 = 0.0, tv_d0 = 0.0, tv_d1 = 0.0;
+    const bool tv_bern = op.dist == FC_BERNOULLI;
+    if (DK == DK_TWOVAL) {
+      DistOut o0 = dist_eval<GRAD>(op.dist, base[0], 0.0, 0.0, 0.0, 0, qnan);
+      DistOut o1 = dist_eval<GRAD>(op.dist, base[0], 0.0, 0.0, 0.0, 1, qnan);
+      tv_lp0 = o0.lp; tv_d0 = o0.dp0; tv_lp1 = o1.lp; tv_d1 = o1.dp0;
     }
-    for (int64_t u = u0 + threadIdx.y; u < u1; u += PL_TY) {
-      int64_t e0 = u, e1 = u + 1;
-      if (A.grp_ptr) { e0 = A.grp_ptr[u]; e1 = A.grp_ptr[u + 1]; }
-      double gv0 = 0.0, gv1 = 0.0, ga0 = 0.0, ga1 = 0.0;
-      if (K0 == EK_GATHER) gv0 = A.q[(int64_t)A.crow[T0.slot + u] * C + c];
-      if (K1 == EK_GATHER) gv1 = A.q[(int64_t)A.crow[T1.slot + u] * C + c];
-      for (int64_t e = e0; e < e1; e++) {
-        const int64_t i = A.grp_elems ? (int64_t)A.grp_elems[e] : e;
-        double aux0, aux1;
-        const double v0 = eterm_value<K0>(F, 0, T0, i, u, c, C, va0, vb0, gv0, aux0);
-        const double v1 = eterm_value<K1>(F, 1, T1, i, u, c, C, va1, vb1, gv1, aux1);
-        double pv0 = base[0], pv1 = base[1], pv2 = base[2];
-        if (K0) { pv0 += (j0 == 0) ? v0 : 0.0; pv1 += (j0 == 1) ? v0 : 0.0; pv2 += (j0 == 2) ? v0 : 0.0; }
-        if (K1) { pv0 += (j1 == 0) ? v1 : 0.0; pv1 += (j1 == 1) ? v1 : 0.0; pv2 += (j1 == 2) ? v1 : 0.0; }
-        double x = 0.0;
-        long long xi = 0;
-        int64_t xrow = 0;
-        if (op.is_sample) {
-          if (op.cont) { xrow = (int64_t)A.crow[op.cslot0 + i] * C + c; x = A.q[xrow]; }
-          else xi = A.qd[(int64_t)A.drow[op.dslot0 + i] * C + c];
-        } else {
-          if (op.cont) x = dcol_f64(op.value_col, i);
-          else xi = dcol_i64(op.value_col, i);
+    // one element: everything after its loads
+    auto body = [&](int64_t i, double raw0, double raw1, double x, long long xi, int64_t xrow, double lg, double gv0, double gv1, double& ga0, double& ga1) {
+      double aux0, aux1;
+      const double v0 = eterm_apply<K0>(raw0, va0, vb0, gv0, aux0);
+      const double v1 = eterm_apply<K1>(raw1, va1, vb1, gv1, aux1);
+      double pv0 = base[0], pv1 = base[1], pv2 = base[2];
+      if (K0) { pv0 += (j0 == 0) ? v0 : 0.0; pv1 += (j0 == 1) ? v0 : 0.0; pv2 += (j0 == 2) ? v0 : 0.0; }
+      if (K1) { pv0 += (j1 == 0) ? v1 : 0.0; pv1 += (j1 == 1) ? v1 : 0.0; pv2 += (j1 == 2) ? v1 : 0.0; }
+      double g_lp, g_dx = 0.0, g_dp0 = 0.0, g_dp1 = 0.0, g_dp2 = 0.0;
+      if (NORMAL) {
+        const bool useb = (sig_is_e0 && aux0 != 0.0) || (sig_is_e1 && aux1 != 0.0);
+        const bool ok = useb ? n_ok_b : n_ok_a;
+        const double inv = useb ? n_inv_b : n_inv_a, lgs = useb ? n_log_b : n_log_a;
+        if (!ok || !d_fin(pv0) || !d_fin(x)) g_lp = d_neg_inf();
+        else {
+          double z = (x - pv0) * inv;
+          g_lp = -0.5 * z * z - lgs - 0.5 * FC_LN_2PI;
+          if (GRAD && d_fin(g_lp)) { g_dp0 = z * inv; g_dx = -g_dp0; g_dp1 = (z * z - 1.0) * inv; }
         }
-        double g_lp, g_dx = 0.0, g_dp0 = 0.0, g_dp1 = 0.0, g_dp2 = 0.0;
-        if (NORMAL) {
-          const bool useb = (sig_is_e0 && aux0 != 0.0) || (sig_is_e1 && aux1 != 0.0);
-          const bool ok = useb ? n_ok_b : n_ok_a;
-          const double inv = useb ? n_inv_b : n_inv_a, lg = useb ? n_log_b : n_log_a;
-          if (!ok || !d_fin(pv0) || !d_fin(x)) g_lp = d_neg_inf();
-          else {
-            double z = (x - pv0) * inv;
-            g_lp = -0.5 * z * z - lg - 0.5 * FC_LN_2PI;
-            if (GRAD && d_fin(g_lp)) { g_dp0 = z * inv; g_dx = -g_dp0; g_dp1 = (z * z - 1.0) * inv; }
-          }
-        } else if (two_valued && (xi == 0 || xi == 1)) {
-          const DistOut& o = xi ? tv1 : tv0;
-          g_lp = o.lp; g_dp0 = o.dp0;
-        } else {
-          DistOut o = dist_eval<GRAD>(op.dist, pv0, pv1, pv2, x, xi, op.lgam ? op.lgam[i] : qnan);
-          g_lp = o.lp; g_dx = o.dx; g_dp0 = o.dp0; g_dp1 = o.dp1; g_dp2 = o.dp2;
+      } else if (DK == DK_TWOVAL) {
+        if (xi == 0) { g_lp = tv_lp0; g_dp0 = tv_d0; }
+        else if (xi == 1 || tv_bern) { g_lp = tv_lp1; g_dp0 = tv_d1; }
+        else g_lp = d_neg_inf();  // two-way Categorical: index out of range (distribution.rs:785-791)
+      } else {
+        DistOut o = dist_eval<GRAD>(op.dist, pv0, pv1, pv2, x, xi, lg);
+        g_lp = o.lp; g_dx = o.dx; g_dp0 = o.dp0; g_dp1 = o.dp1; g_dp2 = o.dp2;
+      }
+      lp += g_lp;
+      if (GRAD) {
+        if (op.is_sample && op.cont) A.grad[xrow] += g_dx;
+        const double w0 = g_dp0 * dl[0], w1 = g_dp1 * dl[1], w2 = g_dp2 * dl[2];
+        acc_c[0] += w0; acc_c[1] += w1; acc_c[2] += w2;
+        if (K0) {
+          const double w = j0 == 0 ? w0 : (j0 == 1 ? w1 : w2);
+          if (K0 == EK_LATENT_X) acc_e[0] += w * aux0;
+          else if (K0 == EK_SELECT2) { if (aux0 != 0.0) acc_eb[0] += w; else acc_e[0] += w; }
+          else if (K0 == EK_GATHER) ga0 += w;
+          else if (K0 == EK_PLATE_LATENT && w != 0.0) A.grad[(int64_t)A.crow[T0.slot + i] * C + c] += w;
         }
-        lp += g_lp;
-        if (GRAD) {
-          if (op.is_sample && op.cont) A.grad[xrow] += g_dx;
-          const double w0 = g_dp0 * dl[0], w1 = g_dp1 * dl[1], w2 = g_dp2 * dl[2];
-          acc_c[0] += w0; acc_c[1] += w1; acc_c[2] += w2;
-          if (K0) {
-            const double w = j0 == 0 ? w0 : (j0 == 1 ? w1 : w2);
-            if (K0 == EK_LATENT_X) acc_e[0] += w * aux0;
-            else if (K0 == EK_SELECT2) { if (aux0 != 0.0) acc_eb[0] += w; else acc_e[0] += w; }
-            else if (K0 == EK_GATHER) ga0 += w;
-            else if (K0 == EK_PLATE_LATENT && w != 0.0) A.grad[(int64_t)A.crow[T0.slot + i] * C + c] += w;
-          }
-          if (K1) {
-            const double w = j1 == 0 ? w0 : (j1 == 1 ? w1 : w2);
-            if (K1 == EK_LATENT_X) acc_e[1] += w * aux1;
-            else if (K1 == EK_SELECT2) { if (aux1 != 0.0) acc_eb[1] += w; else acc_e[1] += w; }
-            else if (K1 == EK_GATHER) ga1 += w;
-            else if (K1 == EK_PLATE_LATENT && w != 0.0) A.grad[(int64_t)A.crow[T1.slot + i] * C + c] += w;
-          }
+        if (K1) {
+          const double w = j1 == 0 ? w0 : (j1 == 1 ? w1 : w2);
+          if (K1 == EK_LATENT_X) acc_e[1] += w * aux1;
+          else if (K1 == EK_SELECT2) { if (aux1 != 0.0) acc_eb[1] += w; else acc_e[1] += w; }
+          else if (K1 == EK_GATHER) ga1 += w;
+          else if (K1 == EK_PLATE_LATENT && w != 0.0) A.grad[(int64_t)A.crow[T1.slot + i] * C + c] += w;
         }
       }
-      if (GRAD) {
-        if (K0 == EK_GATHER) A.grad[(int64_t)A.crow[T0.slot + u] * C + c] += ga0;
-        if (K1 == EK_GATHER) A.grad[(int64_t)A.crow[T1.slot + u] * C + c] += ga1;
+    };
+    // the element's own value (site row or data column) and optional lgamma(value + 1)
+    auto load_x = [&](int64_t i, double& x, long long& xi, int64_t& xrow, double& lg) {
+      x = 0.0; xi = 0; xrow = 0; lg = qnan;
+      if (op.is_sample) {
+        if (op.cont) { xrow = (int64_t)A.crow[op.cslot0 + i] * C + c; x = A.q[xrow]; }
+        else xi = A.qd[(int64_t)A.drow[op.dslot0 + i] * C + c];
+      } else {
+        if (op.cont) x = dcol_f64(op.value_col, i);
+        else xi = dcol_i64(op.value_col, i);
+      }
+      if (DK == DK_GENERIC && op.lgam) lg = op.lgam[i];
+    };
+    if (CSR) {
+      for (int64_t u = u0 + threadIdx.y; u < u1; u += PL_TY) {
+        const int64_t e0 = A.grp_ptr[u], e1 = A.grp_ptr[u + 1];
+        double gv0 = 0.0, gv1 = 0.0, ga0 = 0.0, ga1 = 0.0;
+        if (K0 == EK_GATHER) gv0 = A.q[(int64_t)A.crow[T0.slot + u] * C + c];
+        if (K1 == EK_GATHER) gv1 = A.q[(int64_t)A.crow[T1.slot + u] * C + c];
+        for (int64_t e = e0; e < e1; e++) {
+          const int64_t i = (int64_t)A.grp_elems[e];
+          double x, lg; long long xi; int64_t xrow;
+          const double raw0 = eterm_load<K0>(A, T0, i, c, C), raw1 = eterm_load<K1>(A, T1, i, c, C);
+          load_x(i, x, xi, xrow, lg);
+          body(i, raw0, raw1, x, xi, xrow, lg, gv0, gv1, ga0, ga1);
+        }
+        if (GRAD) {
+          if (K0 == EK_GATHER) A.grad[(int64_t)A.crow[T0.slot + u] * C + c] += ga0;
+          if (K1 == EK_GATHER) A.grad[(int64_t)A.crow[T1.slot + u] * C + c] += ga1;
+        }
+      }
+    } else {
+      // unit == element. PL_UB elements per trip: all their loads first, then the arithmetic.
+      for (int64_t ub = u0 + threadIdx.y; ub < u1; ub += (int64_t)PL_TY * PL_UB) {
+        double raw0[PL_UB], raw1[PL_UB], x[PL_UB], lg[PL_UB];
+        long long xi[PL_UB];
+        int64_t xrow[PL_UB];
+#pragma unroll
+        for (int b = 0; b < PL_UB; b++) {
+          const int64_t i = ub + (int64_t)b * PL_TY;
+          raw0[b] = raw1[b] = 0.0; x[b] = 0.0; xi[b] = 0; xrow[b] = 0; lg[b] = qnan;
+          if (i < u1) {
+            raw0[b] = eterm_load<K0>(A, T0, i, c, C);
+            raw1[b] = eterm_load<K1>(A, T1, i, c, C);
+            load_x(i, x[b], xi[b], xrow[b], lg[b]);
+          }
+        }
+        double ga0 = 0.0, ga1 = 0.0;
+#pragma unroll
+        for (int b = 0; b < PL_UB; b++) {
+          const int64_t i = ub + (int64_t)b * PL_TY;
+          if (i < u1) body(i, raw0[b], raw1[b], x[b], xi[b], xrow[b], lg[b], 0.0, 0.0, ga0, ga1);
+        }
       }
     }
   }
@@ -538,9 +590,9 @@ __global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate_fast(const __grid_con
 }
 
 // host side: eligibility + dispatch. Returns 1 if launched, 0 if the op needs the generic kernel.
-template <bool GRAD, bool NORMAL>
+template <bool GRAD, int DK>
 static int fast_dispatch(int k0, int k1, const FastArgs& F, dim3 grid, dim3 block, cudaStream_t st) {
-#define FAST_CASE(A_, B_) if (k0 == A_ && k1 == B_) { k_plate_fast<GRAD, NORMAL, A_, B_><<<grid, block, 0, st>>>(F); return 1; }
+#define FAST_CASE(A_, B_) if (k0 == A_ && k1 == B_) { k_plate_fast<GRAD, DK, A_, B_><<<grid, block, 0, st>>>(F); return 1; }
   FAST_CASE(EK_NONE, EK_NONE)
   FAST_CASE(EK_LATENT_X, EK_NONE)
   FAST_CASE(EK_GATHER, EK_NONE)
@@ -583,9 +635,13 @@ static int plate_fast_launch(const PlateArgs& A, bool grad, dim3 grid, dim3 bloc
       if (F.ej[k] == 1) { n_sig++; if (kinds[k] != EK_SELECT2) normal = false; }
     if (n_sig > 1) normal = false;
   }
+  int dk = normal ? DK_NORMAL : DK_GENERIC;
+  if (!normal && (op.dist == FC_BERNOULLI || op.dist == FC_CATEGORICAL) && op.p[0].invariant) dk = DK_TWOVAL;
   int ok;
-  if (grad) ok = normal ? fast_dispatch<true, true>(kinds[0], kinds[1], F, grid, block, st) : fast_dispatch<true, false>(kinds[0], kinds[1], F, grid, block, st);
-  else ok = normal ? fast_dispatch<false, true>(kinds[0], kinds[1], F, grid, block, st) : fast_dispatch<false, false>(kinds[0], kinds[1], F, grid, block, st);
+  if (grad) ok = dk == DK_NORMAL ? fast_dispatch<true, DK_NORMAL>(kinds[0], kinds[1], F, grid, block, st)
+               : (dk == DK_TWOVAL ? fast_dispatch<true, DK_TWOVAL>(kinds[0], kinds[1], F, grid, block, st) : fast_dispatch<true, DK_GENERIC>(kinds[0], kinds[1], F, grid, block, st));
+  else ok = dk == DK_NORMAL ? fast_dispatch<false, DK_NORMAL>(kinds[0], kinds[1], F, grid, block, st)
+            : (dk == DK_TWOVAL ? fast_dispatch<false, DK_TWOVAL>(kinds[0], kinds[1], F, grid, block, st) : fast_dispatch<false, DK_GENERIC>(kinds[0], kinds[1], F, grid, block, st));
   return ok;
 }
 

@@ -13,6 +13,7 @@
 // aggregate acceptance rate with gain 2 * sweep^-gamma. Any positive scale leaves pi_beta
 // invariant, so only efficiency is affected, not the target.
 #include "fc_mh.cuh"
+#include "fc_fastmath.cuh"
 
 namespace fc {
 int32_t dev_reduce(int op, const double* d_x, int64_t n, double m, double* d_scratch, double* d_out, cudaStream_t st);
@@ -45,59 +46,126 @@ __global__ void k_sub_exp(const double* __restrict__ x, double sub, double* __re
   if (out_exp) out_exp[i] = exp(v);
 }
 
-// ---- next_beta (smc.rs:588-622): bisection state lives on the device; 65 ESS evaluations, each
-// two fixed-order reductions over (log_w, ll) ----
+// ---- next_beta (smc.rs:588-622) and the reweight log-sum-exp (smc.rs:512-524) ----
+// ess_at(b) = exp(2 lse(lv) - lse(2 lv)), lv_i = log_w_i + (b - beta) ll_i. One launch per
+// evaluation: a single streaming pass keeps the running (max, sum e, sum e^2) triple with
+// e = exp(lv - max) -- sum exp(2 lv - 2 max) is sum e^2, so one exp per particle serves both
+// log-sum-exps -- the last block to finish folds the per-block triples in fixed order and
+// advances the bisection state on the device. The bisection stops issuing work once the
+// interval has collapsed (mid == lo or mid == hi is a fixed point of the reference's loop).
 struct Bisect {
   double beta, lo, hi, mid, target, n;
-  double m1;       // max of lv at `mid`
-  int done;
+  double lse1;     // lse(lv) of the last evaluation (the reweight normaliser when mid == beta_new)
+  int done;        // 1: ess_at(1) >= target; 2: interval collapsed
+  unsigned counter;
 };
-__global__ void k_nb_max(const double* __restrict__ log_w, const double* __restrict__ ll, const Bisect* __restrict__ B, double* __restrict__ part, int64_t P) {
-  double d = B->mid - B->beta;
-  double acc = d_neg_inf();
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (int64_t)gridDim.x * blockDim.x) acc = fmax(acc, log_w[i] + d * ll[i]);
-  __shared__ double sm[256];
-  sm[threadIdx.x] = acc;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + o]); __syncthreads(); }
-  if (threadIdx.x == 0) part[blockIdx.x] = sm[0];
+struct Tri { double m, s1, s2; };
+__device__ __forceinline__ void tri_merge(Tri& a, const Tri& b) {
+  if (b.m == d_neg_inf() && b.s1 == 0.0) return;
+  if (a.m == d_neg_inf() && a.s1 == 0.0) { a = b; return; }
+  double m = fmax(a.m, b.m);
+  double fa = a.m == m ? 1.0 : exp(a.m - m), fb = b.m == m ? 1.0 : exp(b.m - m);
+  a.s1 = a.s1 * fa + b.s1 * fb;
+  a.s2 = a.s2 * (fa * fa) + b.s2 * (fb * fb);
+  a.m = m;
 }
-__global__ void k_nb_max_final(const double* __restrict__ part, int nb, Bisect* __restrict__ B) {
-  __shared__ double sm[256];
-  double acc = d_neg_inf();
-  for (int i = threadIdx.x; i < nb; i += 256) acc = fmax(acc, part[i]);
-  sm[threadIdx.x] = acc;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + o]); __syncthreads(); }
-  if (threadIdx.x == 0) B->m1 = sm[0];
-}
-__global__ void k_nb_sums(const double* __restrict__ log_w, const double* __restrict__ ll, const Bisect* __restrict__ B, double* __restrict__ part, int64_t P) {
-  double d = B->mid - B->beta, m1 = B->m1;
-  double s1 = 0.0, s2 = 0.0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (int64_t)gridDim.x * blockDim.x) {
-    double lv = log_w[i] + d * ll[i];
-    s1 += exp(lv - m1);
-    s2 += exp(2.0 * lv - 2.0 * m1);
+#define NB_THREADS 256
+__device__ __forceinline__ void tri_push8(Tri& acc, const double (&lv)[8]) {
+  double cm = lv[0];
+#pragma unroll
+  for (int k = 1; k < 8; k++) cm = fmax(cm, lv[k]);  // NaN-ignoring, as f64::max (numerical.rs:19)
+  if (cm > acc.m) {
+    double f = acc.m == d_neg_inf() ? 0.0 : exp(acc.m - cm);
+    acc.s1 *= f; acc.s2 *= f * f; acc.m = cm;
   }
-  __shared__ double sa[256], sb[256];
-  sa[threadIdx.x] = s1; sb[threadIdx.x] = s2;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) { sa[threadIdx.x] += sa[threadIdx.x + o]; sb[threadIdx.x] += sb[threadIdx.x + o]; } __syncthreads(); }
-  if (threadIdx.x == 0) { part[blockIdx.x] = sa[0]; part[RDB + blockIdx.x] = sb[0]; }
+  if (acc.m == d_neg_inf()) {  // only -inf (or NaN) so far: exp(x - max) is NaN for NaN, else the lse is -inf
+#pragma unroll
+    for (int k = 0; k < 8; k++) if (lv[k] != lv[k]) { acc.s1 += lv[k]; acc.s2 += lv[k]; }
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    double x = lv[k] - acc.m;
+    double e = (x == x) ? fast_exp(x) : x;  // NaN propagates into the sums as exp(NaN) does
+    if (x < -708.0) e = 0.0;
+    acc.s1 += e;
+    acc.s2 += e * e;
+  }
 }
-// first = 1: this was the ess_at(1.0) probe (smc.rs:605-607)
-__global__ void k_nb_update(const double* __restrict__ part, int nb, Bisect* __restrict__ B, int first) {
-  __shared__ double sa[256], sb[256];
-  double a = 0.0, b = 0.0;
-  for (int i = threadIdx.x; i < nb; i += 256) { a += part[i]; b += part[RDB + i]; }
-  sa[threadIdx.x] = a; sb[threadIdx.x] = b;
+// mode 0: bisection probe at B->mid (first = 1: the ess_at(1.0) probe); mode 1: lse only at d_fixed
+__global__ void __launch_bounds__(NB_THREADS) k_nb_eval(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B,
+                                                        Tri* __restrict__ part, int64_t P, int mode, int first, double d_fixed) {
+  if (mode == 0 && B->done) return;
+  const double d = mode == 0 ? B->mid - B->beta : d_fixed;
+  Tri acc; acc.m = d_neg_inf(); acc.s1 = 0.0; acc.s2 = 0.0;
+  const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
+  const int64_t P2 = P >> 1;  // double2 units
+  for (int64_t v0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; v0 < P2; v0 += nthreads * 4) {
+    double lv[8];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      int64_t v = v0 + (int64_t)k * nthreads;
+      if (v < P2) {
+        double2 a = __ldg((const double2*)ll + v);
+        double2 w = log_w ? __ldg((const double2*)log_w + v) : make_double2(lw_const, lw_const);
+        lv[2 * k] = w.x + d * a.x; lv[2 * k + 1] = w.y + d * a.y;
+      } else lv[2 * k] = lv[2 * k + 1] = d_neg_inf();
+    }
+    tri_push8(acc, lv);
+  }
+  if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    double lv[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) lv[k] = d_neg_inf();
+    lv[0] = (log_w ? log_w[P - 1] : lw_const) + d * ll[P - 1];
+    tri_push8(acc, lv);
+  }
+  __shared__ Tri sm[NB_THREADS / 32];
+  __shared__ bool is_last;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    Tri b;
+    b.m = __shfl_down_sync(0xffffffffu, acc.m, o); b.s1 = __shfl_down_sync(0xffffffffu, acc.s1, o); b.s2 = __shfl_down_sync(0xffffffffu, acc.s2, o);
+    tri_merge(acc, b);
+  }
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
   __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) { sa[threadIdx.x] += sa[threadIdx.x + o]; sb[threadIdx.x] += sb[threadIdx.x + o]; } __syncthreads(); }
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(acc, sm[w]);
+    part[blockIdx.x] = acc;
+    __threadfence();
+    unsigned t = atomicAdd(&B->counter, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // last block: fold the per-block triples in block order (deterministic), then update the state
+  Tri t; t.m = d_neg_inf(); t.s1 = 0.0; t.s2 = 0.0;
+  const int nb = gridDim.x;
+  const int per = (nb + NB_THREADS - 1) / NB_THREADS;
+  for (int i = threadIdx.x * per; i < min(nb, (threadIdx.x + 1) * per); i++) {
+    Tri b;  // written by other blocks: read through L2
+    b.m = __ldcg(&part[i].m); b.s1 = __ldcg(&part[i].s1); b.s2 = __ldcg(&part[i].s2);
+    tri_merge(t, b);
+  }
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {  // ordered (left-to-right) tree
+    Tri b;
+    b.m = __shfl_down_sync(0xffffffffu, t.m, o); b.s1 = __shfl_down_sync(0xffffffffu, t.s1, o); b.s2 = __shfl_down_sync(0xffffffffu, t.s2, o);
+    if (((threadIdx.x & 31) & (2 * o - 1)) == 0) tri_merge(t, b);
+  }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = t;
+  __syncthreads();
   if (threadIdx.x != 0) return;
-  if (B->done) return;
-  double m1 = B->m1;
-  double lse1 = (m1 == d_neg_inf()) ? d_neg_inf() : (sa[0] == 0.0 ? d_neg_inf() : m1 + log(sa[0]));
-  double lse2 = (m1 == d_neg_inf()) ? d_neg_inf() : (sb[0] == 0.0 ? d_neg_inf() : 2.0 * m1 + log(sb[0]));
+  for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(t, sm[w]);
+  B->counter = 0;
+  const double ninf = d_neg_inf();
+  double lse1 = (t.m == ninf && t.s1 == 0.0) ? ninf : (t.s1 == 0.0 ? ninf : t.m + log(t.s1));
+  double lse2 = (t.m == ninf && t.s2 == 0.0) ? ninf : (t.s2 == 0.0 ? ninf : 2.0 * t.m + log(t.s2));
+  B->lse1 = lse1;
+  if (mode != 0) return;
   double ess = (!isfinite(lse1) || !isfinite(lse2)) ? B->n : exp(2.0 * lse1 - lse2);
   if (first) {
     if (ess >= B->target) { B->hi = 1.0; B->done = 1; return; }
@@ -106,15 +174,38 @@ __global__ void k_nb_update(const double* __restrict__ part, int nb, Bisect* __r
     if (ess < B->target) B->hi = B->mid; else B->lo = B->mid;
   }
   B->mid = 0.5 * (B->lo + B->hi);
+  if (B->mid == B->lo || B->mid == B->hi) B->done = 2;
+}
+// normalised weights after the reweight: log_w' = (log_w + d ll) - log_norm, w = exp(log_w')
+__global__ void k_reweight(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, double d, const Bisect* __restrict__ B,
+                           double* __restrict__ out_log, double* __restrict__ out_w, int64_t P) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const double log_norm = B->lse1;
+  if (!isfinite(log_norm)) {  // normalize_particles' uniform fallback (smc.rs:719-753)
+    if (out_log) out_log[i] = -log((double)P);
+    out_w[i] = 1.0 / (double)P;
+    return;
+  }
+  double v = ((log_w ? log_w[i] : lw_const) + d * ll[i]) - log_norm;
+  if (out_log) out_log[i] = v;
+  out_w[i] = exp(v);
 }
 
 // gather particle planes by ancestor index (resample_particles, smc.rs:326-349)
 template <class T>
-__global__ void k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P) {
+__global__ void __launch_bounds__(256) k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P) {
   int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= P) return;
-  int64_t a = (int64_t)idx[j];
-  for (int64_t r = blockIdx.y; r < rows; r += gridDim.y) dst[r * P + j] = src[r * P + a];
+  const int64_t a = (int64_t)idx[j];
+  // rows r = blockIdx.y*8 + k (+ 8*gridDim.y ...): 8 independent loads in flight per thread
+  for (int64_t r0 = (int64_t)blockIdx.y * 8; r0 < rows; r0 += (int64_t)gridDim.y * 8) {
+    T v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) if (r0 + k < rows) v[k] = src[(r0 + k) * P + a];
+#pragma unroll
+    for (int k = 0; k < 8; k++) if (r0 + k < rows) dst[(r0 + k) * P + j] = v[k];
+  }
 }
 __global__ void k_uniform_one(double* out, uint64_t seed, uint64_t tag, int64_t n) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -138,6 +229,8 @@ struct fc_smc_session {
   fc::DevBuf<fc::disc_t> qd, qd2;
   fc::DevBuf<uint64_t> idx, n_accept;
   fc::DevBuf<fc::Bisect> bis;
+  fc::DevBuf<fc::Tri> tri;
+  bool log_w_uniform = true;  // log_w == -ln n everywhere (initially and after every resample)
   fc::ResampleWork* rw = nullptr;
   double beta = 0.0, log_evidence = 0.0;
   uint64_t steps = 0, moves = 0;
@@ -146,29 +239,52 @@ struct fc_smc_session {
 
 namespace fc {
 
-static int32_t smc_next_beta(fc_smc_session* S, double target_ess, double* out) {
-  cudaStream_t st = S->P->stream;
-  int64_t n = S->n;
-  int nb = (int)std::max<int64_t>(1, std::min<int64_t>(RDB, cdiv(n, 256)));
+static int nb_blocks(int64_t n) { return (int)std::max<int64_t>(1, std::min<int64_t>(RDB, cdiv(n, NB_THREADS * 8))); }
+
+static int32_t next_beta_dev(cudaStream_t st, const double* lw, double lwc, const double* ll, int64_t n, double beta, double target_ess, Bisect* d_bis, Tri* d_tri,
+                             uint64_t* launches, double* out) {
+  const int nb = nb_blocks(n);
   Bisect hb;
-  hb.beta = S->beta; hb.lo = S->beta; hb.hi = 1.0; hb.mid = 1.0; hb.target = target_ess; hb.n = (double)n; hb.m1 = 0.0; hb.done = 0;
-  FC_CUDA(cudaMemcpyAsync(S->bis.p, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
+  hb.beta = beta; hb.lo = beta; hb.hi = 1.0; hb.mid = 1.0; hb.target = target_ess; hb.n = (double)n; hb.lse1 = 0.0; hb.done = 0; hb.counter = 0;
+  FC_CUDA(cudaMemcpyAsync(d_bis, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
   for (int it = 0; it < 65; it++) {
-    k_nb_max<<<nb, 256, 0, st>>>(S->log_w.p, S->ll.p, S->bis.p, S->scratch.p, n);
-    k_nb_max_final<<<1, 256, 0, st>>>(S->scratch.p, nb, S->bis.p);
-    k_nb_sums<<<nb, 256, 0, st>>>(S->log_w.p, S->ll.p, S->bis.p, S->scratch.p, n);
-    k_nb_update<<<1, 256, 0, st>>>(S->scratch.p, nb, S->bis.p, it == 0 ? 1 : 0);
-    S->P->n_kernel_launches += 4;
-    if (it == 0) {  // early exit when a full jump to beta = 1 keeps the ESS above target
-      FC_CUDA(cudaMemcpyAsync(&hb, S->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, ll, d_bis, d_tri, n, 0, it == 0 ? 1 : 0, 0.0);
+    if (launches) *launches += 1;
+    if (it == 0 || it == 56) {  // early exits: ess_at(1) >= target, or the interval has collapsed
+      FC_CUDA(cudaMemcpyAsync(&hb, d_bis, sizeof(hb), cudaMemcpyDeviceToHost, st));
       FC_CUDA(cudaStreamSynchronize(st));
-      if (hb.done) { *out = 1.0; return FC_OK; }
+      if (hb.done == 1) { *out = 1.0; return FC_OK; }
+      if (hb.done == 2) break;
     }
   }
   FC_KERNEL_CHECK();
+  FC_CUDA(cudaMemcpyAsync(&hb, d_bis, sizeof(hb), cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  *out = std::fmin(std::fmax(hb.hi, beta + 1e-9), 1.0);  // smc.rs:621
+  return FC_OK;
+}
+static int32_t smc_next_beta(fc_smc_session* S, double target_ess, double* out) {
+  return next_beta_dev(S->P->stream, S->log_w_uniform ? nullptr : S->log_w.p, -std::log((double)S->n), S->ll.p, S->n, S->beta, target_ess, S->bis.p, S->tri.p,
+                       &S->P->n_kernel_launches, out);
+}
+
+// reweight (smc.rs:512-531): log_norm = lse(log_w + d ll); w = exp(log_w + d ll - log_norm).
+// log_w itself is only materialised when it will be read again (the final step).
+static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, double* log_norm) {
+  cudaStream_t st = S->P->stream;
+  int64_t n = S->n;
+  const double* lw = S->log_w_uniform ? nullptr : S->log_w.p;
+  const double lwc = -std::log((double)n);
+  FC_CUDA(cudaMemsetAsync(&S->bis.p->counter, 0, sizeof(unsigned), st));
+  k_nb_eval<<<nb_blocks(n), NB_THREADS, 0, st>>>(lw, lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
+  k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n);
+  FC_KERNEL_CHECK();
+  S->P->n_kernel_launches += 2;
+  Bisect hb;
   FC_CUDA(cudaMemcpyAsync(&hb, S->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
-  *out = std::fmin(std::fmax(hb.hi, S->beta + 1e-9), 1.0);  // smc.rs:621
+  *log_norm = hb.lse1;
+  if (write_log_w) { std::swap(S->log_w.p, S->comb.p); std::swap(S->log_w.n, S->comb.n); S->log_w_uniform = false; }
   return FC_OK;
 }
 
@@ -185,15 +301,9 @@ static int32_t smc_temper_step(fc_smc_session* S) {
   FC_TRY(smc_next_beta(S, target_ess, &beta_new));
   if (S->steps >= 10000) beta_new = 1.0;
   double d_beta = beta_new - S->beta;
-  k_combine<<<nbk, 256, 0, st>>>(S->log_w.p, S->ll.p, d_beta, S->comb.p, n);
-  P->n_kernel_launches += 1;
   double log_norm;
-  FC_TRY(dev_log_sum_exp(S->comb.p, n, S->scratch.p, &log_norm, st));
-  P->n_kernel_launches += 4;
+  FC_TRY(smc_reweight(S, d_beta, beta_new >= 1.0, &log_norm));
   S->log_evidence += log_norm;
-  if (std::isfinite(log_norm)) k_sub_exp<<<nbk, 256, 0, st>>>(S->comb.p, log_norm, S->log_w.p, S->w.p, n);
-  else { k_fill2<<<nbk, 256, 0, st>>>(S->log_w.p, neg_ln_n, n); k_fill2<<<nbk, 256, 0, st>>>(S->w.p, 1.0 / (double)n, n); }
-  P->n_kernel_launches += 1;
   S->beta = beta_new;
   if (S->beta < 1.0) {
     // resample (smc.rs:534-541)
@@ -202,14 +312,14 @@ static int32_t smc_temper_step(fc_smc_session* S) {
     k_uniform_one<<<(unsigned)cdiv(cdiv(nu, 2), 256), 256, 0, st>>>(S->us.p, S->seed, 0x1000000000000000ULL | S->steps, nu);
     FC_TRY(resample_dev(S->cfg.resampling_method, S->w.p, n, S->us.p, S->idx.p, *S->rw, st, &P->n_kernel_launches));
     dim3 gg(nbk, 1);
-    if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(S->q.p, S->q2.p, S->idx.p, P->d_cont, n); std::swap(S->q.p, S->q2.p); std::swap(S->q.n, S->q2.n); }
-    if (P->d_disc) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(S->qd.p, S->qd2.p, S->idx.p, P->d_disc, n); std::swap(S->qd.p, S->qd2.p); std::swap(S->qd.n, S->qd2.n); }
-    gg.y = 3;
+    if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_cont, 8), 64); k_gather<double><<<gg, 256, 0, st>>>(S->q.p, S->q2.p, S->idx.p, P->d_cont, n); std::swap(S->q.p, S->q2.p); std::swap(S->q.n, S->q2.n); }
+    if (P->d_disc) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_disc, 8), 64); k_gather<disc_t><<<gg, 256, 0, st>>>(S->qd.p, S->qd2.p, S->idx.p, P->d_disc, n); std::swap(S->qd.p, S->qd2.p); std::swap(S->qd.n, S->qd2.n); }
+    gg.y = 1;
     k_gather<double><<<gg, 256, 0, st>>>(S->lp3.p, S->lp3b.p, S->idx.p, 3, n);
     std::swap(S->lp3.p, S->lp3b.p); std::swap(S->lp3.n, S->lp3b.n);
-    k_fill2<<<nbk, 256, 0, st>>>(S->log_w.p, neg_ln_n, n);
+    S->log_w_uniform = true;  // weight 1/n, log_weight ln(1/n) (smc.rs:338-345); materialised on demand
     FC_KERNEL_CHECK();
-    P->n_kernel_launches += 5;
+    P->n_kernel_launches += 4;
     // pi_beta-invariant rejuvenation (smc.rs:544-554)
     for (uint64_t r = 0; r < S->cfg.rejuvenation_steps; r++) {
       FC_TRY(S->eng.step(S->q.p, S->qd.p, S->lp3.p, S->total.p, S->n_accept.p, S->moves, S->beta, true, 0.44, 0.7));
@@ -220,12 +330,38 @@ static int32_t smc_temper_step(fc_smc_session* S) {
     FC_KERNEL_CHECK();
     P->n_kernel_launches += 1;
   }
+  (void)neg_ln_n;
+  return FC_OK;
+}
+
+// standalone probe of next_beta on host arrays (parity test against the oracle)
+int32_t next_beta_host(const double* h_log_w, const double* h_ll, size_t n, double beta, double target_ess, double* out) {
+  DevBuf<double> lw, ll;
+  DevBuf<Bisect> bis;
+  DevBuf<Tri> tri;
+  FC_CUDA(lw.reserve(n)); FC_CUDA(ll.reserve(n)); FC_CUDA(bis.reserve(1)); FC_CUDA(tri.reserve(RDB));
+  FC_CUDA(cudaMemcpy(lw.p, h_log_w, n * 8, cudaMemcpyHostToDevice));
+  FC_CUDA(cudaMemcpy(ll.p, h_ll, n * 8, cudaMemcpyHostToDevice));
+  return next_beta_dev(nullptr, lw.p, 0.0, ll.p, (int64_t)n, beta, target_ess, bis.p, tri.p, nullptr, out);
+}
+
+// log_w as an array (callers that read it: fc_smc_get, fc_smc_device_state)
+static int32_t smc_materialise_log_w(fc_smc_session* S) {
+  if (!S->log_w_uniform) return FC_OK;
+  k_fill2<<<(unsigned)cdiv(S->n, 256), 256, 0, S->P->stream>>>(S->log_w.p, -std::log((double)S->n), S->n);
+  FC_KERNEL_CHECK();
+  S->P->n_kernel_launches += 1;
   return FC_OK;
 }
 
 }  // namespace fc
 
 extern "C" {
+
+int32_t fc_next_beta(const double* h_log_w, const double* h_ll, size_t n, double beta, double target_ess, double* out) {  // smc.rs:588-622
+  if (!h_log_w || !h_ll || !out || n == 0) { fc::set_error("NULL / empty argument"); return FC_ERR_INVALID_ARGUMENT; }
+  return fc::next_beta_host(h_log_w, h_ll, n, beta, target_ess, out);
+}
 
 void fc_smc_config_default(fc_smc_config* cfg) {  // SMCConfig::default (smc.rs:181-189)
   cfg->resampling_method = FC_RESAMPLE_SYSTEMATIC;
@@ -258,7 +394,7 @@ int32_t fc_smc_create(fc_program* p, const fc_smc_config* cfg, uint64_t seed, si
   FC_CUDA(S->lp3.reserve(3 * N)); FC_CUDA(S->lp3b.reserve(3 * N));
   for (auto* b : {&S->total, &S->ll, &S->log_w, &S->comb, &S->w}) FC_CUDA(b->reserve(N));
   FC_CUDA(S->scratch.reserve(2 * RDB + 16));
-  FC_CUDA(S->idx.reserve(N)); FC_CUDA(S->n_accept.reserve(N)); FC_CUDA(S->bis.reserve(1));
+  FC_CUDA(S->idx.reserve(N)); FC_CUDA(S->n_accept.reserve(N)); FC_CUDA(S->bis.reserve(1)); FC_CUDA(S->tri.reserve(RDB));
   FC_CUDA(cudaMemsetAsync(S->n_accept.p, 0, N * 8, st));
   S->rw = resample_work_new();
   FC_TRY(S->eng.init(p, N, true, seed ^ 0x5bd1e995u, first_particle));
@@ -292,6 +428,7 @@ int32_t fc_smc_step(fc_smc_session* s, double* beta_out) {
       s->log_evidence = le;
       s->beta = 1.0;
       std::swap(s->log_w.p, s->comb.p); std::swap(s->log_w.n, s->comb.n);
+      s->log_w_uniform = false;
       s->steps = 1;
     } else {
       FC_TRY(smc_temper_step(s));
@@ -310,6 +447,7 @@ int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, doub
   cudaStream_t st = p->stream;
   int64_t n = s->n;
   unsigned nbk = (unsigned)cdiv(n, 256);
+  FC_TRY(smc_materialise_log_w(s));
   if (h_weight || h_log_weight) {
     double log_norm;
     FC_TRY(dev_log_sum_exp(s->log_w.p, n, s->scratch.p, &log_norm, st));
@@ -331,7 +469,7 @@ int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, doub
 int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dvalues, double** d_log_w, double** d_loglik) {
   if (d_values) *d_values = s->q.p;
   if (d_dvalues) *d_dvalues = s->qd.p;
-  if (d_log_w) *d_log_w = s->log_w.p;
+  if (d_log_w) { FC_TRY(fc::smc_materialise_log_w(s)); *d_log_w = s->log_w.p; }
   if (d_loglik) *d_loglik = s->ll.p;
   return FC_OK;
 }

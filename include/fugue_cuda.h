@@ -262,6 +262,11 @@ int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, doub
 int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dvalues,
                             double** d_log_w, double** d_loglik);
 int32_t fc_smc_destroy(fc_smc_session* s);
+/* next_beta (smc.rs:588-622) on host arrays: the largest beta' in (beta, 1] whose incremental
+ * weights log_w + (beta' - beta) * ll keep ESS >= target_ess (64-step bisection; 1.0 if a full
+ * jump already does). Parity probe for the tempering ladder. */
+int32_t fc_next_beta(const double* h_log_w, const double* h_ll, size_t n, double beta,
+                     double target_ess, double* out);
 /* systematic/stratified/multinomial_indices (smc.rs:255-314) with the uniforms passed explicitly:
  * 1 uniform for systematic (the raw rng.gen::<f64>(), before /n), n for the others.
  * Indices are bit-exact w.r.t. the reference's sequential running sum. */
