@@ -1,0 +1,6 @@
+// fc_plate_g8.cu -- instantiations of the specialised plate kernel: GRAD = true, TY = 8
+// (split over translation units so the build parallelises; see fc_plate.cuh).
+#include "fc_plate.cuh"
+namespace fc {
+FC_PLATE_FAST_INSTANTIATE(true, 8)
+}  // namespace fc

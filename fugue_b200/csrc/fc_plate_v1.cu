@@ -1,0 +1,6 @@
+// fc_plate_v1.cu -- instantiations of the specialised plate kernel: GRAD = false, TY = 1
+// (split over translation units so the build parallelises; see fc_plate.cuh).
+#include "fc_plate.cuh"
+namespace fc {
+FC_PLATE_FAST_INSTANTIATE(false, 1)
+}  // namespace fc
