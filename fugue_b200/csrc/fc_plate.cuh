@@ -364,6 +364,10 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
   }
 }
 
+// chain-vectorised value-only kernel (fc_plate_vec.cu): 0 = not eligible, 1 = launched with
+// partials [n_splits][3][C], 2 = launched and lp3 already updated (single split)
+int plate_vec_launch(const PlateArgs& A, int64_t n_splits, double* d_lp3, cudaStream_t st);
+
 // instantiation units: fc_plate_{v8,v1,g8,g1}.cu (value-only / gradient x TY = 8 / 1)
 template <bool GRAD, int TY>
 int plate_fast_dispatch(int dk, int k0, int k1, const FastArgs& F, dim3 grid, cudaStream_t st);

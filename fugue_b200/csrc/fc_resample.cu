@@ -272,7 +272,10 @@ int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_wor
   ScanState hs;
   hs.k0 = 0; hs.s0 = 0.0; hs.first_cross = 0x7fffffffffffffffLL;
   FC_CUDA(cudaMemcpyAsync(d_state, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
-  int64_t win = 1 << 16;
+  // window policy: for near-uniform weights the running sum needs about as many further elements
+  // to leave a binade as it took to reach it, so after a crossing at element k the next window is
+  // 2k (tiny windows while the sum is still tiny); a window without a crossing doubles.
+  int64_t win = 1 << 10;
   int guard = 0;
   while (hs.k0 < n) {
     if (++guard > 100000) { set_error("exact_prefix_sums: no progress"); return FC_ERR_CUDA; }
@@ -307,7 +310,7 @@ int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_wor
     FC_CUDA(cudaMemcpyAsync(&hs, d_state, sizeof(hs), cudaMemcpyDeviceToHost, st));
     FC_CUDA(cudaStreamSynchronize(st));
     bool crossed = hs.k0 < prev_k0 + len || (hs.k0 == prev_k0 + len && !(hs.s0 < T));
-    win = crossed ? (1 << 16) : std::min<int64_t>(win * 2, (int64_t)1 << 26);
+    win = crossed ? std::min<int64_t>(std::max<int64_t>(2 * (int64_t)hs.k0, 1 << 10), (int64_t)1 << 26) : std::min<int64_t>(win * 2, (int64_t)1 << 26);
   }
   return FC_OK;
 }

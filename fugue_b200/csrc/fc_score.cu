@@ -472,17 +472,20 @@ int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t 
     int64_t ns = cdiv(A.n_units, A.units_per_split);
     const int ty = plate_ty(pl, C);
     dim3 grid((unsigned)cdiv(C, PL_TX), (unsigned)ns), block(PL_TX, PL_TY), fgrid((unsigned)cdiv(C, 256 / ty), (unsigned)ns);
-    if (!plate_fast_launch(A, grad, ty, fgrid, st)) {
+    int vec = grad ? 0 : plate_vec_launch(A, ns, d_lp3, st);
+    if (!vec && !plate_fast_launch(A, grad, ty, fgrid, st)) {
       if (grad) k_plate<true><<<grid, block, 0, st>>>(A);
       else k_plate<false><<<grid, block, 0, st>>>(A);
     }
     FC_KERNEL_CHECK();
+    P->n_kernel_launches += 1;
+    if (vec == 2) continue;  // single split: the kernel added straight into lp3
     F.n_splits = ns;
     F.n_acc = grad ? pl.acc.n_acc : 3;
     for (int a = 0; a < pl.acc.n_acc - 3; a++) F.rows[a] = pl.acc.rows[a];
     k_finish<<<dim3(fin_bx, F.n_acc), 128, 0, st>>>(F);
     FC_KERNEL_CHECK();
-    P->n_kernel_launches += 2;
+    P->n_kernel_launches += 1;
   }
   if (d_total) {
     k_total<<<fin_bx, 128, 0, st>>>(d_lp3, d_total, C);

@@ -58,6 +58,9 @@ struct Bisect {
   double lse1;     // lse(lv) of the last evaluation (the reweight normaliser when mid == beta_new)
   int done;        // 1: ess_at(1) >= target; 2: interval collapsed
   unsigned counter;
+  double max_ll;   // pre-pass (uniform log_w only): max of ll
+  int bad;         // pre-pass: some ll is NaN or +inf => every lse is non-finite => ESS := n (smc.rs:595-601)
+  int _pad;
 };
 struct Tri { double m, s1, s2; };
 __device__ __forceinline__ void tri_merge(Tri& a, const Tri& b) {
@@ -74,9 +77,10 @@ __device__ __forceinline__ void tri_push8(Tri& acc, const double (&lv)[8]) {
   double cm = lv[0];
 #pragma unroll
   for (int k = 1; k < 8; k++) cm = fmax(cm, lv[k]);  // NaN-ignoring, as f64::max (numerical.rs:19)
-  if (cm > acc.m) {
-    double f = acc.m == d_neg_inf() ? 0.0 : exp(acc.m - cm);
-    acc.s1 *= f; acc.s2 *= f * f; acc.m = cm;
+  {  // branch-free rescale to the new running max (f == 1 when the max is unchanged)
+    const double mn = fmax(acc.m, cm);
+    const double f = fast_exp(acc.m - mn);  // acc.m == -inf: the sums are still 0
+    acc.s1 *= f; acc.s2 *= f * f; acc.m = mn;
   }
   if (acc.m == d_neg_inf()) {  // only -inf (or NaN) so far: exp(x - max) is NaN for NaN, else the lse is -inf
 #pragma unroll
@@ -92,34 +96,20 @@ __device__ __forceinline__ void tri_push8(Tri& acc, const double (&lv)[8]) {
     acc.s2 += e * e;
   }
 }
-// mode 0: bisection probe at B->mid (first = 1: the ess_at(1.0) probe); mode 1: lse only at d_fixed
-__global__ void __launch_bounds__(NB_THREADS) k_nb_eval(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B,
-                                                        Tri* __restrict__ part, int64_t P, int mode, int first, double d_fixed) {
-  if (mode == 0 && B->done) return;
-  const double d = mode == 0 ? B->mid - B->beta : d_fixed;
-  Tri acc; acc.m = d_neg_inf(); acc.s1 = 0.0; acc.s2 = 0.0;
-  const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
-  const int64_t P2 = P >> 1;  // double2 units
-  for (int64_t v0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; v0 < P2; v0 += nthreads * 4) {
-    double lv[8];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      int64_t v = v0 + (int64_t)k * nthreads;
-      if (v < P2) {
-        double2 a = __ldg((const double2*)ll + v);
-        double2 w = log_w ? __ldg((const double2*)log_w + v) : make_double2(lw_const, lw_const);
-        lv[2 * k] = w.x + d * a.x; lv[2 * k + 1] = w.y + d * a.y;
-      } else lv[2 * k] = lv[2 * k + 1] = d_neg_inf();
-    }
-    tri_push8(acc, lv);
+// bisection update for one ESS evaluation (smc.rs:605-619)
+__device__ __forceinline__ void nb_update(Bisect* B, double ess, int first) {
+  if (first) {
+    if (ess >= B->target) { B->hi = 1.0; B->done = 1; return; }
+    B->lo = B->beta; B->hi = 1.0;
+  } else {
+    if (ess < B->target) B->hi = B->mid; else B->lo = B->mid;
   }
-  if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-    double lv[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) lv[k] = d_neg_inf();
-    lv[0] = (log_w ? log_w[P - 1] : lw_const) + d * ll[P - 1];
-    tri_push8(acc, lv);
-  }
+  B->mid = 0.5 * (B->lo + B->hi);
+  if (B->mid == B->lo || B->mid == B->hi) B->done = 2;
+}
+// CTA reduction of the per-thread triples; the last CTA to finish folds the per-CTA triples in
+// block order (deterministic) and advances the bisection state.
+__device__ __forceinline__ void nb_fold_update(Tri acc, Bisect* __restrict__ B, Tri* __restrict__ part, int mode, int first) {
   __shared__ Tri sm[NB_THREADS / 32];
   __shared__ bool is_last;
 #pragma unroll
@@ -167,15 +157,139 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval(const double* __restrict
   B->lse1 = lse1;
   if (mode != 0) return;
   double ess = (!isfinite(lse1) || !isfinite(lse2)) ? B->n : exp(2.0 * lse1 - lse2);
-  if (first) {
-    if (ess >= B->target) { B->hi = 1.0; B->done = 1; return; }
-    B->lo = B->beta; B->hi = 1.0;
-  } else {
-    if (ess < B->target) B->hi = B->mid; else B->lo = B->mid;
-  }
-  B->mid = 0.5 * (B->lo + B->hi);
-  if (B->mid == B->lo || B->mid == B->hi) B->done = 2;
+  nb_update(B, ess, first);
 }
+
+// mode 0: bisection probe at B->mid (first = 1: the ess_at(1.0) probe); mode 1: lse only at d_fixed
+__global__ void __launch_bounds__(NB_THREADS) k_nb_eval(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B,
+                                                        Tri* __restrict__ part, int64_t P, int mode, int first, double d_fixed) {
+  if (mode == 0 && B->done) return;
+  const double d = mode == 0 ? B->mid - B->beta : d_fixed;
+  Tri acc; acc.m = d_neg_inf(); acc.s1 = 0.0; acc.s2 = 0.0;
+  const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
+  const int64_t P2 = P >> 1;  // double2 units
+  for (int64_t v0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; v0 < P2; v0 += nthreads * 4) {
+    double lv[8];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      int64_t v = v0 + (int64_t)k * nthreads;
+      if (v < P2) {
+        double2 a = __ldg((const double2*)ll + v);
+        double2 w = log_w ? __ldg((const double2*)log_w + v) : make_double2(lw_const, lw_const);
+        lv[2 * k] = w.x + d * a.x; lv[2 * k + 1] = w.y + d * a.y;
+      } else lv[2 * k] = lv[2 * k + 1] = d_neg_inf();
+    }
+    tri_push8(acc, lv);
+  }
+  if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    double lv[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) lv[k] = d_neg_inf();
+    lv[0] = (log_w ? log_w[P - 1] : lw_const) + d * ll[P - 1];
+    tri_push8(acc, lv);
+  }
+  nb_fold_update(acc, B, part, mode, first);
+}
+
+// ---- uniform log_w (the state adaptive_smc is in whenever next_beta runs: initially and after
+// every resample): lv_i = c + d ll_i, so max lv = c + d max(ll) and the pass needs no running max.
+// k_nb_prepass (once per next_beta call): max(ll) and the "some ll is NaN / +inf" flag. ----
+__global__ void __launch_bounds__(NB_THREADS) k_nb_prepass(const double* __restrict__ ll, int64_t P, Bisect* __restrict__ B, double* __restrict__ part) {
+  double mx = d_neg_inf();
+  int bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) {
+    double v = __ldg(ll + i);
+    bad |= (v != v) || v == d_pos_inf();
+    mx = fmax(mx, v);
+  }
+  mx = warp_max(mx);
+  bad = __any_sync(0xffffffffu, bad);
+  __shared__ double sm[NB_THREADS / 32];
+  __shared__ int sbad[NB_THREADS / 32];
+  __shared__ bool is_last;
+  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5] = mx; sbad[threadIdx.x >> 5] = bad; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) { mx = fmax(mx, sm[w]); bad |= sbad[w]; }
+    part[blockIdx.x] = bad ? d_pos_inf() : mx;  // +inf doubles as the bad marker
+    __threadfence();
+    is_last = atomicAdd(&B->counter, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last || threadIdx.x != 0) return;
+  __threadfence();
+  double m = d_neg_inf();
+  for (int i = 0; i < (int)gridDim.x; i++) m = fmax(m, __ldcg(part + i));
+  B->counter = 0;
+  B->bad = m == d_pos_inf();
+  B->max_ll = m;
+}
+// exp(x) for x <= 0 (fast_exp without the upper clamp; below -708 it returns ~3e-308 instead of
+// 0, which is negligible against a sum that contains exp(0) = 1 for the max element)
+__device__ __forceinline__ double exp_nonpos(double x) {
+  x = fmax(x, -708.0);
+  const double L2E = 1.4426950408889634;
+  const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
+  double t = fma(x, L2E, 6755399441055744.0);
+  int k = __double2loint(t);
+  t -= 6755399441055744.0;
+  double r = fma(t, -LN2_HI, x);
+  r = fma(t, -LN2_LO, r);
+  double q = 1.6059043836821613e-10;
+  q = fma(q, r, 2.08767569878681e-09);
+  q = fma(q, r, 2.505210838544172e-08);
+  q = fma(q, r, 2.755731922398589e-07);
+  q = fma(q, r, 2.7557319223985893e-06);
+  q = fma(q, r, 2.48015873015873e-05);
+  q = fma(q, r, 1.984126984126984e-04);
+  q = fma(q, r, 1.388888888888889e-03);
+  q = fma(q, r, 8.333333333333333e-03);
+  q = fma(q, r, 4.1666666666666664e-02);
+  q = fma(q, r, 1.6666666666666666e-01);
+  q = fma(q, r, 0.5);
+  double p = fma(r * r, q, r) + 1.0;
+  return p * __hiloint2double((k + 1023) << 20, 0);
+}
+__global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B, Tri* __restrict__ part, int64_t P,
+                                                            int mode, int first, double d_fixed) {
+  if (mode == 0 && B->done) return;
+  if (B->bad) {  // every lse is non-finite: ess_at(.) = n (smc.rs:595-601); the reweight normaliser is NaN
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      B->lse1 = __longlong_as_double(0x7ff8000000000000LL);
+      if (mode == 0) nb_update(B, B->n, first);
+    }
+    return;
+  }
+  const double d = mode == 0 ? B->mid - B->beta : d_fixed;
+  const double m = fma(d, B->max_ll, lw_const);  // the same expression as lv of the max element: x <= 0, == 0 there
+  Tri acc; acc.m = m; acc.s1 = 0.0; acc.s2 = 0.0;
+  double t1 = 0.0, t2 = 0.0;  // second accumulator pair (shorter dependency chains)
+  if (m > d_neg_inf()) {
+    const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
+    const int64_t P2 = P >> 1;
+    for (int64_t v0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; v0 < P2; v0 += nthreads * 4) {
+      double2 a[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        int64_t v = v0 + (int64_t)k * nthreads;
+        a[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
+      }
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const double e0 = exp_nonpos(fma(d, a[k].x, lw_const) - m), e1 = exp_nonpos(fma(d, a[k].y, lw_const) - m);
+        acc.s1 += e0; acc.s2 = fma(e0, e0, acc.s2);
+        t1 += e1; t2 = fma(e1, e1, t2);
+      }
+    }
+    if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+      const double e0 = exp_nonpos(fma(d, ll[P - 1], lw_const) - m);
+      acc.s1 += e0; acc.s2 = fma(e0, e0, acc.s2);
+    }
+    acc.s1 += t1; acc.s2 += t2;
+  }
+  nb_fold_update(acc, B, part, mode, first);
+}
+
 // normalised weights after the reweight: log_w' = (log_w + d ll) - log_norm, w = exp(log_w')
 __global__ void k_reweight(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, double d, const Bisect* __restrict__ B,
                            double* __restrict__ out_log, double* __restrict__ out_w, int64_t P) {
@@ -239,16 +353,24 @@ struct fc_smc_session {
 
 namespace fc {
 
-static int nb_blocks(int64_t n) { return (int)std::max<int64_t>(1, std::min<int64_t>(RDB, cdiv(n, NB_THREADS * 8))); }
+// one resident wave: 4 CTAs of 256 threads per SM (56 registers), never more than RDB partials
+static int nb_blocks(int64_t n) {
+  static int sms = 0;
+  if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+  return (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(RDB, 4 * sms), cdiv(n, NB_THREADS * 8)));
+}
 
 static int32_t next_beta_dev(cudaStream_t st, const double* lw, double lwc, const double* ll, int64_t n, double beta, double target_ess, Bisect* d_bis, Tri* d_tri,
                              uint64_t* launches, double* out) {
   const int nb = nb_blocks(n);
   Bisect hb;
   hb.beta = beta; hb.lo = beta; hb.hi = 1.0; hb.mid = 1.0; hb.target = target_ess; hb.n = (double)n; hb.lse1 = 0.0; hb.done = 0; hb.counter = 0;
+  hb.max_ll = 0.0; hb.bad = 0; hb._pad = 0;
   FC_CUDA(cudaMemcpyAsync(d_bis, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
+  if (!lw) { k_nb_prepass<<<nb, NB_THREADS, 0, st>>>(ll, n, d_bis, (double*)d_tri); if (launches) *launches += 1; }
   for (int it = 0; it < 65; it++) {
-    k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, ll, d_bis, d_tri, n, 0, it == 0 ? 1 : 0, 0.0);
+    if (lw) k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, ll, d_bis, d_tri, n, 0, it == 0 ? 1 : 0, 0.0);
+    else k_nb_eval_uni<<<nb, NB_THREADS, 0, st>>>(lwc, ll, d_bis, d_tri, n, 0, it == 0 ? 1 : 0, 0.0);
     if (launches) *launches += 1;
     if (it == 0 || it == 56) {  // early exits: ess_at(1) >= target, or the interval has collapsed
       FC_CUDA(cudaMemcpyAsync(&hb, d_bis, sizeof(hb), cudaMemcpyDeviceToHost, st));
@@ -276,7 +398,9 @@ static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, 
   const double* lw = S->log_w_uniform ? nullptr : S->log_w.p;
   const double lwc = -std::log((double)n);
   FC_CUDA(cudaMemsetAsync(&S->bis.p->counter, 0, sizeof(unsigned), st));
-  k_nb_eval<<<nb_blocks(n), NB_THREADS, 0, st>>>(lw, lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
+  // (max_ll / bad in the Bisect block are those of this step's next_beta pre-pass: same ll)
+  if (lw) k_nb_eval<<<nb_blocks(n), NB_THREADS, 0, st>>>(lw, lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
+  else k_nb_eval_uni<<<nb_blocks(n), NB_THREADS, 0, st>>>(lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
   k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n);
   FC_KERNEL_CHECK();
   S->P->n_kernel_launches += 2;
@@ -340,9 +464,11 @@ int32_t next_beta_host(const double* h_log_w, const double* h_ll, size_t n, doub
   DevBuf<Bisect> bis;
   DevBuf<Tri> tri;
   FC_CUDA(lw.reserve(n)); FC_CUDA(ll.reserve(n)); FC_CUDA(bis.reserve(1)); FC_CUDA(tri.reserve(RDB));
-  FC_CUDA(cudaMemcpy(lw.p, h_log_w, n * 8, cudaMemcpyHostToDevice));
+  bool uniform = true;  // the state adaptive_smc calls next_beta in: takes the single-stream path
+  for (size_t i = 1; i < n && uniform; i++) uniform = h_log_w[i] == h_log_w[0];
+  if (!uniform) FC_CUDA(cudaMemcpy(lw.p, h_log_w, n * 8, cudaMemcpyHostToDevice));
   FC_CUDA(cudaMemcpy(ll.p, h_ll, n * 8, cudaMemcpyHostToDevice));
-  return next_beta_dev(nullptr, lw.p, 0.0, ll.p, (int64_t)n, beta, target_ess, bis.p, tri.p, nullptr, out);
+  return next_beta_dev(nullptr, uniform ? nullptr : lw.p, h_log_w[0], ll.p, (int64_t)n, beta, target_ess, bis.p, tri.p, nullptr, out);
 }
 
 // log_w as an array (callers that read it: fc_smc_get, fc_smc_device_state)
