@@ -43,10 +43,11 @@ struct DenseArgs {
   const double* q;
   double* part;
   int64_t C, N;
-  int64_t rows_per_split;  // multiple of DN_TN
+  int64_t rows_per_split;  // multiple of DN_TN * sub
   int32_t K, dj, dt;       // dense width, dense param index, dense term index
   int32_t n_acc;           // accumulators per split in `part`
   int32_t n_red;
+  int32_t sub;             // 32-row sub-tiles per pipeline stage (1 for wide matrices; > 1 amortises the stage hand-over when K is small)
 };
 
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
@@ -123,7 +124,7 @@ __device__ __noinline__ void glm_generic_elem(const DOp& op, int dj, double sarg
 // MT = number of 8-row gradient tiles per warp (K padded to 8*MT); GRAD=false skips the
 // second contraction (value only: MH / SMC).
 template <int MODE, bool GRAD, int MT, int NT>
-__global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_constant__ DenseArgs A) {
+__global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(const __grid_constant__ DenseArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int NW = DN_NW(NT), NTHR = DN_THREADS(NT), LDW = DN_LDW(NT), WC = 8 * NT;  // WC = chains per warp
   const int K = A.K;
@@ -140,11 +141,13 @@ __global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_co
   double* s_beta = (double*)(smem_raw + 128);                             // [KP4][DN_LDB]
   double* s_w = s_beta + (size_t)KP4 * DN_LDB;                            // [8 warps][DN_TN][DN_LDW]
   double* s_x = s_w + NW * DN_TN * LDW;                                 // [DN_STAGES][DN_TN*K + pad]
-  const int x_stage_elems = ((DN_TN * K + 8 + 15) & ~15);                 // + zero pad for k >= K reads
+  constexpr int SUB = MT == 1 ? 8 : (MT == 2 ? 4 : (MT == 4 ? 2 : 1));  // == dense_sub(K): MT is chosen from K on the host
+  constexpr int ST_ROWS = DN_TN * SUB;                                   // rows per pipeline stage
+  const int x_stage_elems = ((ST_ROWS * K + 8 + 15) & ~15);               // + zero pad for k >= K reads
 
   const int64_t row_begin = (int64_t)blockIdx.y * A.rows_per_split;
   const int64_t row_end = min(A.N, row_begin + A.rows_per_split);
-  const int n_tiles = (int)((row_end - row_begin + DN_TN - 1) / DN_TN);
+  const int n_tiles = (int)((row_end - row_begin + ST_ROWS - 1) / ST_ROWS);  // stages
 
   if (tid == 0) {
     for (int s = 0; s < DN_STAGES; s++) { mbar_init(&bars[s], 1); done[s] = 0; }
@@ -160,19 +163,19 @@ __global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_co
   }
   // zero the pad after each X stage once (bulk copies never touch it)
   for (int s = 0; s < DN_STAGES; s++)
-    for (int idx = DN_TN * K + tid; idx < x_stage_elems; idx += NTHR) s_x[(size_t)s * x_stage_elems + idx] = 0.0;
+    for (int idx = ST_ROWS * K + tid; idx < x_stage_elems; idx += NTHR) s_x[(size_t)s * x_stage_elems + idx] = 0.0;
   __syncthreads();
 
   auto issue_tile = [&](int t) {  // called by thread 0 only, full tiles only
     int s = t % DN_STAGES;
-    const double* src = A.X + (row_begin + (int64_t)t * DN_TN) * K;
-    uint32_t bytes = (uint32_t)(DN_TN * K * sizeof(double));
+    const double* src = A.X + (row_begin + (int64_t)t * ST_ROWS) * K;
+    uint32_t bytes = (uint32_t)(ST_ROWS * K * sizeof(double));
     mbar_expect_tx(&bars[s], bytes);
     tma_bulk_g2s(s_x + (size_t)s * x_stage_elems, src, bytes, &bars[s]);
   };
-  auto tile_rows = [&](int t) -> int { return (int)min((int64_t)DN_TN, row_end - (row_begin + (int64_t)t * DN_TN)); };
-  // bulk copies need 16-byte sizes; a partial (last) tile is copied cooperatively instead
-  auto tile_is_bulk = [&](int t) -> bool { return tile_rows(t) == DN_TN && ((DN_TN * K) % 2 == 0); };
+  auto tile_rows = [&](int t) -> int { return (int)min((int64_t)ST_ROWS, row_end - (row_begin + (int64_t)t * ST_ROWS)); };
+  // bulk copies need 16-byte sizes; a partial (last) stage is copied cooperatively instead
+  auto tile_is_bulk = [&](int t) -> bool { return tile_rows(t) == ST_ROWS && ((ST_ROWS * K) % 2 == 0); };
 
   if (tid == 0) {
     for (int t = 0; t < DN_STAGES && t < n_tiles; t++)
@@ -232,31 +235,71 @@ __global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_co
   const double lnk_lo = op.p[A.dj].lo, lnk_hi = op.p[A.dj].hi;
   const int lnk = op.p[A.dj].link;
 
+  // observed values of one 32-row sub-tile: this thread's 4 rows (mt*8 + gid). They are loaded one
+  // sub-tile ahead, so their L1/L2 latency hides behind the previous sub-tile's arithmetic.
+  // The value travels as a double (discrete values are exact below 2^53; the generic path converts
+  // back), the dtype switch is resolved once per sub-tile, not per row.
+#define y_dtype (op.value_col.dtype)
+#define y_ptr (op.value_col.ptr)
+#define lgam_ptr (op.lgam)
+  auto load_y = [&](int64_t rr0, int vrows, double (&yv_)[4], double (&ylg_)[4]) {
+    int64_t ri[4];
+#pragma unroll
+    for (int mt = 0; mt < 4; mt++) { ri[mt] = rr0 + min(mt * 8 + gid, max(vrows - 1, 0)); yv_[mt] = 0.0; ylg_[mt] = qnan; }
+    if (vrows <= 0) return;
+    if (y_dtype == FC_COL_U32) {
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) yv_[mt] = (double)__ldg((const uint32_t*)y_ptr + ri[mt]);
+    } else if (y_dtype == FC_COL_U8) {
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) yv_[mt] = (double)__ldg((const uint8_t*)y_ptr + ri[mt]);
+    } else if (y_dtype == FC_COL_F64) {
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) { double v = __ldg((const double*)y_ptr + ri[mt]); yv_[mt] = op.cont ? v : (double)(long long)v; }
+    } else {
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) yv_[mt] = (double)__ldg((const long long*)y_ptr + ri[mt]);
+    }
+    if (lgam_ptr) {
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) ylg_[mt] = __ldg(lgam_ptr + ri[mt]);
+    }
+  };
+#undef y_dtype
+#undef y_ptr
+#undef lgam_ptr
+  double nyv[4], nylg[4];
+  if (SUB > 1) load_y(row_begin, (int)min((int64_t)DN_TN, row_end - row_begin), nyv, nylg);
+
   for (int t = 0; t < n_tiles; t++) {
     const int s = t % DN_STAGES;
-    double* xs = s_x + (size_t)s * x_stage_elems;
-    const int64_t r0 = row_begin + (int64_t)t * DN_TN;
-    const int valid = tile_rows(t);
-    // observed values for this thread's 4 rows (issued before the wait to overlap)
-    double yx[4], ylg[4];
-    long long yi[4];
-#pragma unroll
-    for (int mt = 0; mt < 4; mt++) {
-      int r = mt * 8 + gid;
-      yx[mt] = 0.0; yi[mt] = 0; ylg[mt] = qnan;
-      if (r < valid) {
-        load_value(op.value_col, r0 + r, op.cont != 0, yx[mt], yi[mt]);
-        if (op.lgam) ylg[mt] = __ldg(op.lgam + r0 + r);
-      }
-    }
+    double* xs0 = s_x + (size_t)s * x_stage_elems;
+    const int64_t st_r0 = row_begin + (int64_t)t * ST_ROWS;
+    const int st_valid = tile_rows(t);
+    if (SUB == 1) load_y(st_r0, st_valid, nyv, nylg);  // issued before the wait to overlap with it
     if (tile_is_bulk(t)) {
       mbar_wait(&bars[s], (uint32_t)((t / DN_STAGES) & 1));
     } else {
       // cooperative copy + zero fill of the missing rows
-      __syncthreads();  // every warp has left tile t-1 (and so t-2, the stage's previous user)
-      const double* src = A.X + r0 * K;
-      for (int idx = tid; idx < DN_TN * K; idx += NTHR) xs[idx] = (idx < valid * K) ? __ldg(src + idx) : 0.0;
+      __syncthreads();  // every warp has left stage t-1 (and so t-2, the buffer's previous user)
+      const double* src = A.X + st_r0 * K;
+      for (int idx = tid; idx < ST_ROWS * K; idx += NTHR) xs0[idx] = (idx < st_valid * K) ? __ldg(src + idx) : 0.0;
       __syncthreads();
+    }
+   for (int sb = 0; sb < SUB; sb++) {
+    const int valid = min(DN_TN, st_valid - sb * DN_TN);
+    if (valid <= 0) break;
+    double* xs = xs0 + (size_t)sb * DN_TN * K;
+    const int64_t r0 = st_r0 + (int64_t)sb * DN_TN;
+    double yv[4], ylg[4];  // rows beyond `valid` hold a copy of the last valid row; they are masked below
+#pragma unroll
+    for (int mt = 0; mt < 4; mt++) { yv[mt] = nyv[mt]; ylg[mt] = nylg[mt]; }
+    bool yb[4];  // Bernoulli outcome as a predicate (keeps the per-pair test off the FP64 pipe)
+#pragma unroll
+    for (int mt = 0; mt < 4; mt++) yb[mt] = yv[mt] != 0.0;
+    if (SUB > 1) {
+      const int64_t nr0 = r0 + DN_TN;
+      load_y(nr0, (int)max((int64_t)0, min((int64_t)DN_TN, row_end - nr0)), nyv, nylg);
     }
 
     // ---- contraction 1: eta[32][16 per warp] = X_tile[32][K] * beta[K][16] ----
@@ -295,29 +338,30 @@ __global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_co
             double p = fast_rcp(1.0 + fast_exp(-sarg));
             bool inside = (p > lnk_lo && p < lnk_hi);
             double pc = fmin(fmax(p, lnk_lo), lnk_hi);
-            lp = fast_log(yi[mt] != 0 ? pc : 1.0 - pc);
-            if (GRAD) w = inside ? ((yi[mt] != 0) ? (1.0 - p) : -p) : 0.0;
+            lp = fast_log(yb[mt] ? pc : 1.0 - pc);
+            if (GRAD) w = inside ? (yb[mt] ? (1.0 - p) : -p) : 0.0;
             if (sarg != sarg) { lp = d_neg_inf(); w = 0.0; }  // NaN eta => Bernoulli(NaN) => -inf
           } else if (MODE == GLM_POISSON_ID) {
-            // distribution.rs:1237-1258 with lambda = eta
-            double lam = sarg;
-            if (!(lam >= 1e-300 && lam <= 1e300) || yi[mt] < 0) {
-              // out of the fast range: exact reference guards via the library functions
-              if (lam <= 0.0 || !d_fin(lam) || yi[mt] < 0) lp = d_neg_inf();
-              else {
-                double kf = (double)yi[mt];
-                lp = (lam > 700.0 && yi[mt] == 0) ? -lam : kf * log(lam) - lam - ylg[mt];
+            // distribution.rs:1237-1258 with lambda = eta. Branch-light: the fast path is evaluated
+            // unconditionally on a clamped lambda, the reference's guards are selects, and only an
+            // out-of-range lambda takes the (rare) library-function branch.
+            const double lam = sarg;
+            const double kf = yv[mt];
+            const bool ok = (lam >= 1e-300 && lam <= 1e300) && kf >= 0.0;
+            const double lamc = ok ? lam : 1.0;
+            lp = kf * fast_log(lamc) - lam - ylg[mt];
+            if (lam > 700.0 && kf == 0.0) lp = -lam;
+            if (GRAD) w = d_fin(lp) ? kf * fast_rcp(lamc) - 1.0 : 0.0;
+            if (!ok) {
+              lp = d_neg_inf(); w = 0.0;
+              if (lam > 0.0 && d_fin(lam) && kf >= 0.0) {  // tiny / huge lambda: exact guards via the library functions
+                lp = (lam > 700.0 && kf == 0.0) ? -lam : kf * log(lam) - lam - ylg[mt];
                 if (GRAD && d_fin(lp)) w = kf / lam - 1.0;
               }
-            } else {
-              double kf = (double)yi[mt];
-              if (lam > 700.0 && yi[mt] == 0) lp = -lam;
-              else lp = kf * fast_log(lam) - lam - ylg[mt];
-              if (GRAD && d_fin(lp)) w = kf * fast_rcp(lam) - 1.0;
             }
           } else {
             double op_other[3];
-            glm_generic_elem<GRAD>(op, A.dj, sarg, po[0][nt][j], po[1][nt][j], po[2][nt][j], pdl[0][nt][j], pdl[1][nt][j], pdl[2][nt][j], yx[mt], yi[mt], ylg[mt], lp, w, op_other);
+            glm_generic_elem<GRAD>(op, A.dj, sarg, po[0][nt][j], po[1][nt][j], po[2][nt][j], pdl[0][nt][j], pdl[1][nt][j], pdl[2][nt][j], yv[mt], (long long)yv[mt], ylg[mt], lp, w, op_other);
             if (GRAD && rv) {
 #pragma unroll
               for (int pj = 0; pj < 3; pj++) a_p[pj][nt][j] += op_other[pj];
@@ -351,6 +395,8 @@ __global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_co
       }
       __syncwarp();
     }
+
+   }  // sub-tiles of this stage
 
     // ---- release the stage and refill it ----
     // Warps are NOT barriered against each other: the last warp to leave the stage refills it, so a
@@ -416,9 +462,12 @@ __global__ void __launch_bounds__(DN_THREADS(NT), 1) k_dense_glm(const __grid_co
   }
 }
 
+// 32-row sub-tiles per pipeline stage: ~16 KB stages for narrow matrices, 1 from K = 64 up
+static int dense_sub(int K) { return K <= 8 ? 8 : (K <= 16 ? 4 : (K <= 32 ? 2 : 1)); }
+
 static size_t dense_smem_bytes(int K, int NT) {
   int KP4 = (K + 3) & ~3;
-  size_t x_stage = ((size_t)DN_TN * K + 8 + 15) & ~(size_t)15;
+  size_t x_stage = ((size_t)DN_TN * dense_sub(K) * K + 8 + 15) & ~(size_t)15;
   return 128 + sizeof(double) * ((size_t)KP4 * DN_LDB + DN_NW(NT) * DN_TN * DN_LDW(NT) + DN_STAGES * x_stage);
 }
 
@@ -430,7 +479,8 @@ int64_t dense_plate_splits(const fc_program* P, const PlateInfo& pl, int64_t C) 
     cudaDeviceGetAttribute(&g_dense_sms, cudaDevAttrMultiProcessorCount, P->device);
     if (g_dense_sms <= 0) g_dense_sms = 148;
   }
-  int64_t n_tiles = cdiv(pl.dop.plate_len, DN_TN);
+  const int K = pl.dop.p[pl.dense_param].t[pl.dense_term].col.width;
+  int64_t n_tiles = cdiv(pl.dop.plate_len, (int64_t)DN_TN * dense_sub(K));  // pipeline stages
   int64_t ncb = cdiv(C, DN_BC);
   // grid = ncb x S CTAs, one CTA per SM at a time: make it a whole number of waves when the
   // plate is long enough (148 = 4*37), with at least 8 tiles per CTA.
@@ -451,7 +501,8 @@ static int32_t launch_mt(const DenseArgs& A, dim3 grid, size_t smem, cudaStream_
     FC_CUDA(cudaFuncSetAttribute(k_dense_glm<MODE, GRAD, M, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     k_dense_glm<MODE, GRAD, M, NT><<<grid, DN_THREADS(NT), smem, st>>>(A);                                            \
   }
-  if (!GRAD) DN_LAUNCH(1)
+  // value-only kernels ignore MT except for the sub-tiling it implies (8 / 4 / 2 / 1 sub-tiles per stage)
+  if (!GRAD) { if (A.K <= 8) DN_LAUNCH(1) else if (A.K <= 16) DN_LAUNCH(2) else if (A.K <= 32) DN_LAUNCH(4) else DN_LAUNCH(13) }
   else if (MT <= 1) DN_LAUNCH(1)
   else if (MT <= 2) DN_LAUNCH(2)
   else if (MT <= 4) DN_LAUNCH(4)
@@ -473,10 +524,12 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
   A.C = C; A.N = op.plate_len; A.K = K; A.dj = pl.dense_param; A.dt = pl.dense_term;
   A.n_red = pl.acc.n_acc - 3;
   A.n_acc = grad ? 3 + A.n_red + K : 3;
-  int64_t n_tiles = cdiv(A.N, DN_TN);
+  A.sub = dense_sub(K);
+  const int64_t st_rows = (int64_t)DN_TN * A.sub;
+  int64_t n_tiles = cdiv(A.N, st_rows);
   int64_t S = std::max<int64_t>(1, std::min(max_splits, n_tiles));
   int64_t tiles_per_split = cdiv(n_tiles, S);
-  A.rows_per_split = tiles_per_split * DN_TN;
+  A.rows_per_split = tiles_per_split * st_rows;
   S = cdiv(A.N, A.rows_per_split);
   *n_splits = S;
   dim3 grid((unsigned)cdiv(C, DN_BC), (unsigned)S);
