@@ -85,6 +85,7 @@ class Program:
     """A model lowered to the flat op list, resident on the current CUDA device."""
 
     def __init__(self, builder):
+        builder = getattr(builder, "builder", builder)  # a dsl.CompiledModel carries its op list
         self._builder = builder
         self._low = builder.lower()  # keeps ctypes arrays and numpy columns alive during create
         ops, n, cols, ncol = self._low

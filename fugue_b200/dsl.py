@@ -1,0 +1,938 @@
+"""Text front-end: the `prob!`-subset model language of the reference's playground, lowered to the
+flat op list of include/fugue_cuda.h instead of being interpreted into closures.
+
+Grammar, tokens, arities, error texts and the total-evaluation policy follow
+/root/reference/crates/fugue-wasm/src/dsl.rs (grammar :10-20, lexer :150-257, parser :338-447 and
+:497-655, static validation :657-692, evaluation of constant expressions :714-803, distribution
+table :807-818, soft errors :926-944 and :1002-1007, data binding :1055-1107):
+
+    let p <- sample(addr!("p"), Beta(2.0, 2.0));
+    for i in 0..data.len() {
+        observe(addr!("flip", i), Bernoulli(p), data[i]);
+    }
+    pure(p)
+
+What differs is the back end. The reference folds the AST into `sample`/`observe`/`factor`/`bind`
+closures that are re-run for every density evaluation; here the program is run ONCE, symbolically:
+
+  * a `for` body whose statements address `addr!(name, i)` with the loop variable and read data as
+    `arr[i]` becomes ONE plate op (PLATE_OBSERVE / PLATE_SAMPLE) over a device-resident column,
+    with byte-identical addresses `name#i` (src/core/address.rs:208-223);
+  * parameters must be of the form link(term + term + term) with terms const | latent |
+    latent * arr[i] (see _ir.py); anything else -- a structure-varying or non-affine model --
+    is rejected with the typed error FC_ERR_UNSUPPORTED_OP (1000): there is no CPU fallback;
+  * loops that are not plates (other index expressions, lower bound != 0) are unrolled into
+    scalar ops when every parameter is still expressible.
+
+Static errors (syntax, unknown variables / distributions / functions, wrong arities) raise
+DslError with the reference's messages ("line N: expected ..., found ..."). Soft errors
+(invalid constant parameters, index out of bounds) degrade to `factor(-inf)` plus a warning, as
+the reference does (dsl.rs:926-944, 1002-1007).
+"""
+import json
+import math
+import numpy as np
+from . import _ir, model as M
+from ._ir import FugueError
+
+
+class DslError(ValueError):
+    """A static (compile-time) error of the model text; the message follows dsl.rs."""
+
+
+# ---------------------------------------------------------------------------------------------
+# Lexer (dsl.rs:150-257)
+# ---------------------------------------------------------------------------------------------
+SYMS = ["<-", "::", "..", "(", ")", "{", "}", "[", "]", ",", ";", "+", "-", "*", "/", "=", ".", "!"]
+
+
+class _Lexer:
+    def __init__(self, src):
+        self.toks, self.pos = [], 0  # (kind, value, byte offset); kind in ident | num | str | sym | eof
+        self.line_starts = [0] + [i + 1 for i, ch in enumerate(src) if ch == "\n"]
+        i, n = 0, len(src)
+        while i < n:
+            c = src[i]
+            if c.isspace():
+                i += 1
+                continue
+            if c == "/" and src[i + 1:i + 2] == "/":
+                while i < n and src[i] != "\n":
+                    i += 1
+                continue
+            if c == '"':
+                j = src.find('"', i + 1)
+                if j < 0:
+                    raise DslError(f"unterminated string at byte {i}")
+                self.toks.append(("str", src[i + 1:j], i))
+                i = j + 1
+                continue
+            if c.isascii() and c.isdigit():
+                start, dotted = i, False
+                while i < n:
+                    d = src[i]
+                    if d.isascii() and d.isdigit():
+                        i += 1
+                    elif d == "." and not dotted and src[i + 1:i + 2].isdigit():
+                        dotted = True  # `0..n` must lex as Num(0) '..' ident
+                        i += 1
+                    elif d in "eE" and (src[i + 1:i + 2].isdigit() or src[i + 1:i + 2] in ("-", "+")) and src[i + 1:i + 2] != "":
+                        dotted = True
+                        i += 2
+                        while i < n and src[i].isdigit():
+                            i += 1
+                        break
+                    else:
+                        break
+                text = src[start:i]
+                try:
+                    v = float(text)
+                except ValueError:
+                    raise DslError(f"bad number `{text}` at byte {start}")
+                self.toks.append(("num", (v, dotted), start))
+                continue
+            if (c.isascii() and c.isalpha()) or c == "_":
+                start = i
+                while i < n and ((src[i].isascii() and src[i].isalnum()) or src[i] == "_"):
+                    i += 1
+                self.toks.append(("ident", src[start:i], start))
+                continue
+            for s in SYMS:
+                if src.startswith(s, i):
+                    self.toks.append(("sym", s, i))
+                    i += len(s)
+                    break
+            else:
+                raise DslError(f"unexpected character `{c}` at byte {i}")
+        self.toks.append(("eof", None, len(src)))
+
+    def line_of(self, byte):
+        import bisect
+        k = bisect.bisect_left(self.line_starts, byte)
+        return k + 1 if k < len(self.line_starts) and self.line_starts[k] == byte else k
+
+    def peek(self):
+        return self.toks[self.pos][:2]
+
+    def peek2(self):
+        return self.toks[min(self.pos + 1, len(self.toks) - 1)][:2]
+
+    def next(self):
+        t = self.toks[self.pos][:2]
+        if self.pos < len(self.toks) - 1:
+            self.pos += 1
+        return t
+
+    def err(self, what):
+        kind, val, byte = self.toks[self.pos]
+        found = {"ident": lambda: f"`{val}`", "num": lambda: f"`{_fmt_num(val[0])}`", "str": lambda: f'"{val}"',
+                 "sym": lambda: f"`{val}`", "eof": lambda: "end of input"}[kind]()
+        return DslError(f"line {self.line_of(byte)}: expected {what}, found {found}")
+
+    def expect_sym(self, s):
+        if self.peek() == ("sym", s):
+            self.next()
+        else:
+            raise self.err(f"`{s}`")
+
+    def expect_ident(self):
+        k, v = self.peek()
+        if k != "ident":
+            raise self.err("an identifier")
+        self.next()
+        return v
+
+    def eat_kw(self, kw):
+        if self.peek() == ("ident", kw):
+            self.next()
+            return True
+        return False
+
+
+def _fmt_num(v):
+    return str(int(v)) if float(v).is_integer() and abs(v) < 1e16 else repr(v)
+
+
+# ---------------------------------------------------------------------------------------------
+# Parser (dsl.rs:338-655). AST nodes are tuples:
+#   expr: ("num", v) ("int", i) ("bool", b) ("var", n) ("index", a, i) ("len", a) ("neg", a)
+#         ("bin", op, a, b) ("call", f, [args])
+#   stmt: ("sample", name, addr, dist) ("let", name, expr) ("observe", addr, dist, value)
+#         ("factor", expr) ("for", var, lo, hi, [body])
+#   addr: (name, index_expr | None); dist: (name, [args])
+# ---------------------------------------------------------------------------------------------
+MATH_FNS = {"exp": 1, "ln": 1, "log": 1, "sqrt": 1, "abs": 1, "floor": 1, "sin": 1, "cos": 1, "tanh": 1, "pow": 2, "min": 2, "max": 2}
+
+# (min_args, max_args) per distribution; Categorical is variadic (dsl.rs:807-818)
+DIST_ARITY = {**{d: (2, 2) for d in ("Normal", "Uniform", "LogNormal", "Beta", "Gamma", "InverseGamma", "Cauchy", "Laplace", "Weibull",
+                                     "Binomial", "DiscreteUniform")},
+              **{d: (1, 1) for d in ("Exponential", "Poisson", "Bernoulli", "ChiSquared")}, "StudentT": (3, 3), "Categorical": (1, 64)}
+
+
+def _parse_program(src):
+    lx = _Lexer(src)
+    stmts = []
+    while True:
+        if lx.eat_kw("pure"):
+            lx.expect_sym("(")
+            ret = _parse_expr(lx)
+            lx.expect_sym(")")
+            if lx.peek() == ("sym", ";"):
+                lx.next()  # optional trailing semicolon
+            if lx.peek()[0] != "eof":
+                raise lx.err("end of input after `pure(..)`")
+            return stmts, ret
+        if lx.peek()[0] == "eof":
+            raise DslError("model must end with `pure(<expr>)`")
+        stmts.append(_parse_stmt(lx))
+
+
+def _parse_stmt(lx):
+    if lx.eat_kw("let"):
+        name = lx.expect_ident()
+        if lx.peek() == ("sym", "<-"):
+            lx.next()
+            if not lx.eat_kw("sample"):
+                raise lx.err("`sample`")
+            lx.expect_sym("(")
+            addr = _parse_addr(lx)
+            lx.expect_sym(",")
+            dist = _parse_dist(lx)
+            lx.expect_sym(")")
+            lx.expect_sym(";")
+            return ("sample", name, addr, dist)
+        lx.expect_sym("=")
+        e = _parse_expr(lx)
+        lx.expect_sym(";")
+        return ("let", name, e)
+    if lx.eat_kw("observe"):
+        lx.expect_sym("(")
+        addr = _parse_addr(lx)
+        lx.expect_sym(",")
+        dist = _parse_dist(lx)
+        lx.expect_sym(",")
+        value = _parse_expr(lx)
+        lx.expect_sym(")")
+        lx.expect_sym(";")
+        return ("observe", addr, dist, value)
+    if lx.eat_kw("factor"):
+        lx.expect_sym("(")
+        e = _parse_expr(lx)
+        lx.expect_sym(")")
+        lx.expect_sym(";")
+        return ("factor", e)
+    if lx.eat_kw("for"):
+        var = lx.expect_ident()
+        if not lx.eat_kw("in"):
+            raise lx.err("`in`")
+        lo = _parse_expr(lx)
+        lx.expect_sym("..")
+        hi = _parse_expr(lx)
+        lx.expect_sym("{")
+        body = []
+        while lx.peek() != ("sym", "}"):
+            if lx.peek()[0] == "eof":
+                raise lx.err("`}`")
+            body.append(_parse_stmt(lx))
+        lx.next()
+        return ("for", var, lo, hi, body)
+    raise lx.err("a statement (`let`, `observe`, `factor`, `for`, or `pure`)")
+
+
+def _parse_addr(lx):
+    if not lx.eat_kw("addr"):
+        raise lx.err("`addr!(..)`")
+    lx.expect_sym("!")
+    lx.expect_sym("(")
+    k, v = lx.peek()
+    if k != "str":
+        raise lx.err("a string literal address name")
+    lx.next()
+    index = None
+    if lx.peek() == ("sym", ","):
+        lx.next()
+        index = _parse_expr(lx)
+    lx.expect_sym(")")
+    return (v, index)
+
+
+def _parse_dist(lx):
+    name = lx.expect_ident()
+    if lx.peek() == ("sym", "::"):
+        lx.next()
+        m = lx.expect_ident()
+        if m != "new":
+            raise DslError(f"unknown distribution constructor `{name}::{m}`")
+    lx.expect_sym("(")
+    args = []
+    if lx.peek() != ("sym", ")"):
+        while True:
+            args.append(_parse_expr(lx))
+            if lx.peek() == ("sym", ","):
+                lx.next()
+            else:
+                break
+    lx.expect_sym(")")
+    if lx.peek() == ("sym", ".") and lx.peek2() == ("ident", "unwrap"):  # optional Rust-ism
+        lx.next(); lx.next()
+        lx.expect_sym("(")
+        lx.expect_sym(")")
+    if name not in DIST_ARITY:
+        raise DslError(f"unknown distribution `{name}`")
+    lo, hi = DIST_ARITY[name]
+    if not (lo <= len(args) <= hi):
+        raise DslError(f"`{name}` takes {lo if lo == hi else f'{lo}..={hi}'} argument(s), got {len(args)}")
+    return (name, args)
+
+
+def _parse_expr(lx):
+    lhs = _parse_mul(lx)
+    while lx.peek() in (("sym", "+"), ("sym", "-")):
+        op = lx.next()[1]
+        lhs = ("bin", op, lhs, _parse_mul(lx))
+    return lhs
+
+
+def _parse_mul(lx):
+    lhs = _parse_unary(lx)
+    while lx.peek() in (("sym", "*"), ("sym", "/")):
+        op = lx.next()[1]
+        lhs = ("bin", op, lhs, _parse_unary(lx))
+    return lhs
+
+
+def _parse_unary(lx):
+    if lx.peek() == ("sym", "-"):
+        lx.next()
+        return ("neg", _parse_unary(lx))
+    return _parse_postfix(lx)
+
+
+def _parse_postfix(lx):
+    e = _parse_primary(lx)
+    while True:
+        if lx.peek() == ("sym", "["):
+            lx.next()
+            idx = _parse_expr(lx)
+            lx.expect_sym("]")
+            e = ("index", e, idx)
+        elif lx.peek() == ("sym", ".") and lx.peek2() == ("ident", "len"):
+            lx.next(); lx.next()
+            lx.expect_sym("(")
+            lx.expect_sym(")")
+            e = ("len", e)
+        else:
+            return e
+
+
+def _parse_primary(lx):
+    k, v = lx.peek()
+    if k == "num":
+        lx.next()
+        return ("num", v[0]) if v[1] else ("int", int(v[0]))
+    if (k, v) == ("sym", "("):
+        lx.next()
+        e = _parse_expr(lx)
+        lx.expect_sym(")")
+        return e
+    if k == "ident":
+        lx.next()
+        if v in ("true", "false"):
+            return ("bool", v == "true")
+        if lx.peek() == ("sym", "("):
+            if v not in MATH_FNS:
+                raise DslError(f"unknown function `{v}`")
+            lx.next()
+            args = []
+            if lx.peek() != ("sym", ")"):
+                while True:
+                    args.append(_parse_expr(lx))
+                    if lx.peek() == ("sym", ","):
+                        lx.next()
+                    else:
+                        break
+            lx.expect_sym(")")
+            if len(args) != MATH_FNS[v]:
+                raise DslError(f"`{v}` takes {MATH_FNS[v]} argument(s)")
+            return ("call", v, args)
+        return ("var", v)
+    raise lx.err("an expression")
+
+
+# ---- static validation of names (dsl.rs:657-692) ----
+def _check_expr(e, scope):
+    t = e[0]
+    if t == "var":
+        if e[1] not in scope:
+            raise DslError(f"unknown variable `{e[1]}`")
+    elif t in ("index", "bin"):
+        for a in e[-2:]:
+            _check_expr(a, scope)
+    elif t in ("len", "neg"):
+        _check_expr(e[1], scope)
+    elif t == "call":
+        for a in e[2]:
+            _check_expr(a, scope)
+
+
+def _check_stmts(stmts, scope):
+    for s in stmts:
+        if s[0] == "sample":
+            _, name, (an, ai), (dn, dargs) = s
+            if ai is not None:
+                _check_expr(ai, scope)
+            for a in dargs:
+                _check_expr(a, scope)
+            scope.append(name)
+        elif s[0] == "let":
+            _check_expr(s[2], scope)
+            scope.append(s[1])
+        elif s[0] == "observe":
+            _, (an, ai), (dn, dargs), value = s
+            if ai is not None:
+                _check_expr(ai, scope)
+            for a in dargs:
+                _check_expr(a, scope)
+            _check_expr(value, scope)
+        elif s[0] == "factor":
+            _check_expr(s[1], scope)
+        else:
+            _, var, lo, hi, body = s
+            _check_expr(lo, scope)
+            _check_expr(hi, scope)
+            depth = len(scope)
+            scope.append(var)
+            _check_stmts(body, scope)
+            del scope[depth:]
+
+
+# ---------------------------------------------------------------------------------------------
+# Symbolic values of the single lowering run
+#   constants: bool | int | float (the reference's Value::{Bool,Int,F64}), np.ndarray (Value::Arr)
+#   _LoopVar : the index of the enclosing plate-candidate loop
+#   _Elem    : arr[i] for the loop index i -- a whole derived column; arithmetic with constants and
+#              other _Elems is folded element-wise (the same f64 operations the reference performs
+#              per iteration)
+#   _ir.Expr : link(term + term + term) over latents (the fc_param form)
+# ---------------------------------------------------------------------------------------------
+class _LoopVar:
+    pass
+
+
+class _Elem:
+    def __init__(self, arr):
+        self.arr = np.asarray(arr, dtype=np.float64)
+
+
+class _Opaque:
+    """A discrete plate element: addressable, but not usable in parameter expressions."""
+
+
+class _NotPlate(Exception):
+    """The loop body does not have the plate shape; the caller unrolls instead."""
+
+
+def _unsupported(msg):
+    return FugueError(_ir.FC_ERR_UNSUPPORTED_OP, msg + " (not expressible as link(term+term+term) over latents; no CPU fallback)")
+
+
+def _is_const(v):
+    return isinstance(v, (bool, int, float))
+
+
+def _as_f64(v):  # Value::as_f64 (dsl.rs:55-69)
+    if isinstance(v, bool):
+        return 1.0 if v else 0.0
+    if isinstance(v, (int, float)):
+        return float(v)
+    return float("nan")
+
+
+def _as_index(v):  # Value::as_index (dsl.rs:71-77)
+    if isinstance(v, bool):
+        return None
+    if isinstance(v, int):
+        return v
+    if isinstance(v, float) and math.isfinite(v) and v == math.floor(v):
+        return int(v)
+    return None
+
+
+def _math(name, a):
+    try:
+        if name == "exp": return math.exp(a[0])
+        if name in ("ln", "log"): return math.log(a[0]) if a[0] > 0 else (float("-inf") if a[0] == 0 else float("nan"))
+        if name == "sqrt": return math.sqrt(a[0]) if a[0] >= 0 else float("nan")
+        if name == "abs": return abs(a[0])
+        if name == "floor": return float(math.floor(a[0])) if math.isfinite(a[0]) else a[0]
+        if name == "sin": return math.sin(a[0])
+        if name == "cos": return math.cos(a[0])
+        if name == "tanh": return math.tanh(a[0])
+        if name == "pow": return math.pow(a[0], a[1])
+        if name == "min": return a[1] if a[0] != a[0] else (a[0] if a[1] != a[1] else min(a[0], a[1]))
+        if name == "max": return a[1] if a[0] != a[0] else (a[0] if a[1] != a[1] else max(a[0], a[1]))
+    except OverflowError:
+        return float("inf")
+    except ValueError:
+        return float("nan")
+    return float("nan")
+
+
+def _bin_const(op, x, y):  # dsl.rs:755-772
+    if isinstance(x, int) and isinstance(y, int) and not isinstance(x, bool) and not isinstance(y, bool) and op in "+-*":
+        return x + y if op == "+" else (x - y if op == "-" else x * y)
+    a, b = _as_f64(x), _as_f64(y)
+    if op == "+": return a + b
+    if op == "-": return a - b
+    if op == "*": return a * b
+    if b == 0.0:
+        return float("nan") if (a == 0.0 or a != a) else math.copysign(float("inf"), a) * (math.copysign(1.0, b))
+    return a / b
+
+
+def _bare_latent(e):
+    return isinstance(e, _ir.Expr) and e.link == _ir.FC_LINK_IDENTITY and len(e.terms) == 1 and e.terms[0][0] == _ir.FC_TERM_LATENT
+
+
+class _Lowering:
+    def __init__(self, builder, warnings):
+        self.m, self.warnings = builder, warnings
+        self.plate_n = None     # length of the plate-candidate loop being lowered, else None
+        self.col_cache = {}
+
+    def warn(self, msg):
+        if len(self.warnings) < 64:
+            self.warnings.append(msg)
+
+    def column(self, arr):
+        key = (arr.dtype.str, arr.tobytes())
+        if key not in self.col_cache:
+            self.col_cache[key] = self.m.data(arr)
+        return self.col_cache[key]
+
+    # ---- expressions ----
+    def ev(self, e, env):
+        t = e[0]
+        if t in ("num", "int", "bool"):
+            return e[1]
+        if t == "var":
+            return env[e[1]]
+        if t == "len":
+            a = self.ev(e[1], env)
+            if isinstance(a, np.ndarray):
+                return int(a.shape[0])
+            self.warn("`.len()` on a non-array value")
+            return 0
+        if t == "index":
+            a, i = self.ev(e[1], env), self.ev(e[2], env)
+            if isinstance(a, np.ndarray) and isinstance(i, _LoopVar):
+                if a.shape[0] < self.plate_n:
+                    raise _NotPlate()  # the tail would be out of bounds: unroll to get the per-element warnings
+                return _Elem(a[:self.plate_n])
+            if isinstance(i, (_LoopVar, _Elem, _ir.Expr, _Opaque)):
+                raise _NotPlate() if self.plate_n is not None else _unsupported("array index depends on a latent")
+            k = _as_index(i)
+            if isinstance(a, np.ndarray) and k is not None:
+                if 0 <= k < a.shape[0]:
+                    return float(a[k])
+                self.warn(f"index {k} out of bounds (len {a.shape[0]})")
+                return float("nan")
+            self.warn("indexing a non-array value")
+            return float("nan")
+        if t == "neg":
+            a = self.ev(e[1], env)
+            if isinstance(a, int) and not isinstance(a, bool):
+                return -a
+            if _is_const(a):
+                return -_as_f64(a)
+            if isinstance(a, _Elem):
+                return _Elem(-a.arr)
+            raise _unsupported("negated latent expression")
+        if t == "bin":
+            sig = self.sigmoid_pattern(e, env)
+            if sig is not None:
+                return sig
+            return self.bin(e[1], self.ev(e[2], env), self.ev(e[3], env))
+        if t == "call":
+            return self.call(e[1], [self.ev(a, env) for a in e[2]])
+        raise AssertionError(t)
+
+    def sigmoid_pattern(self, e, env):
+        """1.0 / (1.0 + exp(-eta)) (examples/classification.rs:124) -> the SIGMOID link."""
+        def is_one(x):
+            return x[0] in ("num", "int") and float(x[1]) == 1.0
+        if e[1] != "/" or not is_one(e[2]) or e[3][0] != "bin" or e[3][1] != "+":
+            return None
+        l, r = e[3][2], e[3][3]
+        ex = r if is_one(l) else (l if is_one(r) else None)
+        if ex is None or ex[0] != "call" or ex[1] != "exp" or ex[2][0][0] != "neg":
+            return None
+        eta = self.ev(ex[2][0][1], env)
+        if not isinstance(eta, _ir.Expr) or eta.link != _ir.FC_LINK_IDENTITY:
+            return None
+        return _ir.sigmoid_clamped(eta, 0.0, 1.0)
+
+    def bin(self, op, x, y):
+        if _is_const(x) and _is_const(y):
+            return _bin_const(op, x, y)
+        for v in (x, y):
+            if isinstance(v, (np.ndarray, _LoopVar, _Opaque)):
+                if isinstance(v, _LoopVar):
+                    raise _NotPlate()
+                raise _unsupported("arithmetic on an array / discrete plate element")
+        if isinstance(x, _Elem) or isinstance(y, _Elem):
+            if isinstance(x, _ir.Expr) or isinstance(y, _ir.Expr):
+                lat, el = (x, y) if isinstance(x, _ir.Expr) else (y, x)
+                if op == "*" and _bare_latent(lat):
+                    return _ir.Expr([(_ir.FC_TERM_LATENT_X, lat.terms[0][1], 0, self.column(el.arr).cid, 0.0)])
+                raise _unsupported(f"`{op}` between a latent expression and a data element")
+            xa = x.arr if isinstance(x, _Elem) else _as_f64(x)
+            ya = y.arr if isinstance(y, _Elem) else _as_f64(y)
+            with np.errstate(all="ignore"):
+                return _Elem({"+": np.add, "-": np.subtract, "*": np.multiply, "/": np.divide}[op](xa, ya))
+        # at least one latent expression, the other a constant or a latent expression
+        if op == "+" or op == "-":
+            if isinstance(x, _ir.Expr) and isinstance(y, _ir.Expr):
+                if op == "-":
+                    raise _unsupported("difference of latent expressions")
+                if x.link != _ir.FC_LINK_IDENTITY or y.link != _ir.FC_LINK_IDENTITY:
+                    raise _unsupported("sum of linked expressions")
+                return _ir.Expr(x.terms + y.terms)
+            if isinstance(x, _ir.Expr):
+                c = _as_f64(y)
+                if x.link != _ir.FC_LINK_IDENTITY:
+                    raise _unsupported("arithmetic after a link function")
+                return _ir.Expr(x.terms + [(_ir.FC_TERM_CONST, 0, 0, 0, c if op == "+" else -c)])
+            if op == "-":
+                raise _unsupported("constant minus latent expression")
+            if y.link != _ir.FC_LINK_IDENTITY:
+                raise _unsupported("arithmetic after a link function")
+            return _ir.Expr([(_ir.FC_TERM_CONST, 0, 0, 0, _as_f64(x))] + y.terms)
+        if op == "*":
+            lat, c = (x, y) if isinstance(x, _ir.Expr) else (y, x)
+            if _is_const(c) and _bare_latent(lat):
+                if _as_f64(c) == 1.0:
+                    return lat
+                if self.plate_n is not None:  # inside a plate a constant factor is a constant column
+                    return _ir.Expr([(_ir.FC_TERM_LATENT_X, lat.terms[0][1], 0, self.column(np.full(self.plate_n, _as_f64(c))).cid, 0.0)])
+            raise _unsupported("product involving a latent expression")
+        raise _unsupported("division involving a latent expression")
+
+    def call(self, name, args):
+        if all(_is_const(a) for a in args):
+            return _math(name, [_as_f64(a) for a in args])
+        if any(isinstance(a, _LoopVar) for a in args):
+            raise _NotPlate()
+        if all(_is_const(a) or isinstance(a, _Elem) for a in args):
+            n = next(a.arr.shape[0] for a in args if isinstance(a, _Elem))
+            cols = [a.arr if isinstance(a, _Elem) else np.full(n, _as_f64(a)) for a in args]
+            return _Elem(np.array([_math(name, [float(c[k]) for c in cols]) for k in range(n)]))
+        if name == "exp" and isinstance(args[0], _ir.Expr) and args[0].link == _ir.FC_LINK_IDENTITY:
+            return _ir.exp(args[0])
+        if name in ("min", "max"):
+            ex, c = (args[0], args[1]) if isinstance(args[0], _ir.Expr) else (args[1], args[0])
+            if isinstance(ex, _ir.Expr) and _is_const(c):
+                c = _as_f64(c)
+                if ex.link == _ir.FC_LINK_IDENTITY:
+                    lo, hi, link = float("-inf"), float("inf"), _ir.FC_LINK_CLAMP
+                elif ex.link in (_ir.FC_LINK_CLAMP, _ir.FC_LINK_SIGMOID_CLAMPED):
+                    lo, hi, link = ex.lo, ex.hi, ex.link
+                else:
+                    raise _unsupported("min/max after exp()")
+                lo, hi = (max(lo, c), hi) if name == "max" else (lo, min(hi, c))
+                if lo > hi:
+                    raise _unsupported("clamp with lower bound above upper bound")
+                return _ir.Expr(ex.terms, link, lo, hi)
+        raise _unsupported(f"`{name}` of a latent expression")
+
+    # ---- distributions (dsl.rs:828-871) ----
+    def dist(self, spec, env):
+        name, arg_asts = spec
+        args = [self.ev(a, env) for a in arg_asts]
+        for a in args:
+            if isinstance(a, _LoopVar):
+                raise _NotPlate()
+            if not (_is_const(a) or isinstance(a, _ir.Expr)):
+                raise _unsupported(f"`{name}` parameter is a data element or an array")
+        p = [a if isinstance(a, _ir.Expr) else _as_f64(a) for a in args]
+        if name == "Binomial":
+            if isinstance(p[0], _ir.Expr):
+                raise _unsupported("Binomial n depends on a latent")
+            if p[0] < 0.0 or p[0] != math.floor(p[0]):
+                raise FugueError(106, f"Binomial n must be a non-negative integer, got {_fmt_num(p[0])}")
+        if name == "DiscreteUniform":
+            if any(isinstance(v, _ir.Expr) for v in p):
+                raise _unsupported("DiscreteUniform bounds depend on a latent")
+            p = [float(int(v)) if math.isfinite(v) else v for v in p]  # `a[0] as i64`
+        if name == "Categorical":
+            # the device Categorical is the two-way [p, 1-p] form (deviation 6)
+            if len(p) != 2:
+                raise _unsupported(f"Categorical with {len(p)} categories (the device form is two-way)")
+            if isinstance(p[0], _ir.Expr) or isinstance(p[1], _ir.Expr):
+                a0, a1 = arg_asts
+                comp = a1[0] == "bin" and a1[1] == "-" and a1[2][0] in ("num", "int") and float(a1[2][1]) == 1.0 and a1[3] == a0
+                if not comp:
+                    raise _unsupported("Categorical(p, q) with latent probabilities needs q written as `1.0 - p`")
+                return M.Categorical(p[0])
+            if not (all(math.isfinite(v) and v >= 0.0 for v in p) and abs(p[0] + p[1] - 1.0) <= 1e-6):  # distribution.rs:679-713
+                raise FugueError(102, f"Categorical probabilities must be non-negative and sum to 1, got {p}")
+            return M.Categorical(p[0])
+        return getattr(M, name)(*p)
+
+    @staticmethod
+    def coerce_value(vt, v):
+        """observe value coercions (dsl.rs:985-1000) for a constant or an array of constants."""
+        arr = np.asarray(v, dtype=np.float64)
+        if vt == "f64":
+            return arr
+        if vt == "bool":
+            return (arr != 0.0).astype(np.uint8)
+        idx = np.where(np.isfinite(arr) & (arr == np.floor(arr)), arr, 0.0)  # as_index().unwrap_or(0)
+        if vt in ("u64", "usize"):
+            idx = np.maximum(idx, 0.0)
+        return idx.astype(np.int64)
+
+    def address(self, spec, env):
+        """(name, kind): kind None = scalar address (already escaped), "plate" = addr!(name, loop index)."""
+        name, ix = spec
+        if ix is None:
+            return M.addr(name), None
+        v = self.ev(ix, env)
+        if isinstance(v, _LoopVar):
+            return M.addr(name), "plate"
+        if not _is_const(v):
+            raise _NotPlate() if self.plate_n is not None else _unsupported("address index depends on a latent")
+        k = _as_index(v)
+        return M.addr(name, k if k is not None else _rust_f64(_as_f64(v))), None
+
+    # ---- statements ----
+    def stmts(self, stmts, env):
+        for s in stmts:
+            kind = s[0]
+            if kind == "let":
+                env[s[1]] = self.ev(s[2], env)
+            elif kind == "factor":
+                lw = self.ev(s[1], env)
+                if not _is_const(lw):
+                    if isinstance(lw, _LoopVar):
+                        raise _NotPlate()
+                    raise _unsupported("factor() of a latent expression")
+                lw = _as_f64(lw)
+                reps = self.plate_n if self.plate_n is not None else 1
+                if reps > 4096:
+                    raise _unsupported("factor() inside a loop of more than 4096 iterations")
+                for _ in range(reps):
+                    self.m.factor(float("-inf") if lw != lw else lw)
+            elif kind == "sample":
+                _, var, aspec, dspec = s
+                a, ak = self.address(aspec, env)
+                if self.plate_n is not None and ak != "plate":
+                    raise _NotPlate()
+                try:
+                    d = self.dist(dspec, env)
+                except FugueError as e:
+                    if e.code >= 1000:
+                        raise
+                    # impossible parameter region: placeholder draw + factor(-inf) (dsl.rs:926-944)
+                    self.warn(f"sample `{var}`: {e}")
+                    if ak == "plate":
+                        site = self.m.plate_sample(a, self.plate_n, M.Normal(0.0, 1.0)).elem()
+                    else:
+                        site = self.m.sample(a, M.Normal(0.0, 1.0))
+                    self.m.factor(float("-inf"))
+                    env[var] = site
+                    continue
+                if ak == "plate":
+                    pl = self.m.plate_sample(a, self.plate_n, d)
+                    env[var] = _Opaque() if pl.discrete else pl.elem()
+                else:
+                    site = self.m.sample(a, d)
+                    env[var] = _Opaque() if site.discrete else site
+            elif kind == "observe":
+                _, aspec, dspec, vast = s
+                a, ak = self.address(aspec, env)
+                if self.plate_n is not None and ak != "plate":
+                    raise _NotPlate()
+                v = self.ev(vast, env)
+                if isinstance(v, _LoopVar):
+                    raise _NotPlate()
+                if not (_is_const(v) or isinstance(v, _Elem)):
+                    raise _unsupported("observed value depends on a latent")
+                try:
+                    d = self.dist(dspec, env)
+                except FugueError as e:
+                    if e.code >= 1000:
+                        raise
+                    self.warn(f"observe at `{a}`: {e}")  # dsl.rs:1002-1007
+                    self.m.factor(float("-inf"))
+                    continue
+                if ak == "plate":
+                    col = v.arr if isinstance(v, _Elem) else np.full(self.plate_n, _as_f64(v))
+                    self.m.plate_observe(a, d, self.column(self.coerce_value(d.value_type, col)))
+                else:
+                    if isinstance(v, _Elem):
+                        raise _NotPlate()
+                    cv = self.coerce_value(d.value_type, _as_f64(v) if not isinstance(v, bool) else float(v))
+                    self.m.observe(a, d, float(cv))
+            else:
+                self.loop(s, env)
+
+    def loop(self, s, env):
+        _, var, lo_e, hi_e, body = s
+        lo, hi = self.ev(lo_e, env), self.ev(hi_e, env)
+        if not (_is_const(lo) and _is_const(hi)):
+            raise _NotPlate() if self.plate_n is not None else _unsupported("loop bound depends on a latent")
+        lo_v, hi_v = _as_index(lo), _as_index(hi)
+        if lo_v is None:
+            self.warn("`for` lower bound is not an integer"); lo_v = 0
+        if hi_v is None:
+            self.warn("`for` upper bound is not an integer"); hi_v = 0
+        if hi_v <= lo_v:
+            return
+        if self.plate_n is not None:
+            raise _NotPlate()  # nested loops: unroll the outer one
+        # 1) as a plate: index 0..n, every address addr!(name, i), data read as arr[i]
+        if lo_v == 0:
+            snap = (len(self.m.ops), len(self.m.cols), self.m.n_cont, self.m.n_disc, dict(self.col_cache), len(self.warnings))
+            env2 = dict(env)
+            env2[var] = _LoopVar()
+            self.plate_n = hi_v
+            try:
+                self.stmts(body, env2)
+                return
+            except _NotPlate:
+                del self.m.ops[snap[0]:]
+                del self.m.cols[snap[1]:]
+                self.m.n_cont, self.m.n_disc, self.col_cache = snap[2], snap[3], snap[4]
+                del self.warnings[snap[5]:]
+            finally:
+                self.plate_n = None
+        # 2) unrolled into scalar ops
+        if hi_v - lo_v > 4096:
+            raise _unsupported(f"loop of {hi_v - lo_v} iterations is not a plate (addresses must be addr!(name, {var}) and data must be read as arr[{var}])")
+        for i in range(lo_v, hi_v):
+            env2 = dict(env)
+            env2[var] = i
+            self.stmts(body, env2)
+
+
+def _rust_f64(x):
+    """Display of an f64 as Rust prints it in make_indexed (address.rs:208-223)."""
+    if x != x:
+        return "NaN"
+    if math.isinf(x):
+        return "inf" if x > 0 else "-inf"
+    return str(int(x)) if x == math.floor(x) and abs(x) < 1e16 else repr(x)
+
+
+# ---------------------------------------------------------------------------------------------
+# Public handle (dsl.rs:1047-1139)
+# ---------------------------------------------------------------------------------------------
+def _bind_data(data):
+    """JSON text (object of number arrays, or a bare array bound to `data`), or the same as Python
+    objects (dict of array-likes / one array-like). Booleans are coerced to 0/1 (dsl.rs:1062-1094)."""
+    if data is None:
+        return {}
+    if isinstance(data, str):
+        trimmed = data.strip()
+        if trimmed == "" or trimmed == "null":
+            return {}
+        try:
+            data = json.loads(trimmed)
+        except json.JSONDecodeError as e:
+            raise DslError(f"data is not valid JSON: {e}")
+
+    def to_arr(v):
+        if isinstance(v, np.ndarray):
+            if v.ndim != 1:
+                raise DslError("data arrays must be JSON arrays")
+            return v.astype(np.float64)
+        if not isinstance(v, (list, tuple)):
+            raise DslError("data arrays must be JSON arrays")
+        for x in v:
+            if not isinstance(x, (bool, int, float)):
+                raise DslError("data arrays must hold numbers or booleans")
+        return np.array([float(x) for x in v], dtype=np.float64)
+
+    if isinstance(data, (list, tuple, np.ndarray)):
+        return {"data": to_arr(data)}
+    if isinstance(data, dict):
+        return {k: to_arr(v) for k, v in data.items()}
+    raise DslError("data must be a JSON array or object of arrays")
+
+
+class CompiledModel:
+    """A parsed, validated and lowered model. `builder` is the op list (a ModelBuilder accepted by
+    every entry point of fugue_b200.api); `warnings` holds the soft errors that were mapped to
+    factor(-inf); `return_value(draws)` evaluates the `pure(..)` expression on returned draws."""
+
+    def __init__(self, stmts, ret, data, builder, warnings):
+        self.stmts, self.ret, self.data, self.builder, self._warnings = stmts, ret, data, builder, warnings
+
+    def build(self):
+        return self.builder
+
+    def take_warnings(self):
+        w, self._warnings[:] = list(self._warnings), []
+        return w
+
+    def data_summary(self):
+        return "".join(f"{k}[{len(v)}] " for k, v in self.data.items())
+
+    def return_value(self, draws):
+        """`pure(expr)` for every draw: `draws` maps a top-level site address to an array of values
+        (any shape; broadcast together). Only top-level `let` bindings are in scope at `pure`."""
+        env = dict(self.data)
+        for s in self.stmts:
+            if s[0] == "sample":
+                name, ix = s[2]
+                if ix is None or ix[0] in ("num", "int"):
+                    a = M.addr(name) if ix is None else M.addr(name, _as_index(ix[1]) if _as_index(ix[1]) is not None else ix[1])
+                    if a in draws:
+                        env[s[1]] = np.asarray(draws[a], dtype=np.float64)
+            elif s[0] == "let":
+                try:
+                    env[s[1]] = _num_eval(s[2], env)
+                except KeyError:
+                    pass
+        return _num_eval(self.ret, env)
+
+
+def _num_eval(e, env):
+    t = e[0]
+    if t in ("num", "int", "bool"):
+        return float(e[1])
+    if t == "var":
+        return env[e[1]]
+    if t == "len":
+        return float(len(_num_eval(e[1], env)))
+    if t == "index":
+        a, i = _num_eval(e[1], env), _num_eval(e[2], env)
+        k = int(i)
+        return float(a[k]) if 0 <= k < len(a) else float("nan")
+    if t == "neg":
+        return -_num_eval(e[1], env)
+    with np.errstate(all="ignore"):
+        if t == "bin":
+            x, y = _num_eval(e[2], env), _num_eval(e[3], env)
+            return {"+": np.add, "-": np.subtract, "*": np.multiply, "/": np.divide}[e[1]](x, y)
+        a = [_num_eval(x, env) for x in e[2]]
+        f = {"exp": np.exp, "ln": np.log, "log": np.log, "sqrt": np.sqrt, "abs": np.abs, "floor": np.floor, "sin": np.sin, "cos": np.cos,
+             "tanh": np.tanh, "pow": np.power, "min": np.fmin, "max": np.fmax}[e[1]]
+        return f(*a)
+
+
+def compile(source, data=None):  # noqa: A001 (the reference's name: CompiledModel::compile)
+    """Parse `source`, bind `data`, validate names statically and lower to the op list."""
+    stmts, ret = _parse_program(source)
+    env = _bind_data(data)
+    scope = list(env.keys())
+    _check_stmts(stmts, scope)
+    _check_expr(ret, scope)
+    builder, warnings = M.ModelBuilder(), []
+    low = _Lowering(builder, warnings)
+    try:
+        low.stmts(stmts, dict(env))
+    except _NotPlate:
+        raise _unsupported("loop index used outside addr!(name, i) / arr[i]")
+    return CompiledModel(stmts, ret, env, builder, warnings)
