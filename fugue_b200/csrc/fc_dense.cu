@@ -123,7 +123,9 @@ __device__ __noinline__ void glm_generic_elem(const DOp& op, int dj, double sarg
 
 // MT = number of 8-row gradient tiles per warp (K padded to 8*MT); GRAD=false skips the
 // second contraction (value only: MH / SMC).
-template <int MODE, bool GRAD, int MT, int NT>
+// VAL=false (with GRAD) is the force-only pass of an interior leapfrog step: the log-density of the
+// element is not evaluated (no log, no clamp), the lp partial is written as 0 and never read.
+template <int MODE, bool GRAD, int MT, int NT, bool VAL = true>
 __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(const __grid_constant__ DenseArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int NW = DN_NW(NT), NTHR = DN_THREADS(NT), LDW = DN_LDW(NT), WC = 8 * NT;  // WC = chains per warp
@@ -337,10 +339,12 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             // Same formula, branch-free primitives (host guarantees 1e-300 < lo <= hi < 1).
             double p = fast_rcp(1.0 + fast_exp(-sarg));
             bool inside = (p > lnk_lo && p < lnk_hi);
-            double pc = fmin(fmax(p, lnk_lo), lnk_hi);
-            lp = fast_log(yb[mt] ? pc : 1.0 - pc);
-            if (GRAD) w = inside ? (yb[mt] ? (1.0 - p) : -p) : 0.0;
-            if (sarg != sarg) { lp = d_neg_inf(); w = 0.0; }  // NaN eta => Bernoulli(NaN) => -inf
+            if (VAL) {
+              double pc = fmin(fmax(p, lnk_lo), lnk_hi);
+              lp = fast_log(yb[mt] ? pc : 1.0 - pc);
+            }
+            if (GRAD) w = inside ? (yb[mt] ? (1.0 - p) : -p) : 0.0;  // NaN p: `inside` is false => w = 0
+            if (VAL && sarg != sarg) { lp = d_neg_inf(); w = 0.0; }  // NaN eta => Bernoulli(NaN) => -inf
           } else if (MODE == GLM_POISSON_ID) {
             // distribution.rs:1237-1258 with lambda = eta. Branch-light: the fast path is evaluated
             // unconditionally on a clamped lambda, the reference's guards are selects, and only an
@@ -349,9 +353,11 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             const double kf = yv[mt];
             const bool ok = (lam >= 1e-300 && lam <= 1e300) && kf >= 0.0;
             const double lamc = ok ? lam : 1.0;
-            lp = kf * fast_log(lamc) - lam - ylg[mt];
-            if (lam > 700.0 && kf == 0.0) lp = -lam;
-            if (GRAD) w = d_fin(lp) ? kf * fast_rcp(lamc) - 1.0 : 0.0;
+            if (VAL) {
+              lp = kf * fast_log(lamc) - lam - ylg[mt];
+              if (lam > 700.0 && kf == 0.0) lp = -lam;
+            }
+            if (GRAD) w = (!VAL || d_fin(lp)) ? kf * fast_rcp(lamc) - 1.0 : 0.0;  // ok => lp is finite (lgamma column is)
             if (!ok) {
               lp = d_neg_inf(); w = 0.0;
               if (lam > 0.0 && d_fin(lam) && kf >= 0.0) {  // tiny / huge lambda: exact guards via the library functions
@@ -493,13 +499,13 @@ int64_t dense_plate_splits(const fc_program* P, const PlateInfo& pl, int64_t C) 
   return std::max<int64_t>(1, S);
 }
 
-template <int MODE, bool GRAD, int NT>
+template <int MODE, bool GRAD, int NT, bool VAL = true>
 static int32_t launch_mt(const DenseArgs& A, dim3 grid, size_t smem, cudaStream_t st) {
   int MT = (A.K + 7) / 8;
 #define DN_LAUNCH(M)                                                                                          \
   {                                                                                                           \
-    FC_CUDA(cudaFuncSetAttribute(k_dense_glm<MODE, GRAD, M, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    k_dense_glm<MODE, GRAD, M, NT><<<grid, DN_THREADS(NT), smem, st>>>(A);                                            \
+    FC_CUDA(cudaFuncSetAttribute(k_dense_glm<MODE, GRAD, M, NT, VAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    k_dense_glm<MODE, GRAD, M, NT, VAL><<<grid, DN_THREADS(NT), smem, st>>>(A);                                            \
   }
   // value-only kernels ignore MT except for the sub-tiling it implies (8 / 4 / 2 / 1 sub-tiles per stage)
   if (!GRAD) { if (A.K <= 8) DN_LAUNCH(1) else if (A.K <= 16) DN_LAUNCH(2) else if (A.K <= 32) DN_LAUNCH(4) else DN_LAUNCH(13) }
@@ -514,7 +520,7 @@ static int32_t launch_mt(const DenseArgs& A, dim3 grid, size_t smem, cudaStream_
   return FC_OK;
 }
 
-int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int64_t C, double* d_part, int64_t max_splits, bool grad, int64_t* n_splits) {
+int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int64_t C, double* d_part, int64_t max_splits, bool grad, int64_t* n_splits, bool need_value) {
   const DOp& op = pl.dop;
   const DTerm& dt = op.p[pl.dense_param].t[pl.dense_term];
   int K = dt.col.width;
@@ -554,7 +560,9 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
 #define DN_DISPATCH(MODE_)                                                                              \
   rc = NT == 1 ? (grad ? launch_mt<MODE_, true, 1>(A, grid, smem, P->stream) : launch_mt<MODE_, false, 1>(A, grid, smem, P->stream)) \
                : (grad ? launch_mt<MODE_, true, 2>(A, grid, smem, P->stream) : launch_mt<MODE_, false, 2>(A, grid, smem, P->stream));
-  if (mode == GLM_BERN_SIGMOID) { DN_DISPATCH(GLM_BERN_SIGMOID) }
+  if (grad && !need_value && NT == 1 && mode == GLM_BERN_SIGMOID) rc = launch_mt<GLM_BERN_SIGMOID, true, 1, false>(A, grid, smem, P->stream);
+  else if (grad && !need_value && NT == 1 && mode == GLM_POISSON_ID) rc = launch_mt<GLM_POISSON_ID, true, 1, false>(A, grid, smem, P->stream);
+  else if (mode == GLM_BERN_SIGMOID) { DN_DISPATCH(GLM_BERN_SIGMOID) }
   else if (mode == GLM_POISSON_ID) { DN_DISPATCH(GLM_POISSON_ID) }
   else { DN_DISPATCH(GLM_GENERIC) }
 #undef DN_DISPATCH

@@ -306,9 +306,10 @@ struct Hmc {
   int64_t nsplit() const { return ew_grid.y; }
 
   // value + force at qv -> (lp3, lj_out, g_out)
-  int32_t force(const double* qv, double* lp3, double* lj_out, double* g_out) {
+  // need_value=false: interior leapfrog step, only the force is consumed (lp3 / lj_out are scratch)
+  int32_t force(const double* qv, double* lp3, double* lj_out, double* g_out, bool need_value = true) {
     if (S->cfg.grad_mode == 0) {
-      FC_TRY(score_dev(P, qv, S->qd.p, C, lp3, lj_out, g_out));
+      FC_TRY(score_dev(P, qv, S->qd.p, C, lp3, lj_out, g_out, need_value));
     } else {
       double h = S->cfg.finite_diff_eps;
       FC_CUDA(S->fd_q.reserve(d * C));
@@ -323,7 +324,7 @@ struct Hmc {
         P->n_kernel_launches += 3;
       }
       FC_KERNEL_CHECK();
-      FC_TRY(score_dev(P, qv, S->qd.p, C, lp3, lj_out, nullptr));
+      if (need_value) FC_TRY(score_dev(P, qv, S->qd.p, C, lp3, lj_out, nullptr));
     }
     S->grad_evals += 1;
     return FC_OK;
@@ -347,7 +348,7 @@ struct Hmc {
   int32_t trajectory(const double* eps, uint64_t L) {
     FC_TRY(leap(S->g_cur.p, eps, 0.5, 1, 0));
     for (uint64_t l = 1; l <= L; l++) {
-      FC_TRY(force(S->q_new.p, S->lp3.p, S->lj_new.p, S->g_new.p));
+      FC_TRY(force(S->q_new.p, S->lp3.p, S->lj_new.p, S->g_new.p, l == L));
       if (l < L) FC_TRY(leap(S->g_new.p, eps, 1.0, 1, 0));
       else FC_TRY(leap(S->g_new.p, eps, 0.5, 0, 1));
     }

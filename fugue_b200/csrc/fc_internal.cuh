@@ -119,9 +119,10 @@ struct fc_program {
 namespace fc {
 // Scores C chains resident on the device. q [d_cont][C] (sorted rows), qd [d_disc][C].
 // d_lp3 [3][C] (prior, lik, factors), d_total [C]; d_grad [d_cont][C] or nullptr (value only).
-int32_t score_dev(fc_program* p, const double* d_q, const disc_t* d_qd, int64_t C, double* d_lp3, double* d_total, double* d_grad);
+// need_value=false (only with d_grad): the caller will not read d_lp3 / d_total (interior leapfrog steps)
+int32_t score_dev(fc_program* p, const double* d_q, const disc_t* d_qd, int64_t C, double* d_lp3, double* d_total, double* d_grad, bool need_value = true);
 // dense GLM plate (fc_dense.cu): writes its partial segment, returns the number of splits used
-int32_t dense_plate_launch(fc_program* p, PlateInfo& pl, const double* d_q, int64_t C, double* d_part, int64_t max_splits, bool grad, int64_t* n_splits);
+int32_t dense_plate_launch(fc_program* p, PlateInfo& pl, const double* d_q, int64_t C, double* d_part, int64_t max_splits, bool grad, int64_t* n_splits, bool need_value = true);
 int64_t dense_plate_splits(const fc_program* p, const PlateInfo& pl, int64_t C);
 // PriorHandler replacement: draws every sample site of chains [0,C) in program order;
 // chain c uses Philox stream (seed, stream0 + c), counter tag `tag`.

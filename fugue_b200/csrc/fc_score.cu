@@ -412,7 +412,7 @@ static int sm_count() {
   return g_sm_count;
 }
 
-int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t C, double* d_lp3, double* d_total, double* d_grad) {
+int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t C, double* d_lp3, double* d_total, double* d_grad, bool need_value) {
   if (C <= 0) return FC_OK;
   cudaStream_t st = P->stream;
   const bool grad = d_grad != nullptr;
@@ -447,7 +447,7 @@ int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t 
     if (pl.dop.plate_len == 0) continue;
     if (pl.dense) {
       int64_t ns = 0;
-      FC_TRY(dense_plate_launch(P, pl, d_q, C, P->ws.part.p, splits[i], grad, &ns));
+      FC_TRY(dense_plate_launch(P, pl, d_q, C, P->ws.part.p, splits[i], grad, &ns, need_value));
       const DTerm& dt = pl.dop.p[pl.dense_param].t[pl.dense_term];
       int K = dt.col.width;
       // accumulators: 0..2 lp, then the AccMap's reduced rows, then K dense rows
