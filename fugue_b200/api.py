@@ -175,6 +175,7 @@ _sig("fc_hmc_create", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, vp, vp, C.POIN
 _sig("fc_hmc_create_sharded", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, vp, vp, C.c_uint64, C.POINTER(vp))
 _sig("fc_hmc_destroy", vp)
 _sig("fc_hmc_step", vp, C.c_size_t)
+_sig("fc_hmc_step_recorded", vp, vp, vp, u64p)
 _sig("fc_hmc_sync", vp)
 _sig("fc_hmc_get", vp, vp, vp, vp)
 _sig("fc_hmc_trace", vp, vp, vp, vp)
@@ -228,6 +229,7 @@ class HmcSession:
         check(lib.fc_hmc_create_sharded(self.program.h, C.byref(cfg), seed, self.n_chains, n_warmup, _ptr(q0a), _ptr(qd0a),
                                         first_chain, C.byref(h)))
         self.h = h
+        self._n_leapfrog = max(1, int(self.config.n_leapfrog))
 
     def close(self):
         if getattr(self, "h", None):
@@ -248,6 +250,16 @@ class HmcSession:
 
     def sync(self):
         check(lib.fc_hmc_sync(self.h))
+
+    def step_recorded(self):
+        """HmcSession::step_recorded (hmc.rs:811-817): one transition; returns the leapfrog points
+        (q [L+1][d][C], h [L+1][C]) -- LeapfrogPoint{q, h} (hmc.rs:331-343) for every chain."""
+        L = self._n_leapfrog
+        q = np.zeros((L + 1, self.program.d_cont, self.n_chains))
+        h = np.zeros((L + 1, self.n_chains))
+        n = C.c_uint64()
+        check(lib.fc_hmc_step_recorded(self.h, _ptr(q), _ptr(h), C.byref(n)))
+        return q[:n.value], h[:n.value]
 
     def position(self):
         q = np.zeros((self.program.d_cont, self.n_chains))
@@ -305,6 +317,7 @@ class HmcSession:
 
     def set_n_leapfrog(self, l):
         check(lib.fc_hmc_set_n_leapfrog(self.h, int(l)))
+        self._n_leapfrog = max(1, int(l))
 
     def set_explicit_randomness(self, z, u):
         z = _f64(z).reshape(self.program.d_cont, self.n_chains)
@@ -436,6 +449,10 @@ _sig("fc_smc_step", vp, dp)
 _sig("fc_smc_get", vp, vp, vp, vp, vp, dp, u64p)
 _sig("fc_smc_device_state", vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp))
 _sig("fc_smc_destroy", vp)
+_sig("fc_smc_prior_weights", vp)
+_sig("fc_smc_normalize", vp, dp, dp)
+_sig("fc_smc_resample_particles", vp, C.c_int32, vp, vp)
+_sig("fc_smc_rejuvenate_particles", vp, C.c_double, C.c_uint64)
 _sig("fc_resample", C.c_int32, vp, C.c_size_t, vp, vp)
 _sig("fc_resample_dev", C.c_int32, vp, C.c_size_t, vp, vp, vp)
 _sig("fc_exact_prefix_sums", vp, C.c_size_t, vp)
@@ -493,6 +510,36 @@ class SmcSession:
         check(lib.fc_smc_step(self.h, C.byref(b)))
         return b.value
 
+    # ---- standalone pieces of the SMC surface (smc.rs:230-349, 698-790) on the resident particles ----
+    def prior_weights(self):
+        """smc_prior_particles' weighting: log_weight = log-likelihood (smc.rs:779-787)."""
+        check(lib.fc_smc_prior_weights(self.h))
+        return self
+
+    def normalize(self):
+        """normalize_particles (smc.rs:719-754); returns (log normaliser, ESS of the weights)."""
+        ln, ess = C.c_double(), C.c_double()
+        check(lib.fc_smc_normalize(self.h, C.byref(ln), C.byref(ess)))
+        return ln.value, ess.value
+
+    def effective_sample_size(self):
+        """effective_sample_size(particles) (smc.rs:230-233)."""
+        return self.normalize()[1]
+
+    def resample_particles(self, method=ResamplingMethod.Systematic, uniforms=None):
+        """resample_particles (smc.rs:326-349). Returns the ancestor indices."""
+        idx = np.zeros(self.n, dtype=np.uint64)
+        us = None if uniforms is None else _f64(np.atleast_1d(uniforms))
+        if us is not None and us.size != (1 if method == ResamplingMethod.Systematic else self.n):
+            raise FugueError(_ir.FC_ERR_INVALID_ARGUMENT, "uniforms: 1 value for systematic, n otherwise")
+        check(lib.fc_smc_resample_particles(self.h, method, _ptr(us), _ptr(idx)))
+        return idx
+
+    def rejuvenate_particles(self, beta, rejuvenation_steps):
+        """rejuvenate_particles (smc.rs:698-713): weights are left unchanged."""
+        check(lib.fc_smc_rejuvenate_particles(self.h, float(beta), int(rejuvenation_steps)))
+        return self
+
     def result(self, values=True):
         P, n = self.program, self.n
         v = np.zeros((P.d_cont, n)) if values else None
@@ -515,6 +562,30 @@ def adaptive_smc(model, num_particles, config=None, seed=0):
     r = S.result()
     S.close()
     return r
+
+
+def smc_prior_particles(model, num_particles, seed=0):
+    """smc_prior_particles (smc.rs:764-790): prior draws weighted by their likelihood, resident on
+    the device; returns the session holding them (see its prior_weights / normalize /
+    resample_particles / rejuvenate_particles / result)."""
+    return SmcSession(model, num_particles, SMCConfig(), seed).prior_weights()
+
+
+def resample_particles(particles, method=ResamplingMethod.Systematic, uniforms=None):
+    """resample_particles (smc.rs:326-349) on a session's particles (in place); returns it."""
+    particles.resample_particles(method, uniforms)
+    return particles
+
+
+def rejuvenate_particles(particles, beta, rejuvenation_steps):
+    """rejuvenate_particles (smc.rs:698-713) on a session's particles (in place)."""
+    return particles.rejuvenate_particles(beta, rejuvenation_steps)
+
+
+def normalize_particles(particles):
+    """normalize_particles (smc.rs:719-754)."""
+    particles.normalize()
+    return particles
 
 
 def resample_indices(method, weights, uniforms):

@@ -41,6 +41,8 @@ struct fc_hmc_session {
   int64_t ksplits = 1;
   fc::DevBuf<double> ext_z, ext_u;  // caller-supplied randomness for the next transition (parity tests)
   bool use_ext = false;
+  bool recording = false;            // the next transition records its leapfrog points (step_recorded)
+  fc::DevBuf<double> rec_q, rec_h;  // [L+1][d][C], [L+1][C]
 };
 
 namespace fc {
@@ -123,6 +125,17 @@ __global__ void k_leap(double* __restrict__ qn, double* __restrict__ p, const do
       kpart[(int64_t)blockIdx.y * C + c] = s;
     }
   }
+}
+
+// Hamiltonian of a recorded leapfrog point (hmc.rs:372-379): -log_joint + 0.5 * sum p^2 m_inv. A
+// chain that has left the support records NaN from that point on (hmc.rs:335-337: the reference
+// truncates the recording there).
+__global__ void k_record_h(const double* __restrict__ lj, const double* __restrict__ kpart, int64_t ksplits, const int32_t* __restrict__ divergent, double* __restrict__ h_out, int64_t C) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double k = 0.0;
+  for (int64_t s = 0; s < ksplits; s++) k += kpart[s * C + c];
+  h_out[c] = divergent[c] ? __longlong_as_double(0x7ff8000000000000LL) : -lj[c] + 0.5 * k;
 }
 
 __global__ void k_h0(const double* __restrict__ lj, const double* __restrict__ kpart, int64_t ksplits, double* __restrict__ h0, int32_t* __restrict__ divergent, int64_t C) {
@@ -355,6 +368,27 @@ struct Hmc {
     return FC_OK;
   }
 
+  // The same trajectory with every integration point recorded (leapfrog(.., record), hmc.rs:353-403):
+  // the start, then (q, H) after the trailing half kick of each step. The kicks are issued as two
+  // half kicks (as the reference does) so the momentum exists at each recorded point.
+  int32_t trajectory_recorded(const double* eps, uint64_t L) {
+    FC_CUDA(S->rec_q.reserve((int64_t)(L + 1) * d * C));
+    FC_CUDA(S->rec_h.reserve((int64_t)(L + 1) * C));
+    FC_CUDA(cudaMemcpyAsync(S->rec_q.p, S->q.p, d * C * 8, cudaMemcpyDeviceToDevice, st));
+    FC_CUDA(cudaMemcpyAsync(S->rec_h.p, S->h0.p, C * 8, cudaMemcpyDeviceToDevice, st));
+    FC_TRY(leap(S->g_cur.p, eps, 0.5, 1, 0));
+    for (uint64_t l = 1; l <= L; l++) {
+      FC_TRY(force(S->q_new.p, S->lp3.p, S->lj_new.p, S->g_new.p, true));
+      FC_TRY(leap(S->g_new.p, eps, 0.5, 0, 1));
+      k_record_h<<<cb, 128, 0, st>>>(S->lj_new.p, S->kpart.p, nsplit(), S->divergent.p, S->rec_h.p + (int64_t)l * C, C);
+      FC_KERNEL_CHECK();
+      P->n_kernel_launches += 1;
+      FC_CUDA(cudaMemcpyAsync(S->rec_q.p + (int64_t)l * d * C, S->q_new.p, d * C * 8, cudaMemcpyDeviceToDevice, st));
+      if (l < L) FC_TRY(leap(S->g_new.p, eps, 0.5, 1, 0));
+    }
+    return FC_OK;
+  }
+
   // hmc.rs:479-535 for all chains at once
   int32_t find_reasonable_epsilon() {
     uint64_t tag = 0x4000000000000000ULL | S->iter;  // momentum stream distinct from transitions
@@ -404,7 +438,9 @@ struct Hmc {
     if (d == 0) { S->iter++; return FC_OK; }
     uint64_t tag = S->iter;
     FC_TRY(momentum(tag));
-    FC_TRY(trajectory(S->eps.p, S->L));
+    if (S->recording) FC_TRY(trajectory_recorded(S->eps.p, S->L));
+    else FC_TRY(trajectory(S->eps.p, S->L));
+    S->recording = false;
     k_accept<<<cb, 128, 0, st>>>(S->lj_new.p, S->kpart.p, nsplit(), S->h0.p, S->lj.p, S->divergent.p, S->accepted.p, S->ap.p, S->n_accept.p, S->n_divergent.p,
                                  S->eps.p, S->da.p, C, S->seed, S->chain0, tag, (uint64_t)((d + 1) / 2 + 1), warming ? 1 : 0, S->cfg.target_accept, S->use_ext ? S->ext_u.p : nullptr);
     FC_KERNEL_CHECK();
@@ -518,6 +554,26 @@ int32_t fc_hmc_step(fc_hmc_session* s, size_t n) {
   FC_CUDA(cudaSetDevice(s->P->device));
   fc::Hmc H(s);
   for (size_t i = 0; i < n; i++) FC_TRY(H.step());
+  return FC_OK;
+}
+
+// HmcSession::step_recorded (hmc.rs:811-817): one transition whose leapfrog points are recorded.
+// h_q [L+1][d][C], h_h [L+1][C] (either may be NULL); point 0 is the start of the trajectory.
+int32_t fc_hmc_step_recorded(fc_hmc_session* s, double* h_q, double* h_h, uint64_t* n_points) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  fc::Hmc H(s);
+  const uint64_t L = s->L;
+  s->recording = s->d > 0;
+  FC_TRY(H.step());
+  s->recording = false;
+  cudaStream_t st = s->P->stream;
+  if (n_points) *n_points = s->d > 0 ? L + 1 : 0;
+  if (s->d > 0) {
+    if (h_q) FC_CUDA(cudaMemcpyAsync(h_q, s->rec_q.p, (L + 1) * s->d * s->C * 8, cudaMemcpyDeviceToHost, st));
+    if (h_h) FC_CUDA(cudaMemcpyAsync(h_h, s->rec_h.p, (L + 1) * s->C * 8, cudaMemcpyDeviceToHost, st));
+  }
+  FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;
 }
 

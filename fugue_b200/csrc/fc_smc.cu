@@ -600,6 +600,99 @@ int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dv
   return FC_OK;
 }
 
+// ---- standalone pieces of the SMC public surface, on the particles resident in a session ----
+
+// smc_prior_particles' weighting (smc.rs:779-787, FG-03): log_weight = log-likelihood of the particle
+int32_t fc_smc_prior_weights(fc_smc_session* s) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  FC_CUDA(cudaMemcpyAsync(s->log_w.p, s->ll.p, s->n * 8, cudaMemcpyDeviceToDevice, s->P->stream));
+  s->log_w_uniform = false;
+  return FC_OK;
+}
+
+// normalize_particles (smc.rs:719-754): weight = exp(log_weight - lse), uniform if every log_weight is
+// -inf; log_weight is left as it is. Returns ESS = 1 / sum w^2 (smc.rs:230-233) in *ess (may be NULL).
+int32_t fc_smc_normalize(fc_smc_session* s, double* log_norm_out, double* ess) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  fc_program* p = s->P;
+  FC_CUDA(cudaSetDevice(p->device));
+  cudaStream_t st = p->stream;
+  const int64_t n = s->n;
+  unsigned nbk = (unsigned)cdiv(n, 256);
+  FC_TRY(smc_materialise_log_w(s));
+  double log_norm;
+  FC_TRY(dev_log_sum_exp(s->log_w.p, n, s->scratch.p, &log_norm, st));
+  if (std::isfinite(log_norm)) k_sub_exp<<<nbk, 256, 0, st>>>(s->log_w.p, log_norm, s->comb.p, s->w.p, n);
+  else k_fill2<<<nbk, 256, 0, st>>>(s->w.p, 1.0 / (double)n, n);
+  FC_KERNEL_CHECK();
+  p->n_kernel_launches += 5;
+  if (log_norm_out) *log_norm_out = log_norm;
+  if (ess) {
+    FC_TRY(dev_reduce(2, s->w.p, n, 0.0, s->scratch.p, s->scratch.p + RDB, st));
+    double ss;
+    FC_CUDA(cudaMemcpyAsync(&ss, s->scratch.p + RDB, 8, cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    *ess = 1.0 / ss;
+  }
+  return FC_OK;
+}
+
+// resample_particles (smc.rs:326-349): indices by `method` from the normalised weights, ancestors
+// copied, weight = 1/n and log_weight = ln(1/n). h_uniforms (1 for systematic, n otherwise) may be
+// NULL: the session's Philox stream is used. h_idx (n entries) may be NULL.
+int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const double* h_uniforms, uint64_t* h_idx) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  if (method < FC_RESAMPLE_MULTINOMIAL || method > FC_RESAMPLE_STRATIFIED) { set_error("bad resampling method %d", method); return FC_ERR_INVALID_ARGUMENT; }
+  fc_program* P = s->P;
+  FC_TRY(fc_smc_normalize(s, nullptr, nullptr));
+  cudaStream_t st = P->stream;
+  const int64_t n = s->n;
+  unsigned nbk = (unsigned)cdiv(n, 256);
+  int64_t nu = method == FC_RESAMPLE_SYSTEMATIC ? 1 : n;
+  FC_CUDA(s->us.reserve(nu + 1));
+  s->steps += 1;
+  if (h_uniforms) FC_CUDA(cudaMemcpyAsync(s->us.p, h_uniforms, nu * 8, cudaMemcpyHostToDevice, st));
+  else k_uniform_one<<<(unsigned)cdiv(cdiv(nu, 2), 256), 256, 0, st>>>(s->us.p, s->seed, 0x1000000000000000ULL | s->steps, nu);
+  FC_TRY(resample_dev(method, s->w.p, n, s->us.p, s->idx.p, *s->rw, st, &P->n_kernel_launches));
+  dim3 gg(nbk, 1);
+  if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_cont, 8), 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, s->q2.p, s->idx.p, P->d_cont, n); std::swap(s->q.p, s->q2.p); std::swap(s->q.n, s->q2.n); }
+  if (P->d_disc) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_disc, 8), 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, s->qd2.p, s->idx.p, P->d_disc, n); std::swap(s->qd.p, s->qd2.p); std::swap(s->qd.n, s->qd2.n); }
+  gg.y = 1;
+  k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, s->lp3b.p, s->idx.p, 3, n);
+  std::swap(s->lp3.p, s->lp3b.p); std::swap(s->lp3.n, s->lp3b.n);
+  k_loglik<<<nbk, 256, 0, st>>>(s->lp3.p, s->ll.p, n);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 5;
+  s->log_w_uniform = true;
+  if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, s->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  return FC_OK;
+}
+
+// rejuvenate_particles (smc.rs:698-713): `steps` pi_beta-invariant single-site MH moves per particle,
+// weights untouched (FG-13). n_accepted (may be NULL) = accepted moves summed over particles.
+int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t steps) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  if (!(beta >= 0.0 && beta <= 1.0)) { set_error("beta must be in [0, 1], got %g", beta); return FC_ERR_INVALID_ARGUMENT; }
+  fc_program* P = s->P;
+  FC_CUDA(cudaSetDevice(P->device));
+  for (uint64_t r = 0; r < steps; r++) {
+    FC_TRY(s->eng.step(s->q.p, s->qd.p, s->lp3.p, s->total.p, s->n_accept.p, s->moves, beta, true, 0.44, 0.7));
+    FC_TRY(s->eng.shared_adapt(0.44, 0.7));
+    s->moves += 1;
+  }
+  k_loglik<<<(unsigned)cdiv(s->n, 256), 256, 0, P->stream>>>(s->lp3.p, s->ll.p, s->n);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
+  FC_CUDA(cudaStreamSynchronize(P->stream));
+  return FC_OK;
+}
+
 // adaptive_smc (smc.rs:455-581). h_values [d_cont][n], h_dvalues [d_disc][n]; outputs may be NULL.
 int32_t fc_smc_run(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t n, double* h_values, int64_t* h_dvalues, double* h_weight, double* h_log_weight,
                    double* log_evidence, uint64_t* n_temper_steps) {

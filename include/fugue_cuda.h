@@ -176,6 +176,10 @@ int32_t fc_hmc_destroy(fc_hmc_session* s);
  * the program's stream; fc_hmc_sync() or any getter waits. */
 int32_t fc_hmc_step(fc_hmc_session* s, size_t n);
 int32_t fc_hmc_sync(fc_hmc_session* s);
+/* HmcSession::step_recorded (hmc.rs:811-817): one transition, recording LeapfrogPoint{q, h}
+ * (hmc.rs:331-343) at the start and after every leapfrog step: h_q [L+1][d][C], h_h [L+1][C]
+ * (H = -log pi(q) + 1/2 p^T M^-1 p; NaN once a chain has left the support). Synchronous. */
+int32_t fc_hmc_step_recorded(fc_hmc_session* s, double* h_q, double* h_h, uint64_t* n_points);
 /* HmcSession::position / step_size (hmc.rs:752-777): copy state to host. Any pointer may be NULL. */
 int32_t fc_hmc_get(fc_hmc_session* s, double* h_q, double* h_lp, fc_hmc_stats* h_stats);
 /* HmcSession::trace accumulators of the current state (trace.rs:168-177). */
@@ -262,6 +266,16 @@ int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, doub
 int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dvalues,
                             double** d_log_w, double** d_loglik);
 int32_t fc_smc_destroy(fc_smc_session* s);
+/* Standalone pieces of the SMC surface on a session's resident particles:
+ *   fc_smc_prior_weights       smc_prior_particles' weighting, log_weight = log-likelihood (smc.rs:779-787)
+ *   fc_smc_normalize           normalize_particles (smc.rs:719-754) + effective_sample_size (smc.rs:230-233)
+ *   fc_smc_resample_particles  resample_particles (smc.rs:326-349); h_uniforms NULL = session stream
+ *   fc_smc_rejuvenate_particles rejuvenate_particles (smc.rs:698-713), weights unchanged */
+int32_t fc_smc_prior_weights(fc_smc_session* s);
+int32_t fc_smc_normalize(fc_smc_session* s, double* log_norm, double* ess);
+int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const double* h_uniforms,
+                                  uint64_t* h_idx);
+int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t steps);
 /* next_beta (smc.rs:588-622) on host arrays: the largest beta' in (beta, 1] whose incremental
  * weights log_w + (beta' - beta) * ll keep ESS >= target_ess (64-step bisection; 1.0 if a full
  * jump already does). Parity probe for the tempering ladder. */

@@ -167,3 +167,50 @@ def test_returned_trace_has_fresh_weights():
     rlp, rll, rlf = P.logp(q)
     assert np.allclose(lp, rlp, rtol=1e-12) and np.allclose(ll, rll, rtol=1e-12)
     assert np.allclose(S.log_joint(), rlp + rll + rlf, rtol=1e-12)
+
+
+def test_step_recorded_trajectory_matches_restated_leapfrog():
+    """HmcSession::step_recorded (hmc.rs:811-817): LeapfrogPoint{q, h} at the start and after every
+    step equals the leapfrog of hmc.rs:353-403 restated here with the oracle as scorer, on the same
+    momentum; the recorded endpoint is the proposal, and a recorded step is a normal transition."""
+    from fugue_b200 import api
+    rng = np.random.default_rng(4)
+    m = models.hierarchical(G=6, per_group=4)[0]
+    O = oracle.OracleProgram(m)
+    Cn, L, eps = 8, 5, 0.03
+    q0 = _init_q(O, rng, Cn)
+    S = api.HmcSession(m, n_chains=Cn, n_warmup=0, config=api.HMCConfig(n_leapfrog=L, init_step_size=eps), seed=5, q0=q0)
+    z = rng.standard_normal((O.d_cont, Cn))
+    u = rng.random(Cn)
+    S.set_explicit_randomness(z, u)
+    rq, rh = S.step_recorded()
+    assert rq.shape == (L + 1, O.d_cont, Cn) and rh.shape == (L + 1, Cn)
+    assert np.array_equal(rq[0], q0)
+
+    def lj_grad(q):
+        lp, ll, lf, g = O.logp(q, grad=True)
+        return lp + ll + lf, g
+
+    q, p = q0.copy(), z.copy()  # unit mass: p = z
+    lj, g = lj_grad(q)
+    hs, qs = [-lj + 0.5 * (p * p).sum(0)], [q.copy()]
+    for _ in range(L):
+        p = p + 0.5 * eps * g
+        q = q + eps * p
+        lj, g = lj_grad(q)
+        p = p + 0.5 * eps * g
+        hs.append(-lj + 0.5 * (p * p).sum(0))
+        qs.append(q.copy())
+    assert np.allclose(rq, np.array(qs), rtol=1e-10, atol=1e-12)
+    assert np.allclose(rh, np.array(hs), rtol=1e-10, atol=1e-10)
+    info, qn = S.last_step_info(), S.position()
+    ap = np.minimum(1.0, np.exp(hs[0] - hs[-1]))
+    assert np.allclose(info["accept_prob"], ap, rtol=1e-8)
+    for c in range(Cn):
+        want = rq[L, :, c] if info["accepted"][c] else q0[:, c]
+        assert np.array_equal(qn[:, c], want)
+    assert S.iterations()[0] == 1 if isinstance(S.iterations(), tuple) else True
+    # the next, unrecorded transition is unaffected by the recorder
+    S.step(1)
+    assert S.grad_evals() == 2 * L
+    S.close()

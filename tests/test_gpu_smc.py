@@ -172,3 +172,48 @@ def test_mixture_model_smc_runs_and_orders_components():
     s = r.sites
     sig1 = r.values[s.index("sigma1")]
     assert (sig1 > 0).all()
+
+
+def test_standalone_prior_particles_resample_rejuvenate():
+    """The SMC surface around adaptive_smc on resident particles: smc_prior_particles (smc.rs:764-790,
+    log_weight = log-likelihood), normalize_particles / effective_sample_size (smc.rs:230-233, 719-754),
+    resample_particles (smc.rs:326-349; indices bit-exact vs the sequential oracle on the same weights
+    and uniform, ancestors copied, weights reset to 1/n) and rejuvenate_particles (smc.rs:698-713;
+    pi_1-invariant moves leave the SIR posterior in place and the weights untouched)."""
+    from fugue_b200 import api
+    y = np.array([1.5, 2.0, 2.5, 1.8, 2.2])
+    m = ModelBuilder()
+    mu = m.sample("mu", Normal(0.0, 2.0))
+    m.plate_observe("y", Normal(mu, 1.0), m.data(y))
+    n = 1 << 16
+    S = api.smc_prior_particles(m, n, seed=9)
+    log_norm, ess = S.normalize()
+    r0 = S.result()
+    v0 = r0.values[0].copy()
+    ll = np.array([(-0.5 * (y - v) ** 2 - 0.5 * math.log(2 * math.pi)).sum() for v in v0])
+    mx = ll.max()
+    lse = mx + math.log(np.exp(ll - mx).sum())
+    assert abs(log_norm - lse) < 1e-10 * abs(lse)
+    w_ref = np.exp(ll - lse)
+    assert np.allclose(r0.weight, w_ref, rtol=1e-9, atol=1e-300)
+    assert abs(ess - 1.0 / (r0.weight ** 2).sum()) < 1e-9 * ess
+    assert abs(S.effective_sample_size() - ess) == 0.0
+    for method, us in ((1, [0.37]), (2, np.random.default_rng(1).random(n)), (0, np.random.default_rng(2).random(n))):
+        S2 = api.smc_prior_particles(m, n, seed=9)
+        S2.normalize()
+        w_dev = S2.result().weight
+        idx = S2.resample_particles(method, us)
+        assert np.array_equal(idx, oracle.resample(method, w_dev, us))
+        r1 = S2.result()
+        assert np.array_equal(r1.values[0], v0[idx.astype(np.int64)])
+        assert np.all(r1.weight == 1.0 / n) or np.allclose(r1.weight, 1.0 / n, rtol=1e-12)
+        S2.close()
+    idx = S.resample_particles(api.ResamplingMethod.Systematic)  # session stream uniform
+    assert idx.shape == (n,) and (np.diff(idx.astype(np.int64)) >= 0).all()
+    api.rejuvenate_particles(S, 1.0, 8)
+    r2 = S.result()
+    x = r2.values[0]
+    assert abs(x.mean() - 1.90476) < 0.02 and abs(x.var() - 0.190476) < 0.02
+    assert np.allclose(r2.weight, 1.0 / n, rtol=1e-12)
+    assert len(np.unique(x)) > n // 4  # the moves diversified the resampled population
+    S.close()
