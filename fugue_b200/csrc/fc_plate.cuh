@@ -368,6 +368,11 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
 // partials [n_splits][3][C], 2 = launched and lp3 already updated (single split)
 int plate_vec_launch(const PlateArgs& A, int64_t n_splits, double* d_lp3, cudaStream_t st);
 
+// grouped Normal observation plate, gradient pass, group walk from shared memory (fc_plate_csr.cu)
+bool plate_csr_eligible(const DOp& op);
+int64_t plate_csr_chain_blocks(int64_t C);
+int plate_csr_launch(const PlateArgs& A, int64_t n_splits, bool need_value, cudaStream_t st);
+
 // instantiation units: fc_plate_{v8,v1,g8,g1}.cu (value-only / gradient x TY = 8 / 1)
 template <bool GRAD, int TY>
 int plate_fast_dispatch(int dk, int k0, int k1, const FastArgs& F, dim3 grid, cudaStream_t st);

@@ -390,12 +390,16 @@ __global__ void k_total(const double* __restrict__ lp3, double* __restrict__ tot
 }
 
 // fast-kernel CTA shape: 256 chains x 1 once there are enough chains to fill whole CTAs
-static int plate_ty(const PlateInfo& pl, int64_t C) { return (C >= 16384 && plate_fast_eligible(pl.dop)) ? 1 : PL_TY; }
+static int g_ty1_min = getenv("FC_PLATE_TY1_MIN") ? atoi(getenv("FC_PLATE_TY1_MIN")) : 16384;
+static int plate_ty(const PlateInfo& pl, int64_t C) { return (C >= g_ty1_min && plate_fast_eligible(pl.dop)) ? 1 : PL_TY; }
 
-static int64_t plate_splits(const PlateInfo& pl, int64_t C, int sm_count) {
-  const int ty = plate_ty(pl, C);
+static bool plate_use_csr(const PlateInfo& pl, bool grad) { return grad && pl.has_gather && plate_csr_eligible(pl.dop); }
+
+static int64_t plate_splits(const PlateInfo& pl, int64_t C, int sm_count, bool grad) {
+  const bool csr = plate_use_csr(pl, grad);
+  const int ty = csr ? 1 : plate_ty(pl, C);
   int64_t units = pl.has_gather ? pl.n_groups : pl.dop.plate_len;
-  int64_t cblocks = cdiv(C, 256 / ty);
+  int64_t cblocks = csr ? plate_csr_chain_blocks(C) : cdiv(C, 256 / ty);
   int64_t want = cdiv((int64_t)sm_count * 8, cblocks);           // ~8 CTAs per SM
   int64_t max_by_work = std::max<int64_t>(1, units / (ty * 4));  // >= 4 units per thread
   return std::max<int64_t>(1, std::min(want, max_by_work));
@@ -422,7 +426,7 @@ int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t 
   std::vector<int64_t> splits(P->plates.size());
   for (size_t i = 0; i < P->plates.size(); i++) {
     PlateInfo& pl = *P->plates[i];
-    splits[i] = pl.dense ? dense_plate_splits(P, pl, C) : plate_splits(pl, C, sm_count());
+    splits[i] = pl.dense ? dense_plate_splits(P, pl, C) : plate_splits(pl, C, sm_count(), grad);
     int64_t n_acc = pl.dense ? (3 + 24 + pl.dop.p[pl.dense_param].t[pl.dense_term].col.width) : pl.acc.n_acc;
     need = std::max(need, splits[i] * n_acc * C);
   }
@@ -473,7 +477,8 @@ int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t 
     const int ty = plate_ty(pl, C);
     dim3 grid((unsigned)cdiv(C, PL_TX), (unsigned)ns), block(PL_TX, PL_TY), fgrid((unsigned)cdiv(C, 256 / ty), (unsigned)ns);
     int vec = grad ? 0 : plate_vec_launch(A, ns, d_lp3, st);
-    if (!vec && !plate_fast_launch(A, grad, ty, fgrid, st)) {
+    if (plate_use_csr(pl, grad)) plate_csr_launch(A, ns, need_value, st);
+    else if (!vec && !plate_fast_launch(A, grad, ty, fgrid, st)) {
       if (grad) k_plate<true><<<grid, block, 0, st>>>(A);
       else k_plate<false><<<grid, block, 0, st>>>(A);
     }
