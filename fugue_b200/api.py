@@ -453,6 +453,14 @@ _sig("fc_smc_prior_weights", vp)
 _sig("fc_smc_normalize", vp, dp, dp)
 _sig("fc_smc_resample_particles", vp, C.c_int32, vp, vp)
 _sig("fc_smc_rejuvenate_particles", vp, C.c_double, C.c_uint64)
+_sig("fc_smc_shard_begin", vp, C.c_uint64)
+_sig("fc_smc_shard_tri", vp, C.c_double, vp)
+_sig("fc_smc_shard_reweight", vp, C.c_double, C.c_double)
+_sig("fc_smc_shard_scan", vp, C.c_double, dp)
+_sig("fc_smc_shard_offspring", vp, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, vp, vp, vp)
+_sig("fc_smc_shard_install", vp, C.c_uint64, C.c_uint64, vp, vp)
+_sig("fc_smc_shard_resampled", vp)
+_sig("fc_smc_shard_weights", vp, vp, vp)
 _sig("fc_resample", C.c_int32, vp, C.c_size_t, vp, vp)
 _sig("fc_resample_dev", C.c_int32, vp, C.c_size_t, vp, vp, vp)
 _sig("fc_exact_prefix_sums", vp, C.c_size_t, vp)

@@ -252,8 +252,11 @@ __global__ void k_scan_serial(const double* __restrict__ w, int64_t from, int64_
 }
 
 // S[0..n] := sequentially rounded prefix sums of w[0..n). d_work: >= cdiv(n, SC_TILE) Inc2 + ScanState.
-int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_work, double* d_scratch, cudaStream_t st, uint64_t* launches) {
-  FC_CUDA(cudaMemsetAsync(d_S, 0, 8, st));
+// carry = the running sum the scan starts from (0 for a whole population; the exact end value of
+// the previous rank for one shard of a rank-major global population)
+int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_work, double* d_scratch, cudaStream_t st, uint64_t* launches, double carry) {
+  FC_CUDA(cudaMemcpyAsync(d_S, &carry, 8, cudaMemcpyHostToDevice, st));
+  FC_CUDA(cudaStreamSynchronize(st));
   if (n == 0) return FC_OK;
   // validity: all weights finite and >= 0, else the serial fallback
   double bad = 0.0;
@@ -270,7 +273,7 @@ int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_wor
   ScanState* d_state = (ScanState*)d_work;
   Inc2* d_agg = (Inc2*)((char*)d_work + 64);
   ScanState hs;
-  hs.k0 = 0; hs.s0 = 0.0; hs.first_cross = 0x7fffffffffffffffLL;
+  hs.k0 = 0; hs.s0 = carry; hs.first_cross = 0x7fffffffffffffffLL;
   FC_CUDA(cudaMemcpyAsync(d_state, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
   // window policy: for near-uniform weights the running sum needs about as many further elements
   // to leave a binade as it took to reach it, so after a crossing at element k the next window is
@@ -370,12 +373,40 @@ int32_t resample_dev(int method, const double* d_w, int64_t n, const double* d_u
   if (n == 0) return FC_OK;
   if (method < FC_RESAMPLE_MULTINOMIAL || method > FC_RESAMPLE_STRATIFIED) { set_error("bad resampling method %d", method); return FC_ERR_INVALID_ARGUMENT; }
   FC_TRY(W.reserve(n));
-  FC_TRY(exact_prefix_sums(d_w, n, W.S.p, W.work.p, W.scratch.p, st, launches));
+  FC_TRY(exact_prefix_sums(d_w, n, W.S.p, W.work.p, W.scratch.p, st, launches, 0.0));
   unsigned nb = (unsigned)cdiv(n, 256);
   if (method == FC_RESAMPLE_MULTINOMIAL) k_resample_multinomial<<<nb, 256, 0, st>>>(W.S.p, n, d_us, d_idx);
   else k_resample_walk<<<nb, 256, 0, st>>>(W.S.p, n, method, d_us, d_idx);
   FC_KERNEL_CHECK();
   if (launches) *launches += 1;
+  return FC_OK;
+}
+
+// One shard of a global systematic resample (smc.rs:255-272 over the rank-major population):
+// S[0..n] is this rank's exact running sum starting from its carry-in. For the global output slots
+// j in [jlo, jhi) -- those whose threshold u/N + j/N falls into (carry, end] of this rank, or past
+// the end of the last rank -- the ancestor is local particle (i - 1).min(n - 1), i the first index
+// with S_i >= threshold.
+__global__ void k_shard_ancestors(const double* __restrict__ S, int64_t n, double n_total, double u_raw, int64_t jlo, int64_t cnt, uint64_t* __restrict__ idx) {
+  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= cnt) return;
+  double thr = __dadd_rn(__ddiv_rn(u_raw, n_total), __ddiv_rn((double)(jlo + k), n_total));
+  int64_t i = lower_bound_S(S, n, thr);
+  if (i > n) i = n;
+  int64_t a = (i == 0) ? 0 : (i - 1 < n - 1 ? i - 1 : n - 1);  // i == 0 cannot happen for a slot routed here (carry < threshold)
+  idx[k] = (uint64_t)a;
+}
+int32_t shard_scan(const double* d_w, int64_t n, double carry, ResampleWork& W, cudaStream_t st, uint64_t* launches, double* end_value) {
+  FC_TRY(W.reserve(n));
+  FC_TRY(exact_prefix_sums(d_w, n, W.S.p, W.work.p, W.scratch.p, st, launches, carry));
+  FC_CUDA(cudaMemcpyAsync(end_value, W.S.p + n, 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  return FC_OK;
+}
+int32_t shard_ancestors(ResampleWork& W, int64_t n, double n_total, double u_raw, int64_t jlo, int64_t cnt, uint64_t* d_idx, cudaStream_t st) {
+  if (cnt <= 0) return FC_OK;
+  k_shard_ancestors<<<(unsigned)cdiv(cnt, 256), 256, 0, st>>>(W.S.p, n, n_total, u_raw, jlo, cnt, d_idx);
+  FC_KERNEL_CHECK();
   return FC_OK;
 }
 
@@ -435,7 +466,7 @@ int32_t fc_exact_prefix_sums(const double* h_w, size_t n, double* h_S) {
   FC_CUDA(w.reserve(n));
   FC_TRY(W.reserve((int64_t)n));
   if (n) FC_CUDA(cudaMemcpyAsync(w.p, h_w, n * 8, cudaMemcpyHostToDevice, st));
-  FC_TRY(exact_prefix_sums(w.p, (int64_t)n, W.S.p, W.work.p, W.scratch.p, st, nullptr));
+  FC_TRY(exact_prefix_sums(w.p, (int64_t)n, W.S.p, W.work.p, W.scratch.p, st, nullptr, 0.0));
   FC_CUDA(cudaMemcpyAsync(h_S, W.S.p, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;

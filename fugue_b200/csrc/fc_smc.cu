@@ -22,6 +22,8 @@ struct ResampleWork;
 ResampleWork* resample_work_new();
 void resample_work_free(ResampleWork*);
 int32_t resample_dev(int method, const double* d_w, int64_t n, const double* d_us, uint64_t* d_idx, ResampleWork& W, cudaStream_t st, uint64_t* launches);
+int32_t shard_scan(const double* d_w, int64_t n, double carry, ResampleWork& W, cudaStream_t st, uint64_t* launches, double* end_value);
+int32_t shard_ancestors(ResampleWork& W, int64_t n, double n_total, double u_raw, int64_t jlo, int64_t cnt, uint64_t* d_idx, cudaStream_t st);
 
 #define RDB 1024  // must match RD_BLOCKS of fc_resample.cu
 
@@ -150,6 +152,7 @@ __device__ __forceinline__ void nb_fold_update(Tri acc, Bisect* __restrict__ B, 
   __syncthreads();
   if (threadIdx.x != 0) return;
   for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(t, sm[w]);
+  part[gridDim.x] = t;  // the folded (max, sum e, sum e^2): read by the sharded driver (fc_smc_shard_tri)
   B->counter = 0;
   const double ninf = d_neg_inf();
   double lse1 = (t.m == ninf && t.s1 == 0.0) ? ninf : (t.s1 == 0.0 ? ninf : t.m + log(t.s1));
@@ -292,13 +295,13 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, con
 
 // normalised weights after the reweight: log_w' = (log_w + d ll) - log_norm, w = exp(log_w')
 __global__ void k_reweight(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, double d, const Bisect* __restrict__ B,
-                           double* __restrict__ out_log, double* __restrict__ out_w, int64_t P) {
+                           double* __restrict__ out_log, double* __restrict__ out_w, int64_t P, double n_unif) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
   const double log_norm = B->lse1;
-  if (!isfinite(log_norm)) {  // normalize_particles' uniform fallback (smc.rs:719-753)
-    if (out_log) out_log[i] = -log((double)P);
-    out_w[i] = 1.0 / (double)P;
+  if (!isfinite(log_norm)) {  // normalize_particles' uniform fallback (smc.rs:719-753); n_unif = population size
+    if (out_log) out_log[i] = -log(n_unif);
+    out_w[i] = 1.0 / n_unif;
     return;
   }
   double v = ((log_w ? log_w[i] : lw_const) + d * ll[i]) - log_norm;
@@ -308,8 +311,14 @@ __global__ void k_reweight(const double* __restrict__ log_w, double lw_const, co
 
 // gather particle planes by ancestor index (resample_particles, smc.rs:326-349)
 template <class T>
-__global__ void __launch_bounds__(256) k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P) {
+__global__ void __launch_bounds__(256) k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P, int64_t n_out = -1) {
   int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n_out >= 0) {  // n_out offspring packed plane-major with stride n_out (sharded resampling)
+    if (j >= n_out) return;
+    const int64_t a2 = (int64_t)idx[j];
+    for (int64_t r = (int64_t)blockIdx.y; r < rows; r += gridDim.y) dst[r * n_out + j] = src[r * P + a2];
+    return;
+  }
   if (j >= P) return;
   const int64_t a = (int64_t)idx[j];
   // rows r = blockIdx.y*8 + k (+ 8*gridDim.y ...): 8 independent loads in flight per thread
@@ -349,6 +358,7 @@ struct fc_smc_session {
   double beta = 0.0, log_evidence = 0.0;
   uint64_t steps = 0, moves = 0;
   bool finished = false;
+  double n_global = 0.0;  // population size the uniform weight refers to (0: this session's own n)
 };
 
 namespace fc {
@@ -401,7 +411,7 @@ static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, 
   // (max_ll / bad in the Bisect block are those of this step's next_beta pre-pass: same ll)
   if (lw) k_nb_eval<<<nb_blocks(n), NB_THREADS, 0, st>>>(lw, lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
   else k_nb_eval_uni<<<nb_blocks(n), NB_THREADS, 0, st>>>(lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
-  k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n);
+  k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n, (double)n);
   FC_KERNEL_CHECK();
   S->P->n_kernel_launches += 2;
   Bisect hb;
@@ -463,7 +473,7 @@ int32_t next_beta_host(const double* h_log_w, const double* h_ll, size_t n, doub
   DevBuf<double> lw, ll;
   DevBuf<Bisect> bis;
   DevBuf<Tri> tri;
-  FC_CUDA(lw.reserve(n)); FC_CUDA(ll.reserve(n)); FC_CUDA(bis.reserve(1)); FC_CUDA(tri.reserve(RDB));
+  FC_CUDA(lw.reserve(n)); FC_CUDA(ll.reserve(n)); FC_CUDA(bis.reserve(1)); FC_CUDA(tri.reserve(RDB + 1));
   bool uniform = true;  // the state adaptive_smc calls next_beta in: takes the single-stream path
   for (size_t i = 1; i < n && uniform; i++) uniform = h_log_w[i] == h_log_w[0];
   if (!uniform) FC_CUDA(cudaMemcpy(lw.p, h_log_w, n * 8, cudaMemcpyHostToDevice));
@@ -474,7 +484,7 @@ int32_t next_beta_host(const double* h_log_w, const double* h_ll, size_t n, doub
 // log_w as an array (callers that read it: fc_smc_get, fc_smc_device_state)
 static int32_t smc_materialise_log_w(fc_smc_session* S) {
   if (!S->log_w_uniform) return FC_OK;
-  k_fill2<<<(unsigned)cdiv(S->n, 256), 256, 0, S->P->stream>>>(S->log_w.p, -std::log((double)S->n), S->n);
+  k_fill2<<<(unsigned)cdiv(S->n, 256), 256, 0, S->P->stream>>>(S->log_w.p, -std::log(S->n_global > 0.0 ? S->n_global : (double)S->n), S->n);
   FC_KERNEL_CHECK();
   S->P->n_kernel_launches += 1;
   return FC_OK;
@@ -520,7 +530,7 @@ int32_t fc_smc_create(fc_program* p, const fc_smc_config* cfg, uint64_t seed, si
   FC_CUDA(S->lp3.reserve(3 * N)); FC_CUDA(S->lp3b.reserve(3 * N));
   for (auto* b : {&S->total, &S->ll, &S->log_w, &S->comb, &S->w}) FC_CUDA(b->reserve(N));
   FC_CUDA(S->scratch.reserve(2 * RDB + 16));
-  FC_CUDA(S->idx.reserve(N)); FC_CUDA(S->n_accept.reserve(N)); FC_CUDA(S->bis.reserve(1)); FC_CUDA(S->tri.reserve(RDB));
+  FC_CUDA(S->idx.reserve(N)); FC_CUDA(S->n_accept.reserve(N)); FC_CUDA(S->bis.reserve(1)); FC_CUDA(S->tri.reserve(RDB + 1));
   FC_CUDA(cudaMemsetAsync(S->n_accept.p, 0, N * 8, st));
   S->rw = resample_work_new();
   FC_TRY(S->eng.init(p, N, true, seed ^ 0x5bd1e995u, first_particle));
@@ -690,6 +700,148 @@ int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t ste
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 1;
   FC_CUDA(cudaStreamSynchronize(P->stream));
+  return FC_OK;
+}
+
+// ---- one shard of a multi-GPU tempered SMC. The per-rank device steps; the few
+// scalars between them travel through torch.distributed / NCCL in fugue_b200/dist.py. ----
+
+// this session holds particles [first, first + n) of a population of n_total: uniform weight 1/n_total
+int32_t fc_smc_shard_begin(fc_smc_session* s, uint64_t n_total) {
+  using namespace fc;
+  if (!s || n_total < (uint64_t)s->n) { set_error("bad shard arguments"); return FC_ERR_INVALID_ARGUMENT; }
+  s->n_global = (double)n_total;
+  return FC_OK;
+}
+
+// (max, sum exp(lv - max), sum exp(2 (lv - max))) of lv_i = log_w_i + d_beta * ll_i over this shard:
+// the three numbers ess_at(beta + d_beta) and the reweight log-sum-exp need (smc.rs:589-602,
+// 512-518); shards merge them exactly like the per-CTA partials of the single-GPU kernel.
+int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3) {
+  using namespace fc;
+  if (!s || !out3) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  cudaStream_t st = s->P->stream;
+  const int64_t n = s->n;
+  const double lwc = -std::log(s->n_global > 0.0 ? s->n_global : (double)n);
+  const double* lw = s->log_w_uniform ? nullptr : s->log_w.p;
+  const int nb = nb_blocks(n);
+  FC_CUDA(cudaMemsetAsync(&s->bis.p->counter, 0, sizeof(unsigned), st));
+  k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, s->ll.p, s->bis.p, s->tri.p, n, 1, 0, d_beta);
+  FC_KERNEL_CHECK();
+  s->P->n_kernel_launches += 1;
+  Tri t;
+  FC_CUDA(cudaMemcpyAsync(&t, s->tri.p + nb, sizeof(Tri), cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  out3[0] = t.m; out3[1] = t.s1; out3[2] = t.s2;
+  return FC_OK;
+}
+
+// reweight with the GLOBAL normaliser (smc.rs:512-531): log_w = (log_w + d_beta ll) - log_norm,
+// w = exp(log_w); advances beta / evidence / step count of the shard.
+int32_t fc_smc_shard_reweight(fc_smc_session* s, double beta_new, double log_norm) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  cudaStream_t st = s->P->stream;
+  const int64_t n = s->n;
+  const double n_unif = s->n_global > 0.0 ? s->n_global : (double)n;
+  const double lwc = -std::log(n_unif);
+  const double* lw = s->log_w_uniform ? nullptr : s->log_w.p;
+  const double d_beta = beta_new - s->beta;
+  FC_CUDA(cudaMemcpyAsync(&s->bis.p->lse1, &log_norm, 8, cudaMemcpyHostToDevice, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, s->ll.p, d_beta, s->bis.p, s->comb.p, s->w.p, n, n_unif);
+  FC_KERNEL_CHECK();
+  s->P->n_kernel_launches += 1;
+  std::swap(s->log_w.p, s->comb.p); std::swap(s->log_w.n, s->comb.n);
+  s->log_w_uniform = false;
+  s->log_evidence += log_norm;
+  s->beta = beta_new;
+  s->steps += 1;
+  if (s->beta >= 1.0) s->finished = true;
+  return FC_OK;
+}
+
+// exact running sum of this shard's weights from the carry-in of the ranks before it
+int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value) {
+  using namespace fc;
+  if (!s || !end_value) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  return shard_scan(s->w.p, s->n, carry_in, *s->rw, s->P->stream, &s->P->n_kernel_launches, end_value);
+}
+
+// the offspring of global output slots [jlo, jhi) (ancestors on this shard, after fc_smc_shard_scan),
+// packed plane-major for migration: d_f64 [(d_cont + 3)][cnt] (values, then the three accumulators),
+// d_i32 [d_disc][cnt]. h_idx (cnt local ancestor indices) may be NULL.
+int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo, uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx) {
+  using namespace fc;
+  if (!s || jhi < jlo) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
+  fc_program* P = s->P;
+  FC_CUDA(cudaSetDevice(P->device));
+  cudaStream_t st = P->stream;
+  const int64_t n = s->n, cnt = (int64_t)(jhi - jlo);
+  if (cnt == 0) return FC_OK;
+  if (cnt > n) FC_CUDA(s->idx.reserve(cnt));
+  FC_TRY(shard_ancestors(*s->rw, n, (double)n_total, u_raw, (int64_t)jlo, cnt, s->idx.p, st));
+  dim3 gg((unsigned)cdiv(cnt, 256), 1);
+  if (P->d_cont && d_f64) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, d_f64, s->idx.p, P->d_cont, n, cnt); }
+  if (d_f64) { gg.y = 3; k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, d_f64 + P->d_cont * cnt, s->idx.p, 3, n, cnt); }
+  if (P->d_disc && d_i32) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, d_i32, s->idx.p, P->d_disc, n, cnt); }
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 4;
+  if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, s->idx.p, cnt * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  return FC_OK;
+}
+
+// install `cnt` migrated particles (one source rank's chunk, packed as fc_smc_shard_offspring packs
+// them) at local positions [offset, offset + cnt). After the last chunk call fc_smc_shard_resampled.
+int32_t fc_smc_shard_install(fc_smc_session* s, uint64_t offset, uint64_t cnt, const double* d_f64, const int32_t* d_i32) {
+  using namespace fc;
+  if (!s || offset + cnt > (uint64_t)s->n) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
+  fc_program* P = s->P;
+  FC_CUDA(cudaSetDevice(P->device));
+  cudaStream_t st = P->stream;
+  const int64_t n = s->n;
+  if (cnt == 0) return FC_OK;
+  // the new population is assembled in the double buffers and swapped in by fc_smc_shard_resampled
+  if (P->d_cont) FC_CUDA(cudaMemcpy2DAsync(s->q2.p + offset, n * 8, d_f64, cnt * 8, cnt * 8, P->d_cont, cudaMemcpyDeviceToDevice, st));
+  FC_CUDA(cudaMemcpy2DAsync(s->lp3b.p + offset, n * 8, d_f64 + P->d_cont * cnt, cnt * 8, cnt * 8, 3, cudaMemcpyDeviceToDevice, st));
+  if (P->d_disc) FC_CUDA(cudaMemcpy2DAsync(s->qd2.p + offset, n * 4, d_i32, cnt * 4, cnt * 4, P->d_disc, cudaMemcpyDeviceToDevice, st));
+  return FC_OK;
+}
+
+// this shard's log weights as they are (normalised by the GLOBAL log-sum-exp after a reweight) and
+// the weights exp(log_w) the resampler sees (valid after fc_smc_shard_reweight) -> host; either may be NULL
+int32_t fc_smc_shard_weights(fc_smc_session* s, double* h_log_w, double* h_w) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  if (h_log_w) {
+    FC_TRY(smc_materialise_log_w(s));
+    FC_CUDA(cudaMemcpyAsync(h_log_w, s->log_w.p, s->n * 8, cudaMemcpyDeviceToHost, s->P->stream));
+  }
+  if (h_w) FC_CUDA(cudaMemcpyAsync(h_w, s->w.p, s->n * 8, cudaMemcpyDeviceToHost, s->P->stream));
+  FC_CUDA(cudaStreamSynchronize(s->P->stream));
+  return FC_OK;
+}
+
+// the migrated population replaces the old one; weights are uniform 1/n_total again (smc.rs:538-541)
+int32_t fc_smc_shard_resampled(fc_smc_session* s) {
+  using namespace fc;
+  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  fc_program* P = s->P;
+  FC_CUDA(cudaSetDevice(P->device));
+  cudaStream_t st = P->stream;
+  std::swap(s->q.p, s->q2.p); std::swap(s->q.n, s->q2.n);
+  std::swap(s->qd.p, s->qd2.p); std::swap(s->qd.n, s->qd2.n);
+  std::swap(s->lp3.p, s->lp3b.p); std::swap(s->lp3.n, s->lp3b.n);
+  k_loglik<<<(unsigned)cdiv(s->n, 256), 256, 0, st>>>(s->lp3.p, s->ll.p, s->n);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
+  s->log_w_uniform = true;
+  FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;
 }
 

@@ -247,3 +247,218 @@ def plan_global_systematic(carry_in, end_value, n_local, u_raw):
     if u_raw == 0.0 and n_total > 0:  # threshold_0 == 0: `cum < thr` fails at once, i = 0, (i-1) wraps to n-1
         ranges = [(max(a, 1), max(b, 1)) if r == 0 else (a, b) for r, (a, b) in enumerate(ranges)]
     return ranges[rank], migration_plan(ranges, bounds), bounds
+
+
+# ---------------------------------------------------------------------------------------------
+# 4. adaptive_smc over all ranks (smc.rs:455-581): particles sharded rank-major, every exchange
+#    step of the ladder as a collective. Device work per rank: the fc_smc_shard_* entry points.
+# ---------------------------------------------------------------------------------------------
+def _merge_tri(tris):
+    """Fold per-rank (max, sum e, sum e^2) triples in rank order -- the same merge the single-GPU
+    kernel applies to its per-CTA partials (fc_smc.cu tri_merge)."""
+    m, s1, s2 = -math.inf, 0.0, 0.0
+    for bm, b1, b2 in tris:
+        if bm == -math.inf and b1 == 0.0:
+            continue
+        if m == -math.inf and s1 == 0.0:
+            m, s1, s2 = bm, b1, b2
+            continue
+        mm = max(m, bm)
+        fa = 1.0 if m == mm else math.exp(m - mm)
+        fb = 1.0 if bm == mm else math.exp(bm - mm)
+        s1, s2, m = s1 * fa + b1 * fb, s2 * fa * fa + b2 * fb * fb, mm
+    return m, s1, s2
+
+
+def _lse_pair(tri):
+    m, s1, s2 = tri
+    ninf = -math.inf
+    if m != m or s1 != s1:
+        return math.nan, math.nan
+    lse1 = ninf if s1 == 0.0 else m + math.log(s1)
+    lse2 = ninf if s2 == 0.0 else 2.0 * m + math.log(s2)
+    return lse1, lse2
+
+
+class ShardedSmc:
+    """One rank's shard of a population of `num_particles` (rank-major, contiguous). Particle j of
+    the global population uses the same random stream on any world size (first_particle offsets)."""
+
+    def __init__(self, model, num_particles, config=None, seed=0):
+        from . import api
+        self.api = api
+        self.rank, self.ws = world()
+        self.n_total = int(num_particles)
+        self.lo, self.hi = shard_range(self.n_total, self.rank, self.ws)
+        self.n = self.hi - self.lo
+        self.config = config or api.SMCConfig()
+        self.seed = int(seed)
+        self.S = api.SmcSession(model, self.n, self.config, seed, first_particle=self.lo)
+        api.check(api.lib.fc_smc_shard_begin(self.S.h, self.n_total))
+        self.P = self.S.program
+        self.beta, self.log_evidence, self.steps = 0.0, 0.0, 0
+        self.bounds = [shard_range(self.n_total, r, self.ws)[0] for r in range(self.ws)] + [self.n_total]
+        self.migrated = 0  # particles that crossed ranks (all resamples)
+
+    def close(self):
+        self.S.close()
+
+    # -- global (max, s1, s2) of lv = log_w + d_beta * ll: one all-gather of 3 doubles --
+    def _tri(self, d_beta):
+        import ctypes as C
+        out = (C.c_double * 3)()
+        self.api.check(self.api.lib.fc_smc_shard_tri(self.S.h, float(d_beta), out))
+        return _merge_tri([tuple(t) for t in all_gather_np(np.array(list(out)))])
+
+    def _ess_at(self, b):
+        lse1, lse2 = _lse_pair(self._tri(b - self.beta))
+        if not (math.isfinite(lse1) and math.isfinite(lse2)):
+            return float(self.n_total)
+        return math.exp(2.0 * lse1 - lse2)
+
+    def next_beta(self, target_ess):
+        """next_beta (smc.rs:588-622) on the global population."""
+        if self._ess_at(1.0) >= target_ess:
+            return 1.0
+        lo, hi = self.beta, 1.0
+        for _ in range(64):
+            mid = 0.5 * (lo + hi)
+            if mid == lo or mid == hi:  # fixed point of the remaining iterations
+                break
+            if self._ess_at(mid) < target_ess:
+                hi = mid
+            else:
+                lo = mid
+        return min(max(hi, self.beta + 1e-9), 1.0)
+
+    def _uniform(self):
+        """The one uniform of a systematic resample, identical on every rank (keyed by seed, step)."""
+        return float(np.random.Generator(np.random.Philox(key=[self.seed & (2**64 - 1), 0x5EED0000 + self.steps])).random())
+
+    def resample_global(self, u_raw=None):
+        """Global systematic resample (smc.rs:255-272 over the rank-major population): exact carry
+        chain, slot ranges, ancestor search on each rank, all-to-all migration. Returns this rank's
+        (global slot range, local ancestor indices) for inspection."""
+        import ctypes as C
+        api, lib, S = self.api, self.api.lib, self.S
+        if u_raw is None:
+            u_raw = self._uniform()
+
+        def scan(carry):
+            e = C.c_double()
+            api.check(lib.fc_smc_shard_scan(S.h, float(carry), C.byref(e)))
+            return e.value
+
+        carry, ends = chain_carries(scan)
+        (jlo, jhi), counts, bounds = plan_global_systematic(carry, ends[self.rank], self.n, u_raw)
+        cnt = jhi - jlo
+        dc, dd = self.P.d_cont, self.P.d_disc
+        dev = torch.device("cuda", torch.cuda.current_device())
+        f64 = torch.empty(((dc + 3), max(cnt, 1)), dtype=torch.float64, device=dev)
+        i32 = torch.empty((max(dd, 1), max(cnt, 1)), dtype=torch.int32, device=dev)
+        idx = np.zeros(max(cnt, 1), dtype=np.uint64)
+        api.check(lib.fc_smc_shard_offspring(S.h, self.n_total, float(u_raw), jlo, jhi, C.c_void_p(f64.data_ptr()), C.c_void_p(i32.data_ptr()),
+                                             idx.ctypes.data_as(C.c_void_p)))
+        # per-destination column ranges of my offspring (slots are rank-major, so they are contiguous)
+        send_f, send_i, col = [], [], 0
+        for t in range(self.ws):
+            c = int(counts[self.rank][t])
+            send_f.append(f64[:, col:col + c].contiguous().reshape(-1))
+            send_i.append(i32[:dd, col:col + c].contiguous().reshape(-1))
+            col += c
+        recv_counts = [int(counts[s][self.rank]) for s in range(self.ws)]
+        recv_f = [torch.empty((dc + 3) * c, dtype=torch.float64, device=dev) for c in recv_counts]
+        recv_i = [torch.empty(dd * c, dtype=torch.int32, device=dev) for c in recv_counts]
+        self._all_to_all(recv_f, send_f)
+        if dd:
+            self._all_to_all(recv_i, send_i)
+        off = 0
+        for s_rank, c in enumerate(recv_counts):
+            if c:
+                api.check(lib.fc_smc_shard_install(S.h, off, c, C.c_void_p(recv_f[s_rank].data_ptr()),
+                                                   C.c_void_p(recv_i[s_rank].data_ptr()) if dd else None))
+            off += c
+        assert off == self.n, (off, self.n)
+        torch.cuda.synchronize()
+        api.check(lib.fc_smc_shard_resampled(S.h))
+        self.migrated += sum(c for s_rank, c in enumerate(recv_counts) if s_rank != self.rank)
+        return (jlo, jhi), idx[:cnt]
+
+    def _all_to_all(self, recv, send):
+        if self.ws == 1:
+            recv[0].copy_(send[0])
+            return
+        if dist.get_backend() == "nccl":
+            dist.all_to_all(recv, send)
+            return
+        # gloo (CPU tests on one GPU): stage through host tensors with point-to-point exchanges
+        for src in range(self.ws):
+            for dst in range(self.ws):
+                if src == dst == self.rank:
+                    recv[src].copy_(send[dst])
+                elif src == self.rank:
+                    dist.send(send[dst].cpu(), dst)
+                elif dst == self.rank:
+                    buf = torch.empty(recv[src].shape, dtype=recv[src].dtype)
+                    dist.recv(buf, src)
+                    recv[src].copy_(buf)
+
+    def step(self):
+        """One pass of the tempering loop (smc.rs:499-560) on the global population."""
+        api, lib, S = self.api, self.api.lib, self.S
+        n = self.n_total
+        target = min(max(self.config.ess_threshold * n, 1.0), float(n))
+        self.steps += 1
+        beta_new = self.next_beta(target)
+        if self.steps >= 10000:
+            beta_new = 1.0
+        lse1, _ = _lse_pair(self._tri(beta_new - self.beta))
+        log_norm = lse1
+        self.log_evidence += log_norm
+        api.check(lib.fc_smc_shard_reweight(S.h, float(beta_new), float(log_norm)))
+        self.beta = beta_new
+        if self.beta < 1.0:
+            self.resample_global()
+            if self.config.rejuvenation_steps:
+                S.rejuvenate_particles(self.beta, self.config.rejuvenation_steps)
+        return self.beta
+
+    def result(self):
+        """This rank's shard of SMCResult: values, normalised global weights, log-evidence."""
+        import ctypes as C
+        api, lib, S, P = self.api, self.api.lib, self.S, self.P
+        v = np.zeros((P.d_cont, self.n))
+        dv = np.zeros((P.d_disc, self.n), dtype=np.int64)
+        api.check(lib.fc_smc_get(S.h, api._ptr(v), api._ptr(dv), None, None, None, None))
+        lw = np.zeros(self.n)
+        api.check(lib.fc_smc_shard_weights(S.h, api._ptr(lw), None))
+        m = all_reduce_np(np.array([lw.max() if self.n else -math.inf]), op="max")[0]
+        log_norm = global_log_sum_exp(m, lambda gm: float(np.exp(lw - gm).sum()))
+        if math.isfinite(log_norm):
+            lwn = lw - log_norm
+            w = np.exp(lwn)
+        else:
+            lwn = np.full(self.n, -math.log(self.n_total))
+            w = np.full(self.n, 1.0 / self.n_total)
+        return self.api.SMCResult(v, dv, w, lwn, self.log_evidence, self.steps, list(P.sites))
+
+
+def adaptive_smc_sharded(model, num_particles, config=None, seed=0):
+    """adaptive_smc (smc.rs:455-581) with the population sharded over all ranks; every rank returns
+    its shard of the result (the log-evidence is global). rejuvenation_steps == 0 degenerates to the
+    single importance-sampling reweight (smc.rs:484-493), which needs only the global log-sum-exp."""
+    from . import api
+    cfg = config or api.SMCConfig()
+    sm = ShardedSmc(model, num_particles, cfg, seed)
+    if cfg.rejuvenation_steps == 0:
+        lse1, _ = _lse_pair(sm._tri(1.0))
+        sm.log_evidence = lse1
+        api.check(api.lib.fc_smc_shard_reweight(sm.S.h, 1.0, 0.0))  # log_w = -ln N + ll (smc.rs:490-493), normalised in result()
+        sm.beta, sm.steps = 1.0, 1
+    else:
+        while sm.step() < 1.0:
+            pass
+    r = sm.result()
+    r.migrated = sm.migrated
+    sm.close()
+    return r

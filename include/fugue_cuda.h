@@ -276,6 +276,30 @@ int32_t fc_smc_normalize(fc_smc_session* s, double* log_norm, double* ess);
 int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const double* h_uniforms,
                                   uint64_t* h_idx);
 int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t steps);
+/* One shard of a multi-GPU tempered SMC (particles sharded rank-major). The exchange
+ * steps -- the global weight log-sum-exp, the exact rank-to-rank running-sum carry and the particle
+ * migration of a global systematic resample (smc.rs:255-272, 499-560) -- are collectives in
+ * fugue_b200/dist.py; these are the per-rank device steps between them:
+ *   shard_begin      this session holds n of n_total particles (uniform weight 1/n_total)
+ *   shard_tri        out3 = (max, sum e, sum e^2) of lv = log_w + d_beta*ll, e = exp(lv - max)
+ *   shard_reweight   log_w = lv - log_norm (the GLOBAL normaliser), w = exp(log_w); beta := beta_new
+ *   shard_scan       exact sequentially-rounded running sum of w continuing from carry_in
+ *   shard_offspring  ancestors of global slots [jlo, jhi) (thresholds u/N + j/N) packed plane-major:
+ *                    d_f64 [(d_cont+3)][cnt] (values + the three accumulators), d_i32 [d_disc][cnt]
+ *   shard_install    place one source rank's chunk at local positions [offset, offset+cnt)
+ *   shard_resampled  swap the migrated population in; weights uniform again
+ *   shard_weights    the shard's log weights as they are (normalised by the GLOBAL log-sum-exp)
+ *                    and the weights exp(log_w) the resampler sees; either pointer may be NULL */
+int32_t fc_smc_shard_begin(fc_smc_session* s, uint64_t n_total);
+int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3);
+int32_t fc_smc_shard_reweight(fc_smc_session* s, double beta_new, double log_norm);
+int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value);
+int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo,
+                               uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx);
+int32_t fc_smc_shard_install(fc_smc_session* s, uint64_t offset, uint64_t cnt, const double* d_f64,
+                             const int32_t* d_i32);
+int32_t fc_smc_shard_resampled(fc_smc_session* s);
+int32_t fc_smc_shard_weights(fc_smc_session* s, double* h_log_w, double* h_w);
 /* next_beta (smc.rs:588-622) on host arrays: the largest beta' in (beta, 1] whose incremental
  * weights log_w + (beta' - beta) * ll keep ESS >= target_ess (64-step bisection; 1.0 if a full
  * jump already does). Parity probe for the tempering ladder. */
