@@ -372,6 +372,8 @@ class ShardedSmc:
         self._all_to_all(recv_f, send_f)
         if dd:
             self._all_to_all(recv_i, send_i)
+        # NCCL enqueues on torch's streams; the library installs on the program's own stream
+        torch.cuda.synchronize()
         off = 0
         for s_rank, c in enumerate(recv_counts):
             if c:
@@ -423,13 +425,14 @@ class ShardedSmc:
                 S.rejuvenate_particles(self.beta, self.config.rejuvenation_steps)
         return self.beta
 
-    def result(self):
+    def result(self, values=True):
         """This rank's shard of SMCResult: values, normalised global weights, log-evidence."""
         import ctypes as C
         api, lib, S, P = self.api, self.api.lib, self.S, self.P
-        v = np.zeros((P.d_cont, self.n))
-        dv = np.zeros((P.d_disc, self.n), dtype=np.int64)
-        api.check(lib.fc_smc_get(S.h, api._ptr(v), api._ptr(dv), None, None, None, None))
+        v = np.zeros((P.d_cont, self.n)) if values else None
+        dv = np.zeros((P.d_disc, self.n), dtype=np.int64) if values else None
+        if values:
+            api.check(lib.fc_smc_get(S.h, api._ptr(v), api._ptr(dv), None, None, None, None))
         lw = np.zeros(self.n)
         api.check(lib.fc_smc_shard_weights(S.h, api._ptr(lw), None))
         m = all_reduce_np(np.array([lw.max() if self.n else -math.inf]), op="max")[0]
@@ -443,7 +446,7 @@ class ShardedSmc:
         return self.api.SMCResult(v, dv, w, lwn, self.log_evidence, self.steps, list(P.sites))
 
 
-def adaptive_smc_sharded(model, num_particles, config=None, seed=0):
+def adaptive_smc_sharded(model, num_particles, config=None, seed=0, values=True):
     """adaptive_smc (smc.rs:455-581) with the population sharded over all ranks; every rank returns
     its shard of the result (the log-evidence is global). rejuvenation_steps == 0 degenerates to the
     single importance-sampling reweight (smc.rs:484-493), which needs only the global log-sum-exp."""
@@ -458,7 +461,7 @@ def adaptive_smc_sharded(model, num_particles, config=None, seed=0):
     else:
         while sm.step() < 1.0:
             pass
-    r = sm.result()
+    r = sm.result(values)
     r.migrated = sm.migrated
     sm.close()
     return r
