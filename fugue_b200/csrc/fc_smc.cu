@@ -311,12 +311,12 @@ __global__ void k_reweight(const double* __restrict__ log_w, double lw_const, co
 
 // gather particle planes by ancestor index (resample_particles, smc.rs:326-349)
 template <class T>
-__global__ void __launch_bounds__(256) k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P, int64_t n_out = -1) {
+__global__ void __launch_bounds__(256) k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P, int64_t n_out = -1, int64_t dst_stride = 0) {
   int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n_out >= 0) {  // n_out offspring packed plane-major with stride n_out (sharded resampling)
+  if (n_out >= 0) {  // n_out offspring written plane-major with stride dst_stride (sharded resampling)
     if (j >= n_out) return;
     const int64_t a2 = (int64_t)idx[j];
-    for (int64_t r = (int64_t)blockIdx.y; r < rows; r += gridDim.y) dst[r * n_out + j] = src[r * P + a2];
+    for (int64_t r = (int64_t)blockIdx.y; r < rows; r += gridDim.y) dst[r * dst_stride + j] = src[r * P + a2];
     return;
   }
   if (j >= P) return;
@@ -359,6 +359,7 @@ struct fc_smc_session {
   uint64_t steps = 0, moves = 0;
   bool finished = false;
   double n_global = 0.0;  // population size the uniform weight refers to (0: this session's own n)
+  bool shard_prepass_ok = false, shard_ll_bad = false;  // max(ll) / bad flag in `bis` describe the current ll (fc_smc_shard_tri)
 };
 
 namespace fc {
@@ -678,6 +679,7 @@ int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const doubl
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 5;
   s->log_w_uniform = true;
+  s->shard_prepass_ok = false;
   if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, s->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;
@@ -699,6 +701,7 @@ int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t ste
   k_loglik<<<(unsigned)cdiv(s->n, 256), 256, 0, P->stream>>>(s->lp3.p, s->ll.p, s->n);
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 1;
+  s->shard_prepass_ok = false;
   FC_CUDA(cudaStreamSynchronize(P->stream));
   return FC_OK;
 }
@@ -727,7 +730,30 @@ int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3) {
   const double* lw = s->log_w_uniform ? nullptr : s->log_w.p;
   const int nb = nb_blocks(n);
   FC_CUDA(cudaMemsetAsync(&s->bis.p->counter, 0, sizeof(unsigned), st));
-  k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, s->ll.p, s->bis.p, s->tri.p, n, 1, 0, d_beta);
+  if (!lw) {
+    // uniform log_w (the state every next_beta search runs in): single-stream pass, the shift is
+    // lwc + d_beta * max(ll) from a pre-pass that is redone only when ll has changed
+    if (!s->shard_prepass_ok) {
+      Bisect hb;
+      std::memset(&hb, 0, sizeof(hb));
+      hb.n = s->n_global > 0.0 ? s->n_global : (double)n;
+      FC_CUDA(cudaMemcpyAsync(s->bis.p, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
+      k_nb_prepass<<<nb, NB_THREADS, 0, st>>>(s->ll.p, n, s->bis.p, (double*)s->tri.p);
+      FC_KERNEL_CHECK();
+      FC_CUDA(cudaMemcpyAsync(&hb, s->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+      FC_CUDA(cudaStreamSynchronize(st));
+      s->shard_ll_bad = hb.bad != 0;
+      s->shard_prepass_ok = true;
+      s->P->n_kernel_launches += 1;
+    }
+    if (s->shard_ll_bad) {  // some ll is NaN / +inf: every log-sum-exp is non-finite (smc.rs:595-601)
+      out3[0] = out3[1] = out3[2] = __builtin_nan("");
+      return FC_OK;
+    }
+    k_nb_eval_uni<<<nb, NB_THREADS, 0, st>>>(lwc, s->ll.p, s->bis.p, s->tri.p, n, 1, 0, d_beta);
+  } else {
+    k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, s->ll.p, s->bis.p, s->tri.p, n, 1, 0, d_beta);
+  }
   FC_KERNEL_CHECK();
   s->P->n_kernel_launches += 1;
   Tri t;
@@ -773,8 +799,10 @@ int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value)
 
 // the offspring of global output slots [jlo, jhi) (ancestors on this shard, after fc_smc_shard_scan),
 // packed plane-major for migration: d_f64 [(d_cont + 3)][cnt] (values, then the three accumulators),
-// d_i32 [d_disc][cnt]. h_idx (cnt local ancestor indices) may be NULL.
-int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo, uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx) {
+// d_i32 [d_disc][cnt]. With d_f64 == d_i32 == NULL the offspring stay on this rank and are written
+// straight to local positions [local_offset, local_offset + cnt) of the new population.
+// h_idx (cnt local ancestor indices) may be NULL.
+int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo, uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx, uint64_t local_offset) {
   using namespace fc;
   if (!s || jhi < jlo) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
   fc_program* P = s->P;
@@ -785,9 +813,19 @@ int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw
   if (cnt > n) FC_CUDA(s->idx.reserve(cnt));
   FC_TRY(shard_ancestors(*s->rw, n, (double)n_total, u_raw, (int64_t)jlo, cnt, s->idx.p, st));
   dim3 gg((unsigned)cdiv(cnt, 256), 1);
-  if (P->d_cont && d_f64) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, d_f64, s->idx.p, P->d_cont, n, cnt); }
-  if (d_f64) { gg.y = 3; k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, d_f64 + P->d_cont * cnt, s->idx.p, 3, n, cnt); }
-  if (P->d_disc && d_i32) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, d_i32, s->idx.p, P->d_disc, n, cnt); }
+  if (!d_f64 && !d_i32) {
+    // offspring that stay on this rank: straight into the double buffers at their final position
+    // (global slot jlo is local position jlo - first slot of this rank = local_offset)
+    const int64_t off = (int64_t)local_offset;
+    if (off < 0 || off + cnt > n) { set_error("local offspring out of range"); return FC_ERR_INVALID_ARGUMENT; }
+    if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, s->q2.p + off, s->idx.p, P->d_cont, n, cnt, n); }
+    gg.y = 3; k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, s->lp3b.p + off, s->idx.p, 3, n, cnt, n);
+    if (P->d_disc) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, s->qd2.p + off, s->idx.p, P->d_disc, n, cnt, n); }
+  } else {
+    if (P->d_cont && d_f64) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, d_f64, s->idx.p, P->d_cont, n, cnt, cnt); }
+    if (d_f64) { gg.y = 3; k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, d_f64 + P->d_cont * cnt, s->idx.p, 3, n, cnt, cnt); }
+    if (P->d_disc && d_i32) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, d_i32, s->idx.p, P->d_disc, n, cnt, cnt); }
+  }
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 4;
   if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, s->idx.p, cnt * 8, cudaMemcpyDeviceToHost, st));
@@ -841,6 +879,7 @@ int32_t fc_smc_shard_resampled(fc_smc_session* s) {
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 1;
   s->log_w_uniform = true;
+  s->shard_prepass_ok = false;
   FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;
 }

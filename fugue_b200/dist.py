@@ -299,6 +299,7 @@ class ShardedSmc:
         self.beta, self.log_evidence, self.steps = 0.0, 0.0, 0
         self.bounds = [shard_range(self.n_total, r, self.ws)[0] for r in range(self.ws)] + [self.n_total]
         self.migrated = 0  # particles that crossed ranks (all resamples)
+        self.timers = {"next_beta": 0.0, "reweight": 0.0, "resample": 0.0, "rejuvenate": 0.0}  # host wall-clock per phase
 
     def close(self):
         self.S.close()
@@ -335,10 +336,10 @@ class ShardedSmc:
         """The one uniform of a systematic resample, identical on every rank (keyed by seed, step)."""
         return float(np.random.Generator(np.random.Philox(key=[self.seed & (2**64 - 1), 0x5EED0000 + self.steps])).random())
 
-    def resample_global(self, u_raw=None):
+    def resample_global(self, u_raw=None, return_idx=False):
         """Global systematic resample (smc.rs:255-272 over the rank-major population): exact carry
         chain, slot ranges, ancestor search on each rank, all-to-all migration. Returns this rank's
-        (global slot range, local ancestor indices) for inspection."""
+        global slot range and, with return_idx (tests), the local ancestor indices."""
         import ctypes as C
         api, lib, S = self.api, self.api.lib, self.S
         if u_raw is None:
@@ -354,29 +355,39 @@ class ShardedSmc:
         cnt = jhi - jlo
         dc, dd = self.P.d_cont, self.P.d_disc
         dev = torch.device("cuda", torch.cuda.current_device())
-        f64 = torch.empty(((dc + 3), max(cnt, 1)), dtype=torch.float64, device=dev)
-        i32 = torch.empty((max(dd, 1), max(cnt, 1)), dtype=torch.int32, device=dev)
-        idx = np.zeros(max(cnt, 1), dtype=np.uint64)
-        api.check(lib.fc_smc_shard_offspring(S.h, self.n_total, float(u_raw), jlo, jhi, C.c_void_p(f64.data_ptr()), C.c_void_p(i32.data_ptr()),
-                                             idx.ctypes.data_as(C.c_void_p)))
-        # per-destination column ranges of my offspring (slots are rank-major, so they are contiguous)
+        idx = np.zeros(max(cnt, 1) if return_idx else 1, dtype=np.uint64)
+        # my offspring per destination rank (slots are rank-major, so each destination's are contiguous).
+        # Those that stay here go straight to their final local position; only the others are packed.
         send_f, send_i, col = [], [], 0
         for t in range(self.ws):
             c = int(counts[self.rank][t])
-            send_f.append(f64[:, col:col + c].contiguous().reshape(-1))
-            send_i.append(i32[:dd, col:col + c].contiguous().reshape(-1))
+            a, b = jlo + col, jlo + col + c
+            hp = idx[col:col + c].ctypes.data_as(C.c_void_p) if (c and return_idx) else None
+            if t == self.rank or c == 0:
+                if c:
+                    api.check(lib.fc_smc_shard_offspring(S.h, self.n_total, float(u_raw), a, b, None, None, hp, a - int(bounds[self.rank])))
+                send_f.append(torch.empty(0, dtype=torch.float64, device=dev))
+                send_i.append(torch.empty(0, dtype=torch.int32, device=dev))
+            else:
+                f64 = torch.empty((dc + 3) * c, dtype=torch.float64, device=dev)
+                i32 = torch.empty(max(dd, 1) * c, dtype=torch.int32, device=dev)
+                api.check(lib.fc_smc_shard_offspring(S.h, self.n_total, float(u_raw), a, b, C.c_void_p(f64.data_ptr()), C.c_void_p(i32.data_ptr()), hp, 0))
+                send_f.append(f64)
+                send_i.append(i32[:dd * c])
             col += c
         recv_counts = [int(counts[s][self.rank]) for s in range(self.ws)]
-        recv_f = [torch.empty((dc + 3) * c, dtype=torch.float64, device=dev) for c in recv_counts]
-        recv_i = [torch.empty(dd * c, dtype=torch.int32, device=dev) for c in recv_counts]
-        self._all_to_all(recv_f, send_f)
-        if dd:
-            self._all_to_all(recv_i, send_i)
+        wire = [0 if s == self.rank else c for s, c in enumerate(recv_counts)]
+        recv_f = [torch.empty((dc + 3) * c, dtype=torch.float64, device=dev) for c in wire]
+        recv_i = [torch.empty(dd * c, dtype=torch.int32, device=dev) for c in wire]
+        if self.ws > 1:
+            self._all_to_all(recv_f, send_f)
+            if dd:
+                self._all_to_all(recv_i, send_i)
         # NCCL enqueues on torch's streams; the library installs on the program's own stream
         torch.cuda.synchronize()
         off = 0
         for s_rank, c in enumerate(recv_counts):
-            if c:
+            if c and s_rank != self.rank:
                 api.check(lib.fc_smc_shard_install(S.h, off, c, C.c_void_p(recv_f[s_rank].data_ptr()),
                                                    C.c_void_p(recv_i[s_rank].data_ptr()) if dd else None))
             off += c
@@ -384,7 +395,7 @@ class ShardedSmc:
         torch.cuda.synchronize()
         api.check(lib.fc_smc_shard_resampled(S.h))
         self.migrated += sum(c for s_rank, c in enumerate(recv_counts) if s_rank != self.rank)
-        return (jlo, jhi), idx[:cnt]
+        return (jlo, jhi), (idx[:cnt] if return_idx else None)
 
     def _all_to_all(self, recv, send):
         if self.ws == 1:
@@ -399,8 +410,9 @@ class ShardedSmc:
                 if src == dst == self.rank:
                     recv[src].copy_(send[dst])
                 elif src == self.rank:
-                    dist.send(send[dst].cpu(), dst)
-                elif dst == self.rank:
+                    if send[dst].numel():
+                        dist.send(send[dst].cpu(), dst)
+                elif dst == self.rank and recv[src].numel():
                     buf = torch.empty(recv[src].shape, dtype=recv[src].dtype)
                     dist.recv(buf, src)
                     recv[src].copy_(buf)
@@ -410,19 +422,28 @@ class ShardedSmc:
         api, lib, S = self.api, self.api.lib, self.S
         n = self.n_total
         target = min(max(self.config.ess_threshold * n, 1.0), float(n))
+        import time
         self.steps += 1
+        t0 = time.perf_counter()
         beta_new = self.next_beta(target)
         if self.steps >= 10000:
             beta_new = 1.0
+        t1 = time.perf_counter()
         lse1, _ = _lse_pair(self._tri(beta_new - self.beta))
         log_norm = lse1
         self.log_evidence += log_norm
         api.check(lib.fc_smc_shard_reweight(S.h, float(beta_new), float(log_norm)))
         self.beta = beta_new
+        t2 = time.perf_counter()
+        t3 = t4 = t2
         if self.beta < 1.0:
             self.resample_global()
+            t3 = time.perf_counter()
             if self.config.rejuvenation_steps:
                 S.rejuvenate_particles(self.beta, self.config.rejuvenation_steps)
+            t4 = time.perf_counter()
+        for k, v in (("next_beta", t1 - t0), ("reweight", t2 - t1), ("resample", t3 - t2), ("rejuvenate", t4 - t3)):
+            self.timers[k] += v
         return self.beta
 
     def result(self, values=True):
@@ -435,8 +456,7 @@ class ShardedSmc:
             api.check(lib.fc_smc_get(S.h, api._ptr(v), api._ptr(dv), None, None, None, None))
         lw = np.zeros(self.n)
         api.check(lib.fc_smc_shard_weights(S.h, api._ptr(lw), None))
-        m = all_reduce_np(np.array([lw.max() if self.n else -math.inf]), op="max")[0]
-        log_norm = global_log_sum_exp(m, lambda gm: float(np.exp(lw - gm).sum()))
+        log_norm, _ = _lse_pair(self._tri(0.0))  # final normalisation (smc.rs:565-575): device reduction + one all-gather
         if math.isfinite(log_norm):
             lwn = lw - log_norm
             w = np.exp(lwn)

@@ -285,7 +285,8 @@ int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t ste
  *   shard_reweight   log_w = lv - log_norm (the GLOBAL normaliser), w = exp(log_w); beta := beta_new
  *   shard_scan       exact sequentially-rounded running sum of w continuing from carry_in
  *   shard_offspring  ancestors of global slots [jlo, jhi) (thresholds u/N + j/N) packed plane-major:
- *                    d_f64 [(d_cont+3)][cnt] (values + the three accumulators), d_i32 [d_disc][cnt]
+ *                    d_f64 [(d_cont+3)][cnt] (values + the three accumulators), d_i32 [d_disc][cnt];
+ *                    both NULL = the offspring stay here: written in place at local_offset
  *   shard_install    place one source rank's chunk at local positions [offset, offset+cnt)
  *   shard_resampled  swap the migrated population in; weights uniform again
  *   shard_weights    the shard's log weights as they are (normalised by the GLOBAL log-sum-exp)
@@ -295,7 +296,8 @@ int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3);
 int32_t fc_smc_shard_reweight(fc_smc_session* s, double beta_new, double log_norm);
 int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value);
 int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo,
-                               uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx);
+                               uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx,
+                               uint64_t local_offset);
 int32_t fc_smc_shard_install(fc_smc_session* s, uint64_t offset, uint64_t cnt, const double* d_f64,
                              const int32_t* d_i32);
 int32_t fc_smc_shard_resampled(fc_smc_session* s);

@@ -47,7 +47,7 @@ def _worker(rank, ws, port, n_total, q):
     api.check(api.lib.fc_smc_shard_weights(sm.S.h, None, api._ptr(w)))
     v_before = sm.result().values[0].copy()
     f_before = sm.result().dvalues[0].copy()
-    (jlo, jhi), idx = sm.resample_global(u_raw=0.37)
+    (jlo, jhi), idx = sm.resample_global(u_raw=0.37, return_idx=True)
     r = sm.result()
     out.update(w=w, v_before=v_before, f_before=f_before, slots=(jlo, jhi), idx=idx.copy(), v_after=r.values[0].copy(), f_after=r.dvalues[0].copy(),
                w_after=r.weight.copy(), lse1=lse1, migrated=sm.migrated)

@@ -31,7 +31,7 @@ w = np.zeros(sm.n)
 api.check(api.lib.fc_smc_shard_weights(sm.S.h, None, api._ptr(w)))
 vb = sm.result().values.copy()
 zb = sm.result().dvalues.copy()
-(jlo, jhi), idx = sm.resample_global(u_raw=0.61)
+(jlo, jhi), idx = sm.resample_global(u_raw=0.61, return_idx=True)
 ra = sm.result()
 
 
@@ -67,14 +67,23 @@ torch.cuda.synchronize()
 if ws > 1:
     dist.barrier()
 t0 = time.perf_counter()
-res = D.adaptive_smc_sharded(m, n_total, cfg, seed=7, values=False)
+big = D.ShardedSmc(m, n_total, cfg, seed=7)  # prior draw + first scoring of the shard
 torch.cuda.synchronize()
-dt = time.perf_counter() - t0
+t1 = time.perf_counter()
+while big.step() < 1.0:
+    pass
+torch.cuda.synchronize()
+dt = time.perf_counter() - t1
+init_s = t1 - t0
+res = big.result(values=False)
+phase = dict(big.timers)
+res.migrated = big.migrated
+big.close()
 dt = D.all_reduce_np(np.array([dt]), op="max")[0]
 mig = D.all_reduce_np(np.array([float(res.migrated)]))[0]
 wsum = D.all_reduce_np(np.array([res.weight.sum()]))[0]
 if rank == 0:
-    out.update(seconds=dt, temper_steps=int(res.n_temper_steps), particle_updates_per_s=n_total * res.n_temper_steps / dt,
+    out.update(seconds=dt, init_seconds=init_s, phase_seconds=phase, temper_steps=int(res.n_temper_steps), particle_updates_per_s=n_total * res.n_temper_steps / dt,
                log_evidence=res.log_evidence, migrated_particles=int(mig), weight_sum=wsum)
     print(json.dumps(out))
 if ws > 1:
