@@ -15,7 +15,10 @@ import numpy as np
 DIST_IDS = {"Normal": 0, "Uniform": 1, "LogNormal": 2, "Exponential": 3, "Bernoulli": 4, "Categorical": 5,
             "Beta": 6, "Gamma": 7, "Binomial": 8, "Poisson": 9, "StudentT": 10, "Cauchy": 11, "Laplace": 12,
             "Weibull": 13, "ChiSquared": 14, "InverseGamma": 15, "DiscreteUniform": 16}
-FC_OP_SAMPLE, FC_OP_OBSERVE, FC_OP_FACTOR, FC_OP_PLATE_SAMPLE, FC_OP_PLATE_OBSERVE = range(5)
+FC_OP_SAMPLE, FC_OP_OBSERVE, FC_OP_FACTOR, FC_OP_PLATE_SAMPLE, FC_OP_PLATE_OBSERVE, FC_OP_FACTOR_EXPR = range(6)
+(FC_X_CONST, FC_X_LATENT, FC_X_ADD, FC_X_SUB, FC_X_MUL, FC_X_DIV, FC_X_NEG, FC_X_EXP, FC_X_LN, FC_X_SQRT, FC_X_ABS, FC_X_FLOOR,
+ FC_X_SIN, FC_X_COS, FC_X_TANH, FC_X_POW, FC_X_MIN, FC_X_MAX) = range(18)
+FC_EXPR_MAX_NODES = 64
 FC_T_F64, FC_T_I64, FC_T_U64, FC_T_USIZE, FC_T_BOOL = range(5)
 (FC_TERM_NONE, FC_TERM_CONST, FC_TERM_LATENT, FC_TERM_LATENT_X, FC_TERM_DENSE, FC_TERM_GATHER,
  FC_TERM_SELECT2, FC_TERM_PLATE_LATENT) = range(8)
@@ -44,7 +47,11 @@ class fc_param(C.Structure):
 class fc_op(C.Structure):
     _fields_ = [("kind", C.c_int32), ("dist", C.c_int32), ("value_type", C.c_int32), ("n_params", C.c_int32),
                 ("name", C.c_char_p), ("plate_len", C.c_int64), ("value_col", C.c_int32), ("_pad", C.c_int32),
-                ("value", C.c_double), ("param", fc_param * 3)]
+                ("value", C.c_double), ("param", fc_param * 3), ("expr_first", C.c_int32), ("expr_len", C.c_int32)]
+
+
+class fc_expr_node(C.Structure):
+    _fields_ = [("op", C.c_int32), ("a", C.c_int32), ("b", C.c_int32), ("slot", C.c_int32), ("c", C.c_double)]
 
 
 class fc_column(C.Structure):
@@ -99,15 +106,83 @@ class Expr:
         self.terms, self.link, self.lo, self.hi = list(terms), link, lo, hi
 
     def __add__(self, o):
+        if isinstance(o, Sym):
+            return Sym.apply(FC_X_ADD, self, o)
         o = as_expr(o)
-        assert self.link == FC_LINK_IDENTITY and o.link == FC_LINK_IDENTITY, "links apply last"
+        if self.link != FC_LINK_IDENTITY or o.link != FC_LINK_IDENTITY:
+            return Sym.apply(FC_X_ADD, self, o)  # arithmetic after a link: a general (factor) expression
         return Expr(self.terms + o.terms)
 
     __radd__ = lambda self, o: as_expr(o).__add__(self)
 
     def __mul__(self, col):
-        assert isinstance(col, Column) and len(self.terms) == 1 and self.terms[0][0] == FC_TERM_LATENT
+        if not isinstance(col, Column):  # latent * number / latent * latent: a general (factor) expression
+            return Sym.apply(FC_X_MUL, self, col)
+        assert len(self.terms) == 1 and self.terms[0][0] == FC_TERM_LATENT
         return Expr([(FC_TERM_LATENT_X, self.terms[0][1], 0, col.cid, 0.0)])
+
+    # everything that is not link(term + term + term) becomes a general expression (factor(..) only)
+    __rmul__ = lambda self, o: Sym.apply(FC_X_MUL, o, self)
+    __sub__ = lambda self, o: Sym.apply(FC_X_SUB, self, o)
+    __rsub__ = lambda self, o: Sym.apply(FC_X_SUB, o, self)
+    __truediv__ = lambda self, o: Sym.apply(FC_X_DIV, self, o)
+    __rtruediv__ = lambda self, o: Sym.apply(FC_X_DIV, o, self)
+    __neg__ = lambda self: Sym.apply(FC_X_NEG, self)
+    __pow__ = lambda self, o: Sym.apply(FC_X_POW, self, o)
+
+
+class Sym:
+    """A general scalar expression over continuous latents (for factor(..)): SSA nodes
+    (op, a, b, slot, c) in evaluation order -- fc_expr_node. Built with + - * / unary -, ** and the
+    functions exp ln sqrt abs floor sin cos tanh pow min max of `fugue_b200.model`."""
+
+    def __init__(self, nodes):
+        self.nodes = nodes
+
+    @staticmethod
+    def lift(x):
+        if isinstance(x, Sym):
+            return x
+        if isinstance(x, Expr):  # a scalar parameter expression: link(const + latent + ...)
+            if getattr(x, "discrete", False) or any(k not in (FC_TERM_CONST, FC_TERM_LATENT) for k, *_ in x.terms):
+                raise FugueError(FC_ERR_UNSUPPORTED_OP, "only continuous scalar latents and constants can enter a factor expression")
+            acc = None
+            for k, slot, _, _, c in x.terms:
+                t = Sym([(FC_X_LATENT, 0, 0, slot, 0.0)]) if k == FC_TERM_LATENT else Sym([(FC_X_CONST, 0, 0, 0, float(c))])
+                acc = t if acc is None else Sym.apply(FC_X_ADD, acc, t)
+            if x.link == FC_LINK_EXP:
+                acc = Sym.apply(FC_X_EXP, acc)
+            elif x.link == FC_LINK_SIGMOID_CLAMPED:
+                acc = Sym.apply(FC_X_DIV, 1.0, Sym.apply(FC_X_ADD, 1.0, Sym.apply(FC_X_EXP, Sym.apply(FC_X_NEG, acc))))
+            if x.link in (FC_LINK_SIGMOID_CLAMPED, FC_LINK_CLAMP):
+                acc = Sym.apply(FC_X_MAX, float(x.lo), Sym.apply(FC_X_MIN, acc, float(x.hi)))
+            return acc
+        return Sym([(FC_X_CONST, 0, 0, 0, float(x))])
+
+    @staticmethod
+    def apply(op, *args):
+        nodes, roots = [], []
+        for a in args:
+            a = Sym.lift(a)
+            off = len(nodes)
+            for (o, x, y, s, c) in a.nodes:
+                nodes.append((o, x + off if o >= FC_X_ADD else 0, y + off if ((FC_X_ADD <= o <= FC_X_DIV) or o >= FC_X_POW) else 0, s, c))
+            roots.append(len(nodes) - 1)
+        nodes.append((op, roots[0], roots[1] if len(roots) > 1 else 0, 0, 0.0))
+        if len(nodes) > FC_EXPR_MAX_NODES:
+            raise FugueError(FC_ERR_UNSUPPORTED_OP, f"factor expression has more than {FC_EXPR_MAX_NODES} nodes")
+        return Sym(nodes)
+
+    __add__ = lambda a, b: Sym.apply(FC_X_ADD, a, b)
+    __radd__ = lambda a, b: Sym.apply(FC_X_ADD, b, a)
+    __sub__ = lambda a, b: Sym.apply(FC_X_SUB, a, b)
+    __rsub__ = lambda a, b: Sym.apply(FC_X_SUB, b, a)
+    __mul__ = lambda a, b: Sym.apply(FC_X_MUL, a, b)
+    __rmul__ = lambda a, b: Sym.apply(FC_X_MUL, b, a)
+    __truediv__ = lambda a, b: Sym.apply(FC_X_DIV, a, b)
+    __rtruediv__ = lambda a, b: Sym.apply(FC_X_DIV, b, a)
+    __neg__ = lambda a: Sym.apply(FC_X_NEG, a)
+    __pow__ = lambda a, b: Sym.apply(FC_X_POW, a, b)
 
 
 class Site(Expr):

@@ -45,6 +45,7 @@ def _sig(name, *argtypes):
 _sig("fc_device_count", C.POINTER(C.c_int32))
 _sig("fc_set_device", C.c_int32)
 _sig("fc_program_create", vp, C.c_size_t, vp, C.c_size_t, C.POINTER(vp))
+_sig("fc_program_create_ex", vp, C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, C.POINTER(vp))
 _sig("fc_program_destroy", vp)
 _sig("fc_program_check_structure", vp, vp, C.c_size_t)
 _sig("fc_program_dims", vp, i64p, i64p)
@@ -90,7 +91,8 @@ class Program:
         self._low = builder.lower()  # keeps ctypes arrays and numpy columns alive during create
         ops, n, cols, ncol = self._low
         h = vp()
-        check(lib.fc_program_create(C.cast(ops, vp), n, C.cast(cols, vp), ncol, C.byref(h)))
+        nodes, n_nodes = builder.nodes_lowered
+        check(lib.fc_program_create_ex(C.cast(ops, vp), n, C.cast(cols, vp), ncol, C.cast(nodes, vp), n_nodes, C.byref(h)))
         self.h = h
         dc, dd = C.c_int64(), C.c_int64()
         check(lib.fc_program_dims(h, C.byref(dc), C.byref(dd)))

@@ -41,6 +41,7 @@ struct DOp {
   DCol value_col;
   double value;
   const double* lgam;  // optional precomputed lgamma(value+1) per element (count data)
+  int32_t expr_first, expr_len;  // FACTOR_EXPR: nodes in the program's expression table
   DParam p[3];
 };
 
@@ -106,6 +107,8 @@ struct fc_program {
   fc::DevBuf<fc::DOp> d_all_ops;
   std::vector<fc::DOp> scalar_ops;
   fc::DevBuf<fc::DOp> d_scalar_ops;
+  std::vector<fc_expr_node> expr_nodes;      // FACTOR_EXPR table, latent slots already as sorted rows
+  fc::DevBuf<fc_expr_node> d_expr_nodes;
   std::vector<std::unique_ptr<fc::PlateInfo>> plates;
   cudaStream_t stream = nullptr;
   int device = 0;

@@ -137,7 +137,7 @@ static int64_t host_col_i64(const fc_column& c, int64_t i) {
   }
 }
 
-static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols) {
+static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols, const fc_expr_node* nodes, size_t n_nodes) {
   if (n_ops > 0 && !ops) { set_error("ops is NULL"); return FC_ERR_INVALID_ARGUMENT; }
   P->ops.assign(ops, ops + n_ops);
   P->names.resize(n_ops);
@@ -150,8 +150,23 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
   // ---- validate ops, assign program slots ----
   for (size_t i = 0; i < n_ops; i++) {
     const fc_op& op = P->ops[i];
-    if (op.kind < FC_OP_SAMPLE || op.kind > FC_OP_PLATE_OBSERVE) { set_error("op %zu: bad kind %d", i, op.kind); return FC_ERR_INVALID_ARGUMENT; }
+    if (op.kind < FC_OP_SAMPLE || op.kind > FC_OP_FACTOR_EXPR) { set_error("op %zu: bad kind %d", i, op.kind); return FC_ERR_INVALID_ARGUMENT; }
     if (op.kind == FC_OP_FACTOR) continue;
+    if (op.kind == FC_OP_FACTOR_EXPR) {
+      // nodes in SSA order; a factor may only read latents sampled EARLIER in program order
+      if (op.expr_len < 1 || op.expr_len > FC_EXPR_MAX_NODES || op.expr_first < 0 || (size_t)op.expr_first + (size_t)op.expr_len > n_nodes || !nodes) {
+        set_error("op %zu: factor expression [%d, +%d) outside the node table (%zu nodes, at most %d per expression)", i, op.expr_first, op.expr_len, n_nodes, FC_EXPR_MAX_NODES);
+        return FC_ERR_INVALID_ARGUMENT;
+      }
+      for (int k = 0; k < op.expr_len; k++) {
+        const fc_expr_node& nd = nodes[op.expr_first + k];
+        if (nd.op < FC_X_CONST || nd.op > FC_X_MAX) { set_error("op %zu: bad expression opcode %d", i, nd.op); return FC_ERR_INVALID_ARGUMENT; }
+        if (nd.op == FC_X_LATENT && (nd.slot < 0 || nd.slot >= P->d_cont)) { set_error("op %zu: factor reads continuous slot %d but only %lld are defined", i, nd.slot, (long long)P->d_cont); return FC_ERR_TRACE_ADDRESS_NOT_FOUND; }
+        bool binary = nd.op >= FC_X_ADD && nd.op <= FC_X_DIV || nd.op >= FC_X_POW;
+        if (nd.op >= FC_X_ADD && (nd.a < 0 || nd.a >= k || (binary && (nd.b < 0 || nd.b >= k)))) { set_error("op %zu: expression node %d refers to a later node", i, k); return FC_ERR_INVALID_ARGUMENT; }
+      }
+      continue;
+    }
     if (op.dist < 0 || op.dist >= FC_N_DISTS) { set_error("op %zu: bad distribution id %d", i, op.dist); return FC_ERR_INVALID_ARGUMENT; }
     static const int np[FC_N_DISTS] = {2, 2, 2, 1, 1, 1, 2, 2, 2, 1, 3, 2, 2, 2, 1, 2, 2};
     if (op.n_params != np[op.dist]) { set_error("op %zu: distribution %d takes %d parameters, got %d", i, op.dist, np[op.dist], op.n_params); return FC_ERR_INVALID_ARGUMENT; }
@@ -274,7 +289,8 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
     const fc_op& op = P->ops[i];
     DOp d;
     memset(&d, 0, sizeof(d));
-    d.kind = op.kind; d.dist = op.dist; d.value_type = op.value_type; d.n_params = op.kind == FC_OP_FACTOR ? 0 : op.n_params;
+    d.kind = op.kind; d.dist = op.dist; d.value_type = op.value_type; d.n_params = (op.kind == FC_OP_FACTOR || op.kind == FC_OP_FACTOR_EXPR) ? 0 : op.n_params;
+    d.expr_first = op.expr_first; d.expr_len = op.kind == FC_OP_FACTOR_EXPR ? op.expr_len : 0;
     d.is_sample = (op.kind == FC_OP_SAMPLE || op.kind == FC_OP_PLATE_SAMPLE);
     d.cont = op.value_type == FC_T_F64;
     d.plate_len = op.plate_len; d.cslot0 = P->cslot0[i]; d.dslot0 = P->dslot0[i];
@@ -385,6 +401,12 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
   }
   FC_CUDA(P->d_all_ops.reserve(P->all_ops.size()));
   if (!P->all_ops.empty()) FC_CUDA(cudaMemcpyAsync(P->d_all_ops.p, P->all_ops.data(), P->all_ops.size() * sizeof(DOp), cudaMemcpyHostToDevice, P->stream));
+  // expression table of FACTOR_EXPR ops: latent slots resolved to sorted state rows
+  P->expr_nodes.assign(nodes, nodes + (nodes ? n_nodes : 0));
+  for (auto& nd : P->expr_nodes)
+    if (nd.op == FC_X_LATENT) nd.slot = (nd.slot >= 0 && nd.slot < P->d_cont) ? P->crow[nd.slot] : 0;
+  FC_CUDA(P->d_expr_nodes.reserve(std::max<size_t>(1, P->expr_nodes.size())));
+  if (!P->expr_nodes.empty()) FC_CUDA(cudaMemcpyAsync(P->d_expr_nodes.p, P->expr_nodes.data(), P->expr_nodes.size() * sizeof(fc_expr_node), cudaMemcpyHostToDevice, P->stream));
   FC_CUDA(P->d_scalar_ops.reserve(P->scalar_ops.size()));
   if (!P->scalar_ops.empty()) FC_CUDA(cudaMemcpyAsync(P->d_scalar_ops.p, P->scalar_ops.data(), P->scalar_ops.size() * sizeof(DOp), cudaMemcpyHostToDevice, P->stream));
   FC_CUDA(cudaStreamSynchronize(P->stream));
@@ -409,10 +431,14 @@ int32_t fc_set_device(int32_t device) {
 }
 
 int32_t fc_program_create(const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols, fc_program** out) {
+  return fc_program_create_ex(ops, n_ops, cols, n_cols, nullptr, 0, out);
+}
+
+int32_t fc_program_create_ex(const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols, const fc_expr_node* nodes, size_t n_nodes, fc_program** out) {
   if (!out) { fc::set_error("out is NULL"); return FC_ERR_INVALID_ARGUMENT; }
   *out = nullptr;
   fc_program* P = new fc_program();
-  int32_t rc = fc::build(P, ops, n_ops, cols, n_cols);
+  int32_t rc = fc::build(P, ops, n_ops, cols, n_cols, nodes, n_nodes);
   if (rc != FC_OK) { fc_program_destroy(P); return rc; }
   *out = P;
   return FC_OK;
@@ -434,7 +460,8 @@ int32_t fc_program_check_structure(const fc_program* p, const fc_op* ops, size_t
     const fc_op& a = p->ops[i];
     const fc_op& b = ops[i];
     std::string nb = b.name ? b.name : "";
-    if (a.kind != b.kind || a.dist != b.dist || a.value_type != b.value_type || a.plate_len != b.plate_len || nb != p->names[i]) {
+    if (a.kind != b.kind || a.dist != b.dist || a.value_type != b.value_type || a.plate_len != b.plate_len || nb != p->names[i] ||
+        (a.kind == FC_OP_FACTOR_EXPR && a.expr_len != b.expr_len)) {
       fc::set_error("model structure changed at op %zu: '%s' (kind %d, dist %d, len %lld) vs traced '%s' (kind %d, dist %d, len %lld)", i, p->names[i].c_str(), a.kind, a.dist, (long long)a.plate_len, nb.c_str(), b.kind, b.dist, (long long)b.plate_len);
       return FC_ERR_UNEXPECTED_MODEL_STRUCTURE;
     }

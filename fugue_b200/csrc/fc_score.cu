@@ -22,15 +22,89 @@ namespace fc {
 // ---------------------------------------------------------------------------------------
 // scalar ops: one thread per chain, program order
 // ---------------------------------------------------------------------------------------
+// factor(f(latents)): forward sweep over the SSA nodes, then (GRAD) a reverse sweep that pushes the
+// adjoints into the gradient rows. Functions as the playground evaluates them (dsl.rs:755-786);
+// abs / floor / min / max use the derivative of the active branch (0 for floor).
+template <bool GRAD>
+__device__ __noinline__ double factor_expr_eval(const fc_expr_node* __restrict__ nd, int n, const double* __restrict__ q, int64_t C, int64_t c, double* __restrict__ grad, bool nan_is_neg_inf) {
+  double v[FC_EXPR_MAX_NODES];
+  for (int k = 0; k < n; k++) {
+    const fc_expr_node e = nd[k];
+    const double a = e.op >= FC_X_ADD ? v[e.a] : 0.0;
+    const double b = ((e.op >= FC_X_ADD && e.op <= FC_X_DIV) || e.op >= FC_X_POW) ? v[e.b] : 0.0;
+    double r;
+    switch (e.op) {
+      case FC_X_CONST: r = e.c; break;
+      case FC_X_LATENT: r = q[(int64_t)e.slot * C + c]; break;
+      case FC_X_ADD: r = a + b; break;
+      case FC_X_SUB: r = a - b; break;
+      case FC_X_MUL: r = a * b; break;
+      case FC_X_DIV: r = a / b; break;
+      case FC_X_NEG: r = -a; break;
+      case FC_X_EXP: r = exp(a); break;
+      case FC_X_LN: r = log(a); break;
+      case FC_X_SQRT: r = sqrt(a); break;
+      case FC_X_ABS: r = fabs(a); break;
+      case FC_X_FLOOR: r = floor(a); break;
+      case FC_X_SIN: r = sin(a); break;
+      case FC_X_COS: r = cos(a); break;
+      case FC_X_TANH: r = tanh(a); break;
+      case FC_X_POW: r = pow(a, b); break;
+      case FC_X_MIN: r = fmin(a, b); break;  // f64::min: the non-NaN operand
+      default: r = fmax(a, b); break;
+    }
+    v[k] = r;
+  }
+  double out = v[n - 1];
+  if (nan_is_neg_inf && out != out) return d_neg_inf();
+  if (GRAD && d_fin(out)) {
+    double adj[FC_EXPR_MAX_NODES];
+    for (int k = 0; k < n; k++) adj[k] = 0.0;
+    adj[n - 1] = 1.0;
+    for (int k = n - 1; k >= 0; k--) {
+      const double g = adj[k];
+      if (g == 0.0) continue;
+      const fc_expr_node e = nd[k];
+      const double a = e.op >= FC_X_ADD ? v[e.a] : 0.0;
+      const double b = ((e.op >= FC_X_ADD && e.op <= FC_X_DIV) || e.op >= FC_X_POW) ? v[e.b] : 0.0;
+      switch (e.op) {
+        case FC_X_LATENT: grad[(int64_t)e.slot * C + c] += g; break;
+        case FC_X_ADD: adj[e.a] += g; adj[e.b] += g; break;
+        case FC_X_SUB: adj[e.a] += g; adj[e.b] -= g; break;
+        case FC_X_MUL: adj[e.a] += g * b; adj[e.b] += g * a; break;
+        case FC_X_DIV: adj[e.a] += g / b; adj[e.b] -= g * a / (b * b); break;
+        case FC_X_NEG: adj[e.a] -= g; break;
+        case FC_X_EXP: adj[e.a] += g * v[k]; break;
+        case FC_X_LN: adj[e.a] += g / a; break;
+        case FC_X_SQRT: adj[e.a] += g * 0.5 / v[k]; break;
+        case FC_X_ABS: adj[e.a] += a < 0.0 ? -g : g; break;
+        case FC_X_SIN: adj[e.a] += g * cos(a); break;
+        case FC_X_COS: adj[e.a] -= g * sin(a); break;
+        case FC_X_TANH: adj[e.a] += g * (1.0 - v[k] * v[k]); break;
+        case FC_X_POW:
+          adj[e.a] += g * b * pow(a, b - 1.0);
+          if (nd[e.b].op != FC_X_CONST) adj[e.b] += g * v[k] * log(a);  // constant exponents (the common case) take no adjoint
+          break;
+        case FC_X_MIN: if (a <= b || b != b) adj[e.a] += g; else adj[e.b] += g; break;
+        case FC_X_MAX: if (a >= b || b != b) adj[e.a] += g; else adj[e.b] += g; break;
+        default: break;  // CONST, FLOOR
+      }
+    }
+  }
+  return out;
+}
+
 template <bool GRAD>
 __global__ void k_scalar(const DOp* __restrict__ ops, int n_ops, const int32_t* __restrict__ crow, const int32_t* __restrict__ drow,
-                         const double* __restrict__ q, const disc_t* __restrict__ qd, int64_t C, double* __restrict__ grad, double* __restrict__ part) {
+                         const double* __restrict__ q, const disc_t* __restrict__ qd, int64_t C, double* __restrict__ grad, double* __restrict__ part,
+                         const fc_expr_node* __restrict__ nodes) {
   int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   double a_prior = 0.0, a_lik = 0.0, a_fac = 0.0;
   for (int oi = 0; oi < n_ops; oi++) {
     const DOp& op = ops[oi];
     if (op.kind == FC_OP_FACTOR) { a_fac += op.value; continue; }
+    if (op.kind == FC_OP_FACTOR_EXPR) { a_fac += factor_expr_eval<GRAD>(nodes + op.expr_first, op.expr_len, q, C, c, grad, op.value != 0.0); continue; }
     double pv[3] = {0.0, 0.0, 0.0}, dl[3] = {0.0, 0.0, 0.0};
     for (int j = 0; j < op.n_params; j++) {
       const DParam& pr = op.p[j];
@@ -438,8 +512,8 @@ int32_t score_dev(fc_program* P, const double* d_q, const disc_t* d_qd, int64_t 
   const unsigned fin_bx = (unsigned)cdiv(C, 128);
   if (!P->scalar_ops.empty()) {
     unsigned nb = (unsigned)cdiv(C, 128);
-    if (grad) k_scalar<true><<<nb, 128, 0, st>>>(P->d_scalar_ops.p, (int)P->scalar_ops.size(), P->d_crow.p, P->d_drow.p, d_q, d_qd, C, d_grad, P->ws.part.p);
-    else k_scalar<false><<<nb, 128, 0, st>>>(P->d_scalar_ops.p, (int)P->scalar_ops.size(), P->d_crow.p, P->d_drow.p, d_q, d_qd, C, d_grad, P->ws.part.p);
+    if (grad) k_scalar<true><<<nb, 128, 0, st>>>(P->d_scalar_ops.p, (int)P->scalar_ops.size(), P->d_crow.p, P->d_drow.p, d_q, d_qd, C, d_grad, P->ws.part.p, P->d_expr_nodes.p);
+    else k_scalar<false><<<nb, 128, 0, st>>>(P->d_scalar_ops.p, (int)P->scalar_ops.size(), P->d_crow.p, P->d_drow.p, d_q, d_qd, C, d_grad, P->ws.part.p, P->d_expr_nodes.p);
     FC_KERNEL_CHECK();
     F.n_splits = 1; F.n_acc = 3;
     k_finish<<<dim3(fin_bx, 3), 128, 0, st>>>(F);

@@ -516,6 +516,8 @@ class _Lowering:
         if t in ("num", "int", "bool"):
             return e[1]
         if t == "var":
+            if isinstance(env[e[1]], _ir.Sym):
+                raise _unsupported(f"`{e[1]}` is a non-affine latent expression: usable in factor(..) and pure(..) only")
             return env[e[1]]
         if t == "len":
             a = self.ev(e[1], env)
@@ -555,6 +557,51 @@ class _Lowering:
             return self.bin(e[1], self.ev(e[2], env), self.ev(e[3], env))
         if t == "call":
             return self.call(e[1], [self.ev(a, env) for a in e[2]])
+        raise AssertionError(t)
+
+    _SYM_FN = {"exp": _ir.FC_X_EXP, "ln": _ir.FC_X_LN, "log": _ir.FC_X_LN, "sqrt": _ir.FC_X_SQRT, "abs": _ir.FC_X_ABS, "floor": _ir.FC_X_FLOOR,
+               "sin": _ir.FC_X_SIN, "cos": _ir.FC_X_COS, "tanh": _ir.FC_X_TANH, "pow": _ir.FC_X_POW, "min": _ir.FC_X_MIN, "max": _ir.FC_X_MAX}
+    _SYM_BIN = {"+": _ir.FC_X_ADD, "-": _ir.FC_X_SUB, "*": _ir.FC_X_MUL, "/": _ir.FC_X_DIV}
+
+    def sym(self, e, env):
+        """The expression as a general function of the continuous latents (fc_expr_node list), with
+        constant sub-expressions folded by the same rules as ev(). Returns a number or an _ir.Sym."""
+        t = e[0]
+        if t in ("num", "int", "bool"):
+            return e[1]
+        if t == "var":
+            v = env[e[1]]
+            if _is_const(v) or isinstance(v, _ir.Sym):
+                return v
+            if isinstance(v, _ir.Expr):
+                if v.link != _ir.FC_LINK_IDENTITY or getattr(v, "discrete", False) or any(k not in (_ir.FC_TERM_CONST, _ir.FC_TERM_LATENT) for k, *_ in v.terms):
+                    raise _unsupported("factor() of a discrete latent or of a linked parameter expression")
+                out = None
+                for k, slot, _, _, c in v.terms:
+                    term = _ir.Sym([(_ir.FC_X_LATENT, 0, 0, slot, 0.0)]) if k == _ir.FC_TERM_LATENT else c
+                    out = term if out is None else _ir.Sym.apply(_ir.FC_X_ADD, out, term)
+                return out
+            raise _unsupported("this value cannot enter a factor expression")
+        if t in ("len", "index"):
+            v = self.ev(e, env)
+            if not _is_const(v):
+                raise _unsupported("array element indexed by a latent")
+            return v
+        if t == "neg":
+            a = self.sym(e[1], env)
+            if _is_const(a):
+                return -a if (isinstance(a, int) and not isinstance(a, bool)) else -_as_f64(a)
+            return _ir.Sym.apply(_ir.FC_X_NEG, a)
+        if t == "bin":
+            x, y = self.sym(e[2], env), self.sym(e[3], env)
+            if _is_const(x) and _is_const(y):
+                return _bin_const(e[1], x, y)
+            return _ir.Sym.apply(self._SYM_BIN[e[1]], _as_f64(x) if _is_const(x) else x, _as_f64(y) if _is_const(y) else y)
+        if t == "call":
+            args = [self.sym(a, env) for a in e[2]]
+            if all(_is_const(a) for a in args):
+                return _math(e[1], [_as_f64(a) for a in args])
+            return _ir.Sym.apply(self._SYM_FN[e[1]], *[_as_f64(a) if _is_const(a) else a for a in args])
         raise AssertionError(t)
 
     def sigmoid_pattern(self, e, env):
@@ -710,13 +757,32 @@ class _Lowering:
         for s in stmts:
             kind = s[0]
             if kind == "let":
-                env[s[1]] = self.ev(s[2], env)
+                try:
+                    env[s[1]] = self.ev(s[2], env)
+                except FugueError as ex:
+                    if ex.code != _ir.FC_ERR_UNSUPPORTED_OP or self.plate_n is not None:
+                        raise
+                    env[s[1]] = self.sym(s[2], env)  # usable by factor(..) and pure(..) only
             elif kind == "factor":
-                lw = self.ev(s[1], env)
+                try:
+                    lw = self.ev(s[1], env)
+                except FugueError as ex:
+                    if ex.code != _ir.FC_ERR_UNSUPPORTED_OP:
+                        raise
+                    lw = None  # not affine: a general expression over the latents
+                if lw is None or isinstance(lw, (_ir.Expr, _ir.Sym)):
+                    if self.plate_n is not None:
+                        raise _NotPlate()  # a latent-dependent factor inside a loop: unroll into scalar factors
+                    sy = self.sym(s[1], env)
+                    if isinstance(sy, _ir.Sym):
+                        # the playground maps a NaN log-weight to -inf (dsl.rs:922-926)
+                        self.m.factor(sy, nan_is_neg_inf=True)
+                        continue
+                    lw = sy
                 if not _is_const(lw):
-                    if isinstance(lw, _LoopVar):
+                    if isinstance(lw, (_LoopVar, _Elem)):
                         raise _NotPlate()
-                    raise _unsupported("factor() of a latent expression")
+                    raise _unsupported("factor() of this expression")
                 lw = _as_f64(lw)
                 reps = self.plate_n if self.plate_n is not None else 1
                 if reps > 4096:

@@ -230,18 +230,28 @@ class ModelBuilder:
         assert isinstance(values, Column)
         self._op(_ir.FC_OP_PLATE_OBSERVE, dist, name, plate_len=len(values), value_col=values.cid)
 
-    def factor(self, logw):
+    def factor(self, logw, nan_is_neg_inf=False):
+        """factor(log_weight) (src/core/model.rs:97-104). A number is a constant factor; a `Sym`
+        (or a bare latent) is evaluated per chain on the device with its analytic gradient."""
+        if isinstance(logw, (_ir.Sym, _ir.Expr)):
+            self._op(_ir.FC_OP_FACTOR_EXPR, None, "", value=1.0 if nan_is_neg_inf else 0.0)
+            self.ops[-1]["expr"] = _ir.Sym.lift(logw)
+            return
         self._op(_ir.FC_OP_FACTOR, None, "", value=float(logw))
 
     # ---- lowering ----
     def lower(self):
         n = len(self.ops)
+        node_list = []
         ops = (_ir.fc_op * max(n, 1))()
         for i, d in enumerate(self.ops):
             o = ops[i]
             o.kind, o.plate_len, o.value_col, o.value = d["kind"], d["plate_len"], d["value_col"], d["value"]
             o.name = d["name"].encode()
             dist = d["dist"]
+            if d["kind"] == _ir.FC_OP_FACTOR_EXPR:
+                o.expr_first, o.expr_len = len(node_list), len(d["expr"].nodes)
+                node_list.extend(d["expr"].nodes)
             if dist is None:
                 continue
             o.dist = _ir.DIST_IDS[dist.name]
@@ -264,4 +274,27 @@ class ModelBuilder:
             cols[i].width = 1 if c.arr.ndim == 1 else c.arr.shape[1]
             cols[i].rows = c.arr.shape[0]
             cols[i].data = c.arr.ctypes.data
+        nodes = (_ir.fc_expr_node * max(len(node_list), 1))()
+        for i, (o, a, b, sl, c) in enumerate(node_list):
+            nodes[i].op, nodes[i].a, nodes[i].b, nodes[i].slot, nodes[i].c = o, a, b, sl, c
+        self.nodes_lowered = (nodes, len(node_list))  # the FACTOR_EXPR table (fc_program_create_ex)
         return ops, n, cols, ncol
+
+
+# ---- functions of factor expressions (the playground's set, crates/fugue-wasm/src/dsl.rs:775-786) ----
+def _fn(op):
+    return lambda *a: _ir.Sym.apply(op, *a)
+
+
+ln, sqrt, abs_, floor, sin, cos, tanh = (_fn(o) for o in (_ir.FC_X_LN, _ir.FC_X_SQRT, _ir.FC_X_ABS, _ir.FC_X_FLOOR,
+                                                             _ir.FC_X_SIN, _ir.FC_X_COS, _ir.FC_X_TANH))
+_link_exp = exp
+
+
+def exp(e):
+    """exp as a LINK on a parameter expression (hierarchical / GLM parameters) or, on a general
+    expression, as a function node of a factor expression."""
+    return _ir.Sym.apply(_ir.FC_X_EXP, e) if isinstance(e, _ir.Sym) else _link_exp(e)
+
+
+pow_, min_, max_ = _fn(_ir.FC_X_POW), _fn(_ir.FC_X_MIN), _fn(_ir.FC_X_MAX)

@@ -42,7 +42,9 @@ enum {
 };
 
 /* ---- op kinds (Model variants: src/core/model.rs:20-131; plate!: src/macros/mod.rs:82-86) ---- */
-enum { FC_OP_SAMPLE = 0, FC_OP_OBSERVE = 1, FC_OP_FACTOR = 2, FC_OP_PLATE_SAMPLE = 3, FC_OP_PLATE_OBSERVE = 4 };
+enum { FC_OP_SAMPLE = 0, FC_OP_OBSERVE = 1, FC_OP_FACTOR = 2, FC_OP_PLATE_SAMPLE = 3, FC_OP_PLATE_OBSERVE = 4,
+       FC_OP_FACTOR_EXPR = 5 /* factor(f(latents)): log-weight computed from the latents (Model::Factor
+                                fed by a bind closure, src/core/model.rs:97-104); see fc_expr_node */ };
 
 /* ---- value types (ChoiceValue: src/runtime/trace.rs:32-47) ---- */
 enum { FC_T_F64 = 0, FC_T_I64 = 1, FC_T_U64 = 2, FC_T_USIZE = 3, FC_T_BOOL = 4 };
@@ -88,9 +90,32 @@ typedef struct fc_op {
   int64_t plate_len;   /* PLATE_*: number of elements; else 0                         */
   int32_t value_col;   /* OBSERVE/PLATE_OBSERVE: data column holding the value(s)     */
   int32_t _pad;
-  double  value;       /* OBSERVE (scalar): observed value; FACTOR: log-weight        */
+  double  value;       /* OBSERVE (scalar): observed value; FACTOR: log-weight;
+                          FACTOR_EXPR: 1.0 = a NaN result counts as -inf (the playground's
+                          policy, crates/fugue-wasm/src/dsl.rs:922-926), 0.0 = added as is */
   fc_param param[3];
+  int32_t expr_first;  /* FACTOR_EXPR: first node / number of nodes in the program's        */
+  int32_t expr_len;    /*   expression table (fc_program_create_ex); the last node is the value */
 } fc_op;
+
+/* ---- expression nodes of FACTOR_EXPR ops, in evaluation (SSA) order: node k may only refer to
+ *      nodes a, b < k of the same expression (indices relative to expr_first). Arithmetic and
+ *      functions are those of the playground's evaluator (crates/fugue-wasm/src/dsl.rs:755-786):
+ *      f64 + - * /, exp ln sqrt abs floor sin cos tanh, powf, f64::min / f64::max. ---- */
+enum {
+  FC_X_CONST = 0,   /* c                                   */
+  FC_X_LATENT = 1,  /* q[slot] (program-order continuous slot) */
+  FC_X_ADD = 2, FC_X_SUB = 3, FC_X_MUL = 4, FC_X_DIV = 5, FC_X_NEG = 6,
+  FC_X_EXP = 7, FC_X_LN = 8, FC_X_SQRT = 9, FC_X_ABS = 10, FC_X_FLOOR = 11, FC_X_SIN = 12,
+  FC_X_COS = 13, FC_X_TANH = 14, FC_X_POW = 15, FC_X_MIN = 16, FC_X_MAX = 17
+};
+#define FC_EXPR_MAX_NODES 64
+typedef struct fc_expr_node {
+  int32_t op;      /* FC_X_*                        */
+  int32_t a, b;    /* operand nodes (unary: a only) */
+  int32_t slot;    /* FC_X_LATENT                   */
+  double  c;       /* FC_X_CONST                    */
+} fc_expr_node;
 
 /* ---- data columns ---- */
 enum { FC_COL_F64 = 0, FC_COL_U8 = 1, FC_COL_U32 = 2, FC_COL_I64 = 3 };
@@ -114,6 +139,9 @@ int32_t fc_set_device(int32_t device);
  * FC_ERR_ADDRESS_CONFLICT. Columns are copied to the current device. */
 int32_t fc_program_create(const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols,
                           fc_program** out);
+/* The same with the expression table FACTOR_EXPR ops index into (nodes may be NULL if n_nodes == 0). */
+int32_t fc_program_create_ex(const fc_op* ops, size_t n_ops, const fc_column* cols, size_t n_cols,
+                             const fc_expr_node* nodes, size_t n_nodes, fc_program** out);
 int32_t fc_program_destroy(fc_program* p);
 /* Checks a second trace of the same model against the program (address sequence, kinds, types);
  * mismatch -> FC_ERR_UNEXPECTED_MODEL_STRUCTURE (src/runtime/interpreters.rs:271-283). */

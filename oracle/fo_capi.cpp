@@ -38,6 +38,12 @@ int fo_program_create(const fc_op* ops, size_t n, const fc_column* cols, size_t 
   if (rc != FC_OK) { delete p; *out = nullptr; return rc; }
   *out = p; return FC_OK;
 }
+int fo_program_create_ex(const fc_op* ops, size_t n, const fc_column* cols, size_t nc, const fc_expr_node* nodes, size_t nn, void** out) {
+  Program* p = new Program();
+  int rc = p->build(ops, n, cols, nc, nodes, nn);
+  if (rc != FC_OK) { delete p; *out = nullptr; return rc; }
+  *out = p; return FC_OK;
+}
 void fo_program_destroy(void* p) { delete (Program*)p; }
 void fo_program_dims(void* p, int64_t* dc, int64_t* dd) { *dc = ((Program*)p)->d_cont; *dd = ((Program*)p)->d_disc; }
 const char* fo_program_site(void* p, int64_t sorted_idx, int discrete) {

@@ -49,8 +49,10 @@ struct Program {
   int64_t d_cont = 0, d_disc = 0;
   std::vector<int64_t> perm_c, perm_d;  // sorted index -> program slot
   std::vector<std::string> site_c, site_d;  // program-order addresses
+  std::vector<fc_expr_node> nodes;          // FACTOR_EXPR table (latent slots in PROGRAM order)
 
-  int build(const fc_op* o, size_t n, const fc_column* c, size_t nc) {
+  int build(const fc_op* o, size_t n, const fc_column* c, size_t nc, const fc_expr_node* nd = nullptr, size_t nn = 0) {
+    nodes.assign(nd, nd + (nd ? nn : 0));
     ops.assign(o, o + n);
     names.resize(n);
     for (size_t i = 0; i < n; i++) { names[i] = o[i].name ? o[i].name : ""; ops[i].name = nullptr; }
@@ -142,6 +144,49 @@ struct ParamEval {
   }
 };
 
+// factor(f(latents)) -- the value the playground's evaluator computes for the expression
+// (crates/fugue-wasm/src/dsl.rs:755-786: f64 arithmetic, exp ln sqrt abs floor sin cos tanh, powf,
+// f64::min / f64::max) and its gradient by FORWARD-mode differentiation, one latent at a time
+// (independent of the device's reverse sweep). NaN -> -inf when the op asks for the playground's
+// policy (dsl.rs:922-926).
+struct Dual { double v, d; };
+inline Dual expr_forward(const fc_expr_node* nd, int n, const double* q, int wrt_slot) {
+  Dual t[FC_EXPR_MAX_NODES];
+  for (int k = 0; k < n; k++) {
+    const fc_expr_node& e = nd[k];
+    Dual a = e.op >= FC_X_ADD ? t[e.a] : Dual{0, 0};
+    Dual b = ((e.op >= FC_X_ADD && e.op <= FC_X_DIV) || e.op >= FC_X_POW) ? t[e.b] : Dual{0, 0};
+    Dual r{0, 0};
+    switch (e.op) {
+      case FC_X_CONST: r = {e.c, 0.0}; break;
+      case FC_X_LATENT: r = {q[e.slot], e.slot == wrt_slot ? 1.0 : 0.0}; break;
+      case FC_X_ADD: r = {a.v + b.v, a.d + b.d}; break;
+      case FC_X_SUB: r = {a.v - b.v, a.d - b.d}; break;
+      case FC_X_MUL: r = {a.v * b.v, a.d * b.v + a.v * b.d}; break;
+      case FC_X_DIV: r = {a.v / b.v, a.d / b.v - a.v * b.d / (b.v * b.v)}; break;
+      case FC_X_NEG: r = {-a.v, -a.d}; break;
+      case FC_X_EXP: { double x = std::exp(a.v); r = {x, x * a.d}; } break;
+      case FC_X_LN: r = {std::log(a.v), a.d / a.v}; break;
+      case FC_X_SQRT: { double x = std::sqrt(a.v); r = {x, 0.5 * a.d / x}; } break;
+      case FC_X_ABS: r = {std::fabs(a.v), a.v < 0.0 ? -a.d : a.d}; break;
+      case FC_X_FLOOR: r = {std::floor(a.v), 0.0}; break;
+      case FC_X_SIN: r = {std::sin(a.v), std::cos(a.v) * a.d}; break;
+      case FC_X_COS: r = {std::cos(a.v), -std::sin(a.v) * a.d}; break;
+      case FC_X_TANH: { double x = std::tanh(a.v); r = {x, (1.0 - x * x) * a.d}; } break;
+      case FC_X_POW: {
+        double x = std::pow(a.v, b.v);
+        double d = b.v * std::pow(a.v, b.v - 1.0) * a.d;
+        if (nd[e.b].op != FC_X_CONST) d += x * std::log(a.v) * b.d;
+        r = {x, d};
+      } break;
+      case FC_X_MIN: r = (a.v <= b.v || b.v != b.v) ? a : b; if (a.v != a.v) r = b; break;  // f64::min ignores a NaN operand
+      default: r = (a.v >= b.v || b.v != b.v) ? a : b; if (a.v != a.v) r = b; break;
+    }
+    t[k] = r;
+  }
+  return t[n - 1];
+}
+
 // q, qd in PROGRAM order. dq (program order, may be null) receives d total / dq.
 inline Score score_program_order(const Program& P, const double* q, const int64_t* qd, double* dq) {
   Score sc;
@@ -150,6 +195,20 @@ inline Score score_program_order(const Program& P, const double* q, const int64_
   for (size_t oi = 0; oi < P.ops.size(); oi++) {
     const fc_op& op = P.ops[oi];
     if (op.kind == FC_OP_FACTOR) { sc.log_factors += op.value; continue; }
+    if (op.kind == FC_OP_FACTOR_EXPR) {
+      const fc_expr_node* nd = P.nodes.data() + op.expr_first;
+      double v = expr_forward(nd, op.expr_len, q, -1).v;
+      if (op.value != 0.0 && v != v) v = -INFINITY;
+      sc.log_factors += v;
+      if (dq && std::isfinite(v))
+        for (int k = 0; k < op.expr_len; k++)
+          if (nd[k].op == FC_X_LATENT) {
+            bool seen = false;  // one forward sweep per distinct latent
+            for (int k2 = 0; k2 < k; k2++) seen |= (nd[k2].op == FC_X_LATENT && nd[k2].slot == nd[k].slot);
+            if (!seen) dq[nd[k].slot] += expr_forward(nd, op.expr_len, q, nd[k].slot).d;
+          }
+      continue;
+    }
     bool is_sample = (op.kind == FC_OP_SAMPLE || op.kind == FC_OP_PLATE_SAMPLE);
     bool plate = (op.kind == FC_OP_PLATE_SAMPLE || op.kind == FC_OP_PLATE_OBSERVE);
     int64_t len = plate ? op.plate_len : 1;

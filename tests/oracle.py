@@ -29,6 +29,7 @@ def lib():
         L.fo_log1p_exp.argtypes = [C.c_double]
         L.fo_safe_ln.argtypes = [C.c_double]
         L.fo_program_create.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.fo_program_create_ex.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
         L.fo_program_destroy.argtypes = [C.c_void_p]
         L.fo_program_dims.argtypes = [C.c_void_p, ip, ip]
         L.fo_program_site.argtypes = [C.c_void_p, C.c_int64, C.c_int]
@@ -92,7 +93,8 @@ class OracleProgram:
         self._low = builder.lower()  # keep ctypes arrays (and numpy data) alive
         ops, n, cols, ncol = self._low
         h = C.c_void_p()
-        rc = lib().fo_program_create(C.cast(ops, C.c_void_p), n, C.cast(cols, C.c_void_p), ncol, C.byref(h))
+        nodes, n_nodes = builder.nodes_lowered
+        rc = lib().fo_program_create_ex(C.cast(ops, C.c_void_p), n, C.cast(cols, C.c_void_p), ncol, C.cast(nodes, C.c_void_p), n_nodes, C.byref(h))
         if rc != 0:
             raise _ir.FugueError(rc, "oracle program create")
         self.h = h

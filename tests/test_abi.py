@@ -28,7 +28,8 @@ def test_ctypes_struct_layouts_match_header():
     from fugue_b200 import _ir
     assert ctypes.sizeof(_ir.fc_term) == 24
     assert ctypes.sizeof(_ir.fc_param) == 3 * 24 + 8 + 16
-    assert ctypes.sizeof(_ir.fc_op) == 16 + 8 + 8 + 8 + 8 + 3 * ctypes.sizeof(_ir.fc_param)
+    assert ctypes.sizeof(_ir.fc_op) == 16 + 8 + 8 + 8 + 8 + 3 * ctypes.sizeof(_ir.fc_param) + 8  # + expr_first, expr_len
+    assert ctypes.sizeof(_ir.fc_expr_node) == 24
     assert ctypes.sizeof(_ir.fc_column) == 24
     assert ctypes.sizeof(_ir.fc_hmc_config) == 40
     assert ctypes.sizeof(_ir.fc_smc_config) == 24

@@ -25,7 +25,7 @@ REGRESSION = """
 """
 REG_DATA = '{"x": [-2, -1, 0, 1, 2], "y": [-2.1, -1.3, -0.4, 0.5, 1.2]}'
 
-KIND_SAMPLE, KIND_OBSERVE, KIND_FACTOR, KIND_PLATE_SAMPLE, KIND_PLATE_OBSERVE = 0, 1, 2, 3, 4
+KIND_SAMPLE, KIND_OBSERVE, KIND_FACTOR, KIND_PLATE_SAMPLE, KIND_PLATE_OBSERVE, KIND_FACTOR_EXPR = 0, 1, 2, 3, 4, 5
 
 
 def _kinds(cm):
@@ -108,14 +108,35 @@ def test_discrete_sites_sample_and_observe():
     assert np.array_equal(r, [4.0, 5.0])
 
 
-def test_pure_expression_evaluates_on_draws():
-    """dsl.rs:1293-1309, the return value: sigmoid(x) in (0,1)."""
-    cm = dsl.compile('let x <- sample(addr!("x"), Normal(0.0, 1.0)); factor(-0.5 * pow(2.0, 2.0)); pure(exp(x) / (1.0 + exp(x)))', "")
-    fac = [op for op in cm.builder.ops if op["kind"] == KIND_FACTOR][0]
-    assert fac["value"] == -2.0
+def test_factor_and_math_functions():
+    """dsl.rs:1293-1309: factor(-0.5 * pow(x - 1.0, 2.0)) is a log-weight computed from a latent -> a
+    FACTOR_EXPR op (expression nodes evaluated per chain on the device); pure(sigmoid(x)) in (0,1)."""
+    cm = dsl.compile('let x <- sample(addr!("x"), Normal(0.0, 1.0)); factor(-0.5 * pow(x - 1.0, 2.0)); pure(exp(x) / (1.0 + exp(x)))', "")
+    assert [k for k, _, _ in _kinds(cm)] == [KIND_SAMPLE, KIND_FACTOR_EXPR]
+    nodes = cm.builder.ops[1]["expr"].nodes
+    assert nodes[-1][0] == 4 and any(n[0] == 15 for n in nodes)  # MUL at the root, a POW inside
+    assert cm.builder.ops[1]["value"] == 1.0  # the playground's NaN -> -inf policy (dsl.rs:922-926)
     r = cm.return_value({"x": np.linspace(-3, 3, 7)})
     assert ((r > 0) & (r < 1)).all()
     assert abs(r[3] - 0.5) < 1e-15
+
+
+def test_constant_factor_folds():
+    cm = dsl.compile('let x <- sample(addr!("x"), Normal(0.0, 1.0)); factor(-0.5 * pow(2.0, 2.0)); pure(x)', "")
+    fac = [op for op in cm.builder.ops if op["kind"] == KIND_FACTOR][0]
+    assert fac["value"] == -2.0
+
+
+def test_symbolic_let_and_unrolled_latent_factors():
+    """A non-affine `let` stays symbolic (factor / pure only); a latent-dependent factor inside a loop
+    is unrolled into one scalar factor per iteration (the data element is a constant there)."""
+    cm = dsl.compile('let x <- sample(addr!("x"), Normal(0.0, 1.0)); let y = x * x; factor(-y);'
+                     'for i in 0..d.len() { factor(-0.5 * pow(x - d[i], 2.0)); } pure(y)', '{"d": [1.0, 2.0]}')
+    assert [k for k, _, _ in _kinds(cm)] == [KIND_SAMPLE, KIND_FACTOR_EXPR, KIND_FACTOR_EXPR, KIND_FACTOR_EXPR]
+    assert np.array_equal(cm.return_value({"x": np.array([2.0, 3.0])}), [4.0, 9.0])
+    with pytest.raises(FugueError) as e:  # ... but not as a distribution parameter
+        dsl.compile('let x <- sample(addr!("x"), Normal(0.0, 1.0)); let y = x * x; observe(addr!("o"), Normal(y, 1.0), 0.3); pure(x)', "")
+    assert e.value.code == 1000
 
 
 def test_non_affine_latent_expression_is_a_typed_rejection():
@@ -196,3 +217,16 @@ def test_invalid_params_total_weight_is_neg_inf_on_device():
     P = api.Program(cm)
     lp, ll, lf = P.logp(np.array([[0.3]]))
     assert (lp[0] + ll[0]) + lf[0] == -math.inf
+
+
+@pytest.mark.gpu
+def test_latent_factor_model_on_device():
+    """x ~ N(0,1) with factor(-0.5 (x-1)^2): the target is N(0.5, 0.5) (dsl.rs:1293-1309 run through
+    inference instead of one prior draw)."""
+    from fugue_b200 import api
+    cm = dsl.compile('let x <- sample(addr!("x"), Normal(0.0, 1.0)); factor(-0.5 * pow(x - 1.0, 2.0)); pure(exp(x) / (1.0 + exp(x)))', "")
+    draws, _, _ = api.hmc_chain(cm, n_samples=300, n_warmup=200, n_chains=256, seed=5)
+    x = draws[:, 0, :]
+    assert abs(x.mean() - 0.5) < 0.02 and abs(x.var() - 0.5) < 0.03
+    r = cm.return_value({"x": x})
+    assert ((r > 0) & (r < 1)).all()
