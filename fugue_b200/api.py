@@ -457,6 +457,7 @@ _sig("fc_smc_resample_particles", vp, C.c_int32, vp, vp)
 _sig("fc_smc_rejuvenate_particles", vp, C.c_double, C.c_uint64)
 _sig("fc_smc_shard_begin", vp, C.c_uint64)
 _sig("fc_smc_shard_tri", vp, C.c_double, vp)
+_sig("fc_smc_shard_tri_multi", vp, vp, C.c_int32, vp)
 _sig("fc_smc_shard_reweight", vp, C.c_double, C.c_double)
 _sig("fc_smc_shard_scan", vp, C.c_double, dp)
 _sig("fc_smc_shard_offspring", vp, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, vp, vp, vp, C.c_uint64)

@@ -293,6 +293,44 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, con
   nb_fold_update(acc, B, part, mode, first);
 }
 
+// K candidate increments in one pass over ll (uniform log_w): the sharded driver evaluates three
+// bisection levels (7 candidates) per round, so a next_beta search costs ~22 collectives instead of
+// ~55. Per-block partial sums [block][2K] (sum e, sum e^2 per candidate, shift m_k = lwc + d_k max ll);
+// the host folds the blocks in order.
+#define NB_MULTI_MAX 8
+struct MultiArgs { double d[NB_MULTI_MAX]; int K; };
+__global__ void __launch_bounds__(NB_THREADS) k_nb_multi(double lw_const, const double* __restrict__ ll, const Bisect* __restrict__ B, int64_t P,
+                                                         const __grid_constant__ MultiArgs A, double* __restrict__ part) {
+  const int K = A.K;
+  double m[NB_MULTI_MAX], s1[NB_MULTI_MAX], s2[NB_MULTI_MAX];
+#pragma unroll
+  for (int k = 0; k < NB_MULTI_MAX; k++) { m[k] = fma(A.d[k], B->max_ll, lw_const); s1[k] = 0.0; s2[k] = 0.0; }
+  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) {
+    const double a = __ldg(ll + i);
+#pragma unroll
+    for (int k = 0; k < NB_MULTI_MAX; k++) {
+      if (k < K) {
+        const double e = m[k] > d_neg_inf() ? exp_nonpos(fma(A.d[k], a, lw_const) - m[k]) : 0.0;
+        s1[k] += e;
+        s2[k] = fma(e, e, s2[k]);
+      }
+    }
+  }
+  __shared__ double sm[NB_THREADS / 32][2 * NB_MULTI_MAX];
+#pragma unroll
+  for (int k = 0; k < NB_MULTI_MAX; k++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s1[k] += __shfl_down_sync(0xffffffffu, s1[k], o); s2[k] += __shfl_down_sync(0xffffffffu, s2[k], o); }
+    if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5][2 * k] = s1[k]; sm[threadIdx.x >> 5][2 * k + 1] = s2[k]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * NB_MULTI_MAX) {
+    double t = 0.0;
+    for (int w = 0; w < NB_THREADS / 32; w++) t += sm[w][threadIdx.x];
+    part[(int64_t)blockIdx.x * 2 * NB_MULTI_MAX + threadIdx.x] = t;
+  }
+}
+
 // normalised weights after the reweight: log_w' = (log_w + d ll) - log_norm, w = exp(log_w')
 __global__ void k_reweight(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, double d, const Bisect* __restrict__ B,
                            double* __restrict__ out_log, double* __restrict__ out_w, int64_t P, double n_unif) {
@@ -760,6 +798,48 @@ int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3) {
   FC_CUDA(cudaMemcpyAsync(&t, s->tri.p + nb, sizeof(Tri), cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
   out3[0] = t.m; out3[1] = t.s1; out3[2] = t.s2;
+  return FC_OK;
+}
+
+// the same for up to 8 increments at once (uniform log_w only: the state every next_beta search runs
+// in): out[3k..3k+3) = (max, sum e, sum e^2) of candidate k. Returns FC_ERR_UNSUPPORTED_OP if log_w is
+// not uniform (the caller falls back to fc_smc_shard_tri).
+int32_t fc_smc_shard_tri_multi(fc_smc_session* s, const double* d_betas, int32_t K, double* out) {
+  using namespace fc;
+  if (!s || !d_betas || !out || K < 1 || K > NB_MULTI_MAX) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
+  if (!s->log_w_uniform) { set_error("log weights are not uniform"); return FC_ERR_UNSUPPORTED_OP; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  cudaStream_t st = s->P->stream;
+  const int64_t n = s->n;
+  const double lwc = -std::log(s->n_global > 0.0 ? s->n_global : (double)n);
+  const int nb = nb_blocks(n);
+  if (!s->shard_prepass_ok) {  // max(ll) and the bad flag: fc_smc_shard_tri's pre-pass
+    double tmp[3];
+    FC_TRY(fc_smc_shard_tri(s, 0.0, tmp));
+  }
+  if (s->shard_ll_bad) {
+    for (int k = 0; k < 3 * K; k++) out[k] = __builtin_nan("");
+    return FC_OK;
+  }
+  MultiArgs A;
+  A.K = K;
+  for (int k = 0; k < NB_MULTI_MAX; k++) A.d[k] = k < K ? d_betas[k] : 0.0;
+  FC_CUDA(s->scratch.reserve((int64_t)RDB * 2 * NB_MULTI_MAX + 16));
+  k_nb_multi<<<nb, NB_THREADS, 0, st>>>(lwc, s->ll.p, s->bis.p, n, A, s->scratch.p);
+  FC_KERNEL_CHECK();
+  s->P->n_kernel_launches += 1;
+  std::vector<double> h((size_t)nb * 2 * NB_MULTI_MAX);
+  Bisect hb;
+  FC_CUDA(cudaMemcpyAsync(h.data(), s->scratch.p, h.size() * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaMemcpyAsync(&hb, s->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  for (int k = 0; k < K; k++) {
+    double a = 0.0, b = 0.0;
+    for (int blk = 0; blk < nb; blk++) { a += h[(size_t)blk * 2 * NB_MULTI_MAX + 2 * k]; b += h[(size_t)blk * 2 * NB_MULTI_MAX + 2 * k + 1]; }
+    out[3 * k] = std::fma(d_betas[k], hb.max_ll, lwc);
+    out[3 * k + 1] = a;
+    out[3 * k + 2] = b;
+  }
   return FC_OK;
 }
 

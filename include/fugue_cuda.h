@@ -321,6 +321,8 @@ int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t ste
  *                    and the weights exp(log_w) the resampler sees; either pointer may be NULL */
 int32_t fc_smc_shard_begin(fc_smc_session* s, uint64_t n_total);
 int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3);
+/* up to 8 increments in one pass (uniform log_w only; else FC_ERR_UNSUPPORTED_OP): out[3k..3k+3) */
+int32_t fc_smc_shard_tri_multi(fc_smc_session* s, const double* d_betas, int32_t K, double* out);
 int32_t fc_smc_shard_reweight(fc_smc_session* s, double beta_new, double log_norm);
 int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value);
 int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo,
