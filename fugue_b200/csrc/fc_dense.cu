@@ -151,6 +151,8 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
   const int64_t row_end = min(A.N, row_begin + A.rows_per_split);
   const int n_tiles = (int)((row_end - row_begin + ST_ROWS - 1) / ST_ROWS);  // stages
 
+  __shared__ double s_exp_tab[32];  // 2^(j/32) for fast_exp_tab (made visible by the __syncthreads below)
+  if (MODE == GLM_BERN_SIGMOID) fast_exp_tab_init(s_exp_tab, tid);
   if (tid == 0) {
     for (int s = 0; s < DN_STAGES; s++) { mbar_init(&bars[s], 1); done[s] = 0; }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -337,7 +339,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
           if (MODE == GLM_BERN_SIGMOID) {
             // classification.rs:124-130: p = 1/(1+exp(-eta)); clamp; Bernoulli::log_prob.
             // Same formula, branch-free primitives (host guarantees 1e-300 < lo <= hi < 1).
-            double p = fast_rcp(1.0 + fast_exp(-sarg));
+            double p = fast_rcp(1.0 + fast_exp_tab(-sarg, s_exp_tab));
             bool inside = (p > lnk_lo && p < lnk_hi);
             if (VAL) {
               double pc = fmin(fmax(p, lnk_lo), lnk_hi);
@@ -580,9 +582,12 @@ int32_t dense_plate_launch(fc_program* P, PlateInfo& pl, const double* d_q, int6
 namespace fc {
 __global__ void k_debug_fastmath(int op, const double* __restrict__ x, int64_t n, double* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ double tab[32];
+  fast_exp_tab_init(tab, threadIdx.x);
+  __syncthreads();
   if (i >= n) return;
   double v = x[i];
-  out[i] = op == 0 ? fast_exp(v) : (op == 1 ? fast_log(v) : fast_rcp(v));
+  out[i] = op == 0 ? fast_exp(v) : (op == 1 ? fast_log(v) : (op == 2 ? fast_rcp(v) : fast_exp_tab(v, tab)));
 }
 }  // namespace fc
 extern "C" int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out) {

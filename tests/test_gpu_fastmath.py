@@ -15,12 +15,15 @@ def test_fastmath_accuracy():
     rng = np.random.default_rng(0)
     cases = {0: (np.concatenate([rng.uniform(-708, 708, 200000), rng.uniform(-40, 40, 200000), [0.0, -0.0, 1e-300, 800.0, -800.0]]), np.exp),
              1: (np.concatenate([rng.uniform(1e-10, 1, 200000), 10 ** rng.uniform(-300, 300, 200000), rng.uniform(0.9, 1.1, 50000)]), np.log),
-             2: (np.concatenate([rng.uniform(1, 2, 100000), 10 ** rng.uniform(-290, 290, 200000)]), lambda v: 1.0 / v)}
+             2: (np.concatenate([rng.uniform(1, 2, 100000), 10 ** rng.uniform(-290, 290, 200000)]), lambda v: 1.0 / v),
+             # op 3: the table-driven exp of the logistic kernel (32-entry 2^(j/32) table + degree-6 polynomial)
+             3: (np.concatenate([rng.uniform(-708, 708, 200000), rng.uniform(-40, 40, 400000), rng.uniform(-1e-3, 1e-3, 50000),
+                                 [0.0, -0.0, 1e-300, 800.0, -800.0, 708.0, -708.0, -707.99, 707.99]]), np.exp)}
     for op, (x, ref_fn) in cases.items():
         x = np.ascontiguousarray(x, dtype=np.float64)
         out = np.zeros_like(x)
         api.check(fn(op, x.ctypes.data, x.size, out.ctypes.data))
-        xr = np.clip(x, -708, 708) if op == 0 else x
+        xr = np.clip(x, -708, 708) if op in (0, 3) else x
         ref = ref_fn(xr.astype(np.longdouble)).astype(np.float64)
         ulp = np.spacing(np.abs(ref))
         err = np.abs(out - ref) / ulp
