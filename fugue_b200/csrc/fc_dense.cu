@@ -152,7 +152,9 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
   const int n_tiles = (int)((row_end - row_begin + ST_ROWS - 1) / ST_ROWS);  // stages
 
   __shared__ double s_exp_tab[32];  // 2^(j/32) for fast_exp_tab (made visible by the __syncthreads below)
+  __shared__ double s_log_tab[(MODE != GLM_GENERIC && VAL) ? 364 : 1];  // 1/c, ln c for fast_log_tab
   if (MODE == GLM_BERN_SIGMOID) fast_exp_tab_init(s_exp_tab, tid);
+  if (MODE != GLM_GENERIC && VAL) fast_log_tab_init(s_log_tab, tid, NTHR);
   if (tid == 0) {
     for (int s = 0; s < DN_STAGES; s++) { mbar_init(&bars[s], 1); done[s] = 0; }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -343,7 +345,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             bool inside = (p > lnk_lo && p < lnk_hi);
             if (VAL) {
               double pc = fmin(fmax(p, lnk_lo), lnk_hi);
-              lp = fast_log(yb[mt] ? pc : 1.0 - pc);
+              lp = fast_log_tab(yb[mt] ? pc : 1.0 - pc, s_log_tab);
             }
             if (GRAD) w = inside ? (yb[mt] ? (1.0 - p) : -p) : 0.0;  // NaN p: `inside` is false => w = 0
             if (VAL && sarg != sarg) { lp = d_neg_inf(); w = 0.0; }  // NaN eta => Bernoulli(NaN) => -inf
@@ -356,7 +358,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             const bool ok = (lam >= 1e-300 && lam <= 1e300) && kf >= 0.0;
             const double lamc = ok ? lam : 1.0;
             if (VAL) {
-              lp = kf * fast_log(lamc) - lam - ylg[mt];
+              lp = kf * fast_log_tab(lamc, s_log_tab) - lam - ylg[mt];
               if (lam > 700.0 && kf == 0.0) lp = -lam;
             }
             if (GRAD) w = (!VAL || d_fin(lp)) ? kf * fast_rcp(lamc) - 1.0 : 0.0;  // ok => lp is finite (lgamma column is)
@@ -583,11 +585,13 @@ namespace fc {
 __global__ void k_debug_fastmath(int op, const double* __restrict__ x, int64_t n, double* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   __shared__ double tab[32];
+  __shared__ double ltab[364];
   fast_exp_tab_init(tab, threadIdx.x);
+  fast_log_tab_init(ltab, threadIdx.x, blockDim.x);
   __syncthreads();
   if (i >= n) return;
   double v = x[i];
-  out[i] = op == 0 ? fast_exp(v) : (op == 1 ? fast_log(v) : (op == 2 ? fast_rcp(v) : fast_exp_tab(v, tab)));
+  out[i] = op == 0 ? fast_exp(v) : (op == 1 ? fast_log(v) : (op == 2 ? fast_rcp(v) : (op == 3 ? fast_exp_tab(v, tab) : fast_log_tab(v, ltab))));
 }
 }  // namespace fc
 extern "C" int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out) {

@@ -18,7 +18,11 @@ def test_fastmath_accuracy():
              2: (np.concatenate([rng.uniform(1, 2, 100000), 10 ** rng.uniform(-290, 290, 200000)]), lambda v: 1.0 / v),
              # op 3: the table-driven exp of the logistic kernel (32-entry 2^(j/32) table + degree-6 polynomial)
              3: (np.concatenate([rng.uniform(-708, 708, 200000), rng.uniform(-40, 40, 400000), rng.uniform(-1e-3, 1e-3, 50000),
-                                 [0.0, -0.0, 1e-300, 800.0, -800.0, 708.0, -708.0, -707.99, 707.99]]), np.exp)}
+                                 [0.0, -0.0, 1e-300, 800.0, -800.0, 708.0, -708.0, -707.99, 707.99]]), np.exp),
+             # op 4: the table-driven log (182 centres c = i/256, reciprocal + ln c tables, degree-7 log1p series)
+             4: (np.concatenate([rng.uniform(1e-10, 1, 200000), 10 ** rng.uniform(-300, 300, 200000), rng.uniform(0.9, 1.1, 100000),
+                                 1.0 + rng.uniform(-1e-9, 1e-9, 20000), rng.uniform(0.70, 0.72, 20000), rng.uniform(1.40, 1.43, 20000),
+                                 [1.0, 0.5, 2.0, 1e-10, 1.0 - 1e-10, 2.2250738585072014e-308]]), np.log)}
     for op, (x, ref_fn) in cases.items():
         x = np.ascontiguousarray(x, dtype=np.float64)
         out = np.zeros_like(x)
@@ -27,6 +31,6 @@ def test_fastmath_accuracy():
         ref = ref_fn(xr.astype(np.longdouble)).astype(np.float64)
         ulp = np.spacing(np.abs(ref))
         err = np.abs(out - ref) / ulp
-        if op == 1:  # near log(1) = 0 the bound is absolute (|f| ulp), as for any log
+        if op in (1, 4):  # near log(1) = 0 the bound is absolute (|f| ulp), as for any log
             err = np.minimum(err, np.abs(out - ref) / 2.3e-16)
         assert err.max() <= 2.0, (op, err.max(), x[err.argmax()])
