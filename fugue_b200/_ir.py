@@ -21,7 +21,7 @@ FC_OP_SAMPLE, FC_OP_OBSERVE, FC_OP_FACTOR, FC_OP_PLATE_SAMPLE, FC_OP_PLATE_OBSER
 FC_EXPR_MAX_NODES = 64
 FC_T_F64, FC_T_I64, FC_T_U64, FC_T_USIZE, FC_T_BOOL = range(5)
 (FC_TERM_NONE, FC_TERM_CONST, FC_TERM_LATENT, FC_TERM_LATENT_X, FC_TERM_DENSE, FC_TERM_GATHER,
- FC_TERM_SELECT2, FC_TERM_PLATE_LATENT) = range(8)
+ FC_TERM_SELECT2, FC_TERM_PLATE_LATENT, FC_TERM_SCALED) = range(9)
 FC_LINK_IDENTITY, FC_LINK_EXP, FC_LINK_SIGMOID_CLAMPED, FC_LINK_CLAMP = range(4)
 FC_COL_F64, FC_COL_U8, FC_COL_U32, FC_COL_I64 = range(4)
 FC_RESAMPLE_MULTINOMIAL, FC_RESAMPLE_SYSTEMATIC, FC_RESAMPLE_STRATIFIED = range(3)
@@ -115,19 +115,56 @@ class Expr:
 
     __radd__ = lambda self, o: as_expr(o).__add__(self)
 
+    def is_affine(self):
+        """const + coef * latent + ... with the identity link (what scale() / negation keep affine)."""
+        return self.link == FC_LINK_IDENTITY and not getattr(self, "discrete", False) and all(k in (FC_TERM_CONST, FC_TERM_LATENT, FC_TERM_SCALED) for k, *_ in self.terms)
+
+    def scale(self, c):
+        """c * (const + coef * latent + ...): CONST terms are multiplied, latents become SCALED terms."""
+        c = float(c)
+        out = []
+        for k, slot, sb, col, v in self.terms:
+            if k == FC_TERM_CONST:
+                out.append((FC_TERM_CONST, 0, 0, 0, c * v))
+            elif k == FC_TERM_LATENT:
+                out.append((FC_TERM_SCALED, slot, 0, 0, c))
+            else:
+                out.append((FC_TERM_SCALED, slot, 0, 0, c * v))
+        return Expr(out)
+
     def __mul__(self, col):
-        if not isinstance(col, Column):  # latent * number / latent * latent: a general (factor) expression
-            return Sym.apply(FC_X_MUL, self, col)
-        assert len(self.terms) == 1 and self.terms[0][0] == FC_TERM_LATENT
-        return Expr([(FC_TERM_LATENT_X, self.terms[0][1], 0, col.cid, 0.0)])
+        if isinstance(col, Column):
+            assert len(self.terms) == 1 and self.terms[0][0] == FC_TERM_LATENT
+            return Expr([(FC_TERM_LATENT_X, self.terms[0][1], 0, col.cid, 0.0)])
+        if isinstance(col, (int, float)) and self.is_affine():
+            return self.scale(col)
+        return Sym.apply(FC_X_MUL, self, col)  # latent * latent, ...: a general (factor) expression
+
+    def __rmul__(self, o):
+        return self.scale(o) if (isinstance(o, (int, float)) and self.is_affine()) else Sym.apply(FC_X_MUL, o, self)
+
+    def __neg__(self):
+        return self.scale(-1.0) if self.is_affine() else Sym.apply(FC_X_NEG, self)
+
+    def __sub__(self, o):
+        if isinstance(o, (int, float)) and self.is_affine():
+            return Expr(self.terms + [(FC_TERM_CONST, 0, 0, 0, -float(o))])
+        if isinstance(o, Expr) and not isinstance(o, Sym) and self.is_affine() and o.is_affine() and len(self.terms) + len(o.terms) <= 3:
+            return Expr(self.terms + o.scale(-1.0).terms)
+        return Sym.apply(FC_X_SUB, self, o)
+
+    def __rsub__(self, o):
+        if isinstance(o, (int, float)) and self.is_affine():
+            return Expr([(FC_TERM_CONST, 0, 0, 0, float(o))] + self.scale(-1.0).terms)
+        return Sym.apply(FC_X_SUB, o, self)
+
+    def __truediv__(self, o):
+        if isinstance(o, (int, float)) and o != 0 and self.is_affine():
+            return self.scale(1.0 / float(o))
+        return Sym.apply(FC_X_DIV, self, o)
 
     # everything that is not link(term + term + term) becomes a general expression (factor(..) only)
-    __rmul__ = lambda self, o: Sym.apply(FC_X_MUL, o, self)
-    __sub__ = lambda self, o: Sym.apply(FC_X_SUB, self, o)
-    __rsub__ = lambda self, o: Sym.apply(FC_X_SUB, o, self)
-    __truediv__ = lambda self, o: Sym.apply(FC_X_DIV, self, o)
     __rtruediv__ = lambda self, o: Sym.apply(FC_X_DIV, o, self)
-    __neg__ = lambda self: Sym.apply(FC_X_NEG, self)
     __pow__ = lambda self, o: Sym.apply(FC_X_POW, self, o)
 
 
@@ -144,11 +181,13 @@ class Sym:
         if isinstance(x, Sym):
             return x
         if isinstance(x, Expr):  # a scalar parameter expression: link(const + latent + ...)
-            if getattr(x, "discrete", False) or any(k not in (FC_TERM_CONST, FC_TERM_LATENT) for k, *_ in x.terms):
+            if getattr(x, "discrete", False) or any(k not in (FC_TERM_CONST, FC_TERM_LATENT, FC_TERM_SCALED) for k, *_ in x.terms):
                 raise FugueError(FC_ERR_UNSUPPORTED_OP, "only continuous scalar latents and constants can enter a factor expression")
             acc = None
             for k, slot, _, _, c in x.terms:
-                t = Sym([(FC_X_LATENT, 0, 0, slot, 0.0)]) if k == FC_TERM_LATENT else Sym([(FC_X_CONST, 0, 0, 0, float(c))])
+                t = Sym([(FC_X_LATENT, 0, 0, slot, 0.0)]) if k != FC_TERM_CONST else Sym([(FC_X_CONST, 0, 0, 0, float(c))])
+                if k == FC_TERM_SCALED:
+                    t = Sym.apply(FC_X_MUL, float(c), t)
                 acc = t if acc is None else Sym.apply(FC_X_ADD, acc, t)
             if x.link == FC_LINK_EXP:
                 acc = Sym.apply(FC_X_EXP, acc)

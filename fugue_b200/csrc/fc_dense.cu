@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
       for (int t = 0; t < 3; t++) {
         const DTerm& tm = op.p[A.dj].t[t];
         if (tm.kind == FC_TERM_CONST) s += tm.c;
-        else if (tm.kind == FC_TERM_LATENT && ok) s += A.q[(int64_t)tm.row * C + c];
+        else if (tm.kind == FC_TERM_LATENT && ok) s += tm.c * A.q[(int64_t)tm.row * C + c];
       }
       off[nt][j] = s;
 #pragma unroll
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
           for (int t = 0; t < 3; t++) {
             const DTerm& tm = op.p[pj].t[t];
             if (tm.kind == FC_TERM_CONST) sp += tm.c;
-            else if (tm.kind == FC_TERM_LATENT && ok) sp += A.q[(int64_t)tm.row * C + c];
+            else if (tm.kind == FC_TERM_LATENT && ok) sp += tm.c * A.q[(int64_t)tm.row * C + c];
           }
           po[pj][nt][j] = link_apply(op.p[pj].link, sp, op.p[pj].lo, op.p[pj].hi, pdl[pj][nt][j]);
         }
@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             for (int pj = 0; pj < 3; pj++)
 #pragma unroll
               for (int t = 0; t < 3; t++)
-                if (A.acc.a_idx[pj][t] == a) v += (pj == A.dj) ? v_w : v_p[pj];
+                if (A.acc.a_idx[pj][t] == a) v += ((pj == A.dj) ? v_w : v_p[pj]) * (op.p[pj].t[t].kind == FC_TERM_LATENT ? op.p[pj].t[t].c : 1.0);
             part[(int64_t)a * C + c] = v;
           }
         }

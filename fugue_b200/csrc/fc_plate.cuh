@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
       for (int t = 0; t < 3; t++) {
         const DTerm& tm = op.p[j].t[t];
         if (tm.kind == FC_TERM_CONST) s += tm.c;
-        else if (tm.kind == FC_TERM_LATENT) s += A.q[(int64_t)tm.row * C + c];
+        else if (tm.kind == FC_TERM_LATENT) s += tm.c * A.q[(int64_t)tm.row * C + c];
       }
       base[j] = op.p[j].invariant ? apply_link(op.p[j].link, s, op.p[j].lo, op.p[j].hi, dl[j]) : s;
     }
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
 #pragma unroll
         for (int t = 0; t < 3; t++) {
           const bool is0 = K0 && j == j0 && t == F.et[0], is1 = K1 && j == j1 && t == F.et[1];
-          if (A.acc.a_idx[j][t] == a) v += is0 ? acc_e[0] : (is1 ? acc_e[1] : acc_c[j]);
+          if (A.acc.a_idx[j][t] == a) v += is0 ? acc_e[0] : (is1 ? acc_e[1] : acc_c[j] * (op.p[j].t[t].kind == FC_TERM_LATENT ? op.p[j].t[t].c : 1.0));
           if (A.acc.b_idx[j][t] == a) v += is0 ? acc_eb[0] : (is1 ? acc_eb[1] : 0.0);
         }
     }

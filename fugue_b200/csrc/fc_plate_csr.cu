@@ -50,13 +50,13 @@ __global__ void __launch_bounds__(CSR_TX, 4) k_plate_csr_normal(const __grid_con
   for (int t = 0; t < 3; t++) {
     const DTerm& tm = op.p[0].t[t];
     if (tm.kind == FC_TERM_CONST) base0 += tm.c;
-    else if (tm.kind == FC_TERM_LATENT) base0 += A.q[(int64_t)tm.row * C + c];
+    else if (tm.kind == FC_TERM_LATENT) base0 += tm.c * A.q[(int64_t)tm.row * C + c];
   }
 #pragma unroll
   for (int t = 0; t < 3; t++) {
     const DTerm& tm = op.p[1].t[t];
     if (tm.kind == FC_TERM_CONST) sig_s += tm.c;
-    else if (tm.kind == FC_TERM_LATENT) sig_s += A.q[(int64_t)tm.row * C + c];
+    else if (tm.kind == FC_TERM_LATENT) sig_s += tm.c * A.q[(int64_t)tm.row * C + c];
   }
   double dl1 = 1.0;
   const double sigma = apply_link(op.p[1].link, sig_s, op.p[1].lo, op.p[1].hi, dl1);
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(CSR_TX, 4) k_plate_csr_normal(const __grid_con
             if (A.acc.a_idx[j][t] != a) continue;
             if (j == 0 && HAS_X && t == F.xt) v += acc_x;
             else if (j == 0 && t == F.gt) v += 0.0;  // gather rows are written directly
-            else v += j == 0 ? acc_w0 : acc_w1;
+            else v += (j == 0 ? acc_w0 : acc_w1) * (op.p[j].t[t].kind == FC_TERM_LATENT ? op.p[j].t[t].c : 1.0);
           }
       }
       A.part[((int64_t)blockIdx.y * n_acc + a) * C + c_raw] = v;

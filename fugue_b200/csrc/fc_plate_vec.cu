@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(PLV_THREADS, 2) k_plate_vec(const __grid_const
           double v[4];
           ld4(q0 + (int64_t)tm.row * C, v);
 #pragma unroll
-          for (int k = 0; k < 4; k++) s[k] += v[k];
+          for (int k = 0; k < 4; k++) s[k] += tm.c * v[k];
         }
       }
       if (op.p[j].invariant) {

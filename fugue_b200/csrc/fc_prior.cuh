@@ -96,7 +96,7 @@ __device__ inline double eval_param_value(const DOp& op, int j, int64_t i, const
     double v = 0.0;
     switch (tm.kind) {
       case FC_TERM_CONST: v = tm.c; break;
-      case FC_TERM_LATENT: v = q[(int64_t)tm.row * C + c]; break;
+      case FC_TERM_LATENT: v = tm.c * q[(int64_t)tm.row * C + c]; break;
       case FC_TERM_LATENT_X: v = q[(int64_t)tm.row * C + c] * ((const double*)tm.col.ptr)[i]; break;
       case FC_TERM_GATHER: {
         long long gi;

@@ -183,7 +183,7 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
         const fc_term& tm = op.param[j].term[t];
         if (tm.kind == FC_TERM_NONE) continue;
         nterms++;
-        if (tm.kind < FC_TERM_NONE || tm.kind > FC_TERM_PLATE_LATENT) { set_error("op %zu: bad term kind %d", i, tm.kind); return FC_ERR_INVALID_ARGUMENT; }
+        if (tm.kind < FC_TERM_NONE || tm.kind > FC_TERM_SCALED) { set_error("op %zu: bad term kind %d", i, tm.kind); return FC_ERR_INVALID_ARGUMENT; }
         bool elem_term = tm.kind == FC_TERM_LATENT_X || tm.kind == FC_TERM_DENSE || tm.kind == FC_TERM_GATHER || tm.kind == FC_TERM_SELECT2 || tm.kind == FC_TERM_PLATE_LATENT;
         if (elem_term && !plate) { set_error("op %zu ('%s'): per-element term %d outside a plate", i, P->names[i].c_str(), tm.kind); return FC_ERR_UNSUPPORTED_OP; }
         int64_t span = 1;
@@ -324,7 +324,9 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
         DTerm& dt = dp.t[t];
         dt.kind = tm.kind; dt.c = tm.c; dt.slot = tm.slot;
         switch (tm.kind) {
-          case FC_TERM_LATENT: dt.row = P->crow[tm.slot]; if (plate) am.a_idx[j][t] = (int8_t)acc_of(dt.row); break;
+          // on the device a LATENT term is coef * q[row]: coef = 1 for LATENT, c for SCALED
+          case FC_TERM_LATENT: dt.c = 1.0; dt.row = P->crow[tm.slot]; if (plate) am.a_idx[j][t] = (int8_t)acc_of(dt.row); break;
+          case FC_TERM_SCALED: dt.kind = FC_TERM_LATENT; dt.c = tm.c; dt.row = P->crow[tm.slot]; if (plate) am.a_idx[j][t] = (int8_t)acc_of(dt.row); break;
           case FC_TERM_LATENT_X: dt.row = P->crow[tm.slot]; dt.col = P->cols[tm.col]; dp.invariant = 0; am.a_idx[j][t] = (int8_t)acc_of(dt.row); break;
           case FC_TERM_SELECT2:
             dt.row = P->crow[tm.slot]; dt.row_b = P->crow[tm.slot_b]; dt.dslot = (int32_t)P->dslot0[tm.col]; dp.invariant = 0;

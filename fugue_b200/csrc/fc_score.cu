@@ -113,7 +113,7 @@ __global__ void k_scalar(const DOp* __restrict__ ops, int n_ops, const int32_t* 
       for (int t = 0; t < 3; t++) {
         const DTerm& tm = pr.t[t];
         if (tm.kind == FC_TERM_NONE) continue;
-        double v = tm.kind == FC_TERM_CONST ? tm.c : q[(int64_t)tm.row * C + c];
+        double v = tm.kind == FC_TERM_CONST ? tm.c : tm.c * q[(int64_t)tm.row * C + c];  // LATENT: coef * q
         s = first ? v : s + v;
         first = false;
       }
@@ -138,7 +138,7 @@ __global__ void k_scalar(const DOp* __restrict__ ops, int n_ops, const int32_t* 
         double w = dpj[j] * dl[j];
         if (w != 0.0)
           for (int t = 0; t < 3; t++)
-            if (op.p[j].t[t].kind == FC_TERM_LATENT) grad[(int64_t)op.p[j].t[t].row * C + c] += w;
+            if (op.p[j].t[t].kind == FC_TERM_LATENT) grad[(int64_t)op.p[j].t[t].row * C + c] += w * op.p[j].t[t].c;
       }
     }
   }
@@ -182,6 +182,7 @@ __global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate(const __grid_constant
         if (tm.kind == FC_TERM_CONST) tva[j][t] = tm.c;
         else if (tm.kind == FC_TERM_LATENT || tm.kind == FC_TERM_LATENT_X || tm.kind == FC_TERM_SELECT2) {
           tva[j][t] = A.q[(int64_t)tm.row * C + c];
+          if (tm.kind == FC_TERM_LATENT) tva[j][t] *= tm.c;  // coef * q
           if (tm.kind == FC_TERM_SELECT2) tvb[j][t] = A.q[(int64_t)tm.row_b * C + c];
         }
       }
@@ -327,7 +328,7 @@ __global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate(const __grid_constant
             for (int t = 0; t < 3; t++) {
               const DTerm& tm = op.p[j].t[t];
               switch (tm.kind) {
-                case FC_TERM_LATENT: acc_a[j][t] += w; break;
+                case FC_TERM_LATENT: acc_a[j][t] += w * tm.c; break;
                 case FC_TERM_LATENT_X: acc_a[j][t] += w * lx[j][t]; break;
                 case FC_TERM_SELECT2: if (zsel[j][t]) acc_b[j][t] += w; else acc_a[j][t] += w; break;
                 case FC_TERM_GATHER:

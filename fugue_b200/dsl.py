@@ -549,6 +549,8 @@ class _Lowering:
                 return -_as_f64(a)
             if isinstance(a, _Elem):
                 return _Elem(-a.arr)
+            if isinstance(a, _ir.Expr) and a.is_affine():
+                return a.scale(-1.0)
             raise _unsupported("negated latent expression")
         if t == "bin":
             sig = self.sigmoid_pattern(e, env)
@@ -574,13 +576,7 @@ class _Lowering:
             if _is_const(v) or isinstance(v, _ir.Sym):
                 return v
             if isinstance(v, _ir.Expr):
-                if v.link != _ir.FC_LINK_IDENTITY or getattr(v, "discrete", False) or any(k not in (_ir.FC_TERM_CONST, _ir.FC_TERM_LATENT) for k, *_ in v.terms):
-                    raise _unsupported("factor() of a discrete latent or of a linked parameter expression")
-                out = None
-                for k, slot, _, _, c in v.terms:
-                    term = _ir.Sym([(_ir.FC_X_LATENT, 0, 0, slot, 0.0)]) if k == _ir.FC_TERM_LATENT else c
-                    out = term if out is None else _ir.Sym.apply(_ir.FC_X_ADD, out, term)
-                return out
+                return _ir.Sym.lift(v)  # const + coef * latent + ..., link applied (typed error for discrete / per-element terms)
             raise _unsupported("this value cannot enter a factor expression")
         if t in ("len", "index"):
             v = self.ev(e, env)
@@ -637,33 +633,38 @@ class _Lowering:
             ya = y.arr if isinstance(y, _Elem) else _as_f64(y)
             with np.errstate(all="ignore"):
                 return _Elem({"+": np.add, "-": np.subtract, "*": np.multiply, "/": np.divide}[op](xa, ya))
-        # at least one latent expression, the other a constant or a latent expression
-        if op == "+" or op == "-":
-            if isinstance(x, _ir.Expr) and isinstance(y, _ir.Expr):
-                if op == "-":
-                    raise _unsupported("difference of latent expressions")
-                if x.link != _ir.FC_LINK_IDENTITY or y.link != _ir.FC_LINK_IDENTITY:
-                    raise _unsupported("sum of linked expressions")
-                return _ir.Expr(x.terms + y.terms)
-            if isinstance(x, _ir.Expr):
-                c = _as_f64(y)
-                if x.link != _ir.FC_LINK_IDENTITY:
-                    raise _unsupported("arithmetic after a link function")
-                return _ir.Expr(x.terms + [(_ir.FC_TERM_CONST, 0, 0, 0, c if op == "+" else -c)])
+        # at least one latent expression, the other a constant or a latent expression: affine forms
+        # const + coef * latent + ... stay parameter expressions (`let mu = 2.0 * p - 1.0`, dsl.rs:12-13)
+        xe, ye = isinstance(x, _ir.Expr), isinstance(y, _ir.Expr)
+        for v in (x, y):
+            if isinstance(v, _ir.Expr) and (v.link != _ir.FC_LINK_IDENTITY or getattr(v, "discrete", False)):
+                raise _unsupported("arithmetic after a link function / on a discrete latent")
+        if op in "+-":
+            a = x if xe else _ir.Expr([(_ir.FC_TERM_CONST, 0, 0, 0, _as_f64(x))])
+            b = y if ye else _ir.Expr([(_ir.FC_TERM_CONST, 0, 0, 0, _as_f64(y))])
             if op == "-":
-                raise _unsupported("constant minus latent expression")
-            if y.link != _ir.FC_LINK_IDENTITY:
-                raise _unsupported("arithmetic after a link function")
-            return _ir.Expr([(_ir.FC_TERM_CONST, 0, 0, 0, _as_f64(x))] + y.terms)
+                if not b.is_affine():
+                    raise _unsupported("subtracting a per-element latent term")
+                b = b.scale(-1.0)
+            out = _ir.Expr(a.terms + b.terms)
+            # fold the constants into one term (keeps `a*x - b + c` within three terms)
+            consts = [t for t in out.terms if t[0] == _ir.FC_TERM_CONST]
+            if len(consts) > 1 and len(out.terms) > 3:
+                first = out.terms.index(consts[0])
+                rest = [t for t in out.terms if t[0] != _ir.FC_TERM_CONST]
+                rest.insert(min(first, len(rest)), (_ir.FC_TERM_CONST, 0, 0, 0, sum(t[4] for t in consts)))
+                out = _ir.Expr(rest)
+            if len(out.terms) > 3:
+                raise _unsupported("more than three affine terms in one expression")
+            return out
         if op == "*":
-            lat, c = (x, y) if isinstance(x, _ir.Expr) else (y, x)
-            if _is_const(c) and _bare_latent(lat):
-                if _as_f64(c) == 1.0:
-                    return lat
-                if self.plate_n is not None:  # inside a plate a constant factor is a constant column
-                    return _ir.Expr([(_ir.FC_TERM_LATENT_X, lat.terms[0][1], 0, self.column(np.full(self.plate_n, _as_f64(c))).cid, 0.0)])
-            raise _unsupported("product involving a latent expression")
-        raise _unsupported("division involving a latent expression")
+            lat, c = (x, y) if xe else (y, x)
+            if _is_const(c) and lat.is_affine():
+                return lat if _as_f64(c) == 1.0 else lat.scale(_as_f64(c))
+            raise _unsupported("product of latent expressions")
+        if xe and _is_const(y) and _as_f64(y) != 0.0 and x.is_affine():
+            return x.scale(1.0 / _as_f64(y))
+        raise _unsupported("division by a latent expression")
 
     def call(self, name, args):
         if all(_is_const(a) for a in args):

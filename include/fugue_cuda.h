@@ -60,7 +60,8 @@ enum {
   FC_TERM_GATHER = 5,     /* q[slot + idx[i]]               (col: index column)           */
   FC_TERM_SELECT2 = 6,    /* z==0 ? q[slot] : q[slot_b]     z = plate-discrete site i of  */
                           /*   PLATE_SAMPLE op `col` (an op index, not a column)          */
-  FC_TERM_PLATE_LATENT = 7/* q[slot + i]  (element i of a continuous plate)               */
+  FC_TERM_PLATE_LATENT = 7,/* q[slot + i]  (element i of a continuous plate)              */
+  FC_TERM_SCALED = 8      /* c * q[slot]   (`let mu = 2.0 * p - 1.0`, dsl.rs:12-13)        */
 };
 enum { FC_LINK_IDENTITY = 0, FC_LINK_EXP = 1, FC_LINK_SIGMOID_CLAMPED = 2, FC_LINK_CLAMP = 3 };
 

@@ -99,6 +99,7 @@ struct ParamEval {
       switch (tm.kind) {
         case FC_TERM_CONST: v = tm.c; break;
         case FC_TERM_LATENT: v = q[tm.slot]; break;
+        case FC_TERM_SCALED: v = tm.c * q[tm.slot]; break;
         case FC_TERM_LATENT_X: v = q[tm.slot] * col_f64(P.cols[tm.col], i); break;
         case FC_TERM_DENSE: {  // classification.rs:119-122: linear_pred = 0.0; += coef*x
           const Column& X = P.cols[tm.col];
@@ -133,6 +134,7 @@ struct ParamEval {
       const fc_term& tm = pr.term[t];
       switch (tm.kind) {
         case FC_TERM_LATENT: dq[tm.slot] += w; break;
+        case FC_TERM_SCALED: dq[tm.slot] += w * tm.c; break;
         case FC_TERM_LATENT_X: dq[tm.slot] += w * col_f64(P.cols[tm.col], i); break;
         case FC_TERM_DENSE: { const Column& X = P.cols[tm.col]; for (int k = 0; k < X.width; k++) dq[tm.slot + k] += w * col_f64(X, i, k); } break;
         case FC_TERM_GATHER: dq[tm.slot + col_i64(P.cols[tm.col], i)] += w; break;

@@ -230,3 +230,62 @@ def test_latent_factor_model_on_device():
     assert abs(x.mean() - 0.5) < 0.02 and abs(x.var() - 0.5) < 0.03
     r = cm.return_value({"x": x})
     assert ((r > 0) & (r < 1)).all()
+
+
+GRAMMAR_EXAMPLE = """
+    let p <- sample(addr!("p"), Beta(2.0, 2.0));
+    let mu = 2.0 * p - 1.0;
+    for i in 0..y.len() {
+        observe(addr!("y", i), Normal(mu, 0.8), y[i]);
+    }
+    factor(-0.5 * mu * mu);
+    pure(p)
+"""
+
+
+def test_grammar_doc_example_lowers_with_a_scaled_latent():
+    """The module's own grammar example (dsl.rs:11-19): `let mu = 2.0 * p - 1.0` is an AFFINE function of
+    a latent and stays a parameter expression (a SCALED term + a constant), usable by the plate and by
+    the latent-dependent factor."""
+    import oracle
+    cm = dsl.compile(GRAMMAR_EXAMPLE, '{"y": [0.1, 0.2, 0.3]}')
+    assert [k for k, _, _ in _kinds(cm)] == [KIND_SAMPLE, KIND_PLATE_OBSERVE, KIND_FACTOR_EXPR]
+    assert cm.builder.ops[1]["dist"].params[0].terms == [(8, 0, 0, 0, 2.0), (1, 0, 0, 0, -1.0)]  # SCALED(2, p), CONST(-1)
+    O = oracle.OracleProgram(cm.builder)
+    q = np.array([[0.3, 0.8]])
+    lp, ll, lf, g = O.logp(q, grad=True)
+    mu, y = 2 * q[0] - 1, np.array([0.1, 0.2, 0.3])
+    assert np.allclose(ll, [(-0.5 * ((y - m) / 0.8) ** 2 - math.log(0.8) - 0.5 * math.log(2 * math.pi)).sum() for m in mu], rtol=1e-14)
+    assert np.allclose(lf, -0.5 * mu * mu, rtol=1e-14)
+    tot = lambda qq: sum(O.logp(qq))
+    assert np.allclose(g[0], (tot(q + 1e-6) - tot(q - 1e-6)) / 2e-6, rtol=1e-6)
+
+
+def test_affine_forms_of_latents():
+    src = ('let a <- sample(addr!("a"), Normal(0.0, 1.0)); let b <- sample(addr!("b"), Normal(0.0, 1.0));'
+           'let m = 0.5 * a - b / 4.0 + 1.5; let z <- sample(addr!("z"), Normal(-m, 1.0)); pure(z)')
+    cm = dsl.compile(src, "")
+    terms = cm.builder.ops[2]["dist"].params[0].terms
+    assert terms == [(8, 0, 0, 0, -0.5), (8, 1, 0, 0, 0.25), (1, 0, 0, 0, -1.5)]
+
+
+@pytest.mark.gpu
+def test_grammar_doc_example_on_device():
+    import oracle
+    from fugue_b200 import api
+    cm = dsl.compile(GRAMMAR_EXAMPLE, '{"y": [0.1, 0.2, 0.3, -0.4, 0.9]}')
+    O, P = oracle.OracleProgram(cm.builder), api.Program(cm)
+    q = np.linspace(0.05, 0.95, 19)[None, :]
+    olp, oll, olf, og = O.logp(q, grad=True)
+    lp, ll, lf = P.logp(q)
+    for a, b in ((lp, olp), (ll, oll), (lf, olf)):
+        assert np.all(np.abs(a - b) <= 1e-10 * np.maximum(np.abs(a), np.abs(b)))
+    tot, g = P.logp_grad(q)
+    assert np.all(np.abs(g - og) <= 1e-10 * np.maximum(np.abs(g), np.abs(og)) + 1e-13)
+    draws, _, _, _ = api.adaptive_mcmc_chain(cm, n_samples=400, n_warmup=300, n_chains=256, seed=1, thin=4)
+    p = draws[:, 0, :]
+    assert ((p > 0) & (p < 1)).all()
+    # posterior mean by quadrature of the same density
+    grid = np.linspace(1e-4, 1 - 1e-4, 4001)[None, :]
+    w = np.exp(sum(O.logp(grid)) - sum(O.logp(grid)).max())
+    assert abs(p.mean() - (w * grid[0]).sum() / w.sum()) < 0.01

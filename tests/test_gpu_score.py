@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import oracle
 from fugue_b200 import models
-from fugue_b200.model import ModelBuilder, Normal, Gamma, Beta, Bernoulli, Poisson, StudentT, Exponential, dense, exp
+from fugue_b200.model import ModelBuilder, Normal, Gamma, Beta, Bernoulli, Poisson, StudentT, Exponential, dense, exp, sigmoid_clamped
 
 pytestmark = pytest.mark.gpu
 REL = 1e-10
@@ -174,3 +174,33 @@ def test_typed_errors():
         P.check_structure(m2)
     assert e.value.code == _ir.FC_ERR_UNEXPECTED_MODEL_STRUCTURE
     P.check_structure(models.linear_regression()[0])
+
+
+def test_scaled_latent_terms_in_every_kernel_family():
+    """FC_TERM_SCALED (c * latent) as a chain-constant part of scalar ops, generic / fast / CSR plates
+    and of a dense GLM offset: value and gradient against the oracle."""
+    from fugue_b200 import api
+    rng = np.random.default_rng(3)
+    N, G, D, Cn = 240, 12, 5, 37
+    m = ModelBuilder()
+    a = m.sample("a", Normal(0.0, 2.0))
+    s = m.sample("s", Gamma(2.0, 2.0))
+    m.sample("z", Normal(2.0 * a - 1.0, 0.5 * s + 0.1))                          # scalar op
+    al = m.plate_sample("al", G, Normal(-0.5 * a, 1.0))                           # fast plate (sample), scaled prior mean
+    gid = m.data(rng.integers(0, G, N).astype(np.uint32))
+    xc = m.data(rng.normal(size=N))
+    m.plate_observe("y", Normal(al[gid] + 1.5 * a, 0.25 * s + 0.2), m.data(rng.normal(size=N)))   # CSR plate, scaled sigma
+    b = m.plate_sample("b", D, Normal(0.0, 1.0))
+    X = m.data(rng.normal(size=(N, D)))
+    m.plate_observe("k", Bernoulli(sigmoid_clamped(dense(X, b) + 0.7 * a, 1e-10, 1 - 1e-10)), m.data((rng.random(N) < 0.5).astype(np.uint8)))
+    m.plate_observe("w", Normal(3.0 * a + a * xc, s), m.data(rng.normal(size=N)))  # LATENT_X + scaled latent
+    O, P = oracle.OracleProgram(m), api.Program(m)
+    q = rng.normal(0, 0.5, (O.d_cont, Cn))
+    q[O.sites().index("s")] = rng.uniform(0.5, 2.0, Cn)
+    olp, oll, olf, og = O.logp(q, grad=True)
+    lp, ll, lf = P.logp(q)
+    assert close(lp, olp).all() and close(ll, oll).all()
+    tot, g = P.logp_grad(q)
+    assert close(tot, (olp + oll) + olf).all()
+    scale = np.abs(og).max(axis=0, keepdims=True) * np.ones_like(og) * 1e-4
+    assert close(g, og, scale=scale).all(), np.abs(g - og).max()
