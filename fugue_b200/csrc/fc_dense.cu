@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
 #pragma unroll
       for (int mt = 0; mt < 4; mt++) yv_[mt] = (double)__ldg((const long long*)y_ptr + ri[mt]);
     }
-    if (lgam_ptr) {
+    if (MODE == GLM_GENERIC && lgam_ptr) {  // the Poisson path subtracts the CTA's lgamma total once (lgam_total)
 #pragma unroll
       for (int mt = 0; mt < 4; mt++) ylg_[mt] = __ldg(lgam_ptr + ri[mt]);
     }
@@ -274,6 +274,20 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
 #undef y_dtype
 #undef y_ptr
 #undef lgam_ptr
+  // Poisson: sum_i lgamma(y_i + 1) over this CTA's rows does not depend on the chain. It is summed
+  // once per CTA (coalesced, fixed tree order) and subtracted from every chain's total in the
+  // epilogue, instead of one load + one add per (row, chain) pair in the hot loop.
+  double lgam_total = 0.0;
+  if (MODE == GLM_POISSON_ID && VAL) {
+    __shared__ double s_lg[32];
+    double v = 0.0;
+    for (int64_t i = row_begin + tid; i < row_end; i += NTHR) v += __ldg(op.lgam + i);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_lg[warp] = v;
+    __syncthreads();
+    for (int w = 0; w < NW; w++) lgam_total += s_lg[w];
+  }
   double nyv[4], nylg[4];
   if (SUB > 1) load_y(row_begin, (int)min((int64_t)DN_TN, row_end - row_begin), nyv, nylg);
 
@@ -355,17 +369,19 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             // out-of-range lambda takes the (rare) library-function branch.
             const double lam = sarg;
             const double kf = yv[mt];
-            const bool ok = (lam >= 1e-300 && lam <= 1e300) && kf >= 0.0;
+            // fast-path range as one unsigned compare on the high word: positive, normal, exponent
+            // field in [2, 0x7fc) (any in-range cut works: everything else takes the exact branch)
+            const bool ok = ((unsigned)__double2hiint(lam) - 0x00200000u < 0x7fa00000u) && kf >= 0.0;
             const double lamc = ok ? lam : 1.0;
             if (VAL) {
-              lp = kf * fast_log_tab(lamc, s_log_tab) - lam - ylg[mt];
+              lp = kf * fast_log_tab(lamc, s_log_tab) - lam;  // - lgamma(k+1): lgam_total, epilogue
               if (lam > 700.0 && kf == 0.0) lp = -lam;
             }
             if (GRAD) w = (!VAL || d_fin(lp)) ? kf * fast_rcp(lamc) - 1.0 : 0.0;  // ok => lp is finite (lgamma column is)
             if (!ok) {
               lp = d_neg_inf(); w = 0.0;
               if (lam > 0.0 && d_fin(lam) && kf >= 0.0) {  // tiny / huge lambda: exact guards via the library functions
-                lp = (lam > 700.0 && kf == 0.0) ? -lam : kf * log(lam) - lam - ylg[mt];
+                lp = (lam > 700.0 && kf == 0.0) ? -lam : kf * log(lam) - lam;
                 if (GRAD && d_fin(lp)) w = kf / lam - 1.0;
               }
             }
@@ -441,6 +457,7 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
       }
       int64_t c = cb0 + warp * WC + nt * 8 + tig * 2 + j;
       if (gid == 0 && c < C) {
+        if (MODE == GLM_POISSON_ID && VAL) v_lp -= lgam_total;  // -inf stays -inf
         for (int a = 0; a < 3; a++) part[(int64_t)a * C + c] = (a == lp_slot) ? v_lp : 0.0;
         if (GRAD) {
           for (int a = 3; a < 3 + A.n_red; a++) {

@@ -188,27 +188,32 @@ __device__ __constant__ long long c_log_lc[182] = {
 __device__ __forceinline__ void fast_log_tab_init(double* tab, int tid, int nthreads) {
   for (int i = tid; i < 182; i += nthreads) { tab[i] = __longlong_as_double(c_log_rc[i]); tab[182 + i] = __longlong_as_double(c_log_lc[i]); }
 }
+// Polynomial / splitting constants of fast_log_tab in the CONSTANT bank: an FP64 literal with a
+// non-zero low word costs two IMAD.MOV per use when the register budget (64 in the 2-CTA/SM
+// value-only dense kernel) keeps the compiler from hoisting it; a c[bank][offset] operand is free.
+__device__ __constant__ double c_logk[8] = {
+    1.4285714285714285e-01, -1.6666666666666666e-01, 0.2, 3.3333333333333331e-01,
+    6.93147180369123816490e-01, 1.90821492927058770002e-10, 256.0, 6755399441055744.0};
 __device__ __forceinline__ double fast_log_tab(double x, const double* __restrict__ tab) {
-  const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
   int hi = __double2hiint(x), lo = __double2loint(x);
   int e = (hi >> 20) - 1023;
   hi = (hi & 0x000fffff) | 0x3ff00000;            // mantissa in [1, 2)
   if (hi > 0x3ff6a09e) { hi -= 0x00100000; e += 1; }  // > sqrt(2): halve
   const double m = __hiloint2double(hi, lo);
-  double t = fma(m, 256.0, 6755399441055744.0);   // round(256 m) in the low mantissa bits
+  double t = fma(m, c_logk[6], c_logk[7]);         // round(256 m) in the low mantissa bits
   const int i = __double2loint(t) - 181;
-  t -= 6755399441055744.0;
+  t -= c_logk[7];
   const double d = fma(t, -0.00390625, m);        // m - c, exact
   const double r = d * tab[i];
-  double q = 1.4285714285714285e-01;              // 1/7
-  q = fma(q, r, -1.6666666666666666e-01);
-  q = fma(q, r, 0.2);
+  double q = c_logk[0];                           // 1/7
+  q = fma(q, r, c_logk[1]);                       // -1/6
+  q = fma(q, r, c_logk[2]);                       // 1/5
   q = fma(q, r, -0.25);
-  q = fma(q, r, 3.3333333333333331e-01);
+  q = fma(q, r, c_logk[3]);                       // 1/3
   q = fma(q, r, -0.5);
   const double p = fma(r * r, q, r);              // log1p(r)
   const double de = (double)e;
-  return fma(de, LN2_HI, tab[182 + i] + fma(de, LN2_LO, p));
+  return fma(de, c_logk[4], tab[182 + i] + fma(de, c_logk[5], p));  // e*ln2_hi + (ln c + (e*ln2_lo + log1p r))
 }
 
 __device__ __forceinline__ double fast_log(double x) {
