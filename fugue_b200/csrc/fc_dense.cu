@@ -369,14 +369,12 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             // out-of-range lambda takes the (rare) library-function branch.
             const double lam = sarg;
             const double kf = yv[mt];
-            // fast-path range as one unsigned compare on the high word: positive, normal, exponent
-            // field in [2, 0x7fc) (any in-range cut works: everything else takes the exact branch)
-            const bool ok = ((unsigned)__double2hiint(lam) - 0x00200000u < 0x7fa00000u) && kf >= 0.0;
+            // fast-path range as one unsigned compare on the high word: positive, normal, below 512
+            // (exponent field in [2, 0x408)). Any in-range cut works: everything else -- including
+            // the reference's lambda > 700 && k == 0 special case -- takes the exact branch below.
+            const bool ok = ((unsigned)__double2hiint(lam) - 0x00200000u < 0x40600000u) && kf >= 0.0;
             const double lamc = ok ? lam : 1.0;
-            if (VAL) {
-              lp = kf * fast_log_tab(lamc, s_log_tab) - lam;  // - lgamma(k+1): lgam_total, epilogue
-              if (lam > 700.0 && kf == 0.0) lp = -lam;
-            }
+            if (VAL) lp = kf * fast_log_tab(lamc, s_log_tab) - lam;  // - lgamma(k+1): lgam_total, epilogue
             if (GRAD) w = (!VAL || d_fin(lp)) ? kf * fast_rcp(lamc) - 1.0 : 0.0;  // ok => lp is finite (lgamma column is)
             if (!ok) {
               lp = d_neg_inf(); w = 0.0;

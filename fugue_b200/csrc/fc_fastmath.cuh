@@ -205,13 +205,14 @@ __device__ __forceinline__ double fast_log_tab(double x, const double* __restric
   t -= c_logk[7];
   const double d = fma(t, -0.00390625, m);        // m - c, exact
   const double r = d * tab[i];
-  double q = c_logk[0];                           // 1/7
-  q = fma(q, r, c_logk[1]);                       // -1/6
-  q = fma(q, r, c_logk[2]);                       // 1/5
-  q = fma(q, r, -0.25);
-  q = fma(q, r, c_logk[3]);                       // 1/3
-  q = fma(q, r, -0.5);
-  const double p = fma(r * r, q, r);              // log1p(r)
+  // log1p(r) = r + r^2 (-1/2 + r/3 - r^2/4 + r^3/5 - r^4/6 + r^5/7), |r| <= 2^-8: Estrin form (depth 4
+  // instead of Horner's 7 -- the kernels that call this run few warps per scheduler)
+  const double r2 = r * r;
+  const double qa = fma(c_logk[3], r, -0.5);       // -1/2 + r/3
+  const double qb = fma(c_logk[2], r, -0.25);      // -1/4 + r/5
+  const double qc = fma(c_logk[0], r, c_logk[1]);  // -1/6 + r/7
+  const double q = fma(r2 * r2, qc, fma(r2, qb, qa));
+  const double p = fma(r2, q, r);
   const double de = (double)e;
   return fma(de, c_logk[4], tab[182 + i] + fma(de, c_logk[5], p));  // e*ln2_hi + (ln c + (e*ln2_lo + log1p r))
 }

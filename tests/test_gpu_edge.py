@@ -175,3 +175,44 @@ def test_structural_errors_are_typed():
     with pytest.raises(FugueError) as e:
         P.check_structure(m2)
     assert e.value.code == 302  # UnexpectedModelStructure
+
+
+def test_poisson_dense_rate_ranges():
+    """Identity-link Poisson plate (distribution.rs:1237-1258) at the edges of the fast path: rates
+    below / above the table-log range (2^-1021, 512), the lambda > 700 && k == 0 special case,
+    zero / negative / NaN / infinite rates (-inf, zero gradient), one chain per regime."""
+    from fugue_b200 import api
+    rng = np.random.default_rng(5)
+    N, D = 300, 3
+    m = ModelBuilder()
+    th = m.plate_sample("th", D, Normal(0.0, 1e6))
+    X = rng.random((N, D)) + 0.5
+    k = rng.poisson(2.0, N).astype(np.uint32)
+    k[::7] = 0
+    m.plate_observe("c", Poisson(dense(m.data(X), th)), m.data(k))
+    O, P = oracle.OracleProgram(m), api.Program(m)
+    scales = [1.0, 100.0, 300.0, 600.0, 2000.0, 1e-5, 1e-200, 1e-305, 1e150, 1e305]
+    q = np.stack([np.full(D, s) for s in scales], axis=1)
+    extra = np.stack([np.array([1.0, -0.2, 0.1]), np.array([-1.0, -1.0, -1.0]), np.array([0.0, 0.0, 0.0]),
+                      np.array([np.nan, 1.0, 1.0]), np.array([np.inf, 1.0, 1.0])], axis=1)
+    q = np.concatenate([q, extra], axis=1)
+    # all-zero observations: every row takes the k == 0 rule
+    olp, oll, olf, og = O.logp(q, grad=True)
+    lp, ll, lf = P.logp(q)
+    assert _close(ll, oll).all(), (ll, oll)
+    tot, g = P.logp_grad(q)
+    assert _close(tot, (olp + oll) + olf).all()
+    fin = np.isfinite(oll)
+    assert fin[:5].all() and not fin[-4:].any()
+    assert _close(g[:, fin], og[:, fin], scale=np.abs(og[:, fin]).max(axis=0, keepdims=True) * 1e-6).all()
+    P.close()
+    m0 = ModelBuilder()
+    th0 = m0.plate_sample("th", D, Normal(0.0, 1e6))
+    m0.plate_observe("c", Poisson(dense(m0.data(X), th0)), m0.data(np.zeros(N, dtype=np.uint32)))
+    O0, P0 = oracle.OracleProgram(m0), api.Program(m0)
+    _, oll0, _, og0 = O0.logp(q[:, :10], grad=True)
+    _, ll0, _ = P0.logp(q[:, :10])
+    assert _close(ll0, oll0).all(), (ll0, oll0)
+    _, g0 = P0.logp_grad(q[:, :10])
+    assert _close(g0, og0, scale=np.abs(og0).max(axis=0, keepdims=True) * 1e-6).all()
+    P0.close()
