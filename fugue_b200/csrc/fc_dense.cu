@@ -288,6 +288,14 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
     __syncthreads();
     for (int w = 0; w < NW; w++) lgam_total += s_lg[w];
   }
+  // K == 8 fast path of contraction 1 (see there): beta fragments for k = 2*tig, 2*tig+1
+  const bool k8_path = (MT == 1) && K == 8;
+  double b8[NT][2];
+#pragma unroll
+  for (int nt = 0; nt < NT; nt++) {
+    b8[nt][0] = k8_path ? s_beta[(2 * tig) * DN_LDB + warp * WC + nt * 8 + gid] : 0.0;
+    b8[nt][1] = k8_path ? s_beta[(2 * tig + 1) * DN_LDB + warp * WC + nt * 8 + gid] : 0.0;
+  }
   double nyv[4], nylg[4];
   if (SUB > 1) load_y(row_begin, (int)min((int64_t)DN_TN, row_end - row_begin), nyv, nylg);
 
@@ -328,6 +336,21 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
     for (int mt = 0; mt < 4; mt++)
 #pragma unroll
       for (int nt = 0; nt < NT; nt++) eta[mt][nt][0] = eta[mt][nt][1] = 0.0;
+    if (MT == 1 && k8_path) {
+      // K == 8: the contraction index is permuted (step 0 takes k = 2*tig, step 1 takes k = 2*tig+1;
+      // a sum over k does not care), so one 16-byte load per row feeds both k-steps. A warp's 32
+      // loads of one 8-row group cover 512 contiguous bytes: no bank conflicts (the k4 + tig
+      // pattern is 4-way conflicted at a row stride of 8 doubles). beta fragments stay in registers.
+#pragma unroll
+      for (int mt = 0; mt < 4; mt++) {
+        const double2 av = *(const double2*)&xs[(mt * 8 + gid) * 8 + 2 * tig];
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+          dmma884(eta[mt][nt][0], eta[mt][nt][1], av.x, b8[nt][0]);
+          dmma884(eta[mt][nt][0], eta[mt][nt][1], av.y, b8[nt][1]);
+        }
+      }
+    } else
 #pragma unroll 5
     for (int k4 = 0; k4 < KP4; k4 += 4) {
       double a[4], b[NT];
