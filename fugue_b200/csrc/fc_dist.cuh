@@ -28,9 +28,16 @@ __device__ __forceinline__ double d_digamma(double x) {
   return r + log(x) - 0.5 / x + t;
 }
 
-// lgam_kp1: optional precomputed lgamma(k+1) for count-valued data (NaN => compute here).
+// lgc: optional normaliser of constant parameters evaluated at lowering (DOp::lgc; NaN => compute here).
+template <bool GRAD>
+__device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1, double lgc);
 template <bool GRAD>
 __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1) {
+  return dist_eval<GRAD>(dist, P0, P1, P2, x, xi, lgam_kp1, __longlong_as_double(0x7ff8000000000000LL));
+}
+// lgam_kp1: optional precomputed lgamma(k+1) for count-valued data (NaN => compute here).
+template <bool GRAD>
+__device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1, double lgc) {
   DistOut g;
   g.lp = d_neg_inf();
   g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
@@ -98,7 +105,7 @@ __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, dou
     case FC_BETA: {  // distribution.rs:897-958
       if (P0 <= 0.0 || P1 <= 0.0 || !d_fin(P0) || !d_fin(P1) || !d_fin(x)) break;
       if (!(x >= 0.0 && x <= 1.0)) break;
-      double log_beta_fn = lgamma(P0) + lgamma(P1) - lgamma(P0 + P1);
+      double log_beta_fn = isnan(lgc) ? lgamma(P0) + lgamma(P1) - lgamma(P0 + P1) : lgc;
       if (x == 0.0) {
         g.lp = P0 > 1.0 ? d_neg_inf() : (P0 < 1.0 ? d_pos_inf() : -log_beta_fn);
         break;
@@ -120,7 +127,7 @@ __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, dou
       if (P0 <= 0.0 || P1 <= 0.0 || !d_fin(P0) || !d_fin(P1) || !d_fin(x)) break;
       if (x <= 0.0) break;
       double log_rate = log(P1), log_x = log(x);
-      g.lp = P0 * log_rate + (P0 - 1.0) * log_x - P1 * x - lgamma(P0);
+      g.lp = P0 * log_rate + (P0 - 1.0) * log_x - P1 * x - (isnan(lgc) ? lgamma(P0) : lgc);
       if (GRAD && d_fin(g.lp)) {
         g.dx = (P0 - 1.0) / x - P1;
         g.dp0 = log_rate + log_x - d_digamma(P0);

@@ -42,6 +42,7 @@ struct DOp {
   double value;
   const double* lgam;  // optional precomputed lgamma(value+1) per element (count data)
   int32_t expr_first, expr_len;  // FACTOR_EXPR: nodes in the program's expression table
+  double lgc;  // normaliser of constant parameters, evaluated once at lowering (NaN: evaluate per call): Gamma lgamma(k), Beta ln B(a, b)
   DParam p[3];
 };
 

@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
         else if (xi == 1 || tv_bern) { g_lp = tv_lp1; g_dp0 = tv_d1; }
         else g_lp = d_neg_inf();  // two-way Categorical: index out of range (distribution.rs:785-791)
       } else {
-        DistOut o = dist_eval<GRAD>(op.dist, pv0, pv1, pv2, x, xi, lg);
+        DistOut o = dist_eval<GRAD>(op.dist, pv0, pv1, pv2, x, xi, lg, op.lgc);
         g_lp = o.lp; g_dx = o.dx; g_dp0 = o.dp0; g_dp1 = o.dp1; g_dp2 = o.dp2;
       }
       lp += g_lp;

@@ -128,7 +128,7 @@ __global__ void k_scalar(const DOp* __restrict__ ops, int n_ops, const int32_t* 
       if (op.cont) x = op.value;
       else xi = (long long)op.value;
     }
-    DistOut g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, __longlong_as_double(0x7ff8000000000000LL));
+    DistOut g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, __longlong_as_double(0x7ff8000000000000LL), op.lgc);
     if (op.is_sample) a_prior += g.lp;
     else a_lik += g.lp;
     if (GRAD) {
@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate(const __grid_constant
         } else if (two_valued && (xi == 0 || xi == 1)) {
           g = xi ? tv1 : tv0;
         } else {
-          g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, op.lgam ? op.lgam[i] : qnan);
+          g = dist_eval<GRAD>(op.dist, pv[0], pv[1], pv[2], x, xi, op.lgam ? op.lgam[i] : qnan, op.lgc);
         }
         lp += g.lp;
         if (GRAD) {

@@ -227,35 +227,35 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_prepass(const double* __restr
   B->bad = m == d_pos_inf();
   B->max_ll = m;
 }
-// exp(x) for x <= 0 (fast_exp without the upper clamp; below -708 it returns ~3e-308 instead of
-// 0, which is negligible against a sum that contains exp(0) = 1 for the max element)
-__device__ __forceinline__ double exp_nonpos(double x) {
+// exp(x) for x <= 0: fast_exp_tab (fc_fastmath.cuh: 2^k * 2^(j/32) * exp(r), 32-entry table in shared
+// memory, degree-6 polynomial, <= 2 ulp) without the upper clamp -- 13 FP64 instructions instead of
+// the 19 of the degree-13 series; these sweeps are bound by the FP64 pipe, not by HBM. Below -708
+// it returns ~3e-308 instead of 0, negligible against a sum that contains exp(0) = 1 for the max.
+__device__ __forceinline__ double exp_nonpos(double x, const double* __restrict__ tab) {
   x = fmax(x, -708.0);
-  const double L2E = 1.4426950408889634;
-  const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
-  double t = fma(x, L2E, 6755399441055744.0);
-  int k = __double2loint(t);
+  const double C32 = 46.16624130844683;
+  const double L_HI = 0.02166084938653512, L_LO = 5.9631716539705866e-12;
+  double t = fma(x, C32, 6755399441055744.0);
+  const int ti = __double2loint(t);
   t -= 6755399441055744.0;
-  double r = fma(t, -LN2_HI, x);
-  r = fma(t, -LN2_LO, r);
-  double q = 1.6059043836821613e-10;
-  q = fma(q, r, 2.08767569878681e-09);
-  q = fma(q, r, 2.505210838544172e-08);
-  q = fma(q, r, 2.755731922398589e-07);
-  q = fma(q, r, 2.7557319223985893e-06);
-  q = fma(q, r, 2.48015873015873e-05);
-  q = fma(q, r, 1.984126984126984e-04);
-  q = fma(q, r, 1.388888888888889e-03);
+  double r = fma(t, -L_HI, x);
+  r = fma(t, -L_LO, r);
+  double q = 1.388888888888889e-03;
   q = fma(q, r, 8.333333333333333e-03);
   q = fma(q, r, 4.1666666666666664e-02);
   q = fma(q, r, 1.6666666666666666e-01);
   q = fma(q, r, 0.5);
-  double p = fma(r * r, q, r) + 1.0;
-  return p * __hiloint2double((k + 1023) << 20, 0);
+  const double p = fma(r * r, q, r);
+  const double T = tab[ti & 31];
+  const double v = fma(T, p, T);
+  return __hiloint2double(__double2hiint(v) + ((ti >> 5) << 20), __double2loint(v));
 }
 __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B, Tri* __restrict__ part, int64_t P,
                                                             int mode, int first, double d_fixed) {
   if (mode == 0 && B->done) return;
+  __shared__ double s_et[32];
+  fast_exp_tab_init(s_et, threadIdx.x);
+  __syncthreads();
   if (B->bad) {  // every lse is non-finite: ess_at(.) = n (smc.rs:595-601); the reweight normaliser is NaN
     if (blockIdx.x == 0 && threadIdx.x == 0) {
       B->lse1 = __longlong_as_double(0x7ff8000000000000LL);
@@ -279,13 +279,13 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, con
       }
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        const double e0 = exp_nonpos(fma(d, a[k].x, lw_const) - m), e1 = exp_nonpos(fma(d, a[k].y, lw_const) - m);
+        const double e0 = exp_nonpos(fma(d, a[k].x, lw_const) - m, s_et), e1 = exp_nonpos(fma(d, a[k].y, lw_const) - m, s_et);
         acc.s1 += e0; acc.s2 = fma(e0, e0, acc.s2);
         t1 += e1; t2 = fma(e1, e1, t2);
       }
     }
     if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-      const double e0 = exp_nonpos(fma(d, ll[P - 1], lw_const) - m);
+      const double e0 = exp_nonpos(fma(d, ll[P - 1], lw_const) - m, s_et);
       acc.s1 += e0; acc.s2 = fma(e0, e0, acc.s2);
     }
     acc.s1 += t1; acc.s2 += t2;
@@ -302,6 +302,9 @@ struct MultiArgs { double d[NB_MULTI_MAX]; int K; };
 __global__ void __launch_bounds__(NB_THREADS) k_nb_multi(double lw_const, const double* __restrict__ ll, const Bisect* __restrict__ B, int64_t P,
                                                          const __grid_constant__ MultiArgs A, double* __restrict__ part) {
   const int K = A.K;
+  __shared__ double s_et[32];
+  fast_exp_tab_init(s_et, threadIdx.x);
+  __syncthreads();
   double m[NB_MULTI_MAX], s1[NB_MULTI_MAX], s2[NB_MULTI_MAX];
 #pragma unroll
   for (int k = 0; k < NB_MULTI_MAX; k++) { m[k] = fma(A.d[k], B->max_ll, lw_const); s1[k] = 0.0; s2[k] = 0.0; }
@@ -310,7 +313,7 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_multi(double lw_const, const 
 #pragma unroll
     for (int k = 0; k < NB_MULTI_MAX; k++) {
       if (k < K) {
-        const double e = m[k] > d_neg_inf() ? exp_nonpos(fma(A.d[k], a, lw_const) - m[k]) : 0.0;
+        const double e = m[k] > d_neg_inf() ? exp_nonpos(fma(A.d[k], a, lw_const) - m[k], s_et) : 0.0;
         s1[k] += e;
         s2[k] = fma(e, e, s2[k]);
       }
