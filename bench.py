@@ -36,8 +36,8 @@ def peaks():
 
 def ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one k_dense_glm launch, from the committed
-    `ncu --set full` capture of this same command (profiles/ncu_dense_r1_v5.txt); None if absent."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_dense_r1_v5.txt")
+    `ncu --set full` capture of this same command (profiles/ncu_dense_r1_v11.txt); None if absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_dense_r1_v11.txt")
     try:
         tot = 0.0
         for line in open(path):
@@ -257,7 +257,7 @@ def main():
             "config": {"workload": f"BASELINE configs[1]: bayesian logistic regression N={N_OBS} D={D}, {Cn} HMC chains per GPU, L={L} leapfrog steps per transition",
                        "chains_per_gpu": Cn, "parallelism": f"chains sharded x{world}, no data-path collective",
                        "l2": "inputs larger than L2 (X = 800 MB streamed every gradient pass)"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": ncu_traffic(), "traffic_unit": "bytes per launch (ncu dram read+write, profiles/ncu_dense_r1_v5.txt)",
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": ncu_traffic(), "traffic_unit": "bytes per launch (ncu dram read+write, profiles/ncu_dense_r1_v11.txt)",
                          "kernel": "k_dense_glm", "launch_ms": per_launch_ms, "launches_timed": int(kern_launches), "peak_source": how,
                          "note": "algorithmic bytes = 801,001,600 B per chain-gradient (SURVEY 8d) x chains per launch; X is shared by the 128 chains of a CTA, so achieved exceeds the streaming roof and the FP64 pipe binds: see roofline_fp64"},
             "roofline_fp64": {"bound": "fp64 tensor/FMA pipe (DMMA)", "achieved": tfl, "peak": f64pk, "unit": "TFLOP/s", "frac": tfl / f64pk, "peak_source": f64how},
