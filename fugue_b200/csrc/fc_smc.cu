@@ -270,12 +270,22 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, con
   if (m > d_neg_inf()) {
     const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
     const int64_t P2 = P >> 1;
-    for (int64_t v0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; v0 < P2; v0 += nthreads * 4) {
-      double2 a[4];
+    // software pipeline: the next trip's four 16-byte loads are in flight while this trip's eight exp
+    // are evaluated (ncu profiles/ncu_c4_nb_eval_r1_v12.txt: 60 % of the warp samples waited on the
+    // loads, DRAM at 33 % -- every warp loaded, then every warp computed)
+    double2 a[4], nx[4];
+    const int64_t vstart = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      int64_t v = vstart + (int64_t)k * nthreads;
+      nx[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
+    }
+    for (int64_t v0 = vstart; v0 < P2; v0 += nthreads * 4) {
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        int64_t v = v0 + (int64_t)k * nthreads;
-        a[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
+        a[k] = nx[k];
+        int64_t v = v0 + nthreads * 4 + (int64_t)k * nthreads;
+        nx[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
       }
 #pragma unroll
       for (int k = 0; k < 4; k++) {
