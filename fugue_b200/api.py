@@ -432,7 +432,6 @@ def adaptive_mcmc_chain(model, n_samples, n_warmup, n_chains=1, seed=0, thin=1, 
     Returns (draws [n_kept][d_cont][C], ddraws [n_kept][d_disc][C], log_joint [n_kept][C], stats)."""
     P = _as_program(model)
     cfg = _ir.fc_mh_config(target_accept, gamma)
-    kept = (n_samples + thin - 1) // thin if n_samples else 0
     kept = n_samples // thin
     draws = np.zeros((kept, P.d_cont, n_chains))
     ddraws = np.zeros((kept, P.d_disc, n_chains), dtype=np.int64)
@@ -455,15 +454,29 @@ _sig("fc_smc_prior_weights", vp)
 _sig("fc_smc_normalize", vp, dp, dp)
 _sig("fc_smc_resample_particles", vp, C.c_int32, vp, vp)
 _sig("fc_smc_rejuvenate_particles", vp, C.c_double, C.c_uint64)
-_sig("fc_smc_shard_begin", vp, C.c_uint64)
-_sig("fc_smc_shard_tri", vp, C.c_double, vp)
-_sig("fc_smc_shard_tri_multi", vp, vp, C.c_int32, vp)
-_sig("fc_smc_shard_reweight", vp, C.c_double, C.c_double)
-_sig("fc_smc_shard_scan", vp, C.c_double, dp)
-_sig("fc_smc_shard_offspring", vp, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, vp, vp, vp, C.c_uint64)
-_sig("fc_smc_shard_install", vp, C.c_uint64, C.c_uint64, vp, vp)
-_sig("fc_smc_shard_resampled", vp)
-_sig("fc_smc_shard_weights", vp, vp, vp)
+_sig("fc_smc_reweight", vp, C.c_double, dp)
+_sig("fc_smc_weights", vp, vp, vp)
+_sig("fc_smc_counters", vp, u64p, u64p, C.POINTER(C.c_int32))
+_sig("fc_smc_create_sharded", vp, vp, C.c_uint64, C.c_size_t, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(vp))
+_sig("fc_smc_export", vp, vp)
+_sig("fc_smc_connect", vp, vp)
+_sig("fc_smc_record_offspring", vp, C.c_int32)
+_sig("fc_smc_last_offspring", vp, u64p, u64p, vp)
+_sig("fc_smc_slot_range", C.c_int32, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, C.c_double, C.c_double, C.c_int32, u64p, u64p)
+_sig("fc_debug_set", C.c_char_p, C.c_int32)
+FC_SMC_HANDLE_BYTES = 128
+
+
+def debug_set(key, value):
+    check(lib.fc_debug_set(key.encode(), int(value)))
+
+
+def smc_slot_range(method, n_total, u_raw, carry_in, end, is_last, seed=0, tag=0):
+    """Output slots [jlo, jhi) of a global systematic / stratified resample whose ancestor lives on the rank
+    whose exact running sum runs from carry_in to end (host arithmetic of the sharded routing)."""
+    a, b = C.c_uint64(), C.c_uint64()
+    check(lib.fc_smc_slot_range(method, n_total, float(u_raw), seed, tag, float(carry_in), float(end), int(is_last), C.byref(a), C.byref(b)))
+    return a.value, b.value
 _sig("fc_resample", C.c_int32, vp, C.c_size_t, vp, vp)
 _sig("fc_resample_dev", C.c_int32, vp, C.c_size_t, vp, vp, vp)
 _sig("fc_exact_prefix_sums", vp, C.c_size_t, vp)
@@ -497,13 +510,31 @@ class SMCResult:
 
 
 class SmcSession:
-    def __init__(self, model, num_particles, config=None, seed=0, first_particle=0):
+    """The particles of adaptive_smc resident on the device. With `shard=(rank, world, n_total,
+    exchange)` this process holds one rank-major shard of a population spread over the GPUs of a box:
+    `exchange(bytes) -> [bytes per rank]` is any host all-gather (torch.distributed in dist.py), used
+    ONCE to swap the 128-byte slab descriptors; every later exchange step runs on the device over peer
+    memory (include/fugue_cuda.h, fc_smc_create_sharded)."""
+
+    def __init__(self, model, num_particles, config=None, seed=0, first_particle=0, shard=None):
         self.program = _as_program(model)
         self.n = int(num_particles)
         cfg = (config or SMCConfig())._c()
         h = vp()
-        check(lib.fc_smc_create(self.program.h, C.byref(cfg), seed, self.n, first_particle, C.byref(h)))
-        self.h = h
+        if shard is None:
+            self.rank, self.world, self.n_total = 0, 1, self.n
+            check(lib.fc_smc_create(self.program.h, C.byref(cfg), seed, self.n, first_particle, C.byref(h)))
+            self.h = h
+        else:
+            self.rank, self.world, self.n_total, exchange = shard
+            check(lib.fc_smc_create_sharded(self.program.h, C.byref(cfg), seed, self.n, first_particle, self.n_total, self.rank, self.world, C.byref(h)))
+            self.h = h
+            mine = (C.c_char * FC_SMC_HANDLE_BYTES)()
+            check(lib.fc_smc_export(h, mine))
+            parts = exchange(bytes(mine))
+            assert len(parts) == self.world and all(len(b) == FC_SMC_HANDLE_BYTES for b in parts)
+            allh = (C.c_char * (FC_SMC_HANDLE_BYTES * self.world)).from_buffer_copy(b"".join(parts))
+            check(lib.fc_smc_connect(h, allh))
 
     def close(self):
         if getattr(self, "h", None):
@@ -537,14 +568,43 @@ class SmcSession:
         """effective_sample_size(particles) (smc.rs:230-233)."""
         return self.normalize()[1]
 
+    def reweight(self, beta_new):
+        """One reweight of the tempering loop (smc.rs:507-531); returns the log normaliser."""
+        ln = C.c_double()
+        check(lib.fc_smc_reweight(self.h, float(beta_new), C.byref(ln)))
+        return ln.value
+
+    def weights(self):
+        """(log weights as they are, globally normalised weights) of this rank's particles."""
+        lw, w = np.zeros(self.n), np.zeros(self.n)
+        check(lib.fc_smc_weights(self.h, _ptr(lw), _ptr(w)))
+        return lw, w
+
     def resample_particles(self, method=ResamplingMethod.Systematic, uniforms=None):
-        """resample_particles (smc.rs:326-349). Returns the ancestor indices."""
-        idx = np.zeros(self.n, dtype=np.uint64)
+        """resample_particles (smc.rs:326-349). Returns the ancestor indices (single-rank sessions)."""
+        idx = np.zeros(self.n, dtype=np.uint64) if self.world == 1 else None
         us = None if uniforms is None else _f64(np.atleast_1d(uniforms))
         if us is not None and us.size != (1 if method == ResamplingMethod.Systematic else self.n):
             raise FugueError(_ir.FC_ERR_INVALID_ARGUMENT, "uniforms: 1 value for systematic, n otherwise")
         check(lib.fc_smc_resample_particles(self.h, method, _ptr(us), _ptr(idx)))
         return idx
+
+    def record_offspring(self, enable=True):
+        check(lib.fc_smc_record_offspring(self.h, int(enable)))
+
+    def last_offspring(self):
+        """(jlo, jhi, global ancestor of every slot in [jlo, jhi)) of the last resample: the slots whose
+        ancestor this rank holds."""
+        a, b = C.c_uint64(), C.c_uint64()
+        check(lib.fc_smc_last_offspring(self.h, C.byref(a), C.byref(b), None))
+        idx = np.zeros(b.value - a.value, dtype=np.uint64)
+        check(lib.fc_smc_last_offspring(self.h, C.byref(a), C.byref(b), _ptr(idx)))
+        return a.value, b.value, idx
+
+    def counters(self):
+        m, e, f = C.c_uint64(), C.c_uint64(), C.c_int32()
+        check(lib.fc_smc_counters(self.h, C.byref(m), C.byref(e), C.byref(f)))
+        return dict(migrated=m.value, ess_evals=e.value, fused=bool(f.value))
 
     def rejuvenate_particles(self, beta, rejuvenation_steps):
         """rejuvenate_particles (smc.rs:698-713): weights are left unchanged."""

@@ -43,6 +43,8 @@ struct DOp {
   const double* lgam;  // optional precomputed lgamma(value+1) per element (count data)
   int32_t expr_first, expr_len;  // FACTOR_EXPR: nodes in the program's expression table
   double lgc;  // normaliser of constant parameters, evaluated once at lowering (NaN: evaluate per call): Gamma lgamma(k), Beta ln B(a, b)
+  const double* probs;  // K-way Categorical with constant probabilities (distribution.rs:679-713): device table, else null
+  int32_t n_probs, _pad2;
   DParam p[3];
 };
 
@@ -121,6 +123,17 @@ struct fc_program {
 };
 
 namespace fc {
+// control block of the device-driven exact prefix scan (fc_resample.cu); lives at the start of the
+// scan's work buffer, followed (at +64 bytes) by the per-tile aggregates
+struct ScanCtl {
+  long long k0;           // elements consumed so far
+  double s0;              // S[k0]
+  long long first_cross;  // window-relative index of the first element that reaches the binade top
+  long long win;          // window policy
+  unsigned cnt_a, cnt_b;  // "last CTA" counters
+  int serial;             // 1: the running sum became non-finite -> finish with the sequential loop
+  int _pad;
+};
 // Scores C chains resident on the device. q [d_cont][C] (sorted rows), qd [d_disc][C].
 // d_lp3 [3][C] (prior, lik, factors), d_total [C]; d_grad [d_cont][C] or nullptr (value only).
 // need_value=false (only with d_grad): the caller will not read d_lp3 / d_total (interior leapfrog steps)

@@ -120,10 +120,10 @@ __global__ void k_move_propose(const __grid_constant__ MoveArgs A) {
         if (!have_params) for (int j = 0; j < op.n_params; j++) pv[j] = eval_param_value(op, j, si.elem, A.q, A.qd, c, C, A.crow, A.drow);
         DevRng r(A.seed, A.chain0 + (uint64_t)c, 0x2000000000000000ULL | A.step_tag);
         long long xi;
-        dist_sample(r, op.dist, pv[0], pv[1], pv[2], prop, xi);
+        op_dist_sample(r, op, pv[0], pv[1], pv[2], prop, xi);
         const double qn = __longlong_as_double(0x7ff8000000000000LL);
-        lqf = dist_eval<false>(op.dist, pv[0], pv[1], pv[2], prop, 0, qn).lp;
-        lqr = dist_eval<false>(op.dist, pv[0], pv[1], pv[2], cur, 0, qn).lp;
+        lqf = op_dist_eval<false>(op, pv[0], pv[1], pv[2], prop, 0, qn).lp;
+        lqr = op_dist_eval<false>(op, pv[0], pv[1], pv[2], cur, 0, qn).lp;
       } break;
       default: prop = cur + scale * z; break;  // Gaussian walk (mh.rs:181-187)
     }
@@ -147,10 +147,10 @@ __global__ void k_move_propose(const __grid_constant__ MoveArgs A) {
         for (int j = 0; j < op.n_params; j++) pv[j] = eval_param_value(op, j, si.elem, A.q, A.qd, c, C, A.crow, A.drow);
         DevRng r(A.seed, A.chain0 + (uint64_t)c, 0x2000000000000000ULL | A.step_tag);
         double xd;
-        dist_sample(r, op.dist, pv[0], pv[1], pv[2], xd, prop);
+        op_dist_sample(r, op, pv[0], pv[1], pv[2], xd, prop);
         const double qn = __longlong_as_double(0x7ff8000000000000LL);
-        lqf = dist_eval<false>(op.dist, pv[0], pv[1], pv[2], 0.0, prop, qn).lp;
-        lqr = dist_eval<false>(op.dist, pv[0], pv[1], pv[2], 0.0, cur, qn).lp;
+        lqf = op_dist_eval<false>(op, pv[0], pv[1], pv[2], 0.0, prop, qn).lp;
+        lqr = op_dist_eval<false>(op, pv[0], pv[1], pv[2], 0.0, cur, qn).lp;
       } break;
     }
     A.old_x[c] = (double)cur;
@@ -440,7 +440,7 @@ int32_t fc_mh_n_sites(const fc_mh_session* s, int64_t* n) { *n = s->eng.n_sites;
 
 // adaptive_mcmc_chain (mh.rs:921-1014): n_warmup adapting steps, then n_samples frozen steps; every
 // `thin`-th sampling step is stored. h_draws [n_kept][d_cont][C], h_ddraws [n_kept][d_disc][C],
-// h_lp [n_kept][C], n_kept = ceil(n_samples / thin). Any output may be NULL.
+// h_lp [n_kept][C], n_kept = floor(n_samples / thin) (every thin-th sampling step). Any output may be NULL.
 int32_t fc_mh_run(fc_program* p, const fc_mh_config* cfg, uint64_t seed, size_t C, size_t n_warmup, size_t n_samples, size_t thin, double* h_draws,
                   int64_t* h_ddraws, double* h_lp, fc_mh_stats* h_stats) {
   fc_mh_session* s = nullptr;

@@ -41,6 +41,21 @@ __device__ __forceinline__ double apply_link(int link, double s, double lo, doub
   }
 }
 
+// dist_eval with the op's lowered extras: the constant normaliser and the K-way Categorical table
+// (log probs[x] if in range and > 0, else -inf: distribution.rs:785-791; constant probabilities carry
+// no parameter gradient)
+template <bool GRAD>
+__device__ __forceinline__ DistOut op_dist_eval(const DOp& op, double P0, double P1, double P2, double x, long long xi, double lgam_kp1) {
+  if (op.dist == FC_CATEGORICAL && op.n_probs > 0) {
+    DistOut g;
+    g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
+    const double pr = (xi >= 0 && xi < (long long)op.n_probs) ? __ldg(op.probs + xi) : 0.0;
+    g.lp = pr > 0.0 ? log(pr) : d_neg_inf();
+    return g;
+  }
+  return dist_eval<GRAD>(op.dist, P0, P1, P2, x, xi, lgam_kp1, op.lgc);
+}
+
 #define PL_TX 32
 #define PL_TY 8
 #define PL_PF 4  // prefetch distance in plate iterations
@@ -188,7 +203,7 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
         else if (xi == 1 || tv_bern) { g_lp = tv_lp1; g_dp0 = tv_d1; }
         else g_lp = d_neg_inf();  // two-way Categorical: index out of range (distribution.rs:785-791)
       } else {
-        DistOut o = dist_eval<GRAD>(op.dist, pv0, pv1, pv2, x, xi, lg, op.lgc);
+        DistOut o = op_dist_eval<GRAD>(op, pv0, pv1, pv2, x, xi, lg);
         g_lp = o.lp; g_dx = o.dx; g_dp0 = o.dp0; g_dp1 = o.dp1; g_dp2 = o.dp2;
       }
       lp += g_lp;

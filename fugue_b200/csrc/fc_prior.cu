@@ -19,7 +19,7 @@ __global__ void k_prior_sample(const DOp* __restrict__ ops, int n_ops, const int
       for (int j = 0; j < op.n_params; j++) pv[j] = eval_param_value(op, j, i, q, qd, c, C, crow, drow);
       double x;
       long long xi;
-      dist_sample(rng, op.dist, pv[0], pv[1], pv[2], x, xi);
+      op_dist_sample(rng, op, pv[0], pv[1], pv[2], x, xi);
       if (op.cont) q[(int64_t)crow[op.cslot0 + i] * C + c] = x;
       else qd[(int64_t)drow[op.dslot0 + i] * C + c] = (disc_t)xi;
     }

@@ -5,8 +5,7 @@
 // (rand_distr 0.4.3 there; here Philox + textbook transforms: distributional parity only,
 // SURVEY H5 / 8c "stream parity unpinned").
 #pragma once
-#include "fc_dist.cuh"
-#include "fc_internal.cuh"
+#include "fc_plate.cuh"
 
 namespace fc {
 
@@ -151,6 +150,21 @@ __device__ inline void dist_sample(DevRng& r, int dist, double P0, double P1, do
     } break;
     default: break;
   }
+}
+
+// one draw from the op's distribution, including the K-way Categorical with a constant table: u ~ U[0,1),
+// first index whose running sum reaches u, capped at K - 1 (distribution.rs:755-784)
+__device__ inline void op_dist_sample(DevRng& r, const DOp& op, double P0, double P1, double P2, double& x, long long& xi) {
+  if (op.dist == FC_CATEGORICAL && op.n_probs > 0) {
+    const double u = r.uniform();
+    double acc = 0.0;
+    int k = 0;
+    for (; k < op.n_probs; k++) { acc += op.probs[k]; if (!(acc < u)) break; }
+    x = 0.0;
+    xi = k < op.n_probs ? k : op.n_probs - 1;
+    return;
+  }
+  dist_sample(r, op.dist, P0, P1, P2, x, xi);
 }
 
 }  // namespace fc

@@ -155,31 +155,80 @@ __device__ __forceinline__ Inc2 block_exclusive_scan(Inc2 v, Inc2* total) {
   return combine(pre, excl);
 }
 
-__global__ void __launch_bounds__(SC_THREADS) k_scan_agg(const double* __restrict__ w, int64_t k0, int64_t len, double base, double U, double lim, Inc2* __restrict__ agg) {
-  int64_t t0 = (int64_t)blockIdx.x * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
-  Inc2 a; a.e = 0; a.o = 0;
-#pragma unroll
-  for (int i = 0; i < SC_ITEMS; i++) {
-    int64_t j = t0 + i;
-    if (j < len) a = combine(a, make_inc(w[k0 + j], base, U, lim));
+// ---- device-driven windows -------------------------------------------------------------------
+// One ROUND handles the window [k0, k0 + len) of the current binade with two launches; everything a
+// round needs (k0, the running sum s0, the window policy) lives in a control block on the device, so
+// the host enqueues a batch of rounds back to back and reads the block once. (Round 1 of this design
+// was host-driven: ~27 windows x (4 launches + a blocking copy) = 2.1 ms per resample at n = 2^24.)
+//   k_scan_round_a  per-tile aggregates of the window; the last CTA to finish scans them
+//   k_scan_round_b  per-element prefix sums -> S, first crossing; the last CTA does the one floating
+//                   add that changes binade and sets up the next window
+struct Binade { double base, U, lim, T; long long need; int parity; };
+__device__ __forceinline__ Binade binade_of(double s0) {
+  Binade b;
+  const double two_m1021 = ldexp(1.0, -1021);
+  if (s0 < two_m1021) { b.base = 0.0; b.U = ldexp(1.0, -1074); b.T = two_m1021; }
+  else {
+    int e;
+    frexp(s0, &e);  // s0 = m * 2^e, m in [0.5, 1)
+    b.base = ldexp(1.0, e - 1); b.U = ldexp(1.0, e - 1 - 52); b.T = ldexp(1.0, e);
   }
-  Inc2 total;
-  block_exclusive_scan(a, &total);
-  if (threadIdx.x == 0) agg[blockIdx.x] = total;
+  b.lim = (b.base == 0.0) ? b.T : b.base;
+  b.need = (long long)((b.T - s0) / b.U);  // exact: both multiples of U, quotient <= 2^53
+  b.parity = (int)(((long long)((s0 - b.base) / b.U)) & 1LL);
+  return b;
 }
-// single block: exclusive scan of the block aggregates (nb <= SC_TILE * 8)
-__global__ void __launch_bounds__(SC_THREADS) k_scan_top(Inc2* __restrict__ agg, int nb) {
-  __shared__ Inc2 carry;
-  if (threadIdx.x == 0) { carry.e = 0; carry.o = 0; }
+#define SC_GRID_MAX 1184  // 8 CTAs per SM on 148 SMs
+
+// the first few hundred elements cross a binade every doubling of the count: one thread walks them
+// exactly as the reference does (the loads do not depend on the add chain, so this is ~2 us)
+__global__ void k_scan_head(const double* __restrict__ w, int64_t n, double* __restrict__ S, ScanCtl* __restrict__ ctl, int64_t head) {
+  double cum = ctl->s0;
+  S[0] = cum;
+  const int64_t m = head < n ? head : n;
+  for (int64_t i = 0; i < m; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
+  ctl->k0 = m; ctl->s0 = cum; ctl->first_cross = 0x7fffffffffffffffLL; ctl->cnt_a = 0; ctl->cnt_b = 0;
+  ctl->win = m > 0 ? 2 * m : 1024;
+  if (ctl->win < 1024) ctl->win = 1024;
+  ctl->serial = (cum != cum || cum == d_pos_inf()) ? 1 : 0;
+}
+__global__ void __launch_bounds__(SC_THREADS) k_scan_round_a(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, Inc2* __restrict__ agg) {
+  const long long k0 = ctl->k0;
+  if (k0 >= n || ctl->serial) return;
+  const Binade B = binade_of(ctl->s0);
+  const int64_t len = min((long long)(n - k0), ctl->win);
+  const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
+    Inc2 a; a.e = 0; a.o = 0;
+#pragma unroll
+    for (int i = 0; i < SC_ITEMS; i++) {
+      const int64_t j = t0 + i;
+      if (j < len) a = combine(a, make_inc(w[k0 + j], B.base, B.U, B.lim));
+    }
+    Inc2 total;
+    block_exclusive_scan(a, &total);
+    if (threadIdx.x == 0) agg[t] = total;
+  }
+  __shared__ bool is_last;
+  __threadfence();
   __syncthreads();
-  for (int base_i = 0; base_i < nb; base_i += SC_TILE) {
+  if (threadIdx.x == 0) is_last = atomicAdd(&ctl->cnt_a, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // exclusive scan of the tile aggregates (written by other CTAs: read through L2)
+  __shared__ Inc2 carry;
+  if (threadIdx.x == 0) { carry.e = 0; carry.o = 0; ctl->cnt_a = 0; }
+  __syncthreads();
+  for (int base_i = 0; base_i < nt; base_i += SC_TILE) {
     Inc2 items[SC_ITEMS];
     Inc2 a; a.e = 0; a.o = 0;
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
-      int j = base_i + threadIdx.x * SC_ITEMS + i;
+      const int j = base_i + threadIdx.x * SC_ITEMS + i;
       items[i].e = 0; items[i].o = 0;
-      if (j < nb) items[i] = agg[j];
+      if (j < nt) { items[i].e = __ldcg(&agg[j].e); items[i].o = __ldcg(&agg[j].o); }
       a = combine(a, items[i]);
     }
     Inc2 total;
@@ -187,8 +236,8 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_top(Inc2* __restrict__ agg,
     Inc2 run = combine(carry, pre);
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
-      int j = base_i + threadIdx.x * SC_ITEMS + i;
-      if (j < nb) agg[j] = run;  // exclusive prefix for block j
+      const int j = base_i + threadIdx.x * SC_ITEMS + i;
+      if (j < nt) agg[j] = run;
       run = combine(run, items[i]);
     }
     __syncthreads();
@@ -196,126 +245,171 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_top(Inc2* __restrict__ agg,
     __syncthreads();
   }
 }
-struct ScanState {
-  long long k0;
-  double s0;
-  long long first_cross;
-};
-// writes S[k0 + j + 1] for every window element j BEFORE the first crossing and records the
-// first element whose addition reaches the binade top.
-__global__ void __launch_bounds__(SC_THREADS) k_scan_apply(const double* __restrict__ w, int64_t k0, int64_t len, double base, double U, double lim, double s0,
-                                                           int parity, long long need, const Inc2* __restrict__ agg, double* __restrict__ S, ScanState* __restrict__ state) {
-  int64_t t0 = (int64_t)blockIdx.x * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
-  Inc2 items[SC_ITEMS];
-  Inc2 a; a.e = 0; a.o = 0;
-#pragma unroll
-  for (int i = 0; i < SC_ITEMS; i++) {
-    int64_t j = t0 + i;
-    items[i].e = 0; items[i].o = 0;
-    if (j < len) items[i] = make_inc(w[k0 + j], base, U, lim);
-    a = combine(a, items[i]);
-  }
-  Inc2 pre = block_exclusive_scan(a, nullptr);
-  Inc2 run = combine(agg[blockIdx.x], pre);
+__global__ void __launch_bounds__(SC_THREADS) k_scan_round_b(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, const Inc2* __restrict__ agg, double* __restrict__ S) {
+  const long long k0 = ctl->k0;
+  if (k0 >= n || ctl->serial) return;
+  const double s0 = ctl->s0;
+  const Binade B = binade_of(s0);
+  const long long win = ctl->win;
+  const int64_t len = min((long long)(n - k0), win);
+  const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
   long long cross = 0x7fffffffffffffffLL;
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
+    Inc2 items[SC_ITEMS];
+    Inc2 a; a.e = 0; a.o = 0;
 #pragma unroll
-  for (int i = 0; i < SC_ITEMS; i++) {
-    int64_t j = t0 + i;
-    run = combine(run, items[i]);
-    if (j < len) {
-      long long p = parity ? run.o : run.e;
-      if (p >= need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
-      else S[k0 + j + 1] = __dadd_rn(s0, __dmul_rn((double)p, U));  // exact: on the U grid below the binade top
+    for (int i = 0; i < SC_ITEMS; i++) {
+      const int64_t j = t0 + i;
+      items[i].e = 0; items[i].o = 0;
+      if (j < len) items[i] = make_inc(w[k0 + j], B.base, B.U, B.lim);
+      a = combine(a, items[i]);
+    }
+    Inc2 pre = block_exclusive_scan(a, nullptr);
+    Inc2 tp; tp.e = __ldcg(&agg[t].e); tp.o = __ldcg(&agg[t].o);
+    Inc2 run = combine(tp, pre);
+#pragma unroll
+    for (int i = 0; i < SC_ITEMS; i++) {
+      const int64_t j = t0 + i;
+      run = combine(run, items[i]);
+      if (j < len) {
+        const long long p = B.parity ? run.o : run.e;
+        if (p >= B.need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
+        else S[k0 + j + 1] = __dadd_rn(s0, __dmul_rn((double)p, B.U));  // exact: on the U grid below the binade top
+      }
     }
   }
-  if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&state->first_cross, (unsigned long long)cross);
-}
-__global__ void k_scan_advance(const double* __restrict__ w, double* __restrict__ S, ScanState* __restrict__ state, int64_t len) {
-  long long k0 = state->k0;
-  long long fc = state->first_cross;
+  if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&ctl->first_cross, (unsigned long long)cross);
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(&ctl->cnt_b, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last || threadIdx.x != 0) return;
+  __threadfence();
+  // advance: the one addition that changes binade is a plain IEEE add, as the reference does.
+  // Window policy: for near-uniform weights the running sum needs about as many further elements to
+  // leave a binade as it took to reach it, so after a crossing at element k the next window is 2k; a
+  // window without a crossing doubles.
+  const long long fc = *(volatile long long*)&ctl->first_cross;
+  long long nk0; double ns0; bool crossed;
   if (fc < len) {
-    long long k = k0 + fc;
-    double nxt = __dadd_rn(S[k], w[k]);  // the one addition that changes binade: plain IEEE add, as the reference does
-    S[k + 1] = nxt;
-    state->k0 = k + 1;
-    state->s0 = nxt;
+    const long long k = k0 + fc;
+    ns0 = __dadd_rn(__ldcg(&S[k]), w[k]);
+    S[k + 1] = ns0;
+    nk0 = k + 1;
+    crossed = true;
   } else {
-    state->k0 = k0 + len;
-    state->s0 = S[k0 + len];
+    nk0 = k0 + len;
+    ns0 = __ldcg(&S[k0 + len]);
+    crossed = !(ns0 < B.T);
   }
-  state->first_cross = 0x7fffffffffffffffLL;
+  long long nw = crossed ? 2 * nk0 : 2 * win;
+  if (nw < 1024) nw = 1024;
+  if (nw > (1LL << 26)) nw = 1LL << 26;
+  ctl->k0 = nk0; ctl->s0 = ns0; ctl->win = nw;
+  ctl->first_cross = 0x7fffffffffffffffLL;
+  ctl->cnt_b = 0;
+  if (ns0 != ns0 || ns0 == d_pos_inf()) ctl->serial = 1;  // cannot happen with finite weights unless the sum overflows
 }
 // correctness fallback (weights with negatives / non-finite values): one thread, the reference loop
 __global__ void k_scan_serial(const double* __restrict__ w, int64_t from, int64_t n, double* __restrict__ S) {
   double cum = S[from];
   for (int64_t i = from; i < n; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
 }
+// finishes a scan whose control block says `serial` (from its k0 on)
+__global__ void k_scan_serial_tail(const double* __restrict__ w, int64_t n, double* __restrict__ S, ScanCtl* __restrict__ ctl) {
+  if (!ctl->serial) return;
+  double cum = ctl->s0;
+  for (int64_t i = ctl->k0; i < n; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
+  ctl->k0 = n; ctl->s0 = cum; ctl->serial = 0;
+}
 
-// S[0..n] := sequentially rounded prefix sums of w[0..n). d_work: >= cdiv(n, SC_TILE) Inc2 + ScanState.
+size_t scan_work_bytes(int64_t n) { return 64 + (size_t)(cdiv(std::max<int64_t>(n, 1), SC_TILE) + 8) * sizeof(Inc2); }
+static int scan_grid() {
+  static int g = 0;
+  if (!g) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    g = std::min(SC_GRID_MAX, 8 * (sms > 0 ? sms : 148));
+  }
+  return g;
+}
+#define SC_HEAD 512
+// enqueue `rounds` rounds (no host synchronisation); d_work: ScanCtl (64 B) followed by the tile aggregates
+int32_t scan_enqueue_rounds(const double* d_w, int64_t n, double* d_S, void* d_work, int rounds, cudaStream_t st, uint64_t* launches) {
+  ScanCtl* ctl = (ScanCtl*)d_work;
+  Inc2* agg = (Inc2*)((char*)d_work + 64);
+  const int g = (int)std::max<int64_t>(1, std::min<int64_t>(scan_grid(), cdiv(n, SC_TILE)));
+  for (int r = 0; r < rounds; r++) {
+    k_scan_round_a<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, agg);
+    k_scan_round_b<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, agg, d_S);
+  }
+  k_scan_serial_tail<<<1, 1, 0, st>>>(d_w, n, d_S, ctl);
+  FC_KERNEL_CHECK();
+  if (launches) *launches += 2 * rounds + 1;
+  return FC_OK;
+}
+// start a scan whose carry-in is already in ctl->s0 on the device (written by the host copy below or
+// by the sharded driver's carry kernel)
+int32_t scan_enqueue_head(const double* d_w, int64_t n, double* d_S, void* d_work, cudaStream_t st, uint64_t* launches) {
+  k_scan_head<<<1, 1, 0, st>>>(d_w, n, d_S, (ScanCtl*)d_work, SC_HEAD);
+  FC_KERNEL_CHECK();
+  if (launches) *launches += 1;
+  return FC_OK;
+}
+// rounds a scan of n elements is expected to need: one per binade the running sum passes after the head
+int scan_expected_rounds(int64_t n) {
+  int r = 4;
+  for (int64_t k = SC_HEAD; k < n; k *= 2) r++;
+  return r;
+}
+// wait until the scan has consumed all n elements, enqueueing more rounds if it has not
+int32_t scan_finish(const double* d_w, int64_t n, double* d_S, void* d_work, cudaStream_t st, uint64_t* launches, double* h_end) {
+  ScanCtl hs;
+  for (int guard = 0; guard < 4096; guard++) {
+    FC_CUDA(cudaMemcpyAsync(&hs, d_work, sizeof(hs), cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    if (hs.k0 >= n) { if (h_end) *h_end = hs.s0; return FC_OK; }
+    FC_TRY(scan_enqueue_rounds(d_w, n, d_S, d_work, 8, st, launches));
+  }
+  set_error("exact_prefix_sums: no progress");
+  return FC_ERR_CUDA;
+}
+
+// S[0..n] := sequentially rounded prefix sums of w[0..n). d_work: >= 64 B + cdiv(n, SC_TILE) Inc2.
 // carry = the running sum the scan starts from (0 for a whole population; the exact end value of
-// the previous rank for one shard of a rank-major global population)
-int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_work, double* d_scratch, cudaStream_t st, uint64_t* launches, double carry) {
-  FC_CUDA(cudaMemcpyAsync(d_S, &carry, 8, cudaMemcpyHostToDevice, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  if (n == 0) return FC_OK;
-  // validity: all weights finite and >= 0, else the serial fallback
-  double bad = 0.0;
-  FC_TRY(dev_reduce(4, d_w, n, 0.0, d_scratch, d_scratch + RD_BLOCKS, st));
-  FC_CUDA(cudaMemcpyAsync(&bad, d_scratch + RD_BLOCKS, 8, cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  if (launches) *launches += 2;
-  if (bad != 0.0) {
-    k_scan_serial<<<1, 1, 0, st>>>(d_w, 0, n, d_S);
-    FC_KERNEL_CHECK();
-    if (launches) *launches += 1;
+// the previous rank for one shard of a rank-major global population).
+// assume_valid: the caller guarantees finite, non-negative weights (skips the check pass).
+int32_t exact_prefix_sums(const double* d_w, int64_t n, double* d_S, void* d_work, double* d_scratch, cudaStream_t st, uint64_t* launches, double carry, bool assume_valid = false) {
+  if (n == 0) {
+    FC_CUDA(cudaMemcpyAsync(d_S, &carry, 8, cudaMemcpyHostToDevice, st));
+    FC_CUDA(cudaStreamSynchronize(st));
     return FC_OK;
   }
-  ScanState* d_state = (ScanState*)d_work;
-  Inc2* d_agg = (Inc2*)((char*)d_work + 64);
-  ScanState hs;
-  hs.k0 = 0; hs.s0 = carry; hs.first_cross = 0x7fffffffffffffffLL;
-  FC_CUDA(cudaMemcpyAsync(d_state, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
-  // window policy: for near-uniform weights the running sum needs about as many further elements
-  // to leave a binade as it took to reach it, so after a crossing at element k the next window is
-  // 2k (tiny windows while the sum is still tiny); a window without a crossing doubles.
-  int64_t win = 1 << 10;
-  int guard = 0;
-  while (hs.k0 < n) {
-    if (++guard > 100000) { set_error("exact_prefix_sums: no progress"); return FC_ERR_CUDA; }
-    double s0 = hs.s0;
-    if (!(s0 == s0) || s0 == INFINITY) {  // cannot happen with finite weights unless the sum overflows
-      k_scan_serial<<<1, 1, 0, st>>>(d_w, hs.k0, n, d_S);
+  if (!assume_valid) {  // validity: all weights finite and >= 0, else the serial fallback
+    double bad = 0.0;
+    FC_TRY(dev_reduce(4, d_w, n, 0.0, d_scratch, d_scratch + RD_BLOCKS, st));
+    FC_CUDA(cudaMemcpyAsync(&bad, d_scratch + RD_BLOCKS, 8, cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    if (launches) *launches += 2;
+    if (bad != 0.0) {
+      FC_CUDA(cudaMemcpyAsync(d_S, &carry, 8, cudaMemcpyHostToDevice, st));
+      k_scan_serial<<<1, 1, 0, st>>>(d_w, 0, n, d_S);
       FC_KERNEL_CHECK();
+      FC_CUDA(cudaStreamSynchronize(st));
       if (launches) *launches += 1;
       return FC_OK;
     }
-    // binade of s0
-    double base, U, T;
-    const double two_m1021 = std::ldexp(1.0, -1021);
-    if (s0 < two_m1021) { base = 0.0; U = std::ldexp(1.0, -1074); T = two_m1021; }
-    else {
-      int e;
-      std::frexp(s0, &e);  // s0 = m * 2^e, m in [0.5,1) => s0 in [2^(e-1), 2^e)
-      base = std::ldexp(1.0, e - 1); U = std::ldexp(1.0, e - 1 - 52); T = std::ldexp(1.0, e);
-    }
-    double lim = (base == 0.0) ? T : base;
-    long long need = (long long)((T - s0) / U);  // exact: both multiples of U, quotient <= 2^53
-    int parity = (int)(((long long)((s0 - base) / U)) & 1LL);
-    int64_t len = std::min<int64_t>(win, n - hs.k0);
-    int nb = (int)cdiv(len, SC_TILE);
-    k_scan_agg<<<nb, SC_THREADS, 0, st>>>(d_w, hs.k0, len, base, U, lim, d_agg);
-    k_scan_top<<<1, SC_THREADS, 0, st>>>(d_agg, nb);
-    k_scan_apply<<<nb, SC_THREADS, 0, st>>>(d_w, hs.k0, len, base, U, lim, s0, parity, need, d_agg, d_S, d_state);
-    k_scan_advance<<<1, 1, 0, st>>>(d_w, d_S, d_state, len);
-    FC_KERNEL_CHECK();
-    if (launches) *launches += 4;
-    long long prev_k0 = hs.k0;
-    FC_CUDA(cudaMemcpyAsync(&hs, d_state, sizeof(hs), cudaMemcpyDeviceToHost, st));
-    FC_CUDA(cudaStreamSynchronize(st));
-    bool crossed = hs.k0 < prev_k0 + len || (hs.k0 == prev_k0 + len && !(hs.s0 < T));
-    win = crossed ? std::min<int64_t>(std::max<int64_t>(2 * (int64_t)hs.k0, 1 << 10), (int64_t)1 << 26) : std::min<int64_t>(win * 2, (int64_t)1 << 26);
   }
-  return FC_OK;
+  ScanCtl hs;
+  memset(&hs, 0, sizeof(hs));
+  hs.s0 = carry;
+  FC_CUDA(cudaMemcpyAsync(d_work, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
+  FC_TRY(scan_enqueue_head(d_w, n, d_S, d_work, st, launches));
+  FC_TRY(scan_enqueue_rounds(d_w, n, d_S, d_work, scan_expected_rounds(n), st, launches));
+  return scan_finish(d_w, n, d_S, d_work, st, launches, nullptr);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -379,34 +473,6 @@ int32_t resample_dev(int method, const double* d_w, int64_t n, const double* d_u
   else k_resample_walk<<<nb, 256, 0, st>>>(W.S.p, n, method, d_us, d_idx);
   FC_KERNEL_CHECK();
   if (launches) *launches += 1;
-  return FC_OK;
-}
-
-// One shard of a global systematic resample (smc.rs:255-272 over the rank-major population):
-// S[0..n] is this rank's exact running sum starting from its carry-in. For the global output slots
-// j in [jlo, jhi) -- those whose threshold u/N + j/N falls into (carry, end] of this rank, or past
-// the end of the last rank -- the ancestor is local particle (i - 1).min(n - 1), i the first index
-// with S_i >= threshold.
-__global__ void k_shard_ancestors(const double* __restrict__ S, int64_t n, double n_total, double u_raw, int64_t jlo, int64_t cnt, uint64_t* __restrict__ idx) {
-  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= cnt) return;
-  double thr = __dadd_rn(__ddiv_rn(u_raw, n_total), __ddiv_rn((double)(jlo + k), n_total));
-  int64_t i = lower_bound_S(S, n, thr);
-  if (i > n) i = n;
-  int64_t a = (i == 0) ? 0 : (i - 1 < n - 1 ? i - 1 : n - 1);  // i == 0 cannot happen for a slot routed here (carry < threshold)
-  idx[k] = (uint64_t)a;
-}
-int32_t shard_scan(const double* d_w, int64_t n, double carry, ResampleWork& W, cudaStream_t st, uint64_t* launches, double* end_value) {
-  FC_TRY(W.reserve(n));
-  FC_TRY(exact_prefix_sums(d_w, n, W.S.p, W.work.p, W.scratch.p, st, launches, carry));
-  FC_CUDA(cudaMemcpyAsync(end_value, W.S.p + n, 8, cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  return FC_OK;
-}
-int32_t shard_ancestors(ResampleWork& W, int64_t n, double n_total, double u_raw, int64_t jlo, int64_t cnt, uint64_t* d_idx, cudaStream_t st) {
-  if (cnt <= 0) return FC_OK;
-  k_shard_ancestors<<<(unsigned)cdiv(cnt, 256), 256, 0, st>>>(W.S.p, n, n_total, u_raw, jlo, cnt, d_idx);
-  FC_KERNEL_CHECK();
   return FC_OK;
 }
 

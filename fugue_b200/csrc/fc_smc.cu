@@ -1,18 +1,43 @@
-// fc_smc.cu -- adaptive (likelihood-tempered) SMC with all particles resident on one B200.
+// fc_smc.cu -- adaptive (likelihood-tempered) SMC with the population resident in HBM, on one B200
+// or sharded rank-major over the GPUs of one box.
 //
 // Device restatement of src/inference/smc.rs: adaptive_smc (:455-581), next_beta (:588-622),
-// tempered_single_site_mh (:631-688, via the move engine of fc_mh.cu), resample + clone
-// (:326-349, 534-541) and smc_prior_particles (:764-790). Particle state is SoA
-// [site][particle]; the cached per-particle accumulators (log_prior, log_lik, log_factors)
-// travel with the particle through resampling, so a rejuvenation move scores the proposal only
-// (the reference re-scores the current state as well: 2 model runs per move, smc.rs:659-676).
+// tempered_single_site_mh (:631-688), resample + clone (:326-349, 534-541), normalize_particles
+// (:719-753) and smc_prior_particles (:764-790).
+//
+// Population container. Continuous sites and the three Trace accumulators are SoA, particle-minor
+// (q [d_cont][n], lp3 [3][n]); discrete sites are one packed record per particle (z [n][zp] bytes,
+// one byte per site when every discrete support fits, else four), because a particle's discrete
+// sites only ever move together (resampling) and are only ever read together (plates). The cached
+// accumulators travel with the particle, so a rejuvenation move scores the proposal only (the
+// reference re-scores the current state as well: 2 model runs per move, smc.rs:659-676).
+//
+// Kernels. For programs made of scalar ops plus two-valued discrete plates and Normal observation
+// plates (BASELINE configs[3], examples/mixture_models.rs:77-111) the three per-particle steps are
+// ONE kernel each: prior draw + score (k_smcx_prior, k_smcx_score), propose + score + accept
+// (k_smcx_move), ancestor search + state copy (k_smcx_gather). Other programs run the generic
+// scoring engine (fc_score.cu) on the same container.
+//
+// Sharding. One process per GPU; the population buffers and a small mailbox live in one
+// cudaIpc-exported slab per rank. Every exchange step of the tempering loop happens ON THE DEVICE
+// over peer memory (NVLink): the per-rank sums of a weight pass are stored into every peer's mailbox
+// by the last CTA of that pass, which then folds all ranks' sums in rank order and advances the
+// replicated bisection state -- the global log-sum-exp is the tail of the weight kernel, not a
+// collective call; the exact running-sum carry travels rank to rank through the same mailboxes; and
+// the resampling gather writes offspring straight into the destination rank's population buffers.
 //
 // Documented deviation: the reference threads ONE DiminishingAdaptation through all particles
 // sequentially (smc.rs:482,551) -- a cross-particle serial dependency. Here every particle of a
 // sweep uses the same per-site scale and the scale is updated once per sweep from the sweep's
-// aggregate acceptance rate with gain 2 * sweep^-gamma. Any positive scale leaves pi_beta
-// invariant, so only efficiency is affected, not the target.
+// aggregate acceptance rate with gain 2 * sweep^-gamma (per rank when sharded). Any positive scale
+// leaves pi_beta invariant, so only efficiency is affected, not the target.
+#include <unistd.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 #include "fc_mh.cuh"
+#include "fc_prior.cuh"
+#include "fc_scalar.cuh"
 #include "fc_fastmath.cuh"
 
 namespace fc {
@@ -22,11 +47,83 @@ struct ResampleWork;
 ResampleWork* resample_work_new();
 void resample_work_free(ResampleWork*);
 int32_t resample_dev(int method, const double* d_w, int64_t n, const double* d_us, uint64_t* d_idx, ResampleWork& W, cudaStream_t st, uint64_t* launches);
-int32_t shard_scan(const double* d_w, int64_t n, double carry, ResampleWork& W, cudaStream_t st, uint64_t* launches, double* end_value);
-int32_t shard_ancestors(ResampleWork& W, int64_t n, double n_total, double u_raw, int64_t jlo, int64_t cnt, uint64_t* d_idx, cudaStream_t st);
+int32_t scan_enqueue_head(const double* d_w, int64_t n, double* d_S, void* d_work, cudaStream_t st, uint64_t* launches);
+int32_t scan_enqueue_rounds(const double* d_w, int64_t n, double* d_S, void* d_work, int rounds, cudaStream_t st, uint64_t* launches);
+int scan_expected_rounds(int64_t n);
+int32_t scan_finish(const double* d_w, int64_t n, double* d_S, void* d_work, cudaStream_t st, uint64_t* launches, double* h_end);
+size_t scan_work_bytes(int64_t n);
 
 #define RDB 1024  // must match RD_BLOCKS of fc_resample.cu
 
+// =============================================================================================
+// peer-memory exchange
+// =============================================================================================
+#define MB_MAXW 8   // ranks (GPUs of one box)
+#define MB_VALS 8   // doubles per rank and exchange
+struct MBox {
+  unsigned long long flag[2][MB_MAXW];      // [sequence parity][source rank] = sequence number
+  double val[2][MB_MAXW][MB_VALS];
+  unsigned long long end_flag[2][MB_MAXW];  // exact running-sum end value of rank r for resample #k
+  double end_val[2][MB_MAXW];
+};
+struct Comm {
+  MBox* box[MB_MAXW];        // box[r]: rank r's mailbox as mapped into this process (box[rank]: local)
+  int rank, world;
+  unsigned long long* seq;   // local device counter of completed exchanges (identical on every rank)
+  int* err;                  // local: set to 1 when a peer did not answer in time
+};
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define COMM_TIMEOUT_NS 20000000000ULL
+__device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long want, int* err) {
+  const unsigned long long t0 = global_ns();
+  while (ld_acquire_sys(p) < want) {
+    if (global_ns() - t0 > COMM_TIMEOUT_NS) { *err = 1; return false; }
+  }
+  return true;
+}
+// All-gather of nv (<= MB_VALS) doubles per rank, executed by one whole CTA (>= 32 threads):
+// s_mine[0..nv) in shared memory -> s_all[r][0..nv) for every rank r. Two mailbox slots alternate by
+// sequence parity: a rank cannot finish exchange s+1 before every peer has contributed to s+1, which
+// a peer does only after it has read exchange s, so slot s&1 is never overwritten while in use.
+__device__ __forceinline__ void comm_allgather(const Comm& cm, const double* s_mine, int nv, double (*s_all)[MB_VALS]) {
+  __shared__ unsigned long long s_seq;
+  if (threadIdx.x == 0) { s_seq = *cm.seq + 1; *cm.seq = s_seq; }
+  __syncthreads();
+  const unsigned long long seq = s_seq;
+  const int par = (int)(seq & 1), t = threadIdx.x;
+  if (t < cm.world) {
+    MBox* d = cm.box[t];
+    for (int i = 0; i < nv; i++) *(volatile double*)&d->val[par][cm.rank][i] = s_mine[i];
+    __threadfence_system();
+    st_release_sys(&d->flag[par][cm.rank], seq);
+    MBox* me = cm.box[cm.rank];
+    wait_flag(&me->flag[par][t], seq, cm.err);
+    for (int i = 0; i < nv; i++) s_all[t][i] = *(volatile double*)&me->val[par][t][i];
+  }
+  __syncthreads();
+}
+__global__ void k_comm_barrier(const __grid_constant__ Comm cm) {
+  __shared__ double s_mine[MB_VALS], s_all[MB_MAXW][MB_VALS];
+  if (threadIdx.x == 0) s_mine[0] = 0.0;
+  __syncthreads();
+  comm_allgather(cm, s_mine, 1, s_all);
+}
+
+// =============================================================================================
+// small elementwise kernels
+// =============================================================================================
 __global__ void k_loglik(const double* __restrict__ lp3, double* __restrict__ ll, int64_t P) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < P) ll[i] = lp3[P + i] + lp3[2 * P + i];  // particle_log_likelihood (smc.rs:381-383)
@@ -36,33 +133,68 @@ __global__ void k_fill2(double* p, double v, int64_t n) {
   if (i < n) p[i] = v;
 }
 // combined = log_w + d_beta * ll   (smc.rs:512-517)
-__global__ void k_combine(const double* __restrict__ log_w, const double* __restrict__ ll, double d_beta, double* __restrict__ out, int64_t P) {
+__global__ void k_combine(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, double d_beta, double* __restrict__ out, int64_t P) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < P) out[i] = log_w[i] + d_beta * ll[i];
+  if (i < P) out[i] = (log_w ? log_w[i] : lw_const) + d_beta * ll[i];
 }
-__global__ void k_sub_exp(const double* __restrict__ x, double sub, double* __restrict__ out_log, double* __restrict__ out_exp, int64_t P) {
+// out_log = x - sub, out_exp = exp(x - sub); a non-finite normaliser gives the uniform fallback
+// (smc.rs:565-575, 719-753)
+__global__ void k_sub_exp(const double* __restrict__ x, const double* __restrict__ d_sub, double n_unif, double* __restrict__ out_log, double* __restrict__ out_exp, int64_t P) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
+  const double sub = *d_sub;
+  if (!isfinite(sub)) {
+    if (out_log) out_log[i] = -log(n_unif);
+    if (out_exp) out_exp[i] = 1.0 / n_unif;
+    return;
+  }
   double v = x[i] - sub;
   if (out_log) out_log[i] = v;
   if (out_exp) out_exp[i] = exp(v);
 }
+__global__ void k_uniform_one(double* out, uint64_t seed, uint64_t tag, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i * 2 >= n) return;
+  Philox ph(seed, 0x8000000000000000ULL);
+  double a, b;
+  ph.uniform2((uint64_t)i, tag, a, b);
+  out[2 * i] = a;
+  if (2 * i + 1 < n) out[2 * i + 1] = b;
+}
 
-// ---- next_beta (smc.rs:588-622) and the reweight log-sum-exp (smc.rs:512-524) ----
-// ess_at(b) = exp(2 lse(lv) - lse(2 lv)), lv_i = log_w_i + (b - beta) ll_i. One launch per
-// evaluation: a single streaming pass keeps the running (max, sum e, sum e^2) triple with
-// e = exp(lv - max) -- sum exp(2 lv - 2 max) is sum e^2, so one exp per particle serves both
-// log-sum-exps -- the last block to finish folds the per-block triples in fixed order and
-// advances the bisection state on the device. The bisection stops issuing work once the
-// interval has collapsed (mid == lo or mid == hi is a fixed point of the reference's loop).
+// =============================================================================================
+// next_beta (smc.rs:588-622) and the reweight log-sum-exp (smc.rs:512-524)
+// =============================================================================================
+// ess_at(b) = exp(2 lse(lv) - lse(2 lv)), lv_i = log_w_i + (b - beta) ll_i. One launch per evaluation:
+// a single streaming pass keeps (sum e, sum e^2) with e = exp(lv - max) -- sum exp(2 lv - 2 max) is
+// sum e^2, so one exp per particle serves both log-sum-exps -- the last CTA folds the per-CTA sums in
+// block order, exchanges the rank's sums with the peers, folds those in rank order and advances the
+// search state, which is therefore replicated bit for bit on every rank. The host only enqueues.
+//
+// The search. The reference bisects [beta, 1] 64 times, one ess_at per iteration. ess_at is
+// non-increasing in b for uniform log_w (d log ESS / d b = 2 (E_b[ll] - E_2b[ll]) <= 0, the tilted mean
+// being non-decreasing), so an iteration whose midpoint lies at or beyond a point where ess_at has
+// ALREADY been evaluated needs no evaluation: its branch is implied. The kernel therefore first
+// localises the crossing with a safeguarded Newton iteration on log ESS in log(b - beta) (the
+// derivative sums come from the same pass), certifies a bracket [a, b] a few ulps wide by actual
+// evaluations on both sides, and then replays the reference loop -- same midpoints 0.5 * (lo + hi),
+// same comparisons -- evaluating ess_at only for midpoints strictly inside (a, b). The returned beta is
+// the reference loop's; ~20 passes instead of ~57. FC_NB_PLAIN=1 disables the search phase.
 struct Bisect {
-  double beta, lo, hi, mid, target, n;
-  double lse1;     // lse(lv) of the last evaluation (the reweight normaliser when mid == beta_new)
-  int done;        // 1: ess_at(1) >= target; 2: interval collapsed
+  double beta, target, n;   // n: global population size (the ESS reported when an lse is not finite)
+  double lo, hi;            // the reference loop's interval (smc.rs:611-619)
+  double a, b;              // certified: ess_at(a) >= target (a == beta: as the reference assumes), ess_at(b) < target
+  double mid;               // the point the next launch evaluates
+  double lse1;              // lse(lv) of the last evaluation (the reweight normaliser when mid == beta_new)
+  double max_ll;            // global max of ll (uniform log_w: max lv = lwc + d max ll)
+  double guess;             // first search point (0: none): a multiple of the previous step's increment
+  double prev_x, delta;     // search bookkeeping
+  int bad;                  // some ll is NaN or +inf => every lse is non-finite => ESS := n (smc.rs:595-601)
+  int done;                 // 1: ess_at(1) >= target; 2: the loop has reached its fixed point / 64 iterations
+  int phase;                // 0: ess_at(1.0) probe, 1: Newton search, 2: two-sided polish, 3: replay
+  int it;                   // iterations of the reference loop performed
+  int n_search, plain, evals;
   unsigned counter;
-  double max_ll;   // pre-pass (uniform log_w only): max of ll
-  int bad;         // pre-pass: some ll is NaN or +inf => every lse is non-finite => ESS := n (smc.rs:595-601)
-  int _pad;
 };
 struct Tri { double m, s1, s2; };
 __device__ __forceinline__ void tri_merge(Tri& a, const Tri& b) {
@@ -98,135 +230,72 @@ __device__ __forceinline__ void tri_push8(Tri& acc, const double (&lv)[8]) {
     acc.s2 += e * e;
   }
 }
-// bisection update for one ESS evaluation (smc.rs:605-619)
-__device__ __forceinline__ void nb_update(Bisect* B, double ess, int first) {
-  if (first) {
+// the reference's bisection update for one ESS evaluation at B->mid (smc.rs:605-619)
+__device__ __forceinline__ void nb_ref_update(Bisect* B, double ess) {
+  if (ess < B->target) { B->hi = B->mid; B->b = fmin(B->b, B->mid); }
+  else { B->lo = B->mid; B->a = fmax(B->a, B->mid); }
+  B->it += 1;
+}
+// walk the reference loop as far as the certified bracket decides it; stops at the first midpoint that
+// needs an evaluation (left in B->mid) or at the loop's end
+__device__ __forceinline__ void nb_replay(Bisect* B) {
+  while (B->it < 64) {
+    const double mid = 0.5 * (B->lo + B->hi);
+    if (mid == B->lo || mid == B->hi) { B->done = 2; return; }  // fixed point of the remaining iterations
+    if (mid <= B->a) { B->lo = mid; B->it += 1; continue; }     // ess_at(mid) >= ess_at(a) >= target
+    if (mid >= B->b) { B->hi = mid; B->it += 1; continue; }     // ess_at(mid) <= ess_at(b) <  target
+    B->mid = mid;
+    return;
+  }
+  B->done = 2;
+}
+// state machine step after ess_at(B->mid) has been evaluated: s1 = sum e, s2 = sum e^2, t1 = sum ll e,
+// t2 = sum ll e^2 over the whole population (shift m), ess as the reference computes it
+__device__ void nb_advance(Bisect* B, double ess, double s1, double s2, double t1, double t2) {
+  B->evals += 1;
+  const double x = B->mid;
+  if (B->phase == 0) {  // the ess_at(1.0) probe (smc.rs:605-608)
     if (ess >= B->target) { B->hi = 1.0; B->done = 1; return; }
-    B->lo = B->beta; B->hi = 1.0;
-  } else {
-    if (ess < B->target) B->hi = B->mid; else B->lo = B->mid;
+    B->lo = B->beta; B->hi = 1.0; B->a = B->beta; B->b = 1.0; B->it = 0;
+    if (B->plain) { B->phase = 3; nb_replay(B); return; }
+    B->phase = 1; B->n_search = 0;
+    if (B->guess > B->beta && B->guess < 1.0) { B->prev_x = x; B->mid = B->guess; return; }
+  } else if (B->phase == 3) {
+    nb_ref_update(B, ess);
+    nb_replay(B);
+    return;
+  } else {  // search phases: certify, then choose the next point
+    if (ess < B->target) B->b = fmin(B->b, x); else B->a = fmax(B->a, x);
   }
-  B->mid = 0.5 * (B->lo + B->hi);
-  if (B->mid == B->lo || B->mid == B->hi) B->done = 2;
-}
-// CTA reduction of the per-thread triples; the last CTA to finish folds the per-CTA triples in
-// block order (deterministic) and advances the bisection state.
-__device__ __forceinline__ void nb_fold_update(Tri acc, Bisect* __restrict__ B, Tri* __restrict__ part, int mode, int first) {
-  __shared__ Tri sm[NB_THREADS / 32];
-  __shared__ bool is_last;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    Tri b;
-    b.m = __shfl_down_sync(0xffffffffu, acc.m, o); b.s1 = __shfl_down_sync(0xffffffffu, acc.s1, o); b.s2 = __shfl_down_sync(0xffffffffu, acc.s2, o);
-    tri_merge(acc, b);
+  if (B->phase == 1) {
+    B->n_search += 1;
+    const double d = x - B->beta, da = B->a - B->beta, db = B->b - B->beta;
+    // Newton on g(d) = ln ESS(d) - ln target in t = ln d: dg/dd = 2 (t1/s1 - t2/s2)
+    const double g = log(ess) - log(B->target);
+    const double gp = 2.0 * (t1 / s1 - t2 / s2);
+    double dn = d * exp(-g / (d * gp));
+    if (!(gp < 0.0) || !isfinite(dn) || !(dn > da) || !(dn < db)) dn = da > 0.0 ? sqrt(da * db) : db * 0.0625;
+    const double xn = B->beta + dn;
+    const bool converged = fabs(dn - d) <= 1e-12 * d || B->n_search >= 24 || !(xn > B->a) || !(xn < B->b);
+    if (!converged) { B->prev_x = x; B->mid = xn; return; }
+    // two-sided polish around the best point: certify the side that is still far away
+    B->phase = 2;
+    B->delta = ldexp(fmax(x, 1e-300), -44);
   }
-  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(acc, sm[w]);
-    part[blockIdx.x] = acc;
-    __threadfence();
-    unsigned t = atomicAdd(&B->counter, 1u);
-    is_last = (t == gridDim.x - 1);
+  if (B->phase == 2) {
+    B->n_search += 1;
+    // the evaluated points so far have moved a or b; step from the near side towards the far one
+    const bool near_a = (x == B->a);
+    const double far_gap = near_a ? (B->b - x) : (x - B->a);
+    if (far_gap <= 8.0 * B->delta || B->n_search >= 40) { B->phase = 3; nb_replay(B); return; }
+    double xn = near_a ? x + B->delta : x - B->delta;
+    B->delta *= 4.0;
+    if (!(xn > B->a) || !(xn < B->b)) { B->phase = 3; nb_replay(B); return; }
+    B->mid = xn;
+    return;
   }
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  // last block: fold the per-block triples in block order (deterministic), then update the state
-  Tri t; t.m = d_neg_inf(); t.s1 = 0.0; t.s2 = 0.0;
-  const int nb = gridDim.x;
-  const int per = (nb + NB_THREADS - 1) / NB_THREADS;
-  for (int i = threadIdx.x * per; i < min(nb, (threadIdx.x + 1) * per); i++) {
-    Tri b;  // written by other blocks: read through L2
-    b.m = __ldcg(&part[i].m); b.s1 = __ldcg(&part[i].s1); b.s2 = __ldcg(&part[i].s2);
-    tri_merge(t, b);
-  }
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {  // ordered (left-to-right) tree
-    Tri b;
-    b.m = __shfl_down_sync(0xffffffffu, t.m, o); b.s1 = __shfl_down_sync(0xffffffffu, t.s1, o); b.s2 = __shfl_down_sync(0xffffffffu, t.s2, o);
-    if (((threadIdx.x & 31) & (2 * o - 1)) == 0) tri_merge(t, b);
-  }
-  __syncthreads();
-  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = t;
-  __syncthreads();
-  if (threadIdx.x != 0) return;
-  for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(t, sm[w]);
-  part[gridDim.x] = t;  // the folded (max, sum e, sum e^2): read by the sharded driver (fc_smc_shard_tri)
-  B->counter = 0;
-  const double ninf = d_neg_inf();
-  double lse1 = (t.m == ninf && t.s1 == 0.0) ? ninf : (t.s1 == 0.0 ? ninf : t.m + log(t.s1));
-  double lse2 = (t.m == ninf && t.s2 == 0.0) ? ninf : (t.s2 == 0.0 ? ninf : 2.0 * t.m + log(t.s2));
-  B->lse1 = lse1;
-  if (mode != 0) return;
-  double ess = (!isfinite(lse1) || !isfinite(lse2)) ? B->n : exp(2.0 * lse1 - lse2);
-  nb_update(B, ess, first);
 }
 
-// mode 0: bisection probe at B->mid (first = 1: the ess_at(1.0) probe); mode 1: lse only at d_fixed
-__global__ void __launch_bounds__(NB_THREADS) k_nb_eval(const double* __restrict__ log_w, double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B,
-                                                        Tri* __restrict__ part, int64_t P, int mode, int first, double d_fixed) {
-  if (mode == 0 && B->done) return;
-  const double d = mode == 0 ? B->mid - B->beta : d_fixed;
-  Tri acc; acc.m = d_neg_inf(); acc.s1 = 0.0; acc.s2 = 0.0;
-  const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
-  const int64_t P2 = P >> 1;  // double2 units
-  for (int64_t v0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; v0 < P2; v0 += nthreads * 4) {
-    double lv[8];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      int64_t v = v0 + (int64_t)k * nthreads;
-      if (v < P2) {
-        double2 a = __ldg((const double2*)ll + v);
-        double2 w = log_w ? __ldg((const double2*)log_w + v) : make_double2(lw_const, lw_const);
-        lv[2 * k] = w.x + d * a.x; lv[2 * k + 1] = w.y + d * a.y;
-      } else lv[2 * k] = lv[2 * k + 1] = d_neg_inf();
-    }
-    tri_push8(acc, lv);
-  }
-  if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-    double lv[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) lv[k] = d_neg_inf();
-    lv[0] = (log_w ? log_w[P - 1] : lw_const) + d * ll[P - 1];
-    tri_push8(acc, lv);
-  }
-  nb_fold_update(acc, B, part, mode, first);
-}
-
-// ---- uniform log_w (the state adaptive_smc is in whenever next_beta runs: initially and after
-// every resample): lv_i = c + d ll_i, so max lv = c + d max(ll) and the pass needs no running max.
-// k_nb_prepass (once per next_beta call): max(ll) and the "some ll is NaN / +inf" flag. ----
-__global__ void __launch_bounds__(NB_THREADS) k_nb_prepass(const double* __restrict__ ll, int64_t P, Bisect* __restrict__ B, double* __restrict__ part) {
-  double mx = d_neg_inf();
-  int bad = 0;
-  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) {
-    double v = __ldg(ll + i);
-    bad |= (v != v) || v == d_pos_inf();
-    mx = fmax(mx, v);
-  }
-  mx = warp_max(mx);
-  bad = __any_sync(0xffffffffu, bad);
-  __shared__ double sm[NB_THREADS / 32];
-  __shared__ int sbad[NB_THREADS / 32];
-  __shared__ bool is_last;
-  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5] = mx; sbad[threadIdx.x >> 5] = bad; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    for (int w = 1; w < NB_THREADS / 32; w++) { mx = fmax(mx, sm[w]); bad |= sbad[w]; }
-    part[blockIdx.x] = bad ? d_pos_inf() : mx;  // +inf doubles as the bad marker
-    __threadfence();
-    is_last = atomicAdd(&B->counter, 1u) == gridDim.x - 1;
-  }
-  __syncthreads();
-  if (!is_last || threadIdx.x != 0) return;
-  __threadfence();
-  double m = d_neg_inf();
-  for (int i = 0; i < (int)gridDim.x; i++) m = fmax(m, __ldcg(part + i));
-  B->counter = 0;
-  B->bad = m == d_pos_inf();
-  B->max_ll = m;
-}
 // exp(x) for x <= 0: fast_exp_tab (fc_fastmath.cuh: 2^k * 2^(j/32) * exp(r), 32-entry table in shared
 // memory, degree-6 polynomial, <= 2 ulp) without the upper clamp -- 13 FP64 instructions instead of
 // the 19 of the degree-13 series; these sweeps are bound by the FP64 pipe, not by HBM. Below -708
@@ -250,8 +319,165 @@ __device__ __forceinline__ double exp_nonpos(double x, const double* __restrict_
   const double v = fma(T, p, T);
   return __hiloint2double(__double2hiint(v) + ((ti >> 5) << 20), __double2loint(v));
 }
-__global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B, Tri* __restrict__ part, int64_t P,
-                                                            int mode, int first, double d_fixed) {
+
+// ---- general log_w (standalone next_beta on arbitrary weights; single rank): plain bisection ----
+__device__ __forceinline__ void nb_fold_update_general(Tri acc, Bisect* __restrict__ B, Tri* __restrict__ part, int mode) {
+  __shared__ Tri sm[NB_THREADS / 32];
+  __shared__ bool is_last;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    Tri b;
+    b.m = __shfl_down_sync(0xffffffffu, acc.m, o); b.s1 = __shfl_down_sync(0xffffffffu, acc.s1, o); b.s2 = __shfl_down_sync(0xffffffffu, acc.s2, o);
+    tri_merge(acc, b);
+  }
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(acc, sm[w]);
+    part[blockIdx.x] = acc;
+    __threadfence();
+    unsigned t = atomicAdd(&B->counter, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  Tri t; t.m = d_neg_inf(); t.s1 = 0.0; t.s2 = 0.0;
+  const int nb = gridDim.x;
+  const int per = (nb + NB_THREADS - 1) / NB_THREADS;
+  for (int i = threadIdx.x * per; i < min(nb, (threadIdx.x + 1) * per); i++) {
+    Tri b;  // written by other blocks: read through L2
+    b.m = __ldcg(&part[i].m); b.s1 = __ldcg(&part[i].s1); b.s2 = __ldcg(&part[i].s2);
+    tri_merge(t, b);
+  }
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {  // ordered (left-to-right) tree
+    Tri b;
+    b.m = __shfl_down_sync(0xffffffffu, t.m, o); b.s1 = __shfl_down_sync(0xffffffffu, t.s1, o); b.s2 = __shfl_down_sync(0xffffffffu, t.s2, o);
+    if (((threadIdx.x & 31) & (2 * o - 1)) == 0) tri_merge(t, b);
+  }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = t;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  for (int w = 1; w < NB_THREADS / 32; w++) tri_merge(t, sm[w]);
+  B->counter = 0;
+  const double ninf = d_neg_inf();
+  double lse1 = (t.m == ninf && t.s1 == 0.0) ? ninf : (t.s1 == 0.0 ? ninf : t.m + log(t.s1));
+  double lse2 = (t.m == ninf && t.s2 == 0.0) ? ninf : (t.s2 == 0.0 ? ninf : 2.0 * t.m + log(t.s2));
+  B->lse1 = lse1;
+  if (mode != 0) return;
+  double ess = (!isfinite(lse1) || !isfinite(lse2)) ? B->n : exp(2.0 * lse1 - lse2);
+  nb_advance(B, ess, 1.0, 1.0, 0.0, 0.0);  // plain = 1: the derivative sums are not used
+}
+// mode 0: probe at B->mid; mode 1: lse only at d_fixed
+__global__ void __launch_bounds__(NB_THREADS) k_nb_eval(const double* __restrict__ log_w, const double* __restrict__ ll, Bisect* __restrict__ B,
+                                                        Tri* __restrict__ part, int64_t P, int mode, double d_fixed) {
+  if (mode == 0 && B->done) return;
+  const double d = mode == 0 ? B->mid - B->beta : d_fixed;
+  Tri acc; acc.m = d_neg_inf(); acc.s1 = 0.0; acc.s2 = 0.0;
+  const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
+  for (int64_t i0 = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i0 < P; i0 += nthreads * 8) {
+    double lv[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int64_t i = i0 + (int64_t)k * nthreads;
+      lv[k] = i < P ? __ldg(log_w + i) + d * __ldg(ll + i) : d_neg_inf();
+    }
+    tri_push8(acc, lv);
+  }
+  nb_fold_update_general(acc, B, part, mode);
+}
+
+// ---- uniform log_w (the state adaptive_smc is in whenever next_beta runs: initially and after every
+// resample): lv_i = c + d ll_i, so max lv = c + d max(ll) and the pass needs no running max.
+// k_nb_prepass (once per next_beta call): GLOBAL max(ll) and the "some ll is NaN / +inf" flag. ----
+__global__ void __launch_bounds__(NB_THREADS) k_nb_prepass(const double* __restrict__ ll, int64_t P, Bisect* __restrict__ B, double* __restrict__ part, const __grid_constant__ Comm cm) {
+  double mx = d_neg_inf();
+  int bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) {
+    double v = __ldg(ll + i);
+    bad |= (v != v) || v == d_pos_inf();
+    mx = fmax(mx, v);
+  }
+  mx = warp_max(mx);
+  bad = __any_sync(0xffffffffu, bad);
+  __shared__ double sm[NB_THREADS / 32];
+  __shared__ int sbad[NB_THREADS / 32];
+  __shared__ bool is_last;
+  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5] = mx; sbad[threadIdx.x >> 5] = bad; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) { mx = fmax(mx, sm[w]); bad |= sbad[w]; }
+    part[blockIdx.x] = bad ? d_pos_inf() : mx;  // +inf doubles as the bad marker
+    __threadfence();
+    is_last = atomicAdd(&B->counter, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  __shared__ double s_mine[MB_VALS], s_all[MB_MAXW][MB_VALS];
+  if (threadIdx.x == 0) {
+    double m = d_neg_inf();
+    for (int i = 0; i < (int)gridDim.x; i++) m = fmax(m, __ldcg(part + i));
+    s_mine[0] = m;
+    B->counter = 0;
+  }
+  __syncthreads();
+  comm_allgather(cm, s_mine, 1, s_all);
+  if (threadIdx.x == 0) {
+    double m = d_neg_inf();
+    for (int r = 0; r < cm.world; r++) m = fmax(m, s_all[r][0]);
+    B->bad = m == d_pos_inf();
+    B->max_ll = m;
+  }
+}
+// one pass over ll at increment d (mode 0: d = B->mid - B->beta, search state advanced; mode 1: lse only
+// at d_fixed). part: per-CTA (s1, s2, t1, t2).
+template <bool DERIV>
+__device__ __forceinline__ void nb_pass(double lw_const, const double* __restrict__ ll, int64_t P, double d, double m, const double* __restrict__ s_et, double (&out)[4]) {
+  double s1 = 0.0, s2 = 0.0, t1 = 0.0, t2 = 0.0, u1 = 0.0, u2 = 0.0, v1 = 0.0, v2 = 0.0;  // two accumulator sets (shorter dependency chains)
+  const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
+  const int64_t P2 = P >> 1;
+  // software pipeline: the next trip's four 16-byte loads are in flight while this trip's eight exp are
+  // evaluated (ncu profiles/ncu_c4_nb_eval_r1_v12.txt: 60 % of the warp samples waited on the loads,
+  // DRAM at 33 % -- every warp loaded, then every warp computed)
+  double2 a[4], nx[4];
+  const int64_t vstart = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    int64_t v = vstart + (int64_t)k * nthreads;
+    nx[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
+  }
+  for (int64_t v0 = vstart; v0 < P2; v0 += nthreads * 4) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      a[k] = nx[k];
+      int64_t v = v0 + nthreads * 4 + (int64_t)k * nthreads;
+      nx[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const double e0 = exp_nonpos(fma(d, a[k].x, lw_const) - m, s_et), e1 = exp_nonpos(fma(d, a[k].y, lw_const) - m, s_et);
+      s1 += e0; s2 = fma(e0, e0, s2);
+      u1 += e1; u2 = fma(e1, e1, u2);
+      if (DERIV) {  // ll = -inf contributes e ~ 3e-308: keep its product out of the derivative sums
+        const double l0 = a[k].x > -1e300 ? a[k].x * e0 : 0.0, l1 = a[k].y > -1e300 ? a[k].y * e1 : 0.0;
+        t1 += l0; t2 = fma(l0, e0, t2);
+        v1 += l1; v2 = fma(l1, e1, v2);
+      }
+    }
+  }
+  if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    const double l = ll[P - 1];
+    const double e0 = exp_nonpos(fma(d, l, lw_const) - m, s_et);
+    s1 += e0; s2 = fma(e0, e0, s2);
+    if (DERIV) { const double l0 = l > -1e300 ? l * e0 : 0.0; t1 += l0; t2 = fma(l0, e0, t2); }
+  }
+  out[0] = s1 + u1; out[1] = s2 + u2; out[2] = t1 + v1; out[3] = t2 + v2;
+}
+__global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, const double* __restrict__ ll, Bisect* __restrict__ B, double* __restrict__ part, int64_t P,
+                                                            int mode, double d_fixed, const __grid_constant__ Comm cm) {
   if (mode == 0 && B->done) return;
   __shared__ double s_et[32];
   fast_exp_tab_init(s_et, threadIdx.x);
@@ -259,89 +485,58 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, con
   if (B->bad) {  // every lse is non-finite: ess_at(.) = n (smc.rs:595-601); the reweight normaliser is NaN
     if (blockIdx.x == 0 && threadIdx.x == 0) {
       B->lse1 = __longlong_as_double(0x7ff8000000000000LL);
-      if (mode == 0) nb_update(B, B->n, first);
+      if (mode == 0) nb_advance(B, B->n, 1.0, 1.0, 0.0, 0.0);  // phase 0: ess_at(1.0) = n >= target -> 1.0
     }
     return;
   }
   const double d = mode == 0 ? B->mid - B->beta : d_fixed;
   const double m = fma(d, B->max_ll, lw_const);  // the same expression as lv of the max element: x <= 0, == 0 there
-  Tri acc; acc.m = m; acc.s1 = 0.0; acc.s2 = 0.0;
-  double t1 = 0.0, t2 = 0.0;  // second accumulator pair (shorter dependency chains)
+  const bool deriv = mode == 0 && (B->phase == 1 || (B->phase == 0 && !B->plain));
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
   if (m > d_neg_inf()) {
-    const int64_t nthreads = (int64_t)gridDim.x * NB_THREADS;
-    const int64_t P2 = P >> 1;
-    // software pipeline: the next trip's four 16-byte loads are in flight while this trip's eight exp
-    // are evaluated (ncu profiles/ncu_c4_nb_eval_r1_v12.txt: 60 % of the warp samples waited on the
-    // loads, DRAM at 33 % -- every warp loaded, then every warp computed)
-    double2 a[4], nx[4];
-    const int64_t vstart = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x;
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      int64_t v = vstart + (int64_t)k * nthreads;
-      nx[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
-    }
-    for (int64_t v0 = vstart; v0 < P2; v0 += nthreads * 4) {
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        a[k] = nx[k];
-        int64_t v = v0 + nthreads * 4 + (int64_t)k * nthreads;
-        nx[k] = v < P2 ? __ldg((const double2*)ll + v) : make_double2(d_neg_inf(), d_neg_inf());
-      }
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const double e0 = exp_nonpos(fma(d, a[k].x, lw_const) - m, s_et), e1 = exp_nonpos(fma(d, a[k].y, lw_const) - m, s_et);
-        acc.s1 += e0; acc.s2 = fma(e0, e0, acc.s2);
-        t1 += e1; t2 = fma(e1, e1, t2);
-      }
-    }
-    if ((P & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-      const double e0 = exp_nonpos(fma(d, ll[P - 1], lw_const) - m, s_et);
-      acc.s1 += e0; acc.s2 = fma(e0, e0, acc.s2);
-    }
-    acc.s1 += t1; acc.s2 += t2;
+    if (deriv) nb_pass<true>(lw_const, ll, P, d, m, s_et, acc);
+    else nb_pass<false>(lw_const, ll, P, d, m, s_et, acc);
   }
-  nb_fold_update(acc, B, part, mode, first);
-}
-
-// K candidate increments in one pass over ll (uniform log_w): the sharded driver evaluates three
-// bisection levels (7 candidates) per round, so a next_beta search costs ~22 collectives instead of
-// ~55. Per-block partial sums [block][2K] (sum e, sum e^2 per candidate, shift m_k = lwc + d_k max ll);
-// the host folds the blocks in order.
-#define NB_MULTI_MAX 8
-struct MultiArgs { double d[NB_MULTI_MAX]; int K; };
-__global__ void __launch_bounds__(NB_THREADS) k_nb_multi(double lw_const, const double* __restrict__ ll, const Bisect* __restrict__ B, int64_t P,
-                                                         const __grid_constant__ MultiArgs A, double* __restrict__ part) {
-  const int K = A.K;
-  __shared__ double s_et[32];
-  fast_exp_tab_init(s_et, threadIdx.x);
+  // CTA reduction; the last CTA folds the per-CTA sums in block order (deterministic)
+  __shared__ double sm[NB_THREADS / 32][4];
+  __shared__ bool is_last;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[k] += __shfl_down_sync(0xffffffffu, acc[k], o);
+  }
+  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5][0] = acc[0]; sm[threadIdx.x >> 5][1] = acc[1]; sm[threadIdx.x >> 5][2] = acc[2]; sm[threadIdx.x >> 5][3] = acc[3]; }
   __syncthreads();
-  double m[NB_MULTI_MAX], s1[NB_MULTI_MAX], s2[NB_MULTI_MAX];
-#pragma unroll
-  for (int k = 0; k < NB_MULTI_MAX; k++) { m[k] = fma(A.d[k], B->max_ll, lw_const); s1[k] = 0.0; s2[k] = 0.0; }
-  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) {
-    const double a = __ldg(ll + i);
-#pragma unroll
-    for (int k = 0; k < NB_MULTI_MAX; k++) {
-      if (k < K) {
-        const double e = m[k] > d_neg_inf() ? exp_nonpos(fma(A.d[k], a, lw_const) - m[k], s_et) : 0.0;
-        s1[k] += e;
-        s2[k] = fma(e, e, s2[k]);
-      }
-    }
-  }
-  __shared__ double sm[NB_THREADS / 32][2 * NB_MULTI_MAX];
-#pragma unroll
-  for (int k = 0; k < NB_MULTI_MAX; k++) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { s1[k] += __shfl_down_sync(0xffffffffu, s1[k], o); s2[k] += __shfl_down_sync(0xffffffffu, s2[k], o); }
-    if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5][2 * k] = s1[k]; sm[threadIdx.x >> 5][2 * k + 1] = s2[k]; }
-  }
-  __syncthreads();
-  if (threadIdx.x < 2 * NB_MULTI_MAX) {
+  if (threadIdx.x < 4) {
     double t = 0.0;
     for (int w = 0; w < NB_THREADS / 32; w++) t += sm[w][threadIdx.x];
-    part[(int64_t)blockIdx.x * 2 * NB_MULTI_MAX + threadIdx.x] = t;
+    part[(int64_t)blockIdx.x * 4 + threadIdx.x] = t;
   }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(&B->counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  __shared__ double s_mine[MB_VALS], s_all[MB_MAXW][MB_VALS];
+  if (threadIdx.x < 4) {
+    double t = 0.0;
+    for (int i = 0; i < (int)gridDim.x; i++) t += __ldcg(part + (int64_t)i * 4 + threadIdx.x);
+    s_mine[threadIdx.x] = t;
+  }
+  if (threadIdx.x == 0) B->counter = 0;
+  __syncthreads();
+  comm_allgather(cm, s_mine, 4, s_all);
+  if (threadIdx.x != 0) return;
+  double s1 = 0.0, s2 = 0.0, t1 = 0.0, t2 = 0.0;
+  for (int r = 0; r < cm.world; r++) { s1 += s_all[r][0]; s2 += s_all[r][1]; t1 += s_all[r][2]; t2 += s_all[r][3]; }
+  const double ninf = d_neg_inf();
+  const double lse1 = (m == ninf || s1 == 0.0) ? ninf : m + log(s1);
+  const double lse2 = (m == ninf || s2 == 0.0) ? ninf : 2.0 * m + log(s2);
+  B->lse1 = lse1;
+  if (mode != 0) return;
+  const double ess = (!isfinite(lse1) || !isfinite(lse2)) ? B->n : exp(2.0 * lse1 - lse2);
+  nb_advance(B, ess, s1, s2, t1, t2);
 }
 
 // normalised weights after the reweight: log_w' = (log_w + d ll) - log_norm, w = exp(log_w')
@@ -360,186 +555,1074 @@ __global__ void k_reweight(const double* __restrict__ log_w, double lw_const, co
   out_w[i] = exp(v);
 }
 
-// gather particle planes by ancestor index (resample_particles, smc.rs:326-349)
-template <class T>
-__global__ void __launch_bounds__(256) k_gather(const T* __restrict__ src, T* __restrict__ dst, const uint64_t* __restrict__ idx, int64_t rows, int64_t P, int64_t n_out = -1, int64_t dst_stride = 0) {
-  int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n_out >= 0) {  // n_out offspring written plane-major with stride dst_stride (sharded resampling)
-    if (j >= n_out) return;
-    const int64_t a2 = (int64_t)idx[j];
-    for (int64_t r = (int64_t)blockIdx.y; r < rows; r += gridDim.y) dst[r * dst_stride + j] = src[r * P + a2];
-    return;
+// ---- global log_sum_exp of an array over all ranks (numerical.rs:15-38): max pass, then sum pass; each
+// ends with the mailbox exchange. out[0] = lse, out[1] = global max. ----
+__global__ void __launch_bounds__(NB_THREADS) k_glse_max(const double* __restrict__ x, int64_t P, double* __restrict__ part, unsigned* __restrict__ counter, double* __restrict__ out, const __grid_constant__ Comm cm) {
+  double mx = d_neg_inf();
+  bool nan = false;
+  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) { double v = __ldg(x + i); nan |= v != v; mx = fmax(mx, v); }
+  mx = warp_max(mx);
+  nan = __any_sync(0xffffffffu, nan);
+  __shared__ double sm[NB_THREADS / 32];
+  __shared__ int snan[NB_THREADS / 32];
+  __shared__ bool is_last;
+  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5] = mx; snan[threadIdx.x >> 5] = nan; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) { mx = fmax(mx, sm[w]); nan |= snan[w] != 0; }
+    part[blockIdx.x] = nan ? d_pos_inf() : mx;  // a NaN element makes the sum pass NaN; flag it through +inf
+    __threadfence();
+    is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
   }
-  if (j >= P) return;
-  const int64_t a = (int64_t)idx[j];
-  // rows r = blockIdx.y*8 + k (+ 8*gridDim.y ...): 8 independent loads in flight per thread
-  for (int64_t r0 = (int64_t)blockIdx.y * 8; r0 < rows; r0 += (int64_t)gridDim.y * 8) {
-    T v[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) if (r0 + k < rows) v[k] = src[(r0 + k) * P + a];
-#pragma unroll
-    for (int k = 0; k < 8; k++) if (r0 + k < rows) dst[(r0 + k) * P + j] = v[k];
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  __shared__ double s_mine[MB_VALS], s_all[MB_MAXW][MB_VALS];
+  if (threadIdx.x == 0) {
+    double m = d_neg_inf();
+    for (int i = 0; i < (int)gridDim.x; i++) m = fmax(m, __ldcg(part + i));
+    s_mine[0] = m;
+    *counter = 0;
+  }
+  __syncthreads();
+  comm_allgather(cm, s_mine, 1, s_all);
+  if (threadIdx.x == 0) {
+    double m = d_neg_inf();
+    for (int r = 0; r < cm.world; r++) m = fmax(m, s_all[r][0]);
+    out[1] = m;
   }
 }
-__global__ void k_uniform_one(double* out, uint64_t seed, uint64_t tag, int64_t n) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i * 2 >= n) return;
+__global__ void __launch_bounds__(NB_THREADS) k_glse_sum(const double* __restrict__ x, int64_t P, double* __restrict__ part, unsigned* __restrict__ counter, double* __restrict__ out, const __grid_constant__ Comm cm) {
+  const double m = out[1];
+  double acc = 0.0;
+  if (isfinite(m))
+    for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) acc += exp(__ldg(x + i) - m);
+  acc = warp_sum(acc);
+  __shared__ double sm[NB_THREADS / 32];
+  __shared__ bool is_last;
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) acc += sm[w];
+    part[blockIdx.x] = acc;
+    __threadfence();
+    is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  __shared__ double s_mine[MB_VALS], s_all[MB_MAXW][MB_VALS];
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < (int)gridDim.x; i++) t += __ldcg(part + i);
+    s_mine[0] = t;
+    *counter = 0;
+  }
+  __syncthreads();
+  comm_allgather(cm, s_mine, 1, s_all);
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int r = 0; r < cm.world; r++) t += s_all[r][0];
+    // numerical.rs:15-38: all -inf -> -inf; a non-finite max (NaN element / +inf) is returned as is
+    out[0] = m == d_neg_inf() ? m : (!isfinite(m) ? __longlong_as_double(0x7ff8000000000000LL) : (t == 0.0 ? d_neg_inf() : m + log(t)));
+  }
+}
+// sum of squares over all ranks (effective_sample_size, smc.rs:230-233): out[2] = 1 / sum w^2
+__global__ void __launch_bounds__(NB_THREADS) k_gsumsq(const double* __restrict__ x, int64_t P, double* __restrict__ part, unsigned* __restrict__ counter, double* __restrict__ out, const __grid_constant__ Comm cm) {
+  double acc = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * NB_THREADS + threadIdx.x; i < P; i += (int64_t)gridDim.x * NB_THREADS) { double v = __ldg(x + i); acc += v * v; }
+  acc = warp_sum(acc);
+  __shared__ double sm[NB_THREADS / 32];
+  __shared__ bool is_last;
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NB_THREADS / 32; w++) acc += sm[w];
+    part[blockIdx.x] = acc;
+    __threadfence();
+    is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  __shared__ double s_mine[MB_VALS], s_all[MB_MAXW][MB_VALS];
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < (int)gridDim.x; i++) t += __ldcg(part + i);
+    s_mine[0] = t;
+    *counter = 0;
+  }
+  __syncthreads();
+  comm_allgather(cm, s_mine, 1, s_all);
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int r = 0; r < cm.world; r++) t += s_all[r][0];
+    out[2] = 1.0 / t;
+  }
+}
+
+// =============================================================================================
+// the exact running-sum carry from rank to rank (global systematic / stratified resampling)
+// =============================================================================================
+// rank r starts its exact scan (fc_resample.cu) from the end value of rank r-1 and publishes its own end
+// value to every rank; afterwards every rank holds all end values (its slot routing needs them).
+__global__ void k_chain_wait(const __grid_constant__ Comm cm, unsigned long long rs, ScanCtl* __restrict__ ctl) {
+  double carry = 0.0;
+  if (cm.rank > 0) {
+    MBox* me = cm.box[cm.rank];
+    const int par = (int)(rs & 1);
+    wait_flag(&me->end_flag[par][cm.rank - 1], rs, cm.err);
+    carry = *(volatile double*)&me->end_val[par][cm.rank - 1];
+  }
+  ctl->s0 = carry;
+}
+__global__ void k_chain_publish(const __grid_constant__ Comm cm, unsigned long long rs, const ScanCtl* __restrict__ ctl) {
+  const int t = threadIdx.x, par = (int)(rs & 1);
+  if (t >= cm.world) return;
+  MBox* d = cm.box[t];
+  *(volatile double*)&d->end_val[par][cm.rank] = ctl->s0;
+  __threadfence_system();
+  st_release_sys(&d->end_flag[par][cm.rank], rs);
+}
+__global__ void k_chain_collect(const __grid_constant__ Comm cm, unsigned long long rs, double* __restrict__ ends) {
+  const int t = threadIdx.x, par = (int)(rs & 1);
+  if (t >= cm.world) return;
+  MBox* me = cm.box[cm.rank];
+  wait_flag(&me->end_flag[par][t], rs, cm.err);
+  ends[t] = *(volatile double*)&me->end_val[par][t];
+}
+
+// =============================================================================================
+// the population container and the fused per-particle kernels
+// =============================================================================================
+struct Pop {
+  double* q;     // [d_cont][n]
+  double* lp3;   // [3][n]: log_prior, log_likelihood, log_factors (trace.rs:168-177)
+  uint8_t* z;    // [n][zp]: discrete sites in PROGRAM slot order, zw bytes each
+  int64_t n;     // row stride of q / lp3 = particles in this buffer set
+};
+struct ZAcc {  // discrete value of a program slot for one particle
+  const uint8_t* rec;
+  int zw;
+  __device__ __forceinline__ long long operator()(int dslot) const { return zw == 1 ? (long long)rec[dslot] : (long long)((const int32_t*)rec)[dslot]; }
+};
+
+// plates the fused evaluator understands (lowered from the program's DOps at session create)
+enum { FP_TWOVAL_SAMPLE = 0, FP_NORMAL_OBS = 1, FP_TWOVAL_OBS = 2, FP_MIX = 3 };
+enum { FM_NONE = 0, FM_SELECT2 = 1, FM_LATENT_X = 2 };
+struct FPlate {
+  int32_t kind, n;
+  int32_t op, op_b;     // index into all_ops (FP_MIX: op = the discrete sample plate, op_b = the Normal observe)
+  int32_t m0, m1, ss;   // Normal observe: kinds of the (up to two) element-dependent mean terms; sigma is base + SELECT2
+  int32_t mt0, mt1, st; // their term indices
+};
+struct FusedProg {
+  const DOp* ops;           // all ops, program order
+  const DOp* scalar_ops;
+  const FPlate* plates;
+  const int32_t* crow;
+  const fc_expr_node* nodes;
+  int32_t n_ops, n_scalar, n_plates, zw;
+  int64_t zp, d_cont;
+};
+
+__device__ __forceinline__ double chain_const_param(const DOp& op, int j, const double* __restrict__ q, int64_t C, int64_t c, bool apply) {
+  double s = 0.0;
+  for (int t = 0; t < 3; t++) {
+    const DTerm& tm = op.p[j].t[t];
+    if (tm.kind == FC_TERM_CONST) s += tm.c;
+    else if (tm.kind == FC_TERM_LATENT) s += tm.c * q[(int64_t)tm.row * C + c];
+  }
+  if (apply && op.p[j].invariant) { double dl; s = apply_link(op.p[j].link, s, op.p[j].lo, op.p[j].hi, dl); }
+  return s;
+}
+struct NormalSetup {  // per-particle constants of a Normal observation plate (same arithmetic as k_plate_vec)
+  double base0, va0, vb0, va1, inv_a, lg_a, inv_b, lg_b;
+};
+__device__ __forceinline__ NormalSetup normal_setup(const DOp& op, const FPlate& fp, const double* __restrict__ q, int64_t C, int64_t c) {
+  NormalSetup S;
+  S.base0 = chain_const_param(op, 0, q, C, c, true);
+  const double base1 = chain_const_param(op, 1, q, C, c, true);
+  S.va0 = S.vb0 = S.va1 = 0.0;
+  if (fp.m0) { const DTerm& T0 = op.p[0].t[fp.mt0]; S.va0 = q[(int64_t)T0.row * C + c]; if (fp.m0 == FM_SELECT2) S.vb0 = q[(int64_t)T0.row_b * C + c]; }
+  if (fp.m1) { const DTerm& T1 = op.p[0].t[fp.mt1]; S.va1 = q[(int64_t)T1.row * C + c]; }
+  double sa = base1, sb = base1;
+  if (fp.ss) { const DTerm& TS = op.p[1].t[fp.st]; sa = base1 + q[(int64_t)TS.row * C + c]; sb = base1 + q[(int64_t)TS.row_b * C + c]; }
+  // an invalid sigma scores -inf through inv = 0, log = +inf (distribution.rs:189-208 guards)
+  const bool oka = sa > 0.0 && d_fin(sa), okb = sb > 0.0 && d_fin(sb);
+  S.inv_a = oka ? 1.0 / sa : 0.0; S.lg_a = oka ? log(sa) : d_pos_inf();
+  S.inv_b = okb ? 1.0 / sb : 0.0; S.lg_b = okb ? log(sb) : d_pos_inf();
+  return S;
+}
+__device__ __forceinline__ double normal_elem(const NormalSetup& S, const FPlate& fp, int zm, int zs, double lx0, double lx1, double x) {
+  double mean = S.base0;
+  if (fp.m0 == FM_SELECT2) mean += zm ? S.vb0 : S.va0;
+  if (fp.m0 == FM_LATENT_X) mean += S.va0 * lx0;
+  if (fp.m1 == FM_LATENT_X) mean += S.va1 * lx1;
+  const bool useb = fp.ss && zs;
+  const double inv = useb ? S.inv_b : S.inv_a, lg = useb ? S.lg_b : S.lg_a;
+  const double z = (x - mean) * inv;
+  double e = -0.5 * z * z - lg - 0.5 * FC_LN_2PI;
+  if (!(e == e)) e = d_neg_inf();  // non-finite mean / value: the reference's guards return -inf
+  return e;
+}
+
+// log_prior / log_likelihood / log_factors of particle c: scalar ops, then every plate, in program
+// order; elements of a plate summed in order with one accumulator (the generic kernels' order).
+__device__ __forceinline__ void fused_eval(const FusedProg& F, const double* __restrict__ q, int64_t C, int64_t c, const uint8_t* __restrict__ zrec, double (&lp)[3]) {
+  double a_prior = 0.0, a_lik = 0.0, a_fac = 0.0;
+  ZAcc za{zrec, F.zw};
+  if (F.n_scalar) scalar_ops_eval<false>(F.scalar_ops, F.n_scalar, F.crow, q, C, c, za, nullptr, F.nodes, a_prior, a_lik, a_fac);
+  lp[0] = 0.0 + a_prior; lp[1] = 0.0 + a_lik; lp[2] = 0.0 + a_fac;
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int pi = 0; pi < F.n_plates; pi++) {
+    const FPlate fp = F.plates[pi];
+    const DOp& op = F.ops[fp.op];
+    if (fp.kind == FP_TWOVAL_SAMPLE || fp.kind == FP_TWOVAL_OBS || fp.kind == FP_MIX) {
+      const double p0 = chain_const_param(op, 0, q, C, c, true);
+      const double tv0 = dist_eval<false>(op.dist, p0, 0.0, 0.0, 0.0, 0, qnan).lp;
+      const double tv1 = dist_eval<false>(op.dist, p0, 0.0, 0.0, 0.0, 1, qnan).lp;
+      const bool bern = op.dist == FC_BERNOULLI;
+      double s = 0.0;
+      if (fp.kind == FP_TWOVAL_OBS) {
+        for (int i = 0; i < fp.n; i++) {
+          const long long xi = dcol_i64(op.value_col, i);
+          s += xi == 0 ? tv0 : ((xi == 1 || bern) ? tv1 : d_neg_inf());
+        }
+        lp[1] += s;
+      } else if (fp.kind == FP_TWOVAL_SAMPLE) {
+        const int z0 = (int)op.dslot0;
+        for (int i = 0; i < fp.n; i++) {
+          const long long xi = za(z0 + i);
+          s += xi == 0 ? tv0 : ((xi == 1 || bern) ? tv1 : d_neg_inf());
+        }
+        lp[0] += s;
+      } else {
+        // FP_MIX: z#i ~ two-valued(p); x#i ~ Normal(mean[z_i], sigma[z_i]) (examples/mixture_models.rs:96-108):
+        // one pass over the particle's z record serves the discrete prior and the observation plate
+        const DOp& ob = F.ops[fp.op_b];
+        const NormalSetup S = normal_setup(ob, fp, q, C, c);
+        const int z0 = (int)op.dslot0;
+        const double* __restrict__ xs = (const double*)ob.value_col.ptr;
+        const bool x_f64 = ob.value_col.dtype == FC_COL_F64;
+        const double* __restrict__ lxc = fp.m1 == FM_LATENT_X ? (const double*)ob.p[0].t[fp.mt1].col.ptr : nullptr;
+        double sl = 0.0;
+        if (F.zw == 1 && (z0 & 15) == 0 && (F.zp & 15) == 0) {
+          for (int i0 = 0; i0 < fp.n; i0 += 16) {
+            const uint4 v = *(const uint4*)(zrec + z0 + i0);
+            const unsigned wv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int b = 0; b < 16; b++) {
+              const int i = i0 + b;
+              if (i < fp.n) {
+                const int zi = (int)((wv[b >> 2] >> ((b & 3) * 8)) & 0xffu);
+                s += zi == 0 ? tv0 : ((zi == 1 || bern) ? tv1 : d_neg_inf());
+                const double x = x_f64 ? __ldg(xs + i) : dcol_f64(ob.value_col, i);
+                sl += normal_elem(S, fp, zi != 0, zi != 0, 0.0, lxc ? __ldg(lxc + i) : 0.0, x);
+              }
+            }
+          }
+        } else {
+          for (int i = 0; i < fp.n; i++) {
+            const int zi = (int)za(z0 + i);
+            s += zi == 0 ? tv0 : ((zi == 1 || bern) ? tv1 : d_neg_inf());
+            const double x = x_f64 ? __ldg(xs + i) : dcol_f64(ob.value_col, i);
+            sl += normal_elem(S, fp, zi != 0, zi != 0, 0.0, lxc ? __ldg(lxc + i) : 0.0, x);
+          }
+        }
+        lp[0] += s;
+        lp[1] += sl;
+      }
+    } else {  // FP_NORMAL_OBS
+      const NormalSetup S = normal_setup(op, fp, q, C, c);
+      const int zm0 = fp.m0 == FM_SELECT2 ? op.p[0].t[fp.mt0].dslot : 0;
+      const int zs0 = fp.ss ? op.p[1].t[fp.st].dslot : 0;
+      const double* __restrict__ lx0c = fp.m0 == FM_LATENT_X ? (const double*)op.p[0].t[fp.mt0].col.ptr : nullptr;
+      const double* __restrict__ lx1c = fp.m1 == FM_LATENT_X ? (const double*)op.p[0].t[fp.mt1].col.ptr : nullptr;
+      double sl = 0.0;
+      for (int i = 0; i < fp.n; i++) {
+        const int zm = fp.m0 == FM_SELECT2 ? (za(zm0 + i) != 0) : 0;
+        const int zs = fp.ss ? (za(zs0 + i) != 0) : 0;
+        sl += normal_elem(S, fp, zm, zs, lx0c ? __ldg(lx0c + i) : 0.0, lx1c ? __ldg(lx1c + i) : 0.0, dcol_f64(op.value_col, i));
+      }
+      lp[1] += sl;
+    }
+  }
+}
+
+// ---- prior draw of every sample site (PriorHandler, interpreters.rs:88-104,355-372) in program order; the
+// same Philox stream and draw order as the generic k_prior_sample, so both paths give the same population ----
+__global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ FusedProg F, Pop pop, int64_t n, uint64_t seed, uint64_t stream0, uint64_t tag) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  DevRng rng(seed, stream0 + (uint64_t)c, tag);
+  uint8_t* zrec = pop.z + c * F.zp;
+  for (int oi = 0; oi < F.n_ops; oi++) {
+    const DOp& op = F.ops[oi];
+    if (!op.is_sample) continue;
+    if (op.kind == FC_OP_SAMPLE) {
+      double pv[3] = {0.0, 0.0, 0.0};
+      for (int j = 0; j < op.n_params; j++) pv[j] = eval_param_value(op, j, 0, pop.q, nullptr, c, n, F.crow, nullptr);  // scalar ops: CONST / LATENT terms only
+      double x;
+      long long xi;
+      op_dist_sample(rng, op, pv[0], pv[1], pv[2], x, xi);
+      if (op.cont) pop.q[(int64_t)F.crow[op.cslot0] * n + c] = x;
+      else if (F.zw == 1) zrec[op.dslot0] = (uint8_t)xi;
+      else ((int32_t*)zrec)[op.dslot0] = (int32_t)xi;
+    } else {  // two-valued discrete plate with a chain-constant parameter
+      const double p0 = chain_const_param(op, 0, pop.q, n, c, true);
+      const bool bern = op.dist == FC_BERNOULLI;
+      const int z0 = (int)op.dslot0;
+      for (int i = 0; i < (int)op.plate_len; i++) {
+        const bool lt = rng.uniform() < p0;
+        zrec[z0 + i] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));  // dist_sample: Bernoulli u < p; Categorical [p, 1-p] CDF search
+      }
+    }
+  }
+}
+__global__ void __launch_bounds__(128) k_smcx_score(const __grid_constant__ FusedProg F, Pop pop, int64_t n, double* __restrict__ ll) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  double lp[3];
+  fused_eval(F, pop.q, n, c, pop.z + c * F.zp, lp);
+  pop.lp3[c] = lp[0]; pop.lp3[n + c] = lp[1]; pop.lp3[2 * n + c] = lp[2];
+  ll[c] = lp[1] + lp[2];
+}
+
+// ---- one tempered single-site MH move per particle (tempered_single_site_mh, smc.rs:631-688): uniform
+// pick among the f64 sites, x' = x + scale * N(0,1), log alpha = d log_prior + beta d (loglik + factors),
+// accept rule log alpha >= 0 || u < exp(log alpha). Same random numbers as k_move_propose / k_move_accept. ----
+struct MoveX {
+  double* scale;          // [d_cont] shared per-site proposal scale
+  uint32_t* acc_cnt;      // [d_cont]
+  uint32_t* tot_cnt;
+  uint64_t seed, chain0, step_tag;
+  double beta;
+  int32_t adapt;
+};
+__global__ void __launch_bounds__(128) k_smcx_move(const __grid_constant__ FusedProg F, Pop pop, int64_t n, double* __restrict__ ll, const __grid_constant__ MoveX M) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = c < n && F.d_cont > 0;
+  int s = -1;
+  bool accept = false;
+  if (active) {
+    Philox ph(M.seed, M.chain0 + (uint64_t)c);
+    double u_site, u_acc, z0, z1;
+    ph.uniform2(0, M.step_tag, u_site, u_acc);
+    ph.normal2(1, M.step_tag, z0, z1);  // Normal::new(0,1).sample (smc.rs:656)
+    int64_t si = (int64_t)(u_site * (double)F.d_cont);
+    if (si >= F.d_cont) si = F.d_cont - 1;
+    s = (int)si;
+    double* qs = pop.q + si * n + c;
+    const double cur = *qs;
+    *qs = cur + M.scale[s] * z0;
+    double lpn[3];
+    fused_eval(F, pop.q, n, c, pop.z + c * F.zp, lpn);
+    const double c0 = pop.lp3[c], c1 = pop.lp3[n + c], c2 = pop.lp3[2 * n + c];
+    const double log_alpha = (lpn[0] - c0) + M.beta * ((lpn[1] + lpn[2]) - (c1 + c2));  // smc.rs:679-680
+    accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);
+    if (accept) {
+      pop.lp3[c] = lpn[0]; pop.lp3[n + c] = lpn[1]; pop.lp3[2 * n + c] = lpn[2];
+      ll[c] = lpn[1] + lpn[2];
+    } else {
+      *qs = cur;
+    }
+  }
+  if (!M.adapt) return;
+  // shared per-site counters: aggregate in shared memory, one global atomic per site per CTA
+  __shared__ unsigned s_tot[64], s_acc[64];
+  if (F.d_cont <= 64) {
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) { s_tot[i] = 0; s_acc[i] = 0; }
+    __syncthreads();
+    if (s >= 0) { atomicAdd(&s_tot[s], 1u); if (accept) atomicAdd(&s_acc[s], 1u); }
+    __syncthreads();
+    for (int i = threadIdx.x; i < (int)F.d_cont; i += blockDim.x) {
+      if (s_tot[i]) atomicAdd(&M.tot_cnt[i], s_tot[i]);
+      if (s_acc[i]) atomicAdd(&M.acc_cnt[i], s_acc[i]);
+    }
+  } else if (s >= 0) { atomicAdd(&M.tot_cnt[s], 1u); if (accept) atomicAdd(&M.acc_cnt[s], 1u); }
+}
+
+// ---- resampling: ancestor search + state copy in one kernel (resample_particles, smc.rs:326-349) ----
+// Output slot j (global) takes the particle at which the walk of smc.rs:263-268 / 284-289 stops: the
+// first i with S_i >= threshold_j over the exact running sums S of the SOURCE rank's weights (S_0 = its
+// carry-in). Ancestors of consecutive slots are non-decreasing, so the source reads are nearly
+// coalesced; the destination (this rank's or a peer's buffers, over NVLink) is written contiguously.
+__device__ __forceinline__ int64_t lower_bound_S(const double* __restrict__ S, int64_t n, double t) {  // first i in [0, n] with S[i] >= t, or n + 1
+  int64_t lo = 0, hi = n + 1;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (S[mid] >= t) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+__device__ __forceinline__ double resample_threshold(int method, double n_total, double u_raw, uint64_t seed, uint64_t tag, int64_t j) {
+  if (method == FC_RESAMPLE_SYSTEMATIC) return __dadd_rn(__ddiv_rn(u_raw, n_total), __ddiv_rn((double)j, n_total));  // u = gen()/n; thr = u + j/n (smc.rs:258,264)
   Philox ph(seed, 0x8000000000000000ULL);
   double a, b;
-  ph.uniform2((uint64_t)i, tag, a, b);
-  out[2 * i] = a;
-  if (2 * i + 1 < n) out[2 * i + 1] = b;
+  ph.uniform2((uint64_t)(j >> 1), tag, a, b);
+  return __ddiv_rn(__dadd_rn((double)j, (j & 1) ? b : a), n_total);  // (j + u_j)/n (smc.rs:281-283)
+}
+struct GatherArgs {
+  const double* S;        // source rank's running sums S[0..n_src] (inline walk) or null
+  const uint64_t* idx_in; // explicit ancestors (local indices), used when S is null
+  const double* us;       // explicit per-slot uniforms of a stratified resample (indexed by global slot), or null
+  int64_t n_src;
+  double n_total, u_raw;
+  int32_t method, wrap0;  // wrap0: this launch is the single u == 0 wrap slot (ancestor = last particle)
+  uint64_t seed, tag;
+  int64_t j0, cnt;        // global output slots [j0, j0 + cnt)
+  int64_t dst_off;        // destination-local index of slot j0
+  Pop src, dst;
+  int64_t d_cont, zp;
+  uint64_t* idx_out;      // optional: GLOBAL ancestor index of slot j0 + k -> idx_out[idx_off + k]
+  int64_t idx_off, first_src;
+};
+#define GA_THREADS 256
+__global__ void __launch_bounds__(GA_THREADS) k_smcx_gather(const __grid_constant__ GatherArgs A) {
+  __shared__ int64_t s_anc[GA_THREADS];
+  const int64_t k = (int64_t)blockIdx.x * GA_THREADS + threadIdx.x;
+  int64_t a = 0;
+  if (k < A.cnt) {
+    if (A.S) {
+      if (A.wrap0) a = A.n_src - 1;
+      else {
+        const int64_t j = A.j0 + k;
+        const double thr = (A.method == FC_RESAMPLE_STRATIFIED && A.us) ? __ddiv_rn(__dadd_rn((double)j, A.us[j]), A.n_total)
+                                                                        : resample_threshold(A.method, A.n_total, A.u_raw, A.seed, A.tag, j);
+        int64_t i = lower_bound_S(A.S, A.n_src, thr);
+        if (i > A.n_src) i = A.n_src;
+        a = (i == 0) ? A.n_src - 1 : (i - 1 < A.n_src - 1 ? i - 1 : A.n_src - 1);  // (i - 1).min(n - 1); i == 0 wraps
+        if (!(thr == thr)) a = A.n_src - 1;
+      }
+    } else a = (int64_t)A.idx_in[k];
+    if (A.idx_out) A.idx_out[A.idx_off + k] = (uint64_t)(A.first_src + a);
+  }
+  s_anc[threadIdx.x] = a;
+  if (k < A.cnt) {
+    const int64_t jd = A.dst_off + k;
+    // rows of q, then the three accumulators: 8 independent loads in flight per thread
+    for (int64_t r0 = 0; r0 < A.d_cont; r0 += 8) {
+      double v[8];
+#pragma unroll
+      for (int b = 0; b < 8; b++) if (r0 + b < A.d_cont) v[b] = A.src.q[(r0 + b) * A.src.n + a];
+#pragma unroll
+      for (int b = 0; b < 8; b++) if (r0 + b < A.d_cont) A.dst.q[(r0 + b) * A.dst.n + jd] = v[b];
+    }
+    const double l0 = A.src.lp3[a], l1 = A.src.lp3[A.src.n + a], l2 = A.src.lp3[2 * A.src.n + a];
+    A.dst.lp3[jd] = l0; A.dst.lp3[A.dst.n + jd] = l1; A.dst.lp3[2 * A.dst.n + jd] = l2;
+  }
+  if (A.zp == 0) return;
+  __syncthreads();
+  // discrete records: 16-byte chunks, consecutive threads on consecutive chunks of the destination
+  const int cpp = (int)(A.zp >> 4);
+  const int64_t base = (int64_t)blockIdx.x * GA_THREADS;
+  const int64_t live = min((int64_t)GA_THREADS, A.cnt - base);
+  for (int64_t ch = threadIdx.x; ch < live * cpp; ch += GA_THREADS) {
+    const int slot = (int)(ch / cpp), part = (int)(ch % cpp);
+    const uint4 v = *(const uint4*)(A.src.z + s_anc[slot] * A.zp + (int64_t)part * 16);
+    *(uint4*)(A.dst.z + (A.dst_off + base + slot) * A.zp + (int64_t)part * 16) = v;
+  }
+}
+
+// ---- container <-> the generic engine's int32 planes ----
+__global__ void k_z_unpack(const uint8_t* __restrict__ z, int64_t zp, int zw, const int32_t* __restrict__ drow, int64_t d_disc, disc_t* __restrict__ qd, int64_t n) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  const uint8_t* rec = z + c * zp;
+  for (int64_t s = 0; s < d_disc; s++) qd[(int64_t)drow[s] * n + c] = zw == 1 ? (disc_t)rec[s] : ((const int32_t*)rec)[s];
+}
+__global__ void k_z_pack(const disc_t* __restrict__ qd, const int32_t* __restrict__ drow, int64_t d_disc, uint8_t* __restrict__ z, int64_t zp, int zw, int64_t n, int* __restrict__ overflow) {
+  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  uint8_t* rec = z + c * zp;
+  for (int64_t s = 0; s < d_disc; s++) {
+    const disc_t v = qd[(int64_t)drow[s] * n + c];
+    if (zw == 1) { if (v < 0 || v > 255) *overflow = 1; rec[s] = (uint8_t)v; }
+    else ((int32_t*)rec)[s] = v;
+  }
 }
 
 }  // namespace fc
+
+// =============================================================================================
+// session
+// =============================================================================================
+#define FC_SMC_HANDLE_MAGIC 0x46435350u
+struct SmcHandle {  // FC_SMC_HANDLE_BYTES
+  cudaIpcMemHandle_t ipc;  // 64 bytes
+  uint32_t magic;
+  int32_t rank, device, _pad;
+  int64_t n_local, first, pid;
+  char _fill[128 - 64 - 16 - 24];
+};
+static_assert(sizeof(SmcHandle) == FC_SMC_HANDLE_BYTES, "handle size");
 
 struct fc_smc_session {
   fc_program* P = nullptr;
   fc_smc_config cfg;
   uint64_t seed = 0;
-  int64_t n = 0;
-  fc::MoveEngine eng;
-  fc::DevBuf<double> q, q2, lp3, lp3b, total, ll, log_w, comb, w, scratch, us;
-  fc::DevBuf<fc::disc_t> qd, qd2;
-  fc::DevBuf<uint64_t> idx, n_accept;
+  int64_t n = 0, n_total = 0, first = 0;  // first: global index of local particle 0
+  uint64_t stream0 = 0;                   // random stream of local particle 0
+  int rank = 0, world = 1;
+  bool connected = false;
+  // slab: mailbox + the two population buffer sets (exported to the peers)
+  char* slab = nullptr;
+  size_t slab_bytes = 0;
+  size_t off_q[2] = {0, 0}, off_lp3[2] = {0, 0}, off_z[2] = {0, 0};
+  int cur = 0;
+  int zw = 1;
+  int64_t zp = 0;
+  char* peer_slab[MB_MAXW] = {nullptr};
+  int64_t peer_n[MB_MAXW] = {0}, bounds[MB_MAXW + 1] = {0};
+  fc::Comm cm;
+  fc::DevBuf<unsigned long long> seq;
+  fc::DevBuf<int> err;
+  unsigned long long resamples = 0;  // global resamples started (mailbox sequence of the carry chain)
+  // local arrays
+  fc::DevBuf<double> ll, log_w, comb, w, S, us, part, scal, ends;
+  fc::DevBuf<char> work;
+  fc::DevBuf<uint64_t> idx;
   fc::DevBuf<fc::Bisect> bis;
   fc::DevBuf<fc::Tri> tri;
-  bool log_w_uniform = true;  // log_w == -ln n everywhere (initially and after every resample)
+  fc::DevBuf<unsigned> counter;
+  bool log_w_uniform = true;  // log_w == -ln n_total everywhere (initially and after every resample)
   fc::ResampleWork* rw = nullptr;
-  double beta = 0.0, log_evidence = 0.0;
-  uint64_t steps = 0, moves = 0;
+  // fused evaluator
+  bool fused = false;
+  fc::DevBuf<fc::FPlate> fplates;
+  fc::FusedProg F;
+  // generic engine
+  fc::MoveEngine eng;
+  fc::DevBuf<fc::disc_t> qd32;
+  fc::DevBuf<double> total;
+  fc::DevBuf<uint64_t> n_accept;
+  bool qd32_valid = false;
+  double beta = 0.0, log_evidence = 0.0, prev_dbeta = 0.0;
+  uint64_t steps = 0, moves = 0, migrated = 0, ess_evals = 0;
   bool finished = false;
-  double n_global = 0.0;  // population size the uniform weight refers to (0: this session's own n)
-  bool shard_prepass_ok = false, shard_ll_bad = false;  // max(ll) / bad flag in `bis` describe the current ll (fc_smc_shard_tri)
+  bool record = false;               // keep the global ancestors of the slots this rank produces (parity tests)
+  int64_t last_jlo = 0, last_jhi = 0;
+  bool bis_ll_valid = false;         // max(ll) / bad flag in `bis` describe the current ll
+
+  fc::Pop pop(int which) const {
+    fc::Pop p;
+    p.q = (double*)(slab + off_q[which]); p.lp3 = (double*)(slab + off_lp3[which]); p.z = (uint8_t*)(slab + off_z[which]); p.n = n;
+    return p;
+  }
+  fc::Pop peer_pop(int r, int which) const {  // rank r's buffer set as mapped here (same layout formula, its own n)
+    fc::Pop p;
+    size_t oq[2], ol[2], oz[2];
+    layout(peer_n[r], P->d_cont, zp, oq, ol, oz);
+    char* b = r == rank ? slab : peer_slab[r];
+    p.q = (double*)(b + oq[which]); p.lp3 = (double*)(b + ol[which]); p.z = (uint8_t*)(b + oz[which]); p.n = peer_n[r];
+    return p;
+  }
+  static size_t layout(int64_t n, int64_t d_cont, int64_t zp, size_t (&oq)[2], size_t (&ol)[2], size_t (&oz)[2]) {
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    size_t o = up(sizeof(fc::MBox));
+    for (int k = 0; k < 2; k++) { oq[k] = o; o = up(o + (size_t)std::max<int64_t>(1, d_cont * n) * 8); }
+    for (int k = 0; k < 2; k++) { ol[k] = o; o = up(o + (size_t)3 * n * 8); }
+    for (int k = 0; k < 2; k++) { oz[k] = o; o = up(o + (size_t)std::max<int64_t>(16, zp * n)); }
+    return o;
+  }
 };
 
 namespace fc {
 
-// one resident wave: 4 CTAs of 256 threads per SM (56 registers), never more than RDB partials
-static int nb_blocks(int64_t n) {
+static int sm_count_cached() {
   static int sms = 0;
   if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
-  return (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(RDB, 4 * sms), cdiv(n, NB_THREADS * 8)));
+  return sms;
+}
+// one resident wave: 4 CTAs of 256 threads per SM, never more than RDB partials
+static int nb_blocks(int64_t n) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(RDB, 4 * sm_count_cached()), cdiv(n, NB_THREADS * 8)));
+}
+// debug switches (fc_debug_set): "nb_plain" = the reference's plain 64-step bisection without the search
+// phase; "smc_generic" = run every program on the generic scoring engine instead of the fused kernels
+static int g_nb_plain = -1, g_smc_generic = -1;
+static bool nb_plain() {
+  if (g_nb_plain < 0) g_nb_plain = getenv("FC_NB_PLAIN") != nullptr;
+  return g_nb_plain != 0;
+}
+static bool smc_generic() {
+  if (g_smc_generic < 0) g_smc_generic = getenv("FC_SMC_GENERIC") != nullptr;
+  return g_smc_generic != 0;
 }
 
-static int32_t next_beta_dev(cudaStream_t st, const double* lw, double lwc, const double* ll, int64_t n, double beta, double target_ess, Bisect* d_bis, Tri* d_tri,
-                             uint64_t* launches, double* out) {
+static int32_t comm_check(fc_smc_session* S) {  // after a stream synchronisation
+  int e = 0;
+  FC_CUDA(cudaMemcpy(&e, S->err.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (e) { set_error("rank %d: a peer did not answer a device-side exchange within %d s", S->rank, (int)(COMM_TIMEOUT_NS / 1000000000ULL)); return FC_ERR_NCCL; }
+  return FC_OK;
+}
+
+// ---- next_beta on the session's (uniform) weights ----
+static void bisect_init(Bisect& hb, double beta, double target, double n_total, double guess) {
+  memset(&hb, 0, sizeof(hb));
+  hb.beta = beta; hb.lo = beta; hb.hi = 1.0; hb.a = beta; hb.b = 1.0; hb.mid = 1.0; hb.target = target; hb.n = n_total;
+  hb.guess = guess; hb.plain = nb_plain() ? 1 : 0;
+}
+static int32_t next_beta_uniform(cudaStream_t st, const Comm& cm, double lwc, const double* ll, int64_t n, double n_total, double beta, double target_ess, double guess,
+                                 Bisect* d_bis, double* d_part, uint64_t* launches, uint64_t* evals, double* out) {
   const int nb = nb_blocks(n);
   Bisect hb;
-  hb.beta = beta; hb.lo = beta; hb.hi = 1.0; hb.mid = 1.0; hb.target = target_ess; hb.n = (double)n; hb.lse1 = 0.0; hb.done = 0; hb.counter = 0;
-  hb.max_ll = 0.0; hb.bad = 0; hb._pad = 0;
+  bisect_init(hb, beta, target_ess, n_total, guess);
   FC_CUDA(cudaMemcpyAsync(d_bis, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
-  if (!lw) { k_nb_prepass<<<nb, NB_THREADS, 0, st>>>(ll, n, d_bis, (double*)d_tri); if (launches) *launches += 1; }
-  for (int it = 0; it < 65; it++) {
-    if (lw) k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, ll, d_bis, d_tri, n, 0, it == 0 ? 1 : 0, 0.0);
-    else k_nb_eval_uni<<<nb, NB_THREADS, 0, st>>>(lwc, ll, d_bis, d_tri, n, 0, it == 0 ? 1 : 0, 0.0);
+  k_nb_prepass<<<nb, NB_THREADS, 0, st>>>(ll, n, d_bis, d_part, cm);
+  int launched = 1;
+  // a batch of evaluations (launches after the search has finished return at once), one read-back per batch
+  int batch = hb.plain ? 58 : 30;
+  for (int round = 0; round < 8 && !hb.done; round++) {
+    for (int it = 0; it < batch; it++) k_nb_eval_uni<<<nb, NB_THREADS, 0, st>>>(lwc, ll, d_bis, d_part, n, 0, 0.0, cm);
+    launched += batch;
+    FC_CUDA(cudaMemcpyAsync(&hb, d_bis, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    batch = 12;
+  }
+  FC_KERNEL_CHECK();
+  if (launches) *launches += launched;
+  if (evals) *evals += hb.evals;
+  if (hb.done == 1) { *out = 1.0; return FC_OK; }
+  if (!hb.done) { set_error("next_beta: the search did not terminate"); return FC_ERR_CUDA; }
+  *out = std::fmin(std::fmax(hb.hi, beta + 1e-9), 1.0);  // smc.rs:621
+  return FC_OK;
+}
+// arbitrary log_w, one rank: the reference's plain bisection
+static int32_t next_beta_general(cudaStream_t st, const double* lw, const double* ll, int64_t n, double beta, double target_ess, Bisect* d_bis, Tri* d_tri, uint64_t* launches, double* out) {
+  const int nb = nb_blocks(n);
+  Bisect hb;
+  bisect_init(hb, beta, target_ess, (double)n, 0.0);
+  hb.plain = 1;
+  FC_CUDA(cudaMemcpyAsync(d_bis, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
+  for (int it = 0; it < 66; it++) {
+    k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, ll, d_bis, d_tri, n, 0, 0.0);
     if (launches) *launches += 1;
-    if (it == 0 || it == 56) {  // early exits: ess_at(1) >= target, or the interval has collapsed
+    if (it == 0 || it == 56) {
       FC_CUDA(cudaMemcpyAsync(&hb, d_bis, sizeof(hb), cudaMemcpyDeviceToHost, st));
       FC_CUDA(cudaStreamSynchronize(st));
-      if (hb.done == 1) { *out = 1.0; return FC_OK; }
-      if (hb.done == 2) break;
+      if (hb.done) break;
     }
   }
   FC_KERNEL_CHECK();
   FC_CUDA(cudaMemcpyAsync(&hb, d_bis, sizeof(hb), cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
-  *out = std::fmin(std::fmax(hb.hi, beta + 1e-9), 1.0);  // smc.rs:621
-  return FC_OK;
-}
-static int32_t smc_next_beta(fc_smc_session* S, double target_ess, double* out) {
-  return next_beta_dev(S->P->stream, S->log_w_uniform ? nullptr : S->log_w.p, -std::log((double)S->n), S->ll.p, S->n, S->beta, target_ess, S->bis.p, S->tri.p,
-                       &S->P->n_kernel_launches, out);
-}
-
-// reweight (smc.rs:512-531): log_norm = lse(log_w + d ll); w = exp(log_w + d ll - log_norm).
-// log_w itself is only materialised when it will be read again (the final step).
-static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, double* log_norm) {
-  cudaStream_t st = S->P->stream;
-  int64_t n = S->n;
-  const double* lw = S->log_w_uniform ? nullptr : S->log_w.p;
-  const double lwc = -std::log((double)n);
-  FC_CUDA(cudaMemsetAsync(&S->bis.p->counter, 0, sizeof(unsigned), st));
-  // (max_ll / bad in the Bisect block are those of this step's next_beta pre-pass: same ll)
-  if (lw) k_nb_eval<<<nb_blocks(n), NB_THREADS, 0, st>>>(lw, lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
-  else k_nb_eval_uni<<<nb_blocks(n), NB_THREADS, 0, st>>>(lwc, S->ll.p, S->bis.p, S->tri.p, n, 1, 0, d_beta);
-  k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n, (double)n);
-  FC_KERNEL_CHECK();
-  S->P->n_kernel_launches += 2;
-  Bisect hb;
-  FC_CUDA(cudaMemcpyAsync(&hb, S->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  *log_norm = hb.lse1;
-  if (write_log_w) { std::swap(S->log_w.p, S->comb.p); std::swap(S->log_w.n, S->comb.n); S->log_w_uniform = false; }
+  if (hb.done == 1) { *out = 1.0; return FC_OK; }
+  *out = std::fmin(std::fmax(hb.hi, beta + 1e-9), 1.0);
   return FC_OK;
 }
 
-// one tempering step (the body of the while loop, smc.rs:502-559); returns beta
-static int32_t smc_temper_step(fc_smc_session* S) {
-  fc_program* P = S->P;
-  cudaStream_t st = P->stream;
-  int64_t n = S->n;
-  unsigned nbk = (unsigned)cdiv(n, 256);
-  const double neg_ln_n = -std::log((double)n);
-  double target_ess = std::fmin(std::fmax(S->cfg.ess_threshold * (double)n, 1.0), (double)n);
-  S->steps += 1;
-  double beta_new;
-  FC_TRY(smc_next_beta(S, target_ess, &beta_new));
-  if (S->steps >= 10000) beta_new = 1.0;
-  double d_beta = beta_new - S->beta;
-  double log_norm;
-  FC_TRY(smc_reweight(S, d_beta, beta_new >= 1.0, &log_norm));
-  S->log_evidence += log_norm;
-  S->beta = beta_new;
-  if (S->beta < 1.0) {
-    // resample (smc.rs:534-541)
-    int64_t nu = S->cfg.resampling_method == FC_RESAMPLE_SYSTEMATIC ? 1 : n;
-    FC_CUDA(S->us.reserve(nu + 1));
-    k_uniform_one<<<(unsigned)cdiv(cdiv(nu, 2), 256), 256, 0, st>>>(S->us.p, S->seed, 0x1000000000000000ULL | S->steps, nu);
-    FC_TRY(resample_dev(S->cfg.resampling_method, S->w.p, n, S->us.p, S->idx.p, *S->rw, st, &P->n_kernel_launches));
-    dim3 gg(nbk, 1);
-    if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_cont, 8), 64); k_gather<double><<<gg, 256, 0, st>>>(S->q.p, S->q2.p, S->idx.p, P->d_cont, n); std::swap(S->q.p, S->q2.p); std::swap(S->q.n, S->q2.n); }
-    // large populations: one CTA row walks all planes (the ancestor index is read once, not once per plane group: 2.89 -> 2.23 ms at 2^24 x 80 planes)
-    if (P->d_disc) { gg.y = n >= (1 << 20) ? 1u : (unsigned)std::min<int64_t>(cdiv(P->d_disc, 8), 64); k_gather<disc_t><<<gg, 256, 0, st>>>(S->qd.p, S->qd2.p, S->idx.p, P->d_disc, n); std::swap(S->qd.p, S->qd2.p); std::swap(S->qd.n, S->qd2.n); }
-    gg.y = 1;
-    k_gather<double><<<gg, 256, 0, st>>>(S->lp3.p, S->lp3b.p, S->idx.p, 3, n);
-    std::swap(S->lp3.p, S->lp3b.p); std::swap(S->lp3.n, S->lp3b.n);
-    S->log_w_uniform = true;  // weight 1/n, log_weight ln(1/n) (smc.rs:338-345); materialised on demand
-    FC_KERNEL_CHECK();
-    P->n_kernel_launches += 4;
-    // pi_beta-invariant rejuvenation (smc.rs:544-554)
-    for (uint64_t r = 0; r < S->cfg.rejuvenation_steps; r++) {
-      FC_TRY(S->eng.step(S->q.p, S->qd.p, S->lp3.p, S->total.p, S->n_accept.p, S->moves, S->beta, true, 0.44, 0.7));
-      FC_TRY(S->eng.shared_adapt(0.44, 0.7));
-      S->moves += 1;
-    }
-    k_loglik<<<nbk, 256, 0, st>>>(S->lp3.p, S->ll.p, n);
-    FC_KERNEL_CHECK();
-    P->n_kernel_launches += 1;
+// a one-rank communicator for the standalone entry points
+struct LocalComm {
+  DevBuf<char> box;
+  DevBuf<unsigned long long> seq;
+  DevBuf<int> err;
+  Comm cm;
+  int32_t init() {
+    FC_CUDA(box.reserve(sizeof(MBox))); FC_CUDA(seq.reserve(1)); FC_CUDA(err.reserve(1));
+    FC_CUDA(cudaMemset(box.p, 0, sizeof(MBox))); FC_CUDA(cudaMemset(seq.p, 0, 8)); FC_CUDA(cudaMemset(err.p, 0, 4));
+    memset(&cm, 0, sizeof(cm));
+    cm.box[0] = (MBox*)box.p; cm.rank = 0; cm.world = 1; cm.seq = seq.p; cm.err = err.p;
+    return FC_OK;
   }
-  (void)neg_ln_n;
-  return FC_OK;
-}
+};
 
 // standalone probe of next_beta on host arrays (parity test against the oracle)
 int32_t next_beta_host(const double* h_log_w, const double* h_ll, size_t n, double beta, double target_ess, double* out) {
-  DevBuf<double> lw, ll;
+  DevBuf<double> lw, ll, part;
   DevBuf<Bisect> bis;
   DevBuf<Tri> tri;
-  FC_CUDA(lw.reserve(n)); FC_CUDA(ll.reserve(n)); FC_CUDA(bis.reserve(1)); FC_CUDA(tri.reserve(RDB + 1));
+  FC_CUDA(lw.reserve(n)); FC_CUDA(ll.reserve(n)); FC_CUDA(bis.reserve(1)); FC_CUDA(tri.reserve(RDB + 1)); FC_CUDA(part.reserve(4 * RDB + 8));
   bool uniform = true;  // the state adaptive_smc calls next_beta in: takes the single-stream path
   for (size_t i = 1; i < n && uniform; i++) uniform = h_log_w[i] == h_log_w[0];
   if (!uniform) FC_CUDA(cudaMemcpy(lw.p, h_log_w, n * 8, cudaMemcpyHostToDevice));
   FC_CUDA(cudaMemcpy(ll.p, h_ll, n * 8, cudaMemcpyHostToDevice));
-  return next_beta_dev(nullptr, uniform ? nullptr : lw.p, h_log_w[0], ll.p, (int64_t)n, beta, target_ess, bis.p, tri.p, nullptr, out);
+  if (!uniform) return next_beta_general(nullptr, lw.p, ll.p, (int64_t)n, beta, target_ess, bis.p, tri.p, nullptr, out);
+  LocalComm lc;
+  FC_TRY(lc.init());
+  return next_beta_uniform(nullptr, lc.cm, h_log_w[0], ll.p, (int64_t)n, (double)n, beta, target_ess, 0.0, bis.p, part.p, nullptr, nullptr, out);
 }
 
-// log_w as an array (callers that read it: fc_smc_get, fc_smc_device_state)
+static double lwc_of(const fc_smc_session* S) { return -std::log((double)S->n_total); }
+
+static int32_t ensure_qd32(fc_smc_session* S) {
+  fc_program* P = S->P;
+  if (S->qd32_valid || P->d_disc == 0) return FC_OK;
+  FC_CUDA(S->qd32.reserve(P->d_disc * S->n));
+  k_z_unpack<<<(unsigned)cdiv(S->n, 256), 256, 0, P->stream>>>(S->pop(S->cur).z, S->zp, S->zw, P->d_drow.p, P->d_disc, S->qd32.p, S->n);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
+  S->qd32_valid = true;
+  return FC_OK;
+}
+
+// log_w as an array (callers that read it: fc_smc_get, fc_smc_device_state, fc_smc_weights)
 static int32_t smc_materialise_log_w(fc_smc_session* S) {
   if (!S->log_w_uniform) return FC_OK;
-  k_fill2<<<(unsigned)cdiv(S->n, 256), 256, 0, S->P->stream>>>(S->log_w.p, -std::log(S->n_global > 0.0 ? S->n_global : (double)S->n), S->n);
+  k_fill2<<<(unsigned)cdiv(S->n, 256), 256, 0, S->P->stream>>>(S->log_w.p, lwc_of(S), S->n);
   FC_KERNEL_CHECK();
   S->P->n_kernel_launches += 1;
+  return FC_OK;
+}
+
+// global log_sum_exp of a local array (+ optional ESS of exp(x - lse)); results in S->scal[0..2] on the device
+static int32_t global_lse(fc_smc_session* S, const double* d_x, double* h_lse) {
+  cudaStream_t st = S->P->stream;
+  const int nb = nb_blocks(S->n);
+  k_glse_max<<<nb, NB_THREADS, 0, st>>>(d_x, S->n, S->part.p, S->counter.p, S->scal.p, S->cm);
+  k_glse_sum<<<nb, NB_THREADS, 0, st>>>(d_x, S->n, S->part.p, S->counter.p, S->scal.p, S->cm);
+  FC_KERNEL_CHECK();
+  S->P->n_kernel_launches += 2;
+  if (h_lse) {
+    FC_CUDA(cudaMemcpyAsync(h_lse, S->scal.p, 8, cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    FC_TRY(comm_check(S));
+  }
+  return FC_OK;
+}
+
+// reweight (smc.rs:512-531): log_norm = lse(log_w + d ll) over ALL ranks; w = exp(log_w + d ll - log_norm).
+// log_w itself is only materialised when it will be read again (write_log_w).
+static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, double* log_norm) {
+  cudaStream_t st = S->P->stream;
+  const int64_t n = S->n;
+  const double lwc = lwc_of(S);
+  if (S->log_w_uniform) {
+    Bisect hb;
+    if (!S->bis_ll_valid) {  // max(ll) / bad flag: those of this step's next_beta pre-pass when it ran on the same ll
+      bisect_init(hb, S->beta, 0.0, (double)S->n_total, 0.0);
+      FC_CUDA(cudaMemcpyAsync(S->bis.p, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
+      k_nb_prepass<<<nb_blocks(n), NB_THREADS, 0, st>>>(S->ll.p, n, S->bis.p, S->part.p, S->cm);
+      S->P->n_kernel_launches += 1;
+      S->bis_ll_valid = true;
+    }
+    k_nb_eval_uni<<<nb_blocks(n), NB_THREADS, 0, st>>>(lwc, S->ll.p, S->bis.p, S->part.p, n, 1, d_beta, S->cm);
+    k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(nullptr, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n, (double)S->n_total);
+    FC_KERNEL_CHECK();
+    S->P->n_kernel_launches += 2;
+    FC_CUDA(cudaMemcpyAsync(&hb, S->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    FC_TRY(comm_check(S));
+    *log_norm = hb.lse1;
+  } else {
+    // general weights: combined = log_w + d ll, global lse, then normalise
+    unsigned nbk = (unsigned)cdiv(n, 256);
+    FC_CUDA(S->us.reserve(n + 1));
+    k_combine<<<nbk, 256, 0, st>>>(S->log_w.p, 0.0, S->ll.p, d_beta, S->us.p, n);
+    FC_TRY(global_lse(S, S->us.p, log_norm));
+    k_sub_exp<<<nbk, 256, 0, st>>>(S->us.p, S->scal.p, (double)S->n_total, write_log_w ? S->comb.p : nullptr, S->w.p, n);
+    FC_KERNEL_CHECK();
+    S->P->n_kernel_launches += 2;
+  }
+  if (write_log_w) { std::swap(S->log_w.p, S->comb.p); std::swap(S->log_w.n, S->comb.n); S->log_w_uniform = false; }
+  return FC_OK;
+}
+
+// ---- host replica of the device threshold arithmetic (slot routing of a sharded resample) ----
+static void host_philox_uniform2(uint64_t seed, uint64_t stream, uint64_t ctr_lo, uint64_t ctr_hi, double& u0, double& u1) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ULL * (stream + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z ^= z >> 31;
+  uint32_t a = (uint32_t)z, b = (uint32_t)(z >> 32);
+  uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+  for (int r = 0; r < 10; r++) {
+    uint64_t m0 = (uint64_t)0xD2511F53u * c0, m1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t hi0 = (uint32_t)(m0 >> 32), lo0 = (uint32_t)m0, hi1 = (uint32_t)(m1 >> 32), lo1 = (uint32_t)m1;
+    uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    a += 0x9E3779B9u; b += 0xBB67AE85u;
+  }
+  uint64_t x = ((uint64_t)c0 << 32) | c1, y = ((uint64_t)c2 << 32) | c3;
+  u0 = (double)(x >> 11) * 0x1.0p-53;
+  u1 = (double)(y >> 11) * 0x1.0p-53;
+}
+static double host_threshold(int method, double n_total, double u_raw, uint64_t seed, uint64_t tag, int64_t j) {
+  if (method == FC_RESAMPLE_SYSTEMATIC) {
+    volatile double a = u_raw / n_total, b = (double)j / n_total;  // two roundings, then the add (no contraction)
+    return a + b;
+  }
+  double u0, u1;
+  host_philox_uniform2(seed, 0x8000000000000000ULL, (uint64_t)(j >> 1), tag, u0, u1);
+  volatile double s = (double)j + ((j & 1) ? u1 : u0);
+  return s / n_total;
+}
+// #{ j in [0, N) : threshold_j <= x } (thresholds are non-decreasing in j)
+static int64_t count_thresholds_le(int method, int64_t N, double u_raw, uint64_t seed, uint64_t tag, double x) {
+  int64_t lo = 0, hi = N;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) / 2;
+    if (host_threshold(method, (double)N, u_raw, seed, tag, mid) <= x) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// Global resample of the rank-major population (smc.rs:255-292, 326-349, 534-541). Weights in S->w are
+// normalised by the GLOBAL log-sum-exp. h_uniforms: explicit uniforms (1 raw value for systematic; n
+// for stratified / multinomial, single rank only) or NULL = the session's Philox stream.
+// h_idx (n entries, optional): GLOBAL ancestor index of every local output slot.
+static int32_t smc_resample(fc_smc_session* S, int method, const double* h_uniforms, uint64_t* h_idx) {
+  fc_program* P = S->P;
+  cudaStream_t st = P->stream;
+  const int64_t n = S->n, N = S->n_total;
+  const int W = S->world;
+  if (method < FC_RESAMPLE_MULTINOMIAL || method > FC_RESAMPLE_STRATIFIED) { set_error("bad resampling method %d", method); return FC_ERR_INVALID_ARGUMENT; }
+  if (W > 1 && method == FC_RESAMPLE_MULTINOMIAL) { set_error("multinomial resampling is not available on a sharded population (its ancestors are not monotone in the slot index); use Systematic or Stratified"); return FC_ERR_UNSUPPORTED_OP; }
+  if (W > 1 && method == FC_RESAMPLE_STRATIFIED && h_uniforms) { set_error("explicit stratified uniforms are not available on a sharded population"); return FC_ERR_UNSUPPORTED_OP; }
+  S->resamples += 1;
+  const uint64_t tag = 0x1000000000000000ULL | S->resamples;
+  const int from = S->cur, to = S->cur ^ 1;
+  GatherArgs G;
+  memset(&G, 0, sizeof(G));
+  G.n_src = n; G.n_total = (double)N; G.method = method; G.seed = S->seed; G.tag = tag; G.src = S->pop(from);
+  G.d_cont = P->d_cont; G.zp = S->zp; G.first_src = S->first;
+  const bool want_idx = h_idx || S->record;
+  double u_raw = 0.0;
+  if (method == FC_RESAMPLE_MULTINOMIAL) {
+    // single rank: ancestors by search over the exact running sums (fc_resample.cu), then the copy
+    FC_CUDA(S->us.reserve(n + 1));
+    if (h_uniforms) FC_CUDA(cudaMemcpyAsync(S->us.p, h_uniforms, n * 8, cudaMemcpyHostToDevice, st));
+    else k_uniform_one<<<(unsigned)cdiv(cdiv(n, 2), 256), 256, 0, st>>>(S->us.p, S->seed, tag, n);
+    FC_TRY(resample_dev(method, S->w.p, n, S->us.p, S->idx.p, *S->rw, st, &P->n_kernel_launches));
+    G.S = nullptr; G.idx_in = S->idx.p; G.idx_out = nullptr; G.j0 = 0; G.cnt = n; G.dst_off = 0; G.dst = S->pop(to);
+    S->last_jlo = 0; S->last_jhi = n;
+    k_smcx_gather<<<(unsigned)cdiv(n, GA_THREADS), GA_THREADS, 0, st>>>(G);
+    FC_KERNEL_CHECK();
+    P->n_kernel_launches += 2;
+    if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, S->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
+  } else {
+    if (method == FC_RESAMPLE_SYSTEMATIC) {
+      if (h_uniforms) u_raw = h_uniforms[0];
+      else { double u1; host_philox_uniform2(S->seed, 0x8000000000000000ULL, 0, tag, u_raw, u1); }  // element 0 of k_uniform_one's stream: identical on every rank
+    } else if (h_uniforms) {
+      FC_CUDA(S->us.reserve(n + 1));
+      FC_CUDA(cudaMemcpyAsync(S->us.p, h_uniforms, n * 8, cudaMemcpyHostToDevice, st));
+      G.us = S->us.p;
+    }
+    G.u_raw = u_raw;
+    // exact running sums of this rank's weights from the carry-in of the ranks before it
+    FC_CUDA(S->work.reserve(scan_work_bytes(n)));
+    ScanCtl hs;
+    memset(&hs, 0, sizeof(hs));
+    FC_CUDA(cudaMemcpyAsync(S->work.p, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
+    k_chain_wait<<<1, 1, 0, st>>>(S->cm, S->resamples, (ScanCtl*)S->work.p);
+    FC_TRY(scan_enqueue_head(S->w.p, n, S->S.p, S->work.p, st, &P->n_kernel_launches));
+    FC_TRY(scan_enqueue_rounds(S->w.p, n, S->S.p, S->work.p, S->rank == 0 ? scan_expected_rounds(n) : 3, st, &P->n_kernel_launches));
+    FC_TRY(scan_finish(S->w.p, n, S->S.p, S->work.p, st, &P->n_kernel_launches, nullptr));
+    P->n_kernel_launches += 1;
+    double ends[MB_MAXW] = {0.0};
+    if (W > 1) {
+      k_chain_publish<<<1, 32, 0, st>>>(S->cm, S->resamples, (const ScanCtl*)S->work.p);
+      k_chain_collect<<<1, 32, 0, st>>>(S->cm, S->resamples, S->ends.p);
+      FC_KERNEL_CHECK();
+      P->n_kernel_launches += 2;
+      FC_CUDA(cudaMemcpyAsync(ends, S->ends.p, W * 8, cudaMemcpyDeviceToHost, st));
+      FC_CUDA(cudaStreamSynchronize(st));
+      FC_TRY(comm_check(S));
+    }
+    // slots whose ancestor lives here: carry_in < threshold_j <= end (the last rank also takes the slots
+    // whose threshold is never reached); the u == 0 wrap slot (threshold_0 == 0 -> i = 0 -> n - 1) belongs to
+    // the last rank's last particle
+    const double carry_in = S->rank == 0 ? 0.0 : ends[S->rank - 1];
+    auto cnt_le = [&](double x) { return count_thresholds_le(method, N, u_raw, S->seed, tag, x); };
+    int64_t jlo, jhi;
+    if (W == 1) { jlo = 0; jhi = N; }
+    else {
+      jlo = cnt_le(carry_in);
+      jhi = S->rank == W - 1 ? N : cnt_le(ends[S->rank]);
+      if (jhi < jlo) jhi = jlo;
+    }
+    G.S = S->S.p;
+    S->last_jlo = jlo; S->last_jhi = jhi;
+    if (want_idx) FC_CUDA(S->idx.reserve(std::max<int64_t>(n, jhi - jlo)));
+    for (int t = 0; t < W; t++) {
+      const int64_t a = std::max(jlo, S->bounds[t]), b = std::min(jhi, S->bounds[t + 1]);
+      if (b <= a) continue;
+      G.j0 = a; G.cnt = b - a; G.dst_off = a - S->bounds[t]; G.dst = S->peer_pop(t, to);
+      G.idx_out = want_idx ? S->idx.p : nullptr;
+      G.idx_off = a - jlo;
+      G.wrap0 = 0;
+      k_smcx_gather<<<(unsigned)cdiv(G.cnt, GA_THREADS), GA_THREADS, 0, st>>>(G);
+      P->n_kernel_launches += 1;
+      if (t != S->rank) S->migrated += (uint64_t)(b - a);
+    }
+    if (W > 1 && S->rank == W - 1 && jlo > 0 && count_thresholds_le(method, N, u_raw, S->seed, tag, 0.0) > 0) {
+      // threshold_0 == 0 exactly: slot 0 wraps to the very last particle of the population
+      G.j0 = 0; G.cnt = 1; G.dst_off = 0; G.dst = S->peer_pop(0, to); G.wrap0 = 1; G.idx_out = nullptr;
+      k_smcx_gather<<<1, GA_THREADS, 0, st>>>(G);
+      P->n_kernel_launches += 1;
+    }
+    FC_KERNEL_CHECK();
+    if (W > 1) {
+      // every rank's offspring have landed in every rank's new buffers
+      k_comm_barrier<<<1, 32, 0, st>>>(S->cm);
+      P->n_kernel_launches += 1;
+    }
+    if (h_idx && W == 1) FC_CUDA(cudaMemcpyAsync(h_idx, S->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
+  }
+  S->cur = to;
+  S->qd32_valid = false;
+  S->bis_ll_valid = false;
+  S->log_w_uniform = true;  // weight 1/n, log_weight ln(1/n) (smc.rs:338-345); materialised on demand
+  k_loglik<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(S->pop(to).lp3, S->ll.p, n);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
+  return FC_OK;
+}
+
+// `steps` pi_beta-invariant single-site moves per particle (smc.rs:544-554, 698-713)
+static int32_t smc_rejuvenate(fc_smc_session* S, double beta, uint64_t steps) {
+  fc_program* P = S->P;
+  cudaStream_t st = P->stream;
+  const int64_t n = S->n;
+  Pop pop = S->pop(S->cur);
+  if (steps) S->bis_ll_valid = false;
+  if (S->fused) {
+    for (uint64_t r = 0; r < steps; r++) {
+      MoveX M;
+      M.scale = S->eng.scale.p; M.acc_cnt = S->eng.acc_cnt.p; M.tot_cnt = S->eng.tot_cnt.p;
+      M.seed = S->eng.seed; M.chain0 = S->eng.chain0; M.step_tag = S->moves; M.beta = beta; M.adapt = 1;
+      k_smcx_move<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(S->F, pop, n, S->ll.p, M);
+      FC_KERNEL_CHECK();
+      P->n_kernel_launches += 1;
+      FC_TRY(S->eng.shared_adapt(0.44, 0.7));
+      S->moves += 1;
+    }
+    return FC_OK;
+  }
+  FC_TRY(ensure_qd32(S));
+  for (uint64_t r = 0; r < steps; r++) {
+    FC_TRY(S->eng.step(pop.q, S->qd32.p, pop.lp3, S->total.p, S->n_accept.p, S->moves, beta, true, 0.44, 0.7));
+    FC_TRY(S->eng.shared_adapt(0.44, 0.7));
+    S->moves += 1;
+  }
+  k_loglik<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(pop.lp3, S->ll.p, n);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
+  return FC_OK;
+}
+
+// one tempering step (the body of the while loop, smc.rs:502-559)
+static int32_t smc_temper_step(fc_smc_session* S) {
+  fc_program* P = S->P;
+  const double N = (double)S->n_total;
+  const double target_ess = std::fmin(std::fmax(S->cfg.ess_threshold * N, 1.0), N);
+  S->steps += 1;
+  double beta_new;
+  if (S->log_w_uniform) {
+    const double guess = S->prev_dbeta > 0.0 ? S->beta + 4.0 * S->prev_dbeta : 0.0;
+    FC_TRY(next_beta_uniform(P->stream, S->cm, lwc_of(S), S->ll.p, S->n, N, S->beta, target_ess, guess, S->bis.p, S->part.p, &P->n_kernel_launches, &S->ess_evals, &beta_new));
+    FC_TRY(comm_check(S));
+    S->bis_ll_valid = true;
+  } else {
+    if (S->world > 1) { set_error("next_beta on non-uniform weights is not available on a sharded population"); return FC_ERR_UNSUPPORTED_OP; }
+    FC_TRY(next_beta_general(P->stream, S->log_w.p, S->ll.p, S->n, S->beta, target_ess, S->bis.p, S->tri.p, &P->n_kernel_launches, &beta_new));
+  }
+  if (S->steps >= 10000) beta_new = 1.0;
+  const double d_beta = beta_new - S->beta;
+  double log_norm;
+  FC_TRY(smc_reweight(S, d_beta, beta_new >= 1.0, &log_norm));
+  S->log_evidence += log_norm;
+  S->prev_dbeta = d_beta;
+  S->beta = beta_new;
+  if (S->beta < 1.0) {
+    FC_TRY(smc_resample(S, S->cfg.resampling_method, nullptr, nullptr));  // smc.rs:534-541
+    FC_TRY(smc_rejuvenate(S, S->beta, S->cfg.rejuvenation_steps));       // smc.rs:544-554
+  }
+  return FC_OK;
+}
+
+// which plates can the fused evaluator take? (the shapes of fc_plate_vec.cu, one particle per thread)
+static bool fused_lower(fc_program* P, std::vector<FPlate>& out, int& zw) {
+  const bool disabled = smc_generic();
+  zw = 1;
+  for (const DOp& op : P->all_ops)
+    if (op.is_sample && !op.cont) {
+      const bool small = op.dist == FC_BERNOULLI || (op.dist == FC_CATEGORICAL && (op.n_probs == 0 || op.n_probs <= 256));
+      if (!small) zw = 4;
+    }
+  if (disabled || zw != 1) return false;
+  for (size_t oi = 0; oi < P->all_ops.size(); oi++) {
+    const DOp& op = P->all_ops[oi];
+    const bool plate = op.kind == FC_OP_PLATE_SAMPLE || op.kind == FC_OP_PLATE_OBSERVE;
+    if (!plate) continue;
+    if (op.plate_len >= (1LL << 30)) return false;
+    FPlate fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.op = (int32_t)oi; fp.op_b = -1; fp.n = (int32_t)op.plate_len;
+    const bool twoval = (op.dist == FC_BERNOULLI || (op.dist == FC_CATEGORICAL && op.n_probs == 0)) && op.n_params == 1 && op.p[0].invariant;
+    if (twoval) {
+      for (int t = 0; t < 3; t++) {
+        const int k = op.p[0].t[t].kind;
+        if (!(k == FC_TERM_NONE || k == FC_TERM_CONST || k == FC_TERM_LATENT)) return false;
+      }
+      fp.kind = op.is_sample ? FP_TWOVAL_SAMPLE : FP_TWOVAL_OBS;
+      out.push_back(fp);
+      continue;
+    }
+    if (op.dist != FC_NORMAL || op.is_sample || op.n_params != 2) return false;
+    int m[2] = {FM_NONE, FM_NONE}, mt[2] = {0, 0}, nm = 0;
+    bool ss = false;
+    int st = 0;
+    for (int j = 0; j < 2; j++)
+      for (int t = 0; t < 3; t++) {
+        const DTerm& tm = op.p[j].t[t];
+        const int k = tm.kind;
+        if (k == FC_TERM_NONE || k == FC_TERM_CONST || k == FC_TERM_LATENT) continue;
+        if (op.p[j].link != FC_LINK_IDENTITY) return false;
+        if (j == 0 && k == FC_TERM_SELECT2) { if (nm == 2) return false; m[nm] = FM_SELECT2; mt[nm] = t; nm++; }
+        else if (j == 0 && k == FC_TERM_LATENT_X && tm.col.dtype == FC_COL_F64) { if (nm == 2) return false; m[nm] = FM_LATENT_X; mt[nm] = t; nm++; }
+        else if (j == 1 && k == FC_TERM_SELECT2 && !ss) { ss = true; st = t; }
+        else return false;
+      }
+    if (m[1] == FM_SELECT2) {  // canonical order: a SELECT2 mean term first
+      if (m[0] == FM_SELECT2) return false;
+      std::swap(m[0], m[1]); std::swap(mt[0], mt[1]);
+    }
+    fp.kind = FP_NORMAL_OBS; fp.m0 = m[0]; fp.m1 = m[1]; fp.ss = ss ? 1 : 0; fp.mt0 = mt[0]; fp.mt1 = mt[1]; fp.st = st;
+    // one pass over z when this plate selects on the discrete plate lowered just before it
+    if (!out.empty() && out.back().kind == FP_TWOVAL_SAMPLE && fp.m0 == FM_SELECT2 && out.back().n == fp.n) {
+      const DOp& zp_op = P->all_ops[out.back().op];
+      const bool same_m = op.p[0].t[fp.mt0].dslot == (int32_t)zp_op.dslot0;
+      const bool same_s = !ss || op.p[1].t[fp.st].dslot == (int32_t)zp_op.dslot0;
+      if (same_m && same_s) {
+        FPlate& z = out.back();
+        z.kind = FP_MIX; z.op_b = (int32_t)oi; z.m0 = fp.m0; z.m1 = fp.m1; z.ss = fp.ss; z.mt0 = fp.mt0; z.mt1 = fp.mt1; z.st = fp.st;
+        continue;
+      }
+    }
+    out.push_back(fp);
+  }
+  return true;
+}
+
+static int32_t smc_init_population(fc_smc_session* S) {
+  fc_program* p = S->P;
+  cudaStream_t st = p->stream;
+  const int64_t N = S->n;
+  Pop pop = S->pop(S->cur);
+  const uint64_t tag = 0x7000000000000000ULL;
+  if (S->fused) {
+    k_smcx_prior<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(S->F, pop, N, S->seed, S->stream0, tag);
+    k_smcx_score<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(S->F, pop, N, S->ll.p);
+    FC_KERNEL_CHECK();
+    p->n_kernel_launches += 2;
+    return FC_OK;
+  }
+  FC_CUDA(S->qd32.reserve(std::max<int64_t>(1, p->d_disc * N)));
+  FC_TRY(prior_sample_dev(p, pop.q, S->qd32.p, N, S->seed, S->stream0, tag));
+  FC_TRY(score_dev(p, pop.q, S->qd32.p, N, pop.lp3, S->total.p, nullptr));
+  unsigned nbk = (unsigned)cdiv(N, 256);
+  if (p->d_disc) {
+    FC_CUDA(cudaMemsetAsync(S->err.p, 0, 4, st));
+    k_z_pack<<<nbk, 256, 0, st>>>(S->qd32.p, p->d_drow.p, p->d_disc, pop.z, S->zp, S->zw, N, S->err.p);
+    p->n_kernel_launches += 1;
+  }
+  S->qd32_valid = true;
+  k_loglik<<<nbk, 256, 0, st>>>(pop.lp3, S->ll.p, N);
+  FC_KERNEL_CHECK();
+  p->n_kernel_launches += 1;
   return FC_OK;
 }
 
@@ -562,40 +1645,116 @@ void fc_smc_config_default(fc_smc_config* cfg) {  // SMCConfig::default (smc.rs:
 int32_t fc_smc_destroy(fc_smc_session* s) {
   if (!s) return FC_OK;
   if (s->P && s->P->stream) cudaStreamSynchronize(s->P->stream);
+  for (int r = 0; r < MB_MAXW; r++)
+    if (s->peer_slab[r]) cudaIpcCloseMemHandle(s->peer_slab[r]);
+  if (s->slab) cudaFree(s->slab);
   if (s->rw) fc::resample_work_free(s->rw);
   delete s;
   return FC_OK;
 }
 
-// smc_prior_particles (smc.rs:764-790) + the state adaptive_smc keeps (smc.rs:470-482)
-int32_t fc_smc_create(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t n, uint64_t first_particle, fc_smc_session** out) {
+// smc_prior_particles (smc.rs:764-790) + the state adaptive_smc keeps (smc.rs:470-482) for the shard
+// [first_particle, first_particle + n) of a population of n_total particles held by `world` ranks.
+// stream0: particle j of this session uses the random stream of global particle stream0 + j.
+static int32_t smc_create_impl(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t n, uint64_t stream0, uint64_t first_particle, uint64_t n_total, int32_t rank, int32_t world, fc_smc_session** out) {
   using namespace fc;
   if (!p || !cfg || !out) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
   *out = nullptr;
   if (n == 0) { set_error("num_particles must be > 0"); return FC_ERR_INVALID_ARGUMENT; }
+  if (world < 1 || world > MB_MAXW || rank < 0 || rank >= world || n_total < n || first_particle + n > n_total) { set_error("bad shard arguments (rank %d of %d, %zu of %llu particles from %llu)", rank, world, n, (unsigned long long)n_total, (unsigned long long)first_particle); return FC_ERR_INVALID_ARGUMENT; }
   FC_CUDA(cudaSetDevice(p->device));
   std::unique_ptr<fc_smc_session> S(new fc_smc_session());
-  S->P = p; S->cfg = *cfg; S->seed = seed; S->n = (int64_t)n;
-  int64_t N = S->n;
+  S->P = p; S->cfg = *cfg; S->seed = seed; S->n = (int64_t)n; S->n_total = (int64_t)n_total; S->first = (int64_t)first_particle; S->stream0 = stream0; S->rank = rank; S->world = world;
+  const int64_t N = S->n;
   cudaStream_t st = p->stream;
-  int64_t nq = std::max<int64_t>(1, p->d_cont * N), nd = std::max<int64_t>(1, p->d_disc * N);
-  FC_CUDA(S->q.reserve(nq)); FC_CUDA(S->q2.reserve(nq)); FC_CUDA(S->qd.reserve(nd)); FC_CUDA(S->qd2.reserve(nd));
-  FC_CUDA(S->lp3.reserve(3 * N)); FC_CUDA(S->lp3b.reserve(3 * N));
-  for (auto* b : {&S->total, &S->ll, &S->log_w, &S->comb, &S->w}) FC_CUDA(b->reserve(N));
-  FC_CUDA(S->scratch.reserve(2 * RDB + 16));
+  std::vector<FPlate> fpl;
+  S->fused = fused_lower(p, fpl, S->zw);
+  S->zp = p->d_disc ? ((p->d_disc * S->zw + 15) / 16) * 16 : 0;
+  S->slab_bytes = fc_smc_session::layout(N, p->d_cont, S->zp, S->off_q, S->off_lp3, S->off_z);
+  FC_CUDA(cudaMalloc((void**)&S->slab, S->slab_bytes));
+  FC_CUDA(cudaMemsetAsync(S->slab, 0, S->off_q[0], st));  // the mailbox
+  if (S->zp) { FC_CUDA(cudaMemsetAsync(S->slab + S->off_z[0], 0, (size_t)S->zp * N, st)); FC_CUDA(cudaMemsetAsync(S->slab + S->off_z[1], 0, (size_t)S->zp * N, st)); }
+  FC_CUDA(S->seq.reserve(1)); FC_CUDA(S->err.reserve(1)); FC_CUDA(S->counter.reserve(1));
+  FC_CUDA(cudaMemsetAsync(S->seq.p, 0, 8, st)); FC_CUDA(cudaMemsetAsync(S->err.p, 0, 4, st)); FC_CUDA(cudaMemsetAsync(S->counter.p, 0, 4, st));
+  memset(&S->cm, 0, sizeof(S->cm));
+  S->cm.rank = rank; S->cm.world = world; S->cm.seq = S->seq.p; S->cm.err = S->err.p;
+  S->cm.box[rank] = (MBox*)S->slab;
+  S->peer_n[rank] = N;
+  if (world == 1) { S->bounds[0] = 0; S->bounds[1] = N; S->connected = true; }
+  for (auto* b : {&S->ll, &S->log_w, &S->comb, &S->w, &S->total}) FC_CUDA(b->reserve(N));
+  FC_CUDA(S->S.reserve(N + 2));
+  FC_CUDA(S->part.reserve(4 * RDB + 8)); FC_CUDA(S->scal.reserve(8)); FC_CUDA(S->ends.reserve(MB_MAXW));
   FC_CUDA(S->idx.reserve(N)); FC_CUDA(S->n_accept.reserve(N)); FC_CUDA(S->bis.reserve(1)); FC_CUDA(S->tri.reserve(RDB + 1));
   FC_CUDA(cudaMemsetAsync(S->n_accept.p, 0, N * 8, st));
   S->rw = resample_work_new();
-  FC_TRY(S->eng.init(p, N, true, seed ^ 0x5bd1e995u, first_particle));
-  FC_TRY(prior_sample_dev(p, S->q.p, S->qd.p, N, seed, first_particle, 0x7000000000000000ULL));
-  FC_TRY(score_dev(p, S->q.p, S->qd.p, N, S->lp3.p, S->total.p, nullptr));
-  unsigned nbk = (unsigned)cdiv(N, 256);
-  k_loglik<<<nbk, 256, 0, st>>>(S->lp3.p, S->ll.p, N);
-  k_fill2<<<nbk, 256, 0, st>>>(S->log_w.p, -std::log((double)N), N);
-  FC_KERNEL_CHECK();
-  p->n_kernel_launches += 2;
+  FC_TRY(S->eng.init(p, N, true, seed ^ 0x5bd1e995u, stream0));
+  if (S->fused) {
+    FC_CUDA(S->fplates.reserve(std::max<size_t>(1, fpl.size())));
+    if (!fpl.empty()) FC_CUDA(cudaMemcpyAsync(S->fplates.p, fpl.data(), fpl.size() * sizeof(FPlate), cudaMemcpyHostToDevice, st));
+    FC_CUDA(cudaStreamSynchronize(st));
+    FusedProg& F = S->F;
+    F.ops = p->d_all_ops.p; F.scalar_ops = p->d_scalar_ops.p; F.plates = S->fplates.p; F.crow = p->d_crow.p; F.nodes = p->d_expr_nodes.p;
+    F.n_ops = (int32_t)p->all_ops.size(); F.n_scalar = (int32_t)p->scalar_ops.size(); F.n_plates = (int32_t)fpl.size(); F.zw = S->zw; F.zp = S->zp; F.d_cont = p->d_cont;
+  }
+  FC_TRY(smc_init_population(S.get()));
   FC_CUDA(cudaStreamSynchronize(st));
+  if (!S->fused && p->d_disc) {
+    int e = 0;
+    FC_CUDA(cudaMemcpy(&e, S->err.p, 4, cudaMemcpyDeviceToHost));
+    if (e) { set_error("discrete prior draw outside the byte range of the packed particle record"); return FC_ERR_UNSUPPORTED_OP; }
+  }
   *out = S.release();
+  return FC_OK;
+}
+int32_t fc_smc_create_sharded(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t n, uint64_t first_particle, uint64_t n_total, int32_t rank, int32_t world, fc_smc_session** out) {
+  return smc_create_impl(p, cfg, seed, n, first_particle, first_particle, n_total, rank, world, out);
+}
+int32_t fc_smc_create(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t n, uint64_t first_particle, fc_smc_session** out) {
+  return smc_create_impl(p, cfg, seed, n, first_particle, 0, n, 0, 1, out);
+}
+
+// the 128-byte descriptor of this rank's slab; gather every rank's (rank order) and pass them to fc_smc_connect
+int32_t fc_smc_export(fc_smc_session* s, void* handle) {
+  using namespace fc;
+  if (!s || !handle) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
+  SmcHandle h;
+  memset(&h, 0, sizeof(h));
+  FC_CUDA(cudaSetDevice(s->P->device));
+  FC_CUDA(cudaIpcGetMemHandle(&h.ipc, s->slab));
+  h.magic = FC_SMC_HANDLE_MAGIC; h.rank = s->rank; h.device = s->P->device; h.n_local = s->n; h.first = s->first; h.pid = (int64_t)getpid();
+  memcpy(handle, &h, sizeof(h));
+  return FC_OK;
+}
+int32_t fc_smc_connect(fc_smc_session* s, const void* handles) {
+  using namespace fc;
+  if (!s || !handles) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
+  const SmcHandle* H = (const SmcHandle*)handles;
+  int64_t acc = 0;
+  for (int r = 0; r < s->world; r++) {
+    if (H[r].magic != FC_SMC_HANDLE_MAGIC || H[r].rank != r) { set_error("handle %d is not rank %d's export", r, r); return FC_ERR_INVALID_ARGUMENT; }
+    if (H[r].first != acc) { set_error("shards are not contiguous in rank order (rank %d starts at %lld, expected %lld)", r, (long long)H[r].first, (long long)acc); return FC_ERR_INVALID_ARGUMENT; }
+    s->bounds[r] = acc;
+    s->peer_n[r] = H[r].n_local;
+    acc += H[r].n_local;
+    if (r == s->rank) continue;
+    if (H[r].pid == (int64_t)getpid()) { set_error("ranks of a sharded population must be separate processes (cudaIpc)"); return FC_ERR_UNSUPPORTED_OP; }
+    void* ptr = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&ptr, H[r].ipc, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { set_error("cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e)); return FC_ERR_NCCL; }
+    s->peer_slab[r] = (char*)ptr;
+    s->cm.box[r] = (MBox*)ptr;
+  }
+  s->bounds[s->world] = acc;
+  if (acc != s->n_total) { set_error("shards hold %lld particles, population is %lld", (long long)acc, (long long)s->n_total); return FC_ERR_INVALID_ARGUMENT; }
+  s->connected = true;
+  return FC_OK;
+}
+
+static int32_t smc_ready(fc_smc_session* s) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  if (!s->connected) { fc::set_error("sharded session: call fc_smc_connect first"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_CUDA(cudaSetDevice(s->P->device));
   return FC_OK;
 }
 
@@ -603,17 +1762,17 @@ int32_t fc_smc_create(fc_program* p, const fc_smc_config* cfg, uint64_t seed, si
 // "step" is the pure importance-sampling reweight (smc.rs:484-493).
 int32_t fc_smc_step(fc_smc_session* s, double* beta_out) {
   using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  FC_CUDA(cudaSetDevice(s->P->device));
+  FC_TRY(smc_ready(s));
   if (!s->finished) {
     if (s->cfg.rejuvenation_steps == 0) {
       cudaStream_t st = s->P->stream;
       unsigned nbk = (unsigned)cdiv(s->n, 256);
-      k_combine<<<nbk, 256, 0, st>>>(s->log_w.p, s->ll.p, 1.0, s->comb.p, s->n);
+      FC_TRY(smc_materialise_log_w(s));
+      k_combine<<<nbk, 256, 0, st>>>(s->log_w.p, 0.0, s->ll.p, 1.0, s->comb.p, s->n);
       FC_KERNEL_CHECK();
+      s->P->n_kernel_launches += 1;
       double le;
-      FC_TRY(dev_log_sum_exp(s->comb.p, s->n, s->scratch.p, &le, st));
-      s->P->n_kernel_launches += 5;
+      FC_TRY(global_lse(s, s->comb.p, &le));
       s->log_evidence = le;
       s->beta = 1.0;
       std::swap(s->log_w.p, s->comb.p); std::swap(s->log_w.n, s->comb.n);
@@ -628,37 +1787,39 @@ int32_t fc_smc_step(fc_smc_session* s, double* beta_out) {
   return FC_OK;
 }
 
-// final normalisation (smc.rs:565-575) and copy-out. Any pointer may be NULL.
+// final normalisation (smc.rs:565-575: log_sum_exp of log_w ALONE, over all ranks) and copy-out of this
+// rank's shard. Any pointer may be NULL.
 int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, double* h_weight, double* h_log_weight, double* log_evidence, uint64_t* n_temper_steps) {
   using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_TRY(smc_ready(s));
   fc_program* p = s->P;
   cudaStream_t st = p->stream;
-  int64_t n = s->n;
+  const int64_t n = s->n;
   unsigned nbk = (unsigned)cdiv(n, 256);
-  FC_TRY(smc_materialise_log_w(s));
+  Pop pop = s->pop(s->cur);
   if (h_weight || h_log_weight) {
-    double log_norm;
-    FC_TRY(dev_log_sum_exp(s->log_w.p, n, s->scratch.p, &log_norm, st));
-    if (std::isfinite(log_norm)) k_sub_exp<<<nbk, 256, 0, st>>>(s->log_w.p, log_norm, s->comb.p, s->w.p, n);
-    else { k_fill2<<<nbk, 256, 0, st>>>(s->comb.p, -std::log((double)n), n); k_fill2<<<nbk, 256, 0, st>>>(s->w.p, 1.0 / (double)n, n); }
+    FC_TRY(smc_materialise_log_w(s));
+    FC_TRY(global_lse(s, s->log_w.p, nullptr));
+    k_sub_exp<<<nbk, 256, 0, st>>>(s->log_w.p, s->scal.p, (double)s->n_total, s->comb.p, s->w.p, n);
     FC_KERNEL_CHECK();
-    p->n_kernel_launches += 5;
+    p->n_kernel_launches += 1;
     if (h_weight) FC_CUDA(cudaMemcpyAsync(h_weight, s->w.p, n * 8, cudaMemcpyDeviceToHost, st));
     if (h_log_weight) FC_CUDA(cudaMemcpyAsync(h_log_weight, s->comb.p, n * 8, cudaMemcpyDeviceToHost, st));
   }
-  if (h_values && p->d_cont) FC_CUDA(cudaMemcpyAsync(h_values, s->q.p, p->d_cont * n * 8, cudaMemcpyDeviceToHost, st));
-  if (h_dvalues && p->d_disc) FC_TRY(disc_to_host(p, s->qd.p, p->d_disc * n, h_dvalues));
+  if (h_values && p->d_cont) FC_CUDA(cudaMemcpyAsync(h_values, pop.q, p->d_cont * n * 8, cudaMemcpyDeviceToHost, st));
+  if (h_dvalues && p->d_disc) { FC_TRY(ensure_qd32(s)); FC_TRY(disc_to_host(p, s->qd32.p, p->d_disc * n, h_dvalues)); }
   if (log_evidence) *log_evidence = s->log_evidence;
   if (n_temper_steps) *n_temper_steps = s->steps;
   FC_CUDA(cudaStreamSynchronize(st));
-  return FC_OK;
+  return comm_check(s);
 }
 
 int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dvalues, double** d_log_w, double** d_loglik) {
-  if (d_values) *d_values = s->q.p;
-  if (d_dvalues) *d_dvalues = s->qd.p;
-  if (d_log_w) { FC_TRY(fc::smc_materialise_log_w(s)); *d_log_w = s->log_w.p; }
+  using namespace fc;
+  FC_TRY(smc_ready(s));
+  if (d_values) *d_values = s->pop(s->cur).q;
+  if (d_dvalues) { FC_TRY(ensure_qd32(s)); *d_dvalues = s->qd32.p; }
+  if (d_log_w) { FC_TRY(smc_materialise_log_w(s)); *d_log_w = s->log_w.p; }
   if (d_loglik) *d_loglik = s->ll.p;
   return FC_OK;
 }
@@ -668,313 +1829,140 @@ int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dv
 // smc_prior_particles' weighting (smc.rs:779-787, FG-03): log_weight = log-likelihood of the particle
 int32_t fc_smc_prior_weights(fc_smc_session* s) {
   using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  FC_CUDA(cudaSetDevice(s->P->device));
+  FC_TRY(smc_ready(s));
   FC_CUDA(cudaMemcpyAsync(s->log_w.p, s->ll.p, s->n * 8, cudaMemcpyDeviceToDevice, s->P->stream));
   s->log_w_uniform = false;
   return FC_OK;
 }
 
-// normalize_particles (smc.rs:719-754): weight = exp(log_weight - lse), uniform if every log_weight is
-// -inf; log_weight is left as it is. Returns ESS = 1 / sum w^2 (smc.rs:230-233) in *ess (may be NULL).
+// normalize_particles (smc.rs:719-754): weight = exp(log_weight - lse) with the lse over ALL ranks,
+// uniform if it is not finite; log_weight is left as it is. Returns ESS = 1 / sum w^2 (smc.rs:230-233)
+// in *ess (may be NULL).
 int32_t fc_smc_normalize(fc_smc_session* s, double* log_norm_out, double* ess) {
   using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  FC_TRY(smc_ready(s));
   fc_program* p = s->P;
-  FC_CUDA(cudaSetDevice(p->device));
   cudaStream_t st = p->stream;
   const int64_t n = s->n;
   unsigned nbk = (unsigned)cdiv(n, 256);
   FC_TRY(smc_materialise_log_w(s));
+  FC_TRY(global_lse(s, s->log_w.p, nullptr));
+  k_sub_exp<<<nbk, 256, 0, st>>>(s->log_w.p, s->scal.p, (double)s->n_total, nullptr, s->w.p, n);
+  if (ess) k_gsumsq<<<nb_blocks(n), NB_THREADS, 0, st>>>(s->w.p, n, s->part.p, s->counter.p, s->scal.p, s->cm);
+  FC_KERNEL_CHECK();
+  p->n_kernel_launches += ess ? 2 : 1;
+  double h[3];
+  FC_CUDA(cudaMemcpyAsync(h, s->scal.p, 24, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  FC_TRY(comm_check(s));
+  if (log_norm_out) *log_norm_out = h[0];
+  if (ess) *ess = h[2];
+  return FC_OK;
+}
+
+// one reweight of the tempering loop (smc.rs:507-531): log_w += (beta_new - beta) * loglik, normalised by
+// the global log-sum-exp, which is added to the evidence estimate; beta := beta_new
+int32_t fc_smc_reweight(fc_smc_session* s, double beta_new, double* log_norm_out) {
+  using namespace fc;
+  FC_TRY(smc_ready(s));
+  if (!(beta_new >= s->beta && beta_new <= 1.0)) { set_error("beta_new must be in [beta, 1], got %g (beta = %g)", beta_new, s->beta); return FC_ERR_INVALID_ARGUMENT; }
   double log_norm;
-  FC_TRY(dev_log_sum_exp(s->log_w.p, n, s->scratch.p, &log_norm, st));
-  if (std::isfinite(log_norm)) k_sub_exp<<<nbk, 256, 0, st>>>(s->log_w.p, log_norm, s->comb.p, s->w.p, n);
-  else k_fill2<<<nbk, 256, 0, st>>>(s->w.p, 1.0 / (double)n, n);
-  FC_KERNEL_CHECK();
-  p->n_kernel_launches += 5;
-  if (log_norm_out) *log_norm_out = log_norm;
-  if (ess) {
-    FC_TRY(dev_reduce(2, s->w.p, n, 0.0, s->scratch.p, s->scratch.p + RDB, st));
-    double ss;
-    FC_CUDA(cudaMemcpyAsync(&ss, s->scratch.p + RDB, 8, cudaMemcpyDeviceToHost, st));
-    FC_CUDA(cudaStreamSynchronize(st));
-    *ess = 1.0 / ss;
-  }
-  return FC_OK;
-}
-
-// resample_particles (smc.rs:326-349): indices by `method` from the normalised weights, ancestors
-// copied, weight = 1/n and log_weight = ln(1/n). h_uniforms (1 for systematic, n otherwise) may be
-// NULL: the session's Philox stream is used. h_idx (n entries) may be NULL.
-int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const double* h_uniforms, uint64_t* h_idx) {
-  using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  if (method < FC_RESAMPLE_MULTINOMIAL || method > FC_RESAMPLE_STRATIFIED) { set_error("bad resampling method %d", method); return FC_ERR_INVALID_ARGUMENT; }
-  fc_program* P = s->P;
-  FC_TRY(fc_smc_normalize(s, nullptr, nullptr));
-  cudaStream_t st = P->stream;
-  const int64_t n = s->n;
-  unsigned nbk = (unsigned)cdiv(n, 256);
-  int64_t nu = method == FC_RESAMPLE_SYSTEMATIC ? 1 : n;
-  FC_CUDA(s->us.reserve(nu + 1));
-  s->steps += 1;
-  if (h_uniforms) FC_CUDA(cudaMemcpyAsync(s->us.p, h_uniforms, nu * 8, cudaMemcpyHostToDevice, st));
-  else k_uniform_one<<<(unsigned)cdiv(cdiv(nu, 2), 256), 256, 0, st>>>(s->us.p, s->seed, 0x1000000000000000ULL | s->steps, nu);
-  FC_TRY(resample_dev(method, s->w.p, n, s->us.p, s->idx.p, *s->rw, st, &P->n_kernel_launches));
-  dim3 gg(nbk, 1);
-  if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_cont, 8), 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, s->q2.p, s->idx.p, P->d_cont, n); std::swap(s->q.p, s->q2.p); std::swap(s->q.n, s->q2.n); }
-  if (P->d_disc) { gg.y = (unsigned)std::min<int64_t>(cdiv(P->d_disc, 8), 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, s->qd2.p, s->idx.p, P->d_disc, n); std::swap(s->qd.p, s->qd2.p); std::swap(s->qd.n, s->qd2.n); }
-  gg.y = 1;
-  k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, s->lp3b.p, s->idx.p, 3, n);
-  std::swap(s->lp3.p, s->lp3b.p); std::swap(s->lp3.n, s->lp3b.n);
-  k_loglik<<<nbk, 256, 0, st>>>(s->lp3.p, s->ll.p, n);
-  FC_KERNEL_CHECK();
-  P->n_kernel_launches += 5;
-  s->log_w_uniform = true;
-  s->shard_prepass_ok = false;
-  if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, s->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  return FC_OK;
-}
-
-// rejuvenate_particles (smc.rs:698-713): `steps` pi_beta-invariant single-site MH moves per particle,
-// weights untouched (FG-13). n_accepted (may be NULL) = accepted moves summed over particles.
-int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t steps) {
-  using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  if (!(beta >= 0.0 && beta <= 1.0)) { set_error("beta must be in [0, 1], got %g", beta); return FC_ERR_INVALID_ARGUMENT; }
-  fc_program* P = s->P;
-  FC_CUDA(cudaSetDevice(P->device));
-  for (uint64_t r = 0; r < steps; r++) {
-    FC_TRY(s->eng.step(s->q.p, s->qd.p, s->lp3.p, s->total.p, s->n_accept.p, s->moves, beta, true, 0.44, 0.7));
-    FC_TRY(s->eng.shared_adapt(0.44, 0.7));
-    s->moves += 1;
-  }
-  k_loglik<<<(unsigned)cdiv(s->n, 256), 256, 0, P->stream>>>(s->lp3.p, s->ll.p, s->n);
-  FC_KERNEL_CHECK();
-  P->n_kernel_launches += 1;
-  s->shard_prepass_ok = false;
-  FC_CUDA(cudaStreamSynchronize(P->stream));
-  return FC_OK;
-}
-
-// ---- one shard of a multi-GPU tempered SMC. The per-rank device steps; the few
-// scalars between them travel through torch.distributed / NCCL in fugue_b200/dist.py. ----
-
-// this session holds particles [first, first + n) of a population of n_total: uniform weight 1/n_total
-int32_t fc_smc_shard_begin(fc_smc_session* s, uint64_t n_total) {
-  using namespace fc;
-  if (!s || n_total < (uint64_t)s->n) { set_error("bad shard arguments"); return FC_ERR_INVALID_ARGUMENT; }
-  s->n_global = (double)n_total;
-  return FC_OK;
-}
-
-// (max, sum exp(lv - max), sum exp(2 (lv - max))) of lv_i = log_w_i + d_beta * ll_i over this shard:
-// the three numbers ess_at(beta + d_beta) and the reweight log-sum-exp need (smc.rs:589-602,
-// 512-518); shards merge them exactly like the per-CTA partials of the single-GPU kernel.
-int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3) {
-  using namespace fc;
-  if (!s || !out3) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
-  FC_CUDA(cudaSetDevice(s->P->device));
-  cudaStream_t st = s->P->stream;
-  const int64_t n = s->n;
-  const double lwc = -std::log(s->n_global > 0.0 ? s->n_global : (double)n);
-  const double* lw = s->log_w_uniform ? nullptr : s->log_w.p;
-  const int nb = nb_blocks(n);
-  FC_CUDA(cudaMemsetAsync(&s->bis.p->counter, 0, sizeof(unsigned), st));
-  if (!lw) {
-    // uniform log_w (the state every next_beta search runs in): single-stream pass, the shift is
-    // lwc + d_beta * max(ll) from a pre-pass that is redone only when ll has changed
-    if (!s->shard_prepass_ok) {
-      Bisect hb;
-      std::memset(&hb, 0, sizeof(hb));
-      hb.n = s->n_global > 0.0 ? s->n_global : (double)n;
-      FC_CUDA(cudaMemcpyAsync(s->bis.p, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
-      k_nb_prepass<<<nb, NB_THREADS, 0, st>>>(s->ll.p, n, s->bis.p, (double*)s->tri.p);
-      FC_KERNEL_CHECK();
-      FC_CUDA(cudaMemcpyAsync(&hb, s->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
-      FC_CUDA(cudaStreamSynchronize(st));
-      s->shard_ll_bad = hb.bad != 0;
-      s->shard_prepass_ok = true;
-      s->P->n_kernel_launches += 1;
-    }
-    if (s->shard_ll_bad) {  // some ll is NaN / +inf: every log-sum-exp is non-finite (smc.rs:595-601)
-      out3[0] = out3[1] = out3[2] = __builtin_nan("");
-      return FC_OK;
-    }
-    k_nb_eval_uni<<<nb, NB_THREADS, 0, st>>>(lwc, s->ll.p, s->bis.p, s->tri.p, n, 1, 0, d_beta);
-  } else {
-    k_nb_eval<<<nb, NB_THREADS, 0, st>>>(lw, lwc, s->ll.p, s->bis.p, s->tri.p, n, 1, 0, d_beta);
-  }
-  FC_KERNEL_CHECK();
-  s->P->n_kernel_launches += 1;
-  Tri t;
-  FC_CUDA(cudaMemcpyAsync(&t, s->tri.p + nb, sizeof(Tri), cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  out3[0] = t.m; out3[1] = t.s1; out3[2] = t.s2;
-  return FC_OK;
-}
-
-// the same for up to 8 increments at once (uniform log_w only: the state every next_beta search runs
-// in): out[3k..3k+3) = (max, sum e, sum e^2) of candidate k. Returns FC_ERR_UNSUPPORTED_OP if log_w is
-// not uniform (the caller falls back to fc_smc_shard_tri).
-int32_t fc_smc_shard_tri_multi(fc_smc_session* s, const double* d_betas, int32_t K, double* out) {
-  using namespace fc;
-  if (!s || !d_betas || !out || K < 1 || K > NB_MULTI_MAX) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
-  if (!s->log_w_uniform) { set_error("log weights are not uniform"); return FC_ERR_UNSUPPORTED_OP; }
-  FC_CUDA(cudaSetDevice(s->P->device));
-  cudaStream_t st = s->P->stream;
-  const int64_t n = s->n;
-  const double lwc = -std::log(s->n_global > 0.0 ? s->n_global : (double)n);
-  const int nb = nb_blocks(n);
-  if (!s->shard_prepass_ok) {  // max(ll) and the bad flag: fc_smc_shard_tri's pre-pass
-    double tmp[3];
-    FC_TRY(fc_smc_shard_tri(s, 0.0, tmp));
-  }
-  if (s->shard_ll_bad) {
-    for (int k = 0; k < 3 * K; k++) out[k] = __builtin_nan("");
-    return FC_OK;
-  }
-  MultiArgs A;
-  A.K = K;
-  for (int k = 0; k < NB_MULTI_MAX; k++) A.d[k] = k < K ? d_betas[k] : 0.0;
-  FC_CUDA(s->scratch.reserve((int64_t)RDB * 2 * NB_MULTI_MAX + 16));
-  k_nb_multi<<<nb, NB_THREADS, 0, st>>>(lwc, s->ll.p, s->bis.p, n, A, s->scratch.p);
-  FC_KERNEL_CHECK();
-  s->P->n_kernel_launches += 1;
-  std::vector<double> h((size_t)nb * 2 * NB_MULTI_MAX);
-  Bisect hb;
-  FC_CUDA(cudaMemcpyAsync(h.data(), s->scratch.p, h.size() * 8, cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaMemcpyAsync(&hb, s->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  for (int k = 0; k < K; k++) {
-    double a = 0.0, b = 0.0;
-    for (int blk = 0; blk < nb; blk++) { a += h[(size_t)blk * 2 * NB_MULTI_MAX + 2 * k]; b += h[(size_t)blk * 2 * NB_MULTI_MAX + 2 * k + 1]; }
-    out[3 * k] = std::fma(d_betas[k], hb.max_ll, lwc);
-    out[3 * k + 1] = a;
-    out[3 * k + 2] = b;
-  }
-  return FC_OK;
-}
-
-// reweight with the GLOBAL normaliser (smc.rs:512-531): log_w = (log_w + d_beta ll) - log_norm,
-// w = exp(log_w); advances beta / evidence / step count of the shard.
-int32_t fc_smc_shard_reweight(fc_smc_session* s, double beta_new, double log_norm) {
-  using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  FC_CUDA(cudaSetDevice(s->P->device));
-  cudaStream_t st = s->P->stream;
-  const int64_t n = s->n;
-  const double n_unif = s->n_global > 0.0 ? s->n_global : (double)n;
-  const double lwc = -std::log(n_unif);
-  const double* lw = s->log_w_uniform ? nullptr : s->log_w.p;
-  const double d_beta = beta_new - s->beta;
-  FC_CUDA(cudaMemcpyAsync(&s->bis.p->lse1, &log_norm, 8, cudaMemcpyHostToDevice, st));
-  FC_CUDA(cudaStreamSynchronize(st));
-  k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(lw, lwc, s->ll.p, d_beta, s->bis.p, s->comb.p, s->w.p, n, n_unif);
-  FC_KERNEL_CHECK();
-  s->P->n_kernel_launches += 1;
-  std::swap(s->log_w.p, s->comb.p); std::swap(s->log_w.n, s->comb.n);
-  s->log_w_uniform = false;
+  FC_TRY(smc_reweight(s, beta_new - s->beta, true, &log_norm));
   s->log_evidence += log_norm;
   s->beta = beta_new;
   s->steps += 1;
-  if (s->beta >= 1.0) s->finished = true;
+  if (log_norm_out) *log_norm_out = log_norm;
   return FC_OK;
 }
 
-// exact running sum of this shard's weights from the carry-in of the ranks before it
-int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value) {
+// this rank's log weights as they are and the normalised weights the resampler would see; either may be NULL
+int32_t fc_smc_weights(fc_smc_session* s, double* h_log_w, double* h_w) {
   using namespace fc;
-  if (!s || !end_value) { set_error("NULL argument"); return FC_ERR_INVALID_ARGUMENT; }
-  FC_CUDA(cudaSetDevice(s->P->device));
-  return shard_scan(s->w.p, s->n, carry_in, *s->rw, s->P->stream, &s->P->n_kernel_launches, end_value);
-}
-
-// the offspring of global output slots [jlo, jhi) (ancestors on this shard, after fc_smc_shard_scan),
-// packed plane-major for migration: d_f64 [(d_cont + 3)][cnt] (values, then the three accumulators),
-// d_i32 [d_disc][cnt]. With d_f64 == d_i32 == NULL the offspring stay on this rank and are written
-// straight to local positions [local_offset, local_offset + cnt) of the new population.
-// h_idx (cnt local ancestor indices) may be NULL.
-int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo, uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx, uint64_t local_offset) {
-  using namespace fc;
-  if (!s || jhi < jlo) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
-  fc_program* P = s->P;
-  FC_CUDA(cudaSetDevice(P->device));
-  cudaStream_t st = P->stream;
-  const int64_t n = s->n, cnt = (int64_t)(jhi - jlo);
-  if (cnt == 0) return FC_OK;
-  if (cnt > n) FC_CUDA(s->idx.reserve(cnt));
-  FC_TRY(shard_ancestors(*s->rw, n, (double)n_total, u_raw, (int64_t)jlo, cnt, s->idx.p, st));
-  dim3 gg((unsigned)cdiv(cnt, 256), 1);
-  if (!d_f64 && !d_i32) {
-    // offspring that stay on this rank: straight into the double buffers at their final position
-    // (global slot jlo is local position jlo - first slot of this rank = local_offset)
-    const int64_t off = (int64_t)local_offset;
-    if (off < 0 || off + cnt > n) { set_error("local offspring out of range"); return FC_ERR_INVALID_ARGUMENT; }
-    if (P->d_cont) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, s->q2.p + off, s->idx.p, P->d_cont, n, cnt, n); }
-    gg.y = 3; k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, s->lp3b.p + off, s->idx.p, 3, n, cnt, n);
-    if (P->d_disc) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, s->qd2.p + off, s->idx.p, P->d_disc, n, cnt, n); }
-  } else {
-    if (P->d_cont && d_f64) { gg.y = (unsigned)std::min<int64_t>(P->d_cont, 64); k_gather<double><<<gg, 256, 0, st>>>(s->q.p, d_f64, s->idx.p, P->d_cont, n, cnt, cnt); }
-    if (d_f64) { gg.y = 3; k_gather<double><<<gg, 256, 0, st>>>(s->lp3.p, d_f64 + P->d_cont * cnt, s->idx.p, 3, n, cnt, cnt); }
-    if (P->d_disc && d_i32) { gg.y = (unsigned)std::min<int64_t>(P->d_disc, 64); k_gather<disc_t><<<gg, 256, 0, st>>>(s->qd.p, d_i32, s->idx.p, P->d_disc, n, cnt, cnt); }
+  FC_TRY(smc_ready(s));
+  cudaStream_t st = s->P->stream;
+  FC_TRY(smc_materialise_log_w(s));
+  if (h_log_w) FC_CUDA(cudaMemcpyAsync(h_log_w, s->log_w.p, s->n * 8, cudaMemcpyDeviceToHost, st));
+  if (h_w) {
+    FC_TRY(fc_smc_normalize(s, nullptr, nullptr));
+    FC_CUDA(cudaMemcpyAsync(h_w, s->w.p, s->n * 8, cudaMemcpyDeviceToHost, st));
   }
-  FC_KERNEL_CHECK();
-  P->n_kernel_launches += 4;
-  if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, s->idx.p, cnt * 8, cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;
 }
 
-// install `cnt` migrated particles (one source rank's chunk, packed as fc_smc_shard_offspring packs
-// them) at local positions [offset, offset + cnt). After the last chunk call fc_smc_shard_resampled.
-int32_t fc_smc_shard_install(fc_smc_session* s, uint64_t offset, uint64_t cnt, const double* d_f64, const int32_t* d_i32) {
+// resample_particles (smc.rs:326-349): indices by `method` from the (globally) normalised weights,
+// ancestors copied -- across ranks when sharded --, weight = 1/n and log_weight = ln(1/n).
+// h_uniforms (1 raw value for systematic, n otherwise) may be NULL: the session's Philox stream is used.
+// h_idx (n entries, single-rank sessions only) may be NULL.
+int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const double* h_uniforms, uint64_t* h_idx) {
   using namespace fc;
-  if (!s || offset + cnt > (uint64_t)s->n) { set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
-  fc_program* P = s->P;
-  FC_CUDA(cudaSetDevice(P->device));
-  cudaStream_t st = P->stream;
-  const int64_t n = s->n;
-  if (cnt == 0) return FC_OK;
-  // the new population is assembled in the double buffers and swapped in by fc_smc_shard_resampled
-  if (P->d_cont) FC_CUDA(cudaMemcpy2DAsync(s->q2.p + offset, n * 8, d_f64, cnt * 8, cnt * 8, P->d_cont, cudaMemcpyDeviceToDevice, st));
-  FC_CUDA(cudaMemcpy2DAsync(s->lp3b.p + offset, n * 8, d_f64 + P->d_cont * cnt, cnt * 8, cnt * 8, 3, cudaMemcpyDeviceToDevice, st));
-  if (P->d_disc) FC_CUDA(cudaMemcpy2DAsync(s->qd2.p + offset, n * 4, d_i32, cnt * 4, cnt * 4, P->d_disc, cudaMemcpyDeviceToDevice, st));
-  return FC_OK;
+  FC_TRY(smc_ready(s));
+  if (h_idx && s->world > 1) { set_error("ancestor indices are reported for single-rank sessions only"); return FC_ERR_UNSUPPORTED_OP; }
+  FC_TRY(fc_smc_normalize(s, nullptr, nullptr));
+  s->steps += 1;
+  FC_TRY(smc_resample(s, method, h_uniforms, h_idx));
+  FC_CUDA(cudaStreamSynchronize(s->P->stream));
+  return comm_check(s);
 }
 
-// this shard's log weights as they are (normalised by the GLOBAL log-sum-exp after a reweight) and
-// the weights exp(log_w) the resampler sees (valid after fc_smc_shard_reweight) -> host; either may be NULL
-int32_t fc_smc_shard_weights(fc_smc_session* s, double* h_log_w, double* h_w) {
+// rejuvenate_particles (smc.rs:698-713): `steps` pi_beta-invariant single-site MH moves per particle,
+// weights untouched (FG-13).
+int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t steps) {
   using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  FC_CUDA(cudaSetDevice(s->P->device));
-  if (h_log_w) {
-    FC_TRY(smc_materialise_log_w(s));
-    FC_CUDA(cudaMemcpyAsync(h_log_w, s->log_w.p, s->n * 8, cudaMemcpyDeviceToHost, s->P->stream));
-  }
-  if (h_w) FC_CUDA(cudaMemcpyAsync(h_w, s->w.p, s->n * 8, cudaMemcpyDeviceToHost, s->P->stream));
+  FC_TRY(smc_ready(s));
+  if (!(beta >= 0.0 && beta <= 1.0)) { set_error("beta must be in [0, 1], got %g", beta); return FC_ERR_INVALID_ARGUMENT; }
+  FC_TRY(smc_rejuvenate(s, beta, steps));
   FC_CUDA(cudaStreamSynchronize(s->P->stream));
   return FC_OK;
 }
 
-// the migrated population replaces the old one; weights are uniform 1/n_total again (smc.rs:538-541)
-int32_t fc_smc_shard_resampled(fc_smc_session* s) {
-  using namespace fc;
-  if (!s) { set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
-  fc_program* P = s->P;
-  FC_CUDA(cudaSetDevice(P->device));
-  cudaStream_t st = P->stream;
-  std::swap(s->q.p, s->q2.p); std::swap(s->q.n, s->q2.n);
-  std::swap(s->qd.p, s->qd2.p); std::swap(s->qd.n, s->qd2.n);
-  std::swap(s->lp3.p, s->lp3b.p); std::swap(s->lp3.n, s->lp3b.n);
-  k_loglik<<<(unsigned)cdiv(s->n, 256), 256, 0, st>>>(s->lp3.p, s->ll.p, s->n);
-  FC_KERNEL_CHECK();
-  P->n_kernel_launches += 1;
-  s->log_w_uniform = true;
-  s->shard_prepass_ok = false;
-  FC_CUDA(cudaStreamSynchronize(st));
+// parity hooks: record the GLOBAL ancestor of every output slot this rank produces in a resample, and
+// read them back: slots [jlo, jhi) (rank-major concatenation over ranks = the whole ancestor array)
+int32_t fc_smc_record_offspring(fc_smc_session* s, int32_t enable) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  s->record = enable != 0;
+  return FC_OK;
+}
+int32_t fc_smc_last_offspring(fc_smc_session* s, uint64_t* jlo, uint64_t* jhi, uint64_t* h_idx) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  if (jlo) *jlo = (uint64_t)s->last_jlo;
+  if (jhi) *jhi = (uint64_t)s->last_jhi;
+  if (h_idx && s->last_jhi > s->last_jlo) {
+    if (!s->record) { fc::set_error("fc_smc_record_offspring was not enabled"); return FC_ERR_INVALID_ARGUMENT; }
+    FC_CUDA(cudaSetDevice(s->P->device));
+    FC_CUDA(cudaMemcpy(h_idx, s->idx.p, (size_t)(s->last_jhi - s->last_jlo) * 8, cudaMemcpyDeviceToHost));
+  }
+  return FC_OK;
+}
+
+// Host arithmetic of the sharded resample's slot routing (no device work): the output slots [jlo, jhi) whose
+// ancestor lives on a rank whose exact running sum goes from carry_in to end -- the walk of smc.rs:263-268
+// stops inside that rank iff carry_in < threshold_j <= end; the last rank also takes the slots whose
+// threshold is never reached. `tag` selects the stratified uniform stream (ignored for systematic).
+int32_t fc_smc_slot_range(int32_t method, uint64_t n_total, double u_raw, uint64_t seed, uint64_t tag, double carry_in, double end, int32_t is_last, uint64_t* jlo, uint64_t* jhi) {
+  if (!jlo || !jhi || (method != FC_RESAMPLE_SYSTEMATIC && method != FC_RESAMPLE_STRATIFIED)) { fc::set_error("bad arguments"); return FC_ERR_INVALID_ARGUMENT; }
+  const int64_t a = fc::count_thresholds_le(method, (int64_t)n_total, u_raw, seed, tag, carry_in);
+  int64_t b = is_last ? (int64_t)n_total : fc::count_thresholds_le(method, (int64_t)n_total, u_raw, seed, tag, end);
+  if (b < a) b = a;
+  *jlo = (uint64_t)a; *jhi = (uint64_t)b;
+  return FC_OK;
+}
+
+// debug switches for A/B parity tests: "nb_plain" (1: next_beta evaluates every bisection midpoint, as the
+// reference does), "smc_generic" (1: sessions created afterwards use the generic scoring engine)
+int32_t fc_debug_set(const char* key, int32_t value) {
+  if (key && !strcmp(key, "nb_plain")) { fc::g_nb_plain = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "smc_generic")) { fc::g_smc_generic = value ? 1 : 0; return FC_OK; }
+  fc::set_error("unknown debug key");
+  return FC_ERR_INVALID_ARGUMENT;
+}
+
+// counters of a session: particles this rank sent to other ranks, ESS evaluations of all next_beta searches
+int32_t fc_smc_counters(const fc_smc_session* s, uint64_t* migrated, uint64_t* ess_evals, int32_t* fused) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  if (migrated) *migrated = s->migrated;
+  if (ess_evals) *ess_evals = s->ess_evals;
+  if (fused) *fused = s->fused ? 1 : 0;
   return FC_OK;
 }
 

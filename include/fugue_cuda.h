@@ -305,34 +305,47 @@ int32_t fc_smc_normalize(fc_smc_session* s, double* log_norm, double* ess);
 int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const double* h_uniforms,
                                   uint64_t* h_idx);
 int32_t fc_smc_rejuvenate_particles(fc_smc_session* s, double beta, uint64_t steps);
-/* One shard of a multi-GPU tempered SMC (particles sharded rank-major). The exchange
- * steps -- the global weight log-sum-exp, the exact rank-to-rank running-sum carry and the particle
- * migration of a global systematic resample (smc.rs:255-272, 499-560) -- are collectives in
- * fugue_b200/dist.py; these are the per-rank device steps between them:
- *   shard_begin      this session holds n of n_total particles (uniform weight 1/n_total)
- *   shard_tri        out3 = (max, sum e, sum e^2) of lv = log_w + d_beta*ll, e = exp(lv - max)
- *   shard_reweight   log_w = lv - log_norm (the GLOBAL normaliser), w = exp(log_w); beta := beta_new
- *   shard_scan       exact sequentially-rounded running sum of w continuing from carry_in
- *   shard_offspring  ancestors of global slots [jlo, jhi) (thresholds u/N + j/N) packed plane-major:
- *                    d_f64 [(d_cont+3)][cnt] (values + the three accumulators), d_i32 [d_disc][cnt];
- *                    both NULL = the offspring stay here: written in place at local_offset
- *   shard_install    place one source rank's chunk at local positions [offset, offset+cnt)
- *   shard_resampled  swap the migrated population in; weights uniform again
- *   shard_weights    the shard's log weights as they are (normalised by the GLOBAL log-sum-exp)
- *                    and the weights exp(log_w) the resampler sees; either pointer may be NULL */
-int32_t fc_smc_shard_begin(fc_smc_session* s, uint64_t n_total);
-int32_t fc_smc_shard_tri(fc_smc_session* s, double d_beta, double* out3);
-/* up to 8 increments in one pass (uniform log_w only; else FC_ERR_UNSUPPORTED_OP): out[3k..3k+3) */
-int32_t fc_smc_shard_tri_multi(fc_smc_session* s, const double* d_betas, int32_t K, double* out);
-int32_t fc_smc_shard_reweight(fc_smc_session* s, double beta_new, double log_norm);
-int32_t fc_smc_shard_scan(fc_smc_session* s, double carry_in, double* end_value);
-int32_t fc_smc_shard_offspring(fc_smc_session* s, uint64_t n_total, double u_raw, uint64_t jlo,
-                               uint64_t jhi, double* d_f64, int32_t* d_i32, uint64_t* h_idx,
-                               uint64_t local_offset);
-int32_t fc_smc_shard_install(fc_smc_session* s, uint64_t offset, uint64_t cnt, const double* d_f64,
-                             const int32_t* d_i32);
-int32_t fc_smc_shard_resampled(fc_smc_session* s);
-int32_t fc_smc_shard_weights(fc_smc_session* s, double* h_log_w, double* h_w);
+/* one reweight of the tempering loop (smc.rs:507-531): log_w += (beta_new - beta) * loglik, normalised by
+ * the log-sum-exp over the WHOLE population (all ranks), which is added to the evidence estimate and
+ * returned in *log_norm (may be NULL); beta := beta_new */
+int32_t fc_smc_reweight(fc_smc_session* s, double beta_new, double* log_norm);
+/* this rank's log weights as they are, and the globally normalised weights exp(log_w - lse) the resampler
+ * sees; either pointer may be NULL */
+int32_t fc_smc_weights(fc_smc_session* s, double* h_log_w, double* h_w);
+/* particles this rank sent to other ranks in global resamples; ESS evaluations spent by all next_beta
+ * searches; whether the program runs on the fused per-particle kernels. Any pointer may be NULL. */
+int32_t fc_smc_counters(const fc_smc_session* s, uint64_t* migrated, uint64_t* ess_evals, int32_t* fused);
+
+/* ---- sharded SMC: the population of n_total particles is split rank-major over `world`
+ * processes, one per GPU of a box. The exchange steps of the tempering loop -- the global weight
+ * log-sum-exp / ESS of every next_beta probe and of the reweight (smc.rs:512-524, 588-602), the exact
+ * rank-to-rank carry of the sequentially rounded running sum and the particle migration of a global
+ * systematic / stratified resample (smc.rs:255-292, 534-541) -- run ON THE DEVICE over peer memory:
+ * every rank exports one cudaIpc slab (mailbox + population buffers), the last CTA of a weight pass
+ * stores the rank's sums into every peer's mailbox and folds all ranks' sums in rank order, and the
+ * resampling gather writes offspring straight into the destination rank's buffers over NVLink.
+ *   create_sharded  rank `rank` holds particles [first_particle, first_particle + n) of n_total
+ *   export          this rank's 128-byte slab descriptor; all-gather them in rank order (any host channel)
+ *   connect         map the peers' slabs; then fc_smc_step / fc_smc_get / the standalone pieces above work
+ *                   on the global population (every rank must make the same sequence of calls)
+ * Multinomial resampling is not available sharded (FC_ERR_UNSUPPORTED_OP): its ancestors are not monotone
+ * in the slot index. A peer that does not answer within 20 s gives FC_ERR_NCCL. */
+#define FC_SMC_HANDLE_BYTES 128
+int32_t fc_smc_create_sharded(fc_program* p, const fc_smc_config* cfg, uint64_t seed, size_t n, uint64_t first_particle,
+                              uint64_t n_total, int32_t rank, int32_t world, fc_smc_session** out);
+int32_t fc_smc_export(fc_smc_session* s, void* handle);
+int32_t fc_smc_connect(fc_smc_session* s, const void* handles);
+/* host arithmetic of the slot routing (no device work): the output slots [jlo, jhi) whose ancestor lives on
+ * a rank whose exact running sum runs from carry_in to end (smc.rs:263-268: the walk stops there iff
+ * carry_in < u/N + j/N <= end; the last rank also takes the slots whose threshold is never reached) */
+int32_t fc_smc_slot_range(int32_t method, uint64_t n_total, double u_raw, uint64_t seed, uint64_t tag, double carry_in,
+                          double end, int32_t is_last, uint64_t* jlo, uint64_t* jhi);
+/* parity hooks: record the GLOBAL ancestor index of every output slot this rank produces in a resample
+ * (the slots whose ancestor it holds), and read the last resample's back: slots [jlo, jhi), h_idx of
+ * jhi - jlo entries (may be NULL). Concatenated over ranks in rank order they are the whole index array
+ * the reference's systematic_indices / stratified_indices return. */
+int32_t fc_smc_record_offspring(fc_smc_session* s, int32_t enable);
+int32_t fc_smc_last_offspring(fc_smc_session* s, uint64_t* jlo, uint64_t* jhi, uint64_t* h_idx);
 /* next_beta (smc.rs:588-622) on host arrays: the largest beta' in (beta, 1] whose incremental
  * weights log_w + (beta' - beta) * ll keep ESS >= target_ess (64-step bisection; 1.0 if a full
  * jump already does). Parity probe for the tempering ladder. */
@@ -366,6 +379,10 @@ int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, doub
 int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean,
                          double* h_seg_ss, double* h_cmean, double* h_lagsum);
 
+/* switches for A/B parity tests: "nb_plain" = 1: next_beta evaluates every midpoint of the reference's
+ * 64-step bisection (no search phase); "smc_generic" = 1: SMC sessions created afterwards run on the
+ * generic scoring engine instead of the fused per-particle kernels */
+int32_t fc_debug_set(const char* key, int32_t value);
 /* accuracy probe of the kernels' branch-free FP64 primitives: op 0 exp, 1 log, 2 reciprocal */
 int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out);
 

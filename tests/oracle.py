@@ -209,3 +209,35 @@ def dim_adapt(accepts, target=0.44, gamma=0.7):
     out = np.zeros(a.size)
     lib().fo_dim_adapt(a.ctypes.data_as(C.POINTER(C.c_uint8)), a.size, target, gamma, _d(out))
     return out
+
+
+def philox_uniforms(seed, stream, tag, n):
+    """The n uniforms of the device's Philox4x32-10 stream (fc_common.cuh): key from (seed, stream) by
+    splitmix64, block i = counter (i, tag) gives uniforms 2i and 2i+1 (53 bits each). Test helper for
+    resamplers that draw their own uniforms (stratified thresholds of an SMC session)."""
+    M64 = (1 << 64) - 1
+    z = (seed + 0x9E3779B97F4A7C15 * (stream + 1)) & M64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M64
+    z ^= z >> 31
+    m = (n + 1) // 2
+    i = np.arange(m, dtype=np.uint64)
+    c0 = (i & np.uint64(0xFFFFFFFF)).astype(np.uint64)
+    c1 = (i >> np.uint64(32)).astype(np.uint64)
+    c2 = np.full(m, tag & 0xFFFFFFFF, dtype=np.uint64)
+    c3 = np.full(m, (tag >> 32) & 0xFFFFFFFF, dtype=np.uint64)
+    a, b = z & 0xFFFFFFFF, (z >> 32) & 0xFFFFFFFF
+    mask = np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        m0 = np.uint64(0xD2511F53) * c0
+        m1 = np.uint64(0xCD9E8D57) * c2
+        hi0, lo0, hi1, lo1 = m0 >> np.uint64(32), m0 & mask, m1 >> np.uint64(32), m1 & mask
+        n0, n1, n2, n3 = hi1 ^ c1 ^ np.uint64(a), lo1, hi0 ^ c3 ^ np.uint64(b), lo0
+        c0, c1, c2, c3 = n0, n1, n2, n3
+        a, b = (a + 0x9E3779B9) & 0xFFFFFFFF, (b + 0xBB67AE85) & 0xFFFFFFFF
+    x = (c0 << np.uint64(32)) | c1
+    y = (c2 << np.uint64(32)) | c3
+    u = np.empty(2 * m)
+    u[0::2] = (x >> np.uint64(11)).astype(np.float64) * 2.0 ** -53
+    u[1::2] = (y >> np.uint64(11)).astype(np.float64) * 2.0 ** -53
+    return u[:n]

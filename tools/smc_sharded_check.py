@@ -1,9 +1,10 @@
-"""Multi-GPU run of the sharded tempered SMC (fugue_b200/dist.py) over NCCL, one rank per GPU:
-  torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/smc_sharded_check.py [particles]
-(1) parity: one reweight + global systematic resample on the C4 mixture model; the ranks' ancestors
-    are gathered on rank 0 and compared, bit for bit, with the single-GPU resampler run on the
-    gathered weights (itself bit-exact vs the sequential loop: tests/test_gpu_smc.py);
-(2) throughput: adaptive_smc_sharded at BASELINE configs[3] (2^24 particles over all ranks,
+"""Multi-GPU run of the sharded tempered SMC (in-library peer-memory exchange), one rank per GPU:
+  torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/smc_sharded_check.py [particles] [parity_particles]
+(1) parity: one reweight + global systematic resample on the C4 mixture model; every rank records the
+    global ancestors of the slots it produced, rank 0 gathers them and the weights and compares the
+    whole index array, bit for bit, with the single-GPU resampler run on the gathered weights (itself
+    bit-exact vs the sequential loop: tests/test_gpu_smc.py); migrated state == state[ancestors];
+(2) throughput: adaptive_smc at BASELINE configs[3] (2^24 particles over all ranks,
     rejuvenation_steps=1), particle-updates/s with the time taken as the max over ranks.
 Rank 0 prints one JSON line."""
 import json, os, sys, time
@@ -18,74 +19,73 @@ from fugue_b200 import api, models, dist as D
 
 api.set_device(lr)
 n_total = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 24
+n_par = int(sys.argv[2]) if len(sys.argv) > 2 else n_total
 m = models.gaussian_mixture()[0]
-out = {"world_size": ws, "particles": n_total, "backend": "nccl" if ws > 1 else "single"}
-
-# ---- (1) parity of the global resample ----
-n_par = min(n_total, 1 << 20) + 1  # ragged shards on purpose
-sm = D.ShardedSmc(m, n_par, api.SMCConfig(ess_threshold=0.5, rejuvenation_steps=1), seed=3)
-lse1, _ = D._lse_pair(sm._tri(0.02))
-api.check(api.lib.fc_smc_shard_reweight(sm.S.h, 0.02, lse1))
-sm.beta = 0.02
-w = np.zeros(sm.n)
-api.check(api.lib.fc_smc_shard_weights(sm.S.h, None, api._ptr(w)))
-vb = sm.result().values.copy()
-zb = sm.result().dvalues.copy()
-(jlo, jhi), idx = sm.resample_global(u_raw=0.61, return_idx=True)
-ra = sm.result()
+out = {"world_size": ws, "particles": n_total, "exchange": "device peer memory (cudaIpc windows)" if ws > 1 else "single"}
 
 
-def gather_rows(a):  # rank-major concatenation along the last axis, on every rank
+def gather_cols(a, dtype=np.float64):
+    """rank-major concatenation along the last axis, on every rank (host channel; test harness only)"""
     a = np.ascontiguousarray(a, dtype=np.float64)
     if ws == 1:
-        return a
+        return a.astype(dtype)
     sizes = [int(x[0]) for x in D.all_gather_np(np.array([float(a.shape[-1])]))]
     mx = max(sizes)
     pad = np.zeros(a.shape[:-1] + (mx,))
     pad[..., :a.shape[-1]] = a
     parts = D.all_gather_np(pad)
-    return np.concatenate([p[..., :s] for p, s in zip(parts, sizes)], axis=-1)
+    return np.concatenate([p[..., :s] for p, s in zip(parts, sizes)], axis=-1).astype(dtype)
 
 
-W = gather_rows(w)
-G = gather_rows((idx.astype(np.int64) + sm.lo).astype(np.float64)).astype(np.int64)
-Vb, Va = gather_rows(vb), gather_rows(ra.values)
-Zb, Za = gather_rows(zb.astype(np.float64)), gather_rows(ra.dvalues.astype(np.float64))
+# ---- (1) parity of the global resample on n_par particles (ragged shards when n_par is odd) ----
+sm = D.ShardedSmc(m, n_par, api.SMCConfig(ess_threshold=0.5, rejuvenation_steps=1), seed=3)
+sm.S.record_offspring(True)
+sm.S.reweight(0.02)
+w = sm.S.weights()[1]
+rb = sm.S.result()
+vb, zb = rb.values.copy(), rb.dvalues.copy()
+sm.S.resample_particles(1, [0.61])
+jlo, jhi, idx = sm.S.last_offspring()
+ra = sm.S.result()
+W = gather_cols(w)
+G = gather_cols(idx.astype(np.float64), np.int64)
+Vb, Va = gather_cols(vb), gather_cols(ra.values)
+Zb, Za = gather_cols(zb.astype(np.float64), np.int64), gather_cols(ra.dvalues.astype(np.float64), np.int64)
+mig = D.all_reduce_np(np.array([float(sm.S.counters()["migrated"])]))[0]
 if rank == 0:
     ref = api.resample_indices(1, W, [0.61]).astype(np.int64)
-    out["resample_bit_exact"] = bool(np.array_equal(G, ref))
+    out["resample_bit_exact"] = bool(G.shape == ref.shape and np.array_equal(G, ref))
     out["migration_exact"] = bool(np.array_equal(Va, Vb[:, ref]) and np.array_equal(Za, Zb[:, ref]))
     out["parity_particles"] = int(n_par)
-mig = D.all_reduce_np(np.array([float(sm.migrated)]))[0]
-out["parity_migrated"] = int(mig)
+    out["parity_migrated"] = int(mig)
 sm.close()
+del W, G, Vb, Va, Zb, Za
 
-# ---- (2) throughput at C4 ----
-cfg = api.SMCConfig(ess_threshold=0.5, rejuvenation_steps=1)
-D.adaptive_smc_sharded(m, min(n_total, 1 << 18), cfg, seed=5, values=False)  # warm-up (module load, NCCL channels)
-torch.cuda.synchronize()
-if ws > 1:
-    dist.barrier()
-t0 = time.perf_counter()
-big = D.ShardedSmc(m, n_total, cfg, seed=7)  # prior draw + first scoring of the shard
-torch.cuda.synchronize()
-t1 = time.perf_counter()
-while big.step() < 1.0:
-    pass
-torch.cuda.synchronize()
-dt = time.perf_counter() - t1
-init_s = t1 - t0
-res = big.result(values=False)
-phase = dict(big.timers)
-res.migrated = big.migrated
-big.close()
-dt = D.all_reduce_np(np.array([dt]), op="max")[0]
-mig = D.all_reduce_np(np.array([float(res.migrated)]))[0]
-wsum = D.all_reduce_np(np.array([res.weight.sum()]))[0]
+# ---- (2) throughput ----
+for rep in range(2):  # first pass warms up allocations / peer mappings
+    sm = D.ShardedSmc(m, n_total, api.SMCConfig(ess_threshold=0.5, rejuvenation_steps=1), seed=5 + rep)
+    torch.cuda.synchronize()
+    if ws > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    steps = 0
+    while sm.step() < 1.0:
+        steps += 1
+    steps += 1
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    if ws > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dt = float(tt.item())
+    r = sm.result(values=False)
+    c = sm.S.counters()
+    if rank == 0:
+        out.update(temper_steps=steps, seconds=dt, particle_updates_per_s=n_total * steps / dt, log_evidence=r.log_evidence,
+                   ess_evals=c["ess_evals"], fused=c["fused"], migrated_rank0=c["migrated"])
+    sm.close()
 if rank == 0:
-    out.update(seconds=dt, init_seconds=init_s, phase_seconds=phase, temper_steps=int(res.n_temper_steps), particle_updates_per_s=n_total * res.n_temper_steps / dt,
-               log_evidence=res.log_evidence, migrated_particles=int(mig), weight_sum=wsum)
-    print(json.dumps(out))
+    print(json.dumps(out), flush=True)
 if ws > 1:
     dist.barrier()
     dist.destroy_process_group()
