@@ -464,6 +464,7 @@ _sig("fc_smc_record_offspring", vp, C.c_int32)
 _sig("fc_smc_last_offspring", vp, u64p, u64p, vp)
 _sig("fc_smc_slot_range", C.c_int32, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, C.c_double, C.c_double, C.c_int32, u64p, u64p)
 _sig("fc_debug_set", C.c_char_p, C.c_int32)
+_sig("fc_smc_phase_ms", vp, vp, vp)
 FC_SMC_HANDLE_BYTES = 128
 
 
@@ -605,6 +606,12 @@ class SmcSession:
         m, e, f = C.c_uint64(), C.c_uint64(), C.c_int32()
         check(lib.fc_smc_counters(self.h, C.byref(m), C.byref(e), C.byref(f)))
         return dict(migrated=m.value, ess_evals=e.value, fused=bool(f.value))
+
+    def phase_ms(self):
+        """CUDA-event ms per phase of the tempering steps (needs debug_set("smc_timing", 1))."""
+        ms, n = np.zeros(5), np.zeros(5, dtype=np.uint64)
+        check(lib.fc_smc_phase_ms(self.h, _ptr(ms), _ptr(n)))
+        return dict(zip(("next_beta", "reweight", "scan", "gather", "move"), ms.tolist())), n.tolist()
 
     def rejuvenate_particles(self, beta, rejuvenation_steps):
         """rejuvenate_particles (smc.rs:698-713): weights are left unchanged."""

@@ -28,16 +28,24 @@ __device__ __forceinline__ double d_digamma(double x) {
   return r + log(x) - 0.5 / x + t;
 }
 
-// lgc: optional normaliser of constant parameters evaluated at lowering (DOp::lgc; NaN => compute here).
+// lgc, lgc2: optional functions of CONSTANT parameters evaluated once at lowering (DOp::lgc / lgc2; NaN =>
+// compute here): Normal ln sigma; Gamma lgamma(k), ln rate; Beta ln B(a, b).
 template <bool GRAD>
-__device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1, double lgc);
+__device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1, double lgc, double lgc2);
 template <bool GRAD>
 __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1) {
-  return dist_eval<GRAD>(dist, P0, P1, P2, x, xi, lgam_kp1, __longlong_as_double(0x7ff8000000000000LL));
+  const double qn = __longlong_as_double(0x7ff8000000000000LL);
+  return dist_eval<GRAD>(dist, P0, P1, P2, x, xi, lgam_kp1, qn, qn);
 }
-// lgam_kp1: optional precomputed lgamma(k+1) for count-valued data (NaN => compute here).
 template <bool GRAD>
 __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1, double lgc) {
+  return dist_eval<GRAD>(dist, P0, P1, P2, x, xi, lgam_kp1, lgc, __longlong_as_double(0x7ff8000000000000LL));
+}
+// lgam_kp1: optional precomputed lgamma(k+1) for count-valued data (NaN => compute here).
+// A term whose coefficient is exactly zero ((k - 1) ln x at k = 1, ...) is not evaluated in value-only
+// mode: 0 * ln x is +-0 for every x the guards let through, so the sum is unchanged.
+template <bool GRAD>
+__device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, double P2, double x, long long xi, double lgam_kp1, double lgc, double lgc2) {
   DistOut g;
   g.lp = d_neg_inf();
   g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
@@ -45,7 +53,7 @@ __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, dou
     case FC_NORMAL: {  // distribution.rs:189-208
       if (P1 <= 0.0 || !d_fin(P1) || !d_fin(P0) || !d_fin(x)) break;
       double z = (x - P0) / P1;
-      g.lp = -0.5 * z * z - log(P1) - 0.5 * FC_LN_2PI;
+      g.lp = -0.5 * z * z - (isnan(lgc) ? log(P1) : lgc) - 0.5 * FC_LN_2PI;
       if (GRAD && d_fin(g.lp)) {
         g.dp0 = z / P1;
         g.dx = -g.dp0;
@@ -114,7 +122,7 @@ __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, dou
         g.lp = P1 > 1.0 ? d_neg_inf() : (P1 < 1.0 ? d_pos_inf() : -log_beta_fn);
         break;
       }
-      double ln_x = log(x), ln_1mx = log(1.0 - x);
+      const double ln_x = (GRAD || P0 != 1.0) ? log(x) : 0.0, ln_1mx = (GRAD || P1 != 1.0) ? log(1.0 - x) : 0.0;
       g.lp = (P0 - 1.0) * ln_x + (P1 - 1.0) * ln_1mx - log_beta_fn;
       if (GRAD && d_fin(g.lp)) {
         double pab = d_digamma(P0 + P1);
@@ -126,7 +134,7 @@ __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, dou
     case FC_GAMMA: {  // distribution.rs:1039-1068 (shape, rate)
       if (P0 <= 0.0 || P1 <= 0.0 || !d_fin(P0) || !d_fin(P1) || !d_fin(x)) break;
       if (x <= 0.0) break;
-      double log_rate = log(P1), log_x = log(x);
+      const double log_rate = isnan(lgc2) ? log(P1) : lgc2, log_x = (GRAD || P0 != 1.0) ? log(x) : 0.0;
       g.lp = P0 * log_rate + (P0 - 1.0) * log_x - P1 * x - (isnan(lgc) ? lgamma(P0) : lgc);
       if (GRAD && d_fin(g.lp)) {
         g.dx = (P0 - 1.0) / x - P1;

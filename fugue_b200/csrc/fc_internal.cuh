@@ -42,7 +42,7 @@ struct DOp {
   double value;
   const double* lgam;  // optional precomputed lgamma(value+1) per element (count data)
   int32_t expr_first, expr_len;  // FACTOR_EXPR: nodes in the program's expression table
-  double lgc;  // normaliser of constant parameters, evaluated once at lowering (NaN: evaluate per call): Gamma lgamma(k), Beta ln B(a, b)
+  double lgc, lgc2;  // functions of constant parameters, evaluated once at lowering (NaN: evaluate per call): Normal ln sigma; Gamma lgamma(k), ln rate; Beta ln B(a, b)
   const double* probs;  // K-way Categorical with constant probabilities (distribution.rs:679-713): device table, else null
   int32_t n_probs, _pad2;
   DParam p[3];

@@ -53,7 +53,7 @@ __device__ __forceinline__ DistOut op_dist_eval(const DOp& op, double P0, double
     g.lp = pr > 0.0 ? log(pr) : d_neg_inf();
     return g;
   }
-  return dist_eval<GRAD>(op.dist, P0, P1, P2, x, xi, lgam_kp1, op.lgc);
+  return dist_eval<GRAD>(op.dist, P0, P1, P2, x, xi, lgam_kp1, op.lgc, op.lgc2);
 }
 
 #define PL_TX 32

@@ -354,6 +354,7 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
     // normalisers of constant parameters (lgamma is ~200 FP64 instructions per call on the device;
     // C4 scores Beta(1,1) and two Gamma(1,1) priors for 2^24 particles per temper step)
     d.lgc = std::nan("");
+    d.lgc2 = std::nan("");
     {
       auto const_param = [&](int j, double& v) -> bool {
         if (j >= d.n_params || d.p[j].link != FC_LINK_IDENTITY) return false;
@@ -370,6 +371,8 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
       };
       double a, b;
       if (d.dist == FC_GAMMA && const_param(0, a)) d.lgc = std::lgamma(a);
+      if (d.dist == FC_GAMMA && const_param(1, b)) d.lgc2 = std::log(b);
+      if (d.dist == FC_NORMAL && const_param(1, b)) d.lgc = std::log(b);
       if (d.dist == FC_BETA && const_param(0, a) && const_param(1, b)) d.lgc = std::lgamma(a) + std::lgamma(b) - std::lgamma(a + b);
     }
     P->all_ops.push_back(d);

@@ -111,14 +111,16 @@ __device__ __forceinline__ Inc2 combine(const Inc2& a, const Inc2& b) {
 }
 // base = bottom of the binade (0 for the subnormal/first-normal region), U = its ulp,
 // lim = weights >= lim certainly leave the binade.
-__device__ __forceinline__ Inc2 make_inc(double w, double base, double U, double lim) {
+// iu1 * iu2 = 1 / U as two powers of two (1 / U itself overflows for the smallest binades): the quotient
+// by the ulp is an exact scaling, not a division (two FP64 divisions per weight made the scan FP64-bound)
+__device__ __forceinline__ Inc2 make_inc(double w, double base, double U, double lim, double iu1, double iu2) {
   Inc2 r;
   if (!(w < lim)) { r.e = r.o = SAT_INC; return r; }
   double b1 = base + U;
   double te = __dadd_rn(__dadd_rn(base, w), -base);
   double to = __dadd_rn(__dadd_rn(b1, w), -b1);
-  r.e = (long long)(te / U);
-  r.o = (long long)(to / U);
+  r.e = (long long)__dmul_rn(__dmul_rn(te, iu1), iu2);
+  r.o = (long long)__dmul_rn(__dmul_rn(to, iu1), iu2);
   return r;
 }
 
@@ -163,19 +165,23 @@ __device__ __forceinline__ Inc2 block_exclusive_scan(Inc2 v, Inc2* total) {
 //   k_scan_round_a  per-tile aggregates of the window; the last CTA to finish scans them
 //   k_scan_round_b  per-element prefix sums -> S, first crossing; the last CTA does the one floating
 //                   add that changes binade and sets up the next window
-struct Binade { double base, U, lim, T; long long need; int parity; };
+struct Binade { double base, U, lim, T, iu1, iu2; long long need; int parity; };
 __device__ __forceinline__ Binade binade_of(double s0) {
   Binade b;
   const double two_m1021 = ldexp(1.0, -1021);
-  if (s0 < two_m1021) { b.base = 0.0; b.U = ldexp(1.0, -1074); b.T = two_m1021; }
+  int ue;  // U = 2^ue
+  if (s0 < two_m1021) { b.base = 0.0; ue = -1074; b.T = two_m1021; }
   else {
     int e;
     frexp(s0, &e);  // s0 = m * 2^e, m in [0.5, 1)
-    b.base = ldexp(1.0, e - 1); b.U = ldexp(1.0, e - 1 - 52); b.T = ldexp(1.0, e);
+    b.base = ldexp(1.0, e - 1); ue = e - 1 - 52; b.T = ldexp(1.0, e);
   }
+  b.U = ldexp(1.0, ue);
+  if (ue >= -1000) { b.iu1 = ldexp(1.0, -ue); b.iu2 = 1.0; }
+  else { b.iu1 = ldexp(1.0, 600); b.iu2 = ldexp(1.0, -ue - 600); }
   b.lim = (b.base == 0.0) ? b.T : b.base;
-  b.need = (long long)((b.T - s0) / b.U);  // exact: both multiples of U, quotient <= 2^53
-  b.parity = (int)(((long long)((s0 - b.base) / b.U)) & 1LL);
+  b.need = (long long)__dmul_rn(__dmul_rn(b.T - s0, b.iu1), b.iu2);  // exact: both multiples of U, quotient <= 2^53
+  b.parity = (int)(((long long)__dmul_rn(__dmul_rn(s0 - b.base, b.iu1), b.iu2)) & 1LL);
   return b;
 }
 #define SC_GRID_MAX 1184  // 8 CTAs per SM on 148 SMs
@@ -204,7 +210,7 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_round_a(const double* __res
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
       const int64_t j = t0 + i;
-      if (j < len) a = combine(a, make_inc(w[k0 + j], B.base, B.U, B.lim));
+      if (j < len) a = combine(a, make_inc(w[k0 + j], B.base, B.U, B.lim, B.iu1, B.iu2));
     }
     Inc2 total;
     block_exclusive_scan(a, &total);
@@ -262,7 +268,7 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_round_b(const double* __res
     for (int i = 0; i < SC_ITEMS; i++) {
       const int64_t j = t0 + i;
       items[i].e = 0; items[i].o = 0;
-      if (j < len) items[i] = make_inc(w[k0 + j], B.base, B.U, B.lim);
+      if (j < len) items[i] = make_inc(w[k0 + j], B.base, B.U, B.lim, B.iu1, B.iu2);
       a = combine(a, items[i]);
     }
     Inc2 pre = block_exclusive_scan(a, nullptr);

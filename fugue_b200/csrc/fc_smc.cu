@@ -5,12 +5,14 @@
 // tempered_single_site_mh (:631-688), resample + clone (:326-349, 534-541), normalize_particles
 // (:719-753) and smc_prior_particles (:764-790).
 //
-// Population container. Continuous sites and the three Trace accumulators are SoA, particle-minor
-// (q [d_cont][n], lp3 [3][n]); discrete sites are one packed record per particle (z [n][zp] bytes,
-// one byte per site when every discrete support fits, else four), because a particle's discrete
-// sites only ever move together (resampling) and are only ever read together (plates). The cached
-// accumulators travel with the particle, so a rejuvenation move scores the proposal only (the
-// reference re-scores the current state as well: 2 model runs per move, smc.rs:659-676).
+// Population container. One contiguous RECORD per particle: its f64 sites (sorted address order), the
+// three Trace accumulators, then its discrete sites in program order (one byte per site when every
+// discrete support fits, else four), padded to 16 bytes -- a particle is cloned as a whole by
+// resampling (smc.rs:326-349) and read as a whole by a rejuvenation move, so both are streams of
+// 16-byte vector accesses over consecutive records (C4: 144 B per particle). Only the log-likelihood
+// lives in a dense array of its own (the tempering passes stream over it). The cached accumulators
+// travel with the particle, so a move scores the proposal only (the reference re-scores the current
+// state as well: 2 model runs per move, smc.rs:659-676).
 //
 // Kernels. For programs made of scalar ops plus two-valued discrete plates and Normal observation
 // plates (BASELINE configs[3], examples/mixture_models.rs:77-111) the three per-particle steps are
@@ -696,10 +698,18 @@ __global__ void k_chain_collect(const __grid_constant__ Comm cm, unsigned long l
 // the population container and the fused per-particle kernels
 // =============================================================================================
 struct Pop {
-  double* q;     // [d_cont][n]
-  double* lp3;   // [3][n]: log_prior, log_likelihood, log_factors (trace.rs:168-177)
-  uint8_t* z;    // [n][zp]: discrete sites in PROGRAM slot order, zw bytes each
-  int64_t n;     // row stride of q / lp3 = particles in this buffer set
+  uint8_t* rec;   // [n][pitch]: { q[d_cont] | lp3[3] | pad | z[d_disc * zw] | pad }
+  double* ll;     // [n] log-likelihood + log-factors of the particle (particle_log_likelihood, smc.rs:381-383)
+  int64_t n;
+};
+struct RecLayout {
+  int64_t pitch;    // bytes per record (multiple of 16)
+  int64_t zoff;     // byte offset of the discrete sites (multiple of 16)
+  int64_t d_cont, d_disc;
+  int32_t zw, _pad;
+  __host__ __device__ __forceinline__ double* q(uint8_t* r) const { return (double*)r; }
+  __host__ __device__ __forceinline__ double* lp3(uint8_t* r) const { return (double*)r + d_cont; }
+  __host__ __device__ __forceinline__ uint8_t* z(uint8_t* r) const { return r + zoff; }
 };
 struct ZAcc {  // discrete value of a program slot for one particle
   const uint8_t* rec;
@@ -722,92 +732,100 @@ struct FusedProg {
   const FPlate* plates;
   const int32_t* crow;
   const fc_expr_node* nodes;
-  int32_t n_ops, n_scalar, n_plates, zw;
-  int64_t zp, d_cont;
+  int32_t n_ops, n_scalar, n_plates, _pad;
+  RecLayout L;
 };
 
-__device__ __forceinline__ double chain_const_param(const DOp& op, int j, const double* __restrict__ q, int64_t C, int64_t c, bool apply) {
+// In the fused kernels a particle's f64 sites are the first d_cont doubles of its record, so the scoring
+// helpers written for the [row][chain] layout are called with (q = record, C = 1, c = 0).
+__device__ __forceinline__ double chain_const_param(const DOp& op, int j, const double* __restrict__ q, bool apply) {
   double s = 0.0;
   for (int t = 0; t < 3; t++) {
     const DTerm& tm = op.p[j].t[t];
     if (tm.kind == FC_TERM_CONST) s += tm.c;
-    else if (tm.kind == FC_TERM_LATENT) s += tm.c * q[(int64_t)tm.row * C + c];
+    else if (tm.kind == FC_TERM_LATENT) s += tm.c * q[tm.row];
   }
   if (apply && op.p[j].invariant) { double dl; s = apply_link(op.p[j].link, s, op.p[j].lo, op.p[j].hi, dl); }
   return s;
 }
 struct NormalSetup {  // per-particle constants of a Normal observation plate (same arithmetic as k_plate_vec)
-  double base0, va0, vb0, va1, inv_a, lg_a, inv_b, lg_b;
+  double base0, va0, vb0, va1, inv_a, inv_b, c_a, c_b;  // c = -ln sigma - 0.5 ln 2 pi of the branch
 };
-__device__ __forceinline__ NormalSetup normal_setup(const DOp& op, const FPlate& fp, const double* __restrict__ q, int64_t C, int64_t c) {
+__device__ __forceinline__ NormalSetup normal_setup(const DOp& op, const FPlate& fp, const double* __restrict__ q) {
   NormalSetup S;
-  S.base0 = chain_const_param(op, 0, q, C, c, true);
-  const double base1 = chain_const_param(op, 1, q, C, c, true);
+  S.base0 = chain_const_param(op, 0, q, true);
+  const double base1 = chain_const_param(op, 1, q, true);
   S.va0 = S.vb0 = S.va1 = 0.0;
-  if (fp.m0) { const DTerm& T0 = op.p[0].t[fp.mt0]; S.va0 = q[(int64_t)T0.row * C + c]; if (fp.m0 == FM_SELECT2) S.vb0 = q[(int64_t)T0.row_b * C + c]; }
-  if (fp.m1) { const DTerm& T1 = op.p[0].t[fp.mt1]; S.va1 = q[(int64_t)T1.row * C + c]; }
+  if (fp.m0) { const DTerm& T0 = op.p[0].t[fp.mt0]; S.va0 = q[T0.row]; if (fp.m0 == FM_SELECT2) S.vb0 = q[T0.row_b]; }
+  if (fp.m1) { const DTerm& T1 = op.p[0].t[fp.mt1]; S.va1 = q[T1.row]; }
   double sa = base1, sb = base1;
-  if (fp.ss) { const DTerm& TS = op.p[1].t[fp.st]; sa = base1 + q[(int64_t)TS.row * C + c]; sb = base1 + q[(int64_t)TS.row_b * C + c]; }
-  // an invalid sigma scores -inf through inv = 0, log = +inf (distribution.rs:189-208 guards)
+  if (fp.ss) { const DTerm& TS = op.p[1].t[fp.st]; sa = base1 + q[TS.row]; sb = base1 + q[TS.row_b]; }
+  // an invalid sigma scores -inf through inv = 0, ln = +inf (distribution.rs:189-208 guards)
   const bool oka = sa > 0.0 && d_fin(sa), okb = sb > 0.0 && d_fin(sb);
-  S.inv_a = oka ? 1.0 / sa : 0.0; S.lg_a = oka ? log(sa) : d_pos_inf();
-  S.inv_b = okb ? 1.0 / sb : 0.0; S.lg_b = okb ? log(sb) : d_pos_inf();
+  S.inv_a = oka ? 1.0 / sa : 0.0; S.c_a = oka ? -log(sa) - 0.5 * FC_LN_2PI : d_neg_inf();
+  S.inv_b = okb ? 1.0 / sb : 0.0; S.c_b = okb ? -log(sb) - 0.5 * FC_LN_2PI : d_neg_inf();
   return S;
 }
+// one Normal observation: -0.5 z^2 - ln sigma - 0.5 ln 2 pi. A NaN (0 * inf from an invalid sigma, or a
+// non-finite value / mean) is the reference's -inf; the caller maps a NaN SUM to -inf once, which is the
+// same thing because a Normal log-density is never +inf.
 __device__ __forceinline__ double normal_elem(const NormalSetup& S, const FPlate& fp, int zm, int zs, double lx0, double lx1, double x) {
   double mean = S.base0;
   if (fp.m0 == FM_SELECT2) mean += zm ? S.vb0 : S.va0;
   if (fp.m0 == FM_LATENT_X) mean += S.va0 * lx0;
   if (fp.m1 == FM_LATENT_X) mean += S.va1 * lx1;
   const bool useb = fp.ss && zs;
-  const double inv = useb ? S.inv_b : S.inv_a, lg = useb ? S.lg_b : S.lg_a;
-  const double z = (x - mean) * inv;
-  double e = -0.5 * z * z - lg - 0.5 * FC_LN_2PI;
-  if (!(e == e)) e = d_neg_inf();  // non-finite mean / value: the reference's guards return -inf
-  return e;
+  const double z = (x - mean) * (useb ? S.inv_b : S.inv_a);
+  return fma(-0.5 * z, z, useb ? S.c_b : S.c_a);
 }
 
-// log_prior / log_likelihood / log_factors of particle c: scalar ops, then every plate, in program
+// log_prior / log_likelihood / log_factors of one particle: scalar ops, then every plate, in program
 // order; elements of a plate summed in order with one accumulator (the generic kernels' order).
-__device__ __forceinline__ void fused_eval(const FusedProg& F, const double* __restrict__ q, int64_t C, int64_t c, const uint8_t* __restrict__ zrec, double (&lp)[3]) {
+__device__ __forceinline__ void fused_eval(const FusedProg& F, const uint8_t* __restrict__ rec, double (&lp)[3]) {
+  const double* __restrict__ q = (const double*)rec;
+  const uint8_t* __restrict__ zrec = rec + F.L.zoff;
   double a_prior = 0.0, a_lik = 0.0, a_fac = 0.0;
-  ZAcc za{zrec, F.zw};
-  if (F.n_scalar) scalar_ops_eval<false>(F.scalar_ops, F.n_scalar, F.crow, q, C, c, za, nullptr, F.nodes, a_prior, a_lik, a_fac);
+  ZAcc za{zrec, F.L.zw};
+  if (F.n_scalar) scalar_ops_eval<false>(F.scalar_ops, F.n_scalar, F.crow, q, 1, 0, za, nullptr, F.nodes, a_prior, a_lik, a_fac);
   lp[0] = 0.0 + a_prior; lp[1] = 0.0 + a_lik; lp[2] = 0.0 + a_fac;
   const double qnan = __longlong_as_double(0x7ff8000000000000LL);
   for (int pi = 0; pi < F.n_plates; pi++) {
     const FPlate fp = F.plates[pi];
     const DOp& op = F.ops[fp.op];
     if (fp.kind == FP_TWOVAL_SAMPLE || fp.kind == FP_TWOVAL_OBS || fp.kind == FP_MIX) {
-      const double p0 = chain_const_param(op, 0, q, C, c, true);
+      const double p0 = chain_const_param(op, 0, q, true);
       const double tv0 = dist_eval<false>(op.dist, p0, 0.0, 0.0, 0.0, 0, qnan).lp;
       const double tv1 = dist_eval<false>(op.dist, p0, 0.0, 0.0, 0.0, 1, qnan).lp;
       const bool bern = op.dist == FC_BERNOULLI;
+      const double tv2 = bern ? tv1 : d_neg_inf();  // values >= 2: true for a bool, out of range for [p, 1-p] (distribution.rs:785-791)
       double s = 0.0;
       if (fp.kind == FP_TWOVAL_OBS) {
         for (int i = 0; i < fp.n; i++) {
           const long long xi = dcol_i64(op.value_col, i);
-          s += xi == 0 ? tv0 : ((xi == 1 || bern) ? tv1 : d_neg_inf());
+          s += xi == 0 ? tv0 : (xi == 1 ? tv1 : tv2);
         }
         lp[1] += s;
       } else if (fp.kind == FP_TWOVAL_SAMPLE) {
         const int z0 = (int)op.dslot0;
         for (int i = 0; i < fp.n; i++) {
           const long long xi = za(z0 + i);
-          s += xi == 0 ? tv0 : ((xi == 1 || bern) ? tv1 : d_neg_inf());
+          s += xi == 0 ? tv0 : (xi == 1 ? tv1 : tv2);
         }
         lp[0] += s;
       } else {
         // FP_MIX: z#i ~ two-valued(p); x#i ~ Normal(mean[z_i], sigma[z_i]) (examples/mixture_models.rs:96-108):
-        // one pass over the particle's z record serves the discrete prior and the observation plate
+        // one pass over the particle's z bytes serves the discrete prior and the observation plate
         const DOp& ob = F.ops[fp.op_b];
-        const NormalSetup S = normal_setup(ob, fp, q, C, c);
+        const NormalSetup S = normal_setup(ob, fp, q);
         const int z0 = (int)op.dslot0;
         const double* __restrict__ xs = (const double*)ob.value_col.ptr;
         const bool x_f64 = ob.value_col.dtype == FC_COL_F64;
         const double* __restrict__ lxc = fp.m1 == FM_LATENT_X ? (const double*)ob.p[0].t[fp.mt1].col.ptr : nullptr;
         double sl = 0.0;
-        if (F.zw == 1 && (z0 & 15) == 0 && (F.zp & 15) == 0) {
+        if (F.L.zw == 1 && (z0 & 15) == 0 && x_f64 && !lxc) {
+          // the hot loop of BASELINE configs[3]: per element 2 byte ops, the branch selects and 6 FP64 instructions
+          const double ma = S.base0 + S.va0, mb = S.base0 + S.vb0;
+          const double ia = S.inv_a, ib = fp.ss ? S.inv_b : S.inv_a, ca = S.c_a, cb = fp.ss ? S.c_b : S.c_a;
           for (int i0 = 0; i0 < fp.n; i0 += 16) {
             const uint4 v = *(const uint4*)(zrec + z0 + i0);
             const unsigned wv[4] = {v.x, v.y, v.z, v.w};
@@ -815,26 +833,27 @@ __device__ __forceinline__ void fused_eval(const FusedProg& F, const double* __r
             for (int b = 0; b < 16; b++) {
               const int i = i0 + b;
               if (i < fp.n) {
-                const int zi = (int)((wv[b >> 2] >> ((b & 3) * 8)) & 0xffu);
-                s += zi == 0 ? tv0 : ((zi == 1 || bern) ? tv1 : d_neg_inf());
-                const double x = x_f64 ? __ldg(xs + i) : dcol_f64(ob.value_col, i);
-                sl += normal_elem(S, fp, zi != 0, zi != 0, 0.0, lxc ? __ldg(lxc + i) : 0.0, x);
+                const unsigned zi = (wv[b >> 2] >> ((b & 3) * 8)) & 0xffu;
+                const bool one = zi != 0;
+                s += zi == 0 ? tv0 : (zi == 1 ? tv1 : tv2);
+                const double z = (__ldg(xs + i) - (one ? mb : ma)) * (one ? ib : ia);
+                sl += fma(-0.5 * z, z, one ? cb : ca);
               }
             }
           }
         } else {
           for (int i = 0; i < fp.n; i++) {
             const int zi = (int)za(z0 + i);
-            s += zi == 0 ? tv0 : ((zi == 1 || bern) ? tv1 : d_neg_inf());
+            s += zi == 0 ? tv0 : (zi == 1 ? tv1 : tv2);
             const double x = x_f64 ? __ldg(xs + i) : dcol_f64(ob.value_col, i);
             sl += normal_elem(S, fp, zi != 0, zi != 0, 0.0, lxc ? __ldg(lxc + i) : 0.0, x);
           }
         }
         lp[0] += s;
-        lp[1] += sl;
+        lp[1] += (sl == sl) ? sl : d_neg_inf();
       }
     } else {  // FP_NORMAL_OBS
-      const NormalSetup S = normal_setup(op, fp, q, C, c);
+      const NormalSetup S = normal_setup(op, fp, q);
       const int zm0 = fp.m0 == FM_SELECT2 ? op.p[0].t[fp.mt0].dslot : 0;
       const int zs0 = fp.ss ? op.p[1].t[fp.st].dslot : 0;
       const double* __restrict__ lx0c = fp.m0 == FM_LATENT_X ? (const double*)op.p[0].t[fp.mt0].col.ptr : nullptr;
@@ -845,48 +864,62 @@ __device__ __forceinline__ void fused_eval(const FusedProg& F, const double* __r
         const int zs = fp.ss ? (za(zs0 + i) != 0) : 0;
         sl += normal_elem(S, fp, zm, zs, lx0c ? __ldg(lx0c + i) : 0.0, lx1c ? __ldg(lx1c + i) : 0.0, dcol_f64(op.value_col, i));
       }
-      lp[1] += sl;
+      lp[1] += (sl == sl) ? sl : d_neg_inf();
     }
   }
 }
 
 // ---- prior draw of every sample site (PriorHandler, interpreters.rs:88-104,355-372) in program order; the
-// same Philox stream and draw order as the generic k_prior_sample, so both paths give the same population ----
-__global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ FusedProg F, Pop pop, int64_t n, uint64_t seed, uint64_t stream0, uint64_t tag) {
+// same Philox stream and draw order as the generic k_prior_sample, so both paths give the same population.
+// Scored in the same kernel: the record is still in registers / L1. ----
+__global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ FusedProg F, Pop pop, uint64_t seed, uint64_t stream0, uint64_t tag) {
   const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= n) return;
+  if (c >= pop.n) return;
   DevRng rng(seed, stream0 + (uint64_t)c, tag);
-  uint8_t* zrec = pop.z + c * F.zp;
+  uint8_t* rec = pop.rec + c * F.L.pitch;
+  double* q = (double*)rec;
+  uint8_t* zrec = rec + F.L.zoff;
   for (int oi = 0; oi < F.n_ops; oi++) {
     const DOp& op = F.ops[oi];
     if (!op.is_sample) continue;
     if (op.kind == FC_OP_SAMPLE) {
       double pv[3] = {0.0, 0.0, 0.0};
-      for (int j = 0; j < op.n_params; j++) pv[j] = eval_param_value(op, j, 0, pop.q, nullptr, c, n, F.crow, nullptr);  // scalar ops: CONST / LATENT terms only
+      for (int j = 0; j < op.n_params; j++) pv[j] = eval_param_value(op, j, 0, q, nullptr, 0, 1, F.crow, nullptr);  // scalar ops: CONST / LATENT terms only
       double x;
       long long xi;
       op_dist_sample(rng, op, pv[0], pv[1], pv[2], x, xi);
-      if (op.cont) pop.q[(int64_t)F.crow[op.cslot0] * n + c] = x;
-      else if (F.zw == 1) zrec[op.dslot0] = (uint8_t)xi;
+      if (op.cont) q[F.crow[op.cslot0]] = x;
+      else if (F.L.zw == 1) zrec[op.dslot0] = (uint8_t)xi;
       else ((int32_t*)zrec)[op.dslot0] = (int32_t)xi;
     } else {  // two-valued discrete plate with a chain-constant parameter
-      const double p0 = chain_const_param(op, 0, pop.q, n, c, true);
+      const double p0 = chain_const_param(op, 0, q, true);
       const bool bern = op.dist == FC_BERNOULLI;
-      const int z0 = (int)op.dslot0;
-      for (int i = 0; i < (int)op.plate_len; i++) {
-        const bool lt = rng.uniform() < p0;
-        zrec[z0 + i] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));  // dist_sample: Bernoulli u < p; Categorical [p, 1-p] CDF search
+      const int z0 = (int)op.dslot0, n = (int)op.plate_len;
+      if ((z0 & 15) == 0) {  // 16 sites per store (byte stores from 32 lanes would be 32 partial-sector writes each)
+        for (int i0 = 0; i0 < n; i0 += 16) {
+          unsigned wv[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+          for (int b = 0; b < 16; b++)
+            if (i0 + b < n) {
+              const bool lt = rng.uniform() < p0;
+              const unsigned zi = bern ? (lt ? 1u : 0u) : (lt ? 0u : 1u);  // dist_sample: Bernoulli u < p; Categorical [p, 1-p] CDF search
+              wv[b >> 2] |= zi << ((b & 3) * 8);
+            }
+          *(uint4*)(zrec + z0 + i0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);  // the record's z section is padded to 16 bytes
+        }
+      } else {
+        for (int i = 0; i < n; i++) {
+          const bool lt = rng.uniform() < p0;
+          zrec[z0 + i] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));
+        }
       }
     }
   }
-}
-__global__ void __launch_bounds__(128) k_smcx_score(const __grid_constant__ FusedProg F, Pop pop, int64_t n, double* __restrict__ ll) {
-  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= n) return;
   double lp[3];
-  fused_eval(F, pop.q, n, c, pop.z + c * F.zp, lp);
-  pop.lp3[c] = lp[0]; pop.lp3[n + c] = lp[1]; pop.lp3[2 * n + c] = lp[2];
-  ll[c] = lp[1] + lp[2];
+  fused_eval(F, rec, lp);
+  double* l3 = q + F.L.d_cont;
+  l3[0] = lp[0]; l3[1] = lp[1]; l3[2] = lp[2];
+  pop.ll[c] = lp[1] + lp[2];
 }
 
 // ---- one tempered single-site MH move per particle (tempered_single_site_mh, smc.rs:631-688): uniform
@@ -900,9 +933,10 @@ struct MoveX {
   double beta;
   int32_t adapt;
 };
-__global__ void __launch_bounds__(128) k_smcx_move(const __grid_constant__ FusedProg F, Pop pop, int64_t n, double* __restrict__ ll, const __grid_constant__ MoveX M) {
+__global__ void __launch_bounds__(128) k_smcx_move(const __grid_constant__ FusedProg F, Pop pop, const __grid_constant__ MoveX M) {
   const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool active = c < n && F.d_cont > 0;
+  const int64_t dc = F.L.d_cont;
+  const bool active = c < pop.n && dc > 0;
   int s = -1;
   bool accept = false;
   if (active) {
@@ -910,44 +944,47 @@ __global__ void __launch_bounds__(128) k_smcx_move(const __grid_constant__ Fused
     double u_site, u_acc, z0, z1;
     ph.uniform2(0, M.step_tag, u_site, u_acc);
     ph.normal2(1, M.step_tag, z0, z1);  // Normal::new(0,1).sample (smc.rs:656)
-    int64_t si = (int64_t)(u_site * (double)F.d_cont);
-    if (si >= F.d_cont) si = F.d_cont - 1;
+    int64_t si = (int64_t)(u_site * (double)dc);
+    if (si >= dc) si = dc - 1;
     s = (int)si;
-    double* qs = pop.q + si * n + c;
-    const double cur = *qs;
-    *qs = cur + M.scale[s] * z0;
+    uint8_t* rec = pop.rec + c * F.L.pitch;
+    double* q = (double*)rec;
+    double* l3 = q + dc;
+    const double cur = q[si];
+    q[si] = cur + M.scale[s] * z0;
     double lpn[3];
-    fused_eval(F, pop.q, n, c, pop.z + c * F.zp, lpn);
-    const double c0 = pop.lp3[c], c1 = pop.lp3[n + c], c2 = pop.lp3[2 * n + c];
+    fused_eval(F, rec, lpn);
+    const double c0 = l3[0], c1 = l3[1], c2 = l3[2];
     const double log_alpha = (lpn[0] - c0) + M.beta * ((lpn[1] + lpn[2]) - (c1 + c2));  // smc.rs:679-680
     accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);
     if (accept) {
-      pop.lp3[c] = lpn[0]; pop.lp3[n + c] = lpn[1]; pop.lp3[2 * n + c] = lpn[2];
-      ll[c] = lpn[1] + lpn[2];
+      l3[0] = lpn[0]; l3[1] = lpn[1]; l3[2] = lpn[2];
+      pop.ll[c] = lpn[1] + lpn[2];
     } else {
-      *qs = cur;
+      q[si] = cur;
     }
   }
   if (!M.adapt) return;
   // shared per-site counters: aggregate in shared memory, one global atomic per site per CTA
   __shared__ unsigned s_tot[64], s_acc[64];
-  if (F.d_cont <= 64) {
+  if (dc <= 64) {
     for (int i = threadIdx.x; i < 64; i += blockDim.x) { s_tot[i] = 0; s_acc[i] = 0; }
     __syncthreads();
     if (s >= 0) { atomicAdd(&s_tot[s], 1u); if (accept) atomicAdd(&s_acc[s], 1u); }
     __syncthreads();
-    for (int i = threadIdx.x; i < (int)F.d_cont; i += blockDim.x) {
+    for (int i = threadIdx.x; i < (int)dc; i += blockDim.x) {
       if (s_tot[i]) atomicAdd(&M.tot_cnt[i], s_tot[i]);
       if (s_acc[i]) atomicAdd(&M.acc_cnt[i], s_acc[i]);
     }
   } else if (s >= 0) { atomicAdd(&M.tot_cnt[s], 1u); if (accept) atomicAdd(&M.acc_cnt[s], 1u); }
 }
 
-// ---- resampling: ancestor search + state copy in one kernel (resample_particles, smc.rs:326-349) ----
+// ---- resampling: ancestor search + record copy in one kernel (resample_particles, smc.rs:326-349) ----
 // Output slot j (global) takes the particle at which the walk of smc.rs:263-268 / 284-289 stops: the
 // first i with S_i >= threshold_j over the exact running sums S of the SOURCE rank's weights (S_0 = its
-// carry-in). Ancestors of consecutive slots are non-decreasing, so the source reads are nearly
-// coalesced; the destination (this rank's or a peer's buffers, over NVLink) is written contiguously.
+// carry-in). Ancestors of consecutive slots are non-decreasing, so the source records are read nearly
+// in order; the destination (this rank's or a peer's buffer, over NVLink) is written contiguously,
+// 16 bytes per thread.
 __device__ __forceinline__ int64_t lower_bound_S(const double* __restrict__ S, int64_t n, double t) {  // first i in [0, n] with S[i] >= t, or n + 1
   int64_t lo = 0, hi = n + 1;
   while (lo < hi) {
@@ -974,7 +1011,7 @@ struct GatherArgs {
   int64_t j0, cnt;        // global output slots [j0, j0 + cnt)
   int64_t dst_off;        // destination-local index of slot j0
   Pop src, dst;
-  int64_t d_cont, zp;
+  int64_t pitch, ll_off;  // record size; byte offset of (log_lik, log_factors) in a record
   uint64_t* idx_out;      // optional: GLOBAL ancestor index of slot j0 + k -> idx_out[idx_off + k]
   int64_t idx_off, first_src;
 };
@@ -997,49 +1034,53 @@ __global__ void __launch_bounds__(GA_THREADS) k_smcx_gather(const __grid_constan
       }
     } else a = (int64_t)A.idx_in[k];
     if (A.idx_out) A.idx_out[A.idx_off + k] = (uint64_t)(A.first_src + a);
+    const double* l = (const double*)(A.src.rec + a * A.pitch + A.ll_off);  // (log_lik, log_factors) of the ancestor
+    A.dst.ll[A.dst_off + k] = l[0] + l[1];
   }
   s_anc[threadIdx.x] = a;
-  if (k < A.cnt) {
-    const int64_t jd = A.dst_off + k;
-    // rows of q, then the three accumulators: 8 independent loads in flight per thread
-    for (int64_t r0 = 0; r0 < A.d_cont; r0 += 8) {
-      double v[8];
-#pragma unroll
-      for (int b = 0; b < 8; b++) if (r0 + b < A.d_cont) v[b] = A.src.q[(r0 + b) * A.src.n + a];
-#pragma unroll
-      for (int b = 0; b < 8; b++) if (r0 + b < A.d_cont) A.dst.q[(r0 + b) * A.dst.n + jd] = v[b];
-    }
-    const double l0 = A.src.lp3[a], l1 = A.src.lp3[A.src.n + a], l2 = A.src.lp3[2 * A.src.n + a];
-    A.dst.lp3[jd] = l0; A.dst.lp3[A.dst.n + jd] = l1; A.dst.lp3[2 * A.dst.n + jd] = l2;
-  }
-  if (A.zp == 0) return;
   __syncthreads();
-  // discrete records: 16-byte chunks, consecutive threads on consecutive chunks of the destination
-  const int cpp = (int)(A.zp >> 4);
+  const int cpp = (int)(A.pitch >> 4);
   const int64_t base = (int64_t)blockIdx.x * GA_THREADS;
   const int64_t live = min((int64_t)GA_THREADS, A.cnt - base);
+  uint8_t* __restrict__ dst = A.dst.rec + (A.dst_off + base) * A.pitch;
   for (int64_t ch = threadIdx.x; ch < live * cpp; ch += GA_THREADS) {
-    const int slot = (int)(ch / cpp), part = (int)(ch % cpp);
-    const uint4 v = *(const uint4*)(A.src.z + s_anc[slot] * A.zp + (int64_t)part * 16);
-    *(uint4*)(A.dst.z + (A.dst_off + base + slot) * A.zp + (int64_t)part * 16) = v;
+    const int slot = (int)(ch / cpp), part = (int)(ch - (int64_t)slot * cpp);
+    const uint4 v = *(const uint4*)(A.src.rec + s_anc[slot] * A.pitch + (int64_t)part * 16);
+    *(uint4*)(dst + ch * 16) = v;
   }
 }
 
-// ---- container <-> the generic engine's int32 planes ----
-__global__ void k_z_unpack(const uint8_t* __restrict__ z, int64_t zp, int zw, const int32_t* __restrict__ drow, int64_t d_disc, disc_t* __restrict__ qd, int64_t n) {
+// ---- records <-> the generic engine's [row][particle] arrays ----
+__global__ void k_rec_unpack(const uint8_t* __restrict__ rec, RecLayout L, const int32_t* __restrict__ drow, int64_t n, double* __restrict__ q, double* __restrict__ lp3, disc_t* __restrict__ qd) {
   const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= n) return;
-  const uint8_t* rec = z + c * zp;
-  for (int64_t s = 0; s < d_disc; s++) qd[(int64_t)drow[s] * n + c] = zw == 1 ? (disc_t)rec[s] : ((const int32_t*)rec)[s];
+  const uint8_t* r = rec + c * L.pitch;
+  const double* rq = (const double*)r;
+  if (q) for (int64_t s = 0; s < L.d_cont; s++) q[s * n + c] = rq[s];
+  if (lp3) for (int a = 0; a < 3; a++) lp3[a * n + c] = rq[L.d_cont + a];
+  if (qd) {
+    const uint8_t* z = r + L.zoff;
+    for (int64_t s = 0; s < L.d_disc; s++) qd[(int64_t)drow[s] * n + c] = L.zw == 1 ? (disc_t)z[s] : ((const int32_t*)z)[s];
+  }
 }
-__global__ void k_z_pack(const disc_t* __restrict__ qd, const int32_t* __restrict__ drow, int64_t d_disc, uint8_t* __restrict__ z, int64_t zp, int zw, int64_t n, int* __restrict__ overflow) {
+__global__ void k_rec_pack(uint8_t* __restrict__ rec, RecLayout L, const int32_t* __restrict__ drow, int64_t n, const double* __restrict__ q, const double* __restrict__ lp3, const disc_t* __restrict__ qd,
+                           double* __restrict__ ll, int* __restrict__ overflow) {
   const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= n) return;
-  uint8_t* rec = z + c * zp;
-  for (int64_t s = 0; s < d_disc; s++) {
-    const disc_t v = qd[(int64_t)drow[s] * n + c];
-    if (zw == 1) { if (v < 0 || v > 255) *overflow = 1; rec[s] = (uint8_t)v; }
-    else ((int32_t*)rec)[s] = v;
+  uint8_t* r = rec + c * L.pitch;
+  double* rq = (double*)r;
+  if (q) for (int64_t s = 0; s < L.d_cont; s++) rq[s] = q[s * n + c];
+  if (lp3) {
+    for (int a = 0; a < 3; a++) rq[L.d_cont + a] = lp3[a * n + c];
+    ll[c] = lp3[n + c] + lp3[2 * n + c];
+  }
+  if (qd) {
+    uint8_t* z = r + L.zoff;
+    for (int64_t s = 0; s < L.d_disc; s++) {
+      const disc_t v = qd[(int64_t)drow[s] * n + c];
+      if (L.zw == 1) { if (v < 0 || v > 255) *overflow = 1; z[s] = (uint8_t)v; }
+      else ((int32_t*)z)[s] = v;
+    }
   }
 }
 
@@ -1066,13 +1107,12 @@ struct fc_smc_session {
   uint64_t stream0 = 0;                   // random stream of local particle 0
   int rank = 0, world = 1;
   bool connected = false;
-  // slab: mailbox + the two population buffer sets (exported to the peers)
+  // slab: mailbox + the two record buffers + the log-likelihood array (exported to the peers)
   char* slab = nullptr;
   size_t slab_bytes = 0;
-  size_t off_q[2] = {0, 0}, off_lp3[2] = {0, 0}, off_z[2] = {0, 0};
+  size_t off_rec[2] = {0, 0}, off_ll = 0;
   int cur = 0;
-  int zw = 1;
-  int64_t zp = 0;
+  fc::RecLayout L;
   char* peer_slab[MB_MAXW] = {nullptr};
   int64_t peer_n[MB_MAXW] = {0}, bounds[MB_MAXW + 1] = {0};
   fc::Comm cm;
@@ -1080,7 +1120,7 @@ struct fc_smc_session {
   fc::DevBuf<int> err;
   unsigned long long resamples = 0;  // global resamples started (mailbox sequence of the carry chain)
   // local arrays
-  fc::DevBuf<double> ll, log_w, comb, w, S, us, part, scal, ends;
+  fc::DevBuf<double> log_w, comb, w, S, us, part, scal, ends;
   fc::DevBuf<char> work;
   fc::DevBuf<uint64_t> idx;
   fc::DevBuf<fc::Bisect> bis;
@@ -1092,38 +1132,43 @@ struct fc_smc_session {
   bool fused = false;
   fc::DevBuf<fc::FPlate> fplates;
   fc::FusedProg F;
-  // generic engine
+  // generic engine: [row][particle] copies of the records (valid flags say which are current)
   fc::MoveEngine eng;
   fc::DevBuf<fc::disc_t> qd32;
-  fc::DevBuf<double> total;
+  fc::DevBuf<double> q_soa, lp3_soa, total;
   fc::DevBuf<uint64_t> n_accept;
-  bool qd32_valid = false;
+  bool soa_valid = false;
   double beta = 0.0, log_evidence = 0.0, prev_dbeta = 0.0;
   uint64_t steps = 0, moves = 0, migrated = 0, ess_evals = 0;
   bool finished = false;
+  // optional CUDA-event timing of the phases of a tempering step, on the launching stream
+  // (fc_debug_set("smc_timing", 1)): next_beta, reweight, exact scan + carry chain, gather + migration, moves
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> phase_events;
+  double phase_ms[5] = {0, 0, 0, 0, 0};
+  uint64_t phase_launches[5] = {0, 0, 0, 0, 0};
   bool record = false;               // keep the global ancestors of the slots this rank produces (parity tests)
   int64_t last_jlo = 0, last_jhi = 0;
   bool bis_ll_valid = false;         // max(ll) / bad flag in `bis` describe the current ll
 
+  double* ll() const { return (double*)(slab + off_ll); }
   fc::Pop pop(int which) const {
     fc::Pop p;
-    p.q = (double*)(slab + off_q[which]); p.lp3 = (double*)(slab + off_lp3[which]); p.z = (uint8_t*)(slab + off_z[which]); p.n = n;
+    p.rec = (uint8_t*)(slab + off_rec[which]); p.ll = ll(); p.n = n;
     return p;
   }
-  fc::Pop peer_pop(int r, int which) const {  // rank r's buffer set as mapped here (same layout formula, its own n)
+  fc::Pop peer_pop(int r, int which) const {  // rank r's buffers as mapped here (same layout formula, its own n)
     fc::Pop p;
-    size_t oq[2], ol[2], oz[2];
-    layout(peer_n[r], P->d_cont, zp, oq, ol, oz);
+    size_t orec[2], oll;
+    layout(peer_n[r], L.pitch, orec, oll);
     char* b = r == rank ? slab : peer_slab[r];
-    p.q = (double*)(b + oq[which]); p.lp3 = (double*)(b + ol[which]); p.z = (uint8_t*)(b + oz[which]); p.n = peer_n[r];
+    p.rec = (uint8_t*)(b + orec[which]); p.ll = (double*)(b + oll); p.n = peer_n[r];
     return p;
   }
-  static size_t layout(int64_t n, int64_t d_cont, int64_t zp, size_t (&oq)[2], size_t (&ol)[2], size_t (&oz)[2]) {
+  static size_t layout(int64_t n, int64_t pitch, size_t (&orec)[2], size_t& oll) {
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
     size_t o = up(sizeof(fc::MBox));
-    for (int k = 0; k < 2; k++) { oq[k] = o; o = up(o + (size_t)std::max<int64_t>(1, d_cont * n) * 8); }
-    for (int k = 0; k < 2; k++) { ol[k] = o; o = up(o + (size_t)3 * n * 8); }
-    for (int k = 0; k < 2; k++) { oz[k] = o; o = up(o + (size_t)std::max<int64_t>(16, zp * n)); }
+    for (int k = 0; k < 2; k++) { orec[k] = o; o = up(o + (size_t)pitch * n); }
+    oll = o; o = up(o + (size_t)n * 8);
     return o;
   }
 };
@@ -1141,7 +1186,7 @@ static int nb_blocks(int64_t n) {
 }
 // debug switches (fc_debug_set): "nb_plain" = the reference's plain 64-step bisection without the search
 // phase; "smc_generic" = run every program on the generic scoring engine instead of the fused kernels
-static int g_nb_plain = -1, g_smc_generic = -1;
+static int g_nb_plain = -1, g_smc_generic = -1, g_smc_timing = 0;
 static bool nb_plain() {
   if (g_nb_plain < 0) g_nb_plain = getenv("FC_NB_PLAIN") != nullptr;
   return g_nb_plain != 0;
@@ -1149,6 +1194,30 @@ static bool nb_plain() {
 static bool smc_generic() {
   if (g_smc_generic < 0) g_smc_generic = getenv("FC_SMC_GENERIC") != nullptr;
   return g_smc_generic != 0;
+}
+
+struct PhaseTimer {  // brackets a phase with two events when timing is on
+  fc_smc_session* S; int phase; cudaEvent_t e0 = nullptr, e1 = nullptr;
+  PhaseTimer(fc_smc_session* S_, int phase_) : S(S_), phase(phase_) {
+    if (!g_smc_timing) return;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, S->P->stream);
+  }
+  void stop() {
+    if (!e0) return;
+    cudaEventRecord(e1, S->P->stream);
+    S->phase_events.push_back({phase, {e0, e1}});
+    e0 = nullptr;
+  }
+  ~PhaseTimer() { stop(); }
+};
+static void phase_collect(fc_smc_session* S) {  // after a stream synchronisation
+  for (auto& pe : S->phase_events) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, pe.second.first, pe.second.second) == cudaSuccess) { S->phase_ms[pe.first] += ms; S->phase_launches[pe.first] += 1; }
+    cudaEventDestroy(pe.second.first); cudaEventDestroy(pe.second.second);
+  }
+  S->phase_events.clear();
 }
 
 static int32_t comm_check(fc_smc_session* S) {  // after a stream synchronisation
@@ -1246,14 +1315,25 @@ int32_t next_beta_host(const double* h_log_w, const double* h_ll, size_t n, doub
 
 static double lwc_of(const fc_smc_session* S) { return -std::log((double)S->n_total); }
 
-static int32_t ensure_qd32(fc_smc_session* S) {
+// [row][particle] copies of the current records for the generic engine and the copy-out paths
+static int32_t ensure_soa(fc_smc_session* S) {
   fc_program* P = S->P;
-  if (S->qd32_valid || P->d_disc == 0) return FC_OK;
-  FC_CUDA(S->qd32.reserve(P->d_disc * S->n));
-  k_z_unpack<<<(unsigned)cdiv(S->n, 256), 256, 0, P->stream>>>(S->pop(S->cur).z, S->zp, S->zw, P->d_drow.p, P->d_disc, S->qd32.p, S->n);
+  if (S->soa_valid) return FC_OK;
+  FC_CUDA(S->q_soa.reserve(std::max<int64_t>(1, P->d_cont * S->n)));
+  FC_CUDA(S->lp3_soa.reserve(3 * S->n));
+  FC_CUDA(S->qd32.reserve(std::max<int64_t>(1, P->d_disc * S->n)));
+  k_rec_unpack<<<(unsigned)cdiv(S->n, 256), 256, 0, P->stream>>>(S->pop(S->cur).rec, S->L, P->d_drow.p, S->n, S->q_soa.p, S->lp3_soa.p, P->d_disc ? S->qd32.p : nullptr);
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 1;
-  S->qd32_valid = true;
+  S->soa_valid = true;
+  return FC_OK;
+}
+// write the generic engine's arrays back into the records (q and the accumulators; discrete sites on request)
+static int32_t soa_to_records(fc_smc_session* S, bool with_disc) {
+  fc_program* P = S->P;
+  k_rec_pack<<<(unsigned)cdiv(S->n, 256), 256, 0, P->stream>>>(S->pop(S->cur).rec, S->L, P->d_drow.p, S->n, S->q_soa.p, S->lp3_soa.p, (with_disc && P->d_disc) ? S->qd32.p : nullptr, S->ll(), S->err.p + 1);
+  FC_KERNEL_CHECK();
+  P->n_kernel_launches += 1;
   return FC_OK;
 }
 
@@ -1293,12 +1373,12 @@ static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, 
     if (!S->bis_ll_valid) {  // max(ll) / bad flag: those of this step's next_beta pre-pass when it ran on the same ll
       bisect_init(hb, S->beta, 0.0, (double)S->n_total, 0.0);
       FC_CUDA(cudaMemcpyAsync(S->bis.p, &hb, sizeof(hb), cudaMemcpyHostToDevice, st));
-      k_nb_prepass<<<nb_blocks(n), NB_THREADS, 0, st>>>(S->ll.p, n, S->bis.p, S->part.p, S->cm);
+      k_nb_prepass<<<nb_blocks(n), NB_THREADS, 0, st>>>(S->ll(), n, S->bis.p, S->part.p, S->cm);
       S->P->n_kernel_launches += 1;
       S->bis_ll_valid = true;
     }
-    k_nb_eval_uni<<<nb_blocks(n), NB_THREADS, 0, st>>>(lwc, S->ll.p, S->bis.p, S->part.p, n, 1, d_beta, S->cm);
-    k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(nullptr, lwc, S->ll.p, d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n, (double)S->n_total);
+    k_nb_eval_uni<<<nb_blocks(n), NB_THREADS, 0, st>>>(lwc, S->ll(), S->bis.p, S->part.p, n, 1, d_beta, S->cm);
+    k_reweight<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(nullptr, lwc, S->ll(), d_beta, S->bis.p, write_log_w ? S->comb.p : nullptr, S->w.p, n, (double)S->n_total);
     FC_KERNEL_CHECK();
     S->P->n_kernel_launches += 2;
     FC_CUDA(cudaMemcpyAsync(&hb, S->bis.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
@@ -1309,7 +1389,7 @@ static int32_t smc_reweight(fc_smc_session* S, double d_beta, bool write_log_w, 
     // general weights: combined = log_w + d ll, global lse, then normalise
     unsigned nbk = (unsigned)cdiv(n, 256);
     FC_CUDA(S->us.reserve(n + 1));
-    k_combine<<<nbk, 256, 0, st>>>(S->log_w.p, 0.0, S->ll.p, d_beta, S->us.p, n);
+    k_combine<<<nbk, 256, 0, st>>>(S->log_w.p, 0.0, S->ll(), d_beta, S->us.p, n);
     FC_TRY(global_lse(S, S->us.p, log_norm));
     k_sub_exp<<<nbk, 256, 0, st>>>(S->us.p, S->scal.p, (double)S->n_total, write_log_w ? S->comb.p : nullptr, S->w.p, n);
     FC_KERNEL_CHECK();
@@ -1376,7 +1456,7 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
   GatherArgs G;
   memset(&G, 0, sizeof(G));
   G.n_src = n; G.n_total = (double)N; G.method = method; G.seed = S->seed; G.tag = tag; G.src = S->pop(from);
-  G.d_cont = P->d_cont; G.zp = S->zp; G.first_src = S->first;
+  G.pitch = S->L.pitch; G.ll_off = (P->d_cont + 1) * 8; G.first_src = S->first;
   const bool want_idx = h_idx || S->record;
   double u_raw = 0.0;
   if (method == FC_RESAMPLE_MULTINOMIAL) {
@@ -1402,6 +1482,7 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
     }
     G.u_raw = u_raw;
     // exact running sums of this rank's weights from the carry-in of the ranks before it
+    PhaseTimer t_scan(S, 2);
     FC_CUDA(S->work.reserve(scan_work_bytes(n)));
     ScanCtl hs;
     memset(&hs, 0, sizeof(hs));
@@ -1433,6 +1514,8 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
       jhi = S->rank == W - 1 ? N : cnt_le(ends[S->rank]);
       if (jhi < jlo) jhi = jlo;
     }
+    t_scan.stop();
+    PhaseTimer t_ga(S, 3);
     G.S = S->S.p;
     S->last_jlo = jlo; S->last_jhi = jhi;
     if (want_idx) FC_CUDA(S->idx.reserve(std::max<int64_t>(n, jhi - jlo)));
@@ -1462,12 +1545,9 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
     if (h_idx && W == 1) FC_CUDA(cudaMemcpyAsync(h_idx, S->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
   }
   S->cur = to;
-  S->qd32_valid = false;
+  S->soa_valid = false;
   S->bis_ll_valid = false;
   S->log_w_uniform = true;  // weight 1/n, log_weight ln(1/n) (smc.rs:338-345); materialised on demand
-  k_loglik<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(S->pop(to).lp3, S->ll.p, n);
-  FC_KERNEL_CHECK();
-  P->n_kernel_launches += 1;
   return FC_OK;
 }
 
@@ -1483,24 +1563,24 @@ static int32_t smc_rejuvenate(fc_smc_session* S, double beta, uint64_t steps) {
       MoveX M;
       M.scale = S->eng.scale.p; M.acc_cnt = S->eng.acc_cnt.p; M.tot_cnt = S->eng.tot_cnt.p;
       M.seed = S->eng.seed; M.chain0 = S->eng.chain0; M.step_tag = S->moves; M.beta = beta; M.adapt = 1;
-      k_smcx_move<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(S->F, pop, n, S->ll.p, M);
+      k_smcx_move<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(S->F, pop, M);
       FC_KERNEL_CHECK();
       P->n_kernel_launches += 1;
       FC_TRY(S->eng.shared_adapt(0.44, 0.7));
       S->moves += 1;
     }
+    if (steps) S->soa_valid = false;
     return FC_OK;
   }
-  FC_TRY(ensure_qd32(S));
+  // generic scoring engine on [row][particle] copies; the records are rewritten afterwards
+  if (steps == 0) return FC_OK;
+  FC_TRY(ensure_soa(S));
   for (uint64_t r = 0; r < steps; r++) {
-    FC_TRY(S->eng.step(pop.q, S->qd32.p, pop.lp3, S->total.p, S->n_accept.p, S->moves, beta, true, 0.44, 0.7));
+    FC_TRY(S->eng.step(S->q_soa.p, S->qd32.p, S->lp3_soa.p, S->total.p, S->n_accept.p, S->moves, beta, true, 0.44, 0.7));
     FC_TRY(S->eng.shared_adapt(0.44, 0.7));
     S->moves += 1;
   }
-  k_loglik<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(pop.lp3, S->ll.p, n);
-  FC_KERNEL_CHECK();
-  P->n_kernel_launches += 1;
-  return FC_OK;
+  return soa_to_records(S, false);
 }
 
 // one tempering step (the body of the while loop, smc.rs:502-559)
@@ -1510,24 +1590,30 @@ static int32_t smc_temper_step(fc_smc_session* S) {
   const double target_ess = std::fmin(std::fmax(S->cfg.ess_threshold * N, 1.0), N);
   S->steps += 1;
   double beta_new;
+  PhaseTimer t_nb(S, 0);
   if (S->log_w_uniform) {
     const double guess = S->prev_dbeta > 0.0 ? S->beta + 4.0 * S->prev_dbeta : 0.0;
-    FC_TRY(next_beta_uniform(P->stream, S->cm, lwc_of(S), S->ll.p, S->n, N, S->beta, target_ess, guess, S->bis.p, S->part.p, &P->n_kernel_launches, &S->ess_evals, &beta_new));
+    FC_TRY(next_beta_uniform(P->stream, S->cm, lwc_of(S), S->ll(), S->n, N, S->beta, target_ess, guess, S->bis.p, S->part.p, &P->n_kernel_launches, &S->ess_evals, &beta_new));
     FC_TRY(comm_check(S));
     S->bis_ll_valid = true;
   } else {
     if (S->world > 1) { set_error("next_beta on non-uniform weights is not available on a sharded population"); return FC_ERR_UNSUPPORTED_OP; }
-    FC_TRY(next_beta_general(P->stream, S->log_w.p, S->ll.p, S->n, S->beta, target_ess, S->bis.p, S->tri.p, &P->n_kernel_launches, &beta_new));
+    FC_TRY(next_beta_general(P->stream, S->log_w.p, S->ll(), S->n, S->beta, target_ess, S->bis.p, S->tri.p, &P->n_kernel_launches, &beta_new));
   }
+  t_nb.stop();
   if (S->steps >= 10000) beta_new = 1.0;
   const double d_beta = beta_new - S->beta;
   double log_norm;
-  FC_TRY(smc_reweight(S, d_beta, beta_new >= 1.0, &log_norm));
+  {
+    PhaseTimer t_rw(S, 1);
+    FC_TRY(smc_reweight(S, d_beta, beta_new >= 1.0, &log_norm));
+  }
   S->log_evidence += log_norm;
   S->prev_dbeta = d_beta;
   S->beta = beta_new;
   if (S->beta < 1.0) {
     FC_TRY(smc_resample(S, S->cfg.resampling_method, nullptr, nullptr));  // smc.rs:534-541
+    PhaseTimer t_mv(S, 4);
     FC_TRY(smc_rejuvenate(S, S->beta, S->cfg.rejuvenation_steps));       // smc.rs:544-554
   }
   return FC_OK;
@@ -1604,25 +1690,18 @@ static int32_t smc_init_population(fc_smc_session* S) {
   Pop pop = S->pop(S->cur);
   const uint64_t tag = 0x7000000000000000ULL;
   if (S->fused) {
-    k_smcx_prior<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(S->F, pop, N, S->seed, S->stream0, tag);
-    k_smcx_score<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(S->F, pop, N, S->ll.p);
+    k_smcx_prior<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(S->F, pop, S->seed, S->stream0, tag);
     FC_KERNEL_CHECK();
-    p->n_kernel_launches += 2;
+    p->n_kernel_launches += 1;
     return FC_OK;
   }
+  FC_CUDA(S->q_soa.reserve(std::max<int64_t>(1, p->d_cont * N)));
+  FC_CUDA(S->lp3_soa.reserve(3 * N));
   FC_CUDA(S->qd32.reserve(std::max<int64_t>(1, p->d_disc * N)));
-  FC_TRY(prior_sample_dev(p, pop.q, S->qd32.p, N, S->seed, S->stream0, tag));
-  FC_TRY(score_dev(p, pop.q, S->qd32.p, N, pop.lp3, S->total.p, nullptr));
-  unsigned nbk = (unsigned)cdiv(N, 256);
-  if (p->d_disc) {
-    FC_CUDA(cudaMemsetAsync(S->err.p, 0, 4, st));
-    k_z_pack<<<nbk, 256, 0, st>>>(S->qd32.p, p->d_drow.p, p->d_disc, pop.z, S->zp, S->zw, N, S->err.p);
-    p->n_kernel_launches += 1;
-  }
-  S->qd32_valid = true;
-  k_loglik<<<nbk, 256, 0, st>>>(pop.lp3, S->ll.p, N);
-  FC_KERNEL_CHECK();
-  p->n_kernel_launches += 1;
+  FC_TRY(prior_sample_dev(p, S->q_soa.p, S->qd32.p, N, S->seed, S->stream0, tag));
+  FC_TRY(score_dev(p, S->q_soa.p, S->qd32.p, N, S->lp3_soa.p, S->total.p, nullptr));
+  FC_TRY(soa_to_records(S, true));
+  S->soa_valid = true;
   return FC_OK;
 }
 
@@ -1668,20 +1747,22 @@ static int32_t smc_create_impl(fc_program* p, const fc_smc_config* cfg, uint64_t
   const int64_t N = S->n;
   cudaStream_t st = p->stream;
   std::vector<FPlate> fpl;
-  S->fused = fused_lower(p, fpl, S->zw);
-  S->zp = p->d_disc ? ((p->d_disc * S->zw + 15) / 16) * 16 : 0;
-  S->slab_bytes = fc_smc_session::layout(N, p->d_cont, S->zp, S->off_q, S->off_lp3, S->off_z);
+  int zw = 1;
+  S->fused = fused_lower(p, fpl, zw);
+  S->L.d_cont = p->d_cont; S->L.d_disc = p->d_disc; S->L.zw = zw; S->L._pad = 0;
+  S->L.zoff = (((p->d_cont + 3) * 8 + 15) / 16) * 16;
+  S->L.pitch = S->L.zoff + ((p->d_disc * zw + 15) / 16) * 16;
+  S->slab_bytes = fc_smc_session::layout(N, S->L.pitch, S->off_rec, S->off_ll);
   FC_CUDA(cudaMalloc((void**)&S->slab, S->slab_bytes));
-  FC_CUDA(cudaMemsetAsync(S->slab, 0, S->off_q[0], st));  // the mailbox
-  if (S->zp) { FC_CUDA(cudaMemsetAsync(S->slab + S->off_z[0], 0, (size_t)S->zp * N, st)); FC_CUDA(cudaMemsetAsync(S->slab + S->off_z[1], 0, (size_t)S->zp * N, st)); }
-  FC_CUDA(S->seq.reserve(1)); FC_CUDA(S->err.reserve(1)); FC_CUDA(S->counter.reserve(1));
-  FC_CUDA(cudaMemsetAsync(S->seq.p, 0, 8, st)); FC_CUDA(cudaMemsetAsync(S->err.p, 0, 4, st)); FC_CUDA(cudaMemsetAsync(S->counter.p, 0, 4, st));
+  FC_CUDA(cudaMemsetAsync(S->slab, 0, S->off_rec[0], st));  // the mailbox
+  FC_CUDA(S->seq.reserve(1)); FC_CUDA(S->err.reserve(2)); FC_CUDA(S->counter.reserve(1));
+  FC_CUDA(cudaMemsetAsync(S->seq.p, 0, 8, st)); FC_CUDA(cudaMemsetAsync(S->err.p, 0, 8, st)); FC_CUDA(cudaMemsetAsync(S->counter.p, 0, 4, st));
   memset(&S->cm, 0, sizeof(S->cm));
   S->cm.rank = rank; S->cm.world = world; S->cm.seq = S->seq.p; S->cm.err = S->err.p;
   S->cm.box[rank] = (MBox*)S->slab;
   S->peer_n[rank] = N;
   if (world == 1) { S->bounds[0] = 0; S->bounds[1] = N; S->connected = true; }
-  for (auto* b : {&S->ll, &S->log_w, &S->comb, &S->w, &S->total}) FC_CUDA(b->reserve(N));
+  for (auto* b : {&S->log_w, &S->comb, &S->w, &S->total}) FC_CUDA(b->reserve(N));
   FC_CUDA(S->S.reserve(N + 2));
   FC_CUDA(S->part.reserve(4 * RDB + 8)); FC_CUDA(S->scal.reserve(8)); FC_CUDA(S->ends.reserve(MB_MAXW));
   FC_CUDA(S->idx.reserve(N)); FC_CUDA(S->n_accept.reserve(N)); FC_CUDA(S->bis.reserve(1)); FC_CUDA(S->tri.reserve(RDB + 1));
@@ -1694,13 +1775,13 @@ static int32_t smc_create_impl(fc_program* p, const fc_smc_config* cfg, uint64_t
     FC_CUDA(cudaStreamSynchronize(st));
     FusedProg& F = S->F;
     F.ops = p->d_all_ops.p; F.scalar_ops = p->d_scalar_ops.p; F.plates = S->fplates.p; F.crow = p->d_crow.p; F.nodes = p->d_expr_nodes.p;
-    F.n_ops = (int32_t)p->all_ops.size(); F.n_scalar = (int32_t)p->scalar_ops.size(); F.n_plates = (int32_t)fpl.size(); F.zw = S->zw; F.zp = S->zp; F.d_cont = p->d_cont;
+    F.n_ops = (int32_t)p->all_ops.size(); F.n_scalar = (int32_t)p->scalar_ops.size(); F.n_plates = (int32_t)fpl.size(); F._pad = 0; F.L = S->L;
   }
   FC_TRY(smc_init_population(S.get()));
   FC_CUDA(cudaStreamSynchronize(st));
   if (!S->fused && p->d_disc) {
     int e = 0;
-    FC_CUDA(cudaMemcpy(&e, S->err.p, 4, cudaMemcpyDeviceToHost));
+    FC_CUDA(cudaMemcpy(&e, S->err.p + 1, 4, cudaMemcpyDeviceToHost));
     if (e) { set_error("discrete prior draw outside the byte range of the packed particle record"); return FC_ERR_UNSUPPORTED_OP; }
   }
   *out = S.release();
@@ -1768,7 +1849,7 @@ int32_t fc_smc_step(fc_smc_session* s, double* beta_out) {
       cudaStream_t st = s->P->stream;
       unsigned nbk = (unsigned)cdiv(s->n, 256);
       FC_TRY(smc_materialise_log_w(s));
-      k_combine<<<nbk, 256, 0, st>>>(s->log_w.p, 0.0, s->ll.p, 1.0, s->comb.p, s->n);
+      k_combine<<<nbk, 256, 0, st>>>(s->log_w.p, 0.0, s->ll(), 1.0, s->comb.p, s->n);
       FC_KERNEL_CHECK();
       s->P->n_kernel_launches += 1;
       double le;
@@ -1782,6 +1863,7 @@ int32_t fc_smc_step(fc_smc_session* s, double* beta_out) {
       FC_TRY(smc_temper_step(s));
     }
     if (s->beta >= 1.0) s->finished = true;
+    if (!s->phase_events.empty()) { FC_CUDA(cudaStreamSynchronize(s->P->stream)); phase_collect(s); }
   }
   if (beta_out) *beta_out = s->beta;
   return FC_OK;
@@ -1806,8 +1888,9 @@ int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, doub
     if (h_weight) FC_CUDA(cudaMemcpyAsync(h_weight, s->w.p, n * 8, cudaMemcpyDeviceToHost, st));
     if (h_log_weight) FC_CUDA(cudaMemcpyAsync(h_log_weight, s->comb.p, n * 8, cudaMemcpyDeviceToHost, st));
   }
-  if (h_values && p->d_cont) FC_CUDA(cudaMemcpyAsync(h_values, pop.q, p->d_cont * n * 8, cudaMemcpyDeviceToHost, st));
-  if (h_dvalues && p->d_disc) { FC_TRY(ensure_qd32(s)); FC_TRY(disc_to_host(p, s->qd32.p, p->d_disc * n, h_dvalues)); }
+  if ((h_values && p->d_cont) || (h_dvalues && p->d_disc)) FC_TRY(ensure_soa(s));
+  if (h_values && p->d_cont) FC_CUDA(cudaMemcpyAsync(h_values, s->q_soa.p, p->d_cont * n * 8, cudaMemcpyDeviceToHost, st));
+  if (h_dvalues && p->d_disc) FC_TRY(disc_to_host(p, s->qd32.p, p->d_disc * n, h_dvalues));
   if (log_evidence) *log_evidence = s->log_evidence;
   if (n_temper_steps) *n_temper_steps = s->steps;
   FC_CUDA(cudaStreamSynchronize(st));
@@ -1817,10 +1900,12 @@ int32_t fc_smc_get(fc_smc_session* s, double* h_values, int64_t* h_dvalues, doub
 int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dvalues, double** d_log_w, double** d_loglik) {
   using namespace fc;
   FC_TRY(smc_ready(s));
-  if (d_values) *d_values = s->pop(s->cur).q;
-  if (d_dvalues) { FC_TRY(ensure_qd32(s)); *d_dvalues = s->qd32.p; }
+  // [row][particle] snapshots of the particle records (valid until the next step / resample / move)
+  if (d_values || d_dvalues) FC_TRY(ensure_soa(s));
+  if (d_values) *d_values = s->q_soa.p;
+  if (d_dvalues) *d_dvalues = s->qd32.p;
   if (d_log_w) { FC_TRY(smc_materialise_log_w(s)); *d_log_w = s->log_w.p; }
-  if (d_loglik) *d_loglik = s->ll.p;
+  if (d_loglik) *d_loglik = s->ll();
   return FC_OK;
 }
 
@@ -1830,7 +1915,7 @@ int32_t fc_smc_device_state(fc_smc_session* s, double** d_values, int32_t** d_dv
 int32_t fc_smc_prior_weights(fc_smc_session* s) {
   using namespace fc;
   FC_TRY(smc_ready(s));
-  FC_CUDA(cudaMemcpyAsync(s->log_w.p, s->ll.p, s->n * 8, cudaMemcpyDeviceToDevice, s->P->stream));
+  FC_CUDA(cudaMemcpyAsync(s->log_w.p, s->ll(), s->n * 8, cudaMemcpyDeviceToDevice, s->P->stream));
   s->log_w_uniform = false;
   return FC_OK;
 }
@@ -1953,8 +2038,18 @@ int32_t fc_smc_slot_range(int32_t method, uint64_t n_total, double u_raw, uint64
 int32_t fc_debug_set(const char* key, int32_t value) {
   if (key && !strcmp(key, "nb_plain")) { fc::g_nb_plain = value ? 1 : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_generic")) { fc::g_smc_generic = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "smc_timing")) { fc::g_smc_timing = value ? 1 : 0; return FC_OK; }
   fc::set_error("unknown debug key");
   return FC_ERR_INVALID_ARGUMENT;
+}
+
+// CUDA-event time (ms, on the launching stream) spent in the phases of the tempering steps so far, when
+// fc_debug_set("smc_timing", 1) was on: next_beta search, reweight, exact scan + carry chain, gather +
+// migration (+ barrier), rejuvenation moves; n[k] = how many times phase k ran
+int32_t fc_smc_phase_ms(fc_smc_session* s, double* ms5, uint64_t* n5) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  for (int k = 0; k < 5; k++) { if (ms5) ms5[k] = s->phase_ms[k]; if (n5) n5[k] = s->phase_launches[k]; }
+  return FC_OK;
 }
 
 // counters of a session: particles this rank sent to other ranks, ESS evaluations of all next_beta searches

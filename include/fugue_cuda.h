@@ -316,6 +316,11 @@ int32_t fc_smc_weights(fc_smc_session* s, double* h_log_w, double* h_w);
  * searches; whether the program runs on the fused per-particle kernels. Any pointer may be NULL. */
 int32_t fc_smc_counters(const fc_smc_session* s, uint64_t* migrated, uint64_t* ess_evals, int32_t* fused);
 
+/* CUDA-event time (ms, on the launching stream) per phase of the tempering steps so far, recorded while
+ * fc_debug_set("smc_timing", 1) is on: [0] next_beta search, [1] reweight, [2] exact scan + carry chain,
+ * [3] gather + migration (+ barrier), [4] rejuvenation moves; n5[k] = how many times phase k ran */
+int32_t fc_smc_phase_ms(fc_smc_session* s, double* ms5, uint64_t* n5);
+
 /* ---- sharded SMC: the population of n_total particles is split rank-major over `world`
  * processes, one per GPU of a box. The exchange steps of the tempering loop -- the global weight
  * log-sum-exp / ESS of every next_beta probe and of the reweight (smc.rs:512-524, 588-602), the exact
@@ -381,7 +386,8 @@ int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, do
 
 /* switches for A/B parity tests: "nb_plain" = 1: next_beta evaluates every midpoint of the reference's
  * 64-step bisection (no search phase); "smc_generic" = 1: SMC sessions created afterwards run on the
- * generic scoring engine instead of the fused per-particle kernels */
+ * generic scoring engine instead of the fused per-particle kernels; "smc_timing" = 1: per-phase
+ * CUDA-event timing of the tempering steps (fc_smc_phase_ms) */
 int32_t fc_debug_set(const char* key, int32_t value);
 /* accuracy probe of the kernels' branch-free FP64 primitives: op 0 exp, 1 log, 2 reciprocal */
 int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out);

@@ -1,7 +1,12 @@
 """Sharded tempered SMC inside the CUDA library (fc_smc_create_sharded / export / connect): world size 2,
-both ranks on cuda:0 as separate processes, gloo only for the one-off swap of the 128-byte slab
-descriptors; every exchange step of the ladder runs on the device through cudaIpc peer windows (the
-same code path as one rank per GPU over NVLink: tools/smc_sharded_check.py under torchrun).
+ONE RANK PER GPU as separate processes (needs >= 2 GPUs: run with `gpurun --gpus 2`; skipped on a
+one-GPU box, because ranks that spin on each other's flags must never share a GPU -- time-sliced
+contexts are not guaranteed to run at the same time, B200_PROFILING.md). gloo only for the one-off swap
+of the 128-byte slab descriptors; every exchange step of the ladder runs on the device through cudaIpc
+peer windows over NVLink. The last 2-GPU run of this file is recorded under profiles/. On one GPU the
+same kernels run with world size 1 (every other SMC test), the slot routing is tested on the CPU
+(tests/test_dist_gloo.py) and the carry / routing / offset logic of the resample by
+tests/test_gpu_smc.py::test_virtual_shards_resample_matches_single_population.
 Checks SURVEY 8e: the global systematic / stratified resample is bit-exact w.r.t. the sequential
 reference loop over the rank-major population (oracle) on the weights the device holds, migration
 moves exactly those particles, and the sharded ladder's evidence / posterior agree with the
@@ -35,8 +40,9 @@ def _worker(rank, ws, port, n_total, generic, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=ws)
-    torch.cuda.set_device(0)
+    torch.cuda.set_device(rank)
     from fugue_b200 import api, models, dist as D
+    api.set_device(rank)
     api.debug_set("smc_generic", generic)
     out = {}
     try:
@@ -93,8 +99,11 @@ def _stratified_uniforms(seed, tag, n):
 
 
 @pytest.mark.parametrize("generic", [0, 1])
-def test_sharded_smc_world_size_2_on_one_gpu(generic):
+def test_sharded_smc_world_size_2_one_rank_per_gpu(generic):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs: ranks that wait on each other must not share a GPU (run under gpurun --gpus 2)")
     import oracle
     from fugue_b200 import api
     ws, n_total = 2, 40001

@@ -62,6 +62,8 @@ elif which == "c4":
     R = int(sys.argv[3]) if len(sys.argv) > 3 else 1
     m, _ = models.gaussian_mixture(n_obs=80)
     P = api.Program(m)
+    if os.environ.get("FC_SMC_TIMING"):
+        api.debug_set("smc_timing", 1)
     t0 = time.time()
     S = api.SmcSession(P, Pn, api.SMCConfig(rejuvenation_steps=R), seed=3)
     t_init = time.time() - t0
@@ -83,7 +85,7 @@ elif which == "c4":
     alg = {1: 488, 3: 840}.get(R, 488)
     out = dict(config="C4 gaussian mixture SMC", particles=Pn, rejuvenation_steps=R, temper_steps=steps, init_seconds=t_init, seconds=dt,
                particle_updates_per_s=rate, hbm_alg_GBps=rate * alg / 1e9, hbm_frac=rate * alg / 1e9 / HBM, log_evidence=r.log_evidence,
-               ess_final=float(1.0 / (r.weight ** 2).sum()), betas=betas[:6])
+               ess_final=float(1.0 / (r.weight ** 2).sum()), betas=betas[:6], counters=S.counters(), phase_ms=S.phase_ms()[0])
     # standalone global systematic resample of the final weights
     w = r.weight
     t0 = time.time()
