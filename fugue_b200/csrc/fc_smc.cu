@@ -181,7 +181,11 @@ __global__ void k_uniform_one(double* out, uint64_t seed, uint64_t tag, int64_t 
 // derivative sums come from the same pass), certifies a bracket [a, b] a few ulps wide by actual
 // evaluations on both sides, and then replays the reference loop -- same midpoints 0.5 * (lo + hi),
 // same comparisons -- evaluating ess_at only for midpoints strictly inside (a, b). The returned beta is
-// the reference loop's; ~20 passes instead of ~57. FC_NB_PLAIN=1 disables the search phase.
+// the reference loop's. By default the search ends as soon as Newton has converged (relative step
+// <= 1e-9, so the crossing is known to the rounding noise of the sums) and ALL remaining midpoints are
+// decided by their side of the crossing: ~7 passes instead of ~57. fc_debug_set("nb_plain", 1) evaluates
+// every midpoint as the reference does; ("nb_plain", 2) certifies a bracket by evaluations on both sides
+// and evaluates the midpoints strictly inside it (~20 passes).
 struct Bisect {
   double beta, target, n;   // n: global population size (the ESS reported when an lse is not finite)
   double lo, hi;            // the reference loop's interval (smc.rs:611-619)
@@ -259,7 +263,7 @@ __device__ void nb_advance(Bisect* B, double ess, double s1, double s2, double t
   if (B->phase == 0) {  // the ess_at(1.0) probe (smc.rs:605-608)
     if (ess >= B->target) { B->hi = 1.0; B->done = 1; return; }
     B->lo = B->beta; B->hi = 1.0; B->a = B->beta; B->b = 1.0; B->it = 0;
-    if (B->plain) { B->phase = 3; nb_replay(B); return; }
+    if (B->plain == 1) { B->phase = 3; nb_replay(B); return; }
     B->phase = 1; B->n_search = 0;
     if (B->guess > B->beta && B->guess < 1.0) { B->prev_x = x; B->mid = B->guess; return; }
   } else if (B->phase == 3) {
@@ -278,6 +282,16 @@ __device__ void nb_advance(Bisect* B, double ess, double s1, double s2, double t
     double dn = d * exp(-g / (d * gp));
     if (!(gp < 0.0) || !isfinite(dn) || !(dn > da) || !(dn < db)) dn = da > 0.0 ? sqrt(da * db) : db * 0.0625;
     const double xn = B->beta + dn;
+    if (B->plain == 0 && fabs(dn - d) <= 1e-9 * d && xn > B->a && xn < B->b) {
+      // Newton has converged quadratically: xn is the crossing to within the rounding noise of the sums
+      // themselves (the next correction would be ~1e-18 relative). Every remaining midpoint of the reference
+      // loop is decided by which side of xn it lies on: for midpoints farther than the noise that is
+      // monotonicity, for nearer ones it is the first-order model of ESS around xn, whose error (second
+      // order, ~1e-26 relative) is far below the ~1e-13 evaluation noise that decides them otherwise.
+      B->a = xn; B->b = xn; B->phase = 3;
+      nb_replay(B);
+      return;
+    }
     const bool converged = fabs(dn - d) <= 1e-12 * d || B->n_search >= 24 || !(xn > B->a) || !(xn < B->b);
     if (!converged) { B->prev_x = x; B->mid = xn; return; }
     // two-sided polish around the best point: certify the side that is still far away
@@ -493,7 +507,7 @@ __global__ void __launch_bounds__(NB_THREADS) k_nb_eval_uni(double lw_const, con
   }
   const double d = mode == 0 ? B->mid - B->beta : d_fixed;
   const double m = fma(d, B->max_ll, lw_const);  // the same expression as lv of the max element: x <= 0, == 0 there
-  const bool deriv = mode == 0 && (B->phase == 1 || (B->phase == 0 && !B->plain));
+  const bool deriv = mode == 0 && (B->phase == 1 || (B->phase == 0 && B->plain != 1));
   double acc[4] = {0.0, 0.0, 0.0, 0.0};
   if (m > d_neg_inf()) {
     if (deriv) nb_pass<true>(lw_const, ll, P, d, m, s_et, acc);
@@ -726,9 +740,17 @@ struct FPlate {
   int32_t m0, m1, ss;   // Normal observe: kinds of the (up to two) element-dependent mean terms; sigma is base + SELECT2
   int32_t mt0, mt1, st; // their term indices
 };
+// scalar ops compiled for the fused evaluator: priors with constant parameters of the three families the
+// BASELINE models use become a few FP64 instructions; everything else goes through the interpreter
+enum { SO_GENERIC = 0, SO_NORMAL_CC = 1, SO_GAMMA_CC = 2, SO_BETA_CC = 3, SO_FACTOR = 4 };
+struct SOp {
+  int32_t kind, row;     // row: the site's f64 row (sample ops)
+  double c0, c1, c2;     // NORMAL: mu, 1/sigma, -ln sigma - 0.5 ln 2pi; GAMMA: k - 1, rate, k ln rate - lgamma k;
+};                       // BETA: a - 1, b - 1, -ln B(a, b); FACTOR: the constant log-weight
 struct FusedProg {
   const DOp* ops;           // all ops, program order
   const DOp* scalar_ops;
+  const SOp* sops;          // one per scalar op, same order
   const FPlate* plates;
   const int32_t* crow;
   const fc_expr_node* nodes;
@@ -786,9 +808,27 @@ __device__ __forceinline__ void fused_eval(const FusedProg& F, const uint8_t* __
   const uint8_t* __restrict__ zrec = rec + F.L.zoff;
   double a_prior = 0.0, a_lik = 0.0, a_fac = 0.0;
   ZAcc za{zrec, F.L.zw};
-  if (F.n_scalar) scalar_ops_eval<false>(F.scalar_ops, F.n_scalar, F.crow, q, 1, 0, za, nullptr, F.nodes, a_prior, a_lik, a_fac);
-  lp[0] = 0.0 + a_prior; lp[1] = 0.0 + a_lik; lp[2] = 0.0 + a_fac;
   const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  for (int oi = 0; oi < F.n_scalar; oi++) {
+    const SOp so = F.sops[oi];
+    if (so.kind == SO_GENERIC) { scalar_ops_eval<false>(F.scalar_ops + oi, 1, F.crow, q, 1, 0, za, nullptr, F.nodes, a_prior, a_lik, a_fac); continue; }
+    if (so.kind == SO_FACTOR) { a_fac += so.c0; continue; }
+    const double x = q[so.row];
+    double v;
+    if (so.kind == SO_NORMAL_CC) {        // distribution.rs:189-208
+      const double z = (x - so.c0) * so.c1;
+      v = fma(-0.5 * z, z, so.c2);
+      if (!(v == v)) v = d_neg_inf();     // non-finite x
+    } else if (so.kind == SO_GAMMA_CC) {  // distribution.rs:1039-1068; (k - 1) ln x is skipped at k = 1 (+-0)
+      if (!(x > 0.0) || !d_fin(x)) v = d_neg_inf();
+      else v = (so.c2 + (so.c0 != 0.0 ? so.c0 * log(x) : 0.0)) - so.c1 * x;
+    } else {                              // SO_BETA_CC, interior points; the endpoint rules stay in dist_eval
+      if (x > 0.0 && x < 1.0) v = ((so.c0 != 0.0 ? so.c0 * log(x) : 0.0) + (so.c1 != 0.0 ? so.c1 * log(1.0 - x) : 0.0)) + so.c2;
+      else { const DOp& op = F.scalar_ops[oi]; v = dist_eval<false>(FC_BETA, so.c0 + 1.0, so.c1 + 1.0, 0.0, x, 0, qnan, op.lgc, qnan).lp; }
+    }
+    a_prior += v;
+  }
+  lp[0] = 0.0 + a_prior; lp[1] = 0.0 + a_lik; lp[2] = 0.0 + a_fac;
   for (int pi = 0; pi < F.n_plates; pi++) {
     const FPlate fp = F.plates[pi];
     const DOp& op = F.ops[fp.op];
@@ -822,32 +862,40 @@ __device__ __forceinline__ void fused_eval(const FusedProg& F, const uint8_t* __
         const bool x_f64 = ob.value_col.dtype == FC_COL_F64;
         const double* __restrict__ lxc = fp.m1 == FM_LATENT_X ? (const double*)ob.p[0].t[fp.mt1].col.ptr : nullptr;
         double sl = 0.0;
-        if (F.L.zw == 1 && (z0 & 15) == 0 && x_f64 && !lxc) {
-          // the hot loop of BASELINE configs[3]: per element 2 byte ops, the branch selects and 6 FP64 instructions
+        const int nfull = (F.L.zw == 1 && (z0 & 15) == 0 && x_f64 && !lxc) ? (fp.n & ~15) : 0;
+        int n1 = 0;
+        unsigned other = 0;
+        if (nfull) {
+          // the hot loop of BASELINE configs[3]: 16 sites per 16-byte load. The observation term costs the
+          // branch selects and 5 FP64 instructions per element; the discrete prior is a population count
+          // (n0 ln p0 + n1 ln p1 instead of 80 sequential adds of the same two values).
           const double ma = S.base0 + S.va0, mb = S.base0 + S.vb0;
           const double ia = S.inv_a, ib = fp.ss ? S.inv_b : S.inv_a, ca = S.c_a, cb = fp.ss ? S.c_b : S.c_a;
-          for (int i0 = 0; i0 < fp.n; i0 += 16) {
+          for (int i0 = 0; i0 < nfull; i0 += 16) {
             const uint4 v = *(const uint4*)(zrec + z0 + i0);
             const unsigned wv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
+            for (int k = 0; k < 4; k++) { n1 += __popc(wv[k] & 0x01010101u); other |= wv[k] & 0xfefefefeu; }
+#pragma unroll
             for (int b = 0; b < 16; b++) {
-              const int i = i0 + b;
-              if (i < fp.n) {
-                const unsigned zi = (wv[b >> 2] >> ((b & 3) * 8)) & 0xffu;
-                const bool one = zi != 0;
-                s += zi == 0 ? tv0 : (zi == 1 ? tv1 : tv2);
-                const double z = (__ldg(xs + i) - (one ? mb : ma)) * (one ? ib : ia);
-                sl += fma(-0.5 * z, z, one ? cb : ca);
-              }
+              const bool one = ((wv[b >> 2] >> ((b & 3) * 8)) & 0xffu) != 0;
+              const double z = (__ldg(xs + i0 + b) - (one ? mb : ma)) * (one ? ib : ia);
+              sl += fma(-0.5 * z, z, one ? cb : ca);
             }
           }
-        } else {
-          for (int i = 0; i < fp.n; i++) {
-            const int zi = (int)za(z0 + i);
-            s += zi == 0 ? tv0 : (zi == 1 ? tv1 : tv2);
-            const double x = x_f64 ? __ldg(xs + i) : dcol_f64(ob.value_col, i);
-            sl += normal_elem(S, fp, zi != 0, zi != 0, 0.0, lxc ? __ldg(lxc + i) : 0.0, x);
+          if (other) {  // a byte >= 2: out of range for [p, 1-p] (distribution.rs:785-791), `true` for a bool
+            s = 0.0;
+            for (int i = 0; i < nfull; i++) { const int zi = (int)za(z0 + i); s += zi == 0 ? tv0 : (zi == 1 ? tv1 : tv2); }
+          } else {
+            const int n0 = nfull - n1;
+            s = (n0 ? (double)n0 * tv0 : 0.0) + (n1 ? (double)n1 * tv1 : 0.0);
           }
+        }
+        for (int i = nfull; i < fp.n; i++) {
+          const int zi = (int)za(z0 + i);
+          s += zi == 0 ? tv0 : (zi == 1 ? tv1 : tv2);
+          const double x = x_f64 ? __ldg(xs + i) : dcol_f64(ob.value_col, i);
+          sl += normal_elem(S, fp, zi != 0, zi != 0, 0.0, lxc ? __ldg(lxc + i) : 0.0, x);
         }
         lp[0] += s;
         lp[1] += (sl == sl) ? sl : d_neg_inf();
@@ -895,23 +943,34 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       const double p0 = chain_const_param(op, 0, q, true);
       const bool bern = op.dist == FC_BERNOULLI;
       const int z0 = (int)op.dslot0, n = (int)op.plate_len;
-      if ((z0 & 15) == 0) {  // 16 sites per store (byte stores from 32 lanes would be 32 partial-sector writes each)
-        for (int i0 = 0; i0 < n; i0 += 16) {
-          unsigned wv[4] = {0u, 0u, 0u, 0u};
-#pragma unroll
-          for (int b = 0; b < 16; b++)
-            if (i0 + b < n) {
-              const bool lt = rng.uniform() < p0;
-              const unsigned zi = bern ? (lt ? 1u : 0u) : (lt ? 0u : 1u);  // dist_sample: Bernoulli u < p; Categorical [p, 1-p] CDF search
-              wv[b >> 2] |= zi << ((b & 3) * 8);
-            }
-          *(uint4*)(zrec + z0 + i0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);  // the record's z section is padded to 16 bytes
-        }
-      } else {
-        for (int i = 0; i < n; i++) {
+      // Uniforms come in pairs from one Philox block (DevRng::uniform's own order: a, then the spare b); the
+      // loops are kept rolled -- 16 inlined draws per trip thrashed the instruction cache (ncu: 18 of 22
+      // stall samples "no instruction", 31 ms) -- and 8 sites are packed per 8-byte store.
+      int i = 0;
+      if ((z0 & 7) == 0) {
+        if (rng.has_spare && n > 0) {  // an odd number of draws so far: realign to whole blocks through the byte path
           const bool lt = rng.uniform() < p0;
-          zrec[z0 + i] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));
+          zrec[z0] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));
+          i = 1;
+          for (; i < n && (i & 7); i++) { const bool l2 = rng.uniform() < p0; zrec[z0 + i] = (uint8_t)(bern ? (l2 ? 1 : 0) : (l2 ? 0 : 1)); }
         }
+#pragma unroll 1
+        for (; i + 8 <= n && !rng.has_spare; i += 8) {
+          unsigned long long wd = 0;
+#pragma unroll 1
+          for (int b = 0; b < 8; b += 2) {
+            double ua, ub;
+            rng.ph.uniform2(rng.lo++, rng.hi, ua, ub);
+            const unsigned long long za_ = bern ? (ua < p0 ? 1u : 0u) : (ua < p0 ? 0u : 1u), zb_ = bern ? (ub < p0 ? 1u : 0u) : (ub < p0 ? 0u : 1u);  // Bernoulli u < p; Categorical [p, 1-p] CDF search
+            wd |= (za_ << (8 * b)) | (zb_ << (8 * b + 8));
+          }
+          *(unsigned long long*)(zrec + z0 + i) = wd;
+        }
+      }
+#pragma unroll 1
+      for (; i < n; i++) {
+        const bool lt = rng.uniform() < p0;
+        zrec[z0 + i] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));
       }
     }
   }
@@ -1131,6 +1190,7 @@ struct fc_smc_session {
   // fused evaluator
   bool fused = false;
   fc::DevBuf<fc::FPlate> fplates;
+  fc::DevBuf<fc::SOp> sops;
   fc::FusedProg F;
   // generic engine: [row][particle] copies of the records (valid flags say which are current)
   fc::MoveEngine eng;
@@ -1188,9 +1248,10 @@ static int nb_blocks(int64_t n) {
 // phase; "smc_generic" = run every program on the generic scoring engine instead of the fused kernels
 static int g_nb_plain = -1, g_smc_generic = -1, g_smc_timing = 0;
 static bool nb_plain() {
-  if (g_nb_plain < 0) g_nb_plain = getenv("FC_NB_PLAIN") != nullptr;
-  return g_nb_plain != 0;
+  if (g_nb_plain < 0) g_nb_plain = getenv("FC_NB_PLAIN") ? atoi(getenv("FC_NB_PLAIN")) : 0;
+  return g_nb_plain == 1;
 }
+static int nb_mode() { nb_plain(); return g_nb_plain; }
 static bool smc_generic() {
   if (g_smc_generic < 0) g_smc_generic = getenv("FC_SMC_GENERIC") != nullptr;
   return g_smc_generic != 0;
@@ -1231,7 +1292,7 @@ static int32_t comm_check(fc_smc_session* S) {  // after a stream synchronisatio
 static void bisect_init(Bisect& hb, double beta, double target, double n_total, double guess) {
   memset(&hb, 0, sizeof(hb));
   hb.beta = beta; hb.lo = beta; hb.hi = 1.0; hb.a = beta; hb.b = 1.0; hb.mid = 1.0; hb.target = target; hb.n = n_total;
-  hb.guess = guess; hb.plain = nb_plain() ? 1 : 0;
+  hb.guess = guess; hb.plain = nb_mode();
 }
 static int32_t next_beta_uniform(cudaStream_t st, const Comm& cm, double lwc, const double* ll, int64_t n, double n_total, double beta, double target_ess, double guess,
                                  Bisect* d_bis, double* d_part, uint64_t* launches, uint64_t* evals, double* out) {
@@ -1242,7 +1303,7 @@ static int32_t next_beta_uniform(cudaStream_t st, const Comm& cm, double lwc, co
   k_nb_prepass<<<nb, NB_THREADS, 0, st>>>(ll, n, d_bis, d_part, cm);
   int launched = 1;
   // a batch of evaluations (launches after the search has finished return at once), one read-back per batch
-  int batch = hb.plain ? 58 : 30;
+  int batch = hb.plain == 1 ? 58 : (hb.plain == 2 ? 30 : 12);
   for (int round = 0; round < 8 && !hb.done; round++) {
     for (int it = 0; it < batch; it++) k_nb_eval_uni<<<nb, NB_THREADS, 0, st>>>(lwc, ll, d_bis, d_part, n, 0, 0.0, cm);
     launched += batch;
@@ -1773,7 +1834,38 @@ static int32_t smc_create_impl(fc_program* p, const fc_smc_config* cfg, uint64_t
     FC_CUDA(S->fplates.reserve(std::max<size_t>(1, fpl.size())));
     if (!fpl.empty()) FC_CUDA(cudaMemcpyAsync(S->fplates.p, fpl.data(), fpl.size() * sizeof(FPlate), cudaMemcpyHostToDevice, st));
     FC_CUDA(cudaStreamSynchronize(st));
+    // compile the scalar ops
+    std::vector<SOp> so(p->scalar_ops.size());
+    for (size_t i = 0; i < so.size(); i++) {
+      const DOp& op = p->scalar_ops[i];
+      SOp& o = so[i];
+      memset(&o, 0, sizeof(o));
+      o.kind = SO_GENERIC;
+      if (op.kind == FC_OP_FACTOR) { o.kind = SO_FACTOR; o.c0 = op.value; continue; }
+      if (op.kind != FC_OP_SAMPLE || !op.cont) continue;
+      auto cparam = [&](int j, double& v) -> bool {  // a constant parameter with the identity link
+        if (j >= op.n_params || op.p[j].link != FC_LINK_IDENTITY) return false;
+        double acc = 0.0;
+        bool first = true;
+        for (int t = 0; t < 3; t++) {
+          if (op.p[j].t[t].kind == FC_TERM_NONE) continue;
+          if (op.p[j].t[t].kind != FC_TERM_CONST) return false;
+          acc = first ? op.p[j].t[t].c : acc + op.p[j].t[t].c;
+          first = false;
+        }
+        v = acc;
+        return !first && std::isfinite(acc);
+      };
+      double a, b;
+      o.row = p->crow[op.cslot0];
+      if (op.dist == FC_NORMAL && cparam(0, a) && cparam(1, b) && b > 0.0) { o.kind = SO_NORMAL_CC; o.c0 = a; o.c1 = 1.0 / b; o.c2 = -std::log(b) - 0.5 * FC_LN_2PI; }
+      else if (op.dist == FC_GAMMA && cparam(0, a) && cparam(1, b) && a > 0.0 && b > 0.0) { o.kind = SO_GAMMA_CC; o.c0 = a - 1.0; o.c1 = b; o.c2 = a * std::log(b) - std::lgamma(a); }
+      else if (op.dist == FC_BETA && cparam(0, a) && cparam(1, b) && a > 0.0 && b > 0.0) { o.kind = SO_BETA_CC; o.c0 = a - 1.0; o.c1 = b - 1.0; o.c2 = -(std::lgamma(a) + std::lgamma(b) - std::lgamma(a + b)); }
+    }
+    FC_CUDA(S->sops.reserve(std::max<size_t>(1, so.size())));
+    if (!so.empty()) FC_CUDA(cudaMemcpy(S->sops.p, so.data(), so.size() * sizeof(SOp), cudaMemcpyHostToDevice));
     FusedProg& F = S->F;
+    F.sops = S->sops.p;
     F.ops = p->d_all_ops.p; F.scalar_ops = p->d_scalar_ops.p; F.plates = S->fplates.p; F.crow = p->d_crow.p; F.nodes = p->d_expr_nodes.p;
     F.n_ops = (int32_t)p->all_ops.size(); F.n_scalar = (int32_t)p->scalar_ops.size(); F.n_plates = (int32_t)fpl.size(); F._pad = 0; F.L = S->L;
   }
@@ -2036,7 +2128,7 @@ int32_t fc_smc_slot_range(int32_t method, uint64_t n_total, double u_raw, uint64
 // debug switches for A/B parity tests: "nb_plain" (1: next_beta evaluates every bisection midpoint, as the
 // reference does), "smc_generic" (1: sessions created afterwards use the generic scoring engine)
 int32_t fc_debug_set(const char* key, int32_t value) {
-  if (key && !strcmp(key, "nb_plain")) { fc::g_nb_plain = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "nb_plain")) { fc::g_nb_plain = (value >= 0 && value <= 2) ? value : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_generic")) { fc::g_smc_generic = value ? 1 : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_timing")) { fc::g_smc_timing = value ? 1 : 0; return FC_OK; }
   fc::set_error("unknown debug key");
