@@ -132,7 +132,7 @@ struct ScanCtl {
   long long win;          // window policy
   unsigned cnt_a, cnt_b;  // "last CTA" counters
   int serial;             // 1: the running sum became non-finite -> finish with the sequential loop
-  int _pad;
+  int round;              // rounds started (tags the look-back descriptors)
 };
 // Scores C chains resident on the device. q [d_cont][C] (sorted rows), qd [d_disc][C].
 // d_lp3 [3][C] (prior, lik, factors), d_total [C]; d_grad [d_cont][C] or nullptr (value only).

@@ -99,14 +99,17 @@ int32_t dev_log_sum_exp(const double* d_x, int64_t n, double* d_scratch, double*
 // ---------------------------------------------------------------------------------------------
 // exact sequentially-rounded prefix sums
 // ---------------------------------------------------------------------------------------------
-#define SAT_INC (1LL << 61)
+// increments are counted in ulps of the binade: a single one is < 2^53, the distance to the binade top
+// is <= 2^53, so everything >= 2^55 means "has left the binade" and sums saturate there (SAT_INC is even:
+// a saturated left operand picks b.e and stays saturated). 56 bits leave room for the look-back tags.
+#define SAT_INC (1LL << 55)
 struct Inc2 { long long e, o; };
 
-__device__ __forceinline__ long long sat_add(long long a, long long b) { return (a >= SAT_INC || b >= SAT_INC || a + b >= SAT_INC) ? SAT_INC : a + b; }
+__device__ __forceinline__ long long sat_add(long long a, long long b) { const long long s = a + b; return s < SAT_INC ? s : SAT_INC; }  // a, b in [0, SAT_INC]
 __device__ __forceinline__ Inc2 combine(const Inc2& a, const Inc2& b) {
   Inc2 r;
-  r.e = a.e >= SAT_INC ? SAT_INC : sat_add(a.e, (a.e & 1) ? b.o : b.e);
-  r.o = a.o >= SAT_INC ? SAT_INC : sat_add(a.o, (a.o & 1) ? b.e : b.o);
+  r.e = sat_add(a.e, (a.e & 1) ? b.o : b.e);
+  r.o = sat_add(a.o, (a.o & 1) ? b.e : b.o);
   return r;
 }
 // base = bottom of the binade (0 for the subnormal/first-normal region), U = its ulp,
@@ -158,13 +161,13 @@ __device__ __forceinline__ Inc2 block_exclusive_scan(Inc2 v, Inc2* total) {
 }
 
 // ---- device-driven windows -------------------------------------------------------------------
-// One ROUND handles the window [k0, k0 + len) of the current binade with two launches; everything a
+// One ROUND handles the window [k0, k0 + len) of the current binade with ONE launch; everything a
 // round needs (k0, the running sum s0, the window policy) lives in a control block on the device, so
 // the host enqueues a batch of rounds back to back and reads the block once. (Round 1 of this design
 // was host-driven: ~27 windows x (4 launches + a blocking copy) = 2.1 ms per resample at n = 2^24.)
-//   k_scan_round_a  per-tile aggregates of the window; the last CTA to finish scans them
-//   k_scan_round_b  per-element prefix sums -> S, first crossing; the last CTA does the one floating
-//                   add that changes binade and sets up the next window
+//   k_scan_round  one pass over the window (chained scan with look-back): per-element prefix sums -> S,
+//                 first crossing; the last CTA does the one floating add that changes binade and sets up
+//                 the next window
 struct Binade { double base, U, lim, T, iu1, iu2; long long need; int parity; };
 __device__ __forceinline__ Binade binade_of(double s0) {
   Binade b;
@@ -193,87 +196,113 @@ __global__ void k_scan_head(const double* __restrict__ w, int64_t n, double* __r
   S[0] = cum;
   const int64_t m = head < n ? head : n;
   for (int64_t i = 0; i < m; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
-  ctl->k0 = m; ctl->s0 = cum; ctl->first_cross = 0x7fffffffffffffffLL; ctl->cnt_a = 0; ctl->cnt_b = 0;
-  ctl->win = m > 0 ? 2 * m : 1024;
-  if (ctl->win < 1024) ctl->win = 1024;
+  ctl->k0 = m; ctl->s0 = cum; ctl->first_cross = 0x7fffffffffffffffLL; ctl->cnt_a = 0; ctl->cnt_b = 0; ctl->round = 1;
+  ctl->win = m > 0 ? 2 * m : 2048;
+  if (ctl->win < 2048) ctl->win = 2048;
   ctl->serial = (cum != cum || cum == d_pos_inf()) ? 1 : 0;
 }
-__global__ void __launch_bounds__(SC_THREADS) k_scan_round_a(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, Inc2* __restrict__ agg) {
-  const long long k0 = ctl->k0;
-  if (k0 >= n || ctl->serial) return;
-  const Binade B = binade_of(ctl->s0);
-  const int64_t len = min((long long)(n - k0), ctl->win);
-  const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
-  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
-    const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
-    Inc2 a; a.e = 0; a.o = 0;
-#pragma unroll
-    for (int i = 0; i < SC_ITEMS; i++) {
-      const int64_t j = t0 + i;
-      if (j < len) a = combine(a, make_inc(w[k0 + j], B.base, B.U, B.lim, B.iu1, B.iu2));
+// ---- one round = ONE pass over the window: chained scan with decoupled look-back (Merrill & Garland) ----
+// CTAs take tiles of 2048 weights in ticket order. A tile publishes its aggregate Inc2 pair, looks back
+// over its predecessors' descriptors (32 at a time, one per lane of warp 0) until it meets one that
+// already carries an inclusive prefix, publishes its own inclusive prefix and writes S. `combine` is
+// associative but not commutative: the farther tile is always the left operand. A descriptor is two
+// 64-bit words (the even-start and odd-start increments, 56 bits each) tagged with a 2-bit status and
+// the 6-bit round number, so descriptors of earlier rounds read as "not ready" without being cleared.
+#define LB_AGG 1ULL
+#define LB_INCL 2ULL
+#define LB_VAL_MASK ((1ULL << 56) - 1)
+__device__ __forceinline__ unsigned long long ld_relaxed_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_gpu(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void lb_publish(unsigned long long* desc, int t, unsigned long long status, unsigned long long epoch, const Inc2& v) {
+  const unsigned long long tag = (status << 62) | (epoch << 56);
+  st_relaxed_gpu(desc + 2 * t, tag | (unsigned long long)v.e);
+  st_relaxed_gpu(desc + 2 * t + 1, tag | (unsigned long long)v.o);
+}
+// exclusive prefix of tile t (t >= 1); all 32 lanes of one warp
+__device__ __forceinline__ Inc2 lb_lookback(const unsigned long long* desc, int t, unsigned long long epoch, int lane, int* give_up) {
+  Inc2 excl; excl.e = 0; excl.o = 0;
+  for (int j = t - 1;; j -= 32) {
+    const int idx = j - lane;
+    unsigned long long we = LB_INCL << 62, wo = LB_INCL << 62;  // tiles before the window: inclusive identity
+    if (idx >= 0) {
+      for (unsigned spin = 0;; spin++) {
+        we = ld_relaxed_gpu(desc + 2 * idx);
+        wo = ld_relaxed_gpu(desc + 2 * idx + 1);
+        const unsigned long long te = we >> 56, to = wo >> 56;
+        if (te == to && (te & 63ULL) == epoch && (te >> 6) != 0) break;  // both words of this round, same status
+        // a predecessor is always a running or finished CTA, so this wait ends; should it ever not, hand the
+        // rest of the scan to the sequential loop instead of hanging the device
+        if (spin > (1u << 27) || *(volatile int*)give_up) { *give_up = 1; we = wo = LB_INCL << 62; break; }
+      }
     }
-    Inc2 total;
-    block_exclusive_scan(a, &total);
-    if (threadIdx.x == 0) agg[t] = total;
-  }
-  __shared__ bool is_last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) is_last = atomicAdd(&ctl->cnt_a, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  // exclusive scan of the tile aggregates (written by other CTAs: read through L2)
-  __shared__ Inc2 carry;
-  if (threadIdx.x == 0) { carry.e = 0; carry.o = 0; ctl->cnt_a = 0; }
-  __syncthreads();
-  for (int base_i = 0; base_i < nt; base_i += SC_TILE) {
-    Inc2 items[SC_ITEMS];
-    Inc2 a; a.e = 0; a.o = 0;
+    Inc2 v; v.e = (long long)(we & LB_VAL_MASK); v.o = (long long)(wo & LB_VAL_MASK);
+    const unsigned incl = __ballot_sync(0xffffffffu, (we >> 62) == LB_INCL);
+    const int first = __ffs(incl) - 1;  // the nearest predecessor that already has an inclusive prefix
+    const int last = first >= 0 ? first : 31;
+    if (lane > last) { v.e = 0; v.o = 0; }
 #pragma unroll
-    for (int i = 0; i < SC_ITEMS; i++) {
-      const int j = base_i + threadIdx.x * SC_ITEMS + i;
-      items[i].e = 0; items[i].o = 0;
-      if (j < nt) { items[i].e = __ldcg(&agg[j].e); items[i].o = __ldcg(&agg[j].o); }
-      a = combine(a, items[i]);
+    for (int o = 1; o < 32; o <<= 1) {  // ordered reduction: lane 0 ends with v[last] o ... o v[1] o v[0]
+      Inc2 far;
+      far.e = __shfl_down_sync(0xffffffffu, v.e, o);
+      far.o = __shfl_down_sync(0xffffffffu, v.o, o);
+      if (lane + o < 32) v = combine(far, v);
     }
-    Inc2 total;
-    Inc2 pre = block_exclusive_scan(a, &total);
-    Inc2 run = combine(carry, pre);
-#pragma unroll
-    for (int i = 0; i < SC_ITEMS; i++) {
-      const int j = base_i + threadIdx.x * SC_ITEMS + i;
-      if (j < nt) agg[j] = run;
-      run = combine(run, items[i]);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) carry = combine(carry, total);
-    __syncthreads();
+    Inc2 part;
+    part.e = __shfl_sync(0xffffffffu, v.e, 0);
+    part.o = __shfl_sync(0xffffffffu, v.o, 0);
+    excl = combine(part, excl);
+    if (first >= 0) return excl;
   }
 }
-__global__ void __launch_bounds__(SC_THREADS) k_scan_round_b(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, const Inc2* __restrict__ agg, double* __restrict__ S) {
+__global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, unsigned long long* __restrict__ desc, double* __restrict__ S) {
   const long long k0 = ctl->k0;
   if (k0 >= n || ctl->serial) return;
   const double s0 = ctl->s0;
   const Binade B = binade_of(s0);
   const long long win = ctl->win;
+  const unsigned long long epoch = (unsigned long long)(ctl->round & 63);
   const int64_t len = min((long long)(n - k0), win);
   const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ int s_tile;
+  __shared__ Inc2 s_excl;
   long long cross = 0x7fffffffffffffffLL;
-  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+  for (;;) {
+    if (threadIdx.x == 0) s_tile = (int)atomicAdd(&ctl->cnt_a, 1u);
+    __syncthreads();
+    const int t = s_tile;
+    if (t >= nt) break;
     const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
+    double wv[SC_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SC_ITEMS; i++) wv[i] = t0 + i < len ? w[k0 + t0 + i] : 0.0;
     Inc2 items[SC_ITEMS];
     Inc2 a; a.e = 0; a.o = 0;
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
-      const int64_t j = t0 + i;
       items[i].e = 0; items[i].o = 0;
-      if (j < len) items[i] = make_inc(w[k0 + j], B.base, B.U, B.lim, B.iu1, B.iu2);
+      if (t0 + i < len) items[i] = make_inc(wv[i], B.base, B.U, B.lim, B.iu1, B.iu2);
       a = combine(a, items[i]);
     }
-    Inc2 pre = block_exclusive_scan(a, nullptr);
-    Inc2 tp; tp.e = __ldcg(&agg[t].e); tp.o = __ldcg(&agg[t].o);
-    Inc2 run = combine(tp, pre);
+    Inc2 total;
+    const Inc2 pre = block_exclusive_scan(a, &total);
+    if (warp == 0) {
+      if (lane == 0) lb_publish(desc, t, t == 0 ? LB_INCL : LB_AGG, epoch, total);
+      Inc2 ex; ex.e = 0; ex.o = 0;
+      if (t > 0) {
+        ex = lb_lookback(desc, t, epoch, lane, &ctl->serial);
+        if (lane == 0) lb_publish(desc, t, LB_INCL, epoch, combine(ex, total));
+      }
+      if (lane == 0) s_excl = ex;
+    }
+    __syncthreads();
+    Inc2 run = combine(s_excl, pre);
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
       const int64_t j = t0 + i;
@@ -287,16 +316,16 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_round_b(const double* __res
   }
   if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&ctl->first_cross, (unsigned long long)cross);
   __shared__ bool is_last;
-  __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) is_last = atomicAdd(&ctl->cnt_b, 1u) == gridDim.x - 1;
+  if (threadIdx.x == 0) { __threadfence(); is_last = atomicAdd(&ctl->cnt_b, 1u) == gridDim.x - 1; }
   __syncthreads();
   if (!is_last || threadIdx.x != 0) return;
   __threadfence();
   // advance: the one addition that changes binade is a plain IEEE add, as the reference does.
   // Window policy: for near-uniform weights the running sum needs about as many further elements to
-  // leave a binade as it took to reach it, so after a crossing at element k the next window is 2k; a
-  // window without a crossing doubles.
+  // leave a binade as it took to reach it, so after a crossing at element k the next window is 1.5 k
+  // (the expected distance plus a margin); a window without a crossing doubles.
+  if (*(volatile int*)&ctl->serial) { ctl->cnt_a = 0; ctl->cnt_b = 0; return; }  // k0 / s0 untouched: the sequential tail finishes from there
   const long long fc = *(volatile long long*)&ctl->first_cross;
   long long nk0; double ns0; bool crossed;
   if (fc < len) {
@@ -310,12 +339,13 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_round_b(const double* __res
     ns0 = __ldcg(&S[k0 + len]);
     crossed = !(ns0 < B.T);
   }
-  long long nw = crossed ? 2 * nk0 : 2 * win;
-  if (nw < 1024) nw = 1024;
+  long long nw = crossed ? nk0 + (nk0 >> 1) : 2 * win;
+  if (nw < 2048) nw = 2048;
   if (nw > (1LL << 26)) nw = 1LL << 26;
   ctl->k0 = nk0; ctl->s0 = ns0; ctl->win = nw;
   ctl->first_cross = 0x7fffffffffffffffLL;
-  ctl->cnt_b = 0;
+  ctl->cnt_a = 0; ctl->cnt_b = 0;
+  ctl->round += 1;
   if (ns0 != ns0 || ns0 == d_pos_inf()) ctl->serial = 1;  // cannot happen with finite weights unless the sum overflows
 }
 // correctness fallback (weights with negatives / non-finite values): one thread, the reference loop
@@ -346,15 +376,17 @@ static int scan_grid() {
 // enqueue `rounds` rounds (no host synchronisation); d_work: ScanCtl (64 B) followed by the tile aggregates
 int32_t scan_enqueue_rounds(const double* d_w, int64_t n, double* d_S, void* d_work, int rounds, cudaStream_t st, uint64_t* launches) {
   ScanCtl* ctl = (ScanCtl*)d_work;
-  Inc2* agg = (Inc2*)((char*)d_work + 64);
-  const int g = (int)std::max<int64_t>(1, std::min<int64_t>(scan_grid(), cdiv(n, SC_TILE)));
-  for (int r = 0; r < rounds; r++) {
-    k_scan_round_a<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, agg);
-    k_scan_round_b<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, agg, d_S);
+  unsigned long long* desc = (unsigned long long*)((char*)d_work + 64);
+  const int64_t tiles = cdiv(std::max<int64_t>(n, 1), SC_TILE);
+  const int g = (int)std::max<int64_t>(1, std::min<int64_t>(scan_grid(), tiles));
+  // descriptors carry the round number modulo 64: clear them once per batch of at most 32 rounds
+  for (int r0 = 0; r0 < rounds; r0 += 32) {
+    FC_CUDA(cudaMemsetAsync(desc, 0, (size_t)tiles * 16, st));
+    for (int r = r0; r < std::min(rounds, r0 + 32); r++) k_scan_round<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, desc, d_S);
   }
   k_scan_serial_tail<<<1, 1, 0, st>>>(d_w, n, d_S, ctl);
   FC_KERNEL_CHECK();
-  if (launches) *launches += 2 * rounds + 1;
+  if (launches) *launches += rounds + 1;
   return FC_OK;
 }
 // start a scan whose carry-in is already in ctl->s0 on the device (written by the host copy below or

@@ -992,7 +992,7 @@ struct MoveX {
   double beta;
   int32_t adapt;
 };
-__global__ void __launch_bounds__(128) k_smcx_move(const __grid_constant__ FusedProg F, Pop pop, const __grid_constant__ MoveX M) {
+__global__ void __launch_bounds__(128, 6) k_smcx_move(const __grid_constant__ FusedProg F, Pop pop, const __grid_constant__ MoveX M) {
   const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t dc = F.L.d_cont;
   const bool active = c < pop.n && dc > 0;
@@ -1077,16 +1077,38 @@ struct GatherArgs {
 #define GA_THREADS 256
 __global__ void __launch_bounds__(GA_THREADS) k_smcx_gather(const __grid_constant__ GatherArgs A) {
   __shared__ int64_t s_anc[GA_THREADS];
+  __shared__ int64_t s_range[2];
   const int64_t k = (int64_t)blockIdx.x * GA_THREADS + threadIdx.x;
+  const int64_t kbase = (int64_t)blockIdx.x * GA_THREADS;
   int64_t a = 0;
+  const bool walk = A.S && !A.wrap0;
+  double thr = 0.0;
+  if (walk && k < A.cnt) {
+    const int64_t j = A.j0 + k;
+    thr = (A.method == FC_RESAMPLE_STRATIFIED && A.us) ? __ddiv_rn(__dadd_rn((double)j, A.us[j]), A.n_total)
+                                                       : resample_threshold(A.method, A.n_total, A.u_raw, A.seed, A.tag, j);
+  }
+  if (walk) {
+    // thresholds are non-decreasing in the slot index, so every search of this CTA ends inside the range
+    // spanned by its first and last slot: two full searches, then 256 short ones that stay in L1 / L2
+    const int64_t klast = min(A.cnt, kbase + GA_THREADS) - 1;
+    if (k == kbase) s_range[0] = lower_bound_S(A.S, A.n_src, thr);
+    if (k == klast) s_range[1] = lower_bound_S(A.S, A.n_src, thr);
+    __syncthreads();
+  }
   if (k < A.cnt) {
     if (A.S) {
       if (A.wrap0) a = A.n_src - 1;
       else {
-        const int64_t j = A.j0 + k;
-        const double thr = (A.method == FC_RESAMPLE_STRATIFIED && A.us) ? __ddiv_rn(__dadd_rn((double)j, A.us[j]), A.n_total)
-                                                                        : resample_threshold(A.method, A.n_total, A.u_raw, A.seed, A.tag, j);
-        int64_t i = lower_bound_S(A.S, A.n_src, thr);
+        int64_t i;
+        if (thr == thr) {
+          int64_t lo = s_range[0], hi = min(s_range[1], A.n_src + 1);  // first i in [lo, hi] with S[i] >= thr
+          while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (A.S[mid] >= thr) hi = mid; else lo = mid + 1;
+          }
+          i = lo;
+        } else i = 0;
         if (i > A.n_src) i = A.n_src;
         a = (i == 0) ? A.n_src - 1 : (i - 1 < A.n_src - 1 ? i - 1 : A.n_src - 1);  // (i - 1).min(n - 1); i == 0 wraps
         if (!(thr == thr)) a = A.n_src - 1;
