@@ -46,7 +46,7 @@ class fc_param(C.Structure):
 
 class fc_op(C.Structure):
     _fields_ = [("kind", C.c_int32), ("dist", C.c_int32), ("value_type", C.c_int32), ("n_params", C.c_int32),
-                ("name", C.c_char_p), ("plate_len", C.c_int64), ("value_col", C.c_int32), ("_pad", C.c_int32),
+                ("name", C.c_char_p), ("plate_len", C.c_int64), ("value_col", C.c_int32), ("probs_col", C.c_int32),
                 ("value", C.c_double), ("param", fc_param * 3), ("expr_first", C.c_int32), ("expr_len", C.c_int32)]
 
 

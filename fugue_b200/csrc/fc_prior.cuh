@@ -71,14 +71,31 @@ struct DevRng {
     if (p >= 1.0) return (long long)n;
     bool flip = p > 0.5;
     double pp = flip ? 1.0 - p : p;
-    // inversion by sequential search on the pmf recurrence (expected O(n p) steps)
-    double qq = 1.0 - pp, s = pp / qq, f = pow(qq, (double)n), u = uniform();
+    const double qq = 1.0 - pp, s = pp / qq, u0 = uniform();
     unsigned long long k = 0;
-    while (u > f && k < n) {
-      u -= f;
-      k++;
-      f *= s * (double)(n - k + 1) / (double)k;
-      if (f <= 0.0) break;
+    if ((double)n * pp < 30.0) {
+      // inversion by sequential search on the pmf recurrence from 0 (expected O(n p) steps; q^n >= e^-42 here)
+      double f = pow(qq, (double)n), u = u0;
+      while (u > f && k < n) {
+        u -= f;
+        k++;
+        f *= s * (double)(n - k + 1) / (double)k;
+        if (f <= 0.0) break;
+      }
+    } else {
+      // large n p: q^n underflows (n >= 1075 at p = 0.5 made every draw 1), so the search starts at the mode with
+      // the pmf evaluated in log space and walks outwards, alternating sides (expected O(sqrt(n p q)) steps)
+      const unsigned long long m = (unsigned long long)(((double)n + 1.0) * pp);
+      const double fm = exp(lgamma((double)n + 1.0) - lgamma((double)m + 1.0) - lgamma((double)(n - m) + 1.0) + (double)m * log(pp) + (double)(n - m) * log(qq));
+      double u = u0 - fm, fu = fm, fd = fm;
+      unsigned long long ku = m, kd = m;
+      k = m;
+      for (int it = 0; u > 0.0 && it < 4000000; it++) {
+        bool moved = false;
+        if (ku < n) { fu *= s * (double)(n - ku) / (double)(ku + 1); ku++; u -= fu; k = ku; moved = true; if (u <= 0.0) break; }
+        if (kd > 0) { fd *= (double)kd / (s * (double)(n - kd + 1)); kd--; u -= fd; k = kd; moved = true; }
+        if (!moved) { k = m; break; }
+      }
     }
     return (long long)(flip ? n - k : k);
   }

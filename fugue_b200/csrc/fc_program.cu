@@ -169,7 +169,17 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
     }
     if (op.dist < 0 || op.dist >= FC_N_DISTS) { set_error("op %zu: bad distribution id %d", i, op.dist); return FC_ERR_INVALID_ARGUMENT; }
     static const int np[FC_N_DISTS] = {2, 2, 2, 1, 1, 1, 2, 2, 2, 1, 3, 2, 2, 2, 1, 2, 2};
-    if (op.n_params != np[op.dist]) { set_error("op %zu: distribution %d takes %d parameters, got %d", i, op.dist, np[op.dist], op.n_params); return FC_ERR_INVALID_ARGUMENT; }
+    const bool kway = op.dist == FC_CATEGORICAL && op.n_params == 0;
+    if (kway) {  // Categorical::new(probs) (distribution.rs:679-713)
+      if (op.probs_col < 0 || (size_t)op.probs_col >= n_cols || cols[op.probs_col].dtype != FC_COL_F64 || cols[op.probs_col].width != 1) { set_error("op %zu: K-way Categorical needs an f64 vector column of probabilities", i); return FC_ERR_INVALID_ARGUMENT; }
+      const fc_column& pc = cols[op.probs_col];
+      if (pc.rows <= 0) { set_error("op %zu ('%s'): Probability vector cannot be empty", i, P->names[i].c_str()); return FC_ERR_INVALID_PROBABILITY; }
+      double sum = 0.0;
+      for (int64_t k = 0; k < pc.rows; k++) sum += ((const double*)pc.data)[k];
+      if (std::fabs(sum - 1.0) > 1e-6) { set_error("op %zu ('%s'): Probabilities must sum to 1.0 (sum %.6f)", i, P->names[i].c_str(), sum); return FC_ERR_INVALID_PROBABILITY; }
+      for (int64_t k = 0; k < pc.rows; k++) { double v = ((const double*)pc.data)[k]; if (!std::isfinite(v) || v < 0.0) { set_error("op %zu ('%s'): All probabilities must be non-negative and finite", i, P->names[i].c_str()); return FC_ERR_INVALID_PROBABILITY; } }
+    }
+    if (!kway && op.n_params != np[op.dist]) { set_error("op %zu: distribution %d takes %d parameters, got %d", i, op.dist, np[op.dist], op.n_params); return FC_ERR_INVALID_ARGUMENT; }
     if (!value_type_matches(op.dist, op.value_type)) { set_error("op %zu ('%s'): value type %d does not match distribution %d", i, P->names[i].c_str(), op.value_type, op.dist); return FC_ERR_TYPE_MISMATCH; }
     bool plate = op.kind == FC_OP_PLATE_SAMPLE || op.kind == FC_OP_PLATE_OBSERVE;
     if (plate && op.plate_len < 0) { set_error("op %zu: negative plate length", i); return FC_ERR_INVALID_ARGUMENT; }
@@ -353,6 +363,7 @@ static int32_t build(fc_program* P, const fc_op* ops, size_t n_ops, const fc_col
     }
     // normalisers of constant parameters (lgamma is ~200 FP64 instructions per call on the device;
     // C4 scores Beta(1,1) and two Gamma(1,1) priors for 2^24 particles per temper step)
+    if (op.dist == FC_CATEGORICAL && op.n_params == 0 && op.kind != FC_OP_FACTOR && op.kind != FC_OP_FACTOR_EXPR) { d.probs = (const double*)P->cols[op.probs_col].ptr; d.n_probs = (int32_t)P->cols[op.probs_col].rows; }
     d.lgc = std::nan("");
     d.lgc2 = std::nan("");
     {

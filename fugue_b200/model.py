@@ -89,8 +89,21 @@ class Bernoulli(_Prob):
 
 
 class Categorical(_Prob):
-    """Two-way Categorical([p, 1-p]) (examples/mixture_models.rs:94); param = p."""
+    """Categorical(p): the two-way form [p, 1-p] of examples/mixture_models.rs:94 (p may depend on
+    latents); Categorical([p0, .., pK-1]): K-way with constant probabilities (Categorical::new,
+    distribution.rs:679-713: non-empty, finite, non-negative, sum within 1e-6 of 1 -> ErrorCode 102)."""
     name, value_type = "Categorical", "usize"
+
+    def __init__(self, p):
+        if isinstance(p, (list, tuple, np.ndarray)):
+            self.probs = np.ascontiguousarray(p, dtype=np.float64).reshape(-1)
+            self.params = []
+            self._need(self.probs.size > 0, 102, "Probability vector cannot be empty")
+            self._need(abs(float(self.probs.sum()) - 1.0) <= 1e-6, 102, "Probabilities must sum to 1.0")
+            self._need(bool(np.all(np.isfinite(self.probs) & (self.probs >= 0.0))), 102, "All probabilities must be non-negative and finite")
+        else:
+            self.probs = None
+            super().__init__(p)
 
     def validate(self):
         self._prob(0)
@@ -202,6 +215,8 @@ class ModelBuilder:
     # ---- ops ----
     def _op(self, kind, dist, name, plate_len=0, value_col=-1, value=0.0):
         d = dict(kind=kind, dist=dist, name=name, plate_len=plate_len, value_col=value_col, value=value)
+        if getattr(dist, "probs", None) is not None:  # K-way Categorical: the probabilities travel as a data column
+            d["probs_col"] = self.data(dist.probs).cid
         self.ops.append(d)
         return len(self.ops) - 1
 
@@ -254,6 +269,7 @@ class ModelBuilder:
                 node_list.extend(d["expr"].nodes)
             if dist is None:
                 continue
+            o.probs_col = d.get("probs_col", 0)
             o.dist = _ir.DIST_IDS[dist.name]
             o.value_type = _VT[dist.value_type]
             o.n_params = len(dist.params)

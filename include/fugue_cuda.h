@@ -85,12 +85,15 @@ typedef struct fc_op {
   int32_t kind;        /* FC_OP_*                                                     */
   int32_t dist;        /* FC_NORMAL.. ; ignored for FACTOR                            */
   int32_t value_type;  /* FC_T_*                                                      */
-  int32_t n_params;    /* 1..3 (Categorical: params = probs of category 0; 2-way)     */
+  int32_t n_params;    /* 1..3. Categorical: 1 = the two-way form [p, 1-p] (p may depend on
+                          latents); 0 = K-way with CONSTANT probabilities taken from the
+                          f64 vector column `probs_col` (Categorical::new(vec), validated as
+                          src/core/distribution.rs:679-713)                            */
   const char* name;    /* address base; scalar ops use addr!(name), plates addr!(name,i)
                           => "name#i" (src/core/address.rs:208-223)                   */
   int64_t plate_len;   /* PLATE_*: number of elements; else 0                         */
   int32_t value_col;   /* OBSERVE/PLATE_OBSERVE: data column holding the value(s)     */
-  int32_t _pad;
+  int32_t probs_col;   /* K-way Categorical (n_params == 0): column of the K probabilities */
   double  value;       /* OBSERVE (scalar): observed value; FACTOR: log-weight;
                           FACTOR_EXPR: 1.0 = a NaN result counts as -inf (the playground's
                           policy, crates/fugue-wasm/src/dsl.rs:922-926), 0.0 = added as is */

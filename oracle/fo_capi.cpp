@@ -3,7 +3,7 @@
 // may load this library.
 #include <atomic>
 #include <thread>
-#include "fo_infer.hpp"
+#include "fo_smc.hpp"
 
 using namespace fo;
 
@@ -120,6 +120,63 @@ double fo_classic_rhat(const double* draws, size_t S, size_t C) { return r_hat(t
 double fo_ess_multichain(const double* draws, size_t S, size_t C) {
   if (C == 0) return 0.0;
   return ess_from_chains(to_chains(draws, S, C));
+}
+// ---- single-site MH / tempered SMC (fo_smc.hpp). State arrays are in SORTED site order (the C ABI's order). ----
+static State state_from_sorted(const Program& P, const double* q, const int64_t* qd) {
+  State s; s.q.resize(P.d_cont); s.qd.resize(P.d_disc);
+  for (int64_t k = 0; k < P.d_cont; k++) s.q[P.perm_c[k]] = q[k];
+  for (int64_t k = 0; k < P.d_disc; k++) s.qd[P.perm_d[k]] = qd[k];
+  return s;
+}
+static void state_to_sorted(const Program& P, const State& s, double* q, int64_t* qd) {
+  for (int64_t k = 0; k < P.d_cont; k++) q[k] = s.q[P.perm_c[k]];
+  for (int64_t k = 0; k < P.d_disc; k++) if (qd) qd[k] = s.qd[P.perm_d[k]];
+}
+int64_t fo_n_sites(void* p) { return (int64_t)all_sites(*(Program*)p).size(); }
+// single_site_mh_step on global site g (address order over ALL sample sites); out3 = {accept, log_alpha, lw_new}
+void fo_mh_step(void* p, double* q, int64_t* qd, double cur_lw, int64_t g, int kind, double scale, double z, double u, double lower, double upper,
+                double prior_x, int64_t prior_xi, double* out3) {
+  Program* P = (Program*)p;
+  State s = state_from_sorted(*P, q, qd);
+  auto sites = all_sites(*P);
+  MhStepOut o = single_site_mh_step(*P, s, cur_lw, sites[(size_t)g], kind, scale, z, u, lower, upper, prior_x, prior_xi);
+  state_to_sorted(*P, s, q, qd);
+  out3[0] = o.accept; out3[1] = o.log_alpha; out3[2] = o.lw_new;
+}
+// the automatic f64 proposal kind of global site g at this state (mh.rs:339-358); -1 for a discrete site
+int fo_mh_kind(void* p, const double* q, const int64_t* qd, int64_t g) {
+  Program* P = (Program*)p;
+  State s = state_from_sorted(*P, q, qd);
+  auto sites = all_sites(*P);
+  return sites[(size_t)g].cont ? f64_kind(*P, s, sites[(size_t)g]) : -1;
+}
+// tempered_single_site_mh on the k-th f64 site (sorted); out5 = {accept, log_alpha, log_prior, log_lik, log_factors} of the kept state
+void fo_tempered_step(void* p, double* q, int64_t* qd, int64_t k, double beta, double scale, double z, double u, double* out5) {
+  Program* P = (Program*)p;
+  State s = state_from_sorted(*P, q, qd);
+  auto fs = f64_sites(*P);
+  TemperedOut t = tempered_single_site_mh(*P, s, fs[(size_t)k], beta, scale, z, u);
+  state_to_sorted(*P, s, q, qd);
+  out5[0] = t.accept; out5[1] = t.log_alpha; out5[2] = t.score.log_prior; out5[3] = t.score.log_lik; out5[4] = t.score.log_factors;
+}
+void fo_normalize_particles(const double* log_w, size_t n, double* w) { normalize_particles(log_w, n, w); }
+// adaptive_smc (smc.rs:455-581). values [d_cont][n] / dvalues [d_disc][n] sorted rows, particle-minor; outputs may be null.
+// nthreads <= 1: one generator and one adaptation object threaded through all particles, as the reference does.
+int fo_adaptive_smc(void* p, size_t n, int method, double ess_threshold, uint64_t rejuvenation_steps, uint64_t seed, int nthreads, double* values,
+                    int64_t* dvalues, double* weight, double* log_weight, double* log_evidence, uint64_t* steps) {
+  Program* P = (Program*)p;
+  SmcOut o;
+  auto pf = [](size_t cnt, int nt, auto f) { par_for(cnt, nt, f); };
+  if (!adaptive_smc(*P, n, method, ess_threshold, rejuvenation_steps, seed, nthreads, pf, o)) return FC_ERR_UNSUPPORTED_OP;
+  for (size_t i = 0; i < n; i++) {
+    if (values) for (int64_t k = 0; k < P->d_cont; k++) values[(size_t)k * n + i] = o.particles[i].q[P->perm_c[k]];
+    if (dvalues) for (int64_t k = 0; k < P->d_disc; k++) dvalues[(size_t)k * n + i] = o.particles[i].qd[P->perm_d[k]];
+    if (weight) weight[i] = o.weight[i];
+    if (log_weight) log_weight[i] = o.log_w[i];
+  }
+  if (log_evidence) *log_evidence = o.log_evidence;
+  if (steps) *steps = o.steps;
+  return FC_OK;
 }
 int fo_max_threads() { unsigned n = std::thread::hardware_concurrency(); return n ? (int)n : 1; }
 }

@@ -226,7 +226,11 @@ inline Score score_program_order(const Program& P, const double* q, const int64_
       } else {
         if (cont) x = op.value; else xi = (int64_t)op.value;
       }
-      LpGrad g = dist_eval(op.dist, pv, x, xi);
+      LpGrad g;
+      if (op.dist == FC_CATEGORICAL && op.n_params == 0) {  // K-way, constant probabilities (distribution.rs:785-791)
+        const Column& pc = P.cols[op.probs_col];
+        g = LpGrad{(xi >= 0) ? categorical_lp((const double*)pc.data, (size_t)pc.rows, (uint64_t)xi) : NEG_INF, 0.0, {0.0, 0.0, 0.0}};
+      } else g = dist_eval(op.dist, pv, x, xi);
       if (is_sample) sc.log_prior += g.lp; else sc.log_lik += g.lp;
       if (dq) {
         if (is_sample && cont) dq[P.cslot0[oi] + i] += g.dx;

@@ -49,6 +49,14 @@ def lib():
         L.fo_next_beta.argtypes = [C.c_double, dp, dp, C.c_size_t, C.c_double]
         for n in ("fo_split_rhat", "fo_classic_rhat", "fo_ess_multichain"):
             getattr(L, n).argtypes = [dp, C.c_size_t, C.c_size_t]
+        L.fo_n_sites.argtypes = [C.c_void_p]
+        L.fo_n_sites.restype = C.c_int64
+        L.fo_mh_step.argtypes = [C.c_void_p, dp, ip, C.c_double, C.c_int64, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
+                                 C.c_double, C.c_int64, dp]
+        L.fo_mh_kind.argtypes = [C.c_void_p, dp, ip, C.c_int64]
+        L.fo_tempered_step.argtypes = [C.c_void_p, dp, ip, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_double, dp]
+        L.fo_normalize_particles.argtypes = [dp, C.c_size_t, dp]
+        L.fo_adaptive_smc.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.c_uint64, C.c_uint64, C.c_int, dp, ip, dp, dp, dp, C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -118,13 +126,56 @@ class OracleProgram:
         return a, a.ctypes.data_as(ip)
 
     def logp(self, q, qd=None, grad=False, nthreads=1):
-        q = f64(q).reshape(self.d_cont, -1)
-        Cn = q.shape[1]
+        if self.d_cont == 0:  # discrete-only program: the chain count comes from qd
+            Cn = np.asarray(qd).reshape(self.d_disc, -1).shape[1]
+            q = np.zeros((0, Cn))
+        else:
+            q = f64(q).reshape(self.d_cont, -1)
+            Cn = q.shape[1]
         a, qdp = self._qd(qd, Cn)
         lp, ll, lf = np.zeros(Cn), np.zeros(Cn), np.zeros(Cn)
         g = np.zeros_like(q) if grad else None
         lib().fo_logp(self.h, _d(q), qdp, Cn, _d(lp), _d(ll), _d(lf), _d(g) if grad else None, nthreads)
         return (lp, ll, lf, g) if grad else (lp, ll, lf)
+
+    # ---- single-site MH / tempered SMC with explicit randomness (oracle/fo_smc.hpp) ----
+    def _state(self, q, qd):
+        q = f64(q).reshape(self.d_cont).copy()
+        d = np.ascontiguousarray(qd if qd is not None else np.zeros(self.d_disc), dtype=np.int64).reshape(self.d_disc).copy()
+        return q, d
+
+    def n_sites(self):
+        return lib().fo_n_sites(self.h)
+
+    def mh_step(self, q, qd, cur_lw, g, z, u, scale=1.0, kind=-1, lower=0.0, upper=0.0, prior_x=0.0, prior_xi=0):
+        """single_site_mh_step (mh.rs:698-744) on global site g -> (q', qd', accept, log_alpha, lw')."""
+        q, d = self._state(q, qd)
+        out = np.zeros(3)
+        lib().fo_mh_step(self.h, _d(q), d.ctypes.data_as(ip), cur_lw, g, kind, scale, z, u, lower, upper, prior_x, prior_xi, _d(out))
+        return q, d, bool(out[0]), out[1], out[2]
+
+    def mh_kind(self, q, qd, g):
+        q, d = self._state(q, qd)
+        return lib().fo_mh_kind(self.h, _d(q), d.ctypes.data_as(ip), g)
+
+    def tempered_step(self, q, qd, k, beta, scale, z, u):
+        """tempered_single_site_mh (smc.rs:631-688) on the k-th f64 site -> (q', accept, log_alpha, (lp, ll, lf))."""
+        q, d = self._state(q, qd)
+        out = np.zeros(5)
+        lib().fo_tempered_step(self.h, _d(q), d.ctypes.data_as(ip), k, beta, scale, z, u, _d(out))
+        return q, bool(out[0]), out[1], out[2:5].copy()
+
+    def adaptive_smc(self, n, rejuvenation_steps=0, ess_threshold=0.5, method=1, seed=0, nthreads=1, values=True):
+        """adaptive_smc (smc.rs:455-581) -> dict(values, dvalues, weight, log_weight, log_evidence, steps)."""
+        v = np.zeros((self.d_cont, n)) if values else None
+        dv = np.zeros((self.d_disc, n), dtype=np.int64) if values else None
+        w, lw = np.zeros(n), np.zeros(n)
+        le, st = C.c_double(), C.c_uint64()
+        rc = lib().fo_adaptive_smc(self.h, n, method, ess_threshold, rejuvenation_steps, seed, nthreads, _d(v) if values else None,
+                                   dv.ctypes.data_as(ip) if values else None, _d(w), _d(lw), C.byref(le), C.byref(st))
+        if rc != 0:
+            raise _ir.FugueError(rc, "oracle adaptive_smc: a prior family that is not restated")
+        return dict(values=v, dvalues=dv, weight=w, log_weight=lw, log_evidence=le.value, steps=st.value)
 
     def grad_fd(self, q, qd=None, h=1e-5, nthreads=1):
         q = f64(q).reshape(self.d_cont, -1)
@@ -156,6 +207,13 @@ class OracleProgram:
         z = f64(z)
         a, qdp = self._qd(qd, 1)
         return lib().fo_find_reasonable_epsilon(self.h, qdp, _d(q), lj, _d(z), _d(m_inv), _d(mass_sqrt), grad_mode, h)
+
+
+def normalize_particles(log_w):
+    lw = f64(log_w)
+    w = np.zeros_like(lw)
+    lib().fo_normalize_particles(_d(lw), lw.size, _d(w))
+    return w
 
 
 def resample(method, w, us):

@@ -115,6 +115,26 @@ def test_c4_resampling_properties_at_two_to_the_24():
     assert S[-1] == np.cumsum(w)[-1]
 
 
+def test_c4_resampling_indices_array_equal_at_two_to_the_24():
+    """The WHOLE index array at the config's size against the sequential reference loop (oracle:
+    smc.rs:255-292), systematic and stratified, on heavy-tailed weights -- bit-exact, not properties."""
+    import oracle
+    from fugue_b200 import api
+    n = 1 << 24
+    rng = np.random.default_rng(9)
+    w = rng.gamma(0.25, 1.0, n)
+    w[rng.integers(0, n, n // 64)] = 0.0
+    w /= w.sum()
+    for u in (0.0, 0.37, 0.999999999):
+        assert np.array_equal(api.resample_indices(1, w, [u]), oracle.resample(1, w, [u]))
+    us = rng.random(n)
+    assert np.array_equal(api.resample_indices(2, w, us), oracle.resample(2, w, us))
+    # the weights an SMC step really sees: normalised exp of tempered log-likelihoods
+    lw = -0.5 * rng.chisquare(3.0, n) * 4.0
+    w2 = np.exp(lw - np.logaddexp.reduce(lw))
+    assert np.array_equal(api.resample_indices(1, w2, [0.61]), oracle.resample(1, w2, [0.61]))
+
+
 def test_c4_smc_full_population_consistent_with_small_run():
     from fugue_b200 import api
     m, _ = models.gaussian_mixture()
@@ -124,10 +144,16 @@ def test_c4_smc_full_population_consistent_with_small_run():
         pass
     big = S.result(values=False)
     S.close()
-    small = api.adaptive_smc(m, 1 << 18, cfg, seed=8)
+    smalls = [api.adaptive_smc(m, 1 << 18, cfg, seed=100 + k) for k in range(8)]
+    small = smalls[0]
     assert abs(big.weight.sum() - 1.0) < 1e-9
     # log-evidence estimates of this label-switching target with ONE rejuvenation sweep per step scatter
-    # by a few nats between seeds (80 discrete allocations per particle barely mix); consistency only
-    assert math.isfinite(big.log_evidence) and abs(big.log_evidence - small.log_evidence) < 8.0
+    # between seeds (80 discrete allocations per particle barely mix). The band is MEASURED: the spread of
+    # eight independent 2^18-particle runs; the 2^24 run must lie within 4 of their standard deviations
+    # (+ the Jensen bias of log Z-hat at the smaller size, about half their variance) of their mean.
+    le = np.array([r.log_evidence for r in smalls])
+    sd = le.std(ddof=1)
+    assert math.isfinite(big.log_evidence) and sd < 2.5, (le, sd)
+    assert abs(big.log_evidence - (le.mean() + 0.5 * sd * sd)) < 4.0 * sd + 0.5 * sd * sd + 0.25, (big.log_evidence, le, sd)
     assert big.n_temper_steps >= 5 and abs(big.n_temper_steps - small.n_temper_steps) <= 2
     assert (big.weight >= 0).all() and big.weight.max() < 1e-4
