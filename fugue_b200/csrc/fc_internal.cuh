@@ -133,6 +133,8 @@ struct ScanCtl {
   unsigned cnt_a, cnt_b;  // "last CTA" counters
   int serial;             // 1: the running sum became non-finite -> finish with the sequential loop
   int round;              // rounds started (tags the look-back descriptors)
+  double c0;              // the carry-in the scan started from (mean weight so far = (s0 - c0) / k0)
+  double w_mean;          // caller's hint of the mean weight (0: none): sizes the first window of a scan that skips the head
 };
 // Scores C chains resident on the device. q [d_cont][C] (sorted rows), qd [d_disc][C].
 // d_lp3 [3][C] (prior, lik, factors), d_total [C]; d_grad [d_cont][C] or nullptr (value only).

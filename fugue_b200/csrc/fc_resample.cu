@@ -191,14 +191,26 @@ __device__ __forceinline__ Binade binade_of(double s0) {
 
 // the first few hundred elements cross a binade every doubling of the count: one thread walks them
 // exactly as the reference does (the loads do not depend on the add chain, so this is ~2 us)
+// window from the mean weight seen so far: the elements the running sum still needs to leave its binade,
+// plus a quarter (a window without a crossing doubles)
+__device__ __forceinline__ long long scan_window(double s0, double mean) {
+  const Binade B = binade_of(s0);
+  double e = mean > 0.0 ? 1.25 * (B.T - s0) / mean : 2048.0;
+  if (!(e >= 2048.0)) e = 2048.0;
+  if (e > 67108864.0) e = 67108864.0;
+  return (long long)e;
+}
 __global__ void k_scan_head(const double* __restrict__ w, int64_t n, double* __restrict__ S, ScanCtl* __restrict__ ctl, int64_t head) {
   double cum = ctl->s0;
   S[0] = cum;
+  ctl->c0 = cum;
+  // a scan that continues a running sum well inside a binade (a later rank of a sharded population) skips the
+  // sequential head: its first window is sized from the caller's mean-weight hint
+  if (cum > 0.0 && ctl->w_mean > 0.0) head = 0;
   const int64_t m = head < n ? head : n;
   for (int64_t i = 0; i < m; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
   ctl->k0 = m; ctl->s0 = cum; ctl->first_cross = 0x7fffffffffffffffLL; ctl->cnt_a = 0; ctl->cnt_b = 0; ctl->round = 1;
-  ctl->win = m > 0 ? 2 * m : 2048;
-  if (ctl->win < 2048) ctl->win = 2048;
+  ctl->win = scan_window(cum, m > 0 ? (cum - ctl->c0) / (double)m : ctl->w_mean);
   ctl->serial = (cum != cum || cum == d_pos_inf()) ? 1 : 0;
 }
 // ---- one round = ONE pass over the window: chained scan with decoupled look-back (Merrill & Garland) ----
@@ -322,9 +334,8 @@ __global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __re
   if (!is_last || threadIdx.x != 0) return;
   __threadfence();
   // advance: the one addition that changes binade is a plain IEEE add, as the reference does.
-  // Window policy: for near-uniform weights the running sum needs about as many further elements to
-  // leave a binade as it took to reach it, so after a crossing at element k the next window is 1.5 k
-  // (the expected distance plus a margin); a window without a crossing doubles.
+  // Window policy: after a crossing the next window is the number of elements the sum still needs to leave
+  // the new binade at the mean weight seen so far, plus a quarter; a window without a crossing doubles.
   if (*(volatile int*)&ctl->serial) { ctl->cnt_a = 0; ctl->cnt_b = 0; return; }  // k0 / s0 untouched: the sequential tail finishes from there
   const long long fc = *(volatile long long*)&ctl->first_cross;
   long long nk0; double ns0; bool crossed;
@@ -339,7 +350,7 @@ __global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __re
     ns0 = __ldcg(&S[k0 + len]);
     crossed = !(ns0 < B.T);
   }
-  long long nw = crossed ? nk0 + (nk0 >> 1) : 2 * win;
+  long long nw = crossed ? scan_window(ns0, (ns0 - ctl->c0) / (double)nk0) : 2 * win;
   if (nw < 2048) nw = 2048;
   if (nw > (1LL << 26)) nw = 1LL << 26;
   ctl->k0 = nk0; ctl->s0 = ns0; ctl->win = nw;

@@ -692,10 +692,11 @@ __global__ void k_chain_wait(const __grid_constant__ Comm cm, unsigned long long
   }
   ctl->s0 = carry;
 }
-__global__ void k_chain_publish(const __grid_constant__ Comm cm, unsigned long long rs, const ScanCtl* __restrict__ ctl) {
+__global__ void k_chain_publish(const __grid_constant__ Comm cm, unsigned long long rs, const ScanCtl* __restrict__ ctl, int64_t n) {
   const int t = threadIdx.x, par = (int)(rs & 1);
-  if (t >= cm.world) return;
+  if (t >= cm.world || ctl->k0 < n) return;  // not complete yet: the host enqueues more rounds, then publishes
   MBox* d = cm.box[t];
+  if (ld_acquire_sys(&cm.box[cm.rank]->end_flag[par][cm.rank]) >= rs) return;  // already published
   *(volatile double*)&d->end_val[par][cm.rank] = ctl->s0;
   __threadfence_system();
   st_release_sys(&d->end_flag[par][cm.rank], rs);
@@ -1569,15 +1570,17 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
     FC_CUDA(S->work.reserve(scan_work_bytes(n)));
     ScanCtl hs;
     memset(&hs, 0, sizeof(hs));
+    hs.w_mean = 1.0 / (double)N;  // the weights are normalised over the whole population
     FC_CUDA(cudaMemcpyAsync(S->work.p, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
     k_chain_wait<<<1, 1, 0, st>>>(S->cm, S->resamples, (ScanCtl*)S->work.p);
     FC_TRY(scan_enqueue_head(S->w.p, n, S->S.p, S->work.p, st, &P->n_kernel_launches));
     FC_TRY(scan_enqueue_rounds(S->w.p, n, S->S.p, S->work.p, S->rank == 0 ? scan_expected_rounds(n) : 3, st, &P->n_kernel_launches));
+    if (W > 1) k_chain_publish<<<1, 32, 0, st>>>(S->cm, S->resamples, (const ScanCtl*)S->work.p, n);  // publishes iff the scan is complete
     FC_TRY(scan_finish(S->w.p, n, S->S.p, S->work.p, st, &P->n_kernel_launches, nullptr));
     P->n_kernel_launches += 1;
     double ends[MB_MAXW] = {0.0};
     if (W > 1) {
-      k_chain_publish<<<1, 32, 0, st>>>(S->cm, S->resamples, (const ScanCtl*)S->work.p);
+      k_chain_publish<<<1, 32, 0, st>>>(S->cm, S->resamples, (const ScanCtl*)S->work.p, n);  // no-op if the first one already did
       k_chain_collect<<<1, 32, 0, st>>>(S->cm, S->resamples, S->ends.p);
       FC_KERNEL_CHECK();
       P->n_kernel_launches += 2;
