@@ -384,8 +384,8 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
               double pc = fmin(fmax(p, lnk_lo), lnk_hi);
               lp = fast_log_tab(yb[mt] ? pc : 1.0 - pc, s_log_tab);
             }
-            if (GRAD) w = inside ? (yb[mt] ? (1.0 - p) : -p) : 0.0;  // NaN p: `inside` is false => w = 0
-            if (VAL && sarg != sarg) { lp = d_neg_inf(); w = 0.0; }  // NaN eta => Bernoulli(NaN) => -inf
+            if (GRAD) w = inside ? (yb[mt] ? (1.0 - p) : -p) : (p - p);  // clamped: 0; NaN eta: NaN force => divergent (hmc.rs:384-386)
+            if (VAL && sarg != sarg) lp = d_neg_inf();  // NaN eta => Bernoulli(NaN) => -inf
           } else if (MODE == GLM_POISSON_ID) {
             // distribution.rs:1237-1258 with lambda = eta. Branch-light: the fast path is evaluated
             // unconditionally on a clamped lambda, the reference's guards are selects, and only an
@@ -400,10 +400,10 @@ __global__ void __launch_bounds__(DN_THREADS(NT), GRAD ? 1 : 2) k_dense_glm(cons
             if (VAL) lp = kf * fast_log_tab(lamc, s_log_tab) - lam;  // - lgamma(k+1): lgam_total, epilogue
             if (GRAD) w = (!VAL || d_fin(lp)) ? kf * fast_rcp(lamc) - 1.0 : 0.0;  // ok => lp is finite (lgamma column is)
             if (!ok) {
-              lp = d_neg_inf(); w = 0.0;
+              lp = d_neg_inf(); w = __longlong_as_double(0x7ff8000000000000LL);  // outside the support: no gradient
               if (lam > 0.0 && d_fin(lam) && kf >= 0.0) {  // tiny / huge lambda: exact guards via the library functions
                 lp = (lam > 700.0 && kf == 0.0) ? -lam : kf * log(lam) - lam;
-                if (GRAD && d_fin(lp)) w = kf / lam - 1.0;
+                w = (GRAD && d_fin(lp)) ? kf / lam - 1.0 : w;
               }
             }
           } else {

@@ -244,6 +244,9 @@ __device__ __forceinline__ DistOut dist_eval(int dist, double P0, double P1, dou
     } break;
     default: break;
   }
+  // A point outside the support (or an invalid parameter) has no gradient: the reference's finite-difference force
+  // is NaN there, which marks the trajectory divergent (hmc.rs:304-329, 384-386). A zero force would let it glide on.
+  if (GRAD && g.lp == d_neg_inf()) g.dx = g.dp0 = g.dp1 = g.dp2 = __longlong_as_double(0x7ff8000000000000LL);
   return g;
 }
 

@@ -435,7 +435,14 @@ struct Hmc {
       }
       S->frozen = true;
     }
-    if (d == 0) { S->iter++; return FC_OK; }
+    if (d == 0) {
+      // no continuous sites: the reference's advance() draws a fresh prior sample each step and rescoring
+      // updates the log-joint and the trace (hmc.rs:826-846)
+      FC_TRY(prior_sample_dev(P, S->q.p, S->qd.p, C, S->seed, S->chain0, 0x7100000000000000ULL | (S->iter + 1)));
+      FC_TRY(score_dev(P, S->q.p, S->qd.p, C, S->lp3_cur.p, S->lj.p, nullptr));
+      S->iter++;
+      return FC_OK;
+    }
     uint64_t tag = S->iter;
     FC_TRY(momentum(tag));
     if (S->recording) FC_TRY(trajectory_recorded(S->eps.p, S->L));

@@ -192,11 +192,11 @@ __global__ void __launch_bounds__(256, GRAD ? 2 : 3) k_plate_fast(const __grid_c
         const bool useb = (sig_is_e0 && aux0 != 0.0) || (sig_is_e1 && aux1 != 0.0);
         const bool ok = useb ? n_ok_b : n_ok_a;
         const double inv = useb ? n_inv_b : n_inv_a, lgs = useb ? n_log_b : n_log_a;
-        if (!ok || !d_fin(pv0) || !d_fin(x)) g_lp = d_neg_inf();
+        if (!ok || !d_fin(pv0) || !d_fin(x)) { g_lp = d_neg_inf(); if (GRAD) g_dx = g_dp0 = g_dp1 = qnan; }  // no gradient outside the support: divergent (hmc.rs:384-386)
         else {
           double z = (x - pv0) * inv;
           g_lp = -0.5 * z * z - lgs - 0.5 * FC_LN_2PI;
-          if (GRAD && d_fin(g_lp)) { g_dp0 = z * inv; g_dx = -g_dp0; g_dp1 = (z * z - 1.0) * inv; }
+          if (GRAD) { if (d_fin(g_lp)) { g_dp0 = z * inv; g_dx = -g_dp0; g_dp1 = (z * z - 1.0) * inv; } else g_dx = g_dp0 = g_dp1 = qnan; }
         }
       } else if (DK == DK_TWOVAL) {
         if (xi == 0) { g_lp = tv_lp0; g_dp0 = tv_d0; }

@@ -194,12 +194,12 @@ __global__ void __launch_bounds__(PL_TX* PL_TY, 2) k_plate(const __grid_constant
             mem_sig[0] = sig; mem_log[0] = log(sig); mem_inv[0] = 1.0 / sig;
           }
           g.dx = g.dp0 = g.dp1 = g.dp2 = 0.0;
-          if (!(sig > 0.0) || !d_fin(sig) || !d_fin(pv[0]) || !d_fin(x)) g.lp = d_neg_inf();
+          if (!(sig > 0.0) || !d_fin(sig) || !d_fin(pv[0]) || !d_fin(x)) { g.lp = d_neg_inf(); if (GRAD) g.dx = g.dp0 = g.dp1 = qnan; }
           else {
             const double inv = m == 0 ? mem_inv[0] : mem_inv[1], lg = m == 0 ? mem_log[0] : mem_log[1];
             double z = (x - pv[0]) * inv;
             g.lp = -0.5 * z * z - lg - 0.5 * FC_LN_2PI;
-            if (GRAD && d_fin(g.lp)) { g.dp0 = z * inv; g.dx = -g.dp0; g.dp1 = (z * z - 1.0) * inv; }
+            if (GRAD) { if (d_fin(g.lp)) { g.dp0 = z * inv; g.dx = -g.dp0; g.dp1 = (z * z - 1.0) * inv; } else g.dx = g.dp0 = g.dp1 = qnan; }
           }
         } else if (two_valued && (xi == 0 || xi == 1)) {
           g = xi ? tv1 : tv0;

@@ -232,6 +232,9 @@ inline Score score_program_order(const Program& P, const double* q, const int64_
         g = LpGrad{(xi >= 0) ? categorical_lp((const double*)pc.data, (size_t)pc.rows, (uint64_t)xi) : NEG_INF, 0.0, {0.0, 0.0, 0.0}};
       } else g = dist_eval(op.dist, pv, x, xi);
       if (is_sample) sc.log_prior += g.lp; else sc.log_lik += g.lp;
+      if (dq && g.lp == NEG_INF) {  // outside the support there is no gradient: the reference's FD force is NaN (hmc.rs:304-329)
+        for (int64_t k = 0; k < P.d_cont; k++) dq[k] = std::nan("");
+      }
       if (dq) {
         if (is_sample && cont) dq[P.cslot0[oi] + i] += g.dx;
         for (int j = 0; j < op.n_params; j++) {

@@ -55,6 +55,59 @@ def test_transition_matches_oracle_on_same_randomness(name):
     S.close()
 
 
+def test_trajectory_leaving_the_support_is_divergent_as_in_the_reference():
+    """A bounded site and a large step: interior leapfrog points leave the support. The reference's finite-difference
+    force is NaN there, so the trajectory is divergent and rejected (hmc.rs:304-329, 384-386); the analytic force
+    must say the same (it used to be a finite zero, letting the trajectory glide on and possibly re-enter)."""
+    from fugue_b200 import api
+    rng = np.random.default_rng(8)
+    m = ModelBuilder()
+    s = m.sample("sigma", Gamma(2.0, 2.0))
+    mu = m.sample("mu", Normal(0.0, 1.0))
+    m.plate_observe("y", Normal(mu, s), m.data(rng.normal(0.3, 0.5, 12)))
+    O = oracle.OracleProgram(m)
+    Cn, L, eps = 64, 9, 0.35
+    q0 = np.stack([rng.normal(0, 0.4, Cn), rng.uniform(0.05, 0.5, Cn)])  # sorted sites: mu, sigma (close to 0)
+    S = api.HmcSession(m, n_chains=Cn, n_warmup=0, config=api.HMCConfig(n_leapfrog=L, init_step_size=eps), seed=5, q0=q0)
+    n_div = 0
+    for it in range(3):
+        qc, ljc = S.position(), S.log_joint()
+        z = rng.standard_normal((O.d_cont, Cn))
+        u = rng.random(Cn)
+        S.set_explicit_randomness(z, u)
+        S.step(1)
+        qn, info = S.position(), S.last_step_info()
+        for c in range(Cn):
+            oq, olj, oinfo = O.hmc_transition(qc[:, c], ljc[c], z[:, c], u[c], eps, L)
+            assert oinfo["divergent"] == info["divergent"][c], (it, c)
+            if oinfo["divergent"]:
+                assert not info["accepted"][c] and np.array_equal(qn[:, c], qc[:, c])
+                n_div += 1
+            elif abs(u[c] - oinfo["accept_prob"]) > 1e-6:
+                assert oinfo["accepted"] == info["accepted"][c] and np.allclose(oq, qn[:, c], rtol=1e-9, atol=1e-11)
+    assert n_div >= 5  # the case is really exercised
+    assert S.stats()["n_divergent"].sum() == n_div
+    S.close()
+
+
+def test_discrete_only_model_yields_fresh_prior_draws():
+    """d == 0: HmcSession::advance draws a fresh prior sample each step (hmc.rs:826-846)."""
+    from fugue_b200 import api
+    from fugue_b200.model import Bernoulli
+    m = ModelBuilder()
+    m.sample("b", Bernoulli(0.3))
+    m.observe("y", Normal(0.0, 1.0), 0.2)
+    S = api.HmcSession(m, n_chains=4096, n_warmup=0, seed=3)
+    lj = []
+    for _ in range(6):
+        S.step(1)
+        lj.append(S.log_joint().copy())
+    lj = np.array(lj)
+    p1 = np.isclose(lj, np.log(0.3) + (-0.5 * 0.04 - 0.5 * np.log(2 * np.pi))).mean(axis=1)
+    assert np.all(np.abs(p1 - 0.3) < 0.04) and (lj[0] != lj[1]).any() and (lj[1] != lj[2]).any()
+    S.close()
+
+
 def test_find_reasonable_epsilon_matches_oracle():
     from fugue_b200 import api
     rng = np.random.default_rng(4)
