@@ -462,6 +462,7 @@ _sig("fc_smc_export", vp, vp)
 _sig("fc_smc_connect", vp, vp)
 _sig("fc_smc_record_offspring", vp, C.c_int32)
 _sig("fc_smc_last_offspring", vp, u64p, u64p, vp)
+_sig("fc_smc_resample_virtual_shards", vp, C.c_int32, C.c_int32, C.c_double, vp)
 _sig("fc_smc_slot_range", C.c_int32, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, C.c_double, C.c_double, C.c_int32, u64p, u64p)
 _sig("fc_debug_set", C.c_char_p, C.c_int32)
 _sig("fc_smc_phase_ms", vp, vp, vp)
@@ -588,6 +589,12 @@ class SmcSession:
         if us is not None and us.size != (1 if method == ResamplingMethod.Systematic else self.n):
             raise FugueError(_ir.FC_ERR_INVALID_ARGUMENT, "uniforms: 1 value for systematic, n otherwise")
         check(lib.fc_smc_resample_particles(self.h, method, _ptr(us), _ptr(idx)))
+        return idx
+
+    def resample_virtual_shards(self, shards, method=ResamplingMethod.Systematic, u_raw=0.5):
+        """resample_particles with the population processed as `shards` virtual ranks (parity hook)."""
+        idx = np.zeros(self.n, dtype=np.uint64)
+        check(lib.fc_smc_resample_virtual_shards(self.h, int(shards), method, float(u_raw), _ptr(idx)))
         return idx
 
     def record_offspring(self, enable=True):

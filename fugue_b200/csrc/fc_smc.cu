@@ -1637,6 +1637,82 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
   return FC_OK;
 }
 
+// The sharded resample's device logic on ONE GPU without any waiting kernel: the session's population is cut
+// into `vw` virtual shards that are processed one after the other exactly as real ranks would -- exact scan of
+// the shard continuing from the previous shard's end value (head skipped, window from the mean-weight hint),
+// host slot routing from the (carry, end) pairs, gather of every (source shard, destination shard) block with
+// its record / index offsets. Only the mailbox transport is not exercised (ranks that spin on each other must
+// not share a GPU). h_idx: the n global ancestors. Systematic (u_raw) or stratified (session stream) thresholds.
+static int32_t smc_resample_virtual(fc_smc_session* S, int vw, int method, double u_raw, uint64_t* h_idx) {
+  fc_program* P = S->P;
+  cudaStream_t st = P->stream;
+  const int64_t n = S->n;
+  if (S->world != 1 || vw < 1 || vw > MB_MAXW || (int64_t)vw > n) { set_error("virtual shards: need a single-rank session and 1 <= shards <= 8"); return FC_ERR_INVALID_ARGUMENT; }
+  if (method != FC_RESAMPLE_SYSTEMATIC && method != FC_RESAMPLE_STRATIFIED) { set_error("virtual shards: systematic or stratified"); return FC_ERR_INVALID_ARGUMENT; }
+  S->resamples += 1;
+  const uint64_t tag = 0x1000000000000000ULL | S->resamples;
+  const int from = S->cur, to = S->cur ^ 1;
+  std::vector<int64_t> b(vw + 1);
+  for (int r = 0; r <= vw; r++) b[r] = (n / vw) * r + std::min<int64_t>(r, n % vw);
+  // every shard's running sums live in their own (n_r + 2)-slice of one buffer
+  DevBuf<double> Sall;
+  FC_CUDA(Sall.reserve(n + 2 * vw + 2));
+  std::vector<double*> Sr(vw);
+  std::vector<double> ends(vw);
+  double carry = 0.0;
+  for (int r = 0; r < vw; r++) {
+    const int64_t nr = b[r + 1] - b[r];
+    Sr[r] = Sall.p + b[r] + 2 * r;
+    FC_CUDA(S->work.reserve(scan_work_bytes(nr)));
+    ScanCtl hs;
+    memset(&hs, 0, sizeof(hs));
+    hs.s0 = carry;
+    hs.w_mean = 1.0 / (double)n;
+    FC_CUDA(cudaMemcpyAsync(S->work.p, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
+    FC_TRY(scan_enqueue_head(S->w.p + b[r], nr, Sr[r], S->work.p, st, &P->n_kernel_launches));
+    FC_TRY(scan_enqueue_rounds(S->w.p + b[r], nr, Sr[r], S->work.p, r == 0 ? scan_expected_rounds(nr) : 3, st, &P->n_kernel_launches));
+    FC_TRY(scan_finish(S->w.p + b[r], nr, Sr[r], S->work.p, st, &P->n_kernel_launches, &ends[r]));
+    carry = ends[r];
+  }
+  FC_CUDA(S->idx.reserve(n));
+  GatherArgs G;
+  memset(&G, 0, sizeof(G));
+  G.n_total = (double)n; G.method = method; G.seed = S->seed; G.tag = tag; G.u_raw = u_raw;
+  G.pitch = S->L.pitch; G.ll_off = (P->d_cont + 1) * 8; G.idx_out = S->idx.p;
+  Pop pf = S->pop(from), pt = S->pop(to);
+  for (int r = 0; r < vw; r++) {
+    const int64_t nr = b[r + 1] - b[r];
+    const double cin = r == 0 ? 0.0 : ends[r - 1];
+    int64_t jlo = count_thresholds_le(method, n, u_raw, S->seed, tag, cin);
+    int64_t jhi = r == vw - 1 ? n : count_thresholds_le(method, n, u_raw, S->seed, tag, ends[r]);
+    if (jhi < jlo) jhi = jlo;
+    G.S = Sr[r]; G.n_src = nr; G.first_src = b[r];
+    G.src = pf; G.src.rec = pf.rec + b[r] * S->L.pitch; G.src.ll = pf.ll + b[r]; G.src.n = nr;
+    for (int t = 0; t < vw; t++) {
+      const int64_t a = std::max(jlo, b[t]), e = std::min(jhi, b[t + 1]);
+      if (e <= a) continue;
+      G.j0 = a; G.cnt = e - a; G.dst_off = a - b[t]; G.idx_off = a; G.wrap0 = 0;
+      G.dst = pt; G.dst.rec = pt.rec + b[t] * S->L.pitch; G.dst.ll = pt.ll + b[t]; G.dst.n = b[t + 1] - b[t];
+      k_smcx_gather<<<(unsigned)cdiv(G.cnt, GA_THREADS), GA_THREADS, 0, st>>>(G);
+      P->n_kernel_launches += 1;
+    }
+    if (r == vw - 1 && jlo > 0 && vw > 1 && count_thresholds_le(method, n, u_raw, S->seed, tag, 0.0) > 0) {  // the u == 0 wrap slot
+      G.j0 = 0; G.cnt = 1; G.dst_off = 0; G.idx_off = 0; G.wrap0 = 1;
+      G.dst = pt; G.dst.n = b[1];
+      k_smcx_gather<<<1, GA_THREADS, 0, st>>>(G);
+      P->n_kernel_launches += 1;
+    }
+  }
+  FC_KERNEL_CHECK();
+  if (h_idx) FC_CUDA(cudaMemcpyAsync(h_idx, S->idx.p, n * 8, cudaMemcpyDeviceToHost, st));
+  FC_CUDA(cudaStreamSynchronize(st));
+  S->cur = to;
+  S->soa_valid = false;
+  S->bis_ll_valid = false;
+  S->log_w_uniform = true;
+  return FC_OK;
+}
+
 // `steps` pi_beta-invariant single-site moves per particle (smc.rs:544-554, 698-713)
 static int32_t smc_rejuvenate(fc_smc_session* S, double beta, uint64_t steps) {
   fc_program* P = S->P;
@@ -2105,6 +2181,16 @@ int32_t fc_smc_resample_particles(fc_smc_session* s, int32_t method, const doubl
   FC_TRY(smc_resample(s, method, h_uniforms, h_idx));
   FC_CUDA(cudaStreamSynchronize(s->P->stream));
   return comm_check(s);
+}
+
+// parity hook: resample_particles with the population processed as `shards` virtual ranks, one after the other
+// (the sharded resample's scan-with-carry, slot routing and offset gather on one GPU; see smc_resample_virtual)
+int32_t fc_smc_resample_virtual_shards(fc_smc_session* s, int32_t shards, int32_t method, double u_raw, uint64_t* h_idx) {
+  using namespace fc;
+  FC_TRY(smc_ready(s));
+  FC_TRY(fc_smc_normalize(s, nullptr, nullptr));
+  s->steps += 1;
+  return smc_resample_virtual(s, shards, method, u_raw, h_idx);
 }
 
 // rejuvenate_particles (smc.rs:698-713): `steps` pi_beta-invariant single-site MH moves per particle,

@@ -353,6 +353,11 @@ int32_t fc_smc_slot_range(int32_t method, uint64_t n_total, double u_raw, uint64
  * jhi - jlo entries (may be NULL). Concatenated over ranks in rank order they are the whole index array
  * the reference's systematic_indices / stratified_indices return. */
 int32_t fc_smc_record_offspring(fc_smc_session* s, int32_t enable);
+/* resample_particles with a single-rank session's population processed as `shards` (1..8) VIRTUAL ranks one after
+ * the other: the sharded resample's exact scan continuing from the previous shard's end value, its host slot
+ * routing and its offset gathers, on one GPU and without any kernel that waits on another. h_idx: the n
+ * ancestors (may be NULL). method: systematic (u_raw) or stratified (the session's uniform stream). */
+int32_t fc_smc_resample_virtual_shards(fc_smc_session* s, int32_t shards, int32_t method, double u_raw, uint64_t* h_idx);
 int32_t fc_smc_last_offspring(fc_smc_session* s, uint64_t* jlo, uint64_t* jhi, uint64_t* h_idx);
 /* next_beta (smc.rs:588-622) on host arrays: the largest beta' in (beta, 1] whose incremental
  * weights log_w + (beta' - beta) * ll keep ESS >= target_ess (64-step bisection; 1.0 if a full

@@ -217,3 +217,27 @@ def test_standalone_prior_particles_resample_rejuvenate():
     assert np.allclose(r2.weight, 1.0 / n, rtol=1e-12)
     assert len(np.unique(x)) > n // 4  # the moves diversified the resampled population
     S.close()
+
+
+@pytest.mark.parametrize("vw", [1, 2, 3, 8])
+@pytest.mark.parametrize("method", [1, 2])
+def test_virtual_shards_resample_matches_single_population(vw, method):
+    """The sharded resample's device logic on one GPU (fc_smc_resample_virtual_shards): the population is cut into
+    vw virtual ranks processed one after the other -- exact scan continuing from the previous shard's end value,
+    slot routing from the (carry, end) pairs, offset gathers -- and must reproduce the sequential reference loop
+    over the whole population bit for bit (the 2-GPU run of the real thing: tests/test_gpu_smc_sharded.py)."""
+    from fugue_b200 import api, models
+    n, seed = 100003, 3
+    S = api.SmcSession(models.gaussian_mixture(n_obs=12)[0], n, api.SMCConfig(rejuvenation_steps=1), seed)
+    S.reweight(0.04)
+    w = S.weights()[1]
+    before = S.result()
+    u = 0.0 if vw == 3 else 0.37
+    idx = S.resample_virtual_shards(vw, method, u).astype(np.int64)
+    us = [u] if method == 1 else oracle.philox_uniforms(seed, 0x8000000000000000, 0x1000000000000000 | 1, n)
+    anc = oracle.resample(method, w, us).astype(np.int64)
+    assert np.array_equal(idx, anc)
+    after = S.result()
+    assert np.array_equal(after.values, before.values[:, anc]) and np.array_equal(after.dvalues, before.dvalues[:, anc])
+    assert np.allclose(after.weight, 1.0 / n, rtol=1e-12)
+    S.close()
