@@ -51,6 +51,7 @@ _sig("fc_program_check_structure", vp, vp, C.c_size_t)
 _sig("fc_program_dims", vp, i64p, i64p)
 _sig("fc_program_sites", vp, C.POINTER(C.POINTER(C.c_char_p)), C.POINTER(i64p), i64p)
 _sig("fc_program_stream", vp, C.POINTER(vp))
+_sig("fc_program_device", vp, C.POINTER(C.c_int32))
 _sig("fc_program_launch_count", vp, u64p)
 _sig("fc_program_kernel_timing", vp, C.c_int32)
 _sig("fc_program_kernel_time", vp, dp, u64p)
@@ -123,6 +124,12 @@ class Program:
         return s.value or 0
 
     @property
+    def device(self):
+        dv = C.c_int32()
+        check(lib.fc_program_device(self.h, C.byref(dv)))
+        return dv.value
+
+    @property
     def launch_count(self):
         n = C.c_uint64()
         check(lib.fc_program_launch_count(self.h, C.byref(n)))
@@ -191,6 +198,8 @@ _sig("fc_hmc_last_accept_prob", vp, vp, vp, vp)
 _sig("fc_hmc_set_explicit_randomness", vp, vp, vp)
 _sig("fc_hmc_find_reasonable_epsilon", vp, vp)
 _sig("fc_hmc_run", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp)
+_sig("fc_hmc_run_dev", vp, vp, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp)
+_sig("fc_hmc_sample_dev", vp, C.c_size_t, vp, vp)
 lib.fc_hmc_config_default.argtypes = [C.POINTER(_ir.fc_hmc_config)]
 lib.fc_hmc_config_default.restype = None
 
@@ -252,6 +261,15 @@ class HmcSession:
 
     def sync(self):
         check(lib.fc_hmc_sync(self.h))
+
+    def sample_dev(self, n):
+        """n further transitions, every post-transition state kept in HBM (fc_hmc_sample_dev): CUDA tensors
+        draws [n][d][C] and log_joint [n][C]."""
+        draws = _device_f64((n, self.program.d_cont, self.n_chains), self.program.device)
+        lp = _device_f64((n, self.n_chains), self.program.device)
+        check(lib.fc_hmc_sample_dev(self.h, n, vp(draws.data_ptr()), vp(lp.data_ptr())))
+        self.sync()
+        return draws, lp
 
     def step_recorded(self):
         """HmcSession::step_recorded (hmc.rs:811-817): one transition; returns the leapfrog points
@@ -347,6 +365,37 @@ def hmc_chain(model, n_samples, n_warmup, config=None, n_chains=1, seed=0):
     lp = np.zeros((n_samples, n_chains))
     st = (_ir.fc_hmc_stats * n_chains)()
     check(lib.fc_hmc_run(P.h, C.byref(cfg), seed, n_chains, n_warmup, n_samples, _ptr(draws), _ptr(lp), C.cast(st, vp)))
+    stats = dict(n_accept=np.array([s.n_accept for s in st]), n_divergent=np.array([s.n_divergent for s in st]),
+                 step_size=np.array([s.step_size for s in st]))
+    return draws, lp, stats
+
+
+def _device_f64(shape, device):
+    """HBM for draws that stay on the device. torch is the allocator only (plumbing); the library reads
+    and writes the buffer through its raw pointer."""
+    import torch
+    return torch.empty(shape, dtype=torch.float64, device=f"cuda:{device}")
+
+
+def hmc_chain_dev(model, n_samples, n_warmup, config=None, n_chains=1, seed=0, q0=None):
+    """hmc_chain with the draws left in HBM (fc_hmc_run_dev): returns (draws, log_joint, stats) where draws
+    [n_samples][d][n_chains] and log_joint [n_samples][n_chains] are CUDA tensors; pass draws to
+    diagnostics_dev. At the C3 shape (1024 chains x 500 draws x 10 004 parameters) that is 41 GB that never
+    crosses PCIe. q0 [d][n_chains]: starting points (default: a prior draw per chain, hmc.rs:673)."""
+    P = _as_program(model)
+    if q0 is not None:
+        S = HmcSession(P, n_chains=n_chains, n_warmup=n_warmup, config=config, seed=seed, q0=q0)
+        S.step(n_warmup)
+        draws, lp = S.sample_dev(n_samples)
+        stats = S.stats()
+        S.close()
+        return draws, lp, stats
+    cfg = (config or HMCConfig())._c()
+    d = P.d_cont
+    draws = _device_f64((n_samples, d, n_chains), P.device)
+    lp = _device_f64((n_samples, n_chains), P.device)
+    st = (_ir.fc_hmc_stats * n_chains)()
+    check(lib.fc_hmc_run_dev(P.h, C.byref(cfg), seed, n_chains, n_warmup, n_samples, vp(draws.data_ptr()), vp(lp.data_ptr()), C.cast(st, vp)))
     stats = dict(n_accept=np.array([s.n_accept for s in st]), n_divergent=np.array([s.n_divergent for s in st]),
                  step_size=np.array([s.step_size for s in st]))
     return draws, lp, stats
@@ -726,6 +775,7 @@ _sig("fc_split_rhat", vp, C.c_size_t, C.c_size_t, dp)
 _sig("fc_classic_rhat", vp, C.c_size_t, C.c_size_t, dp)
 _sig("fc_ess_multichain", vp, C.c_size_t, C.c_size_t, dp)
 _sig("fc_diagnostics", vp, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp)
+_sig("fc_diagnostics_dev", vp, C.c_size_t, C.c_size_t, C.c_size_t, vp, vp, vp, vp)
 
 
 def _one(fn, draws):
@@ -755,6 +805,16 @@ def diagnostics(draws):
     S, d, Cn = x.shape
     mean, std, rh, ess = np.zeros(d), np.zeros(d), np.zeros(d), np.zeros(d)
     check(lib.fc_diagnostics(_ptr(x), S, d, Cn, _ptr(mean), _ptr(std), _ptr(rh), _ptr(ess)))
+    return dict(mean=mean, std=std, r_hat=rh, ess=ess)
+
+
+def diagnostics_dev(draws):
+    """diagnostics() on a CUDA tensor [S][d][C] (hmc_chain_dev's draws), read in place in HBM."""
+    if draws.dim() != 3 or str(draws.dtype) != "torch.float64" or not draws.is_cuda or not draws.is_contiguous():
+        raise ValueError("diagnostics_dev: draws must be a contiguous CUDA float64 tensor [S][d][C]")
+    S, d, Cn = draws.shape
+    mean, std, rh, ess = np.zeros(d), np.zeros(d), np.zeros(d), np.zeros(d)
+    check(lib.fc_diagnostics_dev(vp(draws.data_ptr()), S, d, Cn, _ptr(mean), _ptr(std), _ptr(rh), _ptr(ess)))
     return dict(mean=mean, std=std, r_hat=rh, ess=ess)
 
 

@@ -226,23 +226,31 @@ static int32_t diagnostics_dev(const double* d_draws, int64_t S, int64_t d, int6
 
 static cudaStream_t g_diag_stream = nullptr;
 
-static int32_t diagnostics_host(const double* h_draws, size_t S, size_t d, size_t C, int what, double* h_mean, double* h_std, double* h_rhat, double* h_ess) {
+// x_is_dev: the draws already live in HBM (fc_hmc_run_dev) and are read in place
+static int32_t diagnostics_any(const double* draws, bool x_is_dev, size_t S, size_t d, size_t C, int what, double* h_mean, double* h_std, double* h_rhat, double* h_ess) {
   if (d == 0) return FC_OK;
   if (!g_diag_stream) FC_CUDA(cudaStreamCreateWithFlags(&g_diag_stream, cudaStreamNonBlocking));
   cudaStream_t st = g_diag_stream;
   DiagWork W;
   size_t n = S * d * C;
-  FC_CUDA(W.x.reserve(n));
+  const double* x = draws;
+  if (!x_is_dev) {
+    FC_CUDA(W.x.reserve(n));
+    if (n) FC_CUDA(cudaMemcpyAsync(W.x.p, draws, n * 8, cudaMemcpyHostToDevice, st));
+    x = W.x.p;
+  }
   FC_CUDA(W.out.reserve(4 * d));
-  if (n) FC_CUDA(cudaMemcpyAsync(W.x.p, h_draws, n * 8, cudaMemcpyHostToDevice, st));
   double* o = W.out.p;
-  FC_TRY(diagnostics_dev(W.x.p, (int64_t)S, (int64_t)d, (int64_t)C, what, o, o + d, o + 2 * d, o + 3 * d, W, st));
+  FC_TRY(diagnostics_dev(x, (int64_t)S, (int64_t)d, (int64_t)C, what, o, o + d, o + 2 * d, o + 3 * d, W, st));
   if (h_mean) FC_CUDA(cudaMemcpyAsync(h_mean, o, d * 8, cudaMemcpyDeviceToHost, st));
   if (h_std) FC_CUDA(cudaMemcpyAsync(h_std, o + d, d * 8, cudaMemcpyDeviceToHost, st));
   if (h_rhat) FC_CUDA(cudaMemcpyAsync(h_rhat, o + 2 * d, d * 8, cudaMemcpyDeviceToHost, st));
   if (h_ess) FC_CUDA(cudaMemcpyAsync(h_ess, o + 3 * d, d * 8, cudaMemcpyDeviceToHost, st));
   FC_CUDA(cudaStreamSynchronize(st));
   return FC_OK;
+}
+static int32_t diagnostics_host(const double* h_draws, size_t S, size_t d, size_t C, int what, double* h_mean, double* h_std, double* h_rhat, double* h_ess) {
+  return diagnostics_any(h_draws, false, S, d, C, what, h_mean, h_std, h_rhat, h_ess);
 }
 
 }  // namespace fc
@@ -281,6 +289,18 @@ int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, doub
     return FC_OK;
   }
   return fc::diagnostics_host(h_draws, S, d, C, what, h_mean, h_std, h_rhat, h_ess);
+}
+// fc_diagnostics on draws that never left the device (d_draws [S][d][C] in HBM, as fc_hmc_run_dev leaves
+// them): the same kernels read them in place; only the 4*d results cross to the host. The caller's
+// producer stream must have finished (fc_hmc_run_dev synchronises before it returns).
+int32_t fc_diagnostics_dev(const double* d_draws, size_t S, size_t d, size_t C, double* h_mean, double* h_std, double* h_rhat, double* h_ess) {
+  int what = 0;
+  if (h_rhat) what |= 1;
+  if (h_ess) what |= 4;
+  if (h_mean || h_std) what |= 8;
+  if (S == 0 || C == 0) return fc_diagnostics(nullptr, S, d, C, h_mean, h_std, h_rhat, h_ess);
+  if (!d_draws) { fc::set_error("d_draws is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  return fc::diagnostics_any(d_draws, true, S, d, C, what, h_mean, h_std, h_rhat, h_ess);
 }
 // Per-rank partial statistics for multi-GPU R-hat / ESS: split-half means and sums of
 // squares per chain, chain means, and the chain-SUM of autocovariances per lag. A rank holds

@@ -710,22 +710,40 @@ int32_t fc_hmc_last_accept_prob(fc_hmc_session* s, double* h_ap, int32_t* h_acce
   return FC_OK;
 }
 
-// hmc_chain (hmc.rs:566-583): warmup, then n_samples draws. h_draws [n_samples][d][C], h_lp [n_samples][C].
-int32_t fc_hmc_run(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C, size_t n_warmup, size_t n_samples, double* h_draws, double* h_lp, fc_hmc_stats* h_stats) {
+// n further transitions with every post-transition state kept: out_draws [n][d][C], out_lp [n][C] (either
+// may be NULL). `kind` says where they live: host pointers go through one async copy per draw, device
+// pointers (the draws stay in HBM for fc_diagnostics_dev; 41 GB at the C3 shape) through a device copy.
+static int32_t hmc_sample_into(fc_hmc_session* s, size_t n, double* out_draws, double* out_lp, cudaMemcpyKind kind) {
+  cudaStream_t st = s->P->stream;
+  const size_t d = (size_t)s->d, C = (size_t)s->C;
+  for (size_t i = 0; i < n; i++) {
+    FC_TRY(fc_hmc_step(s, 1));
+    if (out_draws && d > 0) FC_CUDA(cudaMemcpyAsync(out_draws + i * d * C, s->q.p, d * C * 8, kind, st));
+    if (out_lp) FC_CUDA(cudaMemcpyAsync(out_lp + i * C, s->lj.p, C * 8, kind, st));
+  }
+  return FC_OK;
+}
+int32_t fc_hmc_sample_dev(fc_hmc_session* s, size_t n, double* d_draws, double* d_lp) {
+  if (!s) { fc::set_error("session is NULL"); return FC_ERR_INVALID_ARGUMENT; }
+  return hmc_sample_into(s, n, d_draws, d_lp, cudaMemcpyDeviceToDevice);
+}
+static int32_t hmc_run_impl(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C, size_t n_warmup, size_t n_samples, double* draws, double* lp,
+                            fc_hmc_stats* h_stats, cudaMemcpyKind kind) {
   fc_hmc_session* s = nullptr;
   FC_TRY(fc_hmc_create(p, cfg, seed, C, n_warmup, nullptr, nullptr, &s));
   int32_t rc = fc_hmc_step(s, n_warmup);
-  cudaStream_t st = p->stream;
-  int64_t d = s->d;
-  for (size_t i = 0; i < n_samples && rc == FC_OK; i++) {
-    rc = fc_hmc_step(s, 1);
-    if (rc != FC_OK) break;
-    if (h_draws && d > 0 && cudaMemcpyAsync(h_draws + i * d * C, s->q.p, d * C * 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = FC_ERR_CUDA;
-    if (h_lp && cudaMemcpyAsync(h_lp + i * C, s->lj.p, C * 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = FC_ERR_CUDA;
-  }
+  if (rc == FC_OK) rc = hmc_sample_into(s, n_samples, draws, lp, kind);
   if (rc == FC_OK && h_stats) rc = fc_hmc_get(s, nullptr, nullptr, h_stats);
-  cudaStreamSynchronize(st);
+  if (cudaStreamSynchronize(p->stream) != cudaSuccess && rc == FC_OK) rc = FC_ERR_CUDA;
   fc_hmc_destroy(s);
   return rc;
+}
+// hmc_chain (hmc.rs:566-583): warmup, then n_samples draws. h_draws [n_samples][d][C], h_lp [n_samples][C].
+int32_t fc_hmc_run(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C, size_t n_warmup, size_t n_samples, double* h_draws, double* h_lp, fc_hmc_stats* h_stats) {
+  return hmc_run_impl(p, cfg, seed, C, n_warmup, n_samples, h_draws, h_lp, h_stats, cudaMemcpyDeviceToHost);
+}
+// The same run with the draws left on the device: d_draws / d_lp are DEVICE pointers of the same shapes.
+int32_t fc_hmc_run_dev(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C, size_t n_warmup, size_t n_samples, double* d_draws, double* d_lp, fc_hmc_stats* h_stats) {
+  return hmc_run_impl(p, cfg, seed, C, n_warmup, n_samples, d_draws, d_lp, h_stats, cudaMemcpyDeviceToDevice);
 }
 }

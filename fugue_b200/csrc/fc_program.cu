@@ -523,6 +523,10 @@ int32_t fc_program_stream(const fc_program* p, void** stream) {
   *stream = (void*)p->stream;
   return FC_OK;
 }
+int32_t fc_program_device(const fc_program* p, int32_t* device) {
+  *device = (int32_t)p->device;
+  return FC_OK;
+}
 
 // CUDA-event timing of the dominant plate kernel (the dense GLM kernel), recorded on the
 // launching stream. enable(1) clears previous records.

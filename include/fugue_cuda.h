@@ -157,6 +157,9 @@ int32_t fc_program_sites(const fc_program* p, const char* const** names, const i
                          int64_t* n);
 /* cudaStream_t the program launches on (for CUDA-event timing by the caller). */
 int32_t fc_program_stream(const fc_program* p, void** stream);
+/* CUDA device ordinal the program's columns and stream live on (where device-resident buffers handed
+ * to the *_dev entry points must be allocated). */
+int32_t fc_program_device(const fc_program* p, int32_t* device);
 /* Number of kernels this library has launched on behalf of the program (bench.py gpu_launches). */
 int32_t fc_program_launch_count(const fc_program* p, uint64_t* n);
 /* CUDA-event timing (on the launching stream) of the dominant observation-streaming kernel:
@@ -234,6 +237,14 @@ int32_t fc_hmc_find_reasonable_epsilon(fc_hmc_session* s, double* h_eps);  /* hm
 int32_t fc_hmc_run(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
                    size_t n_warmup, size_t n_samples, double* h_draws, double* h_lp,
                    fc_hmc_stats* h_stats);
+/* The same run with the draws left in HBM (1024 chains x 500 draws x 10 004
+ * parameters = 41 GB never crosses PCIe): d_draws [n_samples][d][C] and d_lp [n_samples][C] are
+ * DEVICE pointers (either may be NULL). fc_hmc_sample_dev is the session-level form (n further
+ * transitions, every state kept). Returns after the stream has drained. */
+int32_t fc_hmc_run_dev(fc_program* p, const fc_hmc_config* cfg, uint64_t seed, size_t C,
+                       size_t n_warmup, size_t n_samples, double* d_draws, double* d_lp,
+                       fc_hmc_stats* h_stats);
+int32_t fc_hmc_sample_dev(fc_hmc_session* s, size_t n, double* d_draws, double* d_lp);
 
 /* ---- single-site MH (src/inference/mh.rs:698-744, 921-1014) ---- */
 typedef struct fc_mh_config {
@@ -385,6 +396,10 @@ int32_t fc_ess_multichain(const double* h_draws, size_t S, size_t C, double* out
 /* all parameters at once: h_draws [S][d][C] (the fc_hmc_run layout); out arrays of length d. */
 int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, double* h_mean,
                        double* h_std, double* h_rhat, double* h_ess);
+/* ... on draws resident in HBM (device pointer, same layout); diagnostics.rs:240-304 and
+ * mcmc_utils.rs:231-339 run in place, 4*d doubles come back. */
+int32_t fc_diagnostics_dev(const double* d_draws, size_t S, size_t d, size_t C, double* h_mean,
+                           double* h_std, double* h_rhat, double* h_ess);
 
 /* Per-rank partial statistics for multi-GPU R-hat / ESS (chains sharded over ranks): split-half
  * means / sums of squares per chain [d][2C], chain means [d][C], and chain-summed autocovariances

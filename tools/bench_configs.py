@@ -27,7 +27,7 @@ def timed(P, fn, reps):
 
 if which == "c3":
     G, Cn = int(10000 * scale), int(1024 * max(scale, 0.25))
-    m, _ = models.hierarchical(G=G, per_group=15)
+    m, truth = models.hierarchical(G=G, per_group=15)
     P = api.Program(m)
     N, d = G * 15, P.d_cont
     S = api.HmcSession(P, n_chains=Cn, n_warmup=10**9, config=api.HMCConfig(n_leapfrog=16, adapt_mass=False), seed=1)
@@ -39,12 +39,38 @@ if which == "c3":
     alg = 20 * N + 16 * d
     out = dict(config="C3 hierarchical normal", G=G, N=N, d=d, chains=Cn, ms_per_transition=ms, grad_evals_per_s=rate,
                hbm_alg_GBps=rate * alg / 1e9, hbm_frac=rate * alg / 1e9 / HBM, accept=float(np.mean(S.stats()["n_accept"]) / S.iterations()))
-    # diagnostics on a short run of all d parameters
+    # the stated run shape (hierarchical_models.rs:7-33 scaled): Cn chains x (n_w warm-up + n_s draws) with
+    # adapt_mass, draws kept in HBM (fc_hmc_run_dev), R-hat / ESS / mean / std of all d parameters on
+    # them in place (fc_diagnostics_dev)
+    # Starting points: over-dispersed data-driven inits, relaxed by a pilot of n_p identity-mass transitions.
+    # (From prior draws the 10 000 intercepts sit ~5 prior sd out and the reference's single Welford window,
+    # hmc.rs:868-893, then measures the drift, not the posterior: R-hat stays > 10 after 3000 + 500, see
+    # profiles/c3_convergence_r2.txt. The pilot's end states put that window inside the typical set.)
+    n_w = n_s = int(os.environ.get("FC_C3_DRAWS", max(50, int(500 * min(1.0, scale * 2)))))
+    n_p = n_w
+    S.close()
+    l0 = P.launch_count
     t0 = time.time()
-    draws, lp, st = api.hmc_chain(P, n_samples=40, n_warmup=20, config=api.HMCConfig(n_leapfrog=8), n_chains=min(Cn, 256), seed=2)
+    pilot = api.HmcSession(P, n_chains=Cn, n_warmup=n_p, config=api.HMCConfig(n_leapfrog=16), seed=1, q0=models.hierarchical_inits(truth, P.sites, Cn, 0.5, 0))
+    pilot.step(n_p)
+    q0 = pilot.position()
+    pilot.close()
+    t_pilot = time.time() - t0
+    t0 = time.time()
+    draws, lp, st = api.hmc_chain_dev(P, n_samples=n_s, n_warmup=n_w, config=api.HMCConfig(n_leapfrog=16, adapt_mass=True), n_chains=Cn, seed=2, q0=q0)
+    torch.cuda.synchronize()
+    t_run = time.time() - t0
+    launches = P.launch_count - l0
     t1 = time.time()
-    dg = api.diagnostics(draws)
-    out.update(diag_params=d, diag_seconds=time.time() - t1, rhat_median=float(np.nanmedian(dg["r_hat"])), ess_median=float(np.nanmedian(dg["ess"])))
+    dg = api.diagnostics_dev(draws)
+    t_diag = time.time() - t1
+    rh, ess = dg["r_hat"], dg["ess"]
+    out.update(run_shape=f"{Cn} chains x {n_w}+{n_s}, L=16, adapt_mass; q0 = end of a {n_p}-transition identity-mass pilot from jittered group means", pilot_seconds=t_pilot, run_seconds=t_run, run_launches=launches, draws_bytes_in_hbm=int(draws.numel() * 8),
+               diag_params=d, diag_seconds=t_diag, rhat_max=float(np.nanmax(rh)), rhat_median=float(np.nanmedian(rh)), rhat_n_ge_1_05=int(np.sum(~(rh < 1.05))),
+               ess_min=float(np.nanmin(ess)), ess_median=float(np.nanmedian(ess)), total_draws=int(n_s * Cn),
+               accept_run=float(st["n_accept"].mean() / (n_w + n_s)), divergent_frac=float(st["n_divergent"].mean() / (n_w + n_s)),
+               step_size_median=float(np.median(st["step_size"])),
+               mean_globals={k: float(v) for k, v in zip(P.sites, dg["mean"]) if not k.startswith("alpha")})
 elif which == "c5":
     N, Cn = int(4_000_000 * scale), int(65536 * scale)
     m, _ = models.poisson_glm(N=N, D=8)
