@@ -302,6 +302,49 @@ int32_t fc_diagnostics_dev(const double* d_draws, size_t S, size_t d, size_t C, 
   if (!d_draws) { fc::set_error("d_draws is NULL"); return FC_ERR_INVALID_ARGUMENT; }
   return fc::diagnostics_any(d_draws, true, S, d, C, what, h_mean, h_std, h_rhat, h_ess);
 }
+// ---- allocation-free split-R-hat --------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same kernels as
+// fc_diagnostics_dev's R-hat leg (k_seg_stats -> k_rhat_final); their per-(parameter, chain, half) means and
+// sums of squares live in the file-scope array below instead of a DevBuf. Every GPU that loads the library
+// holds the array (16 MiB) until exit; every call shares it, so calls that overlap on the GPU race.
+// Nothing in it has to start at zero: k_seg_stats overwrites every entry k_rhat_final reads.
+static __device__ __align__(256) double g_rhat_noalloc_scratch[2 * FC_RHAT_NOALLOC_MAX_SEGMENTS];
+int32_t fc_split_rhat_dev_noalloc(const double* d_draws, size_t S, size_t d, size_t C, double* d_rhat, void* stream) {
+  using namespace fc;
+  if (d == 0) return FC_OK;
+  if (!d_rhat || (!d_draws && S > 0 && C > 0)) { set_error("fc_split_rhat_dev_noalloc: NULL device pointer"); return FC_ERR_INVALID_ARGUMENT; }
+  const int nseg = (S / 2 > 0) ? 2 : 1;
+  const size_t m = (size_t)nseg * C;
+  if (m != 0 && d > (size_t)FC_RHAT_NOALLOC_MAX_SEGMENTS / m) {
+    set_error("fc_split_rhat_dev_noalloc: d * segments per parameter = %zu * %zu exceeds the static scratch of %zu segments (FC_RHAT_NOALLOC_MAX_SEGMENTS); use fc_diagnostics_dev",
+              d, m, (size_t)FC_RHAT_NOALLOC_MAX_SEGMENTS);
+    return FC_ERR_INVALID_ARGUMENT;
+  }
+  // the array's name is a host-side stand-in here: resolve its device address once per device, with that device current
+  static double* scratch_of_device[64] = {nullptr};
+  int dev = -1;
+  FC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { set_error("fc_split_rhat_dev_noalloc: device ordinal out of range"); return FC_ERR_INVALID_ARGUMENT; }
+  if (!scratch_of_device[dev]) {
+    double* ptr = nullptr;
+    FC_CUDA(cudaGetSymbolAddress((void**)&ptr, g_rhat_noalloc_scratch));
+    scratch_of_device[dev] = ptr;
+  }
+  double* mean = scratch_of_device[dev];
+  double* ss = mean + FC_RHAT_NOALLOC_MAX_SEGMENTS;
+  cudaStream_t st = (cudaStream_t)stream;
+  Draws D{d_draws, (int64_t)S, (int64_t)d, (int64_t)C};
+  const double n = S == 0 ? 0.0 : (nseg == 2 ? (double)(S / 2) : (double)S);
+  for (size_t k0 = 0; k0 < d; k0 += 32768) {  // gridDim.y limit
+    const int64_t nk = (int64_t)std::min<size_t>(32768, d - k0);
+    if (S > 0 && C > 0) k_seg_stats<<<dim3((unsigned)cdiv((int64_t)C, 128), (unsigned)nk), 128, 0, st>>>(D, (int64_t)k0, nk, 1, mean + k0 * m, ss + k0 * m);
+    k_rhat_final<<<(unsigned)cdiv(nk, 64), 64, 0, st>>>(mean + k0 * m, ss + k0 * m, nk, (int64_t)m, n, d_rhat + k0);
+    FC_KERNEL_CHECK();
+  }
+  return FC_OK;
+}
+
 // Per-rank partial statistics for multi-GPU R-hat / ESS: split-half means and sums of
 // squares per chain, chain means, and the chain-SUM of autocovariances per lag. A rank holds
 // C_local chains; the cross-rank combine needs only all-reduces of O(d * (lags + 3)) doubles

@@ -400,6 +400,21 @@ int32_t fc_diagnostics(const double* h_draws, size_t S, size_t d, size_t C, doub
  * mcmc_utils.rs:231-339 run in place, 4*d doubles come back. */
 int32_t fc_diagnostics_dev(const double* d_draws, size_t S, size_t d, size_t C, double* h_mean,
                            double* h_std, double* h_rhat, double* h_ess);
+/* Allocation-free split-R-hat of draws resident in HBM. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). The same kernels as fc_diagnostics_dev's
+ * R-hat leg, with their scratch (per parameter x chain x half: mean and sum of squares) in a
+ * file-scope static __device__ array of 2 * FC_RHAT_NOALLOC_MAX_SEGMENTS doubles (16 MiB, held by
+ * every GPU that loads the library until exit). d_draws [S][d][C] and d_rhat [d] are DEVICE pointers
+ * on the current device; the work is enqueued on `stream` (a cudaStream_t; NULL = the default
+ * stream) and the call returns without synchronising. It calls no cudaMalloc / cudaFree or
+ * allocating library routine. d * 2 * C > FC_RHAT_NOALLOC_MAX_SEGMENTS -> FC_ERR_INVALID_ARGUMENT
+ * (use fc_diagnostics_dev). Every call shares the one array: calls that overlap on the GPU (two
+ * streams, two threads) race; calls on one stream are safe back to back. The first call on each
+ * device resolves the array's address (cudaGetSymbolAddress): make it before starting a capture. */
+#define FC_RHAT_NOALLOC_MAX_SEGMENTS (1u << 20)
+int32_t fc_split_rhat_dev_noalloc(const double* d_draws, size_t S, size_t d, size_t C,
+                                  double* d_rhat, void* stream);
 
 /* Per-rank partial statistics for multi-GPU R-hat / ESS (chains sharded over ranks): split-half
  * means / sums of squares per chain [d][2C], chain means [d][C], and chain-summed autocovariances
