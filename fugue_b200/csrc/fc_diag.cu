@@ -158,6 +158,7 @@ __global__ void k_pool(const double* __restrict__ part, int64_t C, int64_t nk, d
   out[k] = do_sqrt ? sqrt(s) : s;
 }
 
+constexpr int64_t kMaxGridY = 65535;  // parameters of one batch ride on gridDim.y
 struct DiagWork {
   DevBuf<double> x, a, b, cen, acov, lagsum, rh, out;
 };
@@ -175,7 +176,7 @@ static int32_t diagnostics_dev(const double* d_draws, int64_t S, int64_t d, int6
     int nseg = (split && half > 0) ? 2 : 1;
     int64_t m = nseg * C;
     double n = (nseg == 2) ? (double)half : (double)S;
-    int64_t batch = std::max<int64_t>(1, std::min<int64_t>(d, (int64_t)(1 << 24) / std::max<int64_t>(1, m)));
+    int64_t batch = std::max<int64_t>(1, std::min<int64_t>(kMaxGridY, std::min<int64_t>(d, (int64_t)(1 << 24) / std::max<int64_t>(1, m))));
     FC_CUDA(W.a.reserve(batch * m)); FC_CUDA(W.b.reserve(batch * m));
     for (int64_t k0 = 0; k0 < d; k0 += batch) {
       int64_t nk = std::min(batch, d - k0);
@@ -187,7 +188,7 @@ static int32_t diagnostics_dev(const double* d_draws, int64_t S, int64_t d, int6
   }
   // ---- pooled mean / std ----
   if (what & 8) {
-    int64_t batch = std::max<int64_t>(1, std::min<int64_t>(d, (int64_t)(1 << 24) / std::max<int64_t>(1, C)));
+    int64_t batch = std::max<int64_t>(1, std::min<int64_t>(kMaxGridY, std::min<int64_t>(d, (int64_t)(1 << 24) / std::max<int64_t>(1, C))));
     FC_CUDA(W.a.reserve(batch * C));
     for (int64_t k0 = 0; k0 < d; k0 += batch) {
       int64_t nk = std::min(batch, d - k0);
@@ -209,7 +210,7 @@ static int32_t diagnostics_dev(const double* d_draws, int64_t S, int64_t d, int6
     }
     int64_t max_lag = std::min<int64_t>(S - 1, 2048);  // mcmc_utils.rs:266
     int64_t per_param = (max_lag + 1 + S) * C;
-    int64_t batch = std::max<int64_t>(1, std::min<int64_t>(d, (int64_t)(1 << 26) / std::max<int64_t>(1, per_param)));
+    int64_t batch = std::max<int64_t>(1, std::min<int64_t>(kMaxGridY, std::min<int64_t>(d, (int64_t)(1 << 26) / std::max<int64_t>(1, per_param))));
     FC_CUDA(W.cen.reserve(batch * S * C)); FC_CUDA(W.acov.reserve(batch * (max_lag + 1) * C));
     FC_CUDA(W.a.reserve(batch * C)); FC_CUDA(W.lagsum.reserve(batch * (max_lag + 1))); FC_CUDA(W.rh.reserve(batch * (max_lag + 1)));
     for (int64_t k0 = 0; k0 < d; k0 += batch) {
@@ -368,7 +369,7 @@ int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, do
   int64_t max_lag = std::min<int64_t>((int64_t)S - 1, 2048);
   bool do_acov = h_lagsum && S >= 4;
   int64_t per_param = m * 2 + (do_acov ? ((max_lag + 1 + (int64_t)S) * (int64_t)C) : 0);
-  int64_t batch = std::max<int64_t>(1, std::min<int64_t>((int64_t)d, (int64_t)(1 << 26) / std::max<int64_t>(1, per_param)));
+  int64_t batch = std::max<int64_t>(1, std::min<int64_t>(kMaxGridY, std::min<int64_t>((int64_t)d, (int64_t)(1 << 26) / std::max<int64_t>(1, per_param))));
   FC_CUDA(W.a.reserve(batch * m)); FC_CUDA(W.b.reserve(batch * m));
   if (do_acov) { FC_CUDA(W.cen.reserve(batch * S * C)); FC_CUDA(W.acov.reserve(batch * (max_lag + 1) * C)); FC_CUDA(W.lagsum.reserve(batch * (max_lag + 1))); FC_CUDA(W.out.reserve(batch * C)); }
   for (int64_t k0 = 0; k0 < (int64_t)d; k0 += batch) {

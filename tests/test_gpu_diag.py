@@ -61,3 +61,16 @@ def test_all_parameters_at_once_and_summary():
     srt = np.sort(x[:, 2, :].reshape(-1))
     assert sm["quantiles"]["50%"] == srt[int(round((srt.size - 1) * 0.5))]
     assert sm["quantiles"]["2.5%"] <= sm["quantiles"]["25%"] <= sm["quantiles"]["75%"] <= sm["quantiles"]["97.5%"]
+
+
+def test_many_parameters_few_chains():
+    """d beyond one launch's gridDim.y (65 535 parameters per batch): batches must tile it."""
+    from fugue_b200 import api
+    rng = np.random.default_rng(8)
+    S, d, Cn = 8, 70001, 2
+    x = rng.standard_normal((S, d, Cn))
+    dg = api.diagnostics(x)
+    for k in (0, 65534, 65535, 65536, d - 1):
+        assert abs(dg["r_hat"][k] - oracle.split_rhat(x[:, k, :])) <= 1e-12 * dg["r_hat"][k]
+        assert abs(dg["ess"][k] - oracle.ess_multichain(x[:, k, :])) <= 1e-9 * dg["ess"][k]
+        assert abs(dg["mean"][k] - x[:, k, :].mean()) < 1e-13
