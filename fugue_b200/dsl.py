@@ -1,10 +1,10 @@
 """Text front-end: the `prob!`-subset model language of the reference's playground, lowered to the
 flat op list of include/fugue_cuda.h instead of being interpreted into closures.
 
-Grammar, tokens, arities, error texts and the total-evaluation policy follow
-/root/reference/crates/fugue-wasm/src/dsl.rs (grammar :10-20, lexer :150-257, parser :338-447 and
-:497-655, static validation :657-692, evaluation of constant expressions :714-803, distribution
-table :807-818, soft errors :926-944 and :1002-1007, data binding :1055-1107):
+The language is the one /root/reference/crates/fugue-wasm/src/dsl.rs documents (grammar :10-20,
+distribution table :807-818, evaluation policy of constant expressions :714-803, soft errors :926-944
+and :1002-1007, data binding :1055-1107); its syntax lives in dsl_syntax.py (tokens, productions as
+data, precedence climbing), this file is the lowering:
 
     let p <- sample(addr!("p"), Beta(2.0, 2.0));
     for i in 0..data.len() {
@@ -36,374 +36,8 @@ from . import _ir, model as M
 from ._ir import FugueError
 
 
-class DslError(ValueError):
-    """A static (compile-time) error of the model text; the message follows dsl.rs."""
-
-
-# ---------------------------------------------------------------------------------------------
-# Lexer (dsl.rs:150-257)
-# ---------------------------------------------------------------------------------------------
-SYMS = ["<-", "::", "..", "(", ")", "{", "}", "[", "]", ",", ";", "+", "-", "*", "/", "=", ".", "!"]
-
-
-class _Lexer:
-    def __init__(self, src):
-        self.toks, self.pos = [], 0  # (kind, value, byte offset); kind in ident | num | str | sym | eof
-        self.line_starts = [0] + [i + 1 for i, ch in enumerate(src) if ch == "\n"]
-        i, n = 0, len(src)
-        while i < n:
-            c = src[i]
-            if c.isspace():
-                i += 1
-                continue
-            if c == "/" and src[i + 1:i + 2] == "/":
-                while i < n and src[i] != "\n":
-                    i += 1
-                continue
-            if c == '"':
-                j = src.find('"', i + 1)
-                if j < 0:
-                    raise DslError(f"unterminated string at byte {i}")
-                self.toks.append(("str", src[i + 1:j], i))
-                i = j + 1
-                continue
-            if c.isascii() and c.isdigit():
-                start, dotted = i, False
-                while i < n:
-                    d = src[i]
-                    if d.isascii() and d.isdigit():
-                        i += 1
-                    elif d == "." and not dotted and src[i + 1:i + 2].isdigit():
-                        dotted = True  # `0..n` must lex as Num(0) '..' ident
-                        i += 1
-                    elif d in "eE" and (src[i + 1:i + 2].isdigit() or src[i + 1:i + 2] in ("-", "+")) and src[i + 1:i + 2] != "":
-                        dotted = True
-                        i += 2
-                        while i < n and src[i].isdigit():
-                            i += 1
-                        break
-                    else:
-                        break
-                text = src[start:i]
-                try:
-                    v = float(text)
-                except ValueError:
-                    raise DslError(f"bad number `{text}` at byte {start}")
-                self.toks.append(("num", (v, dotted), start))
-                continue
-            if (c.isascii() and c.isalpha()) or c == "_":
-                start = i
-                while i < n and ((src[i].isascii() and src[i].isalnum()) or src[i] == "_"):
-                    i += 1
-                self.toks.append(("ident", src[start:i], start))
-                continue
-            for s in SYMS:
-                if src.startswith(s, i):
-                    self.toks.append(("sym", s, i))
-                    i += len(s)
-                    break
-            else:
-                raise DslError(f"unexpected character `{c}` at byte {i}")
-        self.toks.append(("eof", None, len(src)))
-
-    def line_of(self, byte):
-        import bisect
-        k = bisect.bisect_left(self.line_starts, byte)
-        return k + 1 if k < len(self.line_starts) and self.line_starts[k] == byte else k
-
-    def peek(self):
-        return self.toks[self.pos][:2]
-
-    def peek2(self):
-        return self.toks[min(self.pos + 1, len(self.toks) - 1)][:2]
-
-    def next(self):
-        t = self.toks[self.pos][:2]
-        if self.pos < len(self.toks) - 1:
-            self.pos += 1
-        return t
-
-    def err(self, what):
-        kind, val, byte = self.toks[self.pos]
-        found = {"ident": lambda: f"`{val}`", "num": lambda: f"`{_fmt_num(val[0])}`", "str": lambda: f'"{val}"',
-                 "sym": lambda: f"`{val}`", "eof": lambda: "end of input"}[kind]()
-        return DslError(f"line {self.line_of(byte)}: expected {what}, found {found}")
-
-    def expect_sym(self, s):
-        if self.peek() == ("sym", s):
-            self.next()
-        else:
-            raise self.err(f"`{s}`")
-
-    def expect_ident(self):
-        k, v = self.peek()
-        if k != "ident":
-            raise self.err("an identifier")
-        self.next()
-        return v
-
-    def eat_kw(self, kw):
-        if self.peek() == ("ident", kw):
-            self.next()
-            return True
-        return False
-
-
-def _fmt_num(v):
-    return str(int(v)) if float(v).is_integer() and abs(v) < 1e16 else repr(v)
-
-
-# ---------------------------------------------------------------------------------------------
-# Parser (dsl.rs:338-655). AST nodes are tuples:
-#   expr: ("num", v) ("int", i) ("bool", b) ("var", n) ("index", a, i) ("len", a) ("neg", a)
-#         ("bin", op, a, b) ("call", f, [args])
-#   stmt: ("sample", name, addr, dist) ("let", name, expr) ("observe", addr, dist, value)
-#         ("factor", expr) ("for", var, lo, hi, [body])
-#   addr: (name, index_expr | None); dist: (name, [args])
-# ---------------------------------------------------------------------------------------------
-MATH_FNS = {"exp": 1, "ln": 1, "log": 1, "sqrt": 1, "abs": 1, "floor": 1, "sin": 1, "cos": 1, "tanh": 1, "pow": 2, "min": 2, "max": 2}
-
-# (min_args, max_args) per distribution; Categorical is variadic (dsl.rs:807-818)
-DIST_ARITY = {**{d: (2, 2) for d in ("Normal", "Uniform", "LogNormal", "Beta", "Gamma", "InverseGamma", "Cauchy", "Laplace", "Weibull",
-                                     "Binomial", "DiscreteUniform")},
-              **{d: (1, 1) for d in ("Exponential", "Poisson", "Bernoulli", "ChiSquared")}, "StudentT": (3, 3), "Categorical": (1, 64)}
-
-
-def _parse_program(src):
-    lx = _Lexer(src)
-    stmts = []
-    while True:
-        if lx.eat_kw("pure"):
-            lx.expect_sym("(")
-            ret = _parse_expr(lx)
-            lx.expect_sym(")")
-            if lx.peek() == ("sym", ";"):
-                lx.next()  # optional trailing semicolon
-            if lx.peek()[0] != "eof":
-                raise lx.err("end of input after `pure(..)`")
-            return stmts, ret
-        if lx.peek()[0] == "eof":
-            raise DslError("model must end with `pure(<expr>)`")
-        stmts.append(_parse_stmt(lx))
-
-
-def _parse_stmt(lx):
-    if lx.eat_kw("let"):
-        name = lx.expect_ident()
-        if lx.peek() == ("sym", "<-"):
-            lx.next()
-            if not lx.eat_kw("sample"):
-                raise lx.err("`sample`")
-            lx.expect_sym("(")
-            addr = _parse_addr(lx)
-            lx.expect_sym(",")
-            dist = _parse_dist(lx)
-            lx.expect_sym(")")
-            lx.expect_sym(";")
-            return ("sample", name, addr, dist)
-        lx.expect_sym("=")
-        e = _parse_expr(lx)
-        lx.expect_sym(";")
-        return ("let", name, e)
-    if lx.eat_kw("observe"):
-        lx.expect_sym("(")
-        addr = _parse_addr(lx)
-        lx.expect_sym(",")
-        dist = _parse_dist(lx)
-        lx.expect_sym(",")
-        value = _parse_expr(lx)
-        lx.expect_sym(")")
-        lx.expect_sym(";")
-        return ("observe", addr, dist, value)
-    if lx.eat_kw("factor"):
-        lx.expect_sym("(")
-        e = _parse_expr(lx)
-        lx.expect_sym(")")
-        lx.expect_sym(";")
-        return ("factor", e)
-    if lx.eat_kw("for"):
-        var = lx.expect_ident()
-        if not lx.eat_kw("in"):
-            raise lx.err("`in`")
-        lo = _parse_expr(lx)
-        lx.expect_sym("..")
-        hi = _parse_expr(lx)
-        lx.expect_sym("{")
-        body = []
-        while lx.peek() != ("sym", "}"):
-            if lx.peek()[0] == "eof":
-                raise lx.err("`}`")
-            body.append(_parse_stmt(lx))
-        lx.next()
-        return ("for", var, lo, hi, body)
-    raise lx.err("a statement (`let`, `observe`, `factor`, `for`, or `pure`)")
-
-
-def _parse_addr(lx):
-    if not lx.eat_kw("addr"):
-        raise lx.err("`addr!(..)`")
-    lx.expect_sym("!")
-    lx.expect_sym("(")
-    k, v = lx.peek()
-    if k != "str":
-        raise lx.err("a string literal address name")
-    lx.next()
-    index = None
-    if lx.peek() == ("sym", ","):
-        lx.next()
-        index = _parse_expr(lx)
-    lx.expect_sym(")")
-    return (v, index)
-
-
-def _parse_dist(lx):
-    name = lx.expect_ident()
-    if lx.peek() == ("sym", "::"):
-        lx.next()
-        m = lx.expect_ident()
-        if m != "new":
-            raise DslError(f"unknown distribution constructor `{name}::{m}`")
-    lx.expect_sym("(")
-    args = []
-    if lx.peek() != ("sym", ")"):
-        while True:
-            args.append(_parse_expr(lx))
-            if lx.peek() == ("sym", ","):
-                lx.next()
-            else:
-                break
-    lx.expect_sym(")")
-    if lx.peek() == ("sym", ".") and lx.peek2() == ("ident", "unwrap"):  # optional Rust-ism
-        lx.next(); lx.next()
-        lx.expect_sym("(")
-        lx.expect_sym(")")
-    if name not in DIST_ARITY:
-        raise DslError(f"unknown distribution `{name}`")
-    lo, hi = DIST_ARITY[name]
-    if not (lo <= len(args) <= hi):
-        raise DslError(f"`{name}` takes {lo if lo == hi else f'{lo}..={hi}'} argument(s), got {len(args)}")
-    return (name, args)
-
-
-def _parse_expr(lx):
-    lhs = _parse_mul(lx)
-    while lx.peek() in (("sym", "+"), ("sym", "-")):
-        op = lx.next()[1]
-        lhs = ("bin", op, lhs, _parse_mul(lx))
-    return lhs
-
-
-def _parse_mul(lx):
-    lhs = _parse_unary(lx)
-    while lx.peek() in (("sym", "*"), ("sym", "/")):
-        op = lx.next()[1]
-        lhs = ("bin", op, lhs, _parse_unary(lx))
-    return lhs
-
-
-def _parse_unary(lx):
-    if lx.peek() == ("sym", "-"):
-        lx.next()
-        return ("neg", _parse_unary(lx))
-    return _parse_postfix(lx)
-
-
-def _parse_postfix(lx):
-    e = _parse_primary(lx)
-    while True:
-        if lx.peek() == ("sym", "["):
-            lx.next()
-            idx = _parse_expr(lx)
-            lx.expect_sym("]")
-            e = ("index", e, idx)
-        elif lx.peek() == ("sym", ".") and lx.peek2() == ("ident", "len"):
-            lx.next(); lx.next()
-            lx.expect_sym("(")
-            lx.expect_sym(")")
-            e = ("len", e)
-        else:
-            return e
-
-
-def _parse_primary(lx):
-    k, v = lx.peek()
-    if k == "num":
-        lx.next()
-        return ("num", v[0]) if v[1] else ("int", int(v[0]))
-    if (k, v) == ("sym", "("):
-        lx.next()
-        e = _parse_expr(lx)
-        lx.expect_sym(")")
-        return e
-    if k == "ident":
-        lx.next()
-        if v in ("true", "false"):
-            return ("bool", v == "true")
-        if lx.peek() == ("sym", "("):
-            if v not in MATH_FNS:
-                raise DslError(f"unknown function `{v}`")
-            lx.next()
-            args = []
-            if lx.peek() != ("sym", ")"):
-                while True:
-                    args.append(_parse_expr(lx))
-                    if lx.peek() == ("sym", ","):
-                        lx.next()
-                    else:
-                        break
-            lx.expect_sym(")")
-            if len(args) != MATH_FNS[v]:
-                raise DslError(f"`{v}` takes {MATH_FNS[v]} argument(s)")
-            return ("call", v, args)
-        return ("var", v)
-    raise lx.err("an expression")
-
-
-# ---- static validation of names (dsl.rs:657-692) ----
-def _check_expr(e, scope):
-    t = e[0]
-    if t == "var":
-        if e[1] not in scope:
-            raise DslError(f"unknown variable `{e[1]}`")
-    elif t in ("index", "bin"):
-        for a in e[-2:]:
-            _check_expr(a, scope)
-    elif t in ("len", "neg"):
-        _check_expr(e[1], scope)
-    elif t == "call":
-        for a in e[2]:
-            _check_expr(a, scope)
-
-
-def _check_stmts(stmts, scope):
-    for s in stmts:
-        if s[0] == "sample":
-            _, name, (an, ai), (dn, dargs) = s
-            if ai is not None:
-                _check_expr(ai, scope)
-            for a in dargs:
-                _check_expr(a, scope)
-            scope.append(name)
-        elif s[0] == "let":
-            _check_expr(s[2], scope)
-            scope.append(s[1])
-        elif s[0] == "observe":
-            _, (an, ai), (dn, dargs), value = s
-            if ai is not None:
-                _check_expr(ai, scope)
-            for a in dargs:
-                _check_expr(a, scope)
-            _check_expr(value, scope)
-        elif s[0] == "factor":
-            _check_expr(s[1], scope)
-        else:
-            _, var, lo, hi, body = s
-            _check_expr(lo, scope)
-            _check_expr(hi, scope)
-            depth = len(scope)
-            scope.append(var)
-            _check_stmts(body, scope)
-            del scope[depth:]
+from .dsl_syntax import DslError, MATH_FNS, DIST_ARITY, _fmt_num  # noqa: F401 (re-exported)
+from .dsl_syntax import parse_program as _parse_program, check_stmts as _check_stmts, check_expr as _check_expr
 
 
 # ---------------------------------------------------------------------------------------------
@@ -713,18 +347,19 @@ class _Lowering:
                 raise _unsupported("DiscreteUniform bounds depend on a latent")
             p = [float(int(v)) if math.isfinite(v) else v for v in p]  # `a[0] as i64`
         if name == "Categorical":
-            # the device Categorical is the two-way [p, 1-p] form (deviation 6)
-            if len(p) != 2:
-                raise _unsupported(f"Categorical with {len(p)} categories (the device form is two-way)")
-            if isinstance(p[0], _ir.Expr) or isinstance(p[1], _ir.Expr):
+            # constant probabilities: K-way (fc_op.probs_col); latent ones: the two-way [p, 1-p] form
+            latent = [isinstance(v, _ir.Expr) for v in p]
+            if any(latent):
+                if len(p) != 2:
+                    raise _unsupported(f"Categorical with {len(p)} latent-dependent categories (the latent form is two-way)")
                 a0, a1 = arg_asts
                 comp = a1[0] == "bin" and a1[1] == "-" and a1[2][0] in ("num", "int") and float(a1[2][1]) == 1.0 and a1[3] == a0
                 if not comp:
                     raise _unsupported("Categorical(p, q) with latent probabilities needs q written as `1.0 - p`")
                 return M.Categorical(p[0])
-            if not (all(math.isfinite(v) and v >= 0.0 for v in p) and abs(p[0] + p[1] - 1.0) <= 1e-6):  # distribution.rs:679-713
+            if not (all(math.isfinite(v) and v >= 0.0 for v in p) and abs(sum(p) - 1.0) <= 1e-6):  # distribution.rs:679-713
                 raise FugueError(102, f"Categorical probabilities must be non-negative and sum to 1, got {p}")
-            return M.Categorical(p[0])
+            return M.Categorical(p[0]) if len(p) == 2 else M.Categorical([float(v) for v in p])
         return getattr(M, name)(*p)
 
     @staticmethod

@@ -289,3 +289,66 @@ def test_grammar_doc_example_on_device():
     grid = np.linspace(1e-4, 1 - 1e-4, 4001)[None, :]
     w = np.exp(sum(O.logp(grid)) - sum(O.logp(grid)).max())
     assert abs(p.mean() - (w * grid[0]).sum() / w.sum()) < 0.01
+
+
+def test_syntax_module_tokens_precedence_and_messages():
+    """fugue_b200/dsl_syntax.py on its own: tokens of `0..n`, exponent numbers, associativity and binding
+    powers, postfix forms, and the wording of the static errors (dsl.rs:1248-1269 behaviour)."""
+    from fugue_b200 import dsl_syntax as sx
+    toks = sx.tokenize("for i in 0..xs.len() { } // tail\n1.5e-3 2E4 7")
+    assert [(t.kind, t.value) for t in toks[:9]] == [("ident", "for"), ("ident", "i"), ("ident", "in"), ("num", 0), ("sym", ".."),
+                                                      ("ident", "xs"), ("sym", "."), ("ident", "len"), ("sym", "(")]
+    assert [t.value for t in toks if t.kind == "num"] == [0, 1.5e-3, 2e4, 7] and isinstance(toks[-2].value, int)
+    e = sx.Parser("a - b - c * -d[i + 1] / xs.len()").p_expr()
+    assert e == ("bin", "-", ("bin", "-", ("var", "a"), ("var", "b")),
+                 ("bin", "/", ("bin", "*", ("var", "c"), ("neg", ("index", ("var", "d"), ("bin", "+", ("var", "i"), ("int", 1))))), ("len", ("var", "xs"))))
+    assert sx.Parser("pow(2.0, (x))").p_expr() == ("call", "pow", [("num", 2.0), ("var", "x")])
+    stmts, ret = sx.parse_program('for i in 0..3 { let t = i; factor(t); }\nlet z <- sample(addr!("z", 2), Categorical(0.2, 0.3, 0.5)); pure(z);')
+    assert stmts[0][0] == "for" and stmts[0][4][0] == ("let", "t", ("var", "i")) and stmts[1] == ("sample", "z", ("z", ("int", 2)), ("Categorical", [("num", 0.2), ("num", 0.3), ("num", 0.5)]))
+    for text, msg in (('let x <- sample(addr!("x") Normal(0,1)); pure(x)', 'line 1: expected `,`, found `Normal`'),
+                      ("let x <- draw(1); pure(x)", "line 1: expected `sample`, found `draw`"),
+                      ("for i 0..3 { } pure(1)", "line 1: expected `in`, found `0`"),
+                      ("for i in 0..3 { factor(1.0);", "line 1: expected `}`, found end of input"),
+                      ('observe(addr!(x), Normal(0,1), 1.0); pure(1)', "line 1: expected a string literal address name, found `x`"),
+                      ("pure(1) pure(2)", "line 1: expected end of input after `pure(..)`, found `pure`"),
+                      ("\n\nwhile", "line 3: expected a statement (`let`, `observe`, `factor`, `for`, or `pure`), found `while`"),
+                      ("let x = ;", "line 1: expected an expression, found `;`"),
+                      ("let x = 1.0;", "model must end with `pure(<expr>)`"),
+                      ('let s = "abc', "unterminated string at byte 8"),
+                      ("let s = 1 # 2;", "unexpected character `#` at byte 10"),
+                      ("pure(sqrt(1, 2))", "`sqrt` takes 1 argument(s)"),
+                      ("pure(nope(1))", "unknown function `nope`"),
+                      ('let x <- sample(addr!("x"), Normal::with(0, 1)); pure(x)', "unknown distribution constructor `Normal::with`"),
+                      ('let x <- sample(addr!("x"), StudentT(1.0)); pure(x)', "`StudentT` takes 3 argument(s), got 1")):
+        with pytest.raises(dsl.DslError) as err:
+            sx.parse_program(text)
+        assert str(err.value) == msg, (text, str(err.value))
+    # scoping: a loop's variable and its lets end with the loop
+    stmts, ret = sx.parse_program("for i in 0..2 { let t = i; } pure(t)")
+    scope = []
+    sx.check_stmts(stmts, scope)
+    with pytest.raises(dsl.DslError, match="unknown variable `t`"):
+        sx.check_expr(ret, scope)
+
+
+def test_k_way_categorical_lowers_to_a_probability_column():
+    """Categorical(p0, .., pK-1) with constant probabilities (distribution.rs:679-713) is K-way on the device
+    (fc_op.probs_col); the latent-dependent form stays two-way; invalid vectors are ErrorCode 102."""
+    cm = dsl.compile('let z <- sample(addr!("z"), Categorical(0.2, 0.3, 0.5)); observe(addr!("c"), Categorical(0.1, 0.2, 0.3, 0.4), 3); pure(z)', "")
+    ops = cm.builder.ops
+    assert [k for k, _, _ in _kinds(cm)] == [KIND_SAMPLE, KIND_OBSERVE]
+    assert np.allclose(ops[0]["dist"].probs, [0.2, 0.3, 0.5]) and np.allclose(ops[1]["dist"].probs, [0.1, 0.2, 0.3, 0.4]) and ops[1]["value"] == 3.0
+    bad = dsl.compile('let z <- sample(addr!("z"), Categorical(0.2, 0.3, 0.6)); pure(z)', "")  # soft error (dsl.rs:926-944)
+    assert [op["value"] for op in bad.builder.ops if op["kind"] == KIND_FACTOR] == [-math.inf] and "sum to 1" in bad.take_warnings()[0]
+    with pytest.raises(FugueError) as e:
+        dsl.compile('let p <- sample(addr!("p"), Beta(1.0, 1.0)); let z <- sample(addr!("z"), Categorical(p, 0.5, 0.5)); pure(z)', "")
+    assert e.value.code == 1000
+
+
+@pytest.mark.gpu
+def test_k_way_categorical_density_on_device():
+    from fugue_b200 import api
+    cm = dsl.compile('let z <- sample(addr!("z"), Categorical(0.2, 0.3, 0.5)); pure(z)', "")
+    P = api.Program(cm)
+    lp = P.logp(np.zeros((0, 4)), np.array([[0, 1, 2, 3]]))[0]
+    assert np.allclose(lp[:3], np.log([0.2, 0.3, 0.5]), rtol=1e-14) and lp[3] == -math.inf
