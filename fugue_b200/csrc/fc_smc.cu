@@ -713,7 +713,7 @@ __global__ void k_chain_collect(const __grid_constant__ Comm cm, unsigned long l
 // the population container and the fused per-particle kernels
 // =============================================================================================
 struct Pop {
-  uint8_t* rec;   // [n][pitch]: { q[d_cont] | lp3[3] | pad | z[d_disc * zw] | pad }
+  uint8_t* rec;   // [n][pitch]: { q[d_cont] | lp3[3] | mixture statistics[5] (when soff) | pad | z[d_disc * zw] | pad }
   double* ll;     // [n] log-likelihood + log-factors of the particle (particle_log_likelihood, smc.rs:381-383)
   int64_t n;
 };
@@ -721,7 +721,8 @@ struct RecLayout {
   int64_t pitch;    // bytes per record (multiple of 16)
   int64_t zoff;     // byte offset of the discrete sites (multiple of 16)
   int64_t d_cont, d_disc;
-  int32_t zw, _pad;
+  int32_t zw;       // bytes per discrete site: 1 or 4; 0 = ONE BIT per site (every discrete site two-valued)
+  int32_t soff;     // byte offset of the mixture plate's sufficient statistics (5 doubles), 0 = none
   __host__ __device__ __forceinline__ double* q(uint8_t* r) const { return (double*)r; }
   __host__ __device__ __forceinline__ double* lp3(uint8_t* r) const { return (double*)r + d_cont; }
   __host__ __device__ __forceinline__ uint8_t* z(uint8_t* r) const { return r + zoff; }
@@ -729,7 +730,10 @@ struct RecLayout {
 struct ZAcc {  // discrete value of a program slot for one particle
   const uint8_t* rec;
   int zw;
-  __device__ __forceinline__ long long operator()(int dslot) const { return zw == 1 ? (long long)rec[dslot] : (long long)((const int32_t*)rec)[dslot]; }
+  __device__ __forceinline__ long long operator()(int dslot) const {
+    if (zw == 0) return (long long)((rec[dslot >> 3] >> (dslot & 7)) & 1u);
+    return zw == 1 ? (long long)rec[dslot] : (long long)((const int32_t*)rec)[dslot];
+  }
 };
 
 // plates the fused evaluator understands (lowered from the program's DOps at session create)
@@ -740,6 +744,7 @@ struct FPlate {
   int32_t op, op_b;     // index into all_ops (FP_MIX: op = the discrete sample plate, op_b = the Normal observe)
   int32_t m0, m1, ss;   // Normal observe: kinds of the (up to two) element-dependent mean terms; sigma is base + SELECT2
   int32_t mt0, mt1, st; // their term indices
+  int32_t stat, _pad;   // FP_MIX: the record carries this plate's per-component sufficient statistics
 };
 // scalar ops compiled for the fused evaluator: priors with constant parameters of the three families the
 // BASELINE models use become a few FP64 instructions; everything else goes through the interpreter
@@ -758,6 +763,38 @@ struct FusedProg {
   int32_t n_ops, n_scalar, n_plates, _pad;
   RecLayout L;
 };
+
+// The commonest fused program -- scalar priors of the compiled families plus ONE mixture plate whose
+// statistics travel in the record -- flattened into a by-value kernel argument: the move kernel then reads
+// its whole "program" from the constant bank (no descriptor loads, no term-kind dispatch), and its
+// arithmetic is the interpreter's, operation for operation (same results bit for bit).
+struct CParam {            // link(sum of up to 3 chain-constant terms), as chain_const_param evaluates it
+  double c[3];
+  int32_t row[3];          // >= 0: c * q[row]; -1: the constant c; -2: unused
+  int32_t link, apply;
+  double lo, hi;
+};
+#define CM_MAX_SOP 8
+#define CM_HOT_MAX 8      // 16-byte chunks of a record's head staged per particle by the compiled move kernel
+#define CM_SROW (2 * CM_HOT_MAX + 1)
+struct CompiledMix {
+  int32_t on, n_sop;
+  SOp sop[CM_MAX_SOP];
+  int32_t dist, n;         // the two-valued plate: FC_BERNOULLI or FC_CATEGORICAL [p, 1-p]; plate length
+  int32_t m0, ss;          // Normal observe: mean / sigma picked by z
+  int32_t row_ma, row_mb, row_sa, row_sb, soff, hot_chunks;  // hot_chunks: ceil((soff + 40) / 16)
+  CParam p0, mean, sigma;
+};
+__device__ __forceinline__ double cparam_eval(const CParam& P, const double* __restrict__ q) {
+  double s = 0.0;
+#pragma unroll
+  for (int t = 0; t < 3; t++) {
+    if (P.row[t] == -1) s += P.c[t];
+    else if (P.row[t] >= 0) s += P.c[t] * q[P.row[t]];
+  }
+  if (P.apply) { double dl; s = apply_link(P.link, s, P.lo, P.hi, dl); }
+  return s;
+}
 
 // In the fused kernels a particle's f64 sites are the first d_cont doubles of its record, so the scoring
 // helpers written for the [row][chain] layout are called with (q = record, C = 1, c = 0).
@@ -800,6 +837,42 @@ __device__ __forceinline__ double normal_elem(const NormalSetup& S, const FPlate
   const bool useb = fp.ss && zs;
   const double z = (x - mean) * (useb ? S.inv_b : S.inv_a);
   return fma(-0.5 * z, z, useb ? S.c_b : S.c_a);
+}
+
+// Sufficient statistics of a mixture plate for one particle. The discrete sites never move in a tempered
+// rejuvenation move (smc.rs:639-645) and are cloned with the particle by resampling, so the assignment z of
+// a particle is FROZEN from the prior draw on, and with it, per component c: how many observations it owns
+// (n_c), their mean m_c and M2_c = sum (x_i - m_c)^2. The component's share of the observation plate is then
+//   sum_{z_i = c} [ -0.5 ((x_i - mu_c) / sigma_c)^2 - ln sigma_c - 0.5 ln 2 pi ]
+//     = -0.5 (M2_c + n_c (m_c - mu_c)^2) / sigma_c^2 + n_c (-ln sigma_c - 0.5 ln 2 pi)
+// (centred form: no cancellation), i.e. a move scores its proposal in O(1) instead of one Normal term per
+// observation, and never reads the z bytes. st[0] = n_1 (NaN: a site outside {0, 1}, statistics unusable),
+// st[1..2] = m_0, M2_0, st[3..4] = m_1, M2_1.
+__device__ __noinline__ void mix_stats(const FusedProg& F, const FPlate& fp, const uint8_t* __restrict__ zrec, double* __restrict__ st) {
+  const int z0 = (int)F.ops[fp.op].dslot0;
+  const double* __restrict__ xs = (const double*)F.ops[fp.op_b].value_col.ptr;
+  const ZAcc za{zrec, F.L.zw};
+  double s0 = 0.0, s1 = 0.0;
+  int n1 = 0;
+  bool other = false;
+#pragma unroll 1
+  for (int i = 0; i < fp.n; i++) {
+    const unsigned zi = (unsigned)za(z0 + i);
+    const double x = __ldg(xs + i);
+    other |= zi > 1u;
+    if (zi) { n1++; s1 += x; } else s0 += x;
+  }
+  const int n0 = fp.n - n1;
+  const double m0 = n0 ? s0 / (double)n0 : 0.0, m1 = n1 ? s1 / (double)n1 : 0.0;
+  double q0 = 0.0, q1 = 0.0;
+#pragma unroll 1
+  for (int i = 0; i < fp.n; i++) {
+    const unsigned zi = (unsigned)za(z0 + i);
+    const double d = __ldg(xs + i) - (zi ? m1 : m0);
+    if (zi) q1 = fma(d, d, q1); else q0 = fma(d, d, q0);
+  }
+  st[0] = other ? __longlong_as_double(0x7ff8000000000000LL) : (double)n1;
+  st[1] = m0; st[2] = q0; st[3] = m1; st[4] = q1;
 }
 
 // log_prior / log_likelihood / log_factors of one particle: scalar ops, then every plate, in program
@@ -858,6 +931,20 @@ __device__ __forceinline__ void fused_eval(const FusedProg& F, const uint8_t* __
         // one pass over the particle's z bytes serves the discrete prior and the observation plate
         const DOp& ob = F.ops[fp.op_b];
         const NormalSetup S = normal_setup(ob, fp, q);
+        if (fp.stat && F.L.soff) {
+          const double* __restrict__ stt = (const double*)(rec + F.L.soff);
+          const double n1 = stt[0];
+          if (n1 == n1) {  // the O(1) path: per-component sufficient statistics (mix_stats)
+            const double n0 = (double)fp.n - n1;
+            const double ia = S.inv_a, ib = fp.ss ? S.inv_b : S.inv_a, ca = S.c_a, cb = fp.ss ? S.c_b : S.c_a;
+            double sl = 0.0;
+            if (n0 > 0.0) { const double d = stt[1] - (S.base0 + S.va0); sl += fma(-0.5 * ia * ia, fma(n0 * d, d, stt[2]), n0 * ca); }
+            if (n1 > 0.0) { const double d = stt[3] - (S.base0 + S.vb0); sl += fma(-0.5 * ib * ib, fma(n1 * d, d, stt[4]), n1 * cb); }
+            lp[0] += (n0 > 0.0 ? n0 * tv0 : 0.0) + (n1 > 0.0 ? n1 * tv1 : 0.0);
+            lp[1] += (sl == sl) ? sl : d_neg_inf();
+            continue;
+          }
+        }
         const int z0 = (int)op.dslot0;
         const double* __restrict__ xs = (const double*)ob.value_col.ptr;
         const bool x_f64 = ob.value_col.dtype == FC_COL_F64;
@@ -918,6 +1005,54 @@ __device__ __forceinline__ void fused_eval(const FusedProg& F, const uint8_t* __
   }
 }
 
+// fused_eval for a CompiledMix program (K.on): the same operations in the same order, operands from K
+__device__ __forceinline__ void compiled_eval(const CompiledMix& K, const FusedProg& F, const uint8_t* __restrict__ rec, double (&lp)[3]) {
+  const double* __restrict__ q = (const double*)rec;
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  double a_prior = 0.0, a_fac = 0.0;
+#pragma unroll 1
+  for (int oi = 0; oi < K.n_sop; oi++) {
+    const SOp so = K.sop[oi];
+    if (so.kind == SO_FACTOR) { a_fac += so.c0; continue; }
+    const double x = q[so.row];
+    double v;
+    if (so.kind == SO_NORMAL_CC) {
+      const double z = (x - so.c0) * so.c1;
+      v = fma(-0.5 * z, z, so.c2);
+      if (!(v == v)) v = d_neg_inf();
+    } else if (so.kind == SO_GAMMA_CC) {
+      if (!(x > 0.0) || !d_fin(x)) v = d_neg_inf();
+      else v = (so.c2 + (so.c0 != 0.0 ? so.c0 * log(x) : 0.0)) - so.c1 * x;
+    } else {
+      if (x > 0.0 && x < 1.0) v = ((so.c0 != 0.0 ? so.c0 * log(x) : 0.0) + (so.c1 != 0.0 ? so.c1 * log(1.0 - x) : 0.0)) + so.c2;
+      else { const DOp& op = F.scalar_ops[oi]; v = dist_eval<false>(FC_BETA, so.c0 + 1.0, so.c1 + 1.0, 0.0, x, 0, qnan, op.lgc, qnan).lp; }
+    }
+    a_prior += v;
+  }
+  lp[0] = 0.0 + a_prior; lp[1] = 0.0 + 0.0; lp[2] = 0.0 + a_fac;
+  const double p0 = cparam_eval(K.p0, q);
+  double tv0, tv1;
+  if (K.dist == FC_BERNOULLI) { tv0 = dist_eval<false>(FC_BERNOULLI, p0, 0.0, 0.0, 0.0, 0, qnan).lp; tv1 = dist_eval<false>(FC_BERNOULLI, p0, 0.0, 0.0, 0.0, 1, qnan).lp; }
+  else { tv0 = dist_eval<false>(FC_CATEGORICAL, p0, 0.0, 0.0, 0.0, 0, qnan).lp; tv1 = dist_eval<false>(FC_CATEGORICAL, p0, 0.0, 0.0, 0.0, 1, qnan).lp; }
+  // normal_setup
+  const double base0 = cparam_eval(K.mean, q), base1 = cparam_eval(K.sigma, q);
+  double va0 = 0.0, vb0 = 0.0;
+  if (K.m0) { va0 = q[K.row_ma]; vb0 = q[K.row_mb]; }
+  double sa = base1, sb = base1;
+  if (K.ss) { sa = base1 + q[K.row_sa]; sb = base1 + q[K.row_sb]; }
+  const bool oka = sa > 0.0 && d_fin(sa), okb = sb > 0.0 && d_fin(sb);
+  const double inv_a = oka ? 1.0 / sa : 0.0, c_a = oka ? -log(sa) - 0.5 * FC_LN_2PI : d_neg_inf();
+  const double inv_b = okb ? 1.0 / sb : 0.0, c_b = okb ? -log(sb) - 0.5 * FC_LN_2PI : d_neg_inf();
+  const double* __restrict__ stt = (const double*)(rec + K.soff);
+  const double n1 = stt[0], n0 = (double)K.n - n1;
+  const double ia = inv_a, ib = K.ss ? inv_b : inv_a, ca = c_a, cb = K.ss ? c_b : c_a;
+  double sl = 0.0;
+  if (n0 > 0.0) { const double d = stt[1] - (base0 + va0); sl += fma(-0.5 * ia * ia, fma(n0 * d, d, stt[2]), n0 * ca); }
+  if (n1 > 0.0) { const double d = stt[3] - (base0 + vb0); sl += fma(-0.5 * ib * ib, fma(n1 * d, d, stt[4]), n1 * cb); }
+  lp[0] += (n0 > 0.0 ? n0 * tv0 : 0.0) + (n1 > 0.0 ? n1 * tv1 : 0.0);
+  lp[1] += (sl == sl) ? sl : d_neg_inf();
+}
+
 // ---- prior draw of every sample site (PriorHandler, interpreters.rs:88-104,355-372) in program order; the
 // same Philox stream and draw order as the generic k_prior_sample, so both paths give the same population.
 // Scored in the same kernel: the record is still in registers / L1. ----
@@ -928,6 +1063,8 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
   uint8_t* rec = pop.rec + c * F.L.pitch;
   double* q = (double*)rec;
   uint8_t* zrec = rec + F.L.zoff;
+  if (F.L.zw == 0)
+    for (int64_t b = F.L.zoff; b < F.L.pitch; b += 16) *(uint4*)(rec + b) = make_uint4(0u, 0u, 0u, 0u);
   for (int oi = 0; oi < F.n_ops; oi++) {
     const DOp& op = F.ops[oi];
     if (!op.is_sample) continue;
@@ -938,6 +1075,7 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       long long xi;
       op_dist_sample(rng, op, pv[0], pv[1], pv[2], x, xi);
       if (op.cont) q[F.crow[op.cslot0]] = x;
+      else if (F.L.zw == 0) { if (xi) zrec[op.dslot0 >> 3] |= (uint8_t)(1u << (op.dslot0 & 7)); }
       else if (F.L.zw == 1) zrec[op.dslot0] = (uint8_t)xi;
       else ((int32_t*)zrec)[op.dslot0] = (int32_t)xi;
     } else {  // two-valued discrete plate with a chain-constant parameter
@@ -948,7 +1086,14 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       // loops are kept rolled -- 16 inlined draws per trip thrashed the instruction cache (ncu: 18 of 22
       // stall samples "no instruction", 31 ms) -- and 8 sites are packed per 8-byte store.
       int i = 0;
-      if ((z0 & 7) == 0) {
+      if (F.L.zw == 0) {  // one bit per site: the z region was cleared above; same draws, same order
+#pragma unroll 1
+        for (; i < n; i++) {
+          const bool lt = rng.uniform() < p0;
+          if (bern ? lt : !lt) zrec[(z0 + i) >> 3] |= (uint8_t)(1u << ((z0 + i) & 7));
+        }
+      }
+      if ((z0 & 7) == 0 && F.L.zw == 1) {
         if (rng.has_spare && n > 0) {  // an odd number of draws so far: realign to whole blocks through the byte path
           const bool lt = rng.uniform() < p0;
           zrec[z0] = (uint8_t)(bern ? (lt ? 1 : 0) : (lt ? 0 : 1));
@@ -975,6 +1120,9 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       }
     }
   }
+  if (F.L.soff)
+    for (int pi = 0; pi < F.n_plates; pi++)
+      if (F.plates[pi].kind == FP_MIX && F.plates[pi].stat) mix_stats(F, F.plates[pi], zrec, (double*)(rec + F.L.soff));
   double lp[3];
   fused_eval(F, rec, lp);
   double* l3 = q + F.L.d_cont;
@@ -993,12 +1141,32 @@ struct MoveX {
   double beta;
   int32_t adapt;
 };
-__global__ void __launch_bounds__(128, 6) k_smcx_move(const __grid_constant__ FusedProg F, Pop pop, const __grid_constant__ MoveX M) {
+template <bool COMPILED>
+__global__ void __launch_bounds__(128, COMPILED ? 8 : 6) k_smcx_move(const __grid_constant__ FusedProg F, const __grid_constant__ CompiledMix K, Pop pop, const __grid_constant__ MoveX M) {
   const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t dc = F.L.d_cont;
   const bool active = c < pop.n && dc > 0;
   int s = -1;
   bool accept = false;
+  // COMPILED: the head of the CTA's 128 consecutive records (f64 sites, accumulators, statistics; not z) is
+  // staged in shared memory by coalesced 16-byte loads -- one exposed DRAM latency per thread and 4 cache lines
+  // per warp-wide load, where per-field reads at a 128-byte stride touched 32 lines each and serialised the
+  // misses (ncu: 84 % L1 throughput, 50 % of the stall samples on the long scoreboard). Row stride 17 doubles:
+  // a thread's own fields are then conflict-free.
+  __shared__ double s_rec[COMPILED ? 128 * CM_SROW : 1];
+  if (COMPILED) {
+    const int64_t first = (int64_t)blockIdx.x * 128;
+    const int live = (int)min((int64_t)128, pop.n - first);
+    const int hot = K.hot_chunks, cpp = (int)(F.L.pitch >> 4);
+    const uint8_t* __restrict__ base = pop.rec + first * F.L.pitch;
+    for (int ch = threadIdx.x; ch < live * hot; ch += 128) {
+      const int slot = ch / hot, part = ch - slot * hot;
+      const double2 v = *(const double2*)(base + ((int64_t)slot * cpp + part) * 16);
+      s_rec[slot * CM_SROW + part * 2] = v.x;
+      s_rec[slot * CM_SROW + part * 2 + 1] = v.y;
+    }
+    __syncthreads();
+  }
   if (active) {
     Philox ph(M.seed, M.chain0 + (uint64_t)c);
     double u_site, u_acc, z0, z1;
@@ -1010,18 +1178,35 @@ __global__ void __launch_bounds__(128, 6) k_smcx_move(const __grid_constant__ Fu
     uint8_t* rec = pop.rec + c * F.L.pitch;
     double* q = (double*)rec;
     double* l3 = q + dc;
-    const double cur = q[si];
-    q[si] = cur + M.scale[s] * z0;
-    double lpn[3];
-    fused_eval(F, rec, lpn);
-    const double c0 = l3[0], c1 = l3[1], c2 = l3[2];
-    const double log_alpha = (lpn[0] - c0) + M.beta * ((lpn[1] + lpn[2]) - (c1 + c2));  // smc.rs:679-680
-    accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);
-    if (accept) {
-      l3[0] = lpn[0]; l3[1] = lpn[1]; l3[2] = lpn[2];
-      pop.ll[c] = lpn[1] + lpn[2];
+    if (COMPILED) {
+      // the proposal is scored on the staged copy; global memory is written only on acceptance
+      double* sq = s_rec + threadIdx.x * CM_SROW;
+      const double prop = sq[si] + M.scale[s] * z0;
+      sq[si] = prop;
+      double lpn[3];
+      compiled_eval(K, F, (const uint8_t*)sq, lpn);  // the plate's sites are two-valued draws: the statistics are always usable
+      const double c0 = sq[dc], c1 = sq[dc + 1], c2 = sq[dc + 2];
+      const double log_alpha = (lpn[0] - c0) + M.beta * ((lpn[1] + lpn[2]) - (c1 + c2));  // smc.rs:679-680
+      accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);
+      if (accept) {
+        q[si] = prop;
+        l3[0] = lpn[0]; l3[1] = lpn[1]; l3[2] = lpn[2];
+        pop.ll[c] = lpn[1] + lpn[2];
+      }
     } else {
-      q[si] = cur;
+      const double cur = q[si];
+      q[si] = cur + M.scale[s] * z0;
+      double lpn[3];
+      fused_eval(F, rec, lpn);
+      const double c0 = l3[0], c1 = l3[1], c2 = l3[2];
+      const double log_alpha = (lpn[0] - c0) + M.beta * ((lpn[1] + lpn[2]) - (c1 + c2));  // smc.rs:679-680
+      accept = log_alpha >= 0.0 || u_acc < exp(log_alpha);
+      if (accept) {
+        l3[0] = lpn[0]; l3[1] = lpn[1]; l3[2] = lpn[2];
+        pop.ll[c] = lpn[1] + lpn[2];
+      } else {
+        q[si] = cur;
+      }
     }
   }
   if (!M.adapt) return;
@@ -1142,7 +1327,7 @@ __global__ void k_rec_unpack(const uint8_t* __restrict__ rec, RecLayout L, const
   if (lp3) for (int a = 0; a < 3; a++) lp3[a * n + c] = rq[L.d_cont + a];
   if (qd) {
     const uint8_t* z = r + L.zoff;
-    for (int64_t s = 0; s < L.d_disc; s++) qd[(int64_t)drow[s] * n + c] = L.zw == 1 ? (disc_t)z[s] : ((const int32_t*)z)[s];
+    for (int64_t s = 0; s < L.d_disc; s++) qd[(int64_t)drow[s] * n + c] = L.zw == 0 ? (disc_t)((z[s >> 3] >> (s & 7)) & 1u) : (L.zw == 1 ? (disc_t)z[s] : ((const int32_t*)z)[s]);
   }
 }
 __global__ void k_rec_pack(uint8_t* __restrict__ rec, RecLayout L, const int32_t* __restrict__ drow, int64_t n, const double* __restrict__ q, const double* __restrict__ lp3, const disc_t* __restrict__ qd,
@@ -1160,7 +1345,8 @@ __global__ void k_rec_pack(uint8_t* __restrict__ rec, RecLayout L, const int32_t
     uint8_t* z = r + L.zoff;
     for (int64_t s = 0; s < L.d_disc; s++) {
       const disc_t v = qd[(int64_t)drow[s] * n + c];
-      if (L.zw == 1) { if (v < 0 || v > 255) *overflow = 1; z[s] = (uint8_t)v; }
+      if (L.zw == 0) { if (v < 0 || v > 1) *overflow = 1; if (v) z[s >> 3] |= (uint8_t)(1u << (s & 7)); else z[s >> 3] &= (uint8_t)~(1u << (s & 7)); }
+      else if (L.zw == 1) { if (v < 0 || v > 255) *overflow = 1; z[s] = (uint8_t)v; }
       else ((int32_t*)z)[s] = v;
     }
   }
@@ -1215,6 +1401,7 @@ struct fc_smc_session {
   fc::DevBuf<fc::FPlate> fplates;
   fc::DevBuf<fc::SOp> sops;
   fc::FusedProg F;
+  fc::CompiledMix K;   // K.on: the move kernel's by-value program (scalar priors + one mixture plate with statistics)
   // generic engine: [row][particle] copies of the records (valid flags say which are current)
   fc::MoveEngine eng;
   fc::DevBuf<fc::disc_t> qd32;
@@ -1275,6 +1462,12 @@ static bool nb_plain() {
   return g_nb_plain == 1;
 }
 static int nb_mode() { nb_plain(); return g_nb_plain; }
+static int g_smc_stats = 1;  // fc_debug_set("smc_stats", 0): score mixture plates term by term (A/B parity)
+static bool smc_stats() { return g_smc_stats != 0; }
+static int g_smc_compiled = 1;  // fc_debug_set("smc_compiled", 0): the move kernel interprets the op descriptors
+static bool smc_compiled() { return g_smc_compiled != 0; }
+static int g_smc_zbits = 1;  // fc_debug_set("smc_zbits", 0): keep one byte per two-valued discrete site
+static bool smc_zbits() { return g_smc_zbits != 0; }
 static bool smc_generic() {
   if (g_smc_generic < 0) g_smc_generic = getenv("FC_SMC_GENERIC") != nullptr;
   return g_smc_generic != 0;
@@ -1725,7 +1918,8 @@ static int32_t smc_rejuvenate(fc_smc_session* S, double beta, uint64_t steps) {
       MoveX M;
       M.scale = S->eng.scale.p; M.acc_cnt = S->eng.acc_cnt.p; M.tot_cnt = S->eng.tot_cnt.p;
       M.seed = S->eng.seed; M.chain0 = S->eng.chain0; M.step_tag = S->moves; M.beta = beta; M.adapt = 1;
-      k_smcx_move<<<(unsigned)cdiv(n, 128), 128, 0, st>>>(S->F, pop, M);
+      if (S->K.on) k_smcx_move<true><<<(unsigned)cdiv(n, 128), 128, 0, st>>>(S->F, S->K, pop, M);
+      else k_smcx_move<false><<<(unsigned)cdiv(n, 128), 128, 0, st>>>(S->F, S->K, pop, M);
       FC_KERNEL_CHECK();
       P->n_kernel_launches += 1;
       FC_TRY(S->eng.shared_adapt(0.44, 0.7));
@@ -1837,6 +2031,10 @@ static bool fused_lower(fc_program* P, std::vector<FPlate>& out, int& zw) {
       if (same_m && same_s) {
         FPlate& z = out.back();
         z.kind = FP_MIX; z.op_b = (int32_t)oi; z.m0 = fp.m0; z.m1 = fp.m1; z.ss = fp.ss; z.mt0 = fp.mt0; z.mt1 = fp.mt1; z.st = fp.st;
+        // the first such plate whose mean has no other element-dependent term keeps its statistics in the record
+        bool have = false;
+        for (const FPlate& o : out) have |= o.stat != 0;
+        z.stat = (!have && smc_stats() && fp.m1 == FM_NONE && op.value_col.dtype == FC_COL_F64) ? 1 : 0;
         continue;
       }
     }
@@ -1911,9 +2109,22 @@ static int32_t smc_create_impl(fc_program* p, const fc_smc_config* cfg, uint64_t
   std::vector<FPlate> fpl;
   int zw = 1;
   S->fused = fused_lower(p, fpl, zw);
-  S->L.d_cont = p->d_cont; S->L.d_disc = p->d_disc; S->L.zw = zw; S->L._pad = 0;
-  S->L.zoff = (((p->d_cont + 3) * 8 + 15) / 16) * 16;
-  S->L.pitch = S->L.zoff + ((p->d_disc * zw + 15) / 16) * 16;
+  S->L.d_cont = p->d_cont; S->L.d_disc = p->d_disc; S->L.zw = zw; S->L.soff = 0;
+  int64_t head = (p->d_cont + 3) * 8;
+  if (S->fused)
+    for (const FPlate& f : fpl)
+      if (f.stat) { S->L.soff = (int32_t)head; head += 5 * 8; }
+  // one bit per discrete site when the record carries the mixture statistics (the moves then never read z) and
+  // every discrete sample site is two-valued: C4's record shrinks from 192 to 128 bytes
+  if (S->fused && S->L.soff && smc_zbits()) {
+    bool two = true;
+    for (const DOp& op : p->all_ops)
+      if (op.is_sample && !op.cont) two &= op.dist == FC_BERNOULLI || (op.dist == FC_CATEGORICAL && op.n_probs == 0);
+    if (two) zw = 0;
+  }
+  S->L.zw = zw;
+  S->L.zoff = ((head + 15) / 16) * 16;
+  S->L.pitch = S->L.zoff + (((zw == 0 ? (p->d_disc + 7) / 8 : p->d_disc * zw) + 15) / 16) * 16;
   S->slab_bytes = fc_smc_session::layout(N, S->L.pitch, S->off_rec, S->off_ll);
   FC_CUDA(cudaMalloc((void**)&S->slab, S->slab_bytes));
   FC_CUDA(cudaMemsetAsync(S->slab, 0, S->off_rec[0], st));  // the mailbox
@@ -1969,6 +2180,32 @@ static int32_t smc_create_impl(fc_program* p, const fc_smc_config* cfg, uint64_t
     F.sops = S->sops.p;
     F.ops = p->d_all_ops.p; F.scalar_ops = p->d_scalar_ops.p; F.plates = S->fplates.p; F.crow = p->d_crow.p; F.nodes = p->d_expr_nodes.p;
     F.n_ops = (int32_t)p->all_ops.size(); F.n_scalar = (int32_t)p->scalar_ops.size(); F.n_plates = (int32_t)fpl.size(); F._pad = 0; F.L = S->L;
+    // by-value program of the move kernel: every scalar op compiled, exactly one plate, a mixture with statistics
+    CompiledMix& K = S->K;
+    memset(&K, 0, sizeof(K));
+    bool ok = smc_compiled() && S->L.soff && fpl.size() == 1 && fpl[0].kind == FP_MIX && fpl[0].stat && so.size() <= CM_MAX_SOP;
+    for (const SOp& o : so) ok = ok && o.kind != SO_GENERIC;
+    if (ok) {
+      const FPlate& fp = fpl[0];
+      const DOp& zp = p->all_ops[fp.op];
+      const DOp& ob = p->all_ops[fp.op_b];
+      auto cp = [&](const DOp& op, int j, CParam& out) {
+        for (int t = 0; t < 3; t++) {
+          const DTerm& tm = op.p[j].t[t];
+          out.c[t] = tm.c;
+          out.row[t] = tm.kind == FC_TERM_CONST ? -1 : (tm.kind == FC_TERM_LATENT ? (int32_t)tm.row : -2);
+        }
+        out.link = op.p[j].link; out.apply = op.p[j].invariant ? 1 : 0; out.lo = op.p[j].lo; out.hi = op.p[j].hi;
+      };
+      K.n_sop = (int32_t)so.size();
+      for (size_t i = 0; i < so.size(); i++) K.sop[i] = so[i];
+      K.dist = zp.dist; K.n = fp.n; K.m0 = fp.m0 == FM_SELECT2 ? 1 : 0; K.ss = fp.ss; K.soff = S->L.soff;
+      cp(zp, 0, K.p0); cp(ob, 0, K.mean); cp(ob, 1, K.sigma);
+      if (K.m0) { K.row_ma = (int32_t)ob.p[0].t[fp.mt0].row; K.row_mb = (int32_t)ob.p[0].t[fp.mt0].row_b; }
+      if (K.ss) { K.row_sa = (int32_t)ob.p[1].t[fp.st].row; K.row_sb = (int32_t)ob.p[1].t[fp.st].row_b; }
+      K.hot_chunks = (S->L.soff + 40 + 15) / 16;
+      K.on = (fp.m0 != FM_LATENT_X && K.hot_chunks <= CM_HOT_MAX) ? 1 : 0;
+    }
   }
   FC_TRY(smc_init_population(S.get()));
   FC_CUDA(cudaStreamSynchronize(st));
@@ -2242,6 +2479,9 @@ int32_t fc_debug_set(const char* key, int32_t value) {
   if (key && !strcmp(key, "nb_plain")) { fc::g_nb_plain = (value >= 0 && value <= 2) ? value : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_generic")) { fc::g_smc_generic = value ? 1 : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_timing")) { fc::g_smc_timing = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "smc_stats")) { fc::g_smc_stats = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "smc_zbits")) { fc::g_smc_zbits = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "smc_compiled")) { fc::g_smc_compiled = value ? 1 : 0; return FC_OK; }
   fc::set_error("unknown debug key");
   return FC_ERR_INVALID_ARGUMENT;
 }

@@ -145,3 +145,47 @@ def test_adaptive_smc_ladder_agrees_with_the_oracles():
     o0 = O.adaptive_smc(n, rejuvenation_steps=0, seed=6)
     d0 = api.adaptive_smc(m, n, api.SMCConfig(rejuvenation_steps=0), seed=6)
     assert o0["steps"] == d0.n_temper_steps == 1 and abs(o0["log_evidence"] - d0.log_evidence) < 0.1
+
+
+def test_mixture_sufficient_statistics_equal_term_by_term_scoring():
+    """The fused SMC kernels score a mixture plate (z#i two-valued, x#i ~ Normal(mu[z_i], sigma[z_i])) from the
+    per-particle, per-component sufficient statistics kept in the record (fc_smc.cu: mix_stats). A/B against the
+    term-by-term loop (fc_debug_set("smc_stats", 0)) on the same seed: same population, accumulators to 1e-12
+    relative, and the same moves -- through resampling (statistics are cloned with the particle) and 3 sweeps."""
+    m = models.gaussian_mixture(n_obs=37)[0]   # not a multiple of 16: the vector loop's tail as well
+    out = []
+    # by-value program + 128-byte records (z as bits); interpreter on the same records; 192-byte; 144-byte term by term
+    for stats, zbits, comp in ((1, 1, 1), (1, 1, 0), (1, 0, 1), (0, 0, 0)):
+        api.debug_set("smc_stats", stats)
+        api.debug_set("smc_zbits", zbits)
+        api.debug_set("smc_compiled", comp)
+        try:
+            S = api.SmcSession(api.Program(m), 4096, api.SMCConfig(rejuvenation_steps=1), 31)
+            assert S.counters()["fused"]
+            r0 = S.result()
+            lw0 = S.prior_weights().weights()[0]
+            S.reweight(0.2)
+            idx = S.resample_particles(api.ResamplingMethod.Systematic)
+            for _ in range(3):
+                S.rejuvenate_particles(0.2, 1)
+            r1 = S.result()
+            lw1 = S.prior_weights().weights()[0]
+            out.append((r0.values, r0.dvalues, lw0, np.asarray(idx), r1.values, r1.dvalues, lw1))
+            S.close()
+        finally:
+            api.debug_set("smc_stats", 1)
+            api.debug_set("smc_zbits", 1)
+            api.debug_set("smc_compiled", 1)
+    b = out[3]
+    for a in out[:3]:
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])          # the same prior population
+        assert set(np.unique(a[1])) == {0, 1}
+        fin = np.isfinite(b[2])
+        assert np.array_equal(np.isfinite(a[2]), fin) and np.allclose(a[2][fin], b[2][fin], rtol=1e-12, atol=0.0)
+        assert np.array_equal(a[3], b[3])                                          # identical ancestors
+        same = np.all(a[4] == b[4], axis=0)                                        # a decision on the rounding noise may differ
+        assert same.mean() > 0.999 and np.array_equal(a[5], b[5])
+        fin = np.isfinite(b[6]) & same
+        assert np.allclose(a[6][fin], b[6][fin], rtol=1e-12, atol=0.0)
+    for o in out[1:3]:   # compiled vs interpreted, bits vs bytes: the same arithmetic, bit for bit
+        assert np.array_equal(out[0][4], o[4]) and np.array_equal(out[0][6], o[6])
