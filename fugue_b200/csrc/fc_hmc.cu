@@ -41,6 +41,9 @@ struct fc_hmc_session {
   int64_t ksplits = 1;
   fc::DevBuf<double> ext_z, ext_u;  // caller-supplied randomness for the next transition (parity tests)
   bool use_ext = false;
+  bool use_hier = false;             // leapfrog steps run as the fused hierarchical kernels (fc_hier.cu)
+  fc::HierPlan hier;
+  int64_t kin_splits = 1;            // rows of kpart the last trajectory's kinetic energy is spread over
   bool recording = false;            // the next transition records its leapfrog points (step_recorded)
   fc::DevBuf<double> rec_q, rec_h;  // [L+1][d][C], [L+1][C]
 };
@@ -360,6 +363,19 @@ struct Hmc {
   // L leapfrog steps from (q, p) using the cached force at q; leaves q_new, p, g_new, lj_new, kpart(K_new)
   int32_t trajectory(const double* eps, uint64_t L) {
     FC_TRY(leap(S->g_cur.p, eps, 0.5, 1, 0));
+    if (S->use_hier) {
+      // force + kick (+ drift) of one leapfrog step in two launches; the last step leaves the force in g_new,
+      // the accumulators / log-joint of the end point and the whole kinetic sum in kpart[0]
+      for (uint64_t l = 1; l <= L; l++) {
+        const bool last = l == L;
+        FC_TRY(hier_step(P, S->hier, S->q_new.p, S->p.p, S->m_inv.p, eps, S->g_new.p, S->divergent.p, S->kpart.p, S->lp3.p, S->lj_new.p, C,
+                         last ? 0.5 : 1.0, !last, last, last));
+        S->grad_evals += 1;
+      }
+      S->kin_splits = 1;
+      return FC_OK;
+    }
+    S->kin_splits = nsplit();
     for (uint64_t l = 1; l <= L; l++) {
       FC_TRY(force(S->q_new.p, S->lp3.p, S->lj_new.p, S->g_new.p, l == L));
       if (l < L) FC_TRY(leap(S->g_new.p, eps, 1.0, 1, 0));
@@ -376,6 +392,7 @@ struct Hmc {
     FC_CUDA(S->rec_h.reserve((int64_t)(L + 1) * C));
     FC_CUDA(cudaMemcpyAsync(S->rec_q.p, S->q.p, d * C * 8, cudaMemcpyDeviceToDevice, st));
     FC_CUDA(cudaMemcpyAsync(S->rec_h.p, S->h0.p, C * 8, cudaMemcpyDeviceToDevice, st));
+    S->kin_splits = nsplit();
     FC_TRY(leap(S->g_cur.p, eps, 0.5, 1, 0));
     for (uint64_t l = 1; l <= L; l++) {
       FC_TRY(force(S->q_new.p, S->lp3.p, S->lj_new.p, S->g_new.p, true));
@@ -410,7 +427,7 @@ struct Hmc {
       FC_TRY(trajectory(S->eps_trial.p, 1));
       int32_t* n_active = S->fre_state.p + C;
       FC_CUDA(cudaMemsetAsync(n_active, 0, 4, st));
-      k_fre_update<<<cb, 128, 0, st>>>(S->lj_new.p, S->kpart.p, nsplit(), S->h0.p, S->divergent.p, S->eps_trial.p, aux, S->fre_state.p, n_active, C);
+      k_fre_update<<<cb, 128, 0, st>>>(S->lj_new.p, S->kpart.p, S->kin_splits, S->h0.p, S->divergent.p, S->eps_trial.p, aux, S->fre_state.p, n_active, C);
       FC_KERNEL_CHECK();
       P->n_kernel_launches += 1;
       int32_t h_active = 0;
@@ -448,7 +465,7 @@ struct Hmc {
     if (S->recording) FC_TRY(trajectory_recorded(S->eps.p, S->L));
     else FC_TRY(trajectory(S->eps.p, S->L));
     S->recording = false;
-    k_accept<<<cb, 128, 0, st>>>(S->lj_new.p, S->kpart.p, nsplit(), S->h0.p, S->lj.p, S->divergent.p, S->accepted.p, S->ap.p, S->n_accept.p, S->n_divergent.p,
+    k_accept<<<cb, 128, 0, st>>>(S->lj_new.p, S->kpart.p, S->kin_splits, S->h0.p, S->lj.p, S->divergent.p, S->accepted.p, S->ap.p, S->n_accept.p, S->n_divergent.p,
                                  S->eps.p, S->da.p, C, S->seed, S->chain0, tag, (uint64_t)((d + 1) / 2 + 1), warming ? 1 : 0, S->cfg.target_accept, S->use_ext ? S->ext_u.p : nullptr);
     FC_KERNEL_CHECK();
     S->use_ext = false;
@@ -507,6 +524,7 @@ int32_t fc_hmc_create_sharded(fc_program* p, const fc_hmc_config* cfg, uint64_t 
   S->mass_adapt_at = (cfg->adapt_mass && n_warmup >= 4) ? (int64_t)(n_warmup / 2) : -1;  // hmc.rs:704-708
   int64_t d = S->d, Cn = S->C, n = std::max<int64_t>(1, d * Cn);
   S->ksplits = std::max<int64_t>(1, std::min<int64_t>(64, cdiv(d, EW_TY * 8)));
+  S->use_hier = cfg->grad_mode == 0 && hier_detect(p, &S->hier);
   cudaStream_t st = p->stream;
   for (auto* b : {&S->q, &S->q_new, &S->p, &S->g_cur, &S->g_new, &S->m_inv, &S->mass_sqrt, &S->wf_mean, &S->wf_m2}) FC_CUDA(b->reserve(n));
   FC_CUDA(S->lp3.reserve(3 * Cn)); FC_CUDA(S->lp3_cur.reserve(3 * Cn));

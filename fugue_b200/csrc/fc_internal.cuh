@@ -147,4 +147,11 @@ int64_t dense_plate_splits(const fc_program* p, const PlateInfo& pl, int64_t C);
 // chain c uses Philox stream (seed, stream0 + c), counter tag `tag`.
 int32_t prior_sample_dev(fc_program* p, double* d_q, disc_t* d_qd, int64_t C, uint64_t seed, uint64_t stream0, uint64_t tag);
 int32_t convert_qd(fc_program* p, const int64_t* h_qd, int64_t C, const disc_t** out);
+// fused leapfrog step of hierarchical programs (fc_hier.cu): which plates play which part, the rows outside the
+// group-latent plate
+struct HierPlan { int pri = -1, obs = -1, gt = -1, xt = -1; int32_t n_glob = 0; int32_t glob[16]; };
+extern int g_hmc_hier;
+bool hier_detect(fc_program* p, HierPlan* out);
+int32_t hier_step(fc_program* p, const HierPlan& H, double* q, double* mom, const double* m_inv, const double* eps, double* g_out, int32_t* divergent,
+                  double* kpart, double* lp3, double* lj, int64_t C, double kick, bool drift, bool store_g, bool need_value);
 }  // namespace fc

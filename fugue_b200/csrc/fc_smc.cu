@@ -2481,6 +2481,7 @@ int32_t fc_debug_set(const char* key, int32_t value) {
   if (key && !strcmp(key, "smc_timing")) { fc::g_smc_timing = value ? 1 : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_stats")) { fc::g_smc_stats = value ? 1 : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_zbits")) { fc::g_smc_zbits = value ? 1 : 0; return FC_OK; }
+  if (key && !strcmp(key, "hmc_hier")) { fc::g_hmc_hier = value ? 1 : 0; return FC_OK; }
   if (key && !strcmp(key, "smc_compiled")) { fc::g_smc_compiled = value ? 1 : 0; return FC_OK; }
   fc::set_error("unknown debug key");
   return FC_ERR_INVALID_ARGUMENT;

@@ -428,7 +428,8 @@ int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, do
  * CUDA-event timing of the tempering steps (fc_smc_phase_ms); "smc_stats" = 0: sessions created afterwards
  * score mixture plates term by term instead of from the per-particle sufficient statistics; "smc_zbits" = 0:
  * keep one byte (not one bit) per two-valued discrete site in the particle record; "smc_compiled" = 0: the move
- * kernel interprets the op descriptors instead of running the by-value flattened program */
+ * kernel interprets the op descriptors instead of running the by-value flattened program; "hmc_hier" = 0: HMC
+ * sessions created afterwards run hierarchical programs through the generic leapfrog kernels (fc_hier.cu off) */
 int32_t fc_debug_set(const char* key, int32_t value);
 /* accuracy probe of the kernels' branch-free FP64 primitives: op 0 exp, 1 log, 2 reciprocal */
 int32_t fc_debug_fastmath(int32_t op, const double* h_x, size_t n, double* h_out);

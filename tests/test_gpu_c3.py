@@ -79,3 +79,42 @@ def test_c3_scaled_converges_and_matches_oracle_chains():
     assert np.abs(z).max() < 8.0 and np.mean(np.abs(z) < 3.0) > 0.9, (np.abs(z).max(), np.mean(np.abs(z) < 3.0))
     o_std = samples.reshape(-1, d).std(0)
     assert np.median(np.abs(o_std / dg["std"] - 1.0)) < 0.15
+
+
+@pytest.mark.parametrize("G,per,adapt", [(137, 7, False), (3, 1500, False), (64, 15, True)])
+def test_fused_hierarchical_leapfrog_equals_generic_path(G, per, adapt):
+    """fc_hier.cu (force of a group latent = prior term + its observations, kick and drift applied in the same
+    kernel; two launches per leapfrog step) against the generic nine-launch path on the same seed: the same
+    trajectories up to the order in which per-CTA partials of the GLOBAL rows are folded (1e-10 after several
+    transitions; group rows of one step are bit-identical). Shapes: ragged against the 8-group batches, groups
+    larger than the 1024-element shared-memory chunk, and a run through mass adaptation + the step-size search."""
+    m, truth = models.hierarchical(G=G, per_group=per)
+    out = []
+    for hier in (1, 0):
+        api.debug_set("hmc_hier", hier)
+        try:
+            P = api.Program(m)
+            q0 = models.hierarchical_inits(truth, P.sites, 160, 0.1, 3)
+            S = api.HmcSession(P, n_chains=160, n_warmup=8, config=api.HMCConfig(n_leapfrog=5, adapt_mass=adapt), seed=5, q0=q0)
+            l0 = P.launch_count
+            S.step(1)
+            launches = P.launch_count - l0
+            first = (S.position(), S.log_joint(), S.last_step_info()["accept_prob"], S.trace())
+            S.step(11)   # through the end of warm-up (and the mass switch at transition 4 when adapt)
+            out.append((first, S.position(), S.log_joint(), S.stats(), launches))
+            S.close()
+        finally:
+            api.debug_set("hmc_hier", 1)
+    (fa, qa, la, sa, na), (fb, qb, lb, sb, nb) = out
+    assert 2 * na < nb, (na, nb)      # 2 launches per leapfrog step instead of 8 (+ 2 memsets)
+    assert np.allclose(fa[2], fb[2], rtol=1e-9, atol=1e-12)
+    same = (fa[0] == fb[0]).all(axis=0) | np.isclose(fa[2], fb[2], rtol=1e-9, atol=1e-12)
+    assert np.allclose(fa[0], fb[0], rtol=1e-11, atol=1e-13) and np.allclose(fa[1], fb[1], rtol=1e-12)
+    for x, y in zip(fa[3], fb[3]):
+        assert np.allclose(x, y, rtol=1e-12, atol=1e-12)
+    # several transitions later: the same chains unless an accept decision sat on the rounding noise
+    agree = np.isclose(la, lb, rtol=1e-8)
+    assert agree.mean() > 0.97, agree.mean()
+    assert np.allclose(qa[:, agree], qb[:, agree], rtol=1e-7, atol=1e-9)
+    assert np.array_equal(sa["n_accept"][agree], sb["n_accept"][agree])
+    assert np.allclose(sa["step_size"][agree], sb["step_size"][agree], rtol=1e-7)
