@@ -15,9 +15,9 @@
 // them in fixed order, adds the scalar ops (same interpreter as k_scalar) and moves the global rows. Two
 // launches per leapfrog step.
 //
-// Per-element formulas are those of k_plate_fast (Normal fast path) and k_plate_csr_normal, including the
-// two interleaved accumulator sets of the latter, so the alpha rows of the force are bit-identical to the
-// generic path; the global rows differ only in how many partials are folded.
+// The prior term is k_plate_fast's Normal fast path; the observation term is accumulated in residual form (see
+// the kernel), so the force agrees with the generic path to rounding, not bit for bit
+// (tests/test_gpu_c3.py::test_fused_hierarchical_leapfrog_equals_generic_path).
 #include "fc_plate.cuh"
 #include "fc_scalar.cuh"
 
@@ -25,7 +25,7 @@ namespace fc {
 
 #define HR_TX 128
 #define HR_TILE 1024
-#define HR_GB 8
+#define HR_GB 4
 #define HR_NACC 8      // partials per (split, chain): lp_prior, lp_obs, w0, w1, wx, p0, p1, kinetic
 #define HR_MAX_GLOB 16
 
@@ -48,7 +48,7 @@ struct HierArgs {
 };
 
 template <bool HAS_X, bool VAL>
-__global__ void __launch_bounds__(HR_TX, 4) k_hier_step(const __grid_constant__ HierArgs A) {
+__global__ void __launch_bounds__(HR_TX, 6) k_hier_step(const __grid_constant__ HierArgs A) {
   const DOp& op = A.obs;
   const DOp& pr = A.pri;
   const int64_t C = A.C;
@@ -110,8 +110,13 @@ __global__ void __launch_bounds__(HR_TX, 4) k_hier_step(const __grid_constant__ 
   const double e = A.eps[c];
   const double ke = A.kick * e;
 
-  double lp = 0.0, lpb = 0.0, acc_w0 = 0.0, acc_w1 = 0.0, acc_w1b = 0.0, acc_x = 0.0, acc_xb = 0.0;
+  // Observation sums in RESIDUAL form: with r_i = y_i - mean_i and one sigma per chain,
+  //   sum z_i / sigma = inv^2 sum r_i,   sum (z_i^2 - 1) / sigma = inv (inv^2 sum r_i^2 - n),   sum z_i x_i / sigma = inv^2 sum r_i x_i,
+  // so an element costs 5 FP64 instructions (mean, r, and three accumulations) instead of 11, and only sum r_i
+  // is per group (ncu on the per-element form: FP64 pipe 39 % busy, 32 issued instructions per element).
+  double acc_w0 = 0.0, srr = 0.0, srrb = 0.0, srx = 0.0, srxb = 0.0;
   double lp_pri = 0.0, acc_p0 = 0.0, acc_p1 = 0.0, kin = 0.0;
+  const double inv2 = inv * inv;
   bool bad = false;
 
   const int e_end = u1 > u0 ? __ldg(A.grp_ptr + u1) : 0;
@@ -127,17 +132,13 @@ __global__ void __launch_bounds__(HR_TX, 4) k_hier_step(const __grid_constant__ 
     }
     __syncthreads();
   };
-  auto elem = [&](int k, double m0, double& lp_, double& ga_, double& w1_, double& ax_) {
+  auto elem = [&](int k, double m0, double& sr_, double& srr_, double& srx_) {
     const double y = s_y[k];
-    double mean = m0, x = 0.0;
-    if (HAS_X) { x = s_x[k]; mean = m0 + va * x; }
-    const double z = (y - mean) * inv, zz = z * z;
-    const bool fin = d_fin(zz);
-    if (VAL) lp_ = fin ? lp_ + (-0.5 * zz - lgs - 0.5 * FC_LN_2PI) : neg_inf;
-    const double w0 = fin ? z * inv : 0.0;
-    ga_ += w0;
-    w1_ += fin ? (zz - 1.0) * inv1 : 0.0;
-    if (HAS_X) ax_ += w0 * x;
+    double r;
+    if (HAS_X) { const double x = s_x[k]; r = y - fma(va, x, m0); srx_ = fma(r, x, srx_); }
+    else r = y - m0;
+    sr_ += r;
+    srr_ = fma(r, r, srr_);
   };
 
   for (int64_t ub = u0; ub < u1; ub += HR_GB) {
@@ -164,12 +165,12 @@ __global__ void __launch_bounds__(HR_TX, 4) k_hier_step(const __grid_constant__ 
         if (k >= clen) { const int nb = chunk_b + k; kend -= k; k = 0; load_chunk(nb); }
         const int kl = min(kend, clen);
         for (; k + 1 < kl; k += 2) {
-          elem(k, m0, lp, ga, acc_w1, acc_x);
-          elem(k + 1, m0, lpb, gab, acc_w1b, acc_xb);
+          elem(k, m0, ga, srr, srx);
+          elem(k + 1, m0, gab, srrb, srxb);
         }
-        if (k < kl) { elem(k, m0, lp, ga, acc_w1, acc_x); k++; }
+        if (k < kl) { elem(k, m0, ga, srr, srx); k++; }
       }
-      ga += gab;
+      ga = (ga + gab) * inv2;  // sum of z / sigma over the group's observations (inv = 0 when sigma is invalid: no force)
       acc_w0 += ga;
       // prior term: alpha_g ~ Normal(loc, scale) (distribution.rs:138-160)
       const double x = gv[b];
@@ -197,8 +198,14 @@ __global__ void __launch_bounds__(HR_TX, 4) k_hier_step(const __grid_constant__ 
       }
     }
   }
-  lp += lpb; acc_w1 += acc_w1b; acc_x += acc_xb;
-  if (!sig_ok && u1 > u0 && e_end > __ldg(A.grp_ptr + u0)) lp = neg_inf;
+  srr += srrb; srx += srxb;
+  const double n_el = u1 > u0 ? (double)(e_end - __ldg(A.grp_ptr + u0)) : 0.0;
+  const double acc_w1 = inv1 * (inv2 * srr - n_el), acc_x = inv2 * srx;
+  double lp = 0.0;
+  if (VAL) {
+    lp = -0.5 * inv2 * srr - n_el * (lgs + 0.5 * FC_LN_2PI);
+    if (!d_fin(srr) || (!sig_ok && n_el > 0.0)) lp = neg_inf;  // a non-finite residual, or Normal::new(.., sigma <= 0): -inf
+  }
   if (active) {
     if (bad) atomicOr(&A.divergent[c], 1);
     double* o = A.part + (int64_t)blockIdx.y * HR_NACC * C + c;
@@ -344,7 +351,7 @@ int32_t hier_step(fc_program* P, const HierPlan& H, double* q, double* p, const 
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int64_t cblocks = cdiv(C, (int64_t)HR_TX);
-  const int64_t want = cdiv((int64_t)sms * 4, cblocks);
+  const int64_t want = cdiv((int64_t)sms * 6, cblocks);
   const int64_t n_splits0 = std::max<int64_t>(1, std::min<int64_t>(want, std::max<int64_t>(1, po.n_groups / 4)));
   const int64_t ups = cdiv(po.n_groups, n_splits0);
   const int64_t n_splits = cdiv(po.n_groups, ups);

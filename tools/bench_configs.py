@@ -38,7 +38,9 @@ if which == "c3":
     rate = Cn * ge / (ms * 1e-3)
     alg = 20 * N + 16 * d
     out = dict(config="C3 hierarchical normal", G=G, N=N, d=d, chains=Cn, ms_per_transition=ms, grad_evals_per_s=rate,
-               hbm_alg_GBps=rate * alg / 1e9, hbm_frac=rate * alg / 1e9 / HBM, accept=float(np.mean(S.stats()["n_accept"]) / S.iterations()))
+               hbm_alg_GBps=rate * alg / 1e9, hbm_frac=rate * alg / 1e9 / HBM, accept=float(np.mean(S.stats()["n_accept"]) / S.iterations()),
+               roof_note="SURVEY 8(d) counts 20 N + 16 d bytes per chain-gradient as if every chain streamed the observations; the fused step stages them once per 128 chains, so that fraction can exceed 1. What the step must move is the state: q, p, m_inv read + q, p written = 40 d bytes per chain and leapfrog step",
+               state_GBps=rate * 40 * d / 1e9, state_frac=rate * 40 * d / 1e9 / HBM, fp64_tflops=rate * N * 8 / 1e12)
     # the stated run shape (hierarchical_models.rs:7-33 scaled): Cn chains x (n_w warm-up + n_s draws) with
     # adapt_mass, draws kept in HBM (fc_hmc_run_dev), R-hat / ESS / mean / std of all d parameters on
     # them in place (fc_diagnostics_dev)
