@@ -112,6 +112,18 @@ __device__ __forceinline__ Inc2 combine(const Inc2& a, const Inc2& b) {
   r.o = sat_add(a.o, (a.o & 1) ? b.e : b.o);
   return r;
 }
+// The same composition without the clamp, for the in-thread walks over SC_ITEMS items: operands are at most
+// SAT_INC, so 1 + SC_ITEMS of them stay below 2^59; the caller clamps the aggregate once (clamp_inc). A value
+// above SAT_INC has long passed the binade top (need <= 2^53), and everything after the first crossing is
+// discarded, so which of b.e / b.o an over-the-top left operand picks does not matter. (ncu: the clamps'
+// 64-bit compare + select pairs were 47 % of the scan's issued instructions.)
+__device__ __forceinline__ Inc2 combine_raw(const Inc2& a, const Inc2& b) {
+  Inc2 r;
+  r.e = a.e + ((a.e & 1) ? b.o : b.e);
+  r.o = a.o + ((a.o & 1) ? b.e : b.o);
+  return r;
+}
+__device__ __forceinline__ Inc2 clamp_inc(Inc2 a) { a.e = a.e < SAT_INC ? a.e : SAT_INC; a.o = a.o < SAT_INC ? a.o : SAT_INC; return a; }
 // base = bottom of the binade (0 for the subnormal/first-normal region), U = its ulp,
 // lim = weights >= lim certainly leave the binade.
 // iu1 * iu2 = 1 / U as two powers of two (1 / U itself overflows for the smallest binades): the quotient
@@ -149,12 +161,25 @@ __device__ __forceinline__ Inc2 block_exclusive_scan(Inc2 v, Inc2* total) {
   excl.e = __shfl_up_sync(0xffffffffu, incl.e, 1);
   excl.o = __shfl_up_sync(0xffffffffu, incl.o, 1);
   if (lane == 0) { excl.e = 0; excl.o = 0; }
-  Inc2 pre; pre.e = 0; pre.o = 0;
-  for (int w = 0; w < warp; w++) pre = combine(pre, warp_agg[w]);
+  // prefix over the warps' aggregates: every warp scans the SC_THREADS / 32 values itself with three shuffle
+  // steps (a serial walk per thread was 15 combines = a fifth of the scan's issued instructions)
+  constexpr int NW = SC_THREADS / 32;
+  Inc2 wv; wv.e = 0; wv.o = 0;
+  if (lane < NW) wv = warp_agg[lane];
+#pragma unroll
+  for (int o = 1; o < NW; o <<= 1) {
+    Inc2 other;
+    other.e = __shfl_up_sync(0xffffffffu, wv.e, o);
+    other.o = __shfl_up_sync(0xffffffffu, wv.o, o);
+    if (lane >= o && lane < NW) wv = combine(other, wv);
+  }
+  Inc2 pre;  // inclusive prefix of warp - 1 (identity for warp 0)
+  pre.e = __shfl_sync(0xffffffffu, wv.e, warp > 0 ? warp - 1 : 0);
+  pre.o = __shfl_sync(0xffffffffu, wv.o, warp > 0 ? warp - 1 : 0);
+  if (warp == 0) { pre.e = 0; pre.o = 0; }
   if (total) {
-    Inc2 t; t.e = 0; t.o = 0;
-    for (int w = 0; w < SC_THREADS / 32; w++) t = combine(t, warp_agg[w]);
-    *total = t;
+    total->e = __shfl_sync(0xffffffffu, wv.e, NW - 1);
+    total->o = __shfl_sync(0xffffffffu, wv.o, NW - 1);
   }
   __syncthreads();
   return combine(pre, excl);
@@ -199,19 +224,6 @@ __device__ __forceinline__ long long scan_window(double s0, double mean) {
   if (!(e >= 2048.0)) e = 2048.0;
   if (e > 67108864.0) e = 67108864.0;
   return (long long)e;
-}
-__global__ void k_scan_head(const double* __restrict__ w, int64_t n, double* __restrict__ S, ScanCtl* __restrict__ ctl, int64_t head) {
-  double cum = ctl->s0;
-  S[0] = cum;
-  ctl->c0 = cum;
-  // a scan that continues a running sum well inside a binade (a later rank of a sharded population) skips the
-  // sequential head: its first window is sized from the caller's mean-weight hint
-  if (cum > 0.0 && ctl->w_mean > 0.0) head = 0;
-  const int64_t m = head < n ? head : n;
-  for (int64_t i = 0; i < m; i++) { cum = __dadd_rn(cum, w[i]); S[i + 1] = cum; }
-  ctl->k0 = m; ctl->s0 = cum; ctl->first_cross = 0x7fffffffffffffffLL; ctl->cnt_a = 0; ctl->cnt_b = 0; ctl->round = 1;
-  ctl->win = scan_window(cum, m > 0 ? (cum - ctl->c0) / (double)m : ctl->w_mean);
-  ctl->serial = (cum != cum || cum == d_pos_inf()) ? 1 : 0;
 }
 // ---- one round = ONE pass over the window: chained scan with decoupled look-back (Merrill & Garland) ----
 // CTAs take tiles of 2048 weights in ticket order. A tile publishes its aggregate Inc2 pair, looks back
@@ -300,8 +312,9 @@ __global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __re
     for (int i = 0; i < SC_ITEMS; i++) {
       items[i].e = 0; items[i].o = 0;
       if (t0 + i < len) items[i] = make_inc(wv[i], B.base, B.U, B.lim, B.iu1, B.iu2);
-      a = combine(a, items[i]);
+      a = combine_raw(a, items[i]);
     }
+    a = clamp_inc(a);
     Inc2 total;
     const Inc2 pre = block_exclusive_scan(a, &total);
     if (warp == 0) {
@@ -318,7 +331,7 @@ __global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __re
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
       const int64_t j = t0 + i;
-      run = combine(run, items[i]);
+      run = combine_raw(run, items[i]);
       if (j < len) {
         const long long p = B.parity ? run.o : run.e;
         if (p >= B.need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
@@ -359,6 +372,109 @@ __global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __re
   ctl->round += 1;
   if (ns0 != ns0 || ns0 == d_pos_inf()) ctl->serial = 1;  // cannot happen with finite weights unless the sum overflows
 }
+// ---- the front of a scan in ONE single-CTA launch ------------------------------------------------------------
+// (a) The first SC_HEAD elements, where the running sum climbs through a binade every doubling of the count: the
+//     weights are staged in shared memory by coalesced loads, one thread walks them exactly as the reference does
+//     (from shared memory: ~10 cycles per add instead of an L2 round trip), S is written back coalesced.
+// (b) Every following window of at most SC_SMALL_MAX elements: the CTA scans its tiles one after the other with a
+//     running carry (no descriptors, no look-back), finds the first crossing, does the one floating add that
+//     changes binade and sizes the next window -- the same arithmetic as k_scan_round + its last-CTA epilogue.
+// ncu on the multi-launch form: a 32 us one-thread head and eight 13 us launches whose work is one tile, per
+// resample. A scan that continues a running sum well inside a binade (a later rank of a sharded population)
+// skips (a): its first window is sized from the caller's mean-weight hint and is normally too large for (b).
+#define SC_HEAD 512
+#define SC_SMALL_MAX 16384
+__global__ void __launch_bounds__(SC_THREADS) k_scan_front(const double* __restrict__ w, int64_t n, double* __restrict__ S, ScanCtl* __restrict__ ctl) {
+  __shared__ double s_w[SC_HEAD];
+  __shared__ double s_S[SC_HEAD + 1];
+  __shared__ long long sh_k0, sh_win, sh_cross;
+  __shared__ double sh_s0, sh_c0;
+  __shared__ int sh_serial;
+  __shared__ Inc2 s_carry;
+  const int tid = threadIdx.x;
+  const double c0 = ctl->s0, hint = ctl->w_mean;
+  const int64_t m = (c0 > 0.0 && hint > 0.0) ? 0 : (SC_HEAD < n ? SC_HEAD : n);
+  for (int64_t i = tid; i < m; i += SC_THREADS) s_w[i] = w[i];
+  __syncthreads();
+  if (tid == 0) {
+    double cum = c0;
+    s_S[0] = cum;
+    for (int64_t i = 0; i < m; i++) { cum = __dadd_rn(cum, s_w[i]); s_S[i + 1] = cum; }
+    sh_k0 = m; sh_s0 = cum; sh_c0 = c0;
+    sh_win = scan_window(cum, m > 0 ? (cum - c0) / (double)m : hint);
+    sh_serial = (cum != cum || cum == d_pos_inf()) ? 1 : 0;
+  }
+  __syncthreads();
+  for (int64_t i = tid; i <= m; i += SC_THREADS) S[i] = s_S[i];
+  for (int it = 0; it < 64; it++) {
+    __syncthreads();
+    const long long k0 = sh_k0, win = sh_win;
+    const double s0 = sh_s0;
+    if (k0 >= n || sh_serial || win > SC_SMALL_MAX) break;
+    const Binade B = binade_of(s0);
+    const int64_t len = min((long long)(n - k0), win);
+    const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
+    if (tid == 0) { s_carry.e = 0; s_carry.o = 0; sh_cross = 0x7fffffffffffffffLL; }
+    __syncthreads();
+    for (int t = 0; t < nt; t++) {
+      const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)tid * SC_ITEMS;
+      Inc2 items[SC_ITEMS];
+      Inc2 a; a.e = 0; a.o = 0;
+#pragma unroll
+      for (int i = 0; i < SC_ITEMS; i++) {
+        items[i].e = 0; items[i].o = 0;
+        if (t0 + i < len) items[i] = make_inc(w[k0 + t0 + i], B.base, B.U, B.lim, B.iu1, B.iu2);
+        a = combine_raw(a, items[i]);
+      }
+      a = clamp_inc(a);
+      Inc2 total;
+      const Inc2 pre = block_exclusive_scan(a, &total);
+      Inc2 run = combine(s_carry, pre);
+      long long cross = 0x7fffffffffffffffLL;
+#pragma unroll
+      for (int i = 0; i < SC_ITEMS; i++) {
+        const int64_t j = t0 + i;
+        run = combine_raw(run, items[i]);
+        if (j < len) {
+          const long long p = B.parity ? run.o : run.e;
+          if (p >= B.need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
+          else S[k0 + j + 1] = __dadd_rn(s0, __dmul_rn((double)p, B.U));
+        }
+      }
+      if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&sh_cross, (unsigned long long)cross);
+      __syncthreads();  // everyone has read s_carry
+      if (tid == 0) s_carry = combine(s_carry, total);
+      __syncthreads();
+      if (sh_cross != 0x7fffffffffffffffLL) break;  // uniform: read after the barrier
+    }
+    __syncthreads();
+    if (tid == 0) {  // advance (k_scan_round's epilogue)
+      const long long fc = sh_cross;
+      long long nk0; double ns0; bool crossed;
+      if (fc < len) {
+        const long long k = k0 + fc;
+        ns0 = __dadd_rn(*(volatile double*)&S[k], w[k]);
+        S[k + 1] = ns0;
+        nk0 = k + 1;
+        crossed = true;
+      } else {
+        nk0 = k0 + len;
+        ns0 = *(volatile double*)&S[k0 + len];
+        crossed = !(ns0 < B.T);
+      }
+      long long nw = crossed ? scan_window(ns0, (ns0 - sh_c0) / (double)nk0) : 2 * win;
+      if (nw < 2048) nw = 2048;
+      if (nw > (1LL << 26)) nw = 1LL << 26;
+      sh_k0 = nk0; sh_s0 = ns0; sh_win = nw;
+      if (ns0 != ns0 || ns0 == d_pos_inf()) sh_serial = 1;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    ctl->c0 = sh_c0; ctl->k0 = sh_k0; ctl->s0 = sh_s0; ctl->win = sh_win; ctl->serial = sh_serial;
+    ctl->first_cross = 0x7fffffffffffffffLL; ctl->cnt_a = 0; ctl->cnt_b = 0; ctl->round = 1;
+  }
+}
 // correctness fallback (weights with negatives / non-finite values): one thread, the reference loop
 __global__ void k_scan_serial(const double* __restrict__ w, int64_t from, int64_t n, double* __restrict__ S) {
   double cum = S[from];
@@ -383,7 +499,6 @@ static int scan_grid() {
   }
   return g;
 }
-#define SC_HEAD 512
 // enqueue `rounds` rounds (no host synchronisation); d_work: ScanCtl (64 B) followed by the tile aggregates
 int32_t scan_enqueue_rounds(const double* d_w, int64_t n, double* d_S, void* d_work, int rounds, cudaStream_t st, uint64_t* launches) {
   ScanCtl* ctl = (ScanCtl*)d_work;
@@ -403,15 +518,15 @@ int32_t scan_enqueue_rounds(const double* d_w, int64_t n, double* d_S, void* d_w
 // start a scan whose carry-in is already in ctl->s0 on the device (written by the host copy below or
 // by the sharded driver's carry kernel)
 int32_t scan_enqueue_head(const double* d_w, int64_t n, double* d_S, void* d_work, cudaStream_t st, uint64_t* launches) {
-  k_scan_head<<<1, 1, 0, st>>>(d_w, n, d_S, (ScanCtl*)d_work, SC_HEAD);
+  k_scan_front<<<1, SC_THREADS, 0, st>>>(d_w, n, d_S, (ScanCtl*)d_work);
   FC_KERNEL_CHECK();
   if (launches) *launches += 1;
   return FC_OK;
 }
 // rounds a scan of n elements is expected to need: one per binade the running sum passes after the head
 int scan_expected_rounds(int64_t n) {
-  int r = 4;
-  for (int64_t k = SC_HEAD; k < n; k *= 2) r++;
+  int r = 3;  // the front kernel has already passed the binades below SC_SMALL_MAX elements
+  for (int64_t k = SC_SMALL_MAX / 2; k < n; k *= 2) r++;
   return r;
 }
 // wait until the scan has consumed all n elements, enqueueing more rounds if it has not

@@ -1088,10 +1088,22 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       int i = 0;
       if (F.L.zw == 0) {  // one bit per site: the z region was cleared above; same draws, same order
 #pragma unroll 1
-        for (; i < n; i++) {
-          const bool lt = rng.uniform() < p0;
-          if (bern ? lt : !lt) zrec[(z0 + i) >> 3] |= (uint8_t)(1u << ((z0 + i) & 7));
+        for (; i < n; i += 56) {  // 56 sites per word: shifted by the start bit's offset in its byte it still fits 64 bits
+          unsigned long long wd = 0;
+          const int m = min(56, n - i);
+#pragma unroll 1
+          for (int b = 0; b < m; b++) {
+            const bool lt = rng.uniform() < p0;
+            if (bern ? lt : !lt) wd |= 1ULL << b;
+          }
+          const int bit0 = z0 + i;
+          wd <<= (bit0 & 7);
+          uint8_t* dstb = zrec + (bit0 >> 3);
+          const int nbytes = ((bit0 & 7) + m + 7) >> 3;
+#pragma unroll 1
+          for (int k = 0; k < nbytes; k++) dstb[k] |= (uint8_t)(wd >> (8 * k));
         }
+        i = n;
       }
       if ((z0 & 7) == 0 && F.L.zw == 1) {
         if (rng.has_spare && n > 0) {  // an odd number of draws so far: realign to whole blocks through the byte path
