@@ -543,7 +543,9 @@ int32_t fc_hmc_create_sharded(fc_program* p, const fc_hmc_config* cfg, uint64_t 
   k_fill<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(S->m_inv.p, 1.0, n);
   k_fill<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(S->mass_sqrt.p, 1.0, n);
   // initial state: prior draw (hmc.rs:673) unless the caller supplies one
-  FC_TRY(prior_sample_dev(p, S->q.p, S->qd.p, Cn, seed, first_chain, 0x7000000000000000ULL));
+  // (the prior pass walks a chain's sites serially: 12 ms at the C3 shape; skipped when the caller's q0 replaces all of it)
+  const bool q0_covers_all = h_q0 && d > 0 && (p->d_disc == 0 || h_qd0);
+  if (!q0_covers_all) FC_TRY(prior_sample_dev(p, S->q.p, S->qd.p, Cn, seed, first_chain, 0x7000000000000000ULL));
   if (h_q0 && d > 0) FC_CUDA(cudaMemcpyAsync(S->q.p, h_q0, d * Cn * 8, cudaMemcpyHostToDevice, st));
   if (h_qd0 && p->d_disc > 0) {
     const disc_t* conv = nullptr;
