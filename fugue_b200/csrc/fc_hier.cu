@@ -59,8 +59,8 @@ __global__ void __launch_bounds__(HR_TX, 6) k_hier_step(const __grid_constant__ 
   const int64_t u0 = (int64_t)blockIdx.y * A.units_per_split;
   const int64_t u1 = min(A.n_groups, u0 + A.units_per_split);
 
-  __shared__ double s_x[HAS_X ? HR_TILE : 1];
-  __shared__ double s_y[HR_TILE];
+  __shared__ double2 s_xy[HAS_X ? HR_TILE : 1];  // (x, y) of a staged element side by side: one 16-byte load per element
+  __shared__ double s_y[HAS_X ? 1 : HR_TILE];
 
   // ---- chain constants of the observation plate (k_plate_csr_normal's prologue) ----
   double base0 = 0.0, sig_s = 0.0;
@@ -127,16 +127,15 @@ __global__ void __launch_bounds__(HR_TX, 6) k_hier_step(const __grid_constant__ 
     clen = min(e_end - b, HR_TILE);
     for (int k = tid; k < clen; k += HR_TX) {
       const int64_t i = (int64_t)__ldg(A.grp_elems + b + k);
-      if (HAS_X) s_x[k] = __ldg(xcol + i);
-      s_y[k] = dcol_f64(op.value_col, i);
+      if (HAS_X) s_xy[k] = make_double2(__ldg(xcol + i), dcol_f64(op.value_col, i));
+      else s_y[k] = dcol_f64(op.value_col, i);
     }
     __syncthreads();
   };
   auto elem = [&](int k, double m0, double& sr_, double& srr_, double& srx_) {
-    const double y = s_y[k];
     double r;
-    if (HAS_X) { const double x = s_x[k]; r = y - fma(va, x, m0); srx_ = fma(r, x, srx_); }
-    else r = y - m0;
+    if (HAS_X) { const double2 xy = s_xy[k]; r = xy.y - fma(va, xy.x, m0); srx_ = fma(r, xy.x, srx_); }
+    else r = s_y[k] - m0;
     sr_ += r;
     srr_ = fma(r, r, srr_);
   };
@@ -237,18 +236,38 @@ struct HierTail {
   int32_t drift, _pad;
 };
 
+// CTA = 32 chains x HR_NACC accumulators: thread (cx, a) folds accumulator a of chain cx over the splits (in split
+// order: run-to-run reproducible; the loads of 8 splits are issued together), then the first warp finishes its 32
+// chains. (One thread per chain doing all of it was 62 us per launch at 1024 chains: 8 CTAs, a serial walk over
+// 880 partials per thread -- a quarter of the leapfrog step.)
 template <bool VAL>
-__global__ void __launch_bounds__(128) k_hier_tail(const __grid_constant__ HierTail A) {
+__global__ void __launch_bounds__(32 * HR_NACC) k_hier_tail(const __grid_constant__ HierTail A) {
   const int64_t C = A.C;
-  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+  const int cx = threadIdx.x & 31, ai = threadIdx.x >> 5;
+  const int64_t c = (int64_t)blockIdx.x * 32 + cx;
+  __shared__ double s_acc[HR_NACC][33];
+  {
+    double acc = 0.0;
+    if (c < C) {
+      const double* __restrict__ src = A.part + (int64_t)ai * C + c;
+      const int64_t stride = (int64_t)HR_NACC * C;
+      int64_t sp = 0;
+      for (; sp + 8 <= A.n_splits; sp += 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) v[u] = src[(sp + u) * stride];
+#pragma unroll
+        for (int u = 0; u < 8; u++) acc += v[u];
+      }
+      for (; sp < A.n_splits; sp++) acc += src[sp * stride];
+    }
+    s_acc[ai][cx] = acc;
+  }
+  __syncthreads();
+  if (ai != 0 || c >= C) return;
   double s[HR_NACC];
 #pragma unroll
-  for (int a = 0; a < HR_NACC; a++) s[a] = 0.0;
-  for (int64_t sp = 0; sp < A.n_splits; sp++) {
-#pragma unroll
-    for (int a = 0; a < HR_NACC; a++) s[a] += A.part[(sp * HR_NACC + a) * C + c];
-  }
+  for (int a = 0; a < HR_NACC; a++) s[a] = s_acc[a][cx];
   for (int i = 0; i < A.n_glob; i++) A.g_out[(int64_t)A.glob[i] * C + c] = 0.0;
   double a_prior = 0.0, a_lik = 0.0, a_fac = 0.0;
   auto za = [](int) -> long long { return 0; };  // no discrete sites in a fused hierarchical program
@@ -379,8 +398,8 @@ int32_t hier_step(fc_program* P, const HierPlan& H, double* q, double* p, const 
   T.n_scalar = (int32_t)P->scalar_ops.size(); T.n_glob = H.n_glob; T.gt = H.gt; T.xt = H.xt;
   for (int i = 0; i < HR_MAX_GLOB; i++) T.glob[i] = i < H.n_glob ? H.glob[i] : 0;
   T.kick = kick; T.drift = drift ? 1 : 0; T._pad = 0;
-  if (need_value) k_hier_tail<true><<<(unsigned)cdiv(C, 128), 128, 0, st>>>(T);
-  else k_hier_tail<false><<<(unsigned)cdiv(C, 128), 128, 0, st>>>(T);
+  if (need_value) k_hier_tail<true><<<(unsigned)cdiv(C, 32), 32 * HR_NACC, 0, st>>>(T);
+  else k_hier_tail<false><<<(unsigned)cdiv(C, 32), 32 * HR_NACC, 0, st>>>(T);
   FC_KERNEL_CHECK();
   P->n_kernel_launches += 2;
   return FC_OK;
