@@ -225,121 +225,141 @@ __device__ __forceinline__ long long scan_window(double s0, double mean) {
   if (e > 67108864.0) e = 67108864.0;
   return (long long)e;
 }
-// ---- one round = ONE pass over the window: chained scan with decoupled look-back (Merrill & Garland) ----
-// CTAs take tiles of 2048 weights in ticket order. A tile publishes its aggregate Inc2 pair, looks back
-// over its predecessors' descriptors (32 at a time, one per lane of warp 0) until it meets one that
-// already carries an inclusive prefix, publishes its own inclusive prefix and writes S. `combine` is
-// associative but not commutative: the farther tile is always the left operand. A descriptor is two
-// 64-bit words (the even-start and odd-start increments, 56 bits each) tagged with a 2-bit status and
-// the 6-bit round number, so descriptors of earlier rounds read as "not ready" without being cleared.
-#define LB_AGG 1ULL
-#define LB_INCL 2ULL
-#define LB_VAL_MASK ((1ULL << 56) - 1)
-__device__ __forceinline__ unsigned long long ld_relaxed_gpu(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_relaxed_gpu(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ void lb_publish(unsigned long long* desc, int t, unsigned long long status, unsigned long long epoch, const Inc2& v) {
-  const unsigned long long tag = (status << 62) | (epoch << 56);
-  st_relaxed_gpu(desc + 2 * t, tag | (unsigned long long)v.e);
-  st_relaxed_gpu(desc + 2 * t + 1, tag | (unsigned long long)v.o);
-}
-// exclusive prefix of tile t (t >= 1); all 32 lanes of one warp
-__device__ __forceinline__ Inc2 lb_lookback(const unsigned long long* desc, int t, unsigned long long epoch, int lane, int* give_up) {
-  Inc2 excl; excl.e = 0; excl.o = 0;
-  for (int j = t - 1;; j -= 32) {
-    const int idx = j - lane;
-    unsigned long long we = LB_INCL << 62, wo = LB_INCL << 62;  // tiles before the window: inclusive identity
-    if (idx >= 0) {
-      for (unsigned spin = 0;; spin++) {
-        we = ld_relaxed_gpu(desc + 2 * idx);
-        wo = ld_relaxed_gpu(desc + 2 * idx + 1);
-        const unsigned long long te = we >> 56, to = wo >> 56;
-        if (te == to && (te & 63ULL) == epoch && (te >> 6) != 0) break;  // both words of this round, same status
-        // a predecessor is always a running or finished CTA, so this wait ends; should it ever not, hand the
-        // rest of the scan to the sequential loop instead of hanging the device
-        if (spin > (1u << 27) || *(volatile int*)give_up) { *give_up = 1; we = wo = LB_INCL << 62; break; }
-      }
-    }
-    Inc2 v; v.e = (long long)(we & LB_VAL_MASK); v.o = (long long)(wo & LB_VAL_MASK);
-    const unsigned incl = __ballot_sync(0xffffffffu, (we >> 62) == LB_INCL);
-    const int first = __ffs(incl) - 1;  // the nearest predecessor that already has an inclusive prefix
-    const int last = first >= 0 ? first : 31;
-    if (lane > last) { v.e = 0; v.o = 0; }
+// ---- one round = the window [k0, k0 + len) of the current binade, as reduce -> scan -> apply ----------------------
+// (The first version of this round was ONE kernel, a chained scan with decoupled look-back. ncu launch lists showed it
+// at ~0.6 TB/s on multi-million-element windows whatever its instruction count: tiles spin on their predecessors'
+// descriptors and take tickets from one atomic. Three plain kernels with no inter-CTA waiting do the same work faster
+// and cannot hang: the weights are read twice, the second time mostly from L2.)
+//   k_scan_agg    per tile of 2048 weights: the Inc2 aggregate (increment pair for an even / odd start)
+//   k_scan_tiles  one CTA: exclusive scan of the tile aggregates under `combine`; the first tile whose inclusive prefix
+//                 reaches the binade top (later tiles need no work)
+//   k_scan_apply  per tile: prefix sums from the tile's exclusive prefix -> S, first crossing; the last CTA does the
+//                 one floating add that changes binade and sets up the next window
+__global__ void __launch_bounds__(SC_THREADS, 4) k_scan_agg(const double* __restrict__ w, int64_t n, const ScanCtl* __restrict__ ctl, Inc2* __restrict__ agg) {
+  const long long k0 = ctl->k0;
+  if (k0 >= n || ctl->serial) return;
+  const Binade B = binade_of(ctl->s0);
+  const int64_t len = min((long long)(n - k0), (long long)ctl->win);
+  const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ Inc2 s_w[SC_THREADS / 32];
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int t0 = t * SC_TILE + (int)threadIdx.x * SC_ITEMS;
+    const int nval = (int)max(0LL, min((long long)SC_ITEMS, (long long)len - t0));
+    const double* __restrict__ wp = w + k0 + t0;
+    double wv[SC_ITEMS];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {  // ordered reduction: lane 0 ends with v[last] o ... o v[1] o v[0]
-      Inc2 far;
-      far.e = __shfl_down_sync(0xffffffffu, v.e, o);
-      far.o = __shfl_down_sync(0xffffffffu, v.o, o);
-      if (lane + o < 32) v = combine(far, v);
+    for (int i = 0; i < SC_ITEMS; i++) wv[i] = i < nval ? wp[i] : 0.0;
+    Inc2 a; a.e = 0; a.o = 0;
+#pragma unroll
+    for (int i = 0; i < SC_ITEMS; i++) {
+      Inc2 it; it.e = 0; it.o = 0;
+      if (i < nval) it = make_inc(wv[i], B.base, B.U, B.lim, B.iu1, B.iu2);
+      a = combine_raw(a, it);
     }
-    Inc2 part;
-    part.e = __shfl_sync(0xffffffffu, v.e, 0);
-    part.o = __shfl_sync(0xffffffffu, v.o, 0);
-    excl = combine(part, excl);
-    if (first >= 0) return excl;
+    a = clamp_inc(a);
+    // ordered reduction over the CTA: lane 31 of each warp ends with the warp's aggregate
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      Inc2 other;
+      other.e = __shfl_up_sync(0xffffffffu, a.e, o);
+      other.o = __shfl_up_sync(0xffffffffu, a.o, o);
+      if (lane >= o) a = combine(other, a);
+    }
+    if (lane == 31) s_w[warp] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      Inc2 tot = s_w[0];
+      for (int q = 1; q < SC_THREADS / 32; q++) tot = combine(tot, s_w[q]);
+      agg[t] = tot;
+    }
+    __syncthreads();
   }
 }
-__global__ void __launch_bounds__(SC_THREADS, 3) k_scan_round(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, unsigned long long* __restrict__ desc, double* __restrict__ S) {
+#define ST_THREADS 1024
+__global__ void __launch_bounds__(ST_THREADS) k_scan_tiles(int64_t n, ScanCtl* __restrict__ ctl, const Inc2* __restrict__ agg, Inc2* __restrict__ excl) {
+  const long long k0 = ctl->k0;
+  if (k0 >= n || ctl->serial) return;
+  const Binade B = binade_of(ctl->s0);
+  const int64_t len = min((long long)(n - k0), (long long)ctl->win);
+  const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
+  const int per = (nt + ST_THREADS - 1) / ST_THREADS;
+  const int b0 = threadIdx.x * per, b1 = min(nt, b0 + per);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ Inc2 s_w[ST_THREADS / 32];
+  __shared__ unsigned s_cross;
+  if (threadIdx.x == 0) s_cross = 0xffffffffu;
+  Inc2 a; a.e = 0; a.o = 0;
+  for (int t = b0; t < b1; t++) a = combine(a, agg[t]);
+  Inc2 incl = a;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    Inc2 other;
+    other.e = __shfl_up_sync(0xffffffffu, incl.e, o);
+    other.o = __shfl_up_sync(0xffffffffu, incl.o, o);
+    if (lane >= o) incl = combine(other, incl);
+  }
+  if (lane == 31) s_w[warp] = incl;
+  __syncthreads();
+  Inc2 pre; pre.e = 0; pre.o = 0;
+  for (int q = 0; q < warp; q++) pre = combine(pre, s_w[q]);
+  Inc2 ex;
+  ex.e = __shfl_up_sync(0xffffffffu, incl.e, 1);
+  ex.o = __shfl_up_sync(0xffffffffu, incl.o, 1);
+  if (lane == 0) { ex.e = 0; ex.o = 0; }
+  Inc2 run = combine(pre, ex);  // exclusive prefix of this thread's first tile
+  unsigned cross = 0xffffffffu;
+  for (int t = b0; t < b1; t++) {
+    excl[t] = run;
+    run = combine(run, agg[t]);
+    if (cross == 0xffffffffu && (B.parity ? run.o : run.e) >= B.need) cross = (unsigned)t;
+  }
+  if (cross != 0xffffffffu) atomicMin(&s_cross, cross);
+  __syncthreads();
+  if (threadIdx.x == 0) ctl->cnt_a = s_cross;  // the first tile in which the sum reaches the binade top (0xffffffff: none)
+}
+__global__ void __launch_bounds__(SC_THREADS, 3) k_scan_apply(const double* __restrict__ w, int64_t n, ScanCtl* __restrict__ ctl, const Inc2* __restrict__ excl, double* __restrict__ S) {
   const long long k0 = ctl->k0;
   if (k0 >= n || ctl->serial) return;
   const double s0 = ctl->s0;
   const Binade B = binade_of(s0);
   const long long win = ctl->win;
-  const unsigned long long epoch = (unsigned long long)(ctl->round & 63);
   const int64_t len = min((long long)(n - k0), win);
-  const int nt = (int)((len + SC_TILE - 1) / SC_TILE);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __shared__ int s_tile;
-  __shared__ Inc2 s_excl;
-  long long cross = 0x7fffffffffffffffLL;
-  for (;;) {
-    if (threadIdx.x == 0) s_tile = (int)atomicAdd(&ctl->cnt_a, 1u);
-    __syncthreads();
-    const int t = s_tile;
-    if (t >= nt) break;
-    const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)threadIdx.x * SC_ITEMS;
+  const int nt_all = (int)((len + SC_TILE - 1) / SC_TILE);
+  const unsigned ct = ctl->cnt_a;
+  const int nt = ct == 0xffffffffu ? nt_all : min(nt_all, (int)ct + 1);  // tiles after the crossing tile are not needed
+  int cross = 0x7fffffff;
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int t0 = t * SC_TILE + (int)threadIdx.x * SC_ITEMS;
+    const int nval = (int)max(0LL, min((long long)SC_ITEMS, (long long)len - t0));
+    const double* __restrict__ wp = w + k0 + t0;
+    double* __restrict__ Sp = S + k0 + t0 + 1;
     double wv[SC_ITEMS];
 #pragma unroll
-    for (int i = 0; i < SC_ITEMS; i++) wv[i] = t0 + i < len ? w[k0 + t0 + i] : 0.0;
+    for (int i = 0; i < SC_ITEMS; i++) wv[i] = i < nval ? wp[i] : 0.0;
     Inc2 items[SC_ITEMS];
     Inc2 a; a.e = 0; a.o = 0;
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
       items[i].e = 0; items[i].o = 0;
-      if (t0 + i < len) items[i] = make_inc(wv[i], B.base, B.U, B.lim, B.iu1, B.iu2);
+      if (i < nval) items[i] = make_inc(wv[i], B.base, B.U, B.lim, B.iu1, B.iu2);
       a = combine_raw(a, items[i]);
     }
     a = clamp_inc(a);
-    Inc2 total;
-    const Inc2 pre = block_exclusive_scan(a, &total);
-    if (warp == 0) {
-      if (lane == 0) lb_publish(desc, t, t == 0 ? LB_INCL : LB_AGG, epoch, total);
-      Inc2 ex; ex.e = 0; ex.o = 0;
-      if (t > 0) {
-        ex = lb_lookback(desc, t, epoch, lane, &ctl->serial);
-        if (lane == 0) lb_publish(desc, t, LB_INCL, epoch, combine(ex, total));
-      }
-      if (lane == 0) s_excl = ex;
-    }
-    __syncthreads();
-    Inc2 run = combine(s_excl, pre);
+    const Inc2 pre = block_exclusive_scan(a, nullptr);
+    // the start of every item is known from here on (the window starts at parity B.parity): follow the one actual path
+    const Inc2 run = combine(excl[t], pre);
+    long long p = B.parity ? run.o : run.e;  // ulps gained since the window start
 #pragma unroll
     for (int i = 0; i < SC_ITEMS; i++) {
-      const int64_t j = t0 + i;
-      run = combine_raw(run, items[i]);
-      if (j < len) {
-        const long long p = B.parity ? run.o : run.e;
-        if (p >= B.need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
-        else S[k0 + j + 1] = __dadd_rn(s0, __dmul_rn((double)p, B.U));  // exact: on the U grid below the binade top
+      p += ((B.parity + (int)p) & 1) ? items[i].o : items[i].e;
+      if (i < nval) {
+        if (p >= B.need) cross = min(cross, t0 + i);
+        else Sp[i] = __dadd_rn(s0, __dmul_rn((double)p, B.U));  // exact: on the U grid below the binade top
       }
     }
   }
-  if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&ctl->first_cross, (unsigned long long)cross);
+  if (cross != 0x7fffffff) atomicMin((unsigned long long*)&ctl->first_cross, (unsigned long long)cross);
   __shared__ bool is_last;
   __syncthreads();
   if (threadIdx.x == 0) { __threadfence(); is_last = atomicAdd(&ctl->cnt_b, 1u) == gridDim.x - 1; }
@@ -417,31 +437,33 @@ __global__ void __launch_bounds__(SC_THREADS) k_scan_front(const double* __restr
     if (tid == 0) { s_carry.e = 0; s_carry.o = 0; sh_cross = 0x7fffffffffffffffLL; }
     __syncthreads();
     for (int t = 0; t < nt; t++) {
-      const int64_t t0 = (int64_t)t * SC_TILE + (int64_t)tid * SC_ITEMS;
+      const int t0 = t * SC_TILE + tid * SC_ITEMS;
+      const int nval = (int)max(0LL, min((long long)SC_ITEMS, (long long)len - t0));
+      const double* __restrict__ wp = w + k0 + t0;
+      double* __restrict__ Sp = S + k0 + t0 + 1;
       Inc2 items[SC_ITEMS];
       Inc2 a; a.e = 0; a.o = 0;
 #pragma unroll
       for (int i = 0; i < SC_ITEMS; i++) {
         items[i].e = 0; items[i].o = 0;
-        if (t0 + i < len) items[i] = make_inc(w[k0 + t0 + i], B.base, B.U, B.lim, B.iu1, B.iu2);
+        if (i < nval) items[i] = make_inc(wp[i], B.base, B.U, B.lim, B.iu1, B.iu2);
         a = combine_raw(a, items[i]);
       }
       a = clamp_inc(a);
       Inc2 total;
       const Inc2 pre = block_exclusive_scan(a, &total);
-      Inc2 run = combine(s_carry, pre);
-      long long cross = 0x7fffffffffffffffLL;
+      const Inc2 run = combine(s_carry, pre);
+      long long p = B.parity ? run.o : run.e;
+      int cross = 0x7fffffff;
 #pragma unroll
       for (int i = 0; i < SC_ITEMS; i++) {
-        const int64_t j = t0 + i;
-        run = combine_raw(run, items[i]);
-        if (j < len) {
-          const long long p = B.parity ? run.o : run.e;
-          if (p >= B.need) { if (cross == 0x7fffffffffffffffLL) cross = j; }
-          else S[k0 + j + 1] = __dadd_rn(s0, __dmul_rn((double)p, B.U));
+        p += ((B.parity + (int)p) & 1) ? items[i].o : items[i].e;
+        if (i < nval) {
+          if (p >= B.need) cross = min(cross, t0 + i);
+          else Sp[i] = __dadd_rn(s0, __dmul_rn((double)p, B.U));
         }
       }
-      if (cross != 0x7fffffffffffffffLL) atomicMin((unsigned long long*)&sh_cross, (unsigned long long)cross);
+      if (cross != 0x7fffffff) atomicMin((unsigned long long*)&sh_cross, (unsigned long long)cross);
       __syncthreads();  // everyone has read s_carry
       if (tid == 0) s_carry = combine(s_carry, total);
       __syncthreads();
@@ -488,7 +510,7 @@ __global__ void k_scan_serial_tail(const double* __restrict__ w, int64_t n, doub
   ctl->k0 = n; ctl->s0 = cum; ctl->serial = 0;
 }
 
-size_t scan_work_bytes(int64_t n) { return 64 + (size_t)(cdiv(std::max<int64_t>(n, 1), SC_TILE) + 8) * sizeof(Inc2); }
+size_t scan_work_bytes(int64_t n) { return 64 + 2 * (size_t)(cdiv(std::max<int64_t>(n, 1), SC_TILE) + 8) * sizeof(Inc2); }  // control block, tile aggregates, tile prefixes
 static int scan_grid() {
   static int g = 0;
   if (!g) {
@@ -502,17 +524,18 @@ static int scan_grid() {
 // enqueue `rounds` rounds (no host synchronisation); d_work: ScanCtl (64 B) followed by the tile aggregates
 int32_t scan_enqueue_rounds(const double* d_w, int64_t n, double* d_S, void* d_work, int rounds, cudaStream_t st, uint64_t* launches) {
   ScanCtl* ctl = (ScanCtl*)d_work;
-  unsigned long long* desc = (unsigned long long*)((char*)d_work + 64);
   const int64_t tiles = cdiv(std::max<int64_t>(n, 1), SC_TILE);
+  Inc2* agg = (Inc2*)((char*)d_work + 64);
+  Inc2* excl = agg + tiles + 8;
   const int g = (int)std::max<int64_t>(1, std::min<int64_t>(scan_grid(), tiles));
-  // descriptors carry the round number modulo 64: clear them once per batch of at most 32 rounds
-  for (int r0 = 0; r0 < rounds; r0 += 32) {
-    FC_CUDA(cudaMemsetAsync(desc, 0, (size_t)tiles * 16, st));
-    for (int r = r0; r < std::min(rounds, r0 + 32); r++) k_scan_round<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, desc, d_S);
+  for (int r = 0; r < rounds; r++) {
+    k_scan_agg<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, agg);
+    k_scan_tiles<<<1, ST_THREADS, 0, st>>>(n, ctl, agg, excl);
+    k_scan_apply<<<g, SC_THREADS, 0, st>>>(d_w, n, ctl, excl, d_S);
   }
   k_scan_serial_tail<<<1, 1, 0, st>>>(d_w, n, d_S, ctl);
   FC_KERNEL_CHECK();
-  if (launches) *launches += rounds + 1;
+  if (launches) *launches += 3 * rounds + 1;
   return FC_OK;
 }
 // start a scan whose carry-in is already in ctl->s0 on the device (written by the host copy below or
@@ -525,7 +548,7 @@ int32_t scan_enqueue_head(const double* d_w, int64_t n, double* d_S, void* d_wor
 }
 // rounds a scan of n elements is expected to need: one per binade the running sum passes after the head
 int scan_expected_rounds(int64_t n) {
-  int r = 3;  // the front kernel has already passed the binades below SC_SMALL_MAX elements
+  int r = 2;  // the front kernel has already passed the binades below SC_SMALL_MAX elements
   for (int64_t k = SC_SMALL_MAX / 2; k < n; k *= 2) r++;
   return r;
 }
@@ -622,7 +645,7 @@ struct ResampleWork {
   int32_t reserve(int64_t n) {
     FC_CUDA(S.reserve(n + 2));
     FC_CUDA(scratch.reserve(RD_BLOCKS + 8));
-    FC_CUDA(work.reserve(64 + (cdiv(std::max<int64_t>(n, 1), SC_TILE) + 8) * sizeof(Inc2)));
+    FC_CUDA(work.reserve(scan_work_bytes(n)));
     return FC_OK;
   }
 };
