@@ -301,8 +301,19 @@ __global__ void __launch_bounds__(ST_THREADS) k_scan_tiles(int64_t n, ScanCtl* _
   }
   if (lane == 31) s_w[warp] = incl;
   __syncthreads();
-  Inc2 pre; pre.e = 0; pre.o = 0;
-  for (int q = 0; q < warp; q++) pre = combine(pre, s_w[q]);
+  // prefix over the 32 warp aggregates: every warp scans them itself with five shuffle steps
+  Inc2 wv = s_w[lane];
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    Inc2 other;
+    other.e = __shfl_up_sync(0xffffffffu, wv.e, o);
+    other.o = __shfl_up_sync(0xffffffffu, wv.o, o);
+    if (lane >= o) wv = combine(other, wv);
+  }
+  Inc2 pre;
+  pre.e = __shfl_sync(0xffffffffu, wv.e, warp > 0 ? warp - 1 : 0);
+  pre.o = __shfl_sync(0xffffffffu, wv.o, warp > 0 ? warp - 1 : 0);
+  if (warp == 0) { pre.e = 0; pre.o = 0; }
   Inc2 ex;
   ex.e = __shfl_up_sync(0xffffffffu, incl.e, 1);
   ex.o = __shfl_up_sync(0xffffffffu, incl.o, 1);
