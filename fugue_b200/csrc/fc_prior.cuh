@@ -33,6 +33,9 @@ struct DevRng {
   __device__ double exponential() { return -log(uniform_open()); }
   __device__ double gamma(double k) {  // Marsaglia & Tsang (2000), unit rate
     if (!(k > 0.0) || !isfinite(k)) return __longlong_as_double(0x7ff8000000000000LL);
+    // shape 1 is the exponential: one uniform and one log instead of a rejection loop whose trip count is the
+    // maximum over the warp's lanes (Gamma(1, .) and Beta(1, 1) priors: a third of the SMC prior kernel's instructions)
+    if (k == 1.0) return exponential();
     double boost = 1.0;
     if (k < 1.0) { boost = pow(uniform_open(), 1.0 / k); k += 1.0; }
     double d = k - 1.0 / 3.0, c = 1.0 / sqrt(9.0 * d);

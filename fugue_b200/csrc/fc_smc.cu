@@ -875,6 +875,31 @@ __device__ __noinline__ void mix_stats(const FusedProg& F, const FPlate& fp, con
   st[1] = m0; st[2] = q0; st[3] = m1; st[4] = q1;
 }
 
+// the same from a discrete state held in two registers (one bit per site, at most 128 sites)
+__device__ __noinline__ void mix_stats_bits(const FusedProg& F, const FPlate& fp, unsigned long long zr0, unsigned long long zr1, double* __restrict__ st) {
+  const int z0 = (int)F.ops[fp.op].dslot0;
+  const double* __restrict__ xs = (const double*)F.ops[fp.op_b].value_col.ptr;
+  auto zbit = [&](int bit) -> unsigned { return (unsigned)(((bit < 64 ? zr0 >> bit : zr1 >> (bit - 64))) & 1ULL); };
+  double s0 = 0.0, s1 = 0.0;
+  int n1 = 0;
+#pragma unroll 1
+  for (int i = 0; i < fp.n; i++) {
+    const unsigned zi = zbit(z0 + i);
+    const double x = __ldg(xs + i);
+    if (zi) { n1++; s1 += x; } else s0 += x;
+  }
+  const int n0 = fp.n - n1;
+  const double m0 = n0 ? s0 / (double)n0 : 0.0, m1 = n1 ? s1 / (double)n1 : 0.0;
+  double q0 = 0.0, q1 = 0.0;
+#pragma unroll 1
+  for (int i = 0; i < fp.n; i++) {
+    const unsigned zi = zbit(z0 + i);
+    const double d = __ldg(xs + i) - (zi ? m1 : m0);
+    if (zi) q1 = fma(d, d, q1); else q0 = fma(d, d, q0);
+  }
+  st[0] = (double)n1; st[1] = m0; st[2] = q0; st[3] = m1; st[4] = q1;
+}
+
 // log_prior / log_likelihood / log_factors of one particle: scalar ops, then every plate, in program
 // order; elements of a plate summed in order with one accumulator (the generic kernels' order).
 __device__ __forceinline__ void fused_eval(const FusedProg& F, const uint8_t* __restrict__ rec, double (&lp)[3]) {
@@ -1063,7 +1088,12 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
   uint8_t* rec = pop.rec + c * F.L.pitch;
   double* q = (double*)rec;
   uint8_t* zrec = rec + F.L.zoff;
-  if (F.L.zw == 0)
+  // one bit per site: up to 128 discrete sites are assembled in two registers and stored once (read-modify-write
+  // on the record's bytes was a chain of dependent global accesses per particle); larger states clear the region
+  // and set bits in memory
+  const bool zregs = F.L.zw == 0 && F.L.d_disc <= 128;
+  unsigned long long zr0 = 0, zr1 = 0;
+  if (F.L.zw == 0 && !zregs)
     for (int64_t b = F.L.zoff; b < F.L.pitch; b += 16) *(uint4*)(rec + b) = make_uint4(0u, 0u, 0u, 0u);
   for (int oi = 0; oi < F.n_ops; oi++) {
     const DOp& op = F.ops[oi];
@@ -1075,6 +1105,7 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       long long xi;
       op_dist_sample(rng, op, pv[0], pv[1], pv[2], x, xi);
       if (op.cont) q[F.crow[op.cslot0]] = x;
+      else if (zregs) { if (xi) { if (op.dslot0 < 64) zr0 |= 1ULL << op.dslot0; else zr1 |= 1ULL << (op.dslot0 - 64); } }
       else if (F.L.zw == 0) { if (xi) zrec[op.dslot0 >> 3] |= (uint8_t)(1u << (op.dslot0 & 7)); }
       else if (F.L.zw == 1) zrec[op.dslot0] = (uint8_t)xi;
       else ((int32_t*)zrec)[op.dslot0] = (int32_t)xi;
@@ -1086,7 +1117,15 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       // loops are kept rolled -- 16 inlined draws per trip thrashed the instruction cache (ncu: 18 of 22
       // stall samples "no instruction", 31 ms) -- and 8 sites are packed per 8-byte store.
       int i = 0;
-      if (F.L.zw == 0) {  // one bit per site: the z region was cleared above; same draws, same order
+      if (zregs) {
+#pragma unroll 1
+        for (; i < n; i++) {
+          const bool lt = rng.uniform() < p0;
+          const int bit = z0 + i;
+          if (bern ? lt : !lt) { if (bit < 64) zr0 |= 1ULL << bit; else zr1 |= 1ULL << (bit - 64); }
+        }
+      }
+      if (F.L.zw == 0 && !zregs) {  // one bit per site: the z region was cleared above; same draws, same order
 #pragma unroll 1
         for (; i < n; i += 56) {  // 56 sites per word: shifted by the start bit's offset in its byte it still fits 64 bits
           unsigned long long wd = 0;
@@ -1132,9 +1171,16 @@ __global__ void __launch_bounds__(128) k_smcx_prior(const __grid_constant__ Fuse
       }
     }
   }
+  if (zregs) {
+    *(ulonglong2*)zrec = make_ulonglong2(zr0, zr1);  // the z region is 16-byte aligned and at least 16 bytes long
+    for (int64_t b = F.L.zoff + 16; b < F.L.pitch; b += 16) *(uint4*)(rec + b) = make_uint4(0u, 0u, 0u, 0u);
+  }
   if (F.L.soff)
     for (int pi = 0; pi < F.n_plates; pi++)
-      if (F.plates[pi].kind == FP_MIX && F.plates[pi].stat) mix_stats(F, F.plates[pi], zrec, (double*)(rec + F.L.soff));
+      if (F.plates[pi].kind == FP_MIX && F.plates[pi].stat) {
+        if (zregs) mix_stats_bits(F, F.plates[pi], zr0, zr1, (double*)(rec + F.L.soff));
+        else mix_stats(F, F.plates[pi], zrec, (double*)(rec + F.L.soff));
+      }
   double lp[3];
   fused_eval(F, rec, lp);
   double* l3 = q + F.L.d_cont;

@@ -185,7 +185,10 @@ CONT = [("Normal", (1.5, 2.0), lambda st: st.norm(1.5, 2.0)), ("Uniform", (-2.0,
         ("Gamma", (3.0, 2.0), lambda st: st.gamma(3.0, scale=0.5)), ("Gamma", (0.4, 1.5), lambda st: st.gamma(0.4, scale=1 / 1.5)),
         ("StudentT", (5.0, 1.0, 2.0), lambda st: st.t(5.0, loc=1.0, scale=2.0)), ("Cauchy", (0.5, 1.5), lambda st: st.cauchy(0.5, 1.5)),
         ("Laplace", (-1.0, 0.8), lambda st: st.laplace(-1.0, 0.8)), ("Weibull", (1.7, 2.5), lambda st: st.weibull_min(1.7, scale=2.5)),
-        ("ChiSquared", (4.0,), lambda st: st.chi2(4.0)), ("InverseGamma", (3.5, 2.0), lambda st: st.invgamma(3.5, scale=2.0))]
+        ("ChiSquared", (4.0,), lambda st: st.chi2(4.0)), ("InverseGamma", (3.5, 2.0), lambda st: st.invgamma(3.5, scale=2.0)),
+        # shape 1 takes the exponential short cut of DevRng::gamma (fc_prior.cuh)
+        ("Gamma", (1.0, 1.5), lambda st: st.gamma(1.0, scale=1 / 1.5)), ("Beta", (1.0, 1.0), lambda st: st.uniform(0.0, 1.0)),
+        ("ChiSquared", (2.0,), lambda st: st.chi2(2.0))]
 
 
 @pytest.mark.parametrize("name,args,ref", CONT, ids=[f"{c[0]}{c[1]}" for c in CONT])
