@@ -288,7 +288,7 @@ def smc_bench(args, rank, world, local, barrier, allmax):
                    "l2": f"population larger than L2 ({n_local * 144 / 1e6:.0f} MB of particle records per GPU)"},
         "temper_steps": steps_seen, "runs": reps, "ms_per_run": sum(times) / len(times), "ms_per_temper_step": sum(times) / sum(steps_seen),
         "roofline": {"bound": "hbm", "achieved": move_gbs, "peak": hbm, "unit": "GB/s", "frac": move_gbs / hbm,
-                     "traffic": ncu_traffic("launches_c4_r2_v5_summary.txt", "k_smcx_move"), "traffic_unit": "bytes per launch at 2^24 particles (ncu dram read+write, profiles/launches_c4_r2_v5_summary.txt)",
+                     "traffic": ncu_traffic("launches_c4_r2_v8_summary.txt", "k_smcx_move"), "traffic_unit": "bytes per launch at 2^24 particles (ncu dram read+write, profiles/launches_c4_r2_v8_summary.txt)",
                      "kernel": "k_smcx_move", "launch_ms": move_ms, "launches_timed": int(nphase[4]), "peak_source": how,
                      "note": f"algorithmic bytes = {SMC_ALG_BYTES_PER_MOVE} B per particle and move (SURVEY 8d) x particles per launch; the kernel scores the proposal in O(1) from the per-particle mixture statistics and is issue-bound (~1300 instructions per particle: Philox, Box-Muller, 9 log): see DESIGN.md 3.2"},
         "roofline_step": {"bound": "hbm", "achieved": value / world * SMC_ALG_BYTES_PER_UPDATE / 1e9, "peak": hbm, "unit": "GB/s", "frac": value / world * SMC_ALG_BYTES_PER_UPDATE / 1e9 / hbm,

@@ -1825,7 +1825,7 @@ static int32_t smc_resample(fc_smc_session* S, int method, const double* h_unifo
     FC_CUDA(cudaMemcpyAsync(S->work.p, &hs, sizeof(hs), cudaMemcpyHostToDevice, st));
     k_chain_wait<<<1, 1, 0, st>>>(S->cm, S->resamples, (ScanCtl*)S->work.p);
     FC_TRY(scan_enqueue_head(S->w.p, n, S->S.p, S->work.p, st, &P->n_kernel_launches));
-    FC_TRY(scan_enqueue_rounds(S->w.p, n, S->S.p, S->work.p, S->rank == 0 ? scan_expected_rounds(n) : 3, st, &P->n_kernel_launches));
+    FC_TRY(scan_enqueue_rounds(S->w.p, n, S->S.p, S->work.p, S->rank == 0 ? scan_expected_rounds(n) : 2, st, &P->n_kernel_launches));  // a later rank: one round, two if its range crosses a binade (scan_finish adds more if ever needed)
     if (W > 1) k_chain_publish<<<1, 32, 0, st>>>(S->cm, S->resamples, (const ScanCtl*)S->work.p, n);  // publishes iff the scan is complete
     FC_TRY(scan_finish(S->w.p, n, S->S.p, S->work.p, st, &P->n_kernel_launches, nullptr));
     P->n_kernel_launches += 1;
