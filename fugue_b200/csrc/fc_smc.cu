@@ -6,19 +6,21 @@
 // (:719-753) and smc_prior_particles (:764-790).
 //
 // Population container. One contiguous RECORD per particle: its f64 sites (sorted address order), the
-// three Trace accumulators, then its discrete sites in program order (one byte per site when every
-// discrete support fits, else four), padded to 16 bytes -- a particle is cloned as a whole by
-// resampling (smc.rs:326-349) and read as a whole by a rejuvenation move, so both are streams of
-// 16-byte vector accesses over consecutive records (C4: 144 B per particle). Only the log-likelihood
-// lives in a dense array of its own (the tempering passes stream over it). The cached accumulators
-// travel with the particle, so a move scores the proposal only (the reference re-scores the current
-// state as well: 2 model runs per move, smc.rs:659-676).
+// three Trace accumulators, the sufficient statistics of a mixture plate (when the program has one), then
+// its discrete sites in program order (one BIT per site when every discrete site is two-valued and the
+// statistics are carried, else one byte when every support fits, else four), padded to 16 bytes -- a particle
+// is cloned as a whole by resampling (smc.rs:326-349) and read as a whole by a rejuvenation move, so both are
+// streams of 16-byte vector accesses over consecutive records (C4: 128 B per particle). Only the
+// log-likelihood lives in a dense array of its own (the tempering passes stream over it). The cached
+// accumulators travel with the particle, so a move scores the proposal only (the reference re-scores the
+// current state as well: 2 model runs per move, smc.rs:659-676).
 //
 // Kernels. For programs made of scalar ops plus two-valued discrete plates and Normal observation
 // plates (BASELINE configs[3], examples/mixture_models.rs:77-111) the three per-particle steps are
-// ONE kernel each: prior draw + score (k_smcx_prior, k_smcx_score), propose + score + accept
-// (k_smcx_move), ancestor search + state copy (k_smcx_gather). Other programs run the generic
-// scoring engine (fc_score.cu) on the same container.
+// ONE kernel each: prior draw + statistics + score (k_smcx_prior), propose + score + accept
+// (k_smcx_move; with the statistics the proposal is scored in O(1) from a by-value flattened program),
+// ancestor search + state copy (k_smcx_gather). Other programs run the generic scoring engine
+// (fc_score.cu) on the same container.
 //
 // Sharding. One process per GPU; the population buffers and a small mailbox live in one
 // cudaIpc-exported slab per rank. Every exchange step of the tempering loop happens ON THE DEVICE
