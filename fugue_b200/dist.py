@@ -12,7 +12,6 @@ The R-hat / ESS part of this file is HOST logic on small arrays plus collectives
 numbers it combines come from the CUDA library (fc_diag_partials).
 It never imports the oracle and has no CPU compute fallback for the device kernels.
 """
-import math
 import numpy as np
 import torch
 import torch.distributed as dist

@@ -1,6 +1,8 @@
-import sys, time, ctypes as C
-sys.path.insert(0, "/root/repo")
-import numpy as np, torch
+"""Where the SMC end-to-end time goes (program build, session + prior pass, ladder, copy-out to pinned host memory, close):
+python tools/smc_e2e_probe.py  (one B200, C4 at 2^24 particles)."""
+import os, sys, time, ctypes as C
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
 from fugue_b200 import api, models
 n = 1 << 24
 cfg = api.SMCConfig(rejuvenation_steps=1)
