@@ -353,16 +353,21 @@ int32_t fc_split_rhat_dev_noalloc(const double* d_draws, size_t S, size_t d, siz
 //   h_seg_mean, h_seg_ss : [d][nseg*C]  (nseg = 2 if S >= 2 else 1; order c0h0, c0h1, c1h0, ...)
 //   h_cmean              : [d][C]
 //   h_lagsum             : [d][max_lag+1], max_lag = min(S-1, 2048)   (NULL or S < 4: skipped)
-int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean, double* h_seg_ss, double* h_cmean, double* h_lagsum) {
+static int32_t diag_partials_any(const double* draws, bool x_is_dev, size_t S, size_t d, size_t C, double* h_seg_mean, double* h_seg_ss, double* h_cmean, double* h_lagsum) {
   using namespace fc;
   if (d == 0 || C == 0 || S == 0) return FC_OK;
+  if (!draws) { set_error("draws is NULL"); return FC_ERR_INVALID_ARGUMENT; }
   if (!g_diag_stream) FC_CUDA(cudaStreamCreateWithFlags(&g_diag_stream, cudaStreamNonBlocking));
   cudaStream_t st = g_diag_stream;
   DiagWork W;
   size_t n = S * d * C;
-  FC_CUDA(W.x.reserve(n));
-  FC_CUDA(cudaMemcpyAsync(W.x.p, h_draws, n * 8, cudaMemcpyHostToDevice, st));
-  Draws D{W.x.p, (int64_t)S, (int64_t)d, (int64_t)C};
+  const double* x = draws;
+  if (!x_is_dev) {
+    FC_CUDA(W.x.reserve(n));
+    FC_CUDA(cudaMemcpyAsync(W.x.p, draws, n * 8, cudaMemcpyHostToDevice, st));
+    x = W.x.p;
+  }
+  Draws D{x, (int64_t)S, (int64_t)d, (int64_t)C};
   const unsigned cbx = (unsigned)cdiv((int64_t)C, 128);
   int nseg = (S / 2 > 0) ? 2 : 1;
   int64_t m = (int64_t)nseg * C;
@@ -389,5 +394,12 @@ int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, do
     FC_CUDA(cudaStreamSynchronize(st));
   }
   return FC_OK;
+}
+int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean, double* h_seg_ss, double* h_cmean, double* h_lagsum) {
+  return diag_partials_any(h_draws, false, S, d, C, h_seg_mean, h_seg_ss, h_cmean, h_lagsum);
+}
+// the same on draws resident in HBM (fc_hmc_run_dev / fc_hmc_sample_dev): read in place, only the partials cross to the host
+int32_t fc_diag_partials_dev(const double* d_draws, size_t S, size_t d, size_t C, double* h_seg_mean, double* h_seg_ss, double* h_cmean, double* h_lagsum) {
+  return diag_partials_any(d_draws, true, S, d, C, h_seg_mean, h_seg_ss, h_cmean, h_lagsum);
 }
 }

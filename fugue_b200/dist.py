@@ -126,20 +126,30 @@ def combine_ess(cmean, lagsum, n_draws):
 
 
 def diagnostics_sharded(draws_local):
-    """R-hat and ESS over ALL ranks' chains. draws_local [S][d][C_local] (host array of this
-    rank's draws). Per-rank partials come from the CUDA library (fc_diag_partials)."""
+    """R-hat and ESS over ALL ranks' chains. draws_local [S][d][C_local]: this rank's draws, a host array or a
+    CUDA float64 tensor (api.hmc_chain_dev / HmcSession.sample_dev: read in place in HBM). Per-rank partials come
+    from the CUDA library (fc_diag_partials / fc_diag_partials_dev)."""
     from . import api
     import ctypes as C
-    x = np.ascontiguousarray(draws_local, dtype=np.float64)
-    S, d, Cn = x.shape
+    on_device = hasattr(draws_local, "is_cuda") and draws_local.is_cuda
+    if on_device:
+        if draws_local.dim() != 3 or str(draws_local.dtype) != "torch.float64" or not draws_local.is_contiguous():
+            raise ValueError("diagnostics_sharded: a device tensor must be contiguous float64 [S][d][C]")
+        S, d, Cn = (int(v) for v in draws_local.shape)
+        ptr = draws_local.data_ptr()
+        fn = api.lib.fc_diag_partials_dev
+    else:
+        x = np.ascontiguousarray(draws_local, dtype=np.float64)
+        S, d, Cn = x.shape
+        ptr = x.ctypes.data
+        fn = api.lib.fc_diag_partials
     nseg = 2 if S // 2 > 0 else 1
     max_lag = min(S - 1, 2048)
     seg_mean, seg_ss = np.zeros((d, nseg * Cn)), np.zeros((d, nseg * Cn))
     cmean, lagsum = np.zeros((d, Cn)), np.zeros((d, max_lag + 1))
-    fn = api.lib.fc_diag_partials
     fn.restype = C.c_int32
     fn.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-    api.check(fn(x.ctypes.data, S, d, Cn, seg_mean.ctypes.data, seg_ss.ctypes.data, cmean.ctypes.data,
+    api.check(fn(ptr, S, d, Cn, seg_mean.ctypes.data, seg_ss.ctypes.data, cmean.ctypes.data,
                  lagsum.ctypes.data if S >= 4 else None))
     rhat = combine_rhat(seg_mean, seg_ss, S // 2 if nseg == 2 else S)
     if S >= 4:

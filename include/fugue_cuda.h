@@ -421,6 +421,9 @@ int32_t fc_split_rhat_dev_noalloc(const double* d_draws, size_t S, size_t d, siz
  * per lag [d][min(S-1,2048)+1]. Combined across ranks by all-reduce (fugue_b200/dist.py). */
 int32_t fc_diag_partials(const double* h_draws, size_t S, size_t d, size_t C, double* h_seg_mean,
                          double* h_seg_ss, double* h_cmean, double* h_lagsum);
+/* ... on draws resident in HBM (device pointer, the fc_hmc_run_dev layout): read in place. */
+int32_t fc_diag_partials_dev(const double* d_draws, size_t S, size_t d, size_t C, double* h_seg_mean,
+                             double* h_seg_ss, double* h_cmean, double* h_lagsum);
 
 /* switches for A/B parity tests: "nb_plain" = 1: next_beta evaluates every midpoint of the reference's
  * 64-step bisection (no search phase); "smc_generic" = 1: SMC sessions created afterwards run on the

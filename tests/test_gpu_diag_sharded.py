@@ -38,6 +38,8 @@ def _worker(rank, ws, port, q):
     lo, hi = D.shard_range(C_TOTAL, rank, ws)
     draws = _run(lo, hi - lo)
     dg = D.diagnostics_sharded(draws)
+    dg_dev = D.diagnostics_sharded(torch.from_numpy(draws).cuda())  # the same draws resident in HBM (fc_diag_partials_dev)
+    assert np.array_equal(dg["r_hat"], dg_dev["r_hat"]) and np.array_equal(dg["ess"], dg_dev["ess"])
     q.put((rank, dict(lo=lo, hi=hi, draws=draws, r_hat=dg["r_hat"], ess=dg["ess"])))
     dist.barrier()
     dist.destroy_process_group()
